@@ -1,0 +1,284 @@
+"""CPU oracle for the ORB front-end hot path — TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs may import this package.  The product package (orb_slam3_vio_fixes_b200) never does.
+
+`oracle.lib()` returns a ctypes handle on liborb_oracle.so (built by `make -C oracle`),
+`oracle.Extractor` wraps the restated ORBextractor, and the free functions wrap the
+individually pinned primitives.  See orb_oracle.cpp for the reference file:line map.
+"""
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+_DIR = Path(__file__).resolve().parent
+_SO = _DIR / "liborb_oracle.so"
+_lib = None
+
+# cv::KeyPoint layout, 28 bytes
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+RES_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i2"), ("second_dist", "<i2"),
+                      ("best_level", "i1"), ("second_level", "i1"), ("pad", "<i2")])
+STRICT_FP = 1
+
+
+def build(force=False):
+    src = _DIR / "orb_oracle.cpp"
+    if force or not _SO.exists() or _SO.stat().st_mtime < src.stat().st_mtime:
+        subprocess.check_call(["make", "-C", str(_DIR), "-B" if force else "-s"],
+                              stdout=subprocess.DEVNULL)
+    return _SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not _SO.exists():
+            build()
+        L = C.CDLL(str(_SO))
+        L.oracle_create.restype = C.c_void_p
+        L.oracle_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int]
+        L.oracle_destroy.argtypes = [C.c_void_p]
+        L.oracle_extract.restype = C.c_int
+        L.oracle_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int,
+                                     C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.oracle_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+        L.oracle_level_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.oracle_get_pyramid.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_int]
+        L.oracle_level_keypoints.restype = C.c_int
+        L.oracle_level_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.oracle_resize_linear.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int]
+        L.oracle_gaussian_blur7.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.oracle_border101.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.oracle_fast_atan2.restype = C.c_float
+        L.oracle_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.oracle_fast_atan2_array.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.oracle_fast.restype = C.c_int
+        L.oracle_fast.argtypes = [C.c_void_p] + [C.c_int] * 7 + [C.c_void_p, C.c_int]
+        L.oracle_distribute.restype = C.c_int
+        L.oracle_distribute.argtypes = [C.c_void_p] + [C.c_int] * 6 + [C.c_void_p]
+        L.oracle_sincos_deg.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_long]
+        L.oracle_sincos_bits.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+        L.oracle_descriptor_distance.restype = C.c_int
+        L.oracle_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p]
+        L.oracle_argmin2_csr.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_int, C.c_void_p]
+        L.oracle_grid_queries.restype = C.c_int
+        L.oracle_grid_queries.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.oracle_stereo_matches.restype = C.c_int
+        L.oracle_stereo_matches.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                            C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_void_p, C.c_float, C.c_float,
+                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.oracle_knn2_dense.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.oracle_bench_extract.restype = C.c_double
+        L.oracle_bench_extract.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                           C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                           C.POINTER(C.c_int)]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Extractor:
+    """Restated ORB_SLAM3::ORBextractor (ctor args as ORBextractor.h:49-50)."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, flags=0):
+        self.L = lib()
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+        self.h = self.L.oracle_create(nfeatures, scale_factor, nlevels, ini_th, min_th, flags)
+        sf, inv, s2, is2 = (np.zeros(nlevels, np.float32) for _ in range(4))
+        nf = np.zeros(nlevels, np.int32)
+        um = np.zeros(16, np.int32)
+        self.L.oracle_tables(self.h, _p(sf), _p(inv), _p(s2), _p(is2), _p(nf), _p(um))
+        self.scale_factors, self.inv_scale_factors = sf, inv
+        self.level_sigma2, self.inv_level_sigma2 = s2, is2
+        self.features_per_level, self.umax = nf, um
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.oracle_destroy(self.h)
+            self.h = None
+
+    def extract(self, img, lap=(0, 0)):
+        """operator(): returns (keypoints[KP_DTYPE], descriptors[n,32] u8, monoIndex)."""
+        img = np.ascontiguousarray(img, np.uint8)
+        hgt, w = img.shape
+        cap = self.nfeatures + 3 * self.nlevels + 64
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int(0)
+        mono = self.L.oracle_extract(self.h, _p(img), w, hgt, w, lap[0], lap[1], _p(kps), _p(desc), cap,
+                                     C.byref(n))
+        assert mono != -2, "capacity"
+        return kps[:n.value].copy(), desc[:n.value].copy(), mono
+
+    def level_size(self, level):
+        w, h = C.c_int(), C.c_int()
+        assert self.L.oracle_level_size(self.h, level, C.byref(w), C.byref(h)) == 0
+        return w.value, h.value
+
+    def pyramid(self, level, with_border=False):
+        w, h = self.level_size(level)
+        if with_border:
+            w, h = w + 38, h + 38
+        out = np.zeros((h, w), np.uint8)
+        self.L.oracle_get_pyramid(self.h, level, _p(out), w, int(with_border))
+        return out
+
+    def level_keypoints(self, level, stage):
+        n = self.L.oracle_level_keypoints(self.h, level, stage, None, 0)
+        out = np.zeros(n, KP_DTYPE)
+        if n:
+            self.L.oracle_level_keypoints(self.h, level, stage, _p(out), n)
+        return out
+
+
+def resize_linear(src, dw, dh):
+    src = np.ascontiguousarray(src, np.uint8)
+    out = np.zeros((dh, dw), np.uint8)
+    lib().oracle_resize_linear(_p(src), src.shape[1], src.shape[0], _p(out), dw, dh)
+    return out
+
+
+def gaussian_blur7(src):
+    src = np.ascontiguousarray(src, np.uint8)
+    out = np.zeros_like(src)
+    lib().oracle_gaussian_blur7(_p(src), src.shape[1], src.shape[0], _p(out))
+    return out
+
+
+def border101(src, b=19):
+    src = np.ascontiguousarray(src, np.uint8)
+    out = np.zeros((src.shape[0] + 2 * b, src.shape[1] + 2 * b), np.uint8)
+    lib().oracle_border101(_p(src), src.shape[1], src.shape[0], b, _p(out))
+    return out
+
+
+def fast_atan2(y, x):
+    y = np.ascontiguousarray(y, np.float32)
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.zeros_like(y)
+    lib().oracle_fast_atan2_array(_p(y), _p(x), _p(out), y.size)
+    return out
+
+
+def fast(img, roi, threshold):
+    """cv::FAST(img[y0:y1, x0:x1], th, nms=True) → int array [n,3] (x, y, score), ROI-relative."""
+    img = np.ascontiguousarray(img, np.uint8)
+    x0, y0, x1, y1 = roi
+    cap = max(1, (x1 - x0) * (y1 - y0))
+    out = np.zeros((cap, 3), np.int32)
+    n = lib().oracle_fast(_p(img), img.shape[1], img.shape[0], x0, y0, x1, y1, threshold, _p(out), cap)
+    return out[:n].copy()
+
+
+def distribute(xyr, min_x, max_x, min_y, max_y, n_target):
+    xyr = np.ascontiguousarray(xyr, np.float32).reshape(-1, 3)
+    out = np.zeros((xyr.shape[0] + 8, 3), np.float32)
+    n = lib().oracle_distribute(_p(xyr), xyr.shape[0], min_x, max_x, min_y, max_y, n_target, _p(out))
+    return out[:n].copy()
+
+
+def sincos_deg(angle_deg):
+    a = np.ascontiguousarray(angle_deg, np.float32)
+    c = np.zeros_like(a)
+    s = np.zeros_like(a)
+    lib().oracle_sincos_deg(_p(a), _p(c), _p(s), a.size)
+    return c, s
+
+
+def sincos_bits(lo, count, stride=1):
+    c = np.zeros(count, np.float32)
+    s = np.zeros(count, np.float32)
+    lib().oracle_sincos_bits(lo, count, stride, _p(c), _p(s))
+    return c, s
+
+
+def descriptor_distance(a, b):
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    return lib().oracle_descriptor_distance(_p(a), _p(b))
+
+
+def argmin2_csr(q, r, cand_off, cand_idx, ref_level=None, tie_rule=0):
+    q = np.ascontiguousarray(q, np.uint8)
+    r = np.ascontiguousarray(r, np.uint8)
+    cand_off = np.ascontiguousarray(cand_off, np.int32)
+    cand_idx = np.ascontiguousarray(cand_idx, np.int32)
+    lv = None if ref_level is None else np.ascontiguousarray(ref_level, np.int8)
+    out = np.zeros(q.shape[0], RES_DTYPE)
+    lib().oracle_argmin2_csr(_p(q), q.shape[0], _p(r), r.shape[0], _p(cand_off), _p(cand_idx),
+                             None if lv is None else _p(lv), tie_rule, _p(out))
+    return out
+
+
+def grid_queries(kps, bounds, qx, qy, qr, qmin, qmax):
+    """AssignFeaturesToGrid + GetFeaturesInArea → (cand_off[nq+1], cand_idx)."""
+    kps = np.ascontiguousarray(kps)
+    qx, qy, qr = (np.ascontiguousarray(v, np.float32) for v in (qx, qy, qr))
+    qmin, qmax = (np.ascontiguousarray(v, np.int32) for v in (qmin, qmax))
+    nq = qx.size
+    off = np.zeros(nq + 1, np.int32)
+    cap = max(1, nq * 64)
+    while True:
+        idx = np.zeros(cap, np.int32)
+        tot = lib().oracle_grid_queries(_p(kps), kps.size, *[float(b) for b in bounds], _p(qx), _p(qy), _p(qr),
+                                        _p(qmin), _p(qmax), nq, _p(off), _p(idx), cap)
+        if tot <= cap:
+            return off, idx[:tot].copy()
+        cap = tot
+
+
+def stereo_matches(kps_l, desc_l, kps_r, desc_r, scale_factors, inv_scale_factors, pyr_l, pyr_r, mb, mbf):
+    nl, nr = kps_l.size, kps_r.size
+    nlev = len(pyr_l)
+    pl = [np.ascontiguousarray(p, np.uint8) for p in pyr_l]
+    pr = [np.ascontiguousarray(p, np.uint8) for p in pyr_r]
+    PL = (C.c_void_p * nlev)(*[p.ctypes.data for p in pl])
+    PR = (C.c_void_p * nlev)(*[p.ctypes.data for p in pr])
+    pw = np.array([p.shape[1] for p in pl], np.int32)
+    ph = np.array([p.shape[0] for p in pl], np.int32)
+    bi = np.zeros(nl, np.int32)
+    bd = np.zeros(nl, np.int32)
+    ur = np.zeros(nl, np.float32)
+    dp = np.zeros(nl, np.float32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    isf = np.ascontiguousarray(inv_scale_factors, np.float32)
+    kept = lib().oracle_stereo_matches(_p(np.ascontiguousarray(kps_l)), _p(np.ascontiguousarray(desc_l)), nl,
+                                       _p(np.ascontiguousarray(kps_r)), _p(np.ascontiguousarray(desc_r)), nr,
+                                       _p(sf), _p(isf), nlev, PL, PR, _p(pw), _p(ph), mb, mbf,
+                                       _p(bi), _p(bd), _p(ur), _p(dp))
+    return bi, bd, ur, dp, kept
+
+
+def knn2_dense(q, r):
+    q = np.ascontiguousarray(q, np.uint8)
+    r = np.ascontiguousarray(r, np.uint8)
+    idx = np.zeros((q.shape[0], 2), np.int32)
+    dist = np.zeros((q.shape[0], 2), np.int32)
+    lib().oracle_knn2_dense(_p(q), q.shape[0], _p(r), r.shape[0], _p(idx), _p(dist))
+    return idx, dist
+
+
+def bench_extract(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, lap, threads, flags=0):
+    """Times the oracle over frames[n,h,w]; returns (seconds, total keypoints)."""
+    frames = np.ascontiguousarray(frames, np.uint8)
+    n, h, w = frames.shape
+    tot = C.c_int(0)
+    sec = lib().oracle_bench_extract(nfeatures, scale_factor, nlevels, ini_th, min_th, flags, _p(frames), n, w, h,
+                                     lap[0], lap[1], threads, C.byref(tot))
+    return sec, tot.value
+
+
+def host_threads():
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
