@@ -1,0 +1,191 @@
+/*
+ * orbx.h — C ABI of the B200-native ORB front-end (liborbx.so).
+ *
+ * This is the drop-in boundary for ORB-SLAM3's per-frame hot path
+ * (vdoom/ORB_SLAM3_VIO_FIXES).  The reference has no FFI layer: the boundary there is two C++
+ * classes.  Each entry point below names the reference interface it replaces (file:line in
+ * the reference tree); include/orbx_compat/ORBextractor.h and ORBmatcher_core.h put the
+ * reference's own C++ signatures back on top of these calls.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 (ORBX_OK) or a
+ * negative ORBX_E_* code; nothing throws, nothing aborts.  "d_" pointers are CUDA device
+ * pointers, `stream` is a cudaStream_t passed as void* (NULL = the handle's own stream).
+ * A handle is single-caller (like an ORBextractor instance, ORBextractor.h:83 mutable
+ * mvImagePyramid); distinct handles may be used concurrently from different threads, as
+ * Frame.cc:122-125 does for the left/right extractors.
+ */
+#ifndef ORBX_H_
+#define ORBX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBX_OK 0
+#define ORBX_E_INVALID (-1)     /* bad argument / unsupported geometry                     */
+#define ORBX_E_CUDA (-2)        /* CUDA runtime error (sticky: destroy and recreate)        */
+#define ORBX_E_CAPACITY (-3)    /* caller's output buffer too small                         */
+#define ORBX_E_NOMEM (-4)       /* device allocation failed                                 */
+#define ORBX_E_EMPTY (-5)       /* empty image: operator() returns -1 (ORBextractor.cc:1090) */
+#define ORBX_E_NODEVICE (-6)    /* no CUDA device / driver: there is no CPU fallback        */
+
+#define ORBX_MAX_LEVELS 12
+
+/* flags */
+#define ORBX_FLAG_STRICT_FP 1u  /* evaluate GET_VALUE (ORBextractor.cc:117-119) uncontracted
+                                   (mul,mul,add) instead of the FMA form g++ -O3 -march=native
+                                   emits for the reference; default = as compiled (FMA).     */
+
+/* cv::KeyPoint memory layout, 28 bytes (what std::vector<cv::KeyPoint> holds). */
+typedef struct orbx_keypoint {
+  float x, y;      /* pt, level-0 pixel coordinates                                  */
+  float size;      /* (int)(31*scale[octave]), ORBextractor.cc:880                   */
+  float angle;     /* degrees in [0,360), IC_Angle + cv::fastAtan2, :76-103          */
+  float response;  /* FAST score                                                     */
+  int32_t octave;  /* pyramid level                                                  */
+  int32_t class_id;/* -1                                                             */
+} orbx_keypoint;
+
+/* Constructor arguments of ORBextractor (ORBextractor.h:49-50) plus the plan geometry. */
+typedef struct orbx_config {
+  int32_t nfeatures;     /* ORBextractor.nFeatures                                       */
+  float scale_factor;    /* ORBextractor.scaleFactor                                     */
+  int32_t nlevels;       /* ORBextractor.nLevels (<= ORBX_MAX_LEVELS)                    */
+  int32_t ini_th_fast;   /* ORBextractor.iniThFAST                                       */
+  int32_t min_th_fast;   /* ORBextractor.minThFAST                                       */
+  int32_t width, height; /* frame size the handle is planned for                         */
+  int32_t max_batch;     /* frames per orbx_extract_batch_* call (>=1)                   */
+  int32_t device;        /* CUDA device ordinal                                          */
+  uint32_t flags;        /* ORBX_FLAG_*                                                  */
+} orbx_config;
+
+typedef struct orbx_extractor_s* orbx_handle;
+
+/* Replaces ORBextractor::ORBextractor (ORBextractor.cc:409-469): builds the scale tables,
+ * per-level feature quotas, umax, resize coefficient tables and FAST cell grid for one frame
+ * size, and allocates every device buffer once (no allocation on the per-frame path). */
+int orbx_create(const orbx_config* cfg, orbx_handle* out);
+void orbx_destroy(orbx_handle h);
+
+/* Upper bound of keypoints one frame can return: nfeatures + 3*nlevels. */
+int orbx_max_keypoints(orbx_handle h);
+
+/* Replaces ORBextractor::operator() (ORBextractor.h:57-59, ORBextractor.cc:1086-1168) for one
+ * frame in HOST memory: H2D copy, all kernels, D2H copy, synchronous.  `lap0/lap1` is
+ * vLappingArea; *mono_index receives operator()'s return value.  `kps`/`desc` (n x 32 bytes,
+ * row-major like the CV_8U descriptor Mat) must hold `capacity` entries. */
+int orbx_extract(orbx_handle h, const uint8_t* img, int width, int height, size_t stride,
+                 int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int capacity,
+                 int* n_out, int* mono_index);
+
+/* Batched operator() on frames resident in device memory (throughput path).  Frame f starts
+ * at d_imgs + f*frame_stride, rows are `pitch` bytes apart.  Outputs are device arrays:
+ * d_kps[batch][capacity], d_desc[batch][capacity][32], d_n_out[batch], d_mono_index[batch].
+ * Asynchronous on `stream`.  The input must stay alive until the stream has drained (level 0
+ * of the pyramid aliases it). */
+int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch,
+                              size_t frame_stride, int batch, int lap0, int lap1,
+                              orbx_keypoint* d_kps, uint8_t* d_desc, int capacity,
+                              int32_t* d_n_out, int32_t* d_mono_index, void* stream);
+
+/* Same through HOST buffers (pinned for full speed): copies the batch in, runs, copies the
+ * results out, synchronises.  Frames are tightly packed width*height. */
+int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int lap0, int lap1,
+                            orbx_keypoint* kps, uint8_t* desc, int capacity, int32_t* n_out,
+                            int32_t* mono_index);
+
+/* The "GetPyramid" surface: replaces reads of the public field mvImagePyramid
+ * (ORBextractor.h:83; Frame.cc:818,908,918,923).  Copies level `level` of frame `frame` of
+ * the last call to host memory; with_border=1 reproduces the (w+38)x(h+38) parent buffer of
+ * the reference's ROI (19-px BORDER_REFLECT_101 ring, ORBextractor.cc:1185-1191). */
+int orbx_get_pyramid(orbx_handle h, int frame, int level, uint8_t* dst, size_t dst_stride,
+                     int with_border);
+/* Device view of the same level (border-free). */
+int orbx_pyramid_device(orbx_handle h, int frame, int level, const uint8_t** d_ptr,
+                        size_t* pitch, int* width, int* height);
+int orbx_level_size(orbx_handle h, int level, int* width, int* height);
+
+/* Replaces GetScaleFactors/GetInverseScaleFactors/GetScaleSigmaSquares/
+ * GetInverseScaleSigmaSquares (ORBextractor.h:61-81); arrays of nlevels floats.  Any pointer
+ * may be NULL.  features_per_level = mnFeaturesPerLevel (ORBextractor.cc:434-445). */
+int orbx_get_scale_tables(orbx_handle h, float* scale, float* inv_scale, float* sigma2,
+                          float* inv_sigma2, int32_t* features_per_level);
+
+/* Introspection for the parity tests: per-level intermediate keypoint lists of frame `frame`
+ * of the last call.  stage 0 = FAST candidates in DistributeOctTree input order (x,y relative
+ * to (16,16), response); stage 1 = after the octree, in list order (level coordinates).
+ * Fills up to cap entries of (x, y, response) int32 triples; returns the count in *n. */
+int orbx_debug_level_keypoints(orbx_handle h, int frame, int level, int stage, int32_t* xyr,
+                               int cap, int* n);
+
+/* ----------------------------------------------------------------------------------------
+ * Matcher cores.  ORBmatcher::DescriptorDistance (ORBmatcher.h:43, ORBmatcher.cc:2058-2074)
+ * for a single pair stays a host inline (include/orbx_compat/ORBmatcher_core.h); the
+ * library exports the batched candidate-scoring loops that sit behind the Search* family.
+ * Descriptors are rows of 32 bytes (the reference's N x 32 CV_8U Mat).
+ * -------------------------------------------------------------------------------------- */
+typedef struct orbm_result {
+  int32_t best_idx;     /* reference index of the best candidate, -1 if none            */
+  int16_t best_dist;    /* its Hamming distance (256 if none)                           */
+  int16_t second_dist;  /* second best distance (256 if none)                           */
+  int8_t best_level;    /* octave of best (-1 if none)                                  */
+  int8_t second_level;  /* octave of second best (-1 if none)                           */
+  int16_t pad;
+} orbm_result;
+
+#define ORBM_TIE_FIRST_MIN 0 /* `dist<bestDist` loops: ORBmatcher.cc:84-120, 273-325, 1743-1768 */
+#define ORBM_TIE_LAST_MIN 1  /* `dist<=bestDist`: SearchForTriangulation, ORBmatcher.cc:1017     */
+
+/* Scores explicit candidate lists (CSR: d_cand_off[nq+1], d_cand_idx in the order the
+ * reference loop visits them).  d_ref_level[nr] = octave of each reference keypoint (may be
+ * NULL).  Result per query as the reference's bestDist/bestIdx/bestLevel/bestDist2/
+ * bestLevel2 after the loop. */
+int orbm_argmin2_csr(const uint8_t* d_q, int nq, const uint8_t* d_r, int nr,
+                     const int32_t* d_cand_off, const int32_t* d_cand_idx,
+                     const int8_t* d_ref_level, int tie_rule, orbm_result* d_out, void* stream);
+
+/* Frame::AssignFeaturesToGrid (Frame.cc:385-416) on device: bins n keypoints into the 64x48
+ * grid over [min_x,max_x) x [min_y,max_y); d_cell_off[64*48+1] / d_cell_idx[n] form a CSR in
+ * (column-major cell, insertion) order — the order GetFeaturesInArea walks.  Batched: frame f
+ * uses d_kps + f*kp_stride, d_n[f] keypoints. */
+int orbm_grid_build(const orbx_keypoint* d_kps, const int32_t* d_n, int kp_stride, int batch,
+                    float min_x, float max_x, float min_y, float max_y, int32_t* d_cell_off,
+                    int32_t* d_cell_idx, void* stream);
+
+/* Fused Frame::GetFeaturesInArea (Frame.cc:657-723) + best/second scoring loop: for each
+ * query (x, y, radius r, octave band [min_level,max_level], descriptor) walks the grid cells
+ * in the reference's order, gates candidates and scores them without materialising the list.
+ * Queries of frame f: d_q* + f*q_stride, d_nq[f] of them; references: frame f's keypoints. */
+int orbm_search_area(const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n,
+                     int kp_stride, const int32_t* d_cell_off, const int32_t* d_cell_idx,
+                     float min_x, float max_x, float min_y, float max_y, const float* d_qx,
+                     const float* d_qy, const float* d_qr, const int8_t* d_qmin_level,
+                     const int8_t* d_qmax_level, const uint8_t* d_qdesc, const int32_t* d_nq,
+                     int q_stride, int batch, int tie_rule, orbm_result* d_out, void* stream);
+
+/* Hamming stage of Frame::ComputeStereoMatches (Frame.cc:811-894): per left keypoint the best
+ * right keypoint in its row band (|dy| within 2*scale[octR], |octave diff|<=1,
+ * uL-max_d <= uR <= uL), first minimum below TH_HIGH=100 wins, candidates visited in
+ * ascending right index (the order vRowIndices is filled).  Batched over `batch` pairs. */
+int orbm_stereo_rowband(const orbx_keypoint* d_kps_l, const uint8_t* d_desc_l,
+                        const int32_t* d_n_l, const orbx_keypoint* d_kps_r,
+                        const uint8_t* d_desc_r, const int32_t* d_n_r, int kp_stride, int batch,
+                        const float* scale_factors_host, int nlevels, float max_d,
+                        int32_t* d_best_idx_r, int32_t* d_best_dist, void* stream);
+
+/* cv::BFMatcher(NORM_HAMMING).knnMatch(k=2) (Frame.cc:1144): all pairs, two best per query,
+ * ties to the lower reference index.  d_idx2/d_dist2 are [nq][2]. */
+int orbm_knn2_dense(const uint8_t* d_q, int nq, const uint8_t* d_r, int nr, int32_t* d_idx2,
+                    int32_t* d_dist2, void* stream);
+
+/* Library / build identification. */
+const char* orbx_version(void);
+const char* orbx_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H_ */

@@ -1,0 +1,95 @@
+"""ctypes binding of liborbx.so — the C ABI declared in include/orbx.h.
+
+There is no CPU fallback: if the library is missing or no CUDA device is present every
+compute entry point fails loudly (ORBX_E_NODEVICE / OSError).
+"""
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+PKG = Path(__file__).resolve().parent
+SO = PKG / "liborbx.so"
+
+ORBX_OK = 0
+ERRORS = {-1: "ORBX_E_INVALID", -2: "ORBX_E_CUDA", -3: "ORBX_E_CAPACITY", -4: "ORBX_E_NOMEM",
+          -5: "ORBX_E_EMPTY", -6: "ORBX_E_NODEVICE"}
+FLAG_STRICT_FP = 1
+TIE_FIRST_MIN, TIE_LAST_MIN = 0, 1
+MAX_LEVELS = 12
+GRID_COLS, GRID_ROWS = 64, 48
+
+# cv::KeyPoint layout (orbx_keypoint), 28 bytes
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+# orbm_result, 12 bytes
+RES_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i2"), ("second_dist", "<i2"),
+                      ("best_level", "i1"), ("second_level", "i1"), ("pad", "<i2")])
+
+# every symbol include/orbx.h declares (tests/test_abi.py checks the library exports them all)
+SYMBOLS = [
+    "orbx_create", "orbx_destroy", "orbx_max_keypoints", "orbx_extract", "orbx_extract_batch_device",
+    "orbx_extract_batch_host", "orbx_get_pyramid", "orbx_pyramid_device", "orbx_level_size",
+    "orbx_get_scale_tables", "orbx_debug_level_keypoints", "orbm_argmin2_csr", "orbm_grid_build",
+    "orbm_search_area", "orbm_stereo_rowband", "orbm_knn2_dense", "orbx_version", "orbx_last_error",
+]
+
+
+class OrbxConfig(C.Structure):
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
+                ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32), ("width", C.c_int32),
+                ("height", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32),
+                ("flags", C.c_uint32)]
+
+
+class OrbxError(RuntimeError):
+    def __init__(self, code, where):
+        self.code = code
+        msg = ""
+        try:
+            msg = lib().orbx_last_error().decode()
+        except Exception:
+            pass
+        super().__init__(f"{where}: {ERRORS.get(code, code)} {msg}")
+
+
+_lib = None
+
+
+def lib():
+    """Loads liborbx.so (building it first if the sources are newer).  Raises if absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not SO.exists():
+        from . import build as _b
+        _b.build()
+    L = C.CDLL(str(SO))
+    vp, i32, f32, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+    L.orbx_create.argtypes = [C.POINTER(OrbxConfig), C.POINTER(vp)]
+    L.orbx_destroy.argtypes = [vp]
+    L.orbx_destroy.restype = None
+    L.orbx_max_keypoints.argtypes = [vp]
+    L.orbx_extract.argtypes = [vp, vp, i32, i32, sz, i32, i32, vp, vp, i32, C.POINTER(i32), C.POINTER(i32)]
+    L.orbx_extract_batch_device.argtypes = [vp, vp, sz, sz, i32, i32, i32, vp, vp, i32, vp, vp, vp]
+    L.orbx_extract_batch_host.argtypes = [vp, vp, i32, i32, i32, vp, vp, i32, vp, vp]
+    L.orbx_get_pyramid.argtypes = [vp, i32, i32, vp, sz, i32]
+    L.orbx_pyramid_device.argtypes = [vp, i32, i32, C.POINTER(vp), C.POINTER(sz), C.POINTER(i32), C.POINTER(i32)]
+    L.orbx_level_size.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32)]
+    L.orbx_get_scale_tables.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.orbx_debug_level_keypoints.argtypes = [vp, i32, i32, i32, vp, i32, C.POINTER(i32)]
+    L.orbm_argmin2_csr.argtypes = [vp, i32, vp, i32, vp, vp, vp, i32, vp, vp]
+    L.orbm_grid_build.argtypes = [vp, vp, i32, i32, f32, f32, f32, f32, vp, vp, vp]
+    L.orbm_search_area.argtypes = [vp, vp, vp, i32, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp, vp,
+                                   i32, i32, i32, vp, vp]
+    L.orbm_stereo_rowband.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, vp, i32, f32, vp, vp, vp]
+    L.orbm_knn2_dense.argtypes = [vp, i32, vp, i32, vp, vp, vp]
+    L.orbx_version.restype = C.c_char_p
+    L.orbx_last_error.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def check(rc, where):
+    if rc != ORBX_OK:
+        raise OrbxError(rc, where)

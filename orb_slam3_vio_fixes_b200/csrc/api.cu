@@ -1,0 +1,348 @@
+// api.cu — the C ABI of include/orbx.h: handle management and the per-frame launch sequence
+// (ORBextractor::operator(), src/ORBextractor.cc:1086-1168).
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "../../include/orbx.h"
+#include "orbx_kernels.cuh"
+
+static thread_local char g_err[256] = "";
+static void set_err(const char* what, cudaError_t e) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", what, e == cudaSuccess ? "" : cudaGetErrorString(e));
+}
+#define CU(call)                                  \
+  do {                                            \
+    cudaError_t e_ = (call);                      \
+    if (e_ != cudaSuccess) {                      \
+      set_err(#call, e_);                         \
+      return e_ == cudaErrorMemoryAllocation ? ORBX_E_NOMEM : ORBX_E_CUDA; \
+    }                                             \
+  } while (0)
+
+struct orbx_extractor_s {
+  orbx_config cfg;
+  OrbxPlan plan;
+  DevPlan dplan;
+  int device;
+  cudaStream_t stream;
+  // device buffers
+  uint8_t* arena = nullptr;
+  OrbxTap *xtaps = nullptr, *ytaps = nullptr;
+  int32_t* cell_cnt = nullptr;
+  uint32_t* cand = nullptr;
+  uint32_t* gkeys = nullptr;
+  int16_t* glabels = nullptr;
+  uint32_t* sel = nullptr;
+  int32_t* sel_cnt = nullptr;
+  int32_t* dst = nullptr;
+  int32_t* status = nullptr;
+  // outputs of the host-pointer entry points
+  OrbxKeyPointDev* o_kps = nullptr;
+  uint8_t* o_desc = nullptr;
+  int32_t *o_n = nullptr, *o_mono = nullptr;
+  uint8_t* border_tmp = nullptr;
+  // octree launch geometry
+  size_t oct_smem;
+  int oct_smem_keys, oct_node_cap, oct_max_cells;
+  // state of the last call
+  Level0 last_l0;
+  int last_batch = 0;
+};
+
+static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
+  memset(D, 0, sizeof(*D));
+  D->nlevels = P.nlevels; D->total_cells = P.total_cells; D->kp_total_cap = P.kp_total_cap;
+  D->ini_th = P.ini_th; D->min_th = P.min_th; D->cand_total = P.cand_total; D->arena_bytes = P.arena_bytes;
+  for (int i = 0; i < 16; i++) D->umax[i] = P.umax[i];
+  for (int l = 0; l < P.nlevels; l++) {
+    const OrbxLevel& s = P.lv[l];
+    DevLevel& d = D->lv[l];
+    d.w = s.w; d.h = s.h; d.pitch = s.pitch; d.nCols = s.nCols; d.nRows = s.nRows; d.wCell = s.wCell;
+    d.hCell = s.hCell; d.cell_base = s.cell_base; d.cell_cap = s.cell_cap; d.nfeat = s.nfeat;
+    d.kp_base = s.kp_base; d.kp_cap = s.kp_cap; d.kp_max = s.kp_max; d.nIni = s.nIni; d.hX = s.hX;
+    d.scale = s.scale; d.patch_size = s.patch_size; d.xtab = s.xtab; d.ytab = s.ytab; d.offset = s.offset;
+    d.cand_base = s.cand_base;
+  }
+}
+
+extern "C" {
+
+const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }
+const char* orbx_last_error(void) { return g_err; }
+
+void orbx_destroy(orbx_handle h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaFree(h->arena); cudaFree(h->xtaps); cudaFree(h->ytaps); cudaFree(h->cell_cnt); cudaFree(h->cand);
+  cudaFree(h->gkeys); cudaFree(h->glabels); cudaFree(h->sel); cudaFree(h->sel_cnt); cudaFree(h->dst);
+  cudaFree(h->status); cudaFree(h->o_kps); cudaFree(h->o_desc); cudaFree(h->o_n); cudaFree(h->o_mono);
+  cudaFree(h->border_tmp);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+int orbx_create(const orbx_config* cfg, orbx_handle* out) {
+  if (!cfg || !out) return ORBX_E_INVALID;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    set_err("no CUDA device (this library has no CPU fallback)", e);
+    return ORBX_E_NODEVICE;
+  }
+  if (cfg->device < 0 || cfg->device >= ndev || cfg->max_batch < 1) return ORBX_E_INVALID;
+  if (cfg->width > 4095 || cfg->height > 4095) { set_err("frame larger than 4095 px", cudaSuccess); return ORBX_E_INVALID; }
+  orbx_extractor_s* h = new (std::nothrow) orbx_extractor_s();
+  if (!h) return ORBX_E_NOMEM;
+  h->cfg = *cfg;
+  h->device = cfg->device;
+  h->stream = nullptr;
+  std::vector<OrbxTap> xt, yt;
+  if (orbx_build_plan(cfg->nfeatures, cfg->scale_factor, cfg->nlevels, cfg->ini_th_fast, cfg->min_th_fast,
+                      cfg->width, cfg->height, &h->plan, &xt, &yt) != 0) {
+    set_err("unsupported geometry (level smaller than one 35-px cell, portrait aspect, or exact 2x scale)",
+            cudaSuccess);
+    delete h;
+    return ORBX_E_INVALID;
+  }
+  const OrbxPlan& P = h->plan;
+  int node_cap = 0, max_cells = 0;
+  for (int l = 0; l < P.nlevels; l++) {
+    if (P.lv[l].nIni > 64) { delete h; set_err("aspect ratio > 64", cudaSuccess); return ORBX_E_INVALID; }
+    node_cap = node_cap > 2 * P.lv[l].kp_max + 8 ? node_cap : 2 * P.lv[l].kp_max + 8;
+    const int nc = P.lv[l].nCols * P.lv[l].nRows;
+    max_cells = max_cells > nc ? max_cells : nc;
+  }
+  if (node_cap > 32000) { delete h; set_err("nfeatures too large for 16-bit node ids", cudaSuccess); return ORBX_E_INVALID; }
+  fill_devplan(P, &h->dplan);
+  h->oct_node_cap = node_cap;
+  h->oct_max_cells = max_cells;
+  // keys that fit next to the node pool in <= ~96 KB of shared memory; larger levels spill to HBM
+  {
+    const size_t fixed = orbx_octree_smem_bytes(0, node_cap, max_cells);
+    const size_t budget = 96 * 1024;
+    long long keys = fixed < budget ? (long long)(budget - fixed) / 6 : 0;
+    if (keys > 8192) keys = 8192;
+    h->oct_smem_keys = (int)(keys & ~7LL);
+    h->oct_smem = orbx_octree_smem_bytes(h->oct_smem_keys, node_cap, max_cells);
+    if (h->oct_smem > 220 * 1024) { delete h; set_err("octree shared memory", cudaSuccess); return ORBX_E_INVALID; }
+  }
+  const long long B = cfg->max_batch;
+#define ALLOC(ptr, bytes)                                                        \
+  do {                                                                           \
+    cudaError_t e_ = cudaMalloc((void**)&(ptr), (size_t)(bytes));                \
+    if (e_ != cudaSuccess) { set_err("cudaMalloc " #ptr, e_); orbx_destroy(h); return e_ == cudaErrorMemoryAllocation ? ORBX_E_NOMEM : ORBX_E_CUDA; } \
+  } while (0)
+  if ((e = cudaSetDevice(h->device)) != cudaSuccess) { set_err("cudaSetDevice", e); delete h; return ORBX_E_CUDA; }
+  if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+    set_err("cudaStreamCreate", e); delete h; return ORBX_E_CUDA;
+  }
+  ALLOC(h->arena, B * P.arena_bytes + 256);
+  ALLOC(h->xtaps, (xt.size() + 1) * sizeof(OrbxTap));
+  ALLOC(h->ytaps, (yt.size() + 1) * sizeof(OrbxTap));
+  ALLOC(h->cell_cnt, B * P.total_cells * sizeof(int32_t));
+  ALLOC(h->cand, B * P.cand_total * sizeof(uint32_t));
+  ALLOC(h->gkeys, B * P.cand_total * sizeof(uint32_t));
+  ALLOC(h->glabels, B * P.cand_total * sizeof(int16_t));
+  ALLOC(h->sel, B * P.kp_total_cap * sizeof(uint32_t));
+  ALLOC(h->sel_cnt, B * P.nlevels * sizeof(int32_t));
+  ALLOC(h->dst, B * P.kp_total_cap * sizeof(int32_t));
+  ALLOC(h->status, sizeof(int32_t));
+  ALLOC(h->o_kps, B * P.max_keypoints * sizeof(OrbxKeyPointDev));
+  ALLOC(h->o_desc, B * P.max_keypoints * 32);
+  ALLOC(h->o_n, B * sizeof(int32_t));
+  ALLOC(h->o_mono, B * sizeof(int32_t));
+  ALLOC(h->border_tmp, (size_t)(P.lv[0].w + 2 * ORBX_EDGE) * (P.lv[0].h + 2 * ORBX_EDGE));
+#undef ALLOC
+  if (!xt.empty()) {
+    CU(cudaMemcpy(h->xtaps, xt.data(), xt.size() * sizeof(OrbxTap), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->ytaps, yt.data(), yt.size() * sizeof(OrbxTap), cudaMemcpyHostToDevice));
+  }
+  CU(cudaMemset(h->status, 0, sizeof(int32_t)));
+  CU(cudaMemset(h->arena, 0, B * P.arena_bytes + 256));
+  CU(orbx_octree_set_smem(h->oct_smem));
+  h->last_l0.base = h->arena; h->last_l0.frame_stride = P.arena_bytes; h->last_l0.pitch = P.lv[0].pitch;
+  *out = h;
+  return ORBX_OK;
+}
+
+int orbx_max_keypoints(orbx_handle h) { return h ? h->plan.max_keypoints : ORBX_E_INVALID; }
+
+static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1, OrbxKeyPointDev* d_kps,
+                        uint8_t* d_desc, int capacity, int32_t* d_n, int32_t* d_mono, cudaStream_t st) {
+  const DevPlan& D = h->dplan;
+  CU(orbx_launch_pyramid(D, l0, h->arena, h->xtaps, h->ytaps, batch, st));
+  CU(orbx_launch_fast(D, l0, h->arena, h->cell_cnt, h->cand, batch, st));
+  CU(orbx_launch_octree(D, h->cell_cnt, h->cand, h->gkeys, h->glabels, h->sel, h->sel_cnt, h->status, batch,
+                        h->oct_smem, h->oct_smem_keys, h->oct_node_cap, h->oct_max_cells, st));
+  CU(orbx_launch_order(D, h->sel, h->sel_cnt, lap0, lap1, h->dst, d_n, d_mono, batch, st));
+  CU(orbx_launch_describe(D, l0, h->arena, h->sel, h->sel_cnt, h->dst, d_kps, d_desc, capacity,
+                          (h->cfg.flags & ORBX_FLAG_STRICT_FP) ? 1 : 0, batch, st));
+  h->last_l0 = l0;
+  h->last_batch = batch;
+  return ORBX_OK;
+}
+
+int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch, size_t frame_stride,
+                              int batch, int lap0, int lap1, orbx_keypoint* d_kps, uint8_t* d_desc,
+                              int capacity, int32_t* d_n_out, int32_t* d_mono_index, void* stream) {
+  if (!h || !d_imgs || !d_kps || !d_desc || !d_n_out || !d_mono_index) return ORBX_E_INVALID;
+  if (batch < 1 || batch > h->cfg.max_batch || (int)pitch < h->plan.width) return ORBX_E_INVALID;
+  if (capacity < h->plan.max_keypoints) { set_err("capacity < orbx_max_keypoints()", cudaSuccess); return ORBX_E_CAPACITY; }
+  CU(cudaSetDevice(h->device));
+  Level0 l0;
+  l0.base = d_imgs; l0.frame_stride = (long long)frame_stride; l0.pitch = (int)pitch;
+  return run_pipeline(h, l0, batch, lap0, lap1, (OrbxKeyPointDev*)d_kps, d_desc, capacity, d_n_out, d_mono_index,
+                      stream ? (cudaStream_t)stream : h->stream);
+}
+
+int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int lap0, int lap1,
+                            orbx_keypoint* kps, uint8_t* desc, int capacity, int32_t* n_out,
+                            int32_t* mono_index) {
+  if (!h || !imgs || !kps || !desc || !n_out || !mono_index) return ORBX_E_INVALID;
+  if (batch < 1 || batch > h->cfg.max_batch) return ORBX_E_INVALID;
+  const OrbxPlan& P = h->plan;
+  if (capacity < P.max_keypoints) { set_err("capacity < orbx_max_keypoints()", cudaSuccess); return ORBX_E_CAPACITY; }
+  CU(cudaSetDevice(h->device));
+  cudaStream_t st = h->stream;
+  const int W = P.width, H = P.height, mk = P.max_keypoints;
+  // H2D straight into each frame's level-0 slot of the arena
+  for (int f = 0; f < batch; f++)
+    CU(cudaMemcpy2DAsync(h->arena + (long long)f * P.arena_bytes, P.lv[0].pitch, imgs + (size_t)f * W * H, W, W, H,
+                         cudaMemcpyHostToDevice, st));
+  Level0 l0;
+  l0.base = h->arena; l0.frame_stride = P.arena_bytes; l0.pitch = P.lv[0].pitch;
+  int rc = run_pipeline(h, l0, batch, lap0, lap1, h->o_kps, h->o_desc, mk, h->o_n, h->o_mono, st);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(n_out, h->o_n, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(mono_index, h->o_mono, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpy2DAsync(kps, (size_t)capacity * sizeof(orbx_keypoint), h->o_kps, (size_t)mk * sizeof(orbx_keypoint),
+                       (size_t)mk * sizeof(orbx_keypoint), batch, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpy2DAsync(desc, (size_t)capacity * 32, h->o_desc, (size_t)mk * 32, (size_t)mk * 32, batch,
+                       cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return ORBX_OK;
+}
+
+int orbx_extract(orbx_handle h, const uint8_t* img, int width, int height, size_t stride, int lap0, int lap1,
+                 orbx_keypoint* kps, uint8_t* desc, int capacity, int* n_out, int* mono_index) {
+  if (!h || !kps || !desc || !n_out || !mono_index) return ORBX_E_INVALID;
+  if (!img || width <= 0 || height <= 0) return ORBX_E_EMPTY;  // operator() returns -1 (:1090-1091)
+  const OrbxPlan& P = h->plan;
+  if (width != P.width || height != P.height || stride < (size_t)width) return ORBX_E_INVALID;
+  CU(cudaSetDevice(h->device));
+  cudaStream_t st = h->stream;
+  CU(cudaMemcpy2DAsync(h->arena, P.lv[0].pitch, img, stride, width, height, cudaMemcpyHostToDevice, st));
+  Level0 l0;
+  l0.base = h->arena; l0.frame_stride = P.arena_bytes; l0.pitch = P.lv[0].pitch;
+  int rc = run_pipeline(h, l0, 1, lap0, lap1, h->o_kps, h->o_desc, P.max_keypoints, h->o_n, h->o_mono, st);
+  if (rc) return rc;
+  int32_t nm[2];
+  CU(cudaMemcpyAsync(&nm[0], h->o_n, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(&nm[1], h->o_mono, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  *n_out = nm[0];
+  *mono_index = nm[1];
+  if (nm[0] > capacity) { set_err("keypoint buffer too small", cudaSuccess); return ORBX_E_CAPACITY; }
+  if (nm[0] > 0) {
+    CU(cudaMemcpyAsync(kps, h->o_kps, (size_t)nm[0] * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(desc, h->o_desc, (size_t)nm[0] * 32, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORBX_OK;
+}
+
+int orbx_level_size(orbx_handle h, int level, int* width, int* height) {
+  if (!h || level < 0 || level >= h->plan.nlevels) return ORBX_E_INVALID;
+  if (width) *width = h->plan.lv[level].w;
+  if (height) *height = h->plan.lv[level].h;
+  return ORBX_OK;
+}
+
+int orbx_pyramid_device(orbx_handle h, int frame, int level, const uint8_t** d_ptr, size_t* pitch, int* width,
+                        int* height) {
+  if (!h || level < 0 || level >= h->plan.nlevels || frame < 0 || frame >= h->cfg.max_batch) return ORBX_E_INVALID;
+  const OrbxLevel& L = h->plan.lv[level];
+  if (level == 0) {
+    if (d_ptr) *d_ptr = h->last_l0.base + (long long)frame * h->last_l0.frame_stride;
+    if (pitch) *pitch = (size_t)h->last_l0.pitch;
+  } else {
+    if (d_ptr) *d_ptr = h->arena + (long long)frame * h->plan.arena_bytes + L.offset;
+    if (pitch) *pitch = (size_t)L.pitch;
+  }
+  if (width) *width = L.w;
+  if (height) *height = L.h;
+  return ORBX_OK;
+}
+
+int orbx_get_pyramid(orbx_handle h, int frame, int level, uint8_t* dst, size_t dst_stride, int with_border) {
+  const uint8_t* p; size_t pitch; int w, hh;
+  int rc = orbx_pyramid_device(h, frame, level, &p, &pitch, &w, &hh);
+  if (rc) return rc;
+  if (!dst) return ORBX_E_INVALID;
+  CU(cudaSetDevice(h->device));
+  if (!with_border) {
+    if (dst_stride < (size_t)w) return ORBX_E_INVALID;
+    CU(cudaMemcpy2DAsync(dst, dst_stride, p, pitch, w, hh, cudaMemcpyDeviceToHost, h->stream));
+  } else {
+    const int bw = w + 2 * ORBX_EDGE, bh = hh + 2 * ORBX_EDGE;
+    if (dst_stride < (size_t)bw) return ORBX_E_INVALID;
+    CU(orbx_launch_border(p, (int)pitch, w, hh, h->border_tmp, bw, h->stream));
+    CU(cudaMemcpy2DAsync(dst, dst_stride, h->border_tmp, bw, bw, bh, cudaMemcpyDeviceToHost, h->stream));
+  }
+  CU(cudaStreamSynchronize(h->stream));
+  return ORBX_OK;
+}
+
+int orbx_get_scale_tables(orbx_handle h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                          int32_t* features_per_level) {
+  if (!h) return ORBX_E_INVALID;
+  for (int l = 0; l < h->plan.nlevels; l++) {
+    if (scale) scale[l] = h->plan.scale[l];
+    if (inv_scale) inv_scale[l] = h->plan.inv_scale[l];
+    if (sigma2) sigma2[l] = h->plan.sigma2[l];
+    if (inv_sigma2) inv_sigma2[l] = h->plan.inv_sigma2[l];
+    if (features_per_level) features_per_level[l] = h->plan.lv[l].nfeat;
+  }
+  return ORBX_OK;
+}
+
+int orbx_debug_level_keypoints(orbx_handle h, int frame, int level, int stage, int32_t* xyr, int cap, int* n) {
+  if (!h || !n || level < 0 || level >= h->plan.nlevels || frame < 0 || frame >= h->cfg.max_batch)
+    return ORBX_E_INVALID;
+  const OrbxPlan& P = h->plan;
+  const OrbxLevel& L = P.lv[level];
+  CU(cudaSetDevice(h->device));
+  CU(cudaStreamSynchronize(h->stream));
+  std::vector<uint32_t> keys;
+  if (stage == 0) {
+    const int ncell = L.nCols * L.nRows;
+    std::vector<int32_t> cnt(ncell);
+    CU(cudaMemcpy(cnt.data(), h->cell_cnt + (long long)frame * P.total_cells + L.cell_base, ncell * sizeof(int32_t),
+                  cudaMemcpyDeviceToHost));
+    std::vector<uint32_t> cellbuf(L.cell_cap);
+    for (int c = 0; c < ncell; c++) {
+      if (cnt[c] <= 0) continue;
+      CU(cudaMemcpy(cellbuf.data(), h->cand + (long long)frame * P.cand_total + L.cand_base + (long long)c * L.cell_cap,
+                    (size_t)cnt[c] * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+      keys.insert(keys.end(), cellbuf.begin(), cellbuf.begin() + cnt[c]);
+    }
+  } else {
+    int32_t m = 0;
+    CU(cudaMemcpy(&m, h->sel_cnt + frame * P.nlevels + level, sizeof(int32_t), cudaMemcpyDeviceToHost));
+    keys.resize(m);
+    if (m) CU(cudaMemcpy(keys.data(), h->sel + (long long)frame * P.kp_total_cap + L.kp_base, (size_t)m * sizeof(uint32_t),
+                         cudaMemcpyDeviceToHost));
+  }
+  *n = (int)keys.size();
+  for (int i = 0; i < (int)keys.size() && i < cap; i++) {
+    xyr[3 * i] = ORBX_KEY_X(keys[i]); xyr[3 * i + 1] = ORBX_KEY_Y(keys[i]); xyr[3 * i + 2] = ORBX_KEY_S(keys[i]);
+  }
+  return ORBX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,369 @@
+// match.cu — 256-bit Hamming candidate scoring behind ORBmatcher's Search* family and
+// Frame::ComputeStereoMatches (src/ORBmatcher.cc, src/Frame.cc), one warp per query.
+//
+// All the reference loops have the shape
+//     for cand in <ordered candidate list>: d = DescriptorDistance(q, cand)
+//         if d < best: second=best; best=d ... else if d < second: second=d      (first-min)
+//     or  if d <= best: best=d                                                   (last-min)
+// which is order dependent only through ties.  Tagging each candidate with its position in
+// the reference's visiting order turns the loop into two min-reductions over the packed key
+// (dist << 20 | pos): best = smallest key, second = second smallest key.
+#include "../../include/orbx.h"
+#include "orbx_kernels.cuh"
+
+#define M_WARPS 8
+#define KEY_NONE 0xFFFFFFFFu
+#define FRAME_GRID_COLS 64  // Frame.h:44
+#define FRAME_GRID_ROWS 48  // Frame.h:45
+
+struct Desc256 {
+  uint4 a, b;
+};
+__device__ __forceinline__ Desc256 load_desc(const uint8_t* p) {
+  Desc256 d;
+  d.a = __ldg(reinterpret_cast<const uint4*>(p));
+  d.b = __ldg(reinterpret_cast<const uint4*>(p) + 1);
+  return d;
+}
+// ORBmatcher::DescriptorDistance (ORBmatcher.cc:2058-2074): popcount of the XOR of 8 words
+__device__ __forceinline__ int hamming(const Desc256& x, const Desc256& y) {
+  return __popc(x.a.x ^ y.a.x) + __popc(x.a.y ^ y.a.y) + __popc(x.a.z ^ y.a.z) + __popc(x.a.w ^ y.a.w) +
+         __popc(x.b.x ^ y.b.x) + __popc(x.b.y ^ y.b.y) + __popc(x.b.z ^ y.b.z) + __popc(x.b.w ^ y.b.w);
+}
+
+// Running (best, second) of packed keys in one lane, with the reference index of each.
+struct Top2 {
+  uint32_t k1 = KEY_NONE, k2 = KEY_NONE;
+  int i1 = -1, i2 = -1;
+  __device__ __forceinline__ void push(uint32_t k, int idx) {
+    if (k < k1) { k2 = k1; i2 = i1; k1 = k; i1 = idx; }
+    else if (k < k2) { k2 = k; i2 = idx; }
+  }
+};
+// Warp-wide merge: after this every lane holds the global best and second.
+__device__ __forceinline__ void warp_top2(Top2& t) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const uint32_t ok1 = __shfl_xor_sync(0xffffffffu, t.k1, o), ok2 = __shfl_xor_sync(0xffffffffu, t.k2, o);
+    const int oi1 = __shfl_xor_sync(0xffffffffu, t.i1, o), oi2 = __shfl_xor_sync(0xffffffffu, t.i2, o);
+    // keys are unique per query (distinct positions), so merging two sorted pairs is exact
+    if (ok1 < t.k1) {
+      if (t.k1 < ok2) { t.k2 = t.k1; t.i2 = t.i1; } else { t.k2 = ok2; t.i2 = oi2; }
+      t.k1 = ok1; t.i1 = oi1;
+    } else if (ok1 < t.k2) {
+      t.k2 = ok1; t.i2 = oi1;
+    }
+  }
+}
+
+__device__ __forceinline__ void write_result(orbm_result* out, const Top2& t, const int8_t* ref_level,
+                                             int tie_rule) {
+  orbm_result r;
+  r.best_idx = t.i1;
+  r.best_dist = t.i1 >= 0 ? (int16_t)(t.k1 >> 20) : (int16_t)256;
+  r.best_level = t.i1 >= 0 ? (ref_level ? ref_level[t.i1] : (int8_t)0) : (int8_t)-1;
+  if (tie_rule == ORBM_TIE_FIRST_MIN && t.i2 >= 0) {
+    r.second_dist = (int16_t)(t.k2 >> 20);
+    r.second_level = ref_level ? ref_level[t.i2] : (int8_t)0;
+  } else {
+    r.second_dist = 256;
+    r.second_level = -1;
+  }
+  r.pad = 0;
+  *out = r;
+}
+
+__device__ __forceinline__ uint32_t make_key(int dist, int pos, int tie_rule) {
+  return ((uint32_t)dist << 20) | (uint32_t)(tie_rule == ORBM_TIE_LAST_MIN ? 0xFFFFF - pos : pos);
+}
+
+// ---- explicit candidate lists -----------------------------------------------------------------
+__global__ void __launch_bounds__(M_WARPS * 32)
+k_argmin2_csr(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ r,
+              const int32_t* __restrict__ cand_off, const int32_t* __restrict__ cand_idx,
+              const int8_t* __restrict__ ref_level, int tie_rule, orbm_result* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int qi = blockIdx.x * M_WARPS + (threadIdx.x >> 5);
+  if (qi >= nq) return;
+  const Desc256 dq = load_desc(q + (size_t)qi * 32);
+  const int c0 = cand_off[qi], c1 = cand_off[qi + 1];
+  Top2 t;
+  for (int c = c0 + lane; c < c1; c += 32) {
+    const int idx = cand_idx[c];
+    const int d = hamming(dq, load_desc(r + (size_t)idx * 32));
+    t.push(make_key(d, (c - c0) & 0xFFFFF, tie_rule), idx);
+  }
+  warp_top2(t);
+  if (lane == 0) write_result(out + qi, t, ref_level, tie_rule);
+}
+
+// ---- Frame::AssignFeaturesToGrid (Frame.cc:385-416): CSR over 64x48 cells, cell = ix*48+iy ------
+#define GRID_CELLS (FRAME_GRID_COLS * FRAME_GRID_ROWS)
+__device__ __forceinline__ int grid_cell(const OrbxKeyPointDev& kp, float min_x, float min_y, float winv,
+                                         float hinv) {
+  // PosInGrid (Frame.cc:725-735): round() = half away from zero
+  const int px = (int)roundf(f_mul(f_sub(kp.x, min_x), winv));
+  const int py = (int)roundf(f_mul(f_sub(kp.y, min_y), hinv));
+  if (px < 0 || px >= FRAME_GRID_COLS || py < 0 || py >= FRAME_GRID_ROWS) return -1;
+  return px * FRAME_GRID_ROWS + py;
+}
+
+__global__ void __launch_bounds__(128)
+k_grid_build(const OrbxKeyPointDev* __restrict__ kps, const int32_t* __restrict__ n_arr, int kp_stride,
+             float min_x, float min_y, float winv, float hinv, int32_t* __restrict__ cell_off,
+             int32_t* __restrict__ cell_idx) {
+  __shared__ int cnt[GRID_CELLS + 1];
+  __shared__ int wsum[4];
+  __shared__ int carry_s;
+  const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const OrbxKeyPointDev* k = kps + (size_t)f * kp_stride;
+  const int n = n_arr[f];
+  int32_t* off = cell_off + (size_t)f * (GRID_CELLS + 1);
+  int32_t* idx = cell_idx + (size_t)f * kp_stride;
+  for (int i = tid; i <= GRID_CELLS; i += 128) cnt[i] = 0;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  for (int i = tid; i < n; i += 128) {
+    const int c = grid_cell(k[i], min_x, min_y, winv, hinv);
+    if (c >= 0) atomicAdd(&cnt[c], 1);
+  }
+  __syncthreads();
+  for (int base = 0; base < GRID_CELLS; base += 128) {  // exclusive scan, 24 chunks
+    const int v = cnt[base + tid];
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    int woff = 0;
+    for (int w = 0; w < warp; w++) woff += wsum[w];
+    const int carry = carry_s;
+    const int ex = carry + woff + inc - v;
+    cnt[base + tid] = ex;  // becomes the write cursor
+    off[base + tid] = ex;
+    __syncthreads();
+    if (tid == 127) carry_s = carry + woff + inc;
+    __syncthreads();
+  }
+  if (tid == 0) off[GRID_CELLS] = carry_s;
+  __syncthreads();
+  // ordered fill: one warp walks the keypoints in index order so that every cell lists its
+  // members in insertion order, exactly like the push_back loop of the reference
+  if (warp == 0) {
+    for (int base = 0; base < n; base += 32) {
+      const int i = base + lane;
+      const int c = i < n ? grid_cell(k[i], min_x, min_y, winv, hinv) : -1;
+      const unsigned peers = __match_any_sync(0xffffffffu, c);
+      const int rank = __popc(peers & ((1u << lane) - 1));
+      int basepos = 0;
+      if (c >= 0 && rank == 0) basepos = atomicAdd(&cnt[c], __popc(peers));
+      basepos = __shfl_sync(0xffffffffu, basepos, __ffs(peers) - 1);
+      if (c >= 0) idx[basepos + rank] = i;
+      __syncwarp();
+    }
+  }
+}
+
+// ---- fused GetFeaturesInArea + scoring --------------------------------------------------------
+__global__ void __launch_bounds__(M_WARPS * 32)
+k_search_area(const OrbxKeyPointDev* __restrict__ kps, const uint8_t* __restrict__ desc,
+              const int32_t* __restrict__ n_arr, int kp_stride, const int32_t* __restrict__ cell_off,
+              const int32_t* __restrict__ cell_idx, float min_x, float min_y, float winv, float hinv,
+              const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qr,
+              const int8_t* __restrict__ qmin, const int8_t* __restrict__ qmax,
+              const uint8_t* __restrict__ qdesc, const int32_t* __restrict__ nq_arr, int q_stride, int tie_rule,
+              orbm_result* __restrict__ out) {
+  const int lane = threadIdx.x & 31, f = blockIdx.y;
+  const int qi = blockIdx.x * M_WARPS + (threadIdx.x >> 5);
+  if (qi >= nq_arr[f]) return;
+  const size_t qo = (size_t)f * q_stride + qi;
+  const float x = qx[qo], y = qy[qo], r = qr[qo];
+  const int minLevel = qmin[qo], maxLevel = qmax[qo];
+  const OrbxKeyPointDev* k = kps + (size_t)f * kp_stride;
+  const uint8_t* dsc = desc + (size_t)f * kp_stride * 32;
+  const int32_t* off = cell_off + (size_t)f * (GRID_CELLS + 1);
+  const int32_t* idx = cell_idx + (size_t)f * kp_stride;
+  Top2 t;
+  // Frame.cc:665-687
+  const int nMinCellX = max(0, (int)floorf(f_mul(f_sub(f_sub(x, min_x), r), winv)));
+  const int nMaxCellX = min(FRAME_GRID_COLS - 1, (int)ceilf(f_mul(f_add(f_sub(x, min_x), r), winv)));
+  const int nMinCellY = max(0, (int)floorf(f_mul(f_sub(f_sub(y, min_y), r), hinv)));
+  const int nMaxCellY = min(FRAME_GRID_ROWS - 1, (int)ceilf(f_mul(f_add(f_sub(y, min_y), r), hinv)));
+  const bool ok = nMinCellX < FRAME_GRID_COLS && nMaxCellX >= 0 && nMinCellY < FRAME_GRID_ROWS && nMaxCellY >= 0;
+  const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+  if (ok) {
+    const Desc256 dq = load_desc(qdesc + qo * 32);
+    int seq = 0;
+    for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
+      // cells (ix, nMinCellY..nMaxCellY) are adjacent in the CSR: one contiguous run
+      const int e0 = off[ix * FRAME_GRID_ROWS + nMinCellY], e1 = off[ix * FRAME_GRID_ROWS + nMaxCellY + 1];
+      for (int e = e0 + lane; e < e1; e += 32) {
+        const int j = idx[e];
+        const OrbxKeyPointDev kp = k[j];
+        bool pass = true;
+        if (bCheckLevels) {
+          if (kp.octave < minLevel) pass = false;
+          if (maxLevel >= 0 && kp.octave > maxLevel) pass = false;
+        }
+        const float distx = f_sub(kp.x, x), disty = f_sub(kp.y, y);
+        if (!(fabsf(distx) < r && fabsf(disty) < r)) pass = false;
+        if (pass) {
+          const int d = hamming(dq, load_desc(dsc + (size_t)j * 32));
+          t.push(make_key(d, (seq + e - e0) & 0xFFFFF, tie_rule), j);
+        }
+      }
+      seq += e1 - e0;
+    }
+  }
+  warp_top2(t);
+  if (lane == 0) {
+    orbm_result res;
+    res.best_idx = t.i1;
+    res.best_dist = t.i1 >= 0 ? (int16_t)(t.k1 >> 20) : (int16_t)256;
+    res.best_level = t.i1 >= 0 ? (int8_t)k[t.i1].octave : (int8_t)-1;
+    const bool has2 = tie_rule == ORBM_TIE_FIRST_MIN && t.i2 >= 0;
+    res.second_dist = has2 ? (int16_t)(t.k2 >> 20) : (int16_t)256;
+    res.second_level = has2 ? (int8_t)k[t.i2].octave : (int8_t)-1;
+    res.pad = 0;
+    out[qo] = res;
+  }
+}
+
+// ---- Hamming stage of Frame::ComputeStereoMatches (Frame.cc:811-894) -------------------------------
+struct ScaleTab { float s[ORBX_MAX_LEVELS]; };
+
+__global__ void __launch_bounds__(M_WARPS * 32)
+k_stereo_rowband(const OrbxKeyPointDev* __restrict__ kl, const uint8_t* __restrict__ dl,
+                 const int32_t* __restrict__ nl_arr, const OrbxKeyPointDev* __restrict__ kr,
+                 const uint8_t* __restrict__ dr, const int32_t* __restrict__ nr_arr, int kp_stride,
+                 ScaleTab scales, float max_d, int32_t* __restrict__ best_idx, int32_t* __restrict__ best_dist) {
+  const int lane = threadIdx.x & 31, f = blockIdx.y;
+  const int iL = blockIdx.x * M_WARPS + (threadIdx.x >> 5);
+  if (iL >= nl_arr[f]) return;
+  const size_t base = (size_t)f * kp_stride;
+  const OrbxKeyPointDev kpL = kl[base + iL];
+  const int nR = nr_arr[f];
+  const int rowL = (int)kpL.y;  // vRowIndices[vL] (:852)
+  const float minU = f_sub(kpL.x, max_d), maxU = kpL.x;  // minD = 0
+  const Desc256 dq = load_desc(dl + (base + iL) * 32);
+  uint32_t bestk = KEY_NONE;
+  if (!(maxU < 0)) {
+    for (int iR = lane; iR < nR; iR += 32) {
+      const OrbxKeyPointDev kpR = kr[base + iR];
+      // membership of iR in vRowIndices[rowL] (:828-838)
+      const float rr = f_mul(2.0f, scales.s[kpR.octave]);
+      const int maxr = (int)ceilf(f_add(kpR.y, rr)), minr = (int)floorf(f_sub(kpR.y, rr));
+      if (rowL < minr || rowL > maxr) continue;
+      if (kpR.octave < kpL.octave - 1 || kpR.octave > kpL.octave + 1) continue;
+      if (!(kpR.x >= minU && kpR.x <= maxU)) continue;
+      const int d = hamming(dq, load_desc(dr + (base + iR) * 32));
+      const uint32_t k = ((uint32_t)d << 20) | (uint32_t)iR;  // ascending iR = visiting order
+      bestk = min(bestk, k);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) bestk = min(bestk, __shfl_xor_sync(0xffffffffu, bestk, o));
+  if (lane == 0) {
+    const int d = bestk == KEY_NONE ? 256 : (int)(bestk >> 20);
+    // bestDist starts at TH_HIGH=100 and only strictly smaller distances replace it (:862,:888)
+    if (d < 100) { best_idx[base + iL] = (int)(bestk & 0xFFFFF); best_dist[base + iL] = d; }
+    else { best_idx[base + iL] = -1; best_dist[base + iL] = 100; }
+  }
+}
+
+// ---- cv::BFMatcher(NORM_HAMMING).knnMatch(k=2) (Frame.cc:1144) ------------------------------------
+__global__ void __launch_bounds__(M_WARPS * 32)
+k_knn2_dense(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ r, int nr,
+             int32_t* __restrict__ idx2, int32_t* __restrict__ dist2) {
+  const int lane = threadIdx.x & 31;
+  const int qi = blockIdx.x * M_WARPS + (threadIdx.x >> 5);
+  if (qi >= nq) return;
+  const Desc256 dq = load_desc(q + (size_t)qi * 32);
+  Top2 t;
+  for (int j = lane; j < nr; j += 32) {
+    const int d = hamming(dq, load_desc(r + (size_t)j * 32));
+    t.push(((uint32_t)d << 20) | (uint32_t)j, j);
+  }
+  warp_top2(t);
+  if (lane == 0) {
+    idx2[2 * qi] = t.i1; idx2[2 * qi + 1] = t.i2;
+    dist2[2 * qi] = t.i1 >= 0 ? (int)(t.k1 >> 20) : -1;
+    dist2[2 * qi + 1] = t.i2 >= 0 ? (int)(t.k2 >> 20) : -1;
+  }
+}
+
+#define CUM(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return ORBX_E_CUDA; } while (0)
+
+extern "C" {
+
+int orbm_argmin2_csr(const uint8_t* d_q, int nq, const uint8_t* d_r, int nr, const int32_t* d_cand_off,
+                     const int32_t* d_cand_idx, const int8_t* d_ref_level, int tie_rule, orbm_result* d_out,
+                     void* stream) {
+  if (nq < 0 || nr < 0 || (nq > 0 && (!d_q || !d_cand_off || !d_out))) return ORBX_E_INVALID;
+  if (nq == 0) return ORBX_OK;
+  k_argmin2_csr<<<(nq + M_WARPS - 1) / M_WARPS, M_WARPS * 32, 0, (cudaStream_t)stream>>>(
+      d_q, nq, d_r, d_cand_off, d_cand_idx, d_ref_level, tie_rule, d_out);
+  CUM(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbm_grid_build(const orbx_keypoint* d_kps, const int32_t* d_n, int kp_stride, int batch, float min_x,
+                    float max_x, float min_y, float max_y, int32_t* d_cell_off, int32_t* d_cell_idx, void* stream) {
+  if (!d_kps || !d_n || !d_cell_off || !d_cell_idx || batch < 1 || !(max_x > min_x) || !(max_y > min_y))
+    return ORBX_E_INVALID;
+  // mfGridElementWidthInv / HeightInv (Frame.cc:171-172)
+  const float winv = (float)FRAME_GRID_COLS / (max_x - min_x), hinv = (float)FRAME_GRID_ROWS / (max_y - min_y);
+  k_grid_build<<<batch, 128, 0, (cudaStream_t)stream>>>((const OrbxKeyPointDev*)d_kps, d_n, kp_stride, min_x, min_y,
+                                                        winv, hinv, d_cell_off, d_cell_idx);
+  CUM(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbm_search_area(const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n, int kp_stride,
+                     const int32_t* d_cell_off, const int32_t* d_cell_idx, float min_x, float max_x, float min_y,
+                     float max_y, const float* d_qx, const float* d_qy, const float* d_qr,
+                     const int8_t* d_qmin_level, const int8_t* d_qmax_level, const uint8_t* d_qdesc,
+                     const int32_t* d_nq, int q_stride, int batch, int tie_rule, orbm_result* d_out, void* stream) {
+  if (!d_kps || !d_desc || !d_n || !d_cell_off || !d_cell_idx || !d_qx || !d_qy || !d_qr || !d_qmin_level ||
+      !d_qmax_level || !d_qdesc || !d_nq || !d_out || batch < 1 || q_stride < 1)
+    return ORBX_E_INVALID;
+  const float winv = (float)FRAME_GRID_COLS / (max_x - min_x), hinv = (float)FRAME_GRID_ROWS / (max_y - min_y);
+  dim3 grd((q_stride + M_WARPS - 1) / M_WARPS, batch);
+  k_search_area<<<grd, M_WARPS * 32, 0, (cudaStream_t)stream>>>(
+      (const OrbxKeyPointDev*)d_kps, d_desc, d_n, kp_stride, d_cell_off, d_cell_idx, min_x, min_y, winv, hinv, d_qx,
+      d_qy, d_qr, d_qmin_level, d_qmax_level, d_qdesc, d_nq, q_stride, tie_rule, d_out);
+  CUM(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbm_stereo_rowband(const orbx_keypoint* d_kps_l, const uint8_t* d_desc_l, const int32_t* d_n_l,
+                        const orbx_keypoint* d_kps_r, const uint8_t* d_desc_r, const int32_t* d_n_r, int kp_stride,
+                        int batch, const float* scale_factors_host, int nlevels, float max_d, int32_t* d_best_idx_r,
+                        int32_t* d_best_dist, void* stream) {
+  if (!d_kps_l || !d_desc_l || !d_n_l || !d_kps_r || !d_desc_r || !d_n_r || !scale_factors_host ||
+      !d_best_idx_r || !d_best_dist || batch < 1 || nlevels < 1 || nlevels > ORBX_MAX_LEVELS)
+    return ORBX_E_INVALID;
+  ScaleTab st;
+  for (int i = 0; i < ORBX_MAX_LEVELS; i++) st.s[i] = i < nlevels ? scale_factors_host[i] : 1.0f;
+  dim3 grd((kp_stride + M_WARPS - 1) / M_WARPS, batch);
+  k_stereo_rowband<<<grd, M_WARPS * 32, 0, (cudaStream_t)stream>>>(
+      (const OrbxKeyPointDev*)d_kps_l, d_desc_l, d_n_l, (const OrbxKeyPointDev*)d_kps_r, d_desc_r, d_n_r, kp_stride, st,
+      max_d, d_best_idx_r, d_best_dist);
+  CUM(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbm_knn2_dense(const uint8_t* d_q, int nq, const uint8_t* d_r, int nr, int32_t* d_idx2, int32_t* d_dist2,
+                    void* stream) {
+  if (nq < 0 || nr < 0 || (nq > 0 && (!d_q || !d_idx2 || !d_dist2))) return ORBX_E_INVALID;
+  if (nq == 0) return ORBX_OK;
+  k_knn2_dense<<<(nq + M_WARPS - 1) / M_WARPS, M_WARPS * 32, 0, (cudaStream_t)stream>>>(d_q, nq, d_r, nr, d_idx2,
+                                                                                       d_dist2);
+  CUM(cudaGetLastError());
+  return ORBX_OK;
+}
+
+}  // extern "C"

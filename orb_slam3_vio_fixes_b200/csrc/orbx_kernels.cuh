@@ -1,0 +1,69 @@
+// orbx_kernels.cuh — device-side plan mirror and launch declarations shared by the .cu files.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "orbx_plan.h"
+
+// Per-level constants as the kernels need them (subset of OrbxLevel, passed by value as a
+// __grid_constant__ kernel parameter: 12 levels * 80 B < 1 KB).
+struct DevLevel {
+  int w, h, pitch;
+  int nCols, nRows, wCell, hCell;
+  int cell_base, cell_cap;
+  int nfeat, kp_base, kp_cap, kp_max;
+  int nIni;
+  float hX, scale, patch_size;
+  int xtab, ytab;
+  long long offset;     // bytes, inside a frame's pyramid arena
+  long long cand_base;  // uint32 units, inside a frame's candidate arena
+};
+
+struct DevPlan {
+  DevLevel lv[ORBX_PLAN_MAX_LEVELS];
+  int nlevels, total_cells, kp_total_cap, ini_th, min_th;
+  long long cand_total;   // uint32 per frame
+  long long arena_bytes;  // per frame
+  int umax[16];
+};
+
+// Where each frame's level-0 image lives (user buffer for the batched device API, or the
+// arena's own level-0 slot for the host API).
+struct Level0 {
+  const uint8_t* base;
+  long long frame_stride;  // bytes
+  int pitch;
+};
+
+// Packed candidate / keypoint key: x<<20 | y<<8 | score  (x,y < 4096, score < 256)
+__host__ __device__ __forceinline__ uint32_t orbx_pack_key(int x, int y, int s) {
+  return ((uint32_t)x << 20) | ((uint32_t)y << 8) | (uint32_t)s;
+}
+#define ORBX_KEY_X(k) ((int)((k) >> 20))
+#define ORBX_KEY_Y(k) ((int)(((k) >> 8) & 0xfff))
+#define ORBX_KEY_S(k) ((int)((k) & 0xff))
+
+struct OrbxKeyPointDev {  // = orbx_keypoint = cv::KeyPoint
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+};
+
+// --- launches (each returns cudaGetLastError()) -------------------------------------------------
+cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, const OrbxTap* xtaps,
+                                const OrbxTap* ytaps, int batch, cudaStream_t st);
+cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, int32_t* cell_cnt,
+                             uint32_t* cand, int batch, cudaStream_t st);
+cudaError_t orbx_launch_octree(const DevPlan& P, const int32_t* cell_cnt, const uint32_t* cand,
+                               uint32_t* gkeys, int16_t* glabels, uint32_t* sel, int32_t* sel_cnt,
+                               int32_t* status, int batch, size_t smem_bytes, int smem_keys, int node_cap,
+                               int max_cells, cudaStream_t st);
+cudaError_t orbx_launch_order(const DevPlan& P, const uint32_t* sel, const int32_t* sel_cnt, int lap0,
+                              int lap1, int32_t* dst, int32_t* n_out, int32_t* mono_index, int batch,
+                              cudaStream_t st);
+cudaError_t orbx_launch_describe(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* sel,
+                                 const int32_t* sel_cnt, const int32_t* dst, OrbxKeyPointDev* kps,
+                                 uint8_t* desc, int capacity, int strict_fp, int batch, cudaStream_t st);
+cudaError_t orbx_launch_border(const uint8_t* src, int pitch, int w, int h, uint8_t* dst, int dst_pitch,
+                               cudaStream_t st);
+size_t orbx_octree_smem_bytes(int smem_keys, int node_cap, int max_cells);
+cudaError_t orbx_octree_set_smem(size_t bytes);

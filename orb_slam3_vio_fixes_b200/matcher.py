@@ -1,0 +1,109 @@
+"""Host-side mirror of the ORBmatcher cores (reference include/ORBmatcher.h:35-105) on the C ABI.
+
+`ORBmatcher.DescriptorDistance` keeps the reference's static signature (a single pair is a host
+popcount, as in include/orbx_compat/ORBmatcher_core.h).  The batched functions are the
+candidate-scoring loops behind SearchByProjection / SearchByBoW / SearchForTriangulation /
+Frame::ComputeStereoMatches; they take torch CUDA tensors and run on the current stream.
+"""
+import numpy as np
+
+from . import _lib
+from ._lib import RES_DTYPE, TIE_FIRST_MIN, TIE_LAST_MIN  # noqa: F401
+
+_POP8 = np.array([bin(i).count("1") for i in range(256)], np.int32)
+
+
+def _stream(dev):
+    import torch
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def _res_tensor(n, dev):
+    import torch
+    return torch.zeros((n, RES_DTYPE.itemsize), dtype=torch.uint8, device=dev)
+
+
+def results_to_numpy(t):
+    a = np.ascontiguousarray(t.detach().cpu().numpy())
+    return a.view(RES_DTYPE).reshape(a.shape[:-1])
+
+
+class ORBmatcher:
+    TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30  # ORBmatcher.cc:35-37
+
+    def __init__(self, nnratio=0.6, checkOri=True):
+        self.mfNNratio, self.mbCheckOrientation = np.float32(nnratio), bool(checkOri)
+
+    @staticmethod
+    def DescriptorDistance(a, b):
+        """Hamming distance of two 32-byte descriptors (ORBmatcher.cc:2058-2074)."""
+        a = np.asarray(a, np.uint8).reshape(-1)
+        b = np.asarray(b, np.uint8).reshape(-1)
+        assert a.size == 32 and b.size == 32
+        return int(_POP8[a ^ b].sum())
+
+    # ---- batched cores ---------------------------------------------------------------------
+    @staticmethod
+    def argmin2_csr(q, r, cand_off, cand_idx, ref_level=None, tie_rule=TIE_FIRST_MIN):
+        """q [nq,32] u8, r [nr,32] u8, cand_off [nq+1] i32, cand_idx [total] i32 (CUDA tensors).
+        Returns a [nq,12] uint8 tensor of orbm_result records."""
+        out = _res_tensor(q.shape[0], q.device)
+        rc = _lib.lib().orbm_argmin2_csr(q.data_ptr(), q.shape[0], r.data_ptr(), r.shape[0], cand_off.data_ptr(),
+                                         cand_idx.data_ptr(), 0 if ref_level is None else ref_level.data_ptr(),
+                                         tie_rule, out.data_ptr(), _stream(q.device))
+        _lib.check(rc, "orbm_argmin2_csr")
+        return out
+
+    @staticmethod
+    def grid_build(kps, n, bounds):
+        """kps [B,cap,7] f32 (cv::KeyPoint records), n [B] i32; bounds = (minX, maxX, minY, maxY).
+        Returns (cell_off [B, 64*48+1] i32, cell_idx [B,cap] i32)."""
+        import torch
+        b, cap = kps.shape[0], kps.shape[1]
+        cell_off = torch.zeros((b, _lib.GRID_COLS * _lib.GRID_ROWS + 1), dtype=torch.int32, device=kps.device)
+        cell_idx = torch.zeros((b, cap), dtype=torch.int32, device=kps.device)
+        rc = _lib.lib().orbm_grid_build(kps.data_ptr(), n.data_ptr(), cap, b, *[float(v) for v in bounds],
+                                        cell_off.data_ptr(), cell_idx.data_ptr(), _stream(kps.device))
+        _lib.check(rc, "orbm_grid_build")
+        return cell_off, cell_idx
+
+    @staticmethod
+    def search_area(kps, desc, n, grid, bounds, qx, qy, qr, qmin, qmax, qdesc, nq, tie_rule=TIE_FIRST_MIN):
+        """Fused GetFeaturesInArea + best/second scoring.  Queries [B,Q] (qx,qy,qr f32; qmin,qmax i8;
+        qdesc [B,Q,32] u8; nq [B] i32).  Returns [B,Q,12] uint8 orbm_result records."""
+        b, cap = kps.shape[0], kps.shape[1]
+        qs = qx.shape[1]
+        out = _res_tensor(b * qs, kps.device).view(b, qs, RES_DTYPE.itemsize)
+        cell_off, cell_idx = grid
+        rc = _lib.lib().orbm_search_area(kps.data_ptr(), desc.data_ptr(), n.data_ptr(), cap, cell_off.data_ptr(),
+                                         cell_idx.data_ptr(), *[float(v) for v in bounds], qx.data_ptr(),
+                                         qy.data_ptr(), qr.data_ptr(), qmin.data_ptr(), qmax.data_ptr(),
+                                         qdesc.data_ptr(), nq.data_ptr(), qs, b, tie_rule, out.data_ptr(),
+                                         _stream(kps.device))
+        _lib.check(rc, "orbm_search_area")
+        return out
+
+    @staticmethod
+    def stereo_rowband(kps_l, desc_l, n_l, kps_r, desc_r, n_r, scale_factors, max_d):
+        """Hamming stage of Frame::ComputeStereoMatches.  Returns (best_idx_r [B,cap] i32, best_dist [B,cap] i32)."""
+        import torch
+        b, cap = kps_l.shape[0], kps_l.shape[1]
+        bi = torch.full((b, cap), -1, dtype=torch.int32, device=kps_l.device)
+        bd = torch.full((b, cap), 100, dtype=torch.int32, device=kps_l.device)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        rc = _lib.lib().orbm_stereo_rowband(kps_l.data_ptr(), desc_l.data_ptr(), n_l.data_ptr(), kps_r.data_ptr(),
+                                            desc_r.data_ptr(), n_r.data_ptr(), cap, b, sf.ctypes.data, sf.size,
+                                            float(max_d), bi.data_ptr(), bd.data_ptr(), _stream(kps_l.device))
+        _lib.check(rc, "orbm_stereo_rowband")
+        return bi, bd
+
+    @staticmethod
+    def knn2_dense(q, r):
+        """cv::BFMatcher(NORM_HAMMING).knnMatch(k=2).  Returns (idx [nq,2] i32, dist [nq,2] i32)."""
+        import torch
+        idx = torch.zeros((q.shape[0], 2), dtype=torch.int32, device=q.device)
+        dist = torch.zeros((q.shape[0], 2), dtype=torch.int32, device=q.device)
+        rc = _lib.lib().orbm_knn2_dense(q.data_ptr(), q.shape[0], r.data_ptr(), r.shape[0], idx.data_ptr(),
+                                        dist.data_ptr(), _stream(q.device))
+        _lib.check(rc, "orbm_knn2_dense")
+        return idx, dist
