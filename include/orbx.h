@@ -39,6 +39,10 @@ extern "C" {
                                    (mul,mul,add) instead of the FMA form g++ -O3 -march=native
                                    emits for the reference; default = as compiled (FMA).     */
 
+#define ORBX_FLAG_STAGE_TIMING 2u /* record CUDA events between the stages of every call so that
+                                   orbx_stage_times() can report per-kernel device time        */
+#define ORBX_NUM_STAGES 5       /* pyramid, fast, octree, order, describe                     */
+
 /* cv::KeyPoint memory layout, 28 bytes (what std::vector<cv::KeyPoint> holds). */
 typedef struct orbx_keypoint {
   float x, y;      /* pt, level-0 pixel coordinates                                  */
@@ -114,6 +118,12 @@ int orbx_level_size(orbx_handle h, int level, int* width, int* height);
 int orbx_get_scale_tables(orbx_handle h, float* scale, float* inv_scale, float* sigma2,
                           float* inv_sigma2, int32_t* features_per_level);
 
+/* Device time of each stage of the last extract call, in milliseconds, measured with CUDA events
+ * on the stream the kernels ran on (the reference's REGISTER_TIMES counterpart,
+ * include/Settings.h:24, Frame.cc:119-146).  Needs ORBX_FLAG_STAGE_TIMING; waits for the call to
+ * finish.  ms[ORBX_NUM_STAGES] = {pyramid (all level launches), fast, octree, order, describe}. */
+int orbx_stage_times(orbx_handle h, float* ms);
+
 /* Introspection for the parity tests: per-level intermediate keypoint lists of frame `frame`
  * of the last call.  stage 0 = FAST candidates in DistributeOctTree input order (x,y relative
  * to (16,16), response); stage 1 = after the octree, in list order (level coordinates).
@@ -165,6 +175,17 @@ int orbm_search_area(const orbx_keypoint* d_kps, const uint8_t* d_desc, const in
                      const float* d_qy, const float* d_qr, const int8_t* d_qmin_level,
                      const int8_t* d_qmax_level, const uint8_t* d_qdesc, const int32_t* d_nq,
                      int q_stride, int batch, int tie_rule, orbm_result* d_out, void* stream);
+
+/* Window queries of SearchByProjection(Frame&, const Frame&, th, bMono) (ORBmatcher.cc:1676-1768)
+ * for a pure image-plane shift: query i of frame f is keypoint i of frame d_src_frame[f] moved by
+ * d_shift_xy[f] = (dx,dy), radius th*scale[octave], octave band [octave+band_lo, octave+band_hi],
+ * descriptor copied.  (The pose-based projection itself is host geometry and stays there.) */
+int orbm_queries_shift(const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n,
+                       int kp_stride, int batch, const int32_t* d_src_frame,
+                       const float* d_shift_xy, float th, const float* scale_factors_host,
+                       int nlevels, int band_lo, int band_hi, float* d_qx, float* d_qy, float* d_qr,
+                       int8_t* d_qmin_level, int8_t* d_qmax_level, uint8_t* d_qdesc, int32_t* d_nq,
+                       void* stream);
 
 /* Hamming stage of Frame::ComputeStereoMatches (Frame.cc:811-894): per left keypoint the best
  * right keypoint in its row band (|dy| within 2*scale[octR], |octave diff|<=1,

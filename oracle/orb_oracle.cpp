@@ -157,7 +157,9 @@ void copy_make_border101(const Image& s, Image& d, int b) {
   for (int y = 0; y < d.h; y++) {
     const uint8_t* S = s.row(reflect101(y - b, s.h));
     uint8_t* D = d.row(y);
-    for (int x = 0; x < d.w; x++) D[x] = S[reflect101(x - b, s.w)];
+    for (int x = 0; x < b; x++) D[x] = S[reflect101(x - b, s.w)];
+    memcpy(D + b, S, s.w);
+    for (int x = b + s.w; x < d.w; x++) D[x] = S[reflect101(x - b, s.w)];
   }
 }
 
@@ -169,21 +171,30 @@ static const int kGauss7[7] = {18, 34, 48, 56, 48, 34, 18};
 
 void gaussian_blur7(const Image& s, Image& d) {
   d.w = s.w; d.h = s.h; d.d.resize(s.d.size());
-  std::vector<uint16_t> tmp((size_t)s.w * s.h);
-  for (int y = 0; y < s.h; y++) {
+  const int w = s.w, h = s.h;
+  std::vector<uint16_t> tmp((size_t)w * h);
+  for (int y = 0; y < h; y++) {
     const uint8_t* S = s.row(y);
-    for (int x = 0; x < s.w; x++) {
+    uint16_t* T = &tmp[(size_t)y * w];
+    auto edge = [&](int x) {
       int acc = 0;
-      for (int k = -3; k <= 3; k++) acc += kGauss7[k + 3] * S[reflect101(x + k, s.w)];
-      tmp[(size_t)y * s.w + x] = (uint16_t)acc;  // <= 255*256
-    }
+      for (int k = -3; k <= 3; k++) acc += kGauss7[k + 3] * S[reflect101(x + k, w)];
+      T[x] = (uint16_t)acc;  // <= 255*256
+    };
+    if (w < 8) { for (int x = 0; x < w; x++) edge(x); continue; }
+    for (int x = 0; x < 3; x++) edge(x);
+    for (int x = w - 3; x < w; x++) edge(x);
+    for (int x = 3; x < w - 3; x++)  // interior: no border handling, vectorises
+      T[x] = (uint16_t)(18 * (S[x - 3] + S[x + 3]) + 34 * (S[x - 2] + S[x + 2]) + 48 * (S[x - 1] + S[x + 1]) +
+                        56 * S[x]);
   }
-  for (int y = 0; y < s.h; y++) {
+  for (int y = 0; y < h; y++) {
+    const uint16_t* r[7];
+    for (int k = 0; k < 7; k++) r[k] = &tmp[(size_t)reflect101(y + k - 3, h) * w];
     uint8_t* D = d.row(y);
-    for (int x = 0; x < s.w; x++) {
-      uint32_t acc = 0;
-      for (int k = -3; k <= 3; k++)
-        acc += (uint32_t)kGauss7[k + 3] * tmp[(size_t)reflect101(y + k, s.h) * s.w + x];
+    for (int x = 0; x < w; x++) {
+      uint32_t acc = 18u * (r[0][x] + r[6][x]) + 34u * (r[1][x] + r[5][x]) + 48u * (r[2][x] + r[4][x]) +
+                     56u * r[3][x];
       D[x] = (uint8_t)((acc + 32768u) >> 16);
     }
   }
@@ -227,10 +238,16 @@ static const int kRing[16][2] = {{0, 3},  {1, 3},   {2, 2},   {3, 1},  {3, 0},  
 // threshold t, i.e. max over the 16 contiguous arcs of 9 of max(min(d), min(-d)), d = centre -
 // ring.  corner(th) <=> A > th, and cornerScore<16>() == A - 1 for every corner.
 inline int fast_arc_strength(const int* d /*[25]*/) {
+  // sliding window of 9 over the circular 16: 2-, 4-, 8-wide partial minima/maxima, then +1
+  int mn2[16], mx2[16], mn4[16], mx4[16];
+  for (int k = 0; k < 16; k++) { mn2[k] = std::min(d[k], d[k + 1]); mx2[k] = std::max(d[k], d[k + 1]); }
+  for (int k = 0; k < 16; k++) {
+    mn4[k] = std::min(mn2[k], mn2[(k + 2) & 15]); mx4[k] = std::max(mx2[k], mx2[(k + 2) & 15]);
+  }
   int best = 0;
   for (int k = 0; k < 16; k++) {
-    int mn = d[k], mx = d[k];
-    for (int j = 1; j < 9; j++) { mn = std::min(mn, d[k + j]); mx = std::max(mx, d[k + j]); }
+    int mn = std::min(std::min(mn4[k], mn4[(k + 4) & 15]), d[k + 8]);
+    int mx = std::max(std::max(mx4[k], mx4[(k + 4) & 15]), d[k + 8]);
     best = std::max(best, std::max(mn, -mx));
   }
   return best;
@@ -954,3 +971,76 @@ double oracle_bench_extract(int nfeatures, float scaleFactor, int nlevels, int i
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// CPU baseline of the whole benchmark step (bench.py cpu_baseline / --impl reference):
+// extract every frame (one frame per task, `threads` workers, one Extractor per worker), then
+// match frame f against frame f-1 (mod n) the way bench.py's GPU step does: last-frame keypoints
+// shifted by the known image motion, window th*scale[octave], octave band [o-1,o+1], 64x48 grid
+// lookup (Frame::GetFeaturesInArea) and the first-min loop of SearchByProjection(Frame,Frame)
+// (ORBmatcher.cc:1676-1768).  Returns wall seconds; *total_matches counts best<=TH_HIGH.
+// ---------------------------------------------------------------------------------------------
+extern "C" double oracle_bench_pipeline(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh,
+                                        int flags, const uint8_t* frames, int n_frames, int w, int h, int lap0,
+                                        int lap1, const float* shift_xy, float th, int threads, int do_match,
+                                        long* total_kps, long* total_matches) {
+  const int cap = nfeatures + 3 * nlevels + 64;
+  std::vector<std::vector<KeyPoint>> K(n_frames);
+  std::vector<std::vector<uint8_t>> D(n_frames);
+  std::vector<float> sf(nlevels);
+  auto t0 = std::chrono::steady_clock::now();
+  {
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; t++)
+      pool.emplace_back([&, t]() {
+        Extractor e(nfeatures, scaleFactor, nlevels, iniTh, minTh, flags);
+        if (t == 0) for (int l = 0; l < nlevels; l++) sf[l] = e.mvScaleFactor[l];
+        for (int f = t; f < n_frames; f += threads) {
+          K[f].resize(cap); D[f].resize((size_t)cap * 32);
+          int n = 0;
+          e.extract(frames + (size_t)f * w * h, w, h, w, lap0, lap1, K[f].data(), D[f].data(), cap, &n);
+          K[f].resize(n);
+        }
+      });
+    for (auto& th_ : pool) th_.join();
+  }
+  std::vector<long> matches(threads, 0);
+  if (do_match) {
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; t++)
+      pool.emplace_back([&, t]() {
+        for (int f = t; f < n_frames; f += threads) {
+          const int src = (f + n_frames - 1) % n_frames;
+          const int nq = (int)K[src].size(), nr = (int)K[f].size();
+          std::vector<float> qx(nq), qy(nq), qr(nq);
+          std::vector<int> qmin(nq), qmax(nq), off(nq + 1), idx((size_t)nq * 256 + 16);
+          for (int i = 0; i < nq; i++) {
+            qx[i] = K[src][i].x + shift_xy[2 * f]; qy[i] = K[src][i].y + shift_xy[2 * f + 1];
+            qr[i] = th * sf[K[src][i].octave];
+            qmin[i] = K[src][i].octave - 1; qmax[i] = K[src][i].octave + 1;
+          }
+          int tot = oracle_grid_queries(K[f].data(), nr, 0.f, (float)w, 0.f, (float)h, qx.data(), qy.data(),
+                                        qr.data(), qmin.data(), qmax.data(), nq, off.data(), idx.data(),
+                                        (int)idx.size());
+          if (tot > (int)idx.size()) {
+            idx.resize(tot);
+            oracle_grid_queries(K[f].data(), nr, 0.f, (float)w, 0.f, (float)h, qx.data(), qy.data(), qr.data(),
+                                qmin.data(), qmax.data(), nq, off.data(), idx.data(), (int)idx.size());
+          }
+          std::vector<int8_t> lv(nr);
+          for (int j = 0; j < nr; j++) lv[j] = (int8_t)K[f][j].octave;
+          std::vector<oracle_result> res(nq);
+          oracle_argmin2_csr(D[src].data(), nq, D[f].data(), nr, off.data(), idx.data(), lv.data(), 0, res.data());
+          for (int i = 0; i < nq; i++) if (res[i].best_idx >= 0 && res[i].best_dist <= 100) matches[t]++;
+        }
+      });
+    for (auto& th_ : pool) th_.join();
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  long tk = 0, tm = 0;
+  for (int f = 0; f < n_frames; f++) tk += (long)K[f].size();
+  for (long m : matches) tm += m;
+  if (total_kps) *total_kps = tk;
+  if (total_matches) *total_matches = tm;
+  return std::chrono::duration<double>(t1 - t0).count();
+}

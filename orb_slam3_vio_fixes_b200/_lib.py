@@ -15,6 +15,8 @@ ORBX_OK = 0
 ERRORS = {-1: "ORBX_E_INVALID", -2: "ORBX_E_CUDA", -3: "ORBX_E_CAPACITY", -4: "ORBX_E_NOMEM",
           -5: "ORBX_E_EMPTY", -6: "ORBX_E_NODEVICE"}
 FLAG_STRICT_FP = 1
+FLAG_STAGE_TIMING = 2
+STAGES = ("pyramid", "fast", "octree", "order", "describe")
 TIE_FIRST_MIN, TIE_LAST_MIN = 0, 1
 MAX_LEVELS = 12
 GRID_COLS, GRID_ROWS = 64, 48
@@ -30,8 +32,8 @@ RES_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i2"), ("second_dist",
 SYMBOLS = [
     "orbx_create", "orbx_destroy", "orbx_max_keypoints", "orbx_extract", "orbx_extract_batch_device",
     "orbx_extract_batch_host", "orbx_get_pyramid", "orbx_pyramid_device", "orbx_level_size",
-    "orbx_get_scale_tables", "orbx_debug_level_keypoints", "orbm_argmin2_csr", "orbm_grid_build",
-    "orbm_search_area", "orbm_stereo_rowband", "orbm_knn2_dense", "orbx_version", "orbx_last_error",
+    "orbx_get_scale_tables", "orbx_stage_times", "orbx_debug_level_keypoints", "orbm_argmin2_csr", "orbm_grid_build",
+    "orbm_search_area", "orbm_queries_shift", "orbm_stereo_rowband", "orbm_knn2_dense", "orbx_version", "orbx_last_error",
 ]
 
 
@@ -77,11 +79,14 @@ def lib():
     L.orbx_pyramid_device.argtypes = [vp, i32, i32, C.POINTER(vp), C.POINTER(sz), C.POINTER(i32), C.POINTER(i32)]
     L.orbx_level_size.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32)]
     L.orbx_get_scale_tables.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.orbx_stage_times.argtypes = [vp, vp]
     L.orbx_debug_level_keypoints.argtypes = [vp, i32, i32, i32, vp, i32, C.POINTER(i32)]
     L.orbm_argmin2_csr.argtypes = [vp, i32, vp, i32, vp, vp, vp, i32, vp, vp]
     L.orbm_grid_build.argtypes = [vp, vp, i32, i32, f32, f32, f32, f32, vp, vp, vp]
     L.orbm_search_area.argtypes = [vp, vp, vp, i32, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp, vp,
                                    i32, i32, i32, vp, vp]
+    L.orbm_queries_shift.argtypes = [vp, vp, vp, i32, i32, vp, vp, f32, vp, i32, i32, i32, vp, vp, vp, vp, vp, vp,
+                                     vp, vp]
     L.orbm_stereo_rowband.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, vp, i32, f32, vp, vp, vp]
     L.orbm_knn2_dense.argtypes = [vp, i32, vp, i32, vp, vp, vp]
     L.orbx_version.restype = C.c_char_p

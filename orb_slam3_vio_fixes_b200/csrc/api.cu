@@ -51,6 +51,8 @@ struct orbx_extractor_s {
   // state of the last call
   Level0 last_l0;
   int last_batch = 0;
+  cudaEvent_t ev[ORBX_NUM_STAGES + 1] = {};
+  bool timed = false;
 };
 
 static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
@@ -81,6 +83,8 @@ void orbx_destroy(orbx_handle h) {
   cudaFree(h->gkeys); cudaFree(h->glabels); cudaFree(h->sel); cudaFree(h->sel_cnt); cudaFree(h->dst);
   cudaFree(h->status); cudaFree(h->o_kps); cudaFree(h->o_desc); cudaFree(h->o_n); cudaFree(h->o_mono);
   cudaFree(h->border_tmp);
+  for (int i = 0; i <= ORBX_NUM_STAGES; i++)
+    if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -165,6 +169,8 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   CU(cudaMemset(h->status, 0, sizeof(int32_t)));
   CU(cudaMemset(h->arena, 0, B * P.arena_bytes + 256));
   CU(orbx_octree_set_smem(h->oct_smem));
+  if (cfg->flags & ORBX_FLAG_STAGE_TIMING)
+    for (int i = 0; i <= ORBX_NUM_STAGES; i++) CU(cudaEventCreate(&h->ev[i]));
   h->last_l0.base = h->arena; h->last_l0.frame_stride = P.arena_bytes; h->last_l0.pitch = P.lv[0].pitch;
   *out = h;
   return ORBX_OK;
@@ -175,13 +181,23 @@ int orbx_max_keypoints(orbx_handle h) { return h ? h->plan.max_keypoints : ORBX_
 static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1, OrbxKeyPointDev* d_kps,
                         uint8_t* d_desc, int capacity, int32_t* d_n, int32_t* d_mono, cudaStream_t st) {
   const DevPlan& D = h->dplan;
+  const bool tm = (h->cfg.flags & ORBX_FLAG_STAGE_TIMING) != 0;
+#define STAGE_MARK(i) do { if (tm) CU(cudaEventRecord(h->ev[i], st)); } while (0)
+  STAGE_MARK(0);
   CU(orbx_launch_pyramid(D, l0, h->arena, h->xtaps, h->ytaps, batch, st));
+  STAGE_MARK(1);
   CU(orbx_launch_fast(D, l0, h->arena, h->cell_cnt, h->cand, batch, st));
+  STAGE_MARK(2);
   CU(orbx_launch_octree(D, h->cell_cnt, h->cand, h->gkeys, h->glabels, h->sel, h->sel_cnt, h->status, batch,
                         h->oct_smem, h->oct_smem_keys, h->oct_node_cap, h->oct_max_cells, st));
+  STAGE_MARK(3);
   CU(orbx_launch_order(D, h->sel, h->sel_cnt, lap0, lap1, h->dst, d_n, d_mono, batch, st));
+  STAGE_MARK(4);
   CU(orbx_launch_describe(D, l0, h->arena, h->sel, h->sel_cnt, h->dst, d_kps, d_desc, capacity,
                           (h->cfg.flags & ORBX_FLAG_STRICT_FP) ? 1 : 0, batch, st));
+  STAGE_MARK(5);
+#undef STAGE_MARK
+  h->timed = tm;
   h->last_l0 = l0;
   h->last_batch = batch;
   return ORBX_OK;
@@ -308,6 +324,14 @@ int orbx_get_scale_tables(orbx_handle h, float* scale, float* inv_scale, float* 
     if (inv_sigma2) inv_sigma2[l] = h->plan.inv_sigma2[l];
     if (features_per_level) features_per_level[l] = h->plan.lv[l].nfeat;
   }
+  return ORBX_OK;
+}
+
+int orbx_stage_times(orbx_handle h, float* ms) {
+  if (!h || !ms || !h->timed) return ORBX_E_INVALID;
+  CU(cudaSetDevice(h->device));
+  CU(cudaEventSynchronize(h->ev[ORBX_NUM_STAGES]));
+  for (int i = 0; i < ORBX_NUM_STAGES; i++) CU(cudaEventElapsedTime(&ms[i], h->ev[i], h->ev[i + 1]));
   return ORBX_OK;
 }
 

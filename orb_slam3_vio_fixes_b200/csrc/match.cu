@@ -274,6 +274,35 @@ k_stereo_rowband(const OrbxKeyPointDev* __restrict__ kl, const uint8_t* __restri
   }
 }
 
+
+// ---- window queries for SearchByProjection(Frame&, const Frame&) under a pure image shift ------------
+// The reference projects last-frame map points with the current pose (host geometry, out of scope)
+// and then searches radius th*scale[octave] in the octave band [o+lo, o+hi] (ORBmatcher.cc:1725-1733).
+// For device-resident pipelines the projection of frame `src` into frame f is a per-frame 2-D shift.
+__global__ void __launch_bounds__(256)
+k_queries_shift(const OrbxKeyPointDev* __restrict__ kps, const uint8_t* __restrict__ desc,
+                const int32_t* __restrict__ n_arr, int kp_stride, const int32_t* __restrict__ src_frame,
+                const float* __restrict__ shift_xy, float th, ScaleTab scales, int band_lo, int band_hi,
+                float* __restrict__ qx, float* __restrict__ qy, float* __restrict__ qr, int8_t* __restrict__ qmin,
+                int8_t* __restrict__ qmax, uint8_t* __restrict__ qdesc, int32_t* __restrict__ nq) {
+  const int f = blockIdx.y, src = src_frame[f];
+  const int n = n_arr[src];
+  if (blockIdx.x == 0 && threadIdx.x == 0) nq[f] = n;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const OrbxKeyPointDev kp = kps[(size_t)src * kp_stride + i];
+  const size_t o = (size_t)f * kp_stride + i;
+  qx[o] = f_add(kp.x, shift_xy[2 * f]);
+  qy[o] = f_add(kp.y, shift_xy[2 * f + 1]);
+  qr[o] = f_mul(th, scales.s[kp.octave]);
+  qmin[o] = (int8_t)(kp.octave + band_lo);
+  qmax[o] = (int8_t)(kp.octave + band_hi);
+  const uint4* s4 = reinterpret_cast<const uint4*>(desc + ((size_t)src * kp_stride + i) * 32);
+  uint4* d4 = reinterpret_cast<uint4*>(qdesc + o * 32);
+  d4[0] = s4[0];
+  d4[1] = s4[1];
+}
+
 // ---- cv::BFMatcher(NORM_HAMMING).knnMatch(k=2) (Frame.cc:1144) ------------------------------------
 __global__ void __launch_bounds__(M_WARPS * 32)
 k_knn2_dense(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ r, int nr,
@@ -352,6 +381,25 @@ int orbm_stereo_rowband(const orbx_keypoint* d_kps_l, const uint8_t* d_desc_l, c
   k_stereo_rowband<<<grd, M_WARPS * 32, 0, (cudaStream_t)stream>>>(
       (const OrbxKeyPointDev*)d_kps_l, d_desc_l, d_n_l, (const OrbxKeyPointDev*)d_kps_r, d_desc_r, d_n_r, kp_stride, st,
       max_d, d_best_idx_r, d_best_dist);
+  CUM(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbm_queries_shift(const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n, int kp_stride,
+                       int batch, const int32_t* d_src_frame, const float* d_shift_xy, float th,
+                       const float* scale_factors_host, int nlevels, int band_lo, int band_hi, float* d_qx,
+                       float* d_qy, float* d_qr, int8_t* d_qmin_level, int8_t* d_qmax_level, uint8_t* d_qdesc,
+                       int32_t* d_nq, void* stream) {
+  if (!d_kps || !d_desc || !d_n || !d_src_frame || !d_shift_xy || !scale_factors_host || !d_qx || !d_qy ||
+      !d_qr || !d_qmin_level || !d_qmax_level || !d_qdesc || !d_nq || batch < 1 || nlevels < 1 ||
+      nlevels > ORBX_MAX_LEVELS)
+    return ORBX_E_INVALID;
+  ScaleTab st;
+  for (int i = 0; i < ORBX_MAX_LEVELS; i++) st.s[i] = i < nlevels ? scale_factors_host[i] : 1.0f;
+  dim3 grd((kp_stride + 255) / 256, batch);
+  k_queries_shift<<<grd, 256, 0, (cudaStream_t)stream>>>((const OrbxKeyPointDev*)d_kps, d_desc, d_n, kp_stride,
+                                                         d_src_frame, d_shift_xy, th, st, band_lo, band_hi, d_qx, d_qy,
+                                                         d_qr, d_qmin_level, d_qmax_level, d_qdesc, d_nq);
   CUM(cudaGetLastError());
   return ORBX_OK;
 }

@@ -18,11 +18,11 @@ class ORBextractor:
     HARRIS_SCORE, FAST_SCORE = 0, 1
 
     def __init__(self, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, *, max_batch=1, device=0,
-                 strict_fp=False):
+                 strict_fp=False, stage_timing=False):
         self.nfeatures, self.scaleFactor, self.nlevels = int(nfeatures), float(scaleFactor), int(nlevels)
         self.iniThFAST, self.minThFAST = int(iniThFAST), int(minThFAST)
         self.max_batch, self.device = int(max_batch), int(device)
-        self.flags = _lib.FLAG_STRICT_FP if strict_fp else 0
+        self.flags = (_lib.FLAG_STRICT_FP if strict_fp else 0) | (_lib.FLAG_STAGE_TIMING if stage_timing else 0)
         self._h = None
         self._size = None
 
@@ -178,6 +178,12 @@ class ORBextractor:
             full = self.GetPyramid(level, with_border=True)
             out.append(full[19:-19, 19:-19])
         return out
+
+    def stage_times(self):
+        """Device milliseconds of each stage of the last call: dict stage -> ms (needs stage_timing=True)."""
+        ms = np.zeros(len(_lib.STAGES), np.float32)
+        _lib.check(_lib.lib().orbx_stage_times(self._h, ms.ctypes.data), "orbx_stage_times")
+        return dict(zip(_lib.STAGES, ms.tolist()))
 
     def debug_level_keypoints(self, level, stage, frame=0):
         cap = 1 << 16

@@ -84,6 +84,31 @@ class ORBmatcher:
         return out
 
     @staticmethod
+    def queries_shift(kps, desc, n, src_frame, shift_xy, th, scale_factors, band=(-1, 1), out=None):
+        """Window queries of SearchByProjection(Frame, Frame) for a per-frame image shift.
+        src_frame [B] i32, shift_xy [B,2] f32.  Returns dict(qx,qy,qr,qmin,qmax,qdesc,nq)."""
+        import torch
+        b, cap = kps.shape[0], kps.shape[1]
+        dev = kps.device
+        if out is None:
+            out = {"qx": torch.zeros((b, cap), dtype=torch.float32, device=dev),
+                   "qy": torch.zeros((b, cap), dtype=torch.float32, device=dev),
+                   "qr": torch.zeros((b, cap), dtype=torch.float32, device=dev),
+                   "qmin": torch.zeros((b, cap), dtype=torch.int8, device=dev),
+                   "qmax": torch.zeros((b, cap), dtype=torch.int8, device=dev),
+                   "qdesc": torch.zeros((b, cap, 32), dtype=torch.uint8, device=dev),
+                   "nq": torch.zeros(b, dtype=torch.int32, device=dev)}
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        rc = _lib.lib().orbm_queries_shift(kps.data_ptr(), desc.data_ptr(), n.data_ptr(), cap, b,
+                                           src_frame.data_ptr(), shift_xy.data_ptr(), float(th), sf.ctypes.data,
+                                           sf.size, int(band[0]), int(band[1]), out["qx"].data_ptr(),
+                                           out["qy"].data_ptr(), out["qr"].data_ptr(), out["qmin"].data_ptr(),
+                                           out["qmax"].data_ptr(), out["qdesc"].data_ptr(), out["nq"].data_ptr(),
+                                           _stream(dev))
+        _lib.check(rc, "orbm_queries_shift")
+        return out
+
+    @staticmethod
     def stereo_rowband(kps_l, desc_l, n_l, kps_r, desc_r, n_r, scale_factors, max_d):
         """Hamming stage of Frame::ComputeStereoMatches.  Returns (best_idx_r [B,cap] i32, best_dist [B,cap] i32)."""
         import torch

@@ -1,0 +1,169 @@
+"""GPU parity of the matcher kernels (through the C ABI) against the oracle's restated loops."""
+import numpy as np
+import pytest
+
+from orb_slam3_vio_fixes_b200 import synthetic as S
+from orb_slam3_vio_fixes_b200.extractor import ORBextractor
+from orb_slam3_vio_fixes_b200.matcher import ORBmatcher, results_to_numpy, TIE_FIRST_MIN, TIE_LAST_MIN
+
+pytestmark = pytest.mark.gpu
+ORB = dict(scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7)
+
+
+def _t(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _same_results(got, ref, with_second=True):
+    assert np.array_equal(got["best_idx"], ref["best_idx"])
+    assert np.array_equal(got["best_dist"], ref["best_dist"])
+    assert np.array_equal(got["best_level"], ref["best_level"])
+    if with_second:
+        assert np.array_equal(got["second_dist"], ref["second_dist"])
+        assert np.array_equal(got["second_level"], ref["second_level"])
+
+
+@pytest.mark.parametrize("tie_rule", [TIE_FIRST_MIN, TIE_LAST_MIN])
+def test_argmin2_csr_random_with_ties(oracle_mod, tie_rule):
+    rng = np.random.default_rng(7)
+    nq, nr = 700, 900
+    base = rng.integers(0, 256, (40, 32), dtype=np.uint8)
+    # few distinct descriptors with 0-2 flipped bits => plenty of exact distance ties
+    r = base[rng.integers(0, 40, nr)].copy()
+    q = base[rng.integers(0, 40, nq)].copy()
+    for a in (r, q):
+        flip = rng.integers(0, 3, len(a))
+        for i, k in enumerate(flip):
+            for _ in range(k):
+                a[i, rng.integers(0, 32)] ^= np.uint8(1 << rng.integers(0, 8))
+    lens = rng.integers(0, 90, nq)
+    lens[:5] = [0, 1, 2, 33, 64]
+    off = np.zeros(nq + 1, np.int32)
+    off[1:] = np.cumsum(lens)
+    idx = rng.integers(0, nr, off[-1]).astype(np.int32)
+    lv = rng.integers(0, 8, nr).astype(np.int8)
+    ref = oracle_mod.argmin2_csr(q, r, off, idx, lv, tie_rule)
+    got = results_to_numpy(ORBmatcher.argmin2_csr(_t(q), _t(r), _t(off), _t(idx), _t(lv), tie_rule))
+    _same_results(got, ref, with_second=(tie_rule == TIE_FIRST_MIN))
+
+
+def test_knn2_dense(oracle_mod):
+    rng = np.random.default_rng(8)
+    q = rng.integers(0, 256, (333, 32), dtype=np.uint8)
+    r = rng.integers(0, 256, (1201, 32), dtype=np.uint8)
+    r[100] = r[7]
+    q[5] = r[7]
+    idx, dist = ORBmatcher.knn2_dense(_t(q), _t(r))
+    ridx, rdist = oracle_mod.knn2_dense(q, r)
+    assert np.array_equal(idx.cpu().numpy(), ridx) and np.array_equal(dist.cpu().numpy(), rdist)
+    idx, dist = ORBmatcher.knn2_dense(_t(q[:3]), _t(r[:1]))   # a single reference: no second
+    assert np.array_equal(idx.cpu().numpy()[:, 1], [-1, -1, -1])
+
+
+def _extract_batch(ex, frames, lap):
+    import torch
+    out = ex.extract_batch_device(_t(frames), lap)
+    torch.cuda.synchronize()
+    return out
+
+
+def test_grid_search_area_matches_reference_loops(oracle_mod):
+    """C1 match shape: frame t-1 keypoints shifted into frame t, window 15*scale, band [o-1,o+1]."""
+    import torch
+    from bench import shifts_for
+    B = 4
+    frames = S.make_frames("C1", B)
+    ex = ORBextractor(1000, max_batch=B, **ORB)
+    out = _extract_batch(ex, frames, (0, 1000))
+    sf = ex.GetScaleFactors()
+    bounds = (0.0, 752.0, 0.0, 480.0)
+    shift = shifts_for(0, B)
+    src = ((np.arange(B) - 1) % B).astype(np.int32)
+    grid = ORBmatcher.grid_build(out["kps"], out["n"], bounds)
+    qb = ORBmatcher.queries_shift(out["kps"], out["desc"], out["n"], _t(src), _t(shift), 15.0, sf, (-1, 1))
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    n = out["n"].cpu().numpy()
+    for tie in (TIE_FIRST_MIN, TIE_LAST_MIN):
+        res = results_to_numpy(ORBmatcher.search_area(out["kps"], out["desc"], out["n"], grid, bounds, qb["qx"],
+                                                      qb["qy"], qb["qr"], qb["qmin"], qb["qmax"], qb["qdesc"],
+                                                      qb["nq"], tie))
+        total_cand = 0
+        for f in range(B):
+            s = src[f]
+            k_ref, k_q = kps[f, :n[f]], kps[s, :n[s]]
+            qx = k_q["x"] + shift[f, 0]
+            qy = k_q["y"] + shift[f, 1]
+            qr = (np.float32(15.0) * sf[k_q["octave"]]).astype(np.float32)
+            assert np.array_equal(qb["qx"][f, :n[s]].cpu().numpy(), qx)
+            assert np.array_equal(qb["qr"][f, :n[s]].cpu().numpy(), qr)
+            off, idx = oracle_mod.grid_queries(k_ref, bounds, qx, qy, qr, k_q["octave"] - 1, k_q["octave"] + 1)
+            total_cand += len(idx)
+            ref = oracle_mod.argmin2_csr(desc[s, :n[s]], desc[f, :n[f]], off, idx, k_ref["octave"].astype(np.int8), tie)
+            _same_results(res[f, :n[s]], ref, with_second=(tie == TIE_FIRST_MIN))
+            # and the explicit-CSR kernel on the same lists
+            got2 = results_to_numpy(ORBmatcher.argmin2_csr(_t(desc[s, :n[s]]), _t(desc[f, :n[f]]), _t(off), _t(idx),
+                                                           _t(k_ref["octave"].astype(np.int8)), tie))
+            _same_results(got2, ref, with_second=(tie == TIE_FIRST_MIN))
+        assert total_cand > 10 * B * 900  # the windows really contain candidates
+        good = (res[1, :n[0]]["best_dist"] <= 100).mean()
+        assert good > 0.7  # consecutive synthetic frames do match
+
+
+def test_grid_build_is_the_reference_grid(oracle_mod):
+    """CSR cells == mGrid[ix][iy] push_back order: queries that cover one whole cell column."""
+    B = 2
+    frames = S.make_frames("C3", B)
+    ex = ORBextractor(1000, max_batch=B, **ORB)
+    out = _extract_batch(ex, frames, (0, 0))
+    bounds = (0.0, 640.0, 0.0, 480.0)
+    cell_off, cell_idx = ORBmatcher.grid_build(out["kps"], out["n"], bounds)
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    n = out["n"].cpu().numpy()
+    co, ci = cell_off.cpu().numpy(), cell_idx.cpu().numpy()
+    for f in range(B):
+        k = kps[f, :n[f]]
+        import ctypes
+        libm = ctypes.CDLL("libm.so.6")
+        libm.roundf.restype = ctypes.c_float
+        libm.roundf.argtypes = [ctypes.c_float]
+        rnd = np.vectorize(lambda v: int(libm.roundf(float(v))))  # PosInGrid uses C round()
+        px = rnd((k["x"] - np.float32(0)) * (np.float32(64) / np.float32(640)))
+        py = rnd((k["y"] - np.float32(0)) * (np.float32(48) / np.float32(480)))
+        ok = (px >= 0) & (px < 64) & (py >= 0) & (py < 48)
+        cell = px * 48 + py
+        assert co[f, -1] == ok.sum()
+        for c in np.unique(cell[ok])[:400]:
+            members = np.nonzero(ok & (cell == c))[0]
+            assert np.array_equal(ci[f, co[f, c]:co[f, c + 1]], members)
+
+
+def test_stereo_rowband(oracle_mod):
+    """C2 shape: left/right extraction, then the Hamming stage of ComputeStereoMatches."""
+    B = 2
+    left = S.make_frames("C2", B)
+    right = S.make_frames("C2", B, right=True)
+    exl = ORBextractor(1200, max_batch=B, **ORB)
+    exr = ORBextractor(1200, max_batch=B, **ORB)
+    ol = _extract_batch(exl, left, (0, 0))
+    orr = _extract_batch(exr, right, (0, 0))
+    sf, isf = exl.GetScaleFactors(), exl.GetInverseScaleFactors()
+    fx, bf = 458.654, 47.90639384423901  # Stereo-Inertial/EuRoC.yaml: maxD = mbf/mb = fx
+    mb = bf / fx
+    bi, bd = ORBmatcher.stereo_rowband(ol["kps"], ol["desc"], ol["n"], orr["kps"], orr["desc"], orr["n"], sf,
+                                       np.float32(bf) / np.float32(mb))
+    kl, kr = ORBextractor.kps_from_tensor(ol["kps"]), ORBextractor.kps_from_tensor(orr["kps"])
+    dl, dr = ol["desc"].cpu().numpy(), orr["desc"].cpu().numpy()
+    nl, nr = ol["n"].cpu().numpy(), orr["n"].cpu().numpy()
+    for f in range(B):
+        pl = [exl.GetPyramid(l, frame=f) for l in range(8)]
+        pr = [exr.GetPyramid(l, frame=f) for l in range(8)]
+        rbi, rbd, ur, dp, kept = oracle_mod.stereo_matches(kl[f, :nl[f]], dl[f, :nl[f]], kr[f, :nr[f]], dr[f, :nr[f]],
+                                                           sf, isf, pl, pr, np.float32(mb), np.float32(bf))
+        assert np.array_equal(bi[f, :nl[f]].cpu().numpy(), rbi)
+        assert np.array_equal(bd[f, :nl[f]].cpu().numpy(), rbd)
+        assert (rbi >= 0).sum() > 300 and kept > 100
+        # constant 24 px disparity in the synthetic pair
+        ok = ur > 0
+        assert np.median(kl[f, :nl[f]]["x"][ok] - ur[ok]) == pytest.approx(24.0, abs=0.5)
