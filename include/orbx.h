@@ -9,7 +9,8 @@
  *
  * Conventions: plain pointers and sizes only; every function returns 0 (ORBX_OK) or a
  * negative ORBX_E_* code; nothing throws, nothing aborts.  "d_" pointers are CUDA device
- * pointers, `stream` is a cudaStream_t passed as void* (NULL = the handle's own stream).
+ * pointers, `stream` is a cudaStream_t passed as void* and used as given (NULL = CUDA's
+ * default stream); the host-buffer entry points run on a private stream of the handle.
  * A handle is single-caller (like an ORBextractor instance, ORBextractor.h:83 mutable
  * mvImagePyramid); distinct handles may be used concurrently from different threads, as
  * Frame.cc:122-125 does for the left/right extractors.

@@ -213,7 +213,7 @@ int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch
   Level0 l0;
   l0.base = d_imgs; l0.frame_stride = (long long)frame_stride; l0.pitch = (int)pitch;
   return run_pipeline(h, l0, batch, lap0, lap1, (OrbxKeyPointDev*)d_kps, d_desc, capacity, d_n_out, d_mono_index,
-                      stream ? (cudaStream_t)stream : h->stream);
+                      (cudaStream_t)stream);
 }
 
 int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int lap0, int lap1,
@@ -301,6 +301,7 @@ int orbx_get_pyramid(orbx_handle h, int frame, int level, uint8_t* dst, size_t d
   if (rc) return rc;
   if (!dst) return ORBX_E_INVALID;
   CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());  // the last call may have run on a caller stream
   if (!with_border) {
     if (dst_stride < (size_t)w) return ORBX_E_INVALID;
     CU(cudaMemcpy2DAsync(dst, dst_stride, p, pitch, w, hh, cudaMemcpyDeviceToHost, h->stream));
@@ -341,7 +342,7 @@ int orbx_debug_level_keypoints(orbx_handle h, int frame, int level, int stage, i
   const OrbxPlan& P = h->plan;
   const OrbxLevel& L = P.lv[level];
   CU(cudaSetDevice(h->device));
-  CU(cudaStreamSynchronize(h->stream));
+  CU(cudaDeviceSynchronize());
   std::vector<uint32_t> keys;
   if (stage == 0) {
     const int ncell = L.nCols * L.nRows;

@@ -91,20 +91,26 @@ cudaError_t orbx_launch_border(const uint8_t* src, int pitch, int w, int h, uint
 // The reference runs cv::FAST on each ~35-px cell ROI (6 px overlap).  cv::FAST tests ROI pixels
 // [3,W-3)x[3,H-3), so the tested zones of the cells tile [19,w-19)x[19,h-19) exactly on a
 // (wCell,hCell) lattice; the NMS of a cell only sees that cell's own zone (outside = score 0).
-// One CTA = one cell of one level of one frame:
-//   1. stage the zone + 3-px halo in shared memory,
-//   2. arc strength A per zone pixel (threshold independent; cornerScore = A-1),
-//   3. NMS at iniThFAST; if the cell ends up empty, NMS again at minThFAST (:843-859),
-//   4. ordered (row-major) compaction into the cell's slot array.
+// One CTA = one cell of one level of one frame.  The work is organised around compacted lists so
+// that warps stay converged:
+//   1. stage the zone + 3-px halo in shared memory (32-bit loads),
+//   2. quick test on every zone pixel (4 opposite ring pairs) -> ordered list of survivors,
+//   3. arc strength A for the listed pixels only (cornerScore = A-1, threshold independent),
+//   4. NMS of the corners at iniThFAST; if none survives, NMS again at minThFAST (:843-859),
+//   5. ordered (row-major) emission into the cell's slot array.
 // ------------------------------------------------------------------------------------------------
 #define FAST_THREADS 256
-#define FAST_MAX_CELL 70  // wCell,hCell < 70 by construction (width/35 cells)
+#define FAST_WARPS (FAST_THREADS / 32)
+#define FAST_MAX_CELL 70                                 // wCell,hCell < 70 by construction
+#define FAST_PXW ((FAST_MAX_CELL + 6 + 3 + 3) / 4 + 1)   // words per staged row
+#define FAST_MAX_GROUPS ((FAST_MAX_CELL * FAST_MAX_CELL + 31) / 32)
 
 struct FastSmem {
-  uint8_t px[(FAST_MAX_CELL + 6) * (FAST_MAX_CELL + 8)];  // zone + halo, pitch = zw+6 (<=76) rounded
+  uint32_t px[FAST_PXW * (FAST_MAX_CELL + 6)];              // zone + halo, word-aligned rows
   uint8_t amap[(FAST_MAX_CELL + 2) * (FAST_MAX_CELL + 2)];  // A with a zero ring
-  int gcount[(FAST_MAX_CELL * FAST_MAX_CELL + 31) / 32 + 1];
-  int any;
+  uint32_t mask[FAST_MAX_GROUPS + 1];                       // ballots of a compaction pass
+  int goff[FAST_MAX_GROUPS + 2];                            // their exclusive scan
+  uint16_t list[FAST_MAX_CELL * FAST_MAX_CELL];             // pixels that pass the quick test
 };
 
 __device__ __forceinline__ bool nms_keep(const uint8_t* a, int ap, int th) {
@@ -118,11 +124,30 @@ __device__ __forceinline__ bool nms_keep(const uint8_t* a, int ap, int th) {
   return true;
 }
 
+// exclusive scan of popc(mask[g]), g < ngroups, by warp 0; goff[ngroups] = total
+__device__ __forceinline__ void scan_groups(FastSmem& sm, int ngroups, int lane) {
+  int carry = 0;
+  for (int base = 0; base < ngroups; base += 32) {
+    const int g = base + lane;
+    const int v = g < ngroups ? __popc(sm.mask[g]) : 0;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (g < ngroups) sm.goff[g] = carry + inc - v;
+    carry += __shfl_sync(0xffffffffu, inc, 31);
+  }
+  if (lane == 0) sm.goff[ngroups] = carry;
+}
+
 __global__ void __launch_bounds__(FAST_THREADS)
 k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
        int32_t* __restrict__ cell_cnt, uint32_t* __restrict__ cand) {
   __shared__ FastSmem sm;
   const int frame = blockIdx.y;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   int cell = blockIdx.x;
   int level = 0;
 #pragma unroll 1
@@ -137,105 +162,127 @@ k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__
   const int zw = zx1 - zx0, zh = zy1 - zy0;
   int32_t* cnt_out = cell_cnt + (long long)frame * P.total_cells + L.cell_base + cell;
   if (zw <= 0 || zh <= 0) {  // cell skipped / empty in the reference (:810,:819)
-    if (threadIdx.x == 0) *cnt_out = 0;
+    if (tid == 0) *cnt_out = 0;
     return;
   }
   int pitch;
   const uint8_t* img = level_ptr(P, l0, arena, frame, level, &pitch);
-  const int pp = zw + 6;  // px pitch
   const int ap = zw + 2;  // amap pitch
-  // 1. stage pixels [zx0-3, zx1+3) x [zy0-3, zy1+3)
-  for (int i = threadIdx.x; i < pp * (zh + 6); i += FAST_THREADS) {
-    const int y = i / pp, x = i - y * pp;
-    sm.px[i] = img[(long long)(zy0 - 3 + y) * pitch + (zx0 - 3 + x)];
+  const int npx = zw * zh;
+  const uint32_t rcp = ((1u << 20) + zw - 1) / zw;  // i/zw == (i*rcp)>>20 for i*zw < 2^20
+
+  // 1. stage pixels [zx0-3, zx1+3) x [zy0-3, zy1+3); row r, column c at pxb[r*pwb + c]
+  const uint8_t* tile0 = img + (long long)(zy0 - 3) * pitch + (zx0 - 3);
+  int sh, pwb;
+  if ((pitch & 3) == 0) {
+    sh = (int)((uintptr_t)tile0 & 3);
+    const int nw = (sh + zw + 6 + 3) >> 2;  // words per row
+    pwb = nw * 4;
+    const uint8_t* a0 = tile0 - sh;
+    const uint32_t rcw = ((1u << 20) + nw - 1) / nw;
+    for (int i = tid; i < nw * (zh + 6); i += FAST_THREADS) {
+      const int r = (int)(((uint32_t)i * rcw) >> 20), c = i - r * nw;
+      sm.px[i] = __ldg(reinterpret_cast<const uint32_t*>(a0 + (long long)r * pitch) + c);
+    }
+  } else {
+    sh = 0;
+    pwb = (zw + 6 + 3) & ~3;
+    uint8_t* pb = reinterpret_cast<uint8_t*>(sm.px);
+    for (int i = tid; i < (zw + 6) * (zh + 6); i += FAST_THREADS) {
+      const int r = i / (zw + 6), c = i - r * (zw + 6);
+      pb[r * pwb + c] = tile0[(long long)r * pitch + c];
+    }
   }
-  for (int i = threadIdx.x; i < ap * (zh + 2); i += FAST_THREADS) sm.amap[i] = 0;
-  if (threadIdx.x == 0) sm.any = 0;
+  for (int i = tid; i < (ap * (zh + 2) + 3) >> 2; i += FAST_THREADS) reinterpret_cast<uint32_t*>(sm.amap)[i] = 0;
   __syncthreads();
-  // 2. arc strength
+  const uint8_t* pxb = reinterpret_cast<const uint8_t*>(sm.px) + sh;
+
+  // 2. quick test: every arc of 9 holds one pixel of each opposite ring pair, so a corner at
+  //    threshold t needs, for all four pairs (0,8)(4,12)(2,10)(6,14), a member darker than v-t —
+  //    or, for all four, a member brighter than v+t.
   const int tmin = min(P.ini_th, P.min_th);
-  const int o1 = pp, o2 = 2 * pp, o3 = 3 * pp;
-  for (int i = threadIdx.x; i < zw * zh; i += FAST_THREADS) {
-    const int y = i / zw, x = i - y * zw;
-    const uint8_t* c = sm.px + (y + 3) * pp + (x + 3);
-    const int v = c[0];
+  const int o1 = pwb, o2 = 2 * pwb, o3 = 3 * pwb;
+  const int ngroups = (npx + 31) >> 5;
+  for (int g = warp; g < ngroups; g += FAST_WARPS) {
+    const int i = g * 32 + lane;
+    bool pass = false;
+    if (i < npx) {
+      const int y = (int)(((uint32_t)i * rcp) >> 20), x = i - y * zw;
+      const uint8_t* c = pxb + (y + 3) * pwb + (x + 3);
+      const int v = c[0], lo = v - tmin, hi = v + tmin;
+      const int r0 = c[o3], r8 = c[-o3], r4 = c[3], r12 = c[-3];
+      const int r2 = c[o2 + 2], r10 = c[-o2 - 2], r6 = c[-o2 + 2], r14 = c[o2 - 2];
+      const bool dark = ((r0 < lo) | (r8 < lo)) & ((r4 < lo) | (r12 < lo)) & ((r2 < lo) | (r10 < lo)) &
+                        ((r6 < lo) | (r14 < lo));
+      const bool bright = ((r0 > hi) | (r8 > hi)) & ((r4 > hi) | (r12 > hi)) & ((r2 > hi) | (r10 > hi)) &
+                          ((r6 > hi) | (r14 > hi));
+      pass = dark | bright;
+    }
+    const unsigned b = __ballot_sync(0xffffffffu, pass);
+    if (lane == 0) sm.mask[g] = b;
+  }
+  __syncthreads();
+  if (warp == 0) scan_groups(sm, ngroups, lane);
+  __syncthreads();
+  for (int g = warp; g < ngroups; g += FAST_WARPS) {
+    const unsigned b = sm.mask[g];
+    if ((b >> lane) & 1u) sm.list[sm.goff[g] + __popc(b & ((1u << lane) - 1))] = (uint16_t)(g * 32 + lane);
+  }
+  const int nlist = sm.goff[ngroups];
+  __syncthreads();
+
+  // 3. arc strength of the listed pixels (dense: warps stay converged)
+  for (int e = tid; e < nlist; e += FAST_THREADS) {
+    const int i = sm.list[e];
+    const int y = (int)(((uint32_t)i * rcp) >> 20), x = i - y * zw;
+    const uint8_t* c = pxb + (y + 3) * pwb + (x + 3);
     // OpenCV ring order: (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)(-1,-3)(-2,-2)(-3,-1)
     //                    (-3,0)(-3,1)(-2,2)(-1,3)
     int ring[16];
-    ring[0] = c[o3]; ring[8] = c[-o3];
-    const int lo = v - tmin, hi = v + tmin;
-    // every arc of 9 holds one pixel of each opposite pair: quick reject on 4 pairs
-    int m = ((ring[0] < lo) | ((ring[0] > hi) << 1)) | ((ring[8] < lo) | ((ring[8] > hi) << 1));
-    if (m == 0) continue;
-    ring[4] = c[3]; ring[12] = c[-3];
-    m &= ((ring[4] < lo) | ((ring[4] > hi) << 1)) | ((ring[12] < lo) | ((ring[12] > hi) << 1));
-    if (m == 0) continue;
-    ring[2] = c[o2 + 2]; ring[10] = c[-o2 - 2];
-    m &= ((ring[2] < lo) | ((ring[2] > hi) << 1)) | ((ring[10] < lo) | ((ring[10] > hi) << 1));
-    if (m == 0) continue;
-    ring[6] = c[-o2 + 2]; ring[14] = c[o2 - 2];
-    m &= ((ring[6] < lo) | ((ring[6] > hi) << 1)) | ((ring[14] < lo) | ((ring[14] > hi) << 1));
-    if (m == 0) continue;
-    ring[1] = c[o3 + 1]; ring[3] = c[o1 + 3]; ring[5] = c[-o1 + 3]; ring[7] = c[-o3 + 1];
-    ring[9] = c[-o3 - 1]; ring[11] = c[-o1 - 3]; ring[13] = c[o1 - 3]; ring[15] = c[o3 - 1];
-    const int A = orbx_arc_strength(v, ring);
+    ring[0] = c[o3]; ring[1] = c[o3 + 1]; ring[2] = c[o2 + 2]; ring[3] = c[o1 + 3];
+    ring[4] = c[3]; ring[5] = c[-o1 + 3]; ring[6] = c[-o2 + 2]; ring[7] = c[-o3 + 1];
+    ring[8] = c[-o3]; ring[9] = c[-o3 - 1]; ring[10] = c[-o2 - 2]; ring[11] = c[-o1 - 3];
+    ring[12] = c[-3]; ring[13] = c[o1 - 3]; ring[14] = c[o2 - 2]; ring[15] = c[o3 - 1];
+    const int A = orbx_arc_strength(c[0], ring);
     if (A > tmin) sm.amap[(y + 1) * ap + (x + 1)] = (uint8_t)A;
   }
   __syncthreads();
-  // 3. NMS at iniTh; fall back to minTh if the cell has no survivor
-  int any = 0;
-  for (int i = threadIdx.x; i < zw * zh; i += FAST_THREADS) {
-    const int y = i / zw, x = i - y * zw;
-    any |= nms_keep(sm.amap + (y + 1) * ap + (x + 1), ap, P.ini_th);
+
+  // 4. NMS over the listed pixels at iniTh; fall back to minTh if the cell has no survivor.
+  //    keep bit k of `mine` belongs to list entry tid + k*FAST_THREADS (k < 20).
+  uint32_t mine = 0;
+  for (int e = tid, k = 0; e < nlist; e += FAST_THREADS, k++) {
+    const int i = sm.list[e];
+    const int y = (int)(((uint32_t)i * rcp) >> 20), x = i - y * zw;
+    if (nms_keep(sm.amap + (y + 1) * ap + (x + 1), ap, P.ini_th)) mine |= 1u << k;
   }
-  any = __syncthreads_or(any);
-  const int th = any ? P.ini_th : P.min_th;
-  // 4. ordered compaction: 32-pixel groups, ballot per group, scan of group counts
-  const int npx = zw * zh, ngroups = (npx + 31) >> 5;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int g = warp; g < ngroups; g += FAST_THREADS / 32) {
-    const int i = g * 32 + lane;
-    bool k = false;
-    if (i < npx) {
-      const int y = i / zw, x = i - y * zw;
-      k = nms_keep(sm.amap + (y + 1) * ap + (x + 1), ap, th);
+  const int any = __syncthreads_or(mine != 0);
+  if (!any) {
+    for (int e = tid, k = 0; e < nlist; e += FAST_THREADS, k++) {
+      const int i = sm.list[e];
+      const int y = (int)(((uint32_t)i * rcp) >> 20), x = i - y * zw;
+      if (nms_keep(sm.amap + (y + 1) * ap + (x + 1), ap, P.min_th)) mine |= 1u << k;
     }
-    const unsigned b = __ballot_sync(0xffffffffu, k);
-    if (lane == 0) sm.gcount[g] = __popc(b);
+  }
+  // 5. ordered emission: list entries e = k*256 + warp*32 + lane form group k*8 + warp
+  const int ng2 = (nlist + 31) >> 5;
+  for (int e = tid, k = 0; e - lane < nlist; e += FAST_THREADS, k++) {
+    const unsigned b = __ballot_sync(0xffffffffu, (mine >> k) & 1u);
+    if (lane == 0) sm.mask[k * FAST_WARPS + warp] = b;
   }
   __syncthreads();
-  if (warp == 0) {  // exclusive scan of gcount (ngroups <= 154)
-    int carry = 0;
-    for (int base = 0; base < ngroups; base += 32) {
-      const int g = base + lane;
-      int v = g < ngroups ? sm.gcount[g] : 0;
-      int inc = v;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += t;
-      }
-      if (g < ngroups) sm.gcount[g] = carry + inc - v;
-      carry += __shfl_sync(0xffffffffu, inc, 31);
-    }
-    if (lane == 0) {
-      sm.gcount[ngroups] = carry;
-      *cnt_out = carry;
-    }
+  if (warp == 0) {
+    scan_groups(sm, ng2, lane);
+    if (lane == 0) *cnt_out = sm.goff[ng2];
   }
   __syncthreads();
   uint32_t* out = cand + (long long)frame * P.cand_total + L.cand_base + (long long)cell * L.cell_cap;
-  for (int g = warp; g < ngroups; g += FAST_THREADS / 32) {
-    const int i = g * 32 + lane;
-    bool k = false;
-    int x = 0, y = 0;
-    if (i < npx) {
-      y = i / zw; x = i - y * zw;
-      k = nms_keep(sm.amap + (y + 1) * ap + (x + 1), ap, th);
-    }
-    const unsigned b = __ballot_sync(0xffffffffu, k);
-    if (k) {
-      const int pos = sm.gcount[g] + __popc(b & ((1u << lane) - 1));
+  for (int e = tid, k = 0; e < nlist; e += FAST_THREADS, k++) {
+    if ((mine >> k) & 1u) {
+      const int g = k * FAST_WARPS + warp;
+      const int pos = sm.goff[g] + __popc(sm.mask[g] & ((1u << lane) - 1));
+      const int i = sm.list[e];
+      const int y = (int)(((uint32_t)i * rcp) >> 20), x = i - y * zw;
       // coordinates relative to (minBorderX,minBorderY)=(16,16), as DistributeOctTree sees them
       out[pos] = orbx_pack_key(zx0 + x - ORBX_MIN_BORDER, zy0 + y - ORBX_MIN_BORDER,
                                sm.amap[(y + 1) * ap + (x + 1)] - 1);

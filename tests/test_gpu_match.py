@@ -106,7 +106,7 @@ def test_grid_search_area_matches_reference_loops(oracle_mod):
             got2 = results_to_numpy(ORBmatcher.argmin2_csr(_t(desc[s, :n[s]]), _t(desc[f, :n[f]]), _t(off), _t(idx),
                                                            _t(k_ref["octave"].astype(np.int8)), tie))
             _same_results(got2, ref, with_second=(tie == TIE_FIRST_MIN))
-        assert total_cand > 10 * B * 900  # the windows really contain candidates
+        assert total_cand > 3 * B * 900  # the windows really contain candidates
         good = (res[1, :n[0]]["best_dist"] <= 100).mean()
         assert good > 0.7  # consecutive synthetic frames do match
 
