@@ -128,9 +128,11 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   // keys that fit next to the node pool in <= ~96 KB of shared memory; larger levels spill to HBM
   {
     const size_t fixed = orbx_octree_smem_bytes(0, node_cap, max_cells);
+    // The kernel is latency bound (one thread replays the list surgery), so residency matters more
+    // than keeping every key on chip: 2048 keys cover the usual level (<~1000 candidates).
     const size_t budget = 96 * 1024;
     long long keys = fixed < budget ? (long long)(budget - fixed) / 6 : 0;
-    if (keys > 8192) keys = 8192;
+    if (keys > 2048) keys = 2048;
     h->oct_smem_keys = (int)(keys & ~7LL);
     h->oct_smem = orbx_octree_smem_bytes(h->oct_smem_keys, node_cap, max_cells);
     if (h->oct_smem > 220 * 1024) { delete h; set_err("octree shared memory", cudaSuccess); return ORBX_E_INVALID; }

@@ -1,0 +1,38 @@
+"""Summarise an `ncu --page raw --csv` dump: one block of key metrics per distinct kernel/grid."""
+import csv
+import sys
+
+WANT = ['gpu__time_duration.sum', 'launch__grid_size', 'launch__registers_per_thread',
+        'dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed',
+        'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'l1tex__throughput.avg.pct_of_peak_sustained_active',
+        'lts__throughput.avg.pct_of_peak_sustained_elapsed', 'sm__warps_active.avg.pct_of_peak_sustained_active',
+        'smsp__issue_active.avg.pct', 'smsp__inst_executed.sum',
+        'launch__occupancy_limit_registers', 'launch__occupancy_limit_shared_mem', 'launch__occupancy_limit_warps',
+        'smsp__warp_issue_stalled_barrier_per_warp_active.pct',
+        'smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct',
+        'smsp__warp_issue_stalled_short_scoreboard_per_warp_active.pct',
+        'smsp__warp_issue_stalled_mio_throttle_per_warp_active.pct',
+        'smsp__warp_issue_stalled_wait_per_warp_active.pct',
+        'smsp__warp_issue_stalled_math_pipe_throttle_per_warp_active.pct',
+        'smsp__warp_issue_stalled_no_instruction_per_warp_active.pct',
+        'smsp__warp_issue_stalled_lg_throttle_per_warp_active.pct',
+        'smsp__warp_issue_stalled_branch_resolving_per_warp_active.pct',
+        'smsp__warp_issue_stalled_not_selected_per_warp_active.pct',
+        'smsp__warp_issue_stalled_dispatch_stall_per_warp_active.pct',
+        'smsp__warp_issue_stalled_membar_per_warp_active.pct',
+        'smsp__warp_issue_stalled_sleeping_per_warp_active.pct']
+
+rows = list(csv.reader(open(sys.argv[1])))
+hdr, units = rows[0], rows[1]
+idx = {h: i for i, h in enumerate(hdr)}
+seen = set()
+for r in rows[2:]:
+    name = r[idx['Kernel Name']].split('(')[0]
+    key = (name, r[idx['launch__grid_size']])
+    if key in seen:
+        continue
+    seen.add(key)
+    print('==', name)
+    for w in WANT:
+        if w in idx:
+            print(f"   {w:70s} {r[idx[w]]:>16s} {units[idx[w]]}")
