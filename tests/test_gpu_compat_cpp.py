@@ -1,0 +1,47 @@
+"""The C++ drop-in classes (include/orbx_compat) built against liborbx.so and run on the GPU."""
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from orb_slam3_vio_fixes_b200 import synthetic as S
+from orb_slam3_vio_fixes_b200 import build as B
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def _build_exe(tmp):
+    B.build()
+    exe = tmp / "compat_main"
+    pkg = ROOT / "orb_slam3_vio_fixes_b200"
+    subprocess.check_call(["nvcc", "-O2", "-std=c++17", "-DORBX_NO_OPENCV", f"-I{ROOT / 'include'}",
+                           str(ROOT / "tests" / "cpp" / "compat_main.cpp"), "-o", str(exe), f"-L{pkg}", "-lorbx",
+                           "-Xlinker", f"-rpath={pkg}"])
+    return exe
+
+
+@pytest.mark.parametrize("lap", [(0, 0), (0, 1000)])
+def test_cpp_dropin_matches_oracle(oracle_mod, tmp_path, lap):
+    exe = _build_exe(tmp_path)
+    img = S.make_frames("C1", 1)[0]
+    raw = tmp_path / "in.raw"
+    img.tofile(raw)
+    out = subprocess.check_output([str(exe), str(raw), "752", "480", "1000", str(lap[0]), str(lap[1]),
+                                   str(tmp_path / "o")], text=True)
+    mono, n, dd, levels, nsf = [int(v) for v in out.split()]
+    orc = oracle_mod.Extractor(1000)
+    okps, odesc, omono = orc.extract(img, lap)
+    kps = np.fromfile(tmp_path / "o.kps", dtype=oracle_mod.KP_DTYPE)
+    desc = np.fromfile(tmp_path / "o.desc", dtype=np.uint8).reshape(-1, 32)
+    assert (mono, n, levels, nsf) == (omono, len(okps), 8, 8)
+    assert np.array_equal(kps, okps) and np.array_equal(desc, odesc)
+    pyr3 = np.fromfile(tmp_path / "o.pyr3", dtype=np.uint8)
+    assert np.array_equal(pyr3, orc.pyramid(3, True).ravel())
+    assert dd == oracle_mod.descriptor_distance(odesc[0], odesc[1])
+    res = np.fromfile(tmp_path / "o.match", dtype=oracle_mod.RES_DTYPE)
+    off = (np.arange(n + 1) * 8).astype(np.int32)
+    idx = ((np.arange(n)[:, None] + np.arange(1, 9)[None, :]) % n).astype(np.int32).ravel()
+    ref = oracle_mod.argmin2_csr(odesc, odesc, off, idx, okps["octave"].astype(np.int8), 0)
+    assert np.array_equal(res, ref)
