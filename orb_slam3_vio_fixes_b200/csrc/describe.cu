@@ -13,19 +13,31 @@
 #define DESC_WARPS 4
 #define PATCH 45        // 2*22+1
 #define PATCH_R 22
-#define PPITCH 52       // 13 words: rows start word aligned, lanes at stride 13 words never conflict
-#define TPITCH 41       // u16 row-pass pitch (odd: spreads banks)
+#define PW 13           // words per staged row: 52 bytes cover (alignment offset <= 3) + 45
 #define BL 39           // blurred window 2*19+1
-#define BPITCH 40
+#define BW 11           // words per blurred row (44 bytes)
 
 __constant__ int8_t c_pattern[1024] = {
 #include "orb_pattern.inc"
 };
 
+// Shared memory of one warp.  Column coordinates are "staged columns": staged byte c of row r is
+// image pixel (ky-22+r, kx-22+c-off), off = alignment offset of the row start (0 on the border path).
+//   patch : 45 rows x 13 words of source pixels; after the column pass it is dead and receives the
+//           blurred 39x39 window (row pitch 11 words, same staged-column coordinates).
+//   t     : column-pass sums for 39 rows x 13 words, two packed 16-bit lanes per register:
+//           t[r][w].x = {T(4w), T(4w+2)}, .y = {T(4w+1), T(4w+3)}   (sums <= 255*256 fit 16 bits)
 struct __align__(16) DescWarpSmem {
-  uint8_t patch[PATCH * PPITCH + 12];  // source neighbourhood; reused for the blurred window
-  uint16_t tmp[PATCH * TPITCH + 3];    // row-pass sums (<= 255*256)
+  uint32_t patch[PATCH * PW + 3];
+  uint2 t[BL * PW];
 };
+
+// One output byte of the row pass: taps 18,34,48,56,48,34,18 over seven 16-bit sums, rounded
+// like cv::GaussianBlur's fixed-point path: (acc + 2^15) >> 16.
+__device__ __forceinline__ uint32_t blur_out(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t a4,
+                                             uint32_t a5, uint32_t a6) {
+  return (18u * (a0 + a6) + 34u * (a1 + a5) + 48u * (a2 + a4) + 56u * a3 + 32768u) >> 16;
+}
 
 __global__ void __launch_bounds__(DESC_WARPS * 32)
 k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
@@ -57,8 +69,7 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
   if (level == 0) { pitch = l0.pitch; img = l0.base + (long long)frame * l0.frame_stride; }
   else { pitch = L.pitch; img = arena + (long long)frame * P.arena_bytes + L.offset; }
 
-  // ---- stage the 45x45 neighbourhood; patch(r,c) = I(ky-22+r, kx-22+c) lives at
-  //      sm.patch[r*PPITCH + c + off]
+  // ---- stage the 45x45 neighbourhood (13 words per row)
   int off;
   {
     const uint8_t* row0 = img + (long long)(ky - PATCH_R) * pitch + (kx - PATCH_R);
@@ -67,29 +78,36 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
     if (interior) {
       off = (int)((uintptr_t)row0 & 3);
       const uint8_t* a0 = row0 - off;  // word aligned; 13 words cover off+45 <= 48 bytes
-      for (int r = 0; r < PATCH; r++) {
-        if (lane < 13)
-          *reinterpret_cast<uint32_t*>(&sm.patch[r * PPITCH + 4 * lane]) =
-              *reinterpret_cast<const uint32_t*>(a0 + (long long)r * pitch + 4 * lane);
+      uint32_t v[19];
+#pragma unroll
+      for (int it = 0; it < 19; it++) {
+        const int i = it * 32 + lane;
+        const int r = (i * 5042) >> 16, c = i - r * PW;  // i / 13 for i < 608
+        v[it] = (it < 18 || lane < PATCH * PW - 18 * 32)
+                    ? __ldg(reinterpret_cast<const uint32_t*>(a0 + (long long)r * pitch) + c) : 0u;
       }
+#pragma unroll
+      for (int it = 0; it < 19; it++)
+        if (it < 18 || lane < PATCH * PW - 18 * 32) sm.patch[it * 32 + lane] = v[it];
     } else {
       off = 0;
+      uint8_t* pb = reinterpret_cast<uint8_t*>(sm.patch);
       for (int i = lane; i < PATCH * PATCH; i += 32) {
         const int r = i / PATCH, c = i - r * PATCH;
         const int sy = orbx_reflect101(ky - PATCH_R + r, L.h), sx = orbx_reflect101(kx - PATCH_R + c, L.w);
-        sm.patch[r * PPITCH + c] = img[(long long)sy * pitch + sx];
+        pb[r * (PW * 4) + c] = img[(long long)sy * pitch + sx];
       }
     }
   }
   __syncwarp();
-  const uint8_t* pc = sm.patch + off;  // pc[r*PPITCH + c]
+  const uint8_t* pc = reinterpret_cast<const uint8_t*>(sm.patch) + off;  // pc[r*52 + c]
 
   // ---- IC_Angle: integer moments over the circular patch of radius 15
   int m01 = 0, m10 = 0;
   if (lane < 31) {
     const int v = lane - ORBX_HALF_PATCH;
     const int d = P.umax[v < 0 ? -v : v];
-    const uint8_t* rowp = pc + (PATCH_R + v) * PPITCH + PATCH_R;
+    const uint8_t* rowp = pc + (PATCH_R + v) * (PW * 4) + PATCH_R;
     int s = 0, su = 0;
     for (int u = -d; u <= d; u++) {
       const int val = rowp[u];
@@ -106,32 +124,48 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
   }
   const float angle = orbx_fast_atan2((float)m01, (float)m10);
 
-  // ---- separable 7-tap Q8 blur on the staged patch.  Row pass: lane = patch row, sliding window.
-  for (int r = lane; r < PATCH; r += 32) {
-    const uint8_t* rp = pc + r * PPITCH;
-    int w0 = rp[0], w1 = rp[1], w2 = rp[2], w3 = rp[3], w4 = rp[4], w5 = rp[5];
-    uint16_t* tp = sm.tmp + r * TPITCH;
-#pragma unroll 3
-    for (int c = 0; c < BL; c++) {
-      const int w6 = rp[c + 6];
-      tp[c] = (uint16_t)(18 * (w0 + w6) + 34 * (w1 + w5) + 48 * (w2 + w4) + 56 * w3);
-      w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; w5 = w6;
+  // ---- separable 7-tap Q8 blur of the staged patch (exact integers, so the pass order is free).
+  // Column pass: lane = (word column w, half), 4 pixels per word as two packed 16-bit pairs,
+  // sliding window down 26 source rows -> 20 rows of sums.
+  if (lane < 2 * PW) {
+    const int w = lane < PW ? lane : lane - PW;
+    const int r0 = lane < PW ? 0 : BL - 20;  // halves overlap on row 19
+    const uint32_t* src = sm.patch + r0 * PW + w;
+    uint2* tp = sm.t + r0 * PW + w;
+    uint32_t e[7], o[7];
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      const uint32_t x = src[k * PW];
+      e[k] = x & 0x00ff00ffu;
+      o[k] = (x >> 8) & 0x00ff00ffu;
+    }
+#pragma unroll
+    for (int r = 0; r < 20; r++) {
+      const uint32_t x = src[(r + 6) * PW];
+      e[6] = x & 0x00ff00ffu;
+      o[6] = (x >> 8) & 0x00ff00ffu;
+      uint2 s;
+      s.x = 18u * (e[0] + e[6]) + 34u * (e[1] + e[5]) + 48u * (e[2] + e[4]) + 56u * e[3];
+      s.y = 18u * (o[0] + o[6]) + 34u * (o[1] + o[5]) + 48u * (o[2] + o[4]) + 56u * o[3];
+      tp[r * PW] = s;
+#pragma unroll
+      for (int k = 0; k < 6; k++) { e[k] = e[k + 1]; o[k] = o[k + 1]; }
     }
   }
   __syncwarp();
-  // Column pass: lane = column, sliding window down the 45 rows.  The source patch is dead now
-  // (orientation and row pass are done), so the blurred 39x39 window overwrites it.
-  uint8_t* blur = sm.patch;
-  for (int c = lane; c < BL; c += 32) {
-    const uint16_t* tp = sm.tmp + c;
-    int w0 = tp[0], w1 = tp[TPITCH], w2 = tp[2 * TPITCH], w3 = tp[3 * TPITCH], w4 = tp[4 * TPITCH],
-        w5 = tp[5 * TPITCH];
-#pragma unroll 3
-    for (int r = 0; r < BL; r++) {
-      const int w6 = tp[(r + 6) * TPITCH];
-      const uint32_t acc = 18u * (w0 + w6) + 34u * (w1 + w5) + 48u * (w2 + w4) + 56u * w3;
-      blur[r * BPITCH + c] = (uint8_t)((acc + 32768u) >> 16);
-      w0 = w1; w1 = w2; w2 = w3; w3 = w4; w4 = w5; w5 = w6;
+  // Row pass: one task = 4 adjacent output bytes (one word) of one row; the source patch is dead
+  // now (orientation and column pass are done), so the blurred window overwrites it.
+  {
+    uint32_t* bw = sm.patch;
+    for (int q = lane; q < BL * BW; q += 32) {
+      const int r = (q * 5958) >> 16, w = q - r * BW;  // q / 11 for q < 429
+      const uint2* tp = sm.t + r * PW + w;
+      const uint2 a = tp[0], b = tp[1], c = tp[2];
+      const uint32_t t0 = a.x & 0xffffu, t1 = a.y & 0xffffu, t2 = a.x >> 16, t3 = a.y >> 16;
+      const uint32_t t4 = b.x & 0xffffu, t5 = b.y & 0xffffu, t6 = b.x >> 16, t7 = b.y >> 16;
+      const uint32_t t8 = c.x & 0xffffu, t9 = c.y & 0xffffu;
+      bw[q] = blur_out(t0, t1, t2, t3, t4, t5, t6) | (blur_out(t1, t2, t3, t4, t5, t6, t7) << 8) |
+              (blur_out(t2, t3, t4, t5, t6, t7, t8) << 16) | (blur_out(t3, t4, t5, t6, t7, t8, t9) << 24);
     }
   }
   __syncwarp();
@@ -140,7 +174,7 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
   const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
   float a, b;
   orbx_sincosf(f_mul(angle, factorPI), &b, &a);
-  const uint8_t* centre = blur + 19 * BPITCH + 19;
+  const uint8_t* centre = reinterpret_cast<const uint8_t*>(sm.patch) + 19 * (BW * 4) + 19 + off;
   uint32_t word_mine = 0;
 #pragma unroll
   for (int j = 0; j < 8; j++) {
@@ -152,14 +186,14 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
       int iy, ix;
       if (strict_fp) { iy = f_round_int(f_add(f_mul(x, b), f_mul(y, a))); ix = f_round_int(f_sub(f_mul(x, a), f_mul(y, b))); }
       else { iy = f_round_int(f_fma(x, b, f_mul(y, a))); ix = f_round_int(f_fma(x, a, -f_mul(y, b))); }
-      v0 = centre[iy * BPITCH + ix];
+      v0 = centre[iy * (BW * 4) + ix];
     }
     {
       const float x = (float)pt.z, y = (float)pt.w;
       int iy, ix;
       if (strict_fp) { iy = f_round_int(f_add(f_mul(x, b), f_mul(y, a))); ix = f_round_int(f_sub(f_mul(x, a), f_mul(y, b))); }
       else { iy = f_round_int(f_fma(x, b, f_mul(y, a))); ix = f_round_int(f_fma(x, a, -f_mul(y, b))); }
-      v1 = centre[iy * BPITCH + ix];
+      v1 = centre[iy * (BW * 4) + ix];
     }
     const uint32_t w = __ballot_sync(0xffffffffu, v0 < v1);
     if (lane == j) word_mine = w;
