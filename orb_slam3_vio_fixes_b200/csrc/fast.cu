@@ -7,19 +7,26 @@
 // (wCell,hCell) lattice, and the NMS of a cell only sees that cell's own zone (outside = 0).
 //
 // One WARP = one cell (no block-level synchronisation at all; a CTA is just 4 independent warps):
-//   1. stage the zone + 3-px halo in the warp's shared-memory slice with 32-bit loads;
-//   2. quick test, four pixels (one 32-bit word, a "quad") per lane with packed-byte arithmetic
-//      (VABSDIFF4): a 9/16 corner at threshold t needs |v-ring| > t on at least one pixel of each
-//      opposite ring pair (0,8)(4,12)(2,10)(6,14); surviving quads are compacted in order;
-//   3. arc strength A of the surviving quads only, dense, with packed 16-bit SIMD
-//      (VIMNMX3.U16x2: the 16 sliding windows of 9 ring pixels are two rounds of 3-input min/max);
-//      corner(th) <=> A > th and cornerScore == A-1, so one pass serves both thresholds;
-//   4. NMS at iniThFAST; if the cell ends up empty, NMS again at minThFAST (:843-859);
-//   5. ordered (row-major) emission into the cell's slot array.
+//   1. stage the zone + 3-px halo in the warp's shared-memory slice with 32-bit loads, plus a
+//      copy with every byte halved (7-bit pixels) for the quick test;
+//   2. quick test at threshold t, four pixels (one 32-bit word, a "quad") per lane per step with
+//      packed-byte arithmetic (VABSDIFF4): a 9/16 corner needs |v-ring| > t on at least one pixel
+//      of each opposite ring pair (0,8)(4,12)(2,10)(6,14).  On 7-bit pixels the test
+//      |v'-r'| >= ceil(t/2) is implied by |v-r| > t (never rejects a corner) and the compare is one
+//      add whose carry lands in bit 7.  A lane walks down one quad column keeping the last 7 rows
+//      in registers, so a step costs 3 shared loads; the pass masks go to a byte map;
+//   3. the byte map is compacted, in row-major order, into a list of pixel PAIRS to score;
+//   4. arc strength A of the listed pairs only, with packed 16-bit SIMD (VIMNMX3.U16x2: the 16
+//      sliding windows of 9 ring pixels are two rounds of 3-input min/max); corner(t) <=> A > t and
+//      cornerScore == A-1;
+//   5. NMS over the listed pairs;
+//   6. if nothing survives at iniThFAST the cell is redone at minThFAST (:843-859), else
+//   7. ordered (row-major) emission into the cell's slot array.
 #include "orbx_kernels.cuh"
 
 #define FAST_WARPS 4
 #define FAST_THREADS (FAST_WARPS * 32)
+#define FAST_LIST_CAP 256  // pair tasks scored per band of rows (a cell is one band unless it is corner-dense)
 
 // 16-bit lanes {w[A], w[A+1]} out of the 12-byte window w0|w1|w2 (A compile-time, 1..9)
 template <int A>
@@ -66,49 +73,208 @@ __device__ __forceinline__ uint32_t arc_pair(const uint32_t (&rw)[7][3]) {
   return (uint32_t)a0 | ((uint32_t)a1 << 8);
 }
 
-// NMS decision for the pixel at byte j of the centre word: score = A-1 if A>th else 0, strict > on
-// all 8 neighbours (cv::FAST_t, nonmax_suppression branch).  n[3][3] = the 3x3 words around it.
-__device__ __forceinline__ bool nms_keep(const uint32_t (&n)[3][3], int j, int th) {
-  auto at = [&](int row, int col) -> int {  // col in [-1, 4]
-    const uint32_t w = col < 0 ? n[row][0] : (col > 3 ? n[row][2] : n[row][1]);
-    return (int)((w >> (8 * (col & 3))) & 0xffu);
-  };
-  const int A = at(1, j);
-  if (A <= th) return false;
-  const int s = A - 1;
+// NMS for the two pixels of a pair.  w0,w1,w2 = the rows above / at / below, each holding the A
+// values (0 where A <= th) of columns c-1, c, c+1, c+2 with the pair at c, c+1.  cv::FAST_t keeps a
+// corner when its score A-1 is strictly greater than all 8 neighbouring scores (0 for non-corners):
+//   keep <=> A != 0 && A > max(1, max of the 8 neighbours' A).
+// Returns bit0 / bit1 for the left / right pixel.
+__device__ __forceinline__ uint32_t nms_pair(uint32_t w0, uint32_t w1, uint32_t w2) {
+  const uint32_t e0 = w0 & 0x00ff00ffu, e1 = w1 & 0x00ff00ffu, e2 = w2 & 0x00ff00ffu;  // columns 0,2
+  const uint32_t o0 = (w0 >> 8) & 0x00ff00ffu, o1 = (w1 >> 8) & 0x00ff00ffu, o2 = (w2 >> 8) & 0x00ff00ffu;  // 1,3
+  const uint32_t ve = __vimax3_u16x2(e0, e1, e2), vo = __vimax3_u16x2(o0, o1, o2);  // column maxima
+  const uint32_t te = __vmaxu2(e0, e2), to = __vmaxu2(o0, o2);                      // without the centre row
+  const uint32_t ma = max(max(ve & 0xffffu, ve >> 16), max(to & 0xffffu, 1u));  // around column 1
+  const uint32_t mb = max(max(vo & 0xffffu, vo >> 16), max(te >> 16, 1u));      // around column 2
+  const uint32_t a = o1 & 0xffffu, b = e1 >> 16;
+  return (a > ma ? 1u : 0u) | (b > mb ? 2u : 0u);
+}
+
+// One step of the quick test for the quad column a lane walks down.  C/L2/R2/L3/R3 hold, per
+// staged row (slot = row mod 7), the centre word and the words shifted by -2, +2, -3, +3 pixels
+// (7-bit pixels).  Slot NEW receives tile row `row`; the quad under test sits 3 rows above it.
+struct QuickWin {
+  uint32_t C[7], L2[7], R2[7], L3[7], R3[7];
+};
+
+template <int NEW>
+__device__ __forceinline__ void quick_load(QuickWin& W, const uint32_t* hrow) {
+  const uint32_t n0 = hrow[-1], n1 = hrow[0], n2 = hrow[1];
+  W.C[NEW] = n1;
+  W.L2[NEW] = __byte_perm(n0, n1, 0x5432);
+  W.R2[NEW] = __byte_perm(n1, n2, 0x5432);
+  W.L3[NEW] = __byte_perm(n0, n1, 0x4321);
+  W.R3[NEW] = __byte_perm(n1, n2, 0x6543);
+}
+
+// PH = slot of the oldest row (tile row yy); the centre row is slot PH+3, the newest PH+6.
+// Returns the 4-bit mask of pixels that pass.
+template <int PH>
+__device__ __forceinline__ uint32_t quick_test(const QuickWin& W, uint32_t cadd) {
+  constexpr int S0 = PH % 7, S1 = (PH + 1) % 7, S3 = (PH + 3) % 7, S5 = (PH + 5) % 7, S6 = (PH + 6) % 7;
+  const uint32_t v = W.C[S3];
+#define QT(x) (__vabsdiffu4(v, (x)) + cadd)
+  uint32_t g = QT(W.C[S6]) | QT(W.C[S0]);     // ring 0 (0,+3) | ring 8 (0,-3)
+  g &= QT(W.R3[S3]) | QT(W.L3[S3]);           // ring 4 (+3,0) | ring 12 (-3,0)
+  g &= QT(W.R2[S5]) | QT(W.L2[S1]);           // ring 2 (+2,+2) | ring 10 (-2,-2)
+  g &= QT(W.R2[S1]) | QT(W.L2[S5]);           // ring 6 (+2,-2) | ring 14 (-2,+2)
+#undef QT
+  return ((g & 0x80808080u) * 0x00204081u) >> 28;  // bits 7,15,23,31 -> 0..3
+}
+
+// Shared memory of one warp, in 32-bit words:
+//   px[pw*rows]   staged pixels: tile row r (= zone row r-3), zone column x at byte r*4*pw + 7+sh + x
+//   hm[pw*rows]   the same tile with 7-bit pixels during the quick test; afterwards the arc-strength
+//                 map A (u8, 0 where A <= th or outside the zone), same geometry
+//   list[FAST_LIST_CAP] u16 tasks (quad*2 + pair), row-major, for the current band of rows
+//   qm[qcap]      u8 per quad: quick-test mask of its 4 pixels
+struct FastCell {
+  uint32_t *px, *hm;
+  uint16_t* list;
+  uint8_t* qm;
+  int pw, nqr, q_first, colbase, zw, zh;
+  uint32_t rcq;
+};
+
+// Arc strength of the listed pairs (dense: the warp stays converged) into the A map.
+__device__ __forceinline__ void fast_score_list(const FastCell& c, int nlist, int th, int lane) {
+  for (int e = lane; e < nlist; e += 32) {
+    const int tk = c.list[e];
+    const int ql = tk >> 1, pr = tk & 1;
+    const int yy = (int)(((uint32_t)ql * c.rcq) >> 20), q = c.q_first + ql - yy * c.nqr;
+    const int fs = 16 * pr;
+    uint32_t rw[7][3];
 #pragma unroll
-  for (int dr = 0; dr < 3; dr++)
-#pragma unroll
-    for (int dc = -1; dc <= 1; dc++) {
-      if (dr == 1 && dc == 0) continue;
-      const int B = at(dr, j + dc);
-      const int sb = B > th ? B - 1 : 0;
-      if (!(s > sb)) return false;
+    for (int d = 0; d < 7; d++) {
+      const uint32_t* p = c.px + (yy + d) * c.pw + q - 1;
+      const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+      rw[d][0] = __funnelshift_r(w0, w1, fs);
+      rw[d][1] = __funnelshift_r(w1, w2, fs);
+      rw[d][2] = w2 >> fs;
     }
-  return true;
+    const uint32_t a = arc_pair<0>(rw);  // A of zone columns x0, x0+1
+    const int x0 = 4 * q - c.colbase + 2 * pr;
+    const int A0 = (int)(a & 0xffu), A1 = (int)(a >> 8);
+    uint32_t keep = 0;
+    if (A0 > th && (unsigned)x0 < (unsigned)c.zw) keep |= 0x00ffu;
+    if (A1 > th && (unsigned)(x0 + 1) < (unsigned)c.zw) keep |= 0xff00u;
+    reinterpret_cast<uint16_t*>(c.hm + (yy + 3) * c.pw + q)[pr] = (uint16_t)(a & keep);
+  }
+  __syncwarp();
 }
 
-// per byte: 0x80 where x > t (t <= 126), via the carry into bit 7; c = (0x7f - t) * 0x01010101
-__device__ __forceinline__ uint32_t gt_bytes(uint32_t x, uint32_t c) {
-  return ((x & 0x7f7f7f7fu) + c) | x;  // bit 7 of each byte is the answer (mask later)
+// NMS over the listed pairs and ordered emission (list order == row-major, pairs and their pixels
+// left to right).  Returns the new running total of the cell.
+__device__ __forceinline__ int fast_nms_emit(const FastCell& c, int nlist, int total, uint32_t* out, int kx0,
+                                             int ky0, int lane) {
+  for (int base = 0; base < nlist; base += 32) {
+    const int e = base + lane;
+    uint32_t f = 0, a = 0;
+    int yy = 0, q = 0, pr = 0;
+    if (e < nlist) {
+      const int tk = c.list[e];
+      const int ql = tk >> 1;
+      pr = tk & 1;
+      yy = (int)(((uint32_t)ql * c.rcq) >> 20);
+      q = c.q_first + ql - yy * c.nqr;
+      const uint32_t* p = c.hm + (yy + 2) * c.pw + q - 1;
+      a = reinterpret_cast<const uint16_t*>(p + c.pw + 1)[pr];
+      if (a != 0) {
+        // columns c-1..c+2 around the pair at c = 2*pr of word q
+        const int fs = pr ? 8 : 24;
+        uint32_t w[3];
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+          const uint32_t lo = pr ? p[d * c.pw + 1] : p[d * c.pw], hi = pr ? p[d * c.pw + 2] : p[d * c.pw + 1];
+          w[d] = __funnelshift_r(lo, hi, fs);
+        }
+        f = nms_pair(w[0], w[1], w[2]);
+      }
+    }
+    const unsigned b = __ballot_sync(0xffffffffu, f != 0);
+    if (b == 0) continue;
+    const int cnt = __popc(f);
+    int inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (f) {
+      int pos = total + inc - cnt;
+      // coordinates relative to (minBorderX,minBorderY)=(16,16), as DistributeOctTree sees them
+      const int x = kx0 + 4 * q + 2 * pr, y = ky0 + yy;
+      if (f & 1u) out[pos++] = orbx_pack_key(x, y, (int)(a & 0xffu) - 1);
+      if (f & 2u) out[pos] = orbx_pack_key(x + 1, y, (int)(a >> 8) - 1);
+    }
+    total += __shfl_sync(0xffffffffu, inc, 31);
+  }
+  return total;
 }
 
-// Shared memory of one warp: px[pw*rows] | am[pw*rows] | list[list_cap] (u16), all in 32-bit words.
-// px: pixel (tile row r, tile col c) at byte r*4*pw + 4 + sh + c;  am: arc strength A (u8), same
-// geometry, 0 outside the zone;  list: quads that passed the quick test, in row-major order.
-__global__ void __launch_bounds__(FAST_THREADS)
+// Walks the quick-test byte map in row-major order, 128 quads (one word of qm per lane) at a time,
+// compacting the pixel pairs that passed into the task list.  The list is handed to the scoring
+// stage (MODE 0) or to NMS + emission (MODE 1) whenever the next 128 quads might not fit, and at the
+// end; *bands counts the hand-overs.  Returns the running emission total (MODE 1).
+template <int MODE>
+__device__ __forceinline__ int fast_sweep(const FastCell& c, int nquads, int th, int lane, int* nlist_out,
+                                          int* bands, int total, uint32_t* out, int kx0, int ky0) {
+  int nlist = 0, nb = 0;
+  for (int base = 0; base < nquads; base += 128) {
+    const int i4 = (base >> 2) + lane;
+    uint32_t bits = 0;
+    if (4 * i4 < nquads) {
+      const uint32_t m = reinterpret_cast<const uint32_t*>(c.qm)[i4];
+      uint32_t x = (m | (m >> 1)) & 0x05050505u;  // per quad: bit0 = left pair, bit2 = right pair
+      x = (x | (x >> 1)) & 0x03030303u;           // -> bits 0,1
+      bits = (x | (x >> 6) | (x >> 12) | (x >> 18)) & 0xffu;
+    }
+    const int cnt = __popc(bits);
+    int inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    const int chunk = __shfl_sync(0xffffffffu, inc, 31);
+    if (nlist + chunk > FAST_LIST_CAP) {
+      __syncwarp();
+      if (MODE == 0) fast_score_list(c, nlist, th, lane);
+      else total = fast_nms_emit(c, nlist, total, out, kx0, ky0, lane);
+      __syncwarp();
+      nlist = 0;
+      nb++;
+    }
+    int pos = nlist + inc - cnt;
+    while (bits) {
+      const int b = __ffs(bits) - 1;
+      bits &= bits - 1;
+      c.list[pos++] = (uint16_t)(8 * i4 + b);  // (4*i4 + b/2)*2 + (b&1)
+    }
+    nlist += chunk;
+  }
+  __syncwarp();
+  if (MODE == 0) fast_score_list(c, nlist, th, lane);
+  else total = fast_nms_emit(c, nlist, total, out, kx0, ky0, lane);
+  *nlist_out = nlist;
+  *bands = nb;
+  return total;
+}
+
+__global__ void __launch_bounds__(FAST_THREADS, 8)
 k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
-       int32_t* __restrict__ cell_cnt, uint32_t* __restrict__ cand, int pw, int rows_max, int list_cap) {
+       int32_t* __restrict__ cell_cnt, uint32_t* __restrict__ cand, int pw, int rows_max, int qcap) {
   extern __shared__ uint32_t fast_smem[];
   const int frame = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int cell = blockIdx.x * FAST_WARPS + warp;
   if (cell >= P.total_cells) return;
-  const int region = 2 * pw * rows_max + ((list_cap + 1) >> 1);
-  uint32_t* px = fast_smem + warp * region;
-  uint32_t* am = px + pw * rows_max;
-  uint16_t* list = reinterpret_cast<uint16_t*>(am + pw * rows_max);
-  uint8_t* flags = reinterpret_cast<uint8_t*>(px);  // px is dead once the arcs are done
+  const int region = 2 * pw * rows_max + FAST_LIST_CAP / 2 + (qcap >> 2);
+  FastCell c;
+  c.px = fast_smem + warp * region;
+  c.hm = c.px + pw * rows_max;
+  c.list = reinterpret_cast<uint16_t*>(c.hm + pw * rows_max);
+  c.qm = reinterpret_cast<uint8_t*>(c.hm + pw * rows_max + FAST_LIST_CAP / 2);
+  c.pw = pw;
 
   int level = 0;
 #pragma unroll 1
@@ -134,161 +300,105 @@ k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__
   // 1. stage pixels [zx0-3, zx1+3) x [zy0-3, zy1+3)
   const uint8_t* tile0 = img + (long long)(zy0 - 3) * pitch + (zx0 - 3);
   int sh;
-  if ((pitch & 3) == 0) {
+  const bool aligned = (pitch & 3) == 0;
+  if (aligned) {
     sh = (int)((uintptr_t)tile0 & 3);
     const int nw = (sh + zw + 6 + 3) >> 2;  // data words per row
-    const uint8_t* a0 = tile0 - sh;
+    const uint32_t* a0 = reinterpret_cast<const uint32_t*>(tile0 - sh);
+    const int wpitch = pitch >> 2;
     const uint32_t rcw = ((1u << 20) + nw - 1) / nw;
-    for (int i = lane; i < nw * (zh + 6); i += 32) {
-      const int r = (int)(((uint32_t)i * rcw) >> 20), c = i - r * nw;
-      px[r * pw + 1 + c] = __ldg(reinterpret_cast<const uint32_t*>(a0 + (long long)r * pitch) + c);
+    const int nwords = nw * (zh + 6);
+#pragma unroll 4
+    for (int i = lane; i < nwords; i += 32) {
+      const int r = (int)(((uint32_t)i * rcw) >> 20), col = i - r * nw;
+      const uint32_t v = __ldg(a0 + r * wpitch + col);
+      const int o = r * pw + 1 + col;
+      c.px[o] = v;
+      c.hm[o] = (v >> 1) & 0x7f7f7f7fu;
     }
   } else {
     sh = 0;
-    uint8_t* pb = reinterpret_cast<uint8_t*>(px);
+    uint8_t* pb = reinterpret_cast<uint8_t*>(c.px);
     for (int i = lane; i < (zw + 6) * (zh + 6); i += 32) {
-      const int r = i / (zw + 6), c = i - r * (zw + 6);
-      pb[r * (pw * 4) + 4 + c] = tile0[(long long)r * pitch + c];
+      const int r = i / (zw + 6), col = i - r * (zw + 6);
+      pb[r * (pw * 4) + 4 + col] = tile0[(long long)r * pitch + col];
     }
   }
   // Quads: word q of tile row r holds smem columns 4q..4q+3 = zone x 4q-(7+sh)+j, j=0..3.
-  const int colbase = 7 + sh;  // smem column of zone x = 0
-  const int q_first = colbase >> 2, q_last = (colbase + zw - 1) >> 2;
-  const int nqr = q_last - q_first + 1;  // quads per zone row
-  const int nquads = nqr * zh;
-  const uint32_t rcq = ((1u << 20) + nqr - 1) / nqr;
-  const int tmin = min(P.ini_th, P.min_th);
-  // zero ring of the A map: rows just above/below the zone and the words left/right of it
-  for (int i = lane; i < nqr + 2; i += 32) {
-    am[2 * pw + q_first - 1 + i] = 0;
-    am[(zh + 3) * pw + q_first - 1 + i] = 0;
-  }
-  for (int i = lane; i < zh; i += 32) {
-    am[(i + 3) * pw + q_first - 1] = 0;
-    am[(i + 3) * pw + q_last + 1] = 0;
-  }
-  __syncwarp();
-
-  // 2. quick test per quad, ordered compaction of the survivors
-  const bool quick = tmin <= 126;
-  const uint32_t cgt = (uint32_t)(0x7f - (quick ? tmin : 0)) * 0x01010101u;
-  int nlist = 0;
-  for (int base = 0; base < nquads; base += 32) {
-    const int ql = base + lane;
-    bool pass = false;
-    if (ql < nquads) {
-      const int yy = (int)(((uint32_t)ql * rcq) >> 20), q = q_first + ql - yy * nqr;
-      const uint32_t* p = px + yy * pw + q;  // tile row yy = zone row yy - 3
-      const uint32_t v = p[3 * pw];
-      am[(yy + 3) * pw + q] = 0;
-      if (quick) {
-        // ring pixels 0 (0,+3) and 8 (0,-3): same columns
-        uint32_t g = gt_bytes(__vabsdiffu4(v, p[6 * pw]), cgt) | gt_bytes(__vabsdiffu4(v, p[0]), cgt);
-        // 4 (+3,0) and 12 (-3,0)
-        const uint32_t c0 = p[3 * pw - 1], c2 = p[3 * pw + 1];
-        g &= gt_bytes(__vabsdiffu4(v, __byte_perm(v, c2, 0x6543)), cgt) |
-             gt_bytes(__vabsdiffu4(v, __byte_perm(c0, v, 0x4321)), cgt);
-        // 2 (+2,+2) and 10 (-2,-2)
-        const uint32_t d0 = p[5 * pw - 1], d1 = p[5 * pw], d2 = p[5 * pw + 1];
-        const uint32_t u0 = p[pw - 1], u1 = p[pw], u2 = p[pw + 1];
-        g &= gt_bytes(__vabsdiffu4(v, __byte_perm(d1, d2, 0x5432)), cgt) |
-             gt_bytes(__vabsdiffu4(v, __byte_perm(u0, u1, 0x5432)), cgt);
-        // 6 (+2,-2) and 14 (-2,+2)
-        g &= gt_bytes(__vabsdiffu4(v, __byte_perm(u1, u2, 0x5432)), cgt) |
-             gt_bytes(__vabsdiffu4(v, __byte_perm(d0, d1, 0x5432)), cgt);
-        pass = (g & 0x80808080u) != 0;
-      } else {
-        pass = true;
-      }
-    }
-    const unsigned b = __ballot_sync(0xffffffffu, pass);
-    if (pass) list[nlist + __popc(b & ((1u << lane) - 1))] = (uint16_t)ql;
-    nlist += __popc(b);
-  }
-  __syncwarp();
-
-  // 3. arc strength of the listed quads (dense: the warp stays converged)
-  for (int e = lane; e < nlist; e += 32) {
-    const int ql = list[e];
-    const int yy = (int)(((uint32_t)ql * rcq) >> 20), q = q_first + ql - yy * nqr;
-    uint32_t rw[7][3];
-#pragma unroll
-    for (int d = 0; d < 7; d++) {
-      const uint32_t* p = px + (yy + d) * pw + q - 1;
-      rw[d][0] = p[0]; rw[d][1] = p[1]; rw[d][2] = p[2];
-    }
-    const uint32_t a = arc_pair<0>(rw) | (arc_pair<2>(rw) << 16);
-    // keep A only where it can matter (A > tmin) and only inside the zone
-    const int x0 = 4 * q - colbase;
-    uint32_t keep = 0;
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const int A = (int)((a >> (8 * j)) & 0xffu);
-      if (A > tmin && (unsigned)(x0 + j) < (unsigned)zw) keep |= 0xffu << (8 * j);
-    }
-    am[(yy + 3) * pw + q] = a & keep;
-  }
-  __syncwarp();
-
-  // 4. NMS at iniTh over the listed quads; fall back to minTh when the cell has no survivor
-  int th = P.ini_th;
-  for (int pass = 0; pass < 2; pass++) {
-    unsigned any = 0;
-    for (int base = 0; base < nlist; base += 32) {
-      const int e = base + lane;
-      uint32_t f = 0;
-      if (e < nlist) {
-        const int ql = list[e];
-        const int yy = (int)(((uint32_t)ql * rcq) >> 20), q = q_first + ql - yy * nqr;
-        if (am[(yy + 3) * pw + q] != 0) {
-          uint32_t n[3][3];
-#pragma unroll
-          for (int d = 0; d < 3; d++) {
-            const uint32_t* p = am + (yy + 2 + d) * pw + q - 1;
-            n[d][0] = p[0]; n[d][1] = p[1]; n[d][2] = p[2];
-          }
-#pragma unroll
-          for (int j = 0; j < 4; j++)
-            if (nms_keep(n, j, th)) f |= 1u << j;
-        }
-        flags[e] = (uint8_t)f;
-      }
-      any |= __ballot_sync(0xffffffffu, f != 0);
-    }
-    if (any || P.min_th == th) break;
-    th = P.min_th;
-  }
-  __syncwarp();
-
-  // 5. ordered emission (list order == row-major quad order, bytes of a quad left to right)
+  c.colbase = 7 + sh;  // smem column of zone x = 0
+  c.q_first = c.colbase >> 2;
+  c.nqr = ((c.colbase + zw - 1) >> 2) - c.q_first + 1;  // quads per zone row
+  c.zw = zw;
+  c.zh = zh;
+  c.rcq = ((1u << 20) + c.nqr - 1) / c.nqr;
+  const int nqr = c.nqr, nquads = nqr * zh;
   uint32_t* out = cand + (long long)frame * P.cand_total + L.cand_base + (long long)cell * L.cell_cap;
-  int total = 0;
-  for (int base = 0; base < nlist; base += 32) {
-    const int e = base + lane;
-    const unsigned f = e < nlist ? flags[e] : 0u;
-    const unsigned b = __ballot_sync(0xffffffffu, f != 0);
-    if (b == 0) continue;
-    const int c = __popc(f);
-    int inc = c;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += t;
+  const int kx0 = zx0 - c.colbase - ORBX_MIN_BORDER, ky0 = zy0 - ORBX_MIN_BORDER;
+
+  int th = P.ini_th, total = 0;
+  bool restage = !aligned;  // hm does not hold the 7-bit tile yet
+#pragma unroll 1
+  for (int attempt = 0; attempt < 2; attempt++) {
+    __syncwarp();
+    if (restage) {
+      for (int i = lane; i < pw * (zh + 6); i += 32) c.hm[i] = (c.px[i] >> 1) & 0x7f7f7f7fu;
+      __syncwarp();
     }
-    if (f) {
-      const int ql = list[e];
-      const int yy = (int)(((uint32_t)ql * rcq) >> 20), q = q_first + ql - yy * nqr;
-      const uint32_t a = am[(yy + 3) * pw + q];
-      int pos = total + inc - c;
-#pragma unroll
-      for (int j = 0; j < 4; j++)
-        if ((f >> j) & 1u) {
-          // coordinates relative to (minBorderX,minBorderY)=(16,16), as DistributeOctTree sees them
-          out[pos++] = orbx_pack_key(zx0 + 4 * q - colbase + j - ORBX_MIN_BORDER, zy0 + yy - ORBX_MIN_BORDER,
-                                     (int)((a >> (8 * j)) & 0xffu) - 1);
-        }
+    if (lane == 0) reinterpret_cast<uint32_t*>(c.qm)[(nquads - 1) >> 2] = 0;  // tail bytes of the last word
+    __syncwarp();
+
+    // 2. quick test: lane = (segment of rows, quad column)
+    const uint32_t cadd = (uint32_t)(128 - ((th + 1) >> 1)) * 0x01010101u;
+#pragma unroll 1
+    for (int cg = 0; cg < nqr; cg += 32) {
+      const int ncols = min(32, nqr - cg);
+      const int nseg = ncols <= 10 ? 3 : (ncols <= 16 ? 2 : 1);
+      const int rps = (zh + nseg - 1) / nseg;
+      int seg = lane >= 2 * ncols ? 2 : (lane >= ncols ? 1 : 0);
+      const int qi = lane - seg * ncols;
+      const bool active = seg < nseg && qi < ncols;
+      if (!active) seg = 0;
+      const int y0 = seg * rps;
+      const int nrow = active ? min(zh, y0 + rps) - y0 : 0;  // rows this lane reports
+      const uint32_t* hcol = c.hm + c.q_first + cg + (active ? qi : 0);
+      const int hlast = (zh + 5) * pw;  // last staged row
+      int hp = y0 * pw;
+      uint8_t* qp = c.qm + y0 * nqr + cg + (active ? qi : 0);
+      QuickWin W;
+      quick_load<0>(W, hcol + hp); hp = min(hp + pw, hlast);
+      quick_load<1>(W, hcol + hp); hp = min(hp + pw, hlast);
+      quick_load<2>(W, hcol + hp); hp = min(hp + pw, hlast);
+      quick_load<3>(W, hcol + hp); hp = min(hp + pw, hlast);
+      quick_load<4>(W, hcol + hp); hp = min(hp + pw, hlast);
+      quick_load<5>(W, hcol + hp); hp = min(hp + pw, hlast);
+#define QSTEP(PH)                                       \
+  {                                                     \
+    quick_load<(PH + 6) % 7>(W, hcol + hp);                  \
+    hp = min(hp + pw, hlast);                           \
+    const uint32_t m = quick_test<PH>(W, cadd);         \
+    if (base + PH < nrow) qp[PH * nqr] = (uint8_t)m;    \
+  }
+#pragma unroll 1
+      for (int base = 0; base < rps; base += 7) {
+        QSTEP(0) QSTEP(1) QSTEP(2) QSTEP(3) QSTEP(4) QSTEP(5) QSTEP(6)
+        qp += 7 * nqr;
+      }
+#undef QSTEP
     }
-    total += __shfl_sync(0xffffffffu, inc, 31);
+    __syncwarp();
+    // hm becomes the A map: clear the rows NMS can read (tile rows 2 .. zh+3)
+    for (int i = 2 * pw + lane; i < (zh + 4) * pw; i += 32) c.hm[i] = 0;
+    __syncwarp();
+
+    // 3.-5. list the pixel pairs that passed, score them, then NMS + ordered emission
+    int nlist, bands;
+    fast_sweep<0>(c, nquads, th, lane, &nlist, &bands, 0, out, kx0, ky0);
+    if (bands == 0) total = fast_nms_emit(c, nlist, 0, out, kx0, ky0, lane);
+    else total = fast_sweep<1>(c, nquads, th, lane, &nlist, &bands, 0, out, kx0, ky0);
+    if (total > 0 || th == P.min_th) break;
+    // 6. nothing at iniThFAST: the reference runs FAST again on the cell with minThFAST
+    th = P.min_th;
+    restage = true;
   }
   if (lane == 0) *cnt_out = total;
 }
@@ -305,7 +415,8 @@ cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, 
     rows = max(rows, P.lv[l].hCell + 6);
     cap = max(cap, ((P.lv[l].wCell + 3 + 3) / 4 + 2) * P.lv[l].hCell);
   }
-  const size_t smem = (size_t)FAST_WARPS * (2 * pw * rows + ((cap + 1) >> 1)) * sizeof(uint32_t);
+  cap = (cap + 15) & ~15;  // quads per cell (bytes of qm), rounded so the regions stay word aligned
+  const size_t smem = (size_t)FAST_WARPS * (2 * pw * rows + FAST_LIST_CAP / 2 + (cap >> 2)) * sizeof(uint32_t);
   if ((int)smem > g_fast_smem_set) {
     cudaError_t e = cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

@@ -90,3 +90,46 @@ def test_empty_image_and_flat_image():
     flat = np.full((480, 752), 77, np.uint8)
     mono, kps, desc = ex(flat, None, (0, 0))
     assert mono == 0 and len(kps) == 0 and desc.shape == (0, 32)
+
+
+@pytest.mark.parametrize("ini,mn,contrast,size", [
+    (20, 7, 0.25, (752, 480)),    # low contrast: most cells fall back to minThFAST
+    (20, 7, 0.08, (640, 480)),    # almost flat: both thresholds fail in many cells
+    (7, 20, 1.0, (400, 300)),     # minTh > iniTh (the retry can only return less)
+    (40, 40, 1.0, (752, 480)),    # no retry
+    (0, 0, 0.05, (320, 240)),     # threshold 0: everything passes the quick test
+    (130, 127, 1.0, (752, 480)),  # thresholds above 126
+    (255, 1, 1.0, (320, 240)),    # nothing at iniTh anywhere
+    (20, 7, 1.0, (1241, 376)),    # KITTI shape (wide cells)
+    (20, 7, 1.0, (501, 317)),     # odd sizes
+])
+def test_fast_thresholds_and_fallback(oracle_mod, ini, mn, contrast, size):
+    w, h = size
+    img = S.make_frames("C1", 1, width=w, height=h)[0].astype(np.float64)
+    img = np.clip((img - 128.0) * contrast + 128.0, 0, 255).astype(np.uint8)
+    ex = ORBextractor(800, 1.2, 8, ini, mn)
+    orc = oracle_mod.Extractor(800, 1.2, 8, ini, mn)
+    mono, kps, desc = ex(img, None, (0, 0))
+    okps, odesc, omono = orc.extract(img, (0, 0))
+    for level in range(ex.nlevels):
+        cand = ex.debug_level_keypoints(level, 0)
+        oc = orc.level_keypoints(level, 0)
+        ocand = np.stack([oc["x"], oc["y"], oc["response"]], 1).astype(np.int32)
+        assert np.array_equal(cand, ocand), f"FAST candidates level {level}: {len(cand)} vs {len(ocand)}"
+    assert mono == omono and np.array_equal(kps, okps) and np.array_equal(desc, odesc)
+
+
+def test_batch_device_unaligned_pitch(oracle_mod):
+    """Caller-owned frames whose row pitch is not a multiple of 4 take the byte-wise staging paths."""
+    import torch
+    frames = S.make_frames("C3", 3, width=501, height=317)
+    ex = ORBextractor(600, max_batch=3, **ORB).plan(501, 317)
+    orc = oracle_mod.Extractor(600, 1.2, 8, 20, 7)
+    out = ex.extract_batch_device(torch.from_numpy(frames).cuda(), (0, 0))
+    torch.cuda.synchronize()
+    n = out["n"].cpu().numpy()
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    for f in range(len(frames)):
+        ok, od, om = orc.extract(frames[f], (0, 0))
+        assert n[f] == len(ok) and np.array_equal(kps[f, :n[f]], ok) and np.array_equal(desc[f, :n[f]], od)
