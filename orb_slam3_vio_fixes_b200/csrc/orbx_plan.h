@@ -31,6 +31,7 @@ struct OrbxLevel {
   int nIni;             // DistributeOctTree root count
   float hX;
   int xtab, ytab;  // offsets into the resize tables (entries), level>=1
+  int fast_resize;  // the 4-column tap windows of k_resize_walk hold for every column group
 };
 
 struct OrbxPlan {
@@ -156,6 +157,14 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
         t.c0 = (int16_t)orbx_cv_round((1.f - fx) * 2048.f);
         t.c1 = (int16_t)orbx_cv_round(fx * 2048.f);
         xtaps->push_back(t);
+      }
+      // k_resize_walk: taps 0,1 of a 4-column group read inside [ofs0, ofs0+4), taps 2,3 inside
+      // [ofs0+2, ofs0+6); true for every down-scale below 4/3
+      L.fast_resize = 1;
+      for (int dx = 0; dx < L.w; dx++) {
+        const int o0 = (*xtaps)[L.xtab + (dx & ~3)].ofs;
+        const int d = (*xtaps)[L.xtab + dx].ofs - o0 - ((dx & 3) < 2 ? 0 : 2);
+        if (d < 0 || d > 2) L.fast_resize = 0;
       }
       for (int dy = 0; dy < L.h; dy++) {
         float fy = (float)((dy + 0.5) * sy_scale - 0.5);
