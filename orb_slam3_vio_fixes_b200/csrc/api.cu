@@ -66,7 +66,7 @@ static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
     d.w = s.w; d.h = s.h; d.pitch = s.pitch; d.nCols = s.nCols; d.nRows = s.nRows; d.wCell = s.wCell;
     d.hCell = s.hCell; d.cell_base = s.cell_base; d.cell_cap = s.cell_cap; d.nfeat = s.nfeat;
     d.kp_base = s.kp_base; d.kp_cap = s.kp_cap; d.kp_max = s.kp_max; d.nIni = s.nIni; d.hX = s.hX;
-    d.scale = s.scale; d.patch_size = s.patch_size; d.xtab = s.xtab; d.ytab = s.ytab; d.fast_resize = s.fast_resize; d.offset = s.offset;
+    d.scale = s.scale; d.patch_size = s.patch_size; d.xtab = s.xtab; d.ytab = s.ytab; d.fast_resize = s.fast_resize; d.tile_resize = s.tile_resize; d.offset = s.offset;
     d.cand_base = s.cand_base;
   }
 }
@@ -147,7 +147,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) {
     set_err("cudaStreamCreate", e); delete h; return ORBX_E_CUDA;
   }
-  ALLOC(h->arena, B * P.arena_bytes + 256);
+  ALLOC(h->arena, B * P.arena_bytes + 512);
   ALLOC(h->xtaps, (xt.size() + 1) * sizeof(OrbxTap));
   ALLOC(h->ytaps, (yt.size() + 1) * sizeof(OrbxTap));
   ALLOC(h->cell_cnt, B * P.total_cells * sizeof(int32_t));
@@ -169,7 +169,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
     CU(cudaMemcpy(h->ytaps, yt.data(), yt.size() * sizeof(OrbxTap), cudaMemcpyHostToDevice));
   }
   CU(cudaMemset(h->status, 0, sizeof(int32_t)));
-  CU(cudaMemset(h->arena, 0, B * P.arena_bytes + 256));
+  CU(cudaMemset(h->arena, 0, B * P.arena_bytes + 512));
   CU(orbx_octree_set_smem(h->oct_smem));
   if (cfg->flags & ORBX_FLAG_STAGE_TIMING)
     for (int i = 0; i <= ORBX_NUM_STAGES; i++) CU(cudaEventCreate(&h->ev[i]));

@@ -14,7 +14,7 @@ struct DevLevel {
   int nfeat, kp_base, kp_cap, kp_max;
   int nIni;
   float hX, scale, patch_size;
-  int xtab, ytab, fast_resize;
+  int xtab, ytab, fast_resize, tile_resize;
   long long offset;     // bytes, inside a frame's pyramid arena
   long long cand_base;  // uint32 units, inside a frame's candidate arena
 };

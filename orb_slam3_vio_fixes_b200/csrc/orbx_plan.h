@@ -32,6 +32,7 @@ struct OrbxLevel {
   float hX;
   int xtab, ytab;  // offsets into the resize tables (entries), level>=1
   int fast_resize;  // the 4-column tap windows of k_resize_walk hold for every column group
+  int tile_resize;  // every 128x64 output tile fits k_resize_tile's shared-memory source window
 };
 
 struct OrbxPlan {
@@ -175,6 +176,19 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
         t.c0 = (int16_t)orbx_cv_round((1.f - fy) * 2048.f);
         t.c1 = (int16_t)orbx_cv_round(fy * 2048.f);
         ytaps->push_back(t);
+      }
+      // k_resize_tile: source window of a 128 x 64 output tile (88 rows x 208 bytes of shared memory)
+      L.tile_resize = L.fast_resize;
+      for (int x0 = 0; x0 < L.w; x0 += 128) {
+        const int xs0 = (*xtaps)[L.xtab + x0].ofs & ~15;
+        const int xl = (*xtaps)[L.xtab + (x0 + 127 < L.w ? x0 + 127 : L.w - 1)].ofs;
+        if (((xl + 12 - xs0 + 15) & ~15) > 208) L.tile_resize = 0;
+      }
+      for (int y0 = 0; y0 < L.h; y0 += 64) {
+        int a = (*ytaps)[L.ytab + y0].ofs, b = (*ytaps)[L.ytab + (y0 + 63 < L.h ? y0 + 63 : L.h - 1)].ofs + 1;
+        a = a < 0 ? 0 : (a > S.h - 1 ? S.h - 1 : a);
+        b = b < 0 ? 0 : (b > S.h - 1 ? S.h - 1 : b);
+        if (b - a + 1 > 88) L.tile_resize = 0;
       }
     }
   }

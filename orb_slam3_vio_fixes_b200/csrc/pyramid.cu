@@ -65,21 +65,52 @@ k_resize(const uint8_t* __restrict__ src, int spitch, long long sframe, int sw, 
 struct RsTapRegs {
   uint32_t selA[4], selB[4];  // PRMT selectors: byte -> position 0 / position 1 (x256), rest zero
   uint32_t C0[4], C1[4];      // c0 << 12, c1 << 4
-  int wa, wa1, wm, wm1;       // word indices of the two windows (clamped to the row)
-  int sa, sm;                 // funnel shifts in bits
+  int sa;                     // funnel shift in bits: 8 * (ofs_0 & 3)
+  int o1, o2;                 // byte offsets of the 2nd and 3rd source word (4, 8 unless clamped)
 };
 
-__device__ __forceinline__ void rs_row(const uint32_t* __restrict__ row, const RsTapRegs& T, uint32_t (&H)[4]) {
-  const uint32_t lo = __funnelshift_r(__ldg(row + T.wa), __ldg(row + T.wa1), T.sa);
-  const uint32_t mid = __funnelshift_r(__ldg(row + T.wm), __ldg(row + T.wm1), T.sm);
+// H[i] = ((r0*c0 + r1*c1) >> 4) << 16 for the thread's 4 columns on one source row.
+// p = the row's word that holds byte ofs_0.
+template <bool CLAMP>
+__device__ __forceinline__ void rs_row(const uint8_t* __restrict__ p, const RsTapRegs& T, uint32_t (&H)[4]) {
+  const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(p));
+  const uint32_t w1 = __ldg(reinterpret_cast<const uint32_t*>(p + (CLAMP ? T.o1 : 4)));
+  const uint32_t w2 = __ldg(reinterpret_cast<const uint32_t*>(p + (CLAMP ? T.o2 : 8)));
+  const uint32_t lo = __funnelshift_r(w0, w1, T.sa);  // source bytes ofs_0 .. ofs_0+3
+  const uint32_t hi = __funnelshift_r(w1, w2, T.sa);  // ofs_0+4 .. ofs_0+7
+  const uint32_t mid = __funnelshift_r(lo, hi, 16);   // ofs_0+2 .. ofs_0+5
 #pragma unroll
   for (int i = 0; i < 4; i++) {
     const uint32_t win = i < 2 ? lo : mid;
     const uint32_t h = __byte_perm(win, 0, T.selA[i]) * T.C0[i] + __byte_perm(win, 0, T.selB[i]) * T.C1[i];
-    H[i] = h & 0xffff0000u;  // ((r0*c0 + r1*c1) >> 4) << 16
+    H[i] = h & 0xffff0000u;
   }
 }
 
+// One output row: source rows sy0 / sy1 live in slots P / P^1 of the two-row register cache
+// (slot = parity of the source row, so a row shared by consecutive output rows never moves).
+template <int P, bool CLAMP>
+__device__ __forceinline__ uint32_t rs_out_row(const uint8_t* __restrict__ base, int spitch, int sy0, int sy1,
+                                               uint32_t b0, uint32_t b1, const RsTapRegs& T,
+                                               uint32_t (&H)[2][4], int (&held)[2]) {
+  if (held[P] != sy0) {
+    rs_row<CLAMP>(base + sy0 * spitch, T, H[P]);
+    held[P] = sy0;
+  }
+  if (held[P ^ 1] != sy1) {
+    rs_row<CLAMP>(base + sy1 * spitch, T, H[P ^ 1]);
+    held[P ^ 1] = sy1;
+  }
+  uint32_t out = 0;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const uint32_t v = (__umulhi(b0, H[P][i]) + __umulhi(b1, H[P ^ 1][i]) + 2u) >> 2;  // <= 255
+    out |= v << (8 * i);
+  }
+  return out;
+}
+
+template <bool CLAMP>
 __global__ void __launch_bounds__(RS_WARPS * 32)
 k_resize_walk(const uint8_t* __restrict__ src, int spitch, long long sframe, int sw, int sh,
               uint8_t* __restrict__ dst, int dpitch, long long dframe, int dw, int dh,
@@ -87,14 +118,13 @@ k_resize_walk(const uint8_t* __restrict__ src, int spitch, long long sframe, int
   const int x4 = (blockIdx.x * 32 + (threadIdx.x & 31)) * 4;
   const int dy0 = (blockIdx.y * RS_WARPS + (threadIdx.x >> 5)) * RS_ROWS;
   if (x4 >= dw || dy0 >= dh) return;
-  const uint8_t* S = src + (long long)blockIdx.z * sframe;
-  uint8_t* D = dst + (long long)blockIdx.z * dframe;
   RsTapRegs T;
+  const int o0 = xt[x4].ofs;
   {
-    const int wlast = (spitch >> 2) - 1;
-    const int o0 = xt[x4].ofs;
-    T.wa = min(o0 >> 2, wlast); T.wa1 = min((o0 >> 2) + 1, wlast); T.sa = 8 * (o0 & 3);
-    T.wm = min((o0 + 2) >> 2, wlast); T.wm1 = min(((o0 + 2) >> 2) + 1, wlast); T.sm = 8 * ((o0 + 2) & 3);
+    T.sa = 8 * (o0 & 3);
+    const int wlast = (spitch >> 2) - 1, wa = o0 >> 2;  // CLAMP: never read past the row's last word
+    T.o1 = 4 * (min(wa + 1, wlast) - wa);
+    T.o2 = 4 * (min(wa + 2, wlast) - wa);
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const OrbxTap t = xt[min(x4 + i, dw - 1)];
@@ -106,37 +136,139 @@ k_resize_walk(const uint8_t* __restrict__ src, int spitch, long long sframe, int
       T.C1[i] = (uint32_t)t.c1 << 4;
     }
   }
-  uint32_t HA[4], HB[4];
-  int ra = -1, rb = -1;  // source rows held in HA / HB
+  const uint8_t* base = src + (long long)blockIdx.z * sframe + (o0 & ~3);
+  uint8_t* out = dst + (long long)blockIdx.z * dframe + (long long)dy0 * dpitch + x4;
+  uint32_t H[2][4];
+  int held[2] = {-1, -1};
   const int dy1 = min(dy0 + RS_ROWS, dh);
-  for (int dy = dy0; dy < dy1; dy++) {
+#pragma unroll 1
+  for (int dy = dy0; dy < dy1; dy++, out += dpitch) {
     const OrbxTap ty = yt[dy];
     const int sy0 = min(max(ty.ofs, 0), sh - 1), sy1 = min(max(ty.ofs + 1, 0), sh - 1);
-    if (sy0 == rb) {
-#pragma unroll
-      for (int i = 0; i < 4; i++) HA[i] = HB[i];
-      ra = rb;
-    } else if (sy0 != ra) {
-      rs_row(reinterpret_cast<const uint32_t*>(S + (long long)sy0 * spitch), T, HA);
-      ra = sy0;
-    }
-    if (sy1 == ra) {
-#pragma unroll
-      for (int i = 0; i < 4; i++) HB[i] = HA[i];
-      rb = ra;
-    } else if (sy1 != rb) {
-      rs_row(reinterpret_cast<const uint32_t*>(S + (long long)sy1 * spitch), T, HB);
-      rb = sy1;
-    }
     const uint32_t b0 = (uint32_t)ty.c0, b1 = (uint32_t)ty.c1;
-    uint32_t out = 0;
+    uint32_t v;
+    if (sy0 & 1) v = rs_out_row<1, CLAMP>(base, spitch, sy0, sy1, b0, b1, T, H, held);
+    else v = rs_out_row<0, CLAMP>(base, spitch, sy0, sy1, b0, b1, T, H, held);
+    // rows are 128-byte aligned and padded, so the full word store stays inside the row
+    *reinterpret_cast<uint32_t*>(out) = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Tiled variant: the CTA's 128 x 64 output tile needs <= RT_SROWS source rows of <= RT_SPITCH bytes.
+// They are brought into shared memory by the TMA engine (cp.async.bulk, one 16-byte-aligned row
+// segment per copy, completion counted on an mbarrier), so the row walk below never waits on HBM:
+// the only global traffic is one coalesced bulk read of the source tile and the word stores.
+// ------------------------------------------------------------------------------------------------
+#define RT_SROWS 88
+#define RT_SPITCH 208
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void rs_row_smem(const uint8_t* p, const RsTapRegs& T, uint32_t (&H)[4]) {
+  const uint32_t w0 = *reinterpret_cast<const uint32_t*>(p);
+  const uint32_t w1 = *reinterpret_cast<const uint32_t*>(p + 4);
+  const uint32_t w2 = *reinterpret_cast<const uint32_t*>(p + 8);
+  const uint32_t lo = __funnelshift_r(w0, w1, T.sa);
+  const uint32_t hi = __funnelshift_r(w1, w2, T.sa);
+  const uint32_t mid = __funnelshift_r(lo, hi, 16);
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const uint32_t win = i < 2 ? lo : mid;
+    const uint32_t h = __byte_perm(win, 0, T.selA[i]) * T.C0[i] + __byte_perm(win, 0, T.selB[i]) * T.C1[i];
+    H[i] = h & 0xffff0000u;
+  }
+}
+
+template <int P>
+__device__ __forceinline__ uint32_t rs_out_row_smem(const uint8_t* base, int sy0, int sy1, uint32_t b0, uint32_t b1,
+                                                    const RsTapRegs& T, uint32_t (&H)[2][4], int (&held)[2]) {
+  if (held[P] != sy0) {
+    rs_row_smem(base + sy0 * RT_SPITCH, T, H[P]);
+    held[P] = sy0;
+  }
+  if (held[P ^ 1] != sy1) {
+    rs_row_smem(base + sy1 * RT_SPITCH, T, H[P ^ 1]);
+    held[P ^ 1] = sy1;
+  }
+  uint32_t out = 0;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const uint32_t v = (__umulhi(b0, H[P][i]) + __umulhi(b1, H[P ^ 1][i]) + 2u) >> 2;  // <= 255
+    out |= v << (8 * i);
+  }
+  return out;
+}
+
+__global__ void __launch_bounds__(RS_WARPS * 32)
+k_resize_tile(const uint8_t* __restrict__ src, int spitch, long long sframe, int sw, int sh,
+              uint8_t* __restrict__ dst, int dpitch, long long dframe, int dw, int dh,
+              const OrbxTap* __restrict__ xt, const OrbxTap* __restrict__ yt) {
+  __shared__ __align__(128) uint8_t tile[RT_SROWS * RT_SPITCH];
+  __shared__ __align__(8) uint64_t bar;
+  const int tid = threadIdx.x;
+  const int x0c = blockIdx.x * 128, dy0c = blockIdx.y * (RS_WARPS * RS_ROWS);
+  // source window of the CTA (uniform)
+  const int sy_first = min(max(yt[dy0c].ofs, 0), sh - 1);
+  const int sy_last = min(max(yt[min(dy0c + RS_WARPS * RS_ROWS - 1, dh - 1)].ofs + 1, 0), sh - 1);
+  const int nrows = sy_last - sy_first + 1;
+  const int xs0 = xt[x0c].ofs & ~15;
+  const int seg = min((xt[min(x0c + 127, dw - 1)].ofs + 12 - xs0 + 15) & ~15, spitch - xs0);
+  const uint32_t bar_a = smem_u32(&bar);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(nrows * seg) : "memory");
+  }
+  __syncthreads();
+  {
+    const uint8_t* g = src + (long long)blockIdx.z * sframe + (long long)sy_first * spitch + xs0;
+    for (int r = tid; r < nrows; r += RS_WARPS * 32)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(smem_u32(tile + r * RT_SPITCH)), "l"(g + (long long)r * spitch), "r"(seg), "r"(bar_a)
+                   : "memory");
+  }
+  const int x4 = x0c + (tid & 31) * 4;
+  const int dy0 = dy0c + (tid >> 5) * RS_ROWS;
+  const bool live = x4 < dw && dy0 < dh;
+  RsTapRegs T;
+  int o0 = 0;
+  if (live) {
+    o0 = xt[x4].ofs;
+    T.sa = 8 * (o0 & 3);
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-      const uint32_t v = (__umulhi(b0, HA[i]) + __umulhi(b1, HB[i]) + 2u) >> 2;  // <= 255, see DESIGN.md
-      out |= v << (8 * i);
+      const OrbxTap t = xt[min(x4 + i, dw - 1)];
+      int d = t.ofs - o0 - (i < 2 ? 0 : 2);
+      d = min(max(d, 0), 2);  // only the padding columns beyond dw can fall outside
+      T.selA[i] = 0x4440u | (uint32_t)d;
+      T.selB[i] = 0x4404u | ((uint32_t)(d + 1) << 4);
+      T.C0[i] = (uint32_t)t.c0 << 12;
+      T.C1[i] = (uint32_t)t.c1 << 4;
     }
+  }
+  {  // wait for the tile
+    uint32_t done = 0;
+    while (!done)
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                   : "=r"(done) : "r"(bar_a) : "memory");
+  }
+  if (!live) return;
+  const uint8_t* base = tile + ((o0 & ~3) - xs0) - sy_first * RT_SPITCH;
+  uint8_t* out = dst + (long long)blockIdx.z * dframe + (long long)dy0 * dpitch + x4;
+  uint32_t H[2][4];
+  int held[2] = {-1, -1};
+  const int dy1 = min(dy0 + RS_ROWS, dh);
+#pragma unroll 1
+  for (int dy = dy0; dy < dy1; dy++, out += dpitch) {
+    const OrbxTap ty = yt[dy];
+    const int sy0 = min(max(ty.ofs, 0), sh - 1), sy1 = min(max(ty.ofs + 1, 0), sh - 1);
+    const uint32_t b0 = (uint32_t)ty.c0, b1 = (uint32_t)ty.c1;
+    uint32_t v;
+    if (sy0 & 1) v = rs_out_row_smem<1>(base, sy0, sy1, b0, b1, T, H, held);
+    else v = rs_out_row_smem<0>(base, sy0, sy1, b0, b1, T, H, held);
     // rows are 128-byte aligned and padded, so the full word store stays inside the row
-    *reinterpret_cast<uint32_t*>(D + (long long)dy * dpitch + x4) = out;
+    *reinterpret_cast<uint32_t*>(out) = v;
   }
 }
 
@@ -151,10 +283,22 @@ cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, con
     if (l == 1) { src = l0.base; spitch = l0.pitch; sframe = l0.frame_stride; }
     else { src = arena + S.offset; spitch = S.pitch; sframe = P.arena_bytes; }
     const bool walk = D.fast_resize && (spitch & 3) == 0 && (sframe & 3) == 0 && ((uintptr_t)src & 3) == 0;
-    if (walk) {
+    const bool tiled = walk && D.tile_resize && (spitch & 15) == 0 && (sframe & 15) == 0 && ((uintptr_t)src & 15) == 0;
+    if (tiled) {
       dim3 grd((D.w + 127) / 128, (D.h + RS_WARPS * RS_ROWS - 1) / (RS_WARPS * RS_ROWS), batch);
-      k_resize_walk<<<grd, RS_WARPS * 32, 0, st>>>(src, spitch, sframe, S.w, S.h, arena + D.offset, D.pitch,
+      k_resize_tile<<<grd, RS_WARPS * 32, 0, st>>>(src, spitch, sframe, S.w, S.h, arena + D.offset, D.pitch,
                                                    P.arena_bytes, D.w, D.h, xtaps + D.xtab, ytaps + D.ytab);
+    } else if (walk) {
+      dim3 grd((D.w + 127) / 128, (D.h + RS_WARPS * RS_ROWS - 1) / (RS_WARPS * RS_ROWS), batch);
+      // Arena rows are padded (and the arena has slack after its last row), so only a caller-owned
+      // level 0 whose pitch leaves < 12 spare bytes needs the clamped word offsets.
+      if (l == 1 && spitch - S.w < 12)
+        k_resize_walk<true><<<grd, RS_WARPS * 32, 0, st>>>(src, spitch, sframe, S.w, S.h, arena + D.offset, D.pitch,
+                                                           P.arena_bytes, D.w, D.h, xtaps + D.xtab, ytaps + D.ytab);
+      else
+        k_resize_walk<false><<<grd, RS_WARPS * 32, 0, st>>>(src, spitch, sframe, S.w, S.h, arena + D.offset,
+                                                            D.pitch, P.arena_bytes, D.w, D.h, xtaps + D.xtab,
+                                                            ytaps + D.ytab);
     } else {
       dim3 blk(32, 8);
       dim3 grd((D.w + 127) / 128, (D.h + 7) / 8, batch);
