@@ -17,7 +17,8 @@
 #define BL 39           // blurred window 2*19+1
 #define BW 11           // words per blurred row (44 bytes)
 
-__constant__ int8_t c_pattern[1024] = {
+// bit_pattern_31_ as floats (x0,y0,x1,y1 per test), read through the L1 with 128-bit loads
+__device__ const __align__(16) float c_patf[1024] = {
 #include "orb_pattern.inc"
 };
 
@@ -39,17 +40,14 @@ __device__ __forceinline__ uint32_t blur_out(uint32_t a0, uint32_t a1, uint32_t 
   return (18u * (a0 + a6) + 34u * (a1 + a5) + 48u * (a2 + a4) + 56u * a3 + 32768u) >> 16;
 }
 
+template <bool STRICT_FP>
 __global__ void __launch_bounds__(DESC_WARPS * 32)
 k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
            const uint32_t* __restrict__ sel, const int32_t* __restrict__ sel_cnt,
            const int32_t* __restrict__ dst, OrbxKeyPointDev* __restrict__ kps, uint8_t* __restrict__ desc,
-           int capacity, int strict_fp) {
+           int capacity) {
   __shared__ DescWarpSmem sm_all[DESC_WARPS];
-  __shared__ __align__(4) int8_t s_pattern[1024];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int i = threadIdx.x; i < 256; i += DESC_WARPS * 32)
-    reinterpret_cast<uint32_t*>(s_pattern)[i] = reinterpret_cast<const uint32_t*>(c_pattern)[i];
-  __syncthreads();
   const int frame = blockIdx.y;
   const int slot = blockIdx.x * DESC_WARPS + warp;
   if (slot >= P.kp_total_cap) return;
@@ -77,25 +75,30 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
                           (ky + PATCH_R < L.h) && ((pitch & 3) == 0);
     if (interior) {
       off = (int)((uintptr_t)row0 & 3);
-      const uint8_t* a0 = row0 - off;  // word aligned; 13 words cover off+45 <= 48 bytes
+      // word aligned; 13 words cover off+45 <= 48 bytes
+      const uint32_t* a0 = reinterpret_cast<const uint32_t*>(row0 - off);
+      const int wpitch = pitch >> 2;
       uint32_t v[19];
 #pragma unroll
       for (int it = 0; it < 19; it++) {
         const int i = it * 32 + lane;
         const int r = (i * 5042) >> 16, c = i - r * PW;  // i / 13 for i < 608
-        v[it] = (it < 18 || lane < PATCH * PW - 18 * 32)
-                    ? __ldg(reinterpret_cast<const uint32_t*>(a0 + (long long)r * pitch) + c) : 0u;
+        v[it] = (it < 18 || lane < PATCH * PW - 18 * 32) ? __ldg(a0 + (r * wpitch + c)) : 0u;
       }
 #pragma unroll
       for (int it = 0; it < 19; it++)
         if (it < 18 || lane < PATCH * PW - 18 * 32) sm.patch[it * 32 + lane] = v[it];
     } else {
+      // near the level edge (or unaligned rows): bytes, BORDER_REFLECT_101; lane = column(s)
       off = 0;
       uint8_t* pb = reinterpret_cast<uint8_t*>(sm.patch);
-      for (int i = lane; i < PATCH * PATCH; i += 32) {
-        const int r = i / PATCH, c = i - r * PATCH;
-        const int sy = orbx_reflect101(ky - PATCH_R + r, L.h), sx = orbx_reflect101(kx - PATCH_R + c, L.w);
-        pb[r * (PW * 4) + c] = img[(long long)sy * pitch + sx];
+      const int c1 = min(lane + 32, PATCH - 1);
+      const int sx0 = orbx_reflect101(kx - PATCH_R + lane, L.w), sx1 = orbx_reflect101(kx - PATCH_R + c1, L.w);
+      for (int r = 0; r < PATCH; r++) {
+        const uint8_t* rowp = img + (long long)orbx_reflect101(ky - PATCH_R + r, L.h) * pitch;
+        const uint8_t p0 = rowp[sx0], p1 = rowp[sx1];
+        pb[r * (PW * 4) + lane] = p0;
+        pb[r * (PW * 4) + c1] = p1;
       }
     }
   }
@@ -175,26 +178,25 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
   float a, b;
   orbx_sincosf(f_mul(angle, factorPI), &b, &a);
   const uint8_t* centre = reinterpret_cast<const uint8_t*>(sm.patch) + 19 * (BW * 4) + 19 + off;
+  // cvRound(v) for |v| < 2^22: v + 1.5*2^23 rounds to nearest-even at integer granularity, and the
+  // integer sits in the low mantissa bits; row*44 + col is formed directly on the biased values.
+  const float kMagic = 12582912.0f;
+  const uint32_t kBias = 0x4B400000u * (uint32_t)(BW * 4 + 1);
   uint32_t word_mine = 0;
 #pragma unroll
   for (int j = 0; j < 8; j++) {
-    const int t = 32 * j + lane;
-    const char4 pt = reinterpret_cast<const char4*>(s_pattern)[t];
-    int v0, v1;
-    {
-      const float x = (float)pt.x, y = (float)pt.y;
-      int iy, ix;
-      if (strict_fp) { iy = f_round_int(f_add(f_mul(x, b), f_mul(y, a))); ix = f_round_int(f_sub(f_mul(x, a), f_mul(y, b))); }
-      else { iy = f_round_int(f_fma(x, b, f_mul(y, a))); ix = f_round_int(f_fma(x, a, -f_mul(y, b))); }
-      v0 = centre[iy * (BW * 4) + ix];
+    const float4 pt = __ldg(reinterpret_cast<const float4*>(c_patf) + 32 * j + lane);
+    float fy0, fx0, fy1, fx1;
+    if (STRICT_FP) {
+      fy0 = f_add(f_mul(pt.x, b), f_mul(pt.y, a)); fx0 = f_sub(f_mul(pt.x, a), f_mul(pt.y, b));
+      fy1 = f_add(f_mul(pt.z, b), f_mul(pt.w, a)); fx1 = f_sub(f_mul(pt.z, a), f_mul(pt.w, b));
+    } else {
+      fy0 = f_fma(pt.x, b, f_mul(pt.y, a)); fx0 = f_fma(pt.x, a, -f_mul(pt.y, b));
+      fy1 = f_fma(pt.z, b, f_mul(pt.w, a)); fx1 = f_fma(pt.z, a, -f_mul(pt.w, b));
     }
-    {
-      const float x = (float)pt.z, y = (float)pt.w;
-      int iy, ix;
-      if (strict_fp) { iy = f_round_int(f_add(f_mul(x, b), f_mul(y, a))); ix = f_round_int(f_sub(f_mul(x, a), f_mul(y, b))); }
-      else { iy = f_round_int(f_fma(x, b, f_mul(y, a))); ix = f_round_int(f_fma(x, a, -f_mul(y, b))); }
-      v1 = centre[iy * (BW * 4) + ix];
-    }
+    const uint32_t i0 = __float_as_uint(f_add(fy0, kMagic)) * (uint32_t)(BW * 4) + __float_as_uint(f_add(fx0, kMagic)) - kBias;
+    const uint32_t i1 = __float_as_uint(f_add(fy1, kMagic)) * (uint32_t)(BW * 4) + __float_as_uint(f_add(fx1, kMagic)) - kBias;
+    const int v0 = centre[(int)i0], v1 = centre[(int)i1];
     const uint32_t w = __ballot_sync(0xffffffffu, v0 < v1);
     if (lane == j) word_mine = w;
   }
@@ -221,6 +223,7 @@ cudaError_t orbx_launch_describe(const DevPlan& P, Level0 l0, const uint8_t* are
                                  const int32_t* sel_cnt, const int32_t* dst, OrbxKeyPointDev* kps,
                                  uint8_t* desc, int capacity, int strict_fp, int batch, cudaStream_t st) {
   dim3 grd((P.kp_total_cap + DESC_WARPS - 1) / DESC_WARPS, batch);
-  k_describe<<<grd, DESC_WARPS * 32, 0, st>>>(P, l0, arena, sel, sel_cnt, dst, kps, desc, capacity, strict_fp);
+  if (strict_fp) k_describe<true><<<grd, DESC_WARPS * 32, 0, st>>>(P, l0, arena, sel, sel_cnt, dst, kps, desc, capacity);
+  else k_describe<false><<<grd, DESC_WARPS * 32, 0, st>>>(P, l0, arena, sel, sel_cnt, dst, kps, desc, capacity);
   return cudaGetLastError();
 }
