@@ -251,22 +251,33 @@ def main():
 
     # ---- end to end through the host-buffer C-ABI call -------------------------------------------
     cap = ex.max_keypoints
-    # Frames start in pinned HOST memory every step; the step copies them to the device, runs the
-    # C-ABI extract + match entry points and copies {n, keypoints, descriptors, match records}
-    # back into pinned host buffers — all inside the timed region.
+    # Frames start in pinned HOST memory every step; the host-buffer C-ABI entry point copies them
+    # to the device, extracts and copies {n, keypoints, descriptors} back; the match entry points
+    # then score the device-resident copies and the match records are copied back — all inside the
+    # timed region.
     res_pin = torch.empty((B, cap, 12), dtype=torch.uint8, pin_memory=True)
     kps_pin = torch.empty((B, cap, 7), dtype=torch.float32, pin_memory=True)
     desc_pin = torch.empty((B, cap, 32), dtype=torch.uint8, pin_memory=True)
     n_pin = torch.empty((B,), dtype=torch.int32, pin_memory=True)
-    stage_dev = torch.empty_like(frames)
+    mono_pin = torch.empty((B,), dtype=torch.int32, pin_memory=True)
+    host_out = (kps_pin.numpy(), desc_pin.numpy(), n_pin.numpy(), mono_pin.numpy())
+    pinned_np = pinned.numpy()
+    ex_host = ORBextractor(nf, ORB["scale"], ORB["nlevels"], ORB["ini"], ORB["mn"], max_batch=B,
+                           device=local_rank).plan(w, h)
+    dv = ex_host.last_outputs_device(B)
+    qbuf2 = None
 
     def e2e():
-        stage_dev.copy_(pinned, non_blocking=True)
-        r = step(stage_dev)
-        n_pin.copy_(out["n"], non_blocking=True)
-        kps_pin.copy_(out["kps"], non_blocking=True)
-        desc_pin.copy_(out["desc"], non_blocking=True)
+        # orbx_extract_batch_host: H2D of the frames, the kernels and D2H of {n, mono, keypoints,
+        # descriptors}, chunked and overlapped inside the C-ABI call (returns synchronised)
+        nonlocal qbuf2
+        ex_host.extract_batch_host(pinned_np, lap, out=host_out)
+        grid = ORBmatcher.grid_build(dv["kps"], dv["n"], bounds)
+        qbuf2 = ORBmatcher.queries_shift(dv["kps"], dv["desc"], dv["n"], src_frame, shift, MATCH_TH, sf, (-1, 1), qbuf2)
+        r = ORBmatcher.search_area(dv["kps"], dv["desc"], dv["n"], grid, bounds, qbuf2["qx"], qbuf2["qy"], qbuf2["qr"],
+                                   qbuf2["qmin"], qbuf2["qmax"], qbuf2["qdesc"], qbuf2["nq"])
         res_pin.copy_(r, non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the step's results are on the host when it returns
 
     for _ in range(2):
         e2e()

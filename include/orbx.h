@@ -102,6 +102,12 @@ int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int l
                             orbx_keypoint* kps, uint8_t* desc, int capacity, int32_t* n_out,
                             int32_t* mono_index);
 
+/* Device copies of what the last orbx_extract / orbx_extract_batch_host call returned, [batch][capacity]
+ * records with capacity = orbx_max_keypoints(): lets the orbm_* entry points score them without a
+ * second upload.  Valid until the next call on the handle. */
+int orbx_last_outputs_device(orbx_handle h, const orbx_keypoint** d_kps, const uint8_t** d_desc,
+                             const int32_t** d_n, const int32_t** d_mono_index, int* capacity);
+
 /* The "GetPyramid" surface: replaces reads of the public field mvImagePyramid
  * (ORBextractor.h:83; Frame.cc:818,908,918,923).  Copies level `level` of frame `frame` of
  * the last call to host memory; with_border=1 reproduces the (w+38)x(h+38) parent buffer of

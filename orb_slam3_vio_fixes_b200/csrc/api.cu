@@ -1,6 +1,7 @@
 // api.cu — the C ABI of include/orbx.h: handle management and the per-frame launch sequence
 // (ORBextractor::operator(), src/ORBextractor.cc:1086-1168).
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -45,6 +46,7 @@ struct orbx_extractor_s {
   uint8_t* o_desc = nullptr;
   int32_t *o_n = nullptr, *o_mono = nullptr;
   uint8_t* border_tmp = nullptr;
+  uint8_t* stage = nullptr;  // tightly packed level-0 frames of the host batch API (lazy)
   // octree launch geometry
   size_t oct_smem;
   int oct_smem_keys, oct_node_cap, oct_max_cells;
@@ -53,6 +55,10 @@ struct orbx_extractor_s {
   int last_batch = 0;
   cudaEvent_t ev[ORBX_NUM_STAGES + 1] = {};
   bool timed = false;
+  // orbx_extract_batch_host pipeline: copy-in / two compute / copy-out streams, one event pair per chunk
+  cudaStream_t s_in = nullptr, s_out = nullptr, s_cmp[2] = {nullptr, nullptr};
+  std::vector<cudaEvent_t> ev_in, ev_done;
+  int host_chunk = 64;
 };
 
 static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
@@ -82,9 +88,15 @@ void orbx_destroy(orbx_handle h) {
   cudaFree(h->arena); cudaFree(h->xtaps); cudaFree(h->ytaps); cudaFree(h->cell_cnt); cudaFree(h->cand);
   cudaFree(h->gkeys); cudaFree(h->glabels); cudaFree(h->sel); cudaFree(h->sel_cnt); cudaFree(h->dst);
   cudaFree(h->status); cudaFree(h->o_kps); cudaFree(h->o_desc); cudaFree(h->o_n); cudaFree(h->o_mono);
-  cudaFree(h->border_tmp);
+  cudaFree(h->border_tmp); cudaFree(h->stage);
   for (int i = 0; i <= ORBX_NUM_STAGES; i++)
     if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+  for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
+  for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
+  if (h->s_in) cudaStreamDestroy(h->s_in);
+  if (h->s_out) cudaStreamDestroy(h->s_out);
+  for (int i = 0; i < 2; i++)
+    if (h->s_cmp[i]) cudaStreamDestroy(h->s_cmp[i]);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -180,28 +192,42 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
 
 int orbx_max_keypoints(orbx_handle h) { return h ? h->plan.max_keypoints : ORBX_E_INVALID; }
 
+// Runs the launch sequence for `batch` frames whose per-frame scratch (pyramid arena, candidate
+// slots, selections) starts at frame slot f0 of the handle; l0 and the outputs point at the first
+// of those frames.
 static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1, OrbxKeyPointDev* d_kps,
-                        uint8_t* d_desc, int capacity, int32_t* d_n, int32_t* d_mono, cudaStream_t st) {
+                        uint8_t* d_desc, int capacity, int32_t* d_n, int32_t* d_mono, cudaStream_t st,
+                        int f0 = 0, bool allow_timing = true) {
   const DevPlan& D = h->dplan;
-  const bool tm = (h->cfg.flags & ORBX_FLAG_STAGE_TIMING) != 0;
+  const bool tm = allow_timing && (h->cfg.flags & ORBX_FLAG_STAGE_TIMING) != 0;
+  uint8_t* arena = h->arena + (long long)f0 * D.arena_bytes;
+  int32_t* cell_cnt = h->cell_cnt + (long long)f0 * D.total_cells;
+  uint32_t* cand = h->cand + (long long)f0 * D.cand_total;
+  uint32_t* gkeys = h->gkeys + (long long)f0 * D.cand_total;
+  int16_t* glabels = h->glabels + (long long)f0 * D.cand_total;
+  uint32_t* sel = h->sel + (long long)f0 * D.kp_total_cap;
+  int32_t* sel_cnt = h->sel_cnt + (long long)f0 * D.nlevels;
+  int32_t* dst = h->dst + (long long)f0 * D.kp_total_cap;
 #define STAGE_MARK(i) do { if (tm) CU(cudaEventRecord(h->ev[i], st)); } while (0)
   STAGE_MARK(0);
-  CU(orbx_launch_pyramid(D, l0, h->arena, h->xtaps, h->ytaps, batch, st));
+  CU(orbx_launch_pyramid(D, l0, arena, h->xtaps, h->ytaps, batch, st));
   STAGE_MARK(1);
-  CU(orbx_launch_fast(D, l0, h->arena, h->cell_cnt, h->cand, batch, st));
+  CU(orbx_launch_fast(D, l0, arena, cell_cnt, cand, batch, st));
   STAGE_MARK(2);
-  CU(orbx_launch_octree(D, h->cell_cnt, h->cand, h->gkeys, h->glabels, h->sel, h->sel_cnt, h->status, batch,
+  CU(orbx_launch_octree(D, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, h->status, batch,
                         h->oct_smem, h->oct_smem_keys, h->oct_node_cap, h->oct_max_cells, st));
   STAGE_MARK(3);
-  CU(orbx_launch_order(D, h->sel, h->sel_cnt, lap0, lap1, h->dst, d_n, d_mono, batch, st));
+  CU(orbx_launch_order(D, sel, sel_cnt, lap0, lap1, dst, d_n, d_mono, batch, st));
   STAGE_MARK(4);
-  CU(orbx_launch_describe(D, l0, h->arena, h->sel, h->sel_cnt, h->dst, d_kps, d_desc, capacity,
+  CU(orbx_launch_describe(D, l0, arena, sel, sel_cnt, dst, d_kps, d_desc, capacity,
                           (h->cfg.flags & ORBX_FLAG_STRICT_FP) ? 1 : 0, batch, st));
   STAGE_MARK(5);
 #undef STAGE_MARK
-  h->timed = tm;
-  h->last_l0 = l0;
-  h->last_batch = batch;
+  if (allow_timing) h->timed = tm;
+  if (f0 == 0) {
+    h->last_l0 = l0;
+    h->last_batch = batch;
+  }
   return ORBX_OK;
 }
 
@@ -226,23 +252,73 @@ int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int l
   const OrbxPlan& P = h->plan;
   if (capacity < P.max_keypoints) { set_err("capacity < orbx_max_keypoints()", cudaSuccess); return ORBX_E_CAPACITY; }
   CU(cudaSetDevice(h->device));
-  cudaStream_t st = h->stream;
   const int W = P.width, H = P.height, mk = P.max_keypoints;
-  // H2D straight into each frame's level-0 slot of the arena
-  for (int f = 0; f < batch; f++)
-    CU(cudaMemcpy2DAsync(h->arena + (long long)f * P.arena_bytes, P.lv[0].pitch, imgs + (size_t)f * W * H, W, W, H,
-                         cudaMemcpyHostToDevice, st));
-  Level0 l0;
-  l0.base = h->arena; l0.frame_stride = P.arena_bytes; l0.pitch = P.lv[0].pitch;
-  int rc = run_pipeline(h, l0, batch, lap0, lap1, h->o_kps, h->o_desc, mk, h->o_n, h->o_mono, st);
-  if (rc) return rc;
-  CU(cudaMemcpyAsync(n_out, h->o_n, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(mono_index, h->o_mono, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpy2DAsync(kps, (size_t)capacity * sizeof(orbx_keypoint), h->o_kps, (size_t)mk * sizeof(orbx_keypoint),
-                       (size_t)mk * sizeof(orbx_keypoint), batch, cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpy2DAsync(desc, (size_t)capacity * 32, h->o_desc, (size_t)mk * 32, (size_t)mk * 32, batch,
-                       cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
+  // Chunked pipeline: while chunk c is being extracted, chunk c+1 is on its way in and chunk c-1 on its
+  // way out (PCIe is full duplex).  Chunks own disjoint frame slots of the handle's scratch, so two
+  // compute streams may run neighbouring chunks concurrently and fill each other's kernel tails.
+  if (!h->s_in) {
+    CU(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&h->s_cmp[0], cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&h->s_cmp[1], cudaStreamNonBlocking));
+    if (const char* e = getenv("ORBX_HOST_CHUNK")) { const int v = atoi(e); if (v > 0) h->host_chunk = v; }
+  }
+  if (!h->stage) {
+    cudaError_t e_ = cudaMalloc((void**)&h->stage, (size_t)h->cfg.max_batch * W * H + 512);
+    if (e_ != cudaSuccess) { set_err("cudaMalloc stage", e_); return e_ == cudaErrorMemoryAllocation ? ORBX_E_NOMEM : ORBX_E_CUDA; }
+  }
+  const int chunk = h->host_chunk < batch ? h->host_chunk : batch;
+  const int nchunks = (batch + chunk - 1) / chunk;
+  while ((int)h->ev_in.size() < nchunks) {
+    cudaEvent_t a, b;
+    CU(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+    h->ev_in.push_back(a); h->ev_done.push_back(b);
+  }
+  // anything still running on the handle's own stream (single-frame API) must be done first
+  CU(cudaStreamSynchronize(h->stream));
+  for (int c = 0; c < nchunks; c++) {
+    const int f0 = c * chunk, nb = (batch - f0) < chunk ? (batch - f0) : chunk;
+    cudaStream_t cs = h->s_cmp[c & 1];
+    // One contiguous H2D per chunk into the tightly packed staging frames, which then serve as
+    // level 0 directly (row pitch = W): strided 2-D copies of 752-byte rows run far below PCIe rate.
+    CU(cudaMemcpyAsync(h->stage + (size_t)f0 * W * H, imgs + (size_t)f0 * W * H, (size_t)nb * W * H,
+                       cudaMemcpyHostToDevice, h->s_in));
+    CU(cudaEventRecord(h->ev_in[c], h->s_in));
+    CU(cudaStreamWaitEvent(cs, h->ev_in[c], 0));
+    Level0 l0;
+    l0.base = h->stage + (size_t)f0 * W * H; l0.frame_stride = (long long)W * H; l0.pitch = W;
+    int rc = run_pipeline(h, l0, nb, lap0, lap1, h->o_kps + (long long)f0 * mk, h->o_desc + (long long)f0 * mk * 32, mk,
+                          h->o_n + f0, h->o_mono + f0, cs, f0, false);
+    if (rc) return rc;
+    CU(cudaEventRecord(h->ev_done[c], cs));
+    CU(cudaStreamWaitEvent(h->s_out, h->ev_done[c], 0));
+    CU(cudaMemcpyAsync(n_out + f0, h->o_n + f0, nb * sizeof(int32_t), cudaMemcpyDeviceToHost, h->s_out));
+    CU(cudaMemcpyAsync(mono_index + f0, h->o_mono + f0, nb * sizeof(int32_t), cudaMemcpyDeviceToHost, h->s_out));
+    CU(cudaMemcpy2DAsync(kps + (size_t)f0 * capacity, (size_t)capacity * sizeof(orbx_keypoint),
+                         h->o_kps + (long long)f0 * mk, (size_t)mk * sizeof(orbx_keypoint),
+                         (size_t)mk * sizeof(orbx_keypoint), nb, cudaMemcpyDeviceToHost, h->s_out));
+    CU(cudaMemcpy2DAsync(desc + (size_t)f0 * capacity * 32, (size_t)capacity * 32, h->o_desc + (long long)f0 * mk * 32,
+                         (size_t)mk * 32, (size_t)mk * 32, nb, cudaMemcpyDeviceToHost, h->s_out));
+  }
+  h->last_l0.base = h->stage; h->last_l0.frame_stride = (long long)W * H; h->last_l0.pitch = W;
+  h->last_batch = batch;
+  CU(cudaStreamSynchronize(h->s_out));
+  CU(cudaStreamSynchronize(h->s_cmp[0]));
+  CU(cudaStreamSynchronize(h->s_cmp[1]));
+  return ORBX_OK;
+}
+
+/* Device copies of what the last orbx_extract / orbx_extract_batch_host call returned (so that the
+ * matcher entry points can run on them without a second upload). */
+int orbx_last_outputs_device(orbx_handle h, const orbx_keypoint** d_kps, const uint8_t** d_desc,
+                             const int32_t** d_n, const int32_t** d_mono, int* capacity) {
+  if (!h) return ORBX_E_INVALID;
+  if (d_kps) *d_kps = (const orbx_keypoint*)h->o_kps;
+  if (d_desc) *d_desc = h->o_desc;
+  if (d_n) *d_n = h->o_n;
+  if (d_mono) *d_mono = h->o_mono;
+  if (capacity) *capacity = h->plan.max_keypoints;
   return ORBX_OK;
 }
 

@@ -14,6 +14,22 @@ from . import _lib
 from ._lib import KP_DTYPE
 
 
+class DevView:
+    """A library-owned device buffer seen as (pointer, shape, device) — the three things the
+    batched matcher wrappers read from a torch tensor."""
+
+    def __init__(self, ptr, shape, device):
+        self._ptr, self.shape, self._dev = int(ptr), tuple(shape), device
+
+    def data_ptr(self):
+        return self._ptr
+
+    @property
+    def device(self):
+        import torch
+        return torch.device(self._dev)
+
+
 class ORBextractor:
     HARRIS_SCORE, FAST_SCORE = 0, 1
 
@@ -75,22 +91,41 @@ class ORBextractor:
         _lib.check(rc, "orbx_extract")
         return mono.value, kps[:n.value].copy(), desc[:n.value].copy()
 
-    def extract_batch_host(self, frames, vLappingArea=(0, 0)):
+    def extract_batch_host(self, frames, vLappingArea=(0, 0), out=None):
         """frames: uint8 [B,H,W] host array (pinned for full speed).  Returns (kps[B,cap], desc[B,cap,32],
-        n[B], mono[B]) as numpy arrays; copies in and out are inside the call."""
+        n[B], mono[B]) as numpy arrays; copies in and out are inside the call (chunked so that H2D,
+        kernels and D2H overlap).  `out` = the same four arrays preallocated (e.g. views of pinned
+        torch tensors; kps may be any C-contiguous [B,cap,28-byte] buffer)."""
         b, hgt, w = frames.shape
         self._ensure(w, hgt)
         cap = self.max_keypoints
-        kps = np.zeros((b, cap), KP_DTYPE)
-        desc = np.zeros((b, cap, 32), np.uint8)
-        n = np.zeros(b, np.int32)
-        mono = np.zeros(b, np.int32)
+        if out is None:
+            kps = np.zeros((b, cap), KP_DTYPE)
+            desc = np.zeros((b, cap, 32), np.uint8)
+            n = np.zeros(b, np.int32)
+            mono = np.zeros(b, np.int32)
+        else:
+            kps, desc, n, mono = out
+            assert kps.nbytes == b * cap * 28 and desc.nbytes == b * cap * 32 and n.nbytes == 4 * b == mono.nbytes
+            assert all(a.flags["C_CONTIGUOUS"] for a in out)
         frames = np.ascontiguousarray(frames)
         rc = _lib.lib().orbx_extract_batch_host(self._h, frames.ctypes.data, b, int(vLappingArea[0]),
                                                 int(vLappingArea[1]), kps.ctypes.data, desc.ctypes.data, cap,
                                                 n.ctypes.data, mono.ctypes.data)
         _lib.check(rc, "orbx_extract_batch_host")
         return kps, desc, n, mono
+
+    def last_outputs_device(self, batch):
+        """Device-resident copies of what the last extract_batch_host / __call__ returned, as
+        pointer views (data_ptr / shape / device) the ORBmatcher batched cores accept."""
+        ptrs = [C.c_void_p() for _ in range(4)]
+        cap = C.c_int(0)
+        _lib.check(_lib.lib().orbx_last_outputs_device(self._h, *[C.byref(p) for p in ptrs], C.byref(cap)),
+                   "orbx_last_outputs_device")
+        dev = f"cuda:{self.device}"
+        return {"kps": DevView(ptrs[0].value, (batch, cap.value, 7), dev),
+                "desc": DevView(ptrs[1].value, (batch, cap.value, 32), dev),
+                "n": DevView(ptrs[2].value, (batch,), dev), "mono": DevView(ptrs[3].value, (batch,), dev)}
 
     def extract_batch_device(self, frames, vLappingArea=(0, 0), out=None, stream=None):
         """frames: torch uint8 CUDA tensor [B,H,W] (row stride = pitch).  Asynchronous on `stream`
