@@ -232,6 +232,71 @@ k_search_area(const OrbxKeyPointDev* __restrict__ kps, const uint8_t* __restrict
   }
 }
 
+// Same result, one THREAD per query: a window holds only a few dozen candidates spread over several
+// short CSR runs, which leaves a warp-per-query mostly idle.  Here a lane walks its own query's runs
+// (best/second are plain sequential updates on the packed keys) and the 32 lanes of a warp work on
+// 32 neighbouring queries; queries are level-major, so the lanes of a warp have similar trip counts.
+#define SA_THREADS 128
+__global__ void __launch_bounds__(SA_THREADS)
+k_search_area_tq(const OrbxKeyPointDev* __restrict__ kps, const uint8_t* __restrict__ desc,
+                 const int32_t* __restrict__ n_arr, int kp_stride, const int32_t* __restrict__ cell_off,
+                 const int32_t* __restrict__ cell_idx, float min_x, float min_y, float winv, float hinv,
+                 const float* __restrict__ qx, const float* __restrict__ qy, const float* __restrict__ qr,
+                 const int8_t* __restrict__ qmin, const int8_t* __restrict__ qmax,
+                 const uint8_t* __restrict__ qdesc, const int32_t* __restrict__ nq_arr, int q_stride, int tie_rule,
+                 orbm_result* __restrict__ out) {
+  const int f = blockIdx.y;
+  const int qi = blockIdx.x * SA_THREADS + threadIdx.x;
+  if (qi >= nq_arr[f]) return;
+  const size_t qo = (size_t)f * q_stride + qi;
+  const float x = qx[qo], y = qy[qo], r = qr[qo];
+  const int minLevel = qmin[qo], maxLevel = qmax[qo];
+  const OrbxKeyPointDev* k = kps + (size_t)f * kp_stride;
+  const uint8_t* dsc = desc + (size_t)f * kp_stride * 32;
+  const int32_t* off = cell_off + (size_t)f * (GRID_CELLS + 1);
+  const int32_t* idx = cell_idx + (size_t)f * kp_stride;
+  Top2 t;
+  // Frame.cc:665-687
+  const int nMinCellX = max(0, (int)floorf(f_mul(f_sub(f_sub(x, min_x), r), winv)));
+  const int nMaxCellX = min(FRAME_GRID_COLS - 1, (int)ceilf(f_mul(f_add(f_sub(x, min_x), r), winv)));
+  const int nMinCellY = max(0, (int)floorf(f_mul(f_sub(f_sub(y, min_y), r), hinv)));
+  const int nMaxCellY = min(FRAME_GRID_ROWS - 1, (int)ceilf(f_mul(f_add(f_sub(y, min_y), r), hinv)));
+  const bool ok = nMinCellX < FRAME_GRID_COLS && nMaxCellX >= 0 && nMinCellY < FRAME_GRID_ROWS && nMaxCellY >= 0;
+  const int lo = minLevel > 0 ? minLevel : -128;     // bCheckLevels folded into a closed band
+  const int hi = maxLevel >= 0 ? maxLevel : 127;
+  if (ok) {
+    const Desc256 dq = load_desc(qdesc + qo * 32);
+    int seq = 0, ix = nMinCellX, e = 0, e1 = 0;
+    while (true) {
+      if (e >= e1) {  // next column of cells: (ix, nMinCellY..nMaxCellY) is one contiguous CSR run
+        if (ix > nMaxCellX) break;
+        e = off[ix * FRAME_GRID_ROWS + nMinCellY];
+        e1 = off[ix * FRAME_GRID_ROWS + nMaxCellY + 1];
+        ix++;
+        continue;
+      }
+      const int j = idx[e];
+      const float kx = k[j].x, ky = k[j].y;
+      const int oct = k[j].octave;
+      if (oct >= lo && oct <= hi && fabsf(f_sub(kx, x)) < r && fabsf(f_sub(ky, y)) < r) {
+        const int d = hamming(dq, load_desc(dsc + (size_t)j * 32));
+        t.push(make_key(d, seq & 0xFFFFF, tie_rule), j);
+      }
+      seq++;
+      e++;
+    }
+  }
+  orbm_result res;
+  res.best_idx = t.i1;
+  res.best_dist = t.i1 >= 0 ? (int16_t)(t.k1 >> 20) : (int16_t)256;
+  res.best_level = t.i1 >= 0 ? (int8_t)k[t.i1].octave : (int8_t)-1;
+  const bool has2 = tie_rule == ORBM_TIE_FIRST_MIN && t.i2 >= 0;
+  res.second_dist = has2 ? (int16_t)(t.k2 >> 20) : (int16_t)256;
+  res.second_level = has2 ? (int8_t)k[t.i2].octave : (int8_t)-1;
+  res.pad = 0;
+  out[qo] = res;
+}
+
 // ---- Hamming stage of Frame::ComputeStereoMatches (Frame.cc:811-894) -------------------------------
 struct ScaleTab { float s[ORBX_MAX_LEVELS]; };
 
@@ -360,8 +425,8 @@ int orbm_search_area(const orbx_keypoint* d_kps, const uint8_t* d_desc, const in
       !d_qmax_level || !d_qdesc || !d_nq || !d_out || batch < 1 || q_stride < 1)
     return ORBX_E_INVALID;
   const float winv = (float)FRAME_GRID_COLS / (max_x - min_x), hinv = (float)FRAME_GRID_ROWS / (max_y - min_y);
-  dim3 grd((q_stride + M_WARPS - 1) / M_WARPS, batch);
-  k_search_area<<<grd, M_WARPS * 32, 0, (cudaStream_t)stream>>>(
+  dim3 grd((q_stride + SA_THREADS - 1) / SA_THREADS, batch);
+  k_search_area_tq<<<grd, SA_THREADS, 0, (cudaStream_t)stream>>>(
       (const OrbxKeyPointDev*)d_kps, d_desc, d_n, kp_stride, d_cell_off, d_cell_idx, min_x, min_y, winv, hinv, d_qx,
       d_qy, d_qr, d_qmin_level, d_qmax_level, d_qdesc, d_nq, q_stride, tie_rule, d_out);
   CUM(cudaGetLastError());
