@@ -137,6 +137,11 @@ int orbx_stage_times(orbx_handle h, float* ms);
  * Fills up to cap entries of (x, y, response) int32 triples; returns the count in *n. */
 int orbx_debug_level_keypoints(orbx_handle h, int frame, int level, int stage, int32_t* xyr,
                                int cap, int* n);
+/* Test hook: DistributeOctTree (ORBextractor.cc:555-779) of one level on caller-supplied keys
+ * (x, y relative to the 16-px border, response); returns the kept keys in list order. */
+int orbx_debug_octree(orbx_handle h, int level, const int32_t* xys, int n, int32_t* out_xys, int cap,
+                      int* n_out);
+
 
 /* ----------------------------------------------------------------------------------------
  * Matcher cores.  ORBmatcher::DescriptorDistance (ORBmatcher.h:43, ORBmatcher.cc:2058-2074)

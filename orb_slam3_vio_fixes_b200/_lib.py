@@ -32,7 +32,7 @@ RES_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i2"), ("second_dist",
 SYMBOLS = [
     "orbx_create", "orbx_destroy", "orbx_max_keypoints", "orbx_extract", "orbx_extract_batch_device",
     "orbx_extract_batch_host", "orbx_last_outputs_device", "orbx_get_pyramid", "orbx_pyramid_device", "orbx_level_size",
-    "orbx_get_scale_tables", "orbx_stage_times", "orbx_debug_level_keypoints", "orbm_argmin2_csr", "orbm_grid_build",
+    "orbx_get_scale_tables", "orbx_stage_times", "orbx_debug_level_keypoints", "orbx_debug_octree", "orbm_argmin2_csr", "orbm_grid_build",
     "orbm_search_area", "orbm_queries_shift", "orbm_stereo_rowband", "orbm_knn2_dense", "orbx_version", "orbx_last_error",
 ]
 
@@ -82,6 +82,7 @@ def lib():
     L.orbx_get_scale_tables.argtypes = [vp, vp, vp, vp, vp, vp]
     L.orbx_stage_times.argtypes = [vp, vp]
     L.orbx_debug_level_keypoints.argtypes = [vp, i32, i32, i32, vp, i32, C.POINTER(i32)]
+    L.orbx_debug_octree.argtypes = [vp, i32, vp, i32, vp, i32, C.POINTER(i32)]
     L.orbm_argmin2_csr.argtypes = [vp, i32, vp, i32, vp, vp, vp, i32, vp, vp]
     L.orbm_grid_build.argtypes = [vp, vp, i32, i32, f32, f32, f32, f32, vp, vp, vp]
     L.orbm_search_area.argtypes = [vp, vp, vp, i32, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp, vp,

@@ -129,11 +129,11 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   int node_cap = 0, max_cells = 0;
   for (int l = 0; l < P.nlevels; l++) {
     if (P.lv[l].nIni > 64) { delete h; set_err("aspect ratio > 64", cudaSuccess); return ORBX_E_INVALID; }
-    node_cap = node_cap > 2 * P.lv[l].kp_max + 8 ? node_cap : 2 * P.lv[l].kp_max + 8;
+    node_cap = node_cap > P.lv[l].kp_max + 4 ? node_cap : P.lv[l].kp_max + 4;  // list never exceeds kp_max
     const int nc = P.lv[l].nCols * P.lv[l].nRows;
     max_cells = max_cells > nc ? max_cells : nc;
   }
-  if (node_cap > 32000) { delete h; set_err("nfeatures too large for 16-bit node ids", cudaSuccess); return ORBX_E_INVALID; }
+  if (node_cap > 8000) { delete h; set_err("nfeatures too large for 16-bit node positions", cudaSuccess); return ORBX_E_INVALID; }
   fill_devplan(P, &h->dplan);
   h->oct_node_cap = node_cap;
   h->oct_max_cells = max_cells;
@@ -444,6 +444,46 @@ int orbx_debug_level_keypoints(orbx_handle h, int frame, int level, int stage, i
   *n = (int)keys.size();
   for (int i = 0; i < (int)keys.size() && i < cap; i++) {
     xyr[3 * i] = ORBX_KEY_X(keys[i]); xyr[3 * i + 1] = ORBX_KEY_Y(keys[i]); xyr[3 * i + 2] = ORBX_KEY_S(keys[i]);
+  }
+  return ORBX_OK;
+}
+
+/* Test hook: runs DistributeOctTree of `level` on caller-supplied keys (x, y relative to the
+ * (16,16) border like the reference's vToDistributeKeys, response) and returns the selected keys in
+ * list order.  The keys are laid into the level's cell slots in order, so the kernel gathers them
+ * back in the given order. */
+int orbx_debug_octree(orbx_handle h, int level, const int32_t* xys, int n, int32_t* out_xys, int cap, int* n_out) {
+  if (!h || !n_out || level < 0 || level >= h->plan.nlevels || n < 0 || (n > 0 && !xys)) return ORBX_E_INVALID;
+  const OrbxPlan& P = h->plan;
+  const OrbxLevel& L = P.lv[level];
+  const int ncell = L.nCols * L.nRows;
+  if ((long long)n > (long long)ncell * L.cell_cap) return ORBX_E_CAPACITY;
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  std::vector<int32_t> cnt(P.total_cells, 0);
+  std::vector<uint32_t> slots((size_t)L.cand_cap, 0);
+  for (int i = 0; i < n; i++) {
+    const int c = i / L.cell_cap, j = i % L.cell_cap;
+    if (xys[3 * i] < 0 || xys[3 * i] > 4095 || xys[3 * i + 1] < 0 || xys[3 * i + 1] > 4095) return ORBX_E_INVALID;
+    slots[(size_t)c * L.cell_cap + j] = orbx_pack_key(xys[3 * i], xys[3 * i + 1], xys[3 * i + 2] & 0xff);
+    cnt[L.cell_base + c]++;
+  }
+  CU(cudaMemcpy(h->cell_cnt, cnt.data(), cnt.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  if (n) CU(cudaMemcpy(h->cand + L.cand_base, slots.data(), slots.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  CU(orbx_launch_octree(h->dplan, h->cell_cnt, h->cand, h->gkeys, h->glabels, h->sel, h->sel_cnt, h->status, 1,
+                        h->oct_smem, h->oct_smem_keys, h->oct_node_cap, h->oct_max_cells, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  int32_t m = 0, st = 0;
+  CU(cudaMemcpy(&m, h->sel_cnt + level, sizeof(int32_t), cudaMemcpyDeviceToHost));
+  CU(cudaMemcpy(&st, h->status, sizeof(int32_t), cudaMemcpyDeviceToHost));
+  if (st) { CU(cudaMemset(h->status, 0, sizeof(int32_t))); set_err("octree node pool overflow", cudaSuccess); return ORBX_E_CUDA; }
+  *n_out = m;
+  std::vector<uint32_t> keys(m > 0 ? m : 1);
+  if (m) CU(cudaMemcpy(keys.data(), h->sel + L.kp_base, (size_t)m * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < m && i < cap; i++) {
+    out_xys[3 * i] = ORBX_KEY_X(keys[i]) - ORBX_MIN_BORDER;
+    out_xys[3 * i + 1] = ORBX_KEY_Y(keys[i]) - ORBX_MIN_BORDER;
+    out_xys[3 * i + 2] = ORBX_KEY_S(keys[i]);
   }
   return ORBX_OK;
 }

@@ -1,34 +1,68 @@
 // octree.cu — ORBextractor::DistributeOctTree (src/ORBextractor.cc:555-779) on device.
-// One CTA per (level, frame).  Per-key work (root/quadrant labelling, counting, best-response
-// selection) is spread over the CTA; the list surgery of each round runs in thread 0 through the
-// shared octree_core.h (the same code the CPU harness checks against the oracle).
+// One CTA per (level, frame).  The node list is an array in list order that is rebuilt every round
+// from block-wide prefix sums (octree_core.h, "scan" form — the CPU harness runs the same
+// formulation with plain loops against the oracle); per-key work (root/quadrant labelling,
+// counting, relabelling, best-response selection) is spread over the CTA.  The only serial step
+// left is the libstdc++ std::sort replica that orders the careful phase.
 #include "octree_core.h"
 #include "orbx_kernels.cuh"
 
 #define OCT_THREADS 256
+#define OCT_WARPS (OCT_THREADS / 32)
 #define OCT_MAX_ROOTS 64
 
 struct OctShared {
-  OctState S;
   int root_cnt[OCT_MAX_ROOTS];
-  int n;         // candidates of this level
-  int finished;  // broadcast copy
+  int root_pos[OCT_MAX_ROOTS];
+  int wsum[2][OCT_WARPS];  // block-scan scratch
+  int bcast[4];            // block-wide results (totals, first hit)
 };
 
 // Dynamic shared memory carve-up (see orbx_octree_smem_bytes):
-//   OctShared | nodes[node_cap] | vec[node_cap] | vec2[node_cap] | divlist[node_cap]
-//   | best[node_cap] | cell_off[max_cells+1] | keys[smem_keys] | labels[smem_keys]
+//   OctShared | nodes A[cap] | nodes B[cap] | qc[4*cap] | vec[cap] | vec2[cap] | best[cap]
+//   | newpos[cap] (i16) | preK[cap] (i16) | preE[cap] (i16) | proc[cap] (u8)
+//   | cell_off[max_cells+1] | keys[smem_keys] | labels[smem_keys]
 size_t orbx_octree_smem_bytes(int smem_keys, int node_cap, int max_cells) {
+  const size_t cap = (size_t)((node_cap + 7) & ~7);
   size_t b = (sizeof(OctShared) + 15) & ~(size_t)15;
-  b += ((size_t)node_cap * sizeof(OctNode) + 15) & ~(size_t)15;
-  b += 2 * (size_t)node_cap * sizeof(uint64_t);
-  b += (size_t)node_cap * sizeof(int);
-  b += (size_t)node_cap * sizeof(uint32_t);
+  b += 2 * cap * sizeof(OctPNode);
+  b += 4 * cap * sizeof(int);
+  b += 2 * cap * sizeof(uint64_t);
+  b += cap * sizeof(uint32_t);
+  b += 3 * cap * sizeof(int16_t);
+  b += cap;
   b += (((size_t)max_cells + 1) * sizeof(int) + 15) & ~(size_t)15;
   b += (size_t)smem_keys * sizeof(uint32_t);
   b += (size_t)smem_keys * sizeof(int16_t);
   return (b + 15) & ~(size_t)15;
 }
+
+// Exclusive block scan of two values per thread (a, b), with the block totals.  Two barriers.
+__device__ __forceinline__ void block_scan2(OctShared& sh, int a, int b, int& ea, int& eb, int& ta, int& tb) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int ia = a, ib = b;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int xa = __shfl_up_sync(0xffffffffu, ia, o), xb = __shfl_up_sync(0xffffffffu, ib, o);
+    if (lane >= o) { ia += xa; ib += xb; }
+  }
+  if (lane == 31) { sh.wsum[0][warp] = ia; sh.wsum[1][warp] = ib; }
+  __syncthreads();
+  int oa = 0, ob = 0;
+  ta = 0; tb = 0;
+#pragma unroll
+  for (int w = 0; w < OCT_WARPS; w++) {
+    const int va = sh.wsum[0][w], vb = sh.wsum[1][w];
+    if (w < warp) { oa += va; ob += vb; }
+    ta += va; tb += vb;
+  }
+  ea = oa + ia - a;
+  eb = ob + ib - b;
+  __syncthreads();
+}
+
+__device__ __forceinline__ int quad_K(const int* c) { return (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0); }
+__device__ __forceinline__ int quad_E(const int* c) { return (c[0] > 1) + (c[1] > 1) + (c[2] > 1) + (c[3] > 1); }
 
 __global__ void __launch_bounds__(OCT_THREADS)
 k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt,
@@ -39,20 +73,31 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
   const int level = blockIdx.x, frame = blockIdx.y;
   const DevLevel& L = P.lv[level];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int cap = (node_cap + 7) & ~7;
 
   unsigned char* p = smem_raw;
   OctShared& sh = *reinterpret_cast<OctShared*>(p);
   p += (sizeof(OctShared) + 15) & ~(size_t)15;
-  OctNode* nodes = reinterpret_cast<OctNode*>(p);
-  p += ((size_t)node_cap * sizeof(OctNode) + 15) & ~(size_t)15;
+  OctPNode* cur = reinterpret_cast<OctPNode*>(p);
+  p += (size_t)cap * sizeof(OctPNode);
+  OctPNode* nxt = reinterpret_cast<OctPNode*>(p);
+  p += (size_t)cap * sizeof(OctPNode);
+  int* qc = reinterpret_cast<int*>(p);
+  p += 4 * (size_t)cap * sizeof(int);
   uint64_t* vec = reinterpret_cast<uint64_t*>(p);
-  p += (size_t)node_cap * sizeof(uint64_t);
+  p += (size_t)cap * sizeof(uint64_t);
   uint64_t* vec2 = reinterpret_cast<uint64_t*>(p);
-  p += (size_t)node_cap * sizeof(uint64_t);
-  int* divlist = reinterpret_cast<int*>(p);
-  p += (size_t)node_cap * sizeof(int);
+  p += (size_t)cap * sizeof(uint64_t);
   uint32_t* best = reinterpret_cast<uint32_t*>(p);
-  p += (size_t)node_cap * sizeof(uint32_t);
+  p += (size_t)cap * sizeof(uint32_t);
+  int16_t* newpos = reinterpret_cast<int16_t*>(p);
+  p += (size_t)cap * sizeof(int16_t);
+  int16_t* preKs = reinterpret_cast<int16_t*>(p);
+  p += (size_t)cap * sizeof(int16_t);
+  int16_t* preEs = reinterpret_cast<int16_t*>(p);
+  p += (size_t)cap * sizeof(int16_t);
+  uint8_t* proc = reinterpret_cast<uint8_t*>(p);
+  p += (size_t)cap;
   int* cell_off = reinterpret_cast<int*>(p);
   p += (((size_t)max_cells + 1) * sizeof(int) + 15) & ~(size_t)15;
   uint32_t* skeys = reinterpret_cast<uint32_t*>(p);
@@ -62,42 +107,30 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
   // ---- 1. exclusive scan of the per-cell counts (cell-major order = reference's input order)
   const int ncell = L.nCols * L.nRows;
   const int32_t* cc = cell_cnt + (long long)frame * P.total_cells + L.cell_base;
-  __shared__ int warp_sums[OCT_THREADS / 32];
-  __shared__ int carry_s;
-  if (tid == 0) carry_s = 0;
-  __syncthreads();
+  int n = 0;
   for (int base = 0; base < ncell; base += OCT_THREADS) {
     const int c = base + tid;
     const int v = c < ncell ? cc[c] : 0;
-    int inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += t;
-    }
-    if (lane == 31) warp_sums[warp] = inc;
-    __syncthreads();
-    int woff = 0;
-#pragma unroll
-    for (int w = 0; w < OCT_THREADS / 32; w++)
-      if (w < warp) woff += warp_sums[w];
-    const int carry = carry_s;
-    if (c < ncell) cell_off[c] = carry + woff + inc - v;
-    __syncthreads();
-    if (tid == OCT_THREADS - 1) carry_s = carry + woff + inc;
-    __syncthreads();
+    int ev, e2, tv, t2;
+    block_scan2(sh, v, 0, ev, e2, tv, t2);
+    if (c < ncell) cell_off[c] = n + ev;
+    n += tv;
   }
-  const int n = carry_s;
-  if (tid == 0) { cell_off[ncell] = n; sh.n = n; }
+  if (tid == 0) cell_off[ncell] = n;
   for (int i = tid; i < OCT_MAX_ROOTS; i += OCT_THREADS) sh.root_cnt[i] = 0;
   __syncthreads();
+  int32_t* cnt_out = sel_cnt + frame * P.nlevels + level;
+  if (n == 0) {
+    if (tid == 0) *cnt_out = 0;
+    return;
+  }
 
   // ---- 2. gather keys (warp per cell), label with the root node, count keys per root
   const long long lvl_off = (long long)frame * P.cand_total + L.cand_base;
   uint32_t* keys = n <= smem_keys ? skeys : gkeys + lvl_off;
   int16_t* labels = n <= smem_keys ? slabels : glabels + lvl_off;
   const uint32_t* lc = cand + lvl_off;
-  for (int c = warp; c < ncell; c += OCT_THREADS / 32) {
+  for (int c = warp; c < ncell; c += OCT_WARPS) {
     const int o = cell_off[c], m = cell_off[c + 1] - o;
     for (int i = lane; i < m; i += 32) {
       const uint32_t k = lc[(long long)c * L.cell_cap + i];
@@ -108,64 +141,160 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
     }
   }
   __syncthreads();
-
-  // ---- 3. rounds
-  if (tid == 0) {
-    OctState& S = sh.S;
-    S.nodes = nodes; S.node_cap = node_cap; S.vec = vec; S.vec2 = vec2; S.divlist = divlist; S.N = L.nfeat;
-    oct_init(S, L.nIni, L.hX, L.h - 2 * ORBX_MIN_BORDER, sh.root_cnt);
-    sh.finished = 0;
+  // roots that received keys, in index order, are the initial list (:589-601)
+  const int N = L.nfeat;
+  int S;
+  {
+    const int nIni = L.nIni;  // <= OCT_MAX_ROOTS (checked at plan time)
+    const int c = tid < nIni ? sh.root_cnt[tid] : 0;
+    int e, e2, tot, t2;
+    block_scan2(sh, c > 0 ? 1 : 0, 0, e, e2, tot, t2);
+    if (tid < nIni) {
+      sh.root_pos[tid] = c > 0 ? e : -1;
+      if (c > 0) cur[e] = octp_root(tid, L.hX, L.h - 2 * ORBX_MIN_BORDER, c);
+    }
+    S = tot;
   }
   __syncthreads();
+  for (int i = tid; i < n; i += OCT_THREADS) labels[i] = (int16_t)sh.root_pos[labels[i]];
+  __syncthreads();
+
+  // ---- 3. rounds (octree_core.h, "scan" form)
+  int nvec = 0;
+  bool careful = false, overflow = false;
   while (true) {
-    // (1) quadrant counts of candidate nodes
+    const int prevS = S;
+    for (int q = tid; q < S; q += OCT_THREADS) {
+      proc[q] = 0;
+      *reinterpret_cast<int4*>(qc + 4 * q) = make_int4(0, 0, 0, 0);
+    }
+    __syncthreads();
+    // (a) keys of nodes that may be divided vote for their quadrant
     for (int i = tid; i < n; i += OCT_THREADS) {
-      OctNode& nd = nodes[labels[i]];
-      if (nd.cand) {
+      const int pl = labels[i];
+      const OctPNode nd = cur[pl];
+      if (nd.cnt > 1) {
         const uint32_t k = keys[i];
-        atomicAdd(&nd.c[oct_quadrant(nd, ORBX_KEY_X(k), ORBX_KEY_Y(k))], 1);
+        atomicAdd(&qc[4 * pl + octp_quadrant(nd, ORBX_KEY_X(k), ORBX_KEY_Y(k))], 1);
       }
     }
     __syncthreads();
-    // (2) list surgery
-    if (tid == 0) {
-      oct_round(sh.S);
-      sh.finished = sh.S.finished;
-    }
-    __syncthreads();
-    // (3) relabel keys of divided nodes
-    for (int i = tid; i < n; i += OCT_THREADS) {
-      const OctNode& nd = nodes[labels[i]];
-      if (nd.divided) {
-        const uint32_t k = keys[i];
-        labels[i] = (int16_t)nd.c[oct_quadrant(nd, ORBX_KEY_X(k), ORBX_KEY_Y(k))];
+    int totK = 0, totE = 0, nproc = 0;
+    if (!careful) {
+      // (b) every node with more than one key is divided, in list order (:620-676)
+      {
+        int sk = 0, sd = 0;
+        for (int q = tid; q < S; q += OCT_THREADS)
+          if (cur[q].cnt > 1) { sk += quad_K(qc + 4 * q); sd++; }
+        int e1, e2;
+        block_scan2(sh, sk, sd, e1, e2, totK, nproc);
+      }
+      if (totK + S - nproc > cap) { overflow = true; break; }
+      int carryK = 0, carryE = 0;
+      for (int base = 0; base < S; base += OCT_THREADS) {
+        const int q = base + tid;
+        const bool dv = q < S && cur[q].cnt > 1;
+        int c[4] = {0, 0, 0, 0};
+        if (dv) { const int4 v = *reinterpret_cast<const int4*>(qc + 4 * q); c[0] = v.x; c[1] = v.y; c[2] = v.z; c[3] = v.w; }
+        const int K = quad_K(c), E = quad_E(c);
+        int eK, eE, tK, tE;
+        block_scan2(sh, K, E, eK, eE, tK, tE);
+        if (dv) {
+          proc[q] = 1;
+          octp_emit(cur[q], c, totK - (carryK + eK) - K, carryE + eE, nxt, vec2);
+          *reinterpret_cast<int4*>(qc + 4 * q) = make_int4(c[0], c[1], c[2], c[3]);
+        }
+        carryK += tK; carryE += tE;
+      }
+      totE = carryE;
+    } else {
+      // (c) careful loop (:691-754): candidates sorted by (count, UL.x) with libstdc++'s std::sort,
+      // divided from the back until the list reaches N
+      if (tid == 0) { oct_std_sort(vec, nvec); sh.bcast[0] = 0x7fffffff; }
+      __syncthreads();
+      int carryK = 0, carryE = 0;
+      bool found = false;
+      for (int base = 0; base < nvec; base += OCT_THREADS) {
+        const int s = base + tid;
+        const bool valid = s < nvec;
+        int K = 0, E = 0;
+        if (valid) { const int* c = qc + 4 * (int)(vec[nvec - 1 - s] & 0xffffu); K = quad_K(c); E = quad_E(c); }
+        int eK, eE, tK, tE;
+        block_scan2(sh, K, E, eK, eE, tK, tE);
+        if (valid) { preKs[s] = (int16_t)(carryK + eK); preEs[s] = (int16_t)(carryE + eE); }
+        const bool hit = valid && (S + carryK + eK + K - (s + 1) >= N);
+        if (hit) atomicMin(&sh.bcast[0], s);
+        __syncthreads();
+        const int f = sh.bcast[0];
+        if (f != 0x7fffffff) {
+          if (s == f) { sh.bcast[1] = carryK + eK + K; sh.bcast[2] = carryE + eE + E; }
+          __syncthreads();
+          totK = sh.bcast[1]; totE = sh.bcast[2]; nproc = f + 1;
+          found = true;
+          break;
+        }
+        carryK += tK; carryE += tE;
+      }
+      if (!found) { totK = carryK; totE = carryE; nproc = nvec; }
+      if (totK + S - nproc > cap) { overflow = true; break; }
+      for (int s = tid; s < nproc; s += OCT_THREADS) {
+        const int q = (int)(vec[nvec - 1 - s] & 0xffffu);
+        const int4 v = *reinterpret_cast<const int4*>(qc + 4 * q);
+        int c[4] = {v.x, v.y, v.z, v.w};
+        proc[q] = 1;
+        octp_emit(cur[q], c, totK - preKs[s] - quad_K(c), preEs[s], nxt, vec2);
+        *reinterpret_cast<int4*>(qc + 4 * q) = make_int4(c[0], c[1], c[2], c[3]);
       }
     }
-    const int fin = sh.finished;
     __syncthreads();
-    if (fin) break;
+    // (d) nodes that were not divided keep their relative order behind all the new children
+    int stay = 0;
+    for (int base = 0; base < S; base += OCT_THREADS) {
+      const int q = base + tid;
+      const bool st = q < S && !proc[q];
+      int e, e2, t, t2;
+      block_scan2(sh, st ? 1 : 0, 0, e, e2, t, t2);
+      if (st) {
+        const int pos = totK + stay + e;
+        nxt[pos] = cur[q];
+        newpos[q] = (int16_t)pos;
+      }
+      stay += t;
+    }
+    __syncthreads();
+    // (e) keys follow their node
+    for (int i = tid; i < n; i += OCT_THREADS) {
+      const int pl = labels[i];
+      if (proc[pl]) {
+        const uint32_t k = keys[i];
+        labels[i] = (int16_t)qc[4 * pl + octp_quadrant(cur[pl], ORBX_KEY_X(k), ORBX_KEY_Y(k))];
+      } else {
+        labels[i] = newpos[pl];
+      }
+    }
+    __syncthreads();
+    { OctPNode* t = cur; cur = nxt; nxt = t; }
+    { uint64_t* t = vec; vec = vec2; vec2 = t; }
+    nvec = totE;
+    S = totK + stay;
+    if (S >= N || S == prevS) break;                       // :678-683, :749-750
+    if (!careful && S + 3 * totE > N) careful = true;      // :684
   }
 
-  // ---- 4. best response per node, first key wins ties (:757-778)
-  for (int i = tid; i < node_cap; i += OCT_THREADS) best[i] = 0;
+  // ---- 4. best response per node, first key wins ties (:757-778); list order = array order
+  if (overflow) {
+    if (tid == 0) { *cnt_out = 0; atomicOr(status, 1); }
+    return;
+  }
+  for (int i = tid; i < S; i += OCT_THREADS) best[i] = 0;
   __syncthreads();
   for (int i = tid; i < n; i += OCT_THREADS)
     atomicMax(&best[labels[i]], ((uint32_t)ORBX_KEY_S(keys[i]) << 24) | (0xFFFFFFu - (uint32_t)i));
   __syncthreads();
-  // list order -> rank (serial walk), then parallel emit
-  int* order = divlist;
-  if (tid == 0) {
-    int r = 0;
-    for (int it = sh.S.head; it >= 0; it = nodes[it].next) order[r++] = it;
-    sel_cnt[frame * P.nlevels + level] = sh.S.overflow ? 0 : r;
-    if (sh.S.overflow) atomicOr(status, 1);
-    sh.n = sh.S.overflow ? 0 : r;
-  }
-  __syncthreads();
-  const int nsel = sh.n;
+  if (tid == 0) *cnt_out = S;
   uint32_t* out = sel + (long long)frame * P.kp_total_cap + L.kp_base;
-  for (int r = tid; r < nsel; r += OCT_THREADS) {
-    const int i = (int)(0xFFFFFFu - (best[order[r]] & 0xFFFFFFu));
+  for (int r = tid; r < S; r += OCT_THREADS) {
+    const int i = (int)(0xFFFFFFu - (best[r] & 0xFFFFFFu));
     const uint32_t k = keys[i];
     // back to level coordinates (:883-884)
     out[r] = orbx_pack_key(ORBX_KEY_X(k) + ORBX_MIN_BORDER, ORBX_KEY_Y(k) + ORBX_MIN_BORDER, ORBX_KEY_S(k));

@@ -296,3 +296,71 @@ ORBX_HD void oct_round(OctState& S) {
   uint64_t* t = S.vec; S.vec = S.vec2; S.vec2 = t;
   S.nvec = S.nvec2;
 }
+
+// =================================================================================================
+// Array ("scan") form of the same procedure, used by the CUDA kernel.
+//
+// lNodes is kept as an ARRAY in list order and rebuilt every round, so a node's id is its list
+// position.  A round processes a sequence of nodes proc_0 .. proc_{m-1} (first loop: every node
+// with more than one key, in list order; "careful" loop: the std::sort'ed candidates from the back,
+// up to and including the first one that brings the list to N).  Because every push goes to the
+// FRONT and every processed node is erased, the list after the round is
+//     kids(proc_{m-1}) , ... , kids(proc_1) , kids(proc_0) , <unprocessed nodes in their old order>
+// with kids(p) = its non-empty children in the order n4,n3,n2,n1, and the next round's candidate
+// vector holds the children with more than one key in creation order (proc order, n1..n4).  All
+// positions are therefore prefix sums over the proc order (children) and over the list order
+// (survivors); octp_emit below is the per-node part, the sums are block scans on the GPU and plain
+// loops in the CPU harness (tests/cpu_harness, h_distribute_scan).
+// =================================================================================================
+struct OctPNode {
+  int16_t x0, y0, x1, y1;
+  int32_t cnt;  // vKeys.size(); bNoMore <=> cnt == 1
+};
+
+ORBX_HD int octp_quadrant(const OctPNode& n, int x, int y) {
+  const int mx = n.x0 + ((n.x1 - n.x0 + 1) >> 1);  // UL.x + ceil((UR.x-UL.x)/2)
+  const int my = n.y0 + ((n.y1 - n.y0 + 1) >> 1);
+  return (x < mx ? 0 : 1) | (y < my ? 0 : 2);
+}
+
+// vSizeAndPointerToNode record: compareNodes looks at (count, UL.x); the low 16 bits carry the node
+ORBX_HD uint64_t octp_rec(int cnt, int x0, int pos) {
+  return ((uint64_t)(uint32_t)cnt << 32) | ((uint64_t)(uint16_t)x0 << 16) | (uint32_t)pos;
+}
+
+// Children of processed node P with quadrant counts c[0..3] (n1..n4).  They take next[blk, blk+K)
+// front to back as n4,n3,n2,n1; those with more than one key are appended to vec2 from index cnd
+// in n1..n4 order; c[] is overwritten with each child's position (-1 if empty) for relabelling.
+ORBX_HD void octp_emit(const OctPNode& P, int* c, int blk, int cnd, OctPNode* next, uint64_t* vec2) {
+  const int hx = (P.x1 - P.x0 + 1) >> 1, hy = (P.y1 - P.y0 + 1) >> 1;
+  int pos = blk + (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0);
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    const int cnt = c[q];
+    if (cnt > 0) {
+      pos--;
+      OctPNode k;
+      k.x0 = (int16_t)((q & 1) ? P.x0 + hx : P.x0);
+      k.x1 = (int16_t)((q & 1) ? P.x1 : P.x0 + hx);
+      k.y0 = (int16_t)((q & 2) ? P.y0 + hy : P.y0);
+      k.y1 = (int16_t)((q & 2) ? P.y1 : P.y0 + hy);
+      k.cnt = cnt;
+      next[pos] = k;
+      if (cnt > 1) vec2[cnd++] = octp_rec(cnt, k.x0, pos);
+      c[q] = pos;
+    } else {
+      c[q] = -1;
+    }
+  }
+}
+
+// Root rectangle i of nIni (:564-583)
+ORBX_HD OctPNode octp_root(int i, float hX, int height, int cnt) {
+  OctPNode n;
+  n.x0 = (int16_t)(int)f_mul(hX, (float)i);
+  n.x1 = (int16_t)(int)f_mul(hX, (float)(i + 1));
+  n.y0 = 0;
+  n.y1 = (int16_t)height;
+  n.cnt = cnt;
+  return n;
+}

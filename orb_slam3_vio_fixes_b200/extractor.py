@@ -220,6 +220,15 @@ class ORBextractor:
         _lib.check(_lib.lib().orbx_stage_times(self._h, ms.ctypes.data), "orbx_stage_times")
         return dict(zip(_lib.STAGES, ms.tolist()))
 
+    def debug_octree(self, level, xys):
+        """DistributeOctTree of `level` on explicit keys [n,3] int32 (x, y relative to the border, response)."""
+        xys = np.ascontiguousarray(xys, np.int32).reshape(-1, 3)
+        out = np.zeros((len(xys) + 64, 3), np.int32)
+        n = C.c_int(0)
+        _lib.check(_lib.lib().orbx_debug_octree(self._h, level, xys.ctypes.data, len(xys), out.ctypes.data, len(out),
+                                                C.byref(n)), "orbx_debug_octree")
+        return out[:n.value].copy()
+
     def debug_level_keypoints(self, level, stage, frame=0):
         cap = 1 << 16
         while True:

@@ -55,6 +55,88 @@ int h_distribute(const int* xys, int n, int width, int height, int N, int* out) 
   return k;
 }
 
+// The array ("scan") form of DistributeOctTree that the CUDA kernel runs (octree_core.h, second
+// half), with the block scans written as plain loops.
+int h_distribute_scan(const int* xys, int n, int width, int height, int N, int* out) {
+  const int nIni = (int)roundf((float)width / (float)height);
+  const float hX = (float)width / (float)nIni;
+  const int cap = (N + 3 > 4 * nIni ? N + 3 : 4 * nIni) + 4;
+  std::vector<OctPNode> bufA(cap), bufB(cap);
+  OctPNode *cur = bufA.data(), *next = bufB.data();
+  std::vector<uint64_t> v1(cap), v2(cap);
+  uint64_t *vec = v1.data(), *vec2 = v2.data();
+  std::vector<int> qc(4 * cap), newpos(cap), label(n), rootc(nIni, 0), rootpos(nIni, -1);
+  std::vector<uint8_t> proc(cap);
+  for (int i = 0; i < n; i++) { label[i] = (int)f_div((float)xys[3 * i], hX); rootc[label[i]]++; }
+  int S = 0;
+  for (int i = 0; i < nIni; i++)
+    if (rootc[i] > 0) { rootpos[i] = S; cur[S++] = octp_root(i, hX, height, rootc[i]); }
+  for (int i = 0; i < n; i++) label[i] = rootpos[label[i]];
+  int nvec = 0, careful = 0, rounds = 0;
+  bool finished = n == 0;
+  while (!finished) {
+    if (++rounds > 100000) return -1;
+    const int prevS = S;
+    for (int p = 0; p < S; p++) { proc[p] = 0; qc[4 * p] = qc[4 * p + 1] = qc[4 * p + 2] = qc[4 * p + 3] = 0; }
+    for (int i = 0; i < n; i++) {
+      const OctPNode& nd = cur[label[i]];
+      if (nd.cnt > 1) qc[4 * label[i] + octp_quadrant(nd, xys[3 * i], xys[3 * i + 1])]++;
+    }
+    auto K = [&](int p) { return (qc[4 * p] > 0) + (qc[4 * p + 1] > 0) + (qc[4 * p + 2] > 0) + (qc[4 * p + 3] > 0); };
+    auto E = [&](int p) { return (qc[4 * p] > 1) + (qc[4 * p + 1] > 1) + (qc[4 * p + 2] > 1) + (qc[4 * p + 3] > 1); };
+    int totK = 0, totE = 0, m = 0;
+    if (!careful) {
+      for (int p = 0; p < S; p++) if (cur[p].cnt > 1) totK += K(p);
+      int preK = 0;
+      for (int p = 0; p < S; p++) {
+        if (cur[p].cnt <= 1) continue;
+        const int k = K(p), e = E(p);
+        proc[p] = 1; m++;
+        octp_emit(cur[p], &qc[4 * p], totK - preK - k, totE, next, vec2);
+        preK += k; totE += e;
+      }
+    } else {
+      oct_std_sort(vec, nvec);
+      int size = S;
+      for (int s = 0; s < nvec; s++) {  // which candidates are processed
+        const int p = (int)(vec[nvec - 1 - s] & 0xffff);
+        totK += K(p); size += K(p) - 1; m = s + 1;
+        if (size >= N) break;
+      }
+      int preK = 0;
+      for (int s = 0; s < m; s++) {
+        const int p = (int)(vec[nvec - 1 - s] & 0xffff);
+        const int k = K(p), e = E(p);
+        proc[p] = 1;
+        octp_emit(cur[p], &qc[4 * p], totK - preK - k, totE, next, vec2);
+        preK += k; totE += e;
+      }
+    }
+    int stay = 0;
+    for (int p = 0; p < S; p++)
+      if (!proc[p]) { newpos[p] = totK + stay; next[totK + stay] = cur[p]; stay++; }
+    for (int i = 0; i < n; i++) {
+      const int p = label[i];
+      label[i] = proc[p] ? qc[4 * p + octp_quadrant(cur[p], xys[3 * i], xys[3 * i + 1])] : newpos[p];
+    }
+    S = totK + stay;
+    if (S > cap) return -2;
+    std::swap(cur, next); std::swap(vec, vec2); nvec = totE;
+    if (S >= N || S == prevS) finished = true;
+    else if (!careful && S + 3 * totE > N) careful = 1;
+  }
+  std::vector<uint32_t> best(cap, 0);
+  for (int i = 0; i < n; i++) {
+    uint32_t key = ((uint32_t)xys[3 * i + 2] << 24) | (0xFFFFFFu - (uint32_t)i);
+    if (key > best[label[i]]) best[label[i]] = key;
+  }
+  for (int r = 0; r < S; r++) {
+    int i = (int)(0xFFFFFFu - (best[r] & 0xFFFFFFu));
+    out[3 * r] = xys[3 * i]; out[3 * r + 1] = xys[3 * i + 1]; out[3 * r + 2] = xys[3 * i + 2];
+  }
+  return S;
+}
+
 // counts float bit patterns in [lo,hi] where orbx_sincosf differs from libm sincosf
 long h_sincos_mismatches(uint32_t lo, uint32_t hi, uint32_t stride) {
   long bad = 0;

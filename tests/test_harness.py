@@ -92,6 +92,10 @@ def test_plan_rejects_unsupported(harness):
 def _distribute_both(harness, oracle_mod, xys, width, height, N):
     out = np.zeros((len(xys) + 64, 3), np.int32)
     k = harness.h_distribute(_p(xys), len(xys), width, height, N, _p(out))
+    # the array ("scan") form the CUDA kernel runs must give the same list
+    out2 = np.zeros((len(xys) + 64, 3), np.int32)
+    k2 = harness.h_distribute_scan(_p(xys), len(xys), width, height, N, _p(out2))
+    assert k2 == k and np.array_equal(out2[:max(k2, 0)], out[:max(k, 0)]), ("scan form differs", N, k, k2)
     ref = oracle_mod.distribute(xys.astype(np.float32), 16, 16 + width, 16, 16 + height, N).astype(np.int32)
     return out[:max(k, 0)], ref, k
 
