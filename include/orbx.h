@@ -42,6 +42,9 @@ extern "C" {
 
 #define ORBX_FLAG_STAGE_TIMING 2u /* record CUDA events between the stages of every call so that
                                    orbx_stage_times() can report per-kernel device time        */
+#define ORBX_FLAG_FUSED_BLUR 4u   /* descriptor stage: blur each keypoint's neighbourhood in shared memory
+                                   * (no blurred level is written); default is chosen per plan */
+#define ORBX_FLAG_LEVEL_BLUR 8u   /* descriptor stage: blur whole levels once, then sample them */
 #define ORBX_NUM_STAGES 5       /* pyramid, fast, octree, order, describe                     */
 
 /* cv::KeyPoint memory layout, 28 bytes (what std::vector<cv::KeyPoint> holds). */

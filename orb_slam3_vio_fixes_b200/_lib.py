@@ -16,6 +16,8 @@ ERRORS = {-1: "ORBX_E_INVALID", -2: "ORBX_E_CUDA", -3: "ORBX_E_CAPACITY", -4: "O
           -5: "ORBX_E_EMPTY", -6: "ORBX_E_NODEVICE"}
 FLAG_STRICT_FP = 1
 FLAG_STAGE_TIMING = 2
+FLAG_FUSED_BLUR = 4
+FLAG_LEVEL_BLUR = 8
 STAGES = ("pyramid", "fast", "octree", "order", "describe")
 TIE_FIRST_MIN, TIE_LAST_MIN = 0, 1
 MAX_LEVELS = 12

@@ -47,6 +47,8 @@ struct orbx_extractor_s {
   int32_t *o_n = nullptr, *o_mono = nullptr;
   uint8_t* border_tmp = nullptr;
   uint8_t* stage = nullptr;  // tightly packed level-0 frames of the host batch API (lazy)
+  uint8_t* blur = nullptr;   // blurred levels (arena layout) in level-blur mode
+  bool level_blur = false;
   // octree launch geometry
   size_t oct_smem;
   int oct_smem_keys, oct_node_cap, oct_max_cells;
@@ -64,7 +66,7 @@ struct orbx_extractor_s {
 static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
   memset(D, 0, sizeof(*D));
   D->nlevels = P.nlevels; D->total_cells = P.total_cells; D->kp_total_cap = P.kp_total_cap;
-  D->ini_th = P.ini_th; D->min_th = P.min_th; D->cand_total = P.cand_total; D->arena_bytes = P.arena_bytes;
+  D->ini_th = P.ini_th; D->min_th = P.min_th; D->total_btiles = P.total_btiles; D->cand_total = P.cand_total; D->arena_bytes = P.arena_bytes;
   for (int i = 0; i < 16; i++) D->umax[i] = P.umax[i];
   for (int l = 0; l < P.nlevels; l++) {
     const OrbxLevel& s = P.lv[l];
@@ -72,7 +74,7 @@ static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
     d.w = s.w; d.h = s.h; d.pitch = s.pitch; d.nCols = s.nCols; d.nRows = s.nRows; d.wCell = s.wCell;
     d.hCell = s.hCell; d.cell_base = s.cell_base; d.cell_cap = s.cell_cap; d.nfeat = s.nfeat;
     d.kp_base = s.kp_base; d.kp_cap = s.kp_cap; d.kp_max = s.kp_max; d.nIni = s.nIni; d.hX = s.hX;
-    d.scale = s.scale; d.patch_size = s.patch_size; d.xtab = s.xtab; d.ytab = s.ytab; d.fast_resize = s.fast_resize; d.tile_resize = s.tile_resize; d.offset = s.offset;
+    d.scale = s.scale; d.patch_size = s.patch_size; d.xtab = s.xtab; d.ytab = s.ytab; d.fast_resize = s.fast_resize; d.tile_resize = s.tile_resize; d.btile_base = s.btile_base; d.btiles_x = s.btiles_x; d.offset = s.offset;
     d.cand_base = s.cand_base;
   }
 }
@@ -88,7 +90,7 @@ void orbx_destroy(orbx_handle h) {
   cudaFree(h->arena); cudaFree(h->xtaps); cudaFree(h->ytaps); cudaFree(h->cell_cnt); cudaFree(h->cand);
   cudaFree(h->gkeys); cudaFree(h->glabels); cudaFree(h->sel); cudaFree(h->sel_cnt); cudaFree(h->dst);
   cudaFree(h->status); cudaFree(h->o_kps); cudaFree(h->o_desc); cudaFree(h->o_n); cudaFree(h->o_mono);
-  cudaFree(h->border_tmp); cudaFree(h->stage);
+  cudaFree(h->border_tmp); cudaFree(h->stage); cudaFree(h->blur);
   for (int i = 0; i <= ORBX_NUM_STAGES; i++)
     if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
@@ -174,6 +176,19 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   ALLOC(h->o_desc, B * P.max_keypoints * 32);
   ALLOC(h->o_n, B * sizeof(int32_t));
   ALLOC(h->o_mono, B * sizeof(int32_t));
+  {
+    // Descriptor stage mode.  Measured on B200 (profiles/): blurring whole levels costs ~55 instructions
+    // per level pixel plus a per-keypoint sampler that is L1-bound on its scattered byte reads; blurring
+    // each keypoint's own 45x45 neighbourhood in shared memory costs ~2100 warp instructions per keypoint
+    // and nothing per pixel (and writes no blurred level).  The level mode only pays off when keypoints
+    // are dense (< ~600 level pixels per keypoint); EuRoC-shaped frames at 1000 kp are not.
+    long long px = 0;
+    for (int l = 0; l < P.nlevels; l++) px += (long long)P.lv[l].w * P.lv[l].h;
+    h->level_blur = px < 600LL * P.max_keypoints;
+    if (cfg->flags & ORBX_FLAG_LEVEL_BLUR) h->level_blur = true;
+    if (cfg->flags & ORBX_FLAG_FUSED_BLUR) h->level_blur = false;
+    if (h->level_blur) ALLOC(h->blur, B * P.arena_bytes + 512);
+  }
   ALLOC(h->border_tmp, (size_t)(P.lv[0].w + 2 * ORBX_EDGE) * (P.lv[0].h + 2 * ORBX_EDGE));
 #undef ALLOC
   if (!xt.empty()) {
@@ -183,6 +198,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   CU(cudaMemset(h->status, 0, sizeof(int32_t)));
   CU(cudaMemset(h->arena, 0, B * P.arena_bytes + 512));
   CU(orbx_octree_set_smem(h->oct_smem));
+  CU(orbx_describe_init_tables(P.umax));
   if (cfg->flags & ORBX_FLAG_STAGE_TIMING)
     for (int i = 0; i <= ORBX_NUM_STAGES; i++) CU(cudaEventCreate(&h->ev[i]));
   h->last_l0.base = h->arena; h->last_l0.frame_stride = P.arena_bytes; h->last_l0.pitch = P.lv[0].pitch;
@@ -219,8 +235,15 @@ static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1,
   STAGE_MARK(3);
   CU(orbx_launch_order(D, sel, sel_cnt, lap0, lap1, dst, d_n, d_mono, batch, st));
   STAGE_MARK(4);
-  CU(orbx_launch_describe(D, l0, arena, sel, sel_cnt, dst, d_kps, d_desc, capacity,
-                          (h->cfg.flags & ORBX_FLAG_STRICT_FP) ? 1 : 0, batch, st));
+  if (h->level_blur) {
+    uint8_t* blur = h->blur + (long long)f0 * D.arena_bytes;
+    CU(orbx_launch_blur(D, l0, arena, blur, batch, st));
+    CU(orbx_launch_describe_lite(D, l0, arena, blur, sel, sel_cnt, dst, d_kps, d_desc, capacity,
+                                 (h->cfg.flags & ORBX_FLAG_STRICT_FP) ? 1 : 0, batch, st));
+  } else {
+    CU(orbx_launch_describe(D, l0, arena, sel, sel_cnt, dst, d_kps, d_desc, capacity,
+                            (h->cfg.flags & ORBX_FLAG_STRICT_FP) ? 1 : 0, batch, st));
+  }
   STAGE_MARK(5);
 #undef STAGE_MARK
   if (allow_timing) h->timed = tm;

@@ -219,6 +219,155 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// "Level blur" mode: the levels were blurred once by k_blur_levels (blur.cu), so a keypoint only
+// needs its orientation (moments straight from the level image: lane = patch row, 9 aligned words
+// per row, two dp4a per word against constant column weights) and 512 samples from the blurred level.
+// No shared memory.
+// ------------------------------------------------------------------------------------------------
+// c_mom_mask[|v|][j]: bytes of word j (patch columns u = 4j-15 .. 4j-12) with |u| <= umax[|v|]
+__device__ uint32_t c_mom_mask[16 * 8];
+
+__device__ __forceinline__ int dp4a_us(uint32_t a_u8x4, uint32_t b_s8x4, int c) {
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_u8x4), "r"(b_s8x4), "r"(c));
+  return d;
+}
+
+template <bool STRICT_FP>
+__global__ void __launch_bounds__(DESC_WARPS * 32)
+k_describe_lite(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
+                const uint8_t* __restrict__ blur, const uint32_t* __restrict__ sel,
+                const int32_t* __restrict__ sel_cnt, const int32_t* __restrict__ dst,
+                OrbxKeyPointDev* __restrict__ kps, uint8_t* __restrict__ desc, int capacity) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int frame = blockIdx.y;
+  const int slot = blockIdx.x * DESC_WARPS + warp;
+  if (slot >= P.kp_total_cap) return;
+  int level = 0;
+#pragma unroll 1
+  for (int l = 1; l < P.nlevels; l++)
+    if (slot >= P.lv[l].kp_base) level = l;
+  const DevLevel& L = P.lv[level];
+  const int idx = slot - L.kp_base;
+  if (idx >= sel_cnt[frame * P.nlevels + level]) return;
+  const uint32_t key = sel[(long long)frame * P.kp_total_cap + slot];
+  const int kx = ORBX_KEY_X(key), ky = ORBX_KEY_Y(key);
+  int pitch;
+  const uint8_t* img;
+  if (level == 0) { pitch = l0.pitch; img = l0.base + (long long)frame * l0.frame_stride; }
+  else { pitch = L.pitch; img = arena + (long long)frame * P.arena_bytes + L.offset; }
+
+  // ---- IC_Angle: integer moments over the circular patch of radius 15 (rows v = lane - 15)
+  int m01 = 0, m10 = 0;
+  if (lane < 31) {
+    const int v = lane - ORBX_HALF_PATCH, av = v < 0 ? -v : v;
+    const uint8_t* rowp = img + (long long)(ky + v) * pitch + (kx - ORBX_HALF_PATCH);  // u = -15
+    int s = 0, su = 0;
+    if ((pitch & 3) == 0 && ((uintptr_t)img & 3) == 0 && kx + ORBX_HALF_PATCH + 8 < L.w) {
+      const int sh = 8 * (int)((uintptr_t)rowp & 3);
+      const uint32_t* wp = reinterpret_cast<const uint32_t*>(rowp - ((uintptr_t)rowp & 3));
+      uint32_t w[9];
+#pragma unroll
+      for (int j = 0; j < 9; j++) w[j] = __ldg(wp + j);
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        const uint32_t px = __funnelshift_r(w[j], w[j + 1], sh) & c_mom_mask[av * 8 + j];  // u = 4j-15 .. 4j-12
+        const int u0 = 4 * j - 15;
+        const uint32_t wt = (uint32_t)(u0 & 0xff) | ((uint32_t)((u0 + 1) & 0xff) << 8) |
+                            ((uint32_t)((u0 + 2) & 0xff) << 16) | ((uint32_t)((u0 + 3) & 0xff) << 24);
+        s = dp4a_us(px, 0x01010101u, s);
+        su = dp4a_us(px, wt, su);
+      }
+    } else {
+      const int d = P.umax[av];
+      for (int u = -d; u <= d; u++) {
+        const int val = rowp[ORBX_HALF_PATCH + u];
+        s += val;
+        su += u * val;
+      }
+    }
+    m10 = su;
+    m01 = v * s;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+  }
+  const float angle = orbx_fast_atan2((float)m01, (float)m10);
+
+  // ---- rotated BRIEF on the blurred level: test t = 32*j + lane -> bit `lane` of descriptor word j
+  const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
+  float a, b;
+  orbx_sincosf(f_mul(angle, factorPI), &b, &a);
+  const uint8_t* centre = blur + (long long)frame * P.arena_bytes + L.offset + (long long)ky * L.pitch + kx;
+  const float kMagic = 12582912.0f;  // cvRound through the mantissa, see k_describe
+  const int bp = L.pitch;
+  const uint32_t kBias = 0x4B400000u * (uint32_t)(bp + 1);
+  uint32_t word_mine = 0;
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    const float4 pt = __ldg(reinterpret_cast<const float4*>(c_patf) + 32 * j + lane);
+    float fy0, fx0, fy1, fx1;
+    if (STRICT_FP) {
+      fy0 = f_add(f_mul(pt.x, b), f_mul(pt.y, a)); fx0 = f_sub(f_mul(pt.x, a), f_mul(pt.y, b));
+      fy1 = f_add(f_mul(pt.z, b), f_mul(pt.w, a)); fx1 = f_sub(f_mul(pt.z, a), f_mul(pt.w, b));
+    } else {
+      fy0 = f_fma(pt.x, b, f_mul(pt.y, a)); fx0 = f_fma(pt.x, a, -f_mul(pt.y, b));
+      fy1 = f_fma(pt.z, b, f_mul(pt.w, a)); fx1 = f_fma(pt.z, a, -f_mul(pt.w, b));
+    }
+    const uint32_t i0 = __float_as_uint(f_add(fy0, kMagic)) * (uint32_t)bp + __float_as_uint(f_add(fx0, kMagic)) - kBias;
+    const uint32_t i1 = __float_as_uint(f_add(fy1, kMagic)) * (uint32_t)bp + __float_as_uint(f_add(fx1, kMagic)) - kBias;
+    const int v0 = __ldg(centre + (int)i0), v1 = __ldg(centre + (int)i1);
+    const uint32_t wd = __ballot_sync(0xffffffffu, v0 < v1);
+    if (lane == j) word_mine = wd;
+  }
+
+  // ---- emit
+  const int d = dst[(long long)frame * P.kp_total_cap + slot];
+  if (d < 0 || d >= capacity) return;
+  const long long o = (long long)frame * capacity + d;
+  if (lane < 8) reinterpret_cast<uint32_t*>(desc + o * 32)[lane] = word_mine;
+  if (lane == 8) {
+    OrbxKeyPointDev kp;
+    kp.x = (float)kx; kp.y = (float)ky;
+    if (level != 0) { kp.x = f_mul(kp.x, L.scale); kp.y = f_mul(kp.y, L.scale); }
+    kp.size = L.patch_size;
+    kp.angle = angle;
+    kp.response = (float)ORBX_KEY_S(key);
+    kp.octave = level;
+    kp.class_id = -1;
+    kps[o] = kp;
+  }
+}
+
+// Fills c_mom_mask from the plan's umax table (once per process; the table is a constant of the
+// algorithm, ORBextractor.cc:453-468).
+cudaError_t orbx_describe_init_tables(const int* umax) {
+  uint32_t m[16 * 8];
+  for (int av = 0; av < 16; av++)
+    for (int j = 0; j < 8; j++) {
+      uint32_t w = 0;
+      for (int k = 0; k < 4; k++) {
+        const int u = 4 * j - 15 + k;
+        if ((u < 0 ? -u : u) <= umax[av]) w |= 0xffu << (8 * k);
+      }
+      m[av * 8 + j] = w;
+    }
+  return cudaMemcpyToSymbol(c_mom_mask, m, sizeof(m));
+}
+
+cudaError_t orbx_launch_describe_lite(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint8_t* blur,
+                                      const uint32_t* sel, const int32_t* sel_cnt, const int32_t* dst,
+                                      OrbxKeyPointDev* kps, uint8_t* desc, int capacity, int strict_fp, int batch,
+                                      cudaStream_t st) {
+  dim3 grd((P.kp_total_cap + DESC_WARPS - 1) / DESC_WARPS, batch);
+  if (strict_fp) k_describe_lite<true><<<grd, DESC_WARPS * 32, 0, st>>>(P, l0, arena, blur, sel, sel_cnt, dst, kps, desc, capacity);
+  else k_describe_lite<false><<<grd, DESC_WARPS * 32, 0, st>>>(P, l0, arena, blur, sel, sel_cnt, dst, kps, desc, capacity);
+  return cudaGetLastError();
+}
+
 cudaError_t orbx_launch_describe(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* sel,
                                  const int32_t* sel_cnt, const int32_t* dst, OrbxKeyPointDev* kps,
                                  uint8_t* desc, int capacity, int strict_fp, int batch, cudaStream_t st) {

@@ -15,13 +15,14 @@ struct DevLevel {
   int nIni;
   float hX, scale, patch_size;
   int xtab, ytab, fast_resize, tile_resize;
+  int btile_base, btiles_x;
   long long offset;     // bytes, inside a frame's pyramid arena
   long long cand_base;  // uint32 units, inside a frame's candidate arena
 };
 
 struct DevPlan {
   DevLevel lv[ORBX_PLAN_MAX_LEVELS];
-  int nlevels, total_cells, kp_total_cap, ini_th, min_th;
+  int nlevels, total_cells, kp_total_cap, ini_th, min_th, total_btiles;
   long long cand_total;   // uint32 per frame
   long long arena_bytes;  // per frame
   int umax[16];
@@ -63,6 +64,13 @@ cudaError_t orbx_launch_order(const DevPlan& P, const uint32_t* sel, const int32
 cudaError_t orbx_launch_describe(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* sel,
                                  const int32_t* sel_cnt, const int32_t* dst, OrbxKeyPointDev* kps,
                                  uint8_t* desc, int capacity, int strict_fp, int batch, cudaStream_t st);
+cudaError_t orbx_launch_blur(const DevPlan& P, Level0 l0, const uint8_t* arena, uint8_t* blur, int batch,
+                             cudaStream_t st);
+cudaError_t orbx_launch_describe_lite(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint8_t* blur,
+                                      const uint32_t* sel, const int32_t* sel_cnt, const int32_t* dst,
+                                      OrbxKeyPointDev* kps, uint8_t* desc, int capacity, int strict_fp, int batch,
+                                      cudaStream_t st);
+cudaError_t orbx_describe_init_tables(const int* umax);
 cudaError_t orbx_launch_border(const uint8_t* src, int pitch, int w, int h, uint8_t* dst, int dst_pitch,
                                cudaStream_t st);
 size_t orbx_octree_smem_bytes(int smem_keys, int node_cap, int max_cells);

@@ -33,6 +33,7 @@ struct OrbxLevel {
   int xtab, ytab;  // offsets into the resize tables (entries), level>=1
   int fast_resize;  // the 4-column tap windows of k_resize_walk hold for every column group
   int tile_resize;  // every 128x64 output tile fits k_resize_tile's shared-memory source window
+  int btile_base, btiles_x;  // 128x32 tiles of k_blur_levels: first tile of this level, tiles per row
 };
 
 struct OrbxPlan {
@@ -42,6 +43,7 @@ struct OrbxPlan {
   long long cand_total;      // uint32 per frame
   long long arena_bytes;     // pyramid bytes per frame (all levels)
   int kp_total_cap;          // Σ kp_cap
+  int total_btiles;          // Σ blur tiles per frame
   int max_keypoints;         // Σ kp_max (what one frame can return; nfeatures+3*nlevels normally)
   float scale[ORBX_PLAN_MAX_LEVELS], inv_scale[ORBX_PLAN_MAX_LEVELS];
   float sigma2[ORBX_PLAN_MAX_LEVELS], inv_sigma2[ORBX_PLAN_MAX_LEVELS];
@@ -103,7 +105,7 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
     }
   }
   long long offset = 0, cand = 0;
-  int cells = 0, kpb = 0, maxk = 0;
+  int cells = 0, kpb = 0, maxk = 0, btiles = 0;
   xtaps->clear(); ytaps->clear();
   for (int l = 0; l < nlevels; l++) {
     OrbxLevel& L = P->lv[l];
@@ -112,6 +114,9 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
     L.pitch = (L.w + 127) & ~127;
     L.offset = offset;
     offset += (long long)L.pitch * L.h;
+    L.btile_base = btiles;
+    L.btiles_x = (L.w + 127) / 128;
+    btiles += L.btiles_x * ((L.h + 31) / 32);
     L.scale = P->scale[l];
     L.patch_size = (float)(int)(31 * P->scale[l]);
     L.nfeat = nfeat[l];
@@ -196,6 +201,7 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
   P->cand_total = cand;
   P->arena_bytes = (offset + 255) & ~255LL;
   P->kp_total_cap = kpb;
+  P->total_btiles = btiles;
   P->max_keypoints = maxk;
   return 0;
 }

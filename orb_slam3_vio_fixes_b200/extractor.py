@@ -34,11 +34,15 @@ class ORBextractor:
     HARRIS_SCORE, FAST_SCORE = 0, 1
 
     def __init__(self, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, *, max_batch=1, device=0,
-                 strict_fp=False, stage_timing=False):
+                 strict_fp=False, stage_timing=False, blur_mode=None):
         self.nfeatures, self.scaleFactor, self.nlevels = int(nfeatures), float(scaleFactor), int(nlevels)
         self.iniThFAST, self.minThFAST = int(iniThFAST), int(minThFAST)
         self.max_batch, self.device = int(max_batch), int(device)
-        self.flags = (_lib.FLAG_STRICT_FP if strict_fp else 0) | (_lib.FLAG_STAGE_TIMING if stage_timing else 0)
+        # blur_mode: None = chosen per plan, "fused" = per-keypoint blur in shared memory,
+        # "level" = whole levels blurred once (ORBX_FLAG_FUSED_BLUR / ORBX_FLAG_LEVEL_BLUR)
+        assert blur_mode in (None, "fused", "level")
+        self.flags = (_lib.FLAG_STRICT_FP if strict_fp else 0) | (_lib.FLAG_STAGE_TIMING if stage_timing else 0) | \
+            {None: 0, "fused": _lib.FLAG_FUSED_BLUR, "level": _lib.FLAG_LEVEL_BLUR}[blur_mode]
         self._h = None
         self._size = None
 

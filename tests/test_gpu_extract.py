@@ -133,3 +133,42 @@ def test_batch_device_unaligned_pitch(oracle_mod):
     for f in range(len(frames)):
         ok, od, om = orc.extract(frames[f], (0, 0))
         assert n[f] == len(ok) and np.array_equal(kps[f, :n[f]], ok) and np.array_equal(desc[f, :n[f]], od)
+
+
+@pytest.mark.parametrize("mode", ["fused", "level"])
+@pytest.mark.parametrize("cfg,size", [("C1", None), ("C3", None), ("C4", None), ("C1", (501, 317))])
+def test_descriptor_modes_match_oracle(oracle_mod, mode, cfg, size):
+    """Both descriptor-stage modes (per-keypoint blur in shared memory / whole-level blur) give the
+    oracle's keypoints, angles and descriptors, including tiles and patches at the level edges."""
+    w, h, nf, seed, _ = S.CONFIGS[cfg]
+    if size:
+        w, h = size
+    frames = S.make_frames(cfg, 2, width=w, height=h)
+    ex = ORBextractor(nf, blur_mode=mode, **ORB)
+    orc = oracle_mod.Extractor(nf, 1.2, 8, 20, 7)
+    for img in frames:
+        mono, kps, desc = ex(img, None, (0, 0))
+        okps, odesc, omono = orc.extract(img, (0, 0))
+        assert mono == omono and np.array_equal(kps, okps)
+        assert np.array_equal(desc, odesc)
+    for strict in (True,):
+        ex2 = ORBextractor(nf, blur_mode=mode, strict_fp=strict, **ORB)
+        orc2 = oracle_mod.Extractor(nf, 1.2, 8, 20, 7, flags=1)  # ORACLE_STRICT_FP
+        mono, kps, desc = ex2(frames[0], None, (0, 0))
+        okps, odesc, omono = orc2.extract(frames[0], (0, 0))
+        assert np.array_equal(kps, okps) and np.array_equal(desc, odesc)
+
+
+def test_batch_device_unaligned_pitch_level_blur(oracle_mod):
+    import torch
+    frames = S.make_frames("C3", 2, width=501, height=317)
+    ex = ORBextractor(600, max_batch=2, blur_mode="level", **ORB).plan(501, 317)
+    orc = oracle_mod.Extractor(600, 1.2, 8, 20, 7)
+    out = ex.extract_batch_device(torch.from_numpy(frames).cuda(), (0, 0))
+    torch.cuda.synchronize()
+    n = out["n"].cpu().numpy()
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    for f in range(len(frames)):
+        ok, od, om = orc.extract(frames[f], (0, 0))
+        assert n[f] == len(ok) and np.array_equal(kps[f, :n[f]], ok) and np.array_equal(desc[f, :n[f]], od)
