@@ -323,6 +323,17 @@ def main():
                    "alg_bytes_per_frame": int(match_bytes),
                    "achieved_gbs": round(match_bytes * B / (match_ms * 1e-3) / 1e9, 1) if match_ms > 0 else 0.0})
     top = max(stages[:5], key=lambda s: s["ms"])
+    # DRAM bytes of that kernel per launch from the committed `ncu --set full` capture (same command,
+    # same batch), or null when no capture matches this batch size
+    traffic = None
+    try:
+        caps = sorted((ROOT / "profiles").glob("*traffic_batch%d.json" % B))
+        if caps:
+            kern = json.loads(caps[-1].read_text())["kernels"].get("k_" + top["kernel"])
+            if kern:
+                traffic = int(kern[0]["dram_read_bytes"] + kern[0]["dram_write_bytes"])
+    except Exception:
+        traffic = None
     total_bytes = sum(ext_bytes.values()) + match_bytes
     fps = world * B * args.steps / (ms * 1e-3)
     line = {
@@ -337,7 +348,8 @@ def main():
                 "d2h_bytes_per_step": d2h},
         "gpu_launches": launches_per_step * args.steps,
         "roofline": {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved_gbs"], "peak": peak,
-                     "unit": "GB/s", "frac": top["frac"], "traffic": None, "peak_source": peak_src},
+                     "unit": "GB/s", "frac": top["frac"], "traffic": traffic, "peak_source": peak_src,
+                     "alg_bytes_per_launch": int(top["alg_bytes_per_frame"] * B)},
         "roofline_pipeline": {"alg_bytes_per_frame": int(total_bytes), "achieved_gbs": round(total_bytes * fps / world / 1e9, 1),
                               "frac": round(total_bytes * fps / world / 1e9 / peak, 4)},
         "stages": stages, "clocks": clocks,
