@@ -34,6 +34,7 @@ struct orbx_extractor_s {
   uint8_t* arena = nullptr;
   OrbxTap *xtaps = nullptr, *ytaps = nullptr;
   int32_t* cell_cnt = nullptr;
+  uint32_t* cell_tab = nullptr;  // per cell: level << 24 | row << 12 | column
   uint32_t* cand = nullptr;
   uint32_t* gkeys = nullptr;
   int16_t* glabels = nullptr;
@@ -87,7 +88,7 @@ const char* orbx_last_error(void) { return g_err; }
 void orbx_destroy(orbx_handle h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->arena); cudaFree(h->xtaps); cudaFree(h->ytaps); cudaFree(h->cell_cnt); cudaFree(h->cand);
+  cudaFree(h->arena); cudaFree(h->xtaps); cudaFree(h->ytaps); cudaFree(h->cell_cnt); cudaFree(h->cell_tab); cudaFree(h->cand);
   cudaFree(h->gkeys); cudaFree(h->glabels); cudaFree(h->sel); cudaFree(h->sel_cnt); cudaFree(h->dst);
   cudaFree(h->status); cudaFree(h->o_kps); cudaFree(h->o_desc); cudaFree(h->o_n); cudaFree(h->o_mono);
   cudaFree(h->border_tmp); cudaFree(h->stage); cudaFree(h->blur);
@@ -165,6 +166,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   ALLOC(h->xtaps, (xt.size() + 1) * sizeof(OrbxTap));
   ALLOC(h->ytaps, (yt.size() + 1) * sizeof(OrbxTap));
   ALLOC(h->cell_cnt, B * P.total_cells * sizeof(int32_t));
+  ALLOC(h->cell_tab, (size_t)P.total_cells * sizeof(uint32_t));
   ALLOC(h->cand, B * P.cand_total * sizeof(uint32_t));
   ALLOC(h->gkeys, B * P.cand_total * sizeof(uint32_t));
   ALLOC(h->glabels, B * P.cand_total * sizeof(int16_t));
@@ -194,6 +196,13 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   if (!xt.empty()) {
     CU(cudaMemcpy(h->xtaps, xt.data(), xt.size() * sizeof(OrbxTap), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(h->ytaps, yt.data(), yt.size() * sizeof(OrbxTap), cudaMemcpyHostToDevice));
+  }
+  {
+    std::vector<uint32_t> tab(P.total_cells);
+    for (int l = 0; l < P.nlevels; l++)
+      for (int c = 0; c < P.lv[l].nCols * P.lv[l].nRows; c++)
+        tab[P.lv[l].cell_base + c] = ((uint32_t)l << 24) | ((uint32_t)(c / P.lv[l].nCols) << 12) | (uint32_t)(c % P.lv[l].nCols);
+    CU(cudaMemcpy(h->cell_tab, tab.data(), tab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
   }
   CU(cudaMemset(h->status, 0, sizeof(int32_t)));
   CU(cudaMemset(h->arena, 0, B * P.arena_bytes + 512));
@@ -228,7 +237,7 @@ static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1,
   STAGE_MARK(0);
   CU(orbx_launch_pyramid(D, l0, arena, h->xtaps, h->ytaps, batch, st));
   STAGE_MARK(1);
-  CU(orbx_launch_fast(D, l0, arena, cell_cnt, cand, batch, st));
+  CU(orbx_launch_fast(D, l0, arena, h->cell_tab, cell_cnt, cand, batch, st));
   STAGE_MARK(2);
   CU(orbx_launch_octree(D, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, h->status, batch,
                         h->oct_smem, h->oct_smem_keys, h->oct_node_cap, h->oct_max_cells, st));

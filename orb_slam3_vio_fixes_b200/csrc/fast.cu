@@ -26,7 +26,7 @@
 
 #define FAST_WARPS 4
 #define FAST_THREADS (FAST_WARPS * 32)
-#define FAST_LIST_CAP 256  // pair tasks scored per band of rows (a cell is one band unless it is corner-dense)
+#define FAST_LIST_CAP 512  // pair tasks scored per band of rows (a cell is one band unless it is corner-dense)
 
 // 16-bit lanes {w[A], w[A+1]} out of the 12-byte window w0|w1|w2 (A compile-time, 1..9)
 template <int A>
@@ -211,22 +211,25 @@ __device__ __forceinline__ int fast_nms_emit(const FastCell& c, int nlist, int t
   return total;
 }
 
-// Walks the quick-test byte map in row-major order, 128 quads (one word of qm per lane) at a time,
+// Walks the quick-test byte map in row-major order, 256 quads (two words of qm per lane) at a time,
 // compacting the pixel pairs that passed into the task list.  The list is handed to the scoring
-// stage (MODE 0) or to NMS + emission (MODE 1) whenever the next 128 quads might not fit, and at the
+// stage (MODE 0) or to NMS + emission (MODE 1) whenever the next 256 quads might not fit, and at the
 // end; *bands counts the hand-overs.  Returns the running emission total (MODE 1).
 template <int MODE>
 __device__ __forceinline__ int fast_sweep(const FastCell& c, int nquads, int th, int lane, int* nlist_out,
                                           int* bands, int total, uint32_t* out, int kx0, int ky0) {
   int nlist = 0, nb = 0;
-  for (int base = 0; base < nquads; base += 128) {
-    const int i4 = (base >> 2) + lane;
+  for (int base = 0; base < nquads; base += 256) {
+    const int i4 = (base >> 2) + 2 * lane;  // this lane's two words of qm = 8 quads
     uint32_t bits = 0;
     if (4 * i4 < nquads) {
-      const uint32_t m = reinterpret_cast<const uint32_t*>(c.qm)[i4];
-      uint32_t x = (m | (m >> 1)) & 0x05050505u;  // per quad: bit0 = left pair, bit2 = right pair
-      x = (x | (x >> 1)) & 0x03030303u;           // -> bits 0,1
+      const uint2 mm = *reinterpret_cast<const uint2*>(c.qm + 4 * i4);
+      uint32_t x = (mm.x | (mm.x >> 1)) & 0x05050505u;  // per quad: bit0 = left pair, bit2 = right pair
+      uint32_t y = (mm.y | (mm.y >> 1)) & 0x05050505u;
+      x = (x | (x >> 1)) & 0x03030303u;                 // -> bits 0,1
+      y = (y | (y >> 1)) & 0x03030303u;
       bits = (x | (x >> 6) | (x >> 12) | (x >> 18)) & 0xffu;
+      if (4 * i4 + 4 < nquads) bits |= ((y | (y >> 6) | (y >> 12) | (y >> 18)) & 0xffu) << 8;
     }
     const int cnt = __popc(bits);
     int inc = cnt;
@@ -248,7 +251,7 @@ __device__ __forceinline__ int fast_sweep(const FastCell& c, int nquads, int th,
     while (bits) {
       const int b = __ffs(bits) - 1;
       bits &= bits - 1;
-      c.list[pos++] = (uint16_t)(8 * i4 + b);  // (4*i4 + b/2)*2 + (b&1)
+      c.list[pos++] = (uint16_t)(8 * i4 + b);  // (4*i4 + b/2)*2 + (b&1), b < 16 spans both words
     }
     nlist += chunk;
   }
@@ -262,7 +265,8 @@ __device__ __forceinline__ int fast_sweep(const FastCell& c, int nquads, int th,
 
 __global__ void __launch_bounds__(FAST_THREADS, 8)
 k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
-       int32_t* __restrict__ cell_cnt, uint32_t* __restrict__ cand, int pw, int rows_max, int qcap) {
+       const uint32_t* __restrict__ cell_tab, int32_t* __restrict__ cell_cnt, uint32_t* __restrict__ cand,
+       int pw, int rows_max, int qcap) {
   extern __shared__ uint32_t fast_smem[];
   const int frame = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -276,13 +280,11 @@ k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__
   c.qm = reinterpret_cast<uint8_t*>(c.hm + pw * rows_max + FAST_LIST_CAP / 2);
   c.pw = pw;
 
-  int level = 0;
-#pragma unroll 1
-  for (int l = 1; l < P.nlevels; l++)
-    if (cell >= P.lv[l].cell_base) level = l;
+  // cell_tab: level << 24 | cell row << 12 | cell column (built with the plan)
+  const uint32_t ct = __ldg(cell_tab + cell);
+  const int level = (int)(ct >> 24), ci = (int)((ct >> 12) & 0xfff), cj = (int)(ct & 0xfff);
   const DevLevel& L = P.lv[level];
   cell -= L.cell_base;
-  const int ci = cell / L.nCols, cj = cell - ci * L.nCols;
   // tested zone of this cell, level coordinates
   const int zx0 = ORBX_EDGE + cj * L.wCell, zy0 = ORBX_EDGE + ci * L.hCell;
   const int zx1 = min(zx0 + L.wCell, L.w - ORBX_EDGE), zy1 = min(zy0 + L.hCell, L.h - ORBX_EDGE);
@@ -306,15 +308,30 @@ k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__
     const int nw = (sh + zw + 6 + 3) >> 2;  // data words per row
     const uint32_t* a0 = reinterpret_cast<const uint32_t*>(tile0 - sh);
     const int wpitch = pitch >> 2;
-    const uint32_t rcw = ((1u << 20) + nw - 1) / nw;
-    const int nwords = nw * (zh + 6);
+    if (nw <= 16) {
+      // half a warp per row: lane = (row parity, word)
+      const int col = lane & 15;
+      if (col < nw) {
+        const uint32_t* g = a0 + (lane >> 4) * wpitch + col;
+        int o = (lane >> 4) * pw + 1 + col;
 #pragma unroll 4
-    for (int i = lane; i < nwords; i += 32) {
-      const int r = (int)(((uint32_t)i * rcw) >> 20), col = i - r * nw;
-      const uint32_t v = __ldg(a0 + r * wpitch + col);
-      const int o = r * pw + 1 + col;
-      c.px[o] = v;
-      c.hm[o] = (v >> 1) & 0x7f7f7f7fu;
+        for (int r = lane >> 4; r < zh + 6; r += 2, g += 2 * wpitch, o += 2 * pw) {
+          const uint32_t v = __ldg(g);
+          c.px[o] = v;
+          c.hm[o] = (v >> 1) & 0x7f7f7f7fu;
+        }
+      }
+    } else {
+      const uint32_t rcw = ((1u << 20) + nw - 1) / nw;
+      const int nwords = nw * (zh + 6);
+#pragma unroll 4
+      for (int i = lane; i < nwords; i += 32) {
+        const int r = (int)(((uint32_t)i * rcw) >> 20), col = i - r * nw;
+        const uint32_t v = __ldg(a0 + r * wpitch + col);
+        const int o = r * pw + 1 + col;
+        c.px[o] = v;
+        c.hm[o] = (v >> 1) & 0x7f7f7f7fu;
+      }
     }
   } else {
     sh = 0;
@@ -405,8 +422,8 @@ k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__
 
 static int g_fast_smem_set = 0;
 
-cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, int32_t* cell_cnt,
-                             uint32_t* cand, int batch, cudaStream_t st) {
+cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* cell_tab,
+                             int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st) {
   // shared-memory geometry from the largest cell of the plan
   int pw = 0, rows = 0, cap = 0;
   for (int l = 0; l < P.nlevels; l++) {
@@ -415,7 +432,7 @@ cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, 
     rows = max(rows, P.lv[l].hCell + 6);
     cap = max(cap, ((P.lv[l].wCell + 3 + 3) / 4 + 2) * P.lv[l].hCell);
   }
-  cap = (cap + 15) & ~15;  // quads per cell (bytes of qm), rounded so the regions stay word aligned
+  cap = (cap + 8 + 15) & ~15;  // quads per cell (bytes of qm) + one spare uint2, regions stay 8-byte aligned
   const size_t smem = (size_t)FAST_WARPS * (2 * pw * rows + FAST_LIST_CAP / 2 + (cap >> 2)) * sizeof(uint32_t);
   if ((int)smem > g_fast_smem_set) {
     cudaError_t e = cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -423,6 +440,6 @@ cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, 
     g_fast_smem_set = (int)smem;
   }
   dim3 grd((P.total_cells + FAST_WARPS - 1) / FAST_WARPS, batch);
-  k_fast<<<grd, FAST_THREADS, smem, st>>>(P, l0, arena, cell_cnt, cand, pw, rows, cap);
+  k_fast<<<grd, FAST_THREADS, smem, st>>>(P, l0, arena, cell_tab, cell_cnt, cand, pw, rows, cap);
   return cudaGetLastError();
 }

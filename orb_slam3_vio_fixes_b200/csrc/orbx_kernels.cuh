@@ -52,8 +52,8 @@ struct OrbxKeyPointDev {  // = orbx_keypoint = cv::KeyPoint
 // --- launches (each returns cudaGetLastError()) -------------------------------------------------
 cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, const OrbxTap* xtaps,
                                 const OrbxTap* ytaps, int batch, cudaStream_t st);
-cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, int32_t* cell_cnt,
-                             uint32_t* cand, int batch, cudaStream_t st);
+cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* cell_tab,
+                             int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st);
 cudaError_t orbx_launch_octree(const DevPlan& P, const int32_t* cell_cnt, const uint32_t* cand,
                                uint32_t* gkeys, int16_t* glabels, uint32_t* sel, int32_t* sel_cnt,
                                int32_t* status, int batch, size_t smem_bytes, int smem_keys, int node_cap,
