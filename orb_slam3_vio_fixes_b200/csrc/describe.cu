@@ -8,6 +8,10 @@
 // window + 3-px blur halo, BORDER_REFLECT_101 at the level edge), runs the separable Q8 filter
 // on it in shared memory — identical integer arithmetic, out = (sum + 32768) >> 16 — and samples
 // from that.  No blurred level is ever written to HBM.
+#include <math.h>
+
+#include <vector>
+
 #include "orbx_kernels.cuh"
 
 #define DESC_WARPS 4
@@ -32,6 +36,13 @@ struct __align__(16) DescWarpSmem {
   uint32_t patch[PATCH * PW + 3];
   uint2 t[BL * PW];
 };
+
+// Row-pass tasks (row << 4 | word) that cover the blurred pixels BRIEF can sample: the pattern points lie
+// within radius R = max |p| (18.4) of the keypoint, so after rotation and cvRound only pixels whose
+// unit square meets that disc are read — 74 % of the 39x39 window.  One list per alignment offset.
+#define ROW_TASKS_MAX 448
+__device__ uint16_t c_row_tasks[4 * ROW_TASKS_MAX];
+__device__ int c_row_ntasks[4];
 
 // One output byte of the row pass: taps 18,34,48,56,48,34,18 over seven 16-bit sums, rounded
 // like cv::GaussianBlur's fixed-point path: (acc + 2^15) >> 16.
@@ -160,8 +171,11 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
   // now (orientation and column pass are done), so the blurred window overwrites it.
   {
     uint32_t* bw = sm.patch;
-    for (int q = lane; q < BL * BW; q += 32) {
-      const int r = (q * 5958) >> 16, w = q - r * BW;  // q / 11 for q < 429
+    const int ntask = c_row_ntasks[off];
+    const uint16_t* tasks = c_row_tasks + off * ROW_TASKS_MAX;
+    for (int i = lane; i < ntask; i += 32) {
+      const int tk = tasks[i];
+      const int r = tk >> 4, w = tk & 15, q = r * BW + w;
       const uint2* tp = sm.t + r * PW + w;
       const uint2 a = tp[0], b = tp[1], c = tp[2];
       const uint32_t t0 = a.x & 0xffffu, t1 = a.y & 0xffffu, t2 = a.x >> 16, t3 = a.y >> 16;
@@ -344,7 +358,35 @@ k_describe_lite(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __r
 
 // Fills c_mom_mask from the plan's umax table (once per process; the table is a constant of the
 // algorithm, ORBextractor.cc:453-468).
+static const float h_patf[1024] = {
+#include "orb_pattern.inc"
+};
+
 cudaError_t orbx_describe_init_tables(const int* umax) {
+  {
+    // blurred pixels (dx, dy) whose unit square meets the disc of radius max|p| (+ margin for fp32)
+    double R = 0;
+    for (int i = 0; i < 512; i++) R = fmax(R, hypot((double)h_patf[2 * i], (double)h_patf[2 * i + 1]));
+    R += 0.05;
+    std::vector<uint16_t> tab(4 * ROW_TASKS_MAX, 0);
+    int cnt[4];
+    for (int off = 0; off < 4; off++) {
+      int n = 0;
+      for (int r = 0; r < BL; r++) {
+        const double ay = fmax(fabs((double)(r - 19)) - 0.5, 0.0);
+        int m = -1;
+        for (int dx = 0; dx <= 19; dx++)
+          if (hypot(fmax(dx - 0.5, 0.0), ay) <= R) m = dx;
+        if (m < 0) continue;
+        for (int w = (19 - m + off) >> 2; w <= (19 + m + off) >> 2; w++) tab[off * ROW_TASKS_MAX + n++] = (uint16_t)(r << 4 | w);
+      }
+      cnt[off] = n;
+    }
+    cudaError_t e = cudaMemcpyToSymbol(c_row_tasks, tab.data(), tab.size() * sizeof(uint16_t));
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpyToSymbol(c_row_ntasks, cnt, sizeof(cnt));
+    if (e != cudaSuccess) return e;
+  }
   uint32_t m[16 * 8];
   for (int av = 0; av < 16; av++)
     for (int j = 0; j < 8; j++) {
