@@ -172,3 +172,16 @@ def test_batch_device_unaligned_pitch_level_blur(oracle_mod):
     for f in range(len(frames)):
         ok, od, om = orc.extract(frames[f], (0, 0))
         assert n[f] == len(ok) and np.array_equal(kps[f, :n[f]], ok) and np.array_equal(desc[f, :n[f]], od)
+
+
+@pytest.mark.parametrize("cfg,lap,nframes", [("C2", (0, 0), 2), ("C5", (0, 1000), 1)])
+def test_full_size_configs(oracle_mod, cfg, lap, nframes):
+    """BASELINE configs not covered above at their full sizes: C2 (K=1200/eye, both eyes) and the
+    4K stress shape C5 (3840x2160, K=5000: 19.7 k FAST cells, ~1 k keypoints per octree level)."""
+    w, h, nf, seed, stereo = S.CONFIGS[cfg]
+    ex = ORBextractor(nf, **ORB)
+    orc = oracle_mod.Extractor(nf, 1.2, 8, 20, 7)
+    eyes = (False, True) if stereo else (False,)
+    for right in eyes:
+        for img in S.make_frames(cfg, nframes, right=right):
+            _compare_frame(oracle_mod, ex, orc, img, lap)
