@@ -212,6 +212,27 @@ int orbm_stereo_rowband(const orbx_keypoint* d_kps_l, const uint8_t* d_desc_l,
                         const float* scale_factors_host, int nlevels, float max_d,
                         int32_t* d_best_idx_r, int32_t* d_best_dist, void* stream);
 
+/* Sub-pixel stage and median cut of Frame::ComputeStereoMatches (Frame.cc:896-981), after
+ * orbm_stereo_rowband: for every left keypoint whose best Hamming distance is < (TH_HIGH+TH_LOW)/2
+ * the 11x11 L1-SAD slide over +-5 px on its pyramid level, the parabola fit, the disparity gate
+ * 0 <= d < max_d (= mbf/mb) and depth = mbf/d; then matches whose SAD >= 1.5f*1.4f*median are
+ * erased.  The pyramids are read on the device from the two extractor handles (frame f of the last
+ * orbx_extract_batch_device call of each).  d_u_right / d_depth = mvuRight / mvDepth (-1 = none),
+ * d_sad = best SAD per kept-or-cut match (-1 where no match was formed), d_kept[f] = matches left. */
+int orbm_stereo_refine(orbx_handle left, orbx_handle right, const orbx_keypoint* d_kps_l,
+                       const int32_t* d_n_l, const orbx_keypoint* d_kps_r, int kp_stride, int batch,
+                       const int32_t* d_best_idx_r, const int32_t* d_best_dist, float mbf,
+                       float max_d, float* d_u_right, float* d_depth, int32_t* d_sad,
+                       int32_t* d_kept, void* stream);
+
+/* Frame::ComputeStereoFromRGBD (Frame.cc:984-1005): d = imDepth.at<float>(v,u) at the (truncated)
+ * keypoint position; d > 0 -> mvDepth = d, mvuRight = kpUn.x - mbf/d, else -1.  d_kps_un = the
+ * undistorted keypoints (NULL = same as d_kps).  The depth image is float32, pitched. */
+int orbm_rgbd_depth(const orbx_keypoint* d_kps, const orbx_keypoint* d_kps_un, const int32_t* d_n,
+                    int kp_stride, int batch, const float* d_depth_img, size_t pitch_bytes,
+                    size_t frame_stride_bytes, int width, int height, float mbf, float* d_u_right,
+                    float* d_depth, void* stream);
+
 /* cv::BFMatcher(NORM_HAMMING).knnMatch(k=2) (Frame.cc:1144): all pairs, two best per query,
  * ties to the lower reference index.  d_idx2/d_dist2 are [nq][2]. */
 int orbm_knn2_dense(const uint8_t* d_q, int nq, const uint8_t* d_r, int nr, int32_t* d_idx2,

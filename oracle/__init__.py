@@ -261,6 +261,21 @@ def stereo_matches(kps_l, desc_l, kps_r, desc_r, scale_factors, inv_scale_factor
     return bi, bd, ur, dp, kept
 
 
+def rgbd_depth(kps, kps_un, depth_img, mbf):
+    """Frame::ComputeStereoFromRGBD.  Returns (uRight, depth)."""
+    kps = np.ascontiguousarray(kps)
+    kps_un = np.ascontiguousarray(kps_un)
+    d = np.ascontiguousarray(depth_img, np.float32)
+    ur = np.zeros(kps.size, np.float32)
+    dp = np.zeros(kps.size, np.float32)
+    L = lib()
+    L.oracle_rgbd_depth.restype = None
+    L.oracle_rgbd_depth.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float,
+                                    C.c_void_p, C.c_void_p]
+    L.oracle_rgbd_depth(_p(kps), _p(kps_un), kps.size, _p(d), d.shape[1], d.shape[0], mbf, _p(ur), _p(dp))
+    return ur, dp
+
+
 def knn2_dense(q, r):
     q = np.ascontiguousarray(q, np.uint8)
     r = np.ascontiguousarray(r, np.uint8)

@@ -910,7 +910,7 @@ int oracle_stereo_matches(const void* kpsL_v, const uint8_t* descL, int nL, cons
       float bestuR = scaleFactors[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
       float disparity = (uL - bestuR);
       if (disparity >= minD && disparity < maxD) {
-        if (disparity <= 0) { disparity = 0.01f; bestuR = uL - 0.01f; }
+        if (disparity <= 0) { disparity = 0.01; bestuR = uL - 0.01; }  // double literals, as Frame.cc:956-957
         depth[iL] = mbf / disparity;
         uRight[iL] = bestuR;
         vDistIdx.push_back(std::pair<int, int>(bestSad, iL));
@@ -927,6 +927,22 @@ int oracle_stereo_matches(const void* kpsL_v, const uint8_t* descL, int nL, cons
     uRight[vDistIdx[i].second] = -1; depth[vDistIdx[i].second] = -1; kept--;
   }
   return kept;
+}
+
+// Frame::ComputeStereoFromRGBD (Frame.cc:984-1005).  depth_img is float32 [h][w]; kps_un are the
+// undistorted keypoints (mvKeysUn).
+void oracle_rgbd_depth(const void* kps_v, const void* kps_un_v, int n, const float* depth_img, int w, int h,
+                       float mbf, float* uRight, float* depth) {
+  const KeyPoint* k = (const KeyPoint*)kps_v;
+  const KeyPoint* ku = (const KeyPoint*)kps_un_v;
+  for (int i = 0; i < n; i++) {
+    uRight[i] = -1; depth[i] = -1;
+    const float v = k[i].y, u = k[i].x;
+    const int vi = (int)v, ui = (int)u;  // Mat::at<float>(int,int) takes the truncated floats
+    if (vi < 0 || vi >= h || ui < 0 || ui >= w) continue;  // reference indexes unchecked
+    const float d = depth_img[(size_t)vi * w + ui];
+    if (d > 0) { depth[i] = d; uRight[i] = ku[i].x - mbf / d; }
+  }
 }
 
 // cv::BFMatcher(NORM_HAMMING).knnMatch(q, r, k=2) (Frame.cc:1144): per query the two smallest

@@ -438,6 +438,56 @@ int orbx_get_scale_tables(orbx_handle h, float* scale, float* inv_scale, float* 
   return ORBX_OK;
 }
 
+// Sub-pixel stage + median cut of Frame::ComputeStereoMatches (Frame.cc:896-981), reading both eyes'
+// pyramids where the two extractors left them (frame f of each handle's last batch).
+int orbm_stereo_refine(orbx_handle hl, orbx_handle hr, const orbx_keypoint* d_kps_l, const int32_t* d_n_l,
+                       const orbx_keypoint* d_kps_r, int kp_stride, int batch, const int32_t* d_best_idx_r,
+                       const int32_t* d_best_dist, float mbf, float max_d, float* d_u_right, float* d_depth,
+                       int32_t* d_sad, int32_t* d_kept, void* stream) {
+  if (!hl || !hr || !d_kps_l || !d_n_l || !d_kps_r || !d_best_idx_r || !d_best_dist || !d_u_right || !d_depth ||
+      !d_sad || !d_kept || batch < 1 || kp_stride < 1)
+    return ORBX_E_INVALID;
+  if (hl->device != hr->device || hl->plan.nlevels != hr->plan.nlevels || batch > hl->last_batch ||
+      batch > hr->last_batch) {
+    set_err("orbm_stereo_refine: handles disagree or no extraction of this batch yet", cudaSuccess);
+    return ORBX_E_INVALID;
+  }
+  OrbxStereoPyr pyr;
+  memset(&pyr, 0, sizeof(pyr));
+  for (int l = 0; l < hl->plan.nlevels; l++) {
+    const OrbxLevel &A = hl->plan.lv[l], &B = hr->plan.lv[l];
+    if (A.w != B.w || A.h != B.h) { set_err("orbm_stereo_refine: level sizes differ", cudaSuccess); return ORBX_E_INVALID; }
+    if (l == 0) {
+      pyr.base_l[0] = hl->last_l0.base; pyr.stride_l[0] = hl->last_l0.frame_stride; pyr.pitch_l[0] = hl->last_l0.pitch;
+      pyr.base_r[0] = hr->last_l0.base; pyr.stride_r[0] = hr->last_l0.frame_stride; pyr.pitch_r[0] = hr->last_l0.pitch;
+    } else {
+      pyr.base_l[l] = hl->arena + A.offset; pyr.stride_l[l] = hl->plan.arena_bytes; pyr.pitch_l[l] = A.pitch;
+      pyr.base_r[l] = hr->arena + B.offset; pyr.stride_r[l] = hr->plan.arena_bytes; pyr.pitch_r[l] = B.pitch;
+    }
+    pyr.w[l] = A.w; pyr.h[l] = A.h;
+    pyr.scale[l] = hl->plan.scale[l]; pyr.inv_scale[l] = hl->plan.inv_scale[l];  // Frame copies the left extractor's tables (Frame.cc:110-116)
+  }
+  CU(cudaSetDevice(hl->device));
+  CU(orbx_launch_stereo_refine((const OrbxKeyPointDev*)d_kps_l, d_n_l, (const OrbxKeyPointDev*)d_kps_r, kp_stride,
+                               batch, d_best_idx_r, d_best_dist, pyr, mbf, max_d, d_u_right, d_depth, d_sad, d_kept,
+                               (cudaStream_t)stream));
+  return ORBX_OK;
+}
+
+// Frame::ComputeStereoFromRGBD (Frame.cc:984-1005)
+int orbm_rgbd_depth(const orbx_keypoint* d_kps, const orbx_keypoint* d_kps_un, const int32_t* d_n, int kp_stride,
+                    int batch, const float* d_depth_img, size_t pitch_bytes, size_t frame_stride_bytes, int width,
+                    int height, float mbf, float* d_u_right, float* d_depth, void* stream) {
+  if (!d_kps || !d_n || !d_depth_img || !d_u_right || !d_depth || batch < 1 || kp_stride < 1 || width < 1 ||
+      height < 1 || (pitch_bytes & 3) || (frame_stride_bytes & 3) || pitch_bytes < (size_t)width * 4)
+    return ORBX_E_INVALID;
+  if (!d_kps_un) d_kps_un = d_kps;  // no distortion: mvKeysUn = mvKeys (Frame.cc:747-752)
+  CU(orbx_launch_rgbd_depth((const OrbxKeyPointDev*)d_kps, (const OrbxKeyPointDev*)d_kps_un, d_n, kp_stride, batch,
+                            d_depth_img, (long long)(pitch_bytes / 4), (long long)(frame_stride_bytes / 4), width,
+                            height, mbf, d_u_right, d_depth, (cudaStream_t)stream));
+  return ORBX_OK;
+}
+
 int orbx_stage_times(orbx_handle h, float* ms) {
   if (!h || !ms || !h->timed) return ORBX_E_INVALID;
   CU(cudaSetDevice(h->device));

@@ -49,6 +49,16 @@ struct OrbxKeyPointDev {  // = orbx_keypoint = cv::KeyPoint
   int32_t octave, class_id;
 };
 
+// Both eyes' pyramids as the stereo refinement reads them (levels of frame f of each handle's last batch).
+struct OrbxStereoPyr {
+  const uint8_t* base_l[ORBX_PLAN_MAX_LEVELS];
+  const uint8_t* base_r[ORBX_PLAN_MAX_LEVELS];
+  long long stride_l[ORBX_PLAN_MAX_LEVELS], stride_r[ORBX_PLAN_MAX_LEVELS];  // bytes between frames
+  int pitch_l[ORBX_PLAN_MAX_LEVELS], pitch_r[ORBX_PLAN_MAX_LEVELS];
+  int w[ORBX_PLAN_MAX_LEVELS], h[ORBX_PLAN_MAX_LEVELS];
+  float scale[ORBX_PLAN_MAX_LEVELS], inv_scale[ORBX_PLAN_MAX_LEVELS];
+};
+
 // --- launches (each returns cudaGetLastError()) -------------------------------------------------
 cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, const OrbxTap* xtaps,
                                 const OrbxTap* ytaps, int batch, cudaStream_t st);
@@ -70,6 +80,14 @@ cudaError_t orbx_launch_describe_lite(const DevPlan& P, Level0 l0, const uint8_t
                                       const uint32_t* sel, const int32_t* sel_cnt, const int32_t* dst,
                                       OrbxKeyPointDev* kps, uint8_t* desc, int capacity, int strict_fp, int batch,
                                       cudaStream_t st);
+cudaError_t orbx_launch_stereo_refine(const OrbxKeyPointDev* kl, const int32_t* nl, const OrbxKeyPointDev* kr,
+                                      int kp_stride, int batch, const int32_t* best_idx, const int32_t* best_dist,
+                                      const OrbxStereoPyr& pyr, float mbf, float max_d, float* u_right, float* depth,
+                                      int32_t* sad, int32_t* kept, cudaStream_t st);
+cudaError_t orbx_launch_rgbd_depth(const OrbxKeyPointDev* kps, const OrbxKeyPointDev* kps_un, const int32_t* n,
+                                   int kp_stride, int batch, const float* depth_img, long long pitch_f,
+                                   long long frame_stride_f, int w, int h, float mbf, float* u_right, float* depth,
+                                   cudaStream_t st);
 cudaError_t orbx_describe_init_tables(const int* umax);
 cudaError_t orbx_launch_border(const uint8_t* src, int pitch, int w, int h, uint8_t* dst, int dst_pitch,
                                cudaStream_t st);

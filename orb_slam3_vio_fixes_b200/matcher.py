@@ -123,6 +123,42 @@ class ORBmatcher:
         return bi, bd
 
     @staticmethod
+    def stereo_refine(ex_l, ex_r, kps_l, n_l, kps_r, best_idx, best_dist, mbf, max_d):
+        """Sub-pixel stage + median cut of Frame::ComputeStereoMatches (Frame.cc:896-981) on the pyramids the
+        two extractors (ORBextractor objects) hold on the device.  Returns dict(u_right, depth [B,cap] f32,
+        sad [B,cap] i32, kept [B] i32)."""
+        import torch
+        b, cap = kps_l.shape[0], kps_l.shape[1]
+        dev = kps_l.device
+        out = {"u_right": torch.empty((b, cap), dtype=torch.float32, device=dev),
+               "depth": torch.empty((b, cap), dtype=torch.float32, device=dev),
+               "sad": torch.empty((b, cap), dtype=torch.int32, device=dev),
+               "kept": torch.empty((b,), dtype=torch.int32, device=dev)}
+        rc = _lib.lib().orbm_stereo_refine(ex_l._h, ex_r._h, kps_l.data_ptr(), n_l.data_ptr(),
+                                           kps_r.data_ptr(), cap, b, best_idx.data_ptr(), best_dist.data_ptr(),
+                                           float(mbf), float(max_d), out["u_right"].data_ptr(),
+                                           out["depth"].data_ptr(), out["sad"].data_ptr(), out["kept"].data_ptr(),
+                                           _stream(dev))
+        _lib.check(rc, "orbm_stereo_refine")
+        return out
+
+    @staticmethod
+    def rgbd_depth(kps, n, depth_img, mbf, kps_un=None):
+        """Frame::ComputeStereoFromRGBD (Frame.cc:984-1005).  depth_img: float32 CUDA tensor [B,h,w].
+        Returns (u_right, depth) [B,cap] f32."""
+        import torch
+        b, cap = kps.shape[0], kps.shape[1]
+        assert depth_img.dtype == torch.float32 and depth_img.dim() == 3 and depth_img.stride(2) == 1
+        ur = torch.empty((b, cap), dtype=torch.float32, device=kps.device)
+        dp = torch.empty((b, cap), dtype=torch.float32, device=kps.device)
+        rc = _lib.lib().orbm_rgbd_depth(kps.data_ptr(), kps_un.data_ptr() if kps_un is not None else None,
+                                        n.data_ptr(), cap, b, depth_img.data_ptr(), depth_img.stride(1) * 4,
+                                        depth_img.stride(0) * 4, depth_img.shape[2], depth_img.shape[1], float(mbf),
+                                        ur.data_ptr(), dp.data_ptr(), _stream(kps.device))
+        _lib.check(rc, "orbm_rgbd_depth")
+        return ur, dp
+
+    @staticmethod
     def knn2_dense(q, r):
         """cv::BFMatcher(NORM_HAMMING).knnMatch(k=2).  Returns (idx [nq,2] i32, dist [nq,2] i32)."""
         import torch

@@ -66,3 +66,9 @@ def test_match_and_stereo_match_golden():
     n = int(ol["n"][0])
     assert n == len(s["kps_l"])
     assert np.array_equal(bi[0, :n].cpu().numpy(), s["best_idx_r"]) and np.array_equal(bd[0, :n].cpu().numpy(), s["best_dist"])
+    # sub-pixel stage + median cut (Frame.cc:896-981) on the device-resident pyramids
+    res = ORBmatcher.stereo_refine(exl, exr, ol["kps"], ol["n"], orr["kps"], bi, bd, np.float32(s["bf"]),
+                                   np.float32(s["bf"]) / np.float32(s["mb"]))
+    assert np.array_equal(res["u_right"][0, :n].cpu().numpy().view(np.uint32), s["u_right"].view(np.uint32))
+    assert np.array_equal(res["depth"][0, :n].cpu().numpy().view(np.uint32), s["depth"].view(np.uint32))
+    assert int(res["kept"][0]) == int(s["kept"])

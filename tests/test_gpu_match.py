@@ -167,3 +167,94 @@ def test_stereo_rowband(oracle_mod):
         # constant 24 px disparity in the synthetic pair
         ok = ur > 0
         assert np.median(kl[f, :nl[f]]["x"][ok] - ur[ok]) == pytest.approx(24.0, abs=0.5)
+
+
+def _stereo_case(oracle_mod, left, right, nfeat=1200):
+    """Full ComputeStereoMatches on the device (rowband -> refine -> median cut) vs the oracle, bit for bit."""
+    B = left.shape[0]
+    exl = ORBextractor(nfeat, max_batch=B, **ORB)
+    exr = ORBextractor(nfeat, max_batch=B, **ORB)
+    ol = _extract_batch(exl, left, (0, 0))
+    orr = _extract_batch(exr, right, (0, 0))
+    sf, isf = exl.GetScaleFactors(), exl.GetInverseScaleFactors()
+    fx, bf = 458.654, 47.90639384423901
+    mb = np.float32(bf / fx)
+    mbf = np.float32(bf)
+    max_d = mbf / mb
+    bi, bd = ORBmatcher.stereo_rowband(ol["kps"], ol["desc"], ol["n"], orr["kps"], orr["desc"], orr["n"], sf, max_d)
+    res = ORBmatcher.stereo_refine(exl, exr, ol["kps"], ol["n"], orr["kps"], bi, bd, mbf, max_d)
+    kl, kr = ORBextractor.kps_from_tensor(ol["kps"]), ORBextractor.kps_from_tensor(orr["kps"])
+    dl, dr = ol["desc"].cpu().numpy(), orr["desc"].cpu().numpy()
+    nl, nr = ol["n"].cpu().numpy(), orr["n"].cpu().numpy()
+    ur_g, dp_g, kept_g = res["u_right"].cpu().numpy(), res["depth"].cpu().numpy(), res["kept"].cpu().numpy()
+    out = []
+    for f in range(B):
+        pl = [exl.GetPyramid(l, frame=f) for l in range(8)]
+        pr = [exr.GetPyramid(l, frame=f) for l in range(8)]
+        rbi, rbd, ur, dp, kept = oracle_mod.stereo_matches(kl[f, :nl[f]], dl[f, :nl[f]], kr[f, :nr[f]], dr[f, :nr[f]],
+                                                           sf, isf, pl, pr, mb, mbf)
+        assert np.array_equal(ur_g[f, :nl[f]].view(np.uint32), ur.view(np.uint32))
+        assert np.array_equal(dp_g[f, :nl[f]].view(np.uint32), dp.view(np.uint32))
+        assert kept_g[f] == kept == int((ur > 0).sum())
+        out.append((kl[f, :nl[f]], ur, dp, kept))
+    return out
+
+
+def test_stereo_refine_constant_disparity(oracle_mod):
+    left = S.make_frames("C2", 3)
+    right = S.make_frames("C2", 3, right=True)
+    for kl, ur, dp, kept in _stereo_case(oracle_mod, left, right):
+        ok = ur > 0
+        assert kept > 100
+        d = kl["x"][ok] - ur[ok]
+        assert np.median(d) == pytest.approx(24.0, abs=0.5)
+        assert len(np.unique(ur[ok] - np.floor(ur[ok]))) > 20  # the parabola really moves things off the grid
+
+
+def test_stereo_refine_zero_and_mixed_disparity(oracle_mod):
+    """Edge cases of Frame.cc:951-980: identical eyes (median SAD 0 -> every match is cut), the same view with
+    independent noise (disparity ~0: negative ones rejected, exact 0 clamped to 0.01 with uL-0.01 in double),
+    and a (2,1) px offset pair."""
+    left = np.stack([S.make_frames("C2", 1, t0=0)[0], S.make_frames("C2", 1, t0=2)[0],
+                     S.make_frames("C2", 1, t0=100)[0]])
+    right = np.stack([left[0], S.make_frames("C2", 1, t0=34)[0],   # t and t+32 share the crop, not the noise
+                      S.make_frames("C2", 1, t0=101)[0]])
+    res = _stereo_case(oracle_mod, left, right)
+    assert res[0][3] == 0
+    kl, ur, dp, kept = res[1]
+    assert kept > 200
+    clamped = ur == (kl["x"].astype(np.float64) - 0.01).astype(np.float32)
+    assert (clamped & (dp == np.float32(47.90639384423901) / np.float32(0.01))).sum() >= 3
+    assert res[2][3] > 500
+
+
+def test_rgbd_depth(oracle_mod):
+    import torch
+    B = 2
+    frames = S.make_frames("C3", B)
+    ex = ORBextractor(1000, max_batch=B, **ORB)
+    o = _extract_batch(ex, frames, (0, 0))
+    rng = np.random.default_rng(5)
+    depth = rng.uniform(-0.5, 6.0, (B, 480, 640)).astype(np.float32)
+    depth[rng.random(depth.shape) < 0.2] = 0.0
+    mbf = np.float32(40.0)
+    d_t = torch.from_numpy(depth).cuda()
+    ur, dp = ORBmatcher.rgbd_depth(o["kps"], o["n"], d_t, mbf)
+    k = ORBextractor.kps_from_tensor(o["kps"])
+    n = o["n"].cpu().numpy()
+    for f in range(B):
+        rur, rdp = oracle_mod.rgbd_depth(k[f, :n[f]], k[f, :n[f]], depth[f], mbf)
+        assert np.array_equal(ur[f, :n[f]].cpu().numpy().view(np.uint32), rur.view(np.uint32))
+        assert np.array_equal(dp[f, :n[f]].cpu().numpy().view(np.uint32), rdp.view(np.uint32))
+        assert (rdp > 0).sum() > 300 and (rdp < 0).sum() > 50
+    # pitched view + separate undistorted keypoints
+    big = torch.zeros((B, 480, 704), dtype=torch.float32, device="cuda")
+    big[:, :, :640] = d_t
+    kun = o["kps"].clone()
+    kun[:, :, 0] += 0.25
+    kun_np = ORBextractor.kps_from_tensor(kun)
+    ur2, dp2 = ORBmatcher.rgbd_depth(o["kps"], o["n"], big[:, :, :640], mbf, kps_un=kun)
+    for f in range(B):
+        rur, rdp = oracle_mod.rgbd_depth(k[f, :n[f]], kun_np[f, :n[f]], depth[f], mbf)
+        assert np.array_equal(ur2[f, :n[f]].cpu().numpy().view(np.uint32), rur.view(np.uint32))
+        assert np.array_equal(dp2[f, :n[f]].cpu().numpy().view(np.uint32), rdp.view(np.uint32))

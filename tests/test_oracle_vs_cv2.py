@@ -123,3 +123,69 @@ def test_end_to_end_strict_fp_flag(oracle_mod):
     k, d, m = e.extract(img, (0, 0))
     k2, d2, m2 = c.extract(img, (0, 0))
     assert np.array_equal(k, k2) and np.array_equal(d, d2)
+
+
+def test_stereo_subpixel_vs_cv2_norm(oracle_mod):
+    """Frame.cc:896-981 re-expressed with cv2.norm(NORM_L1) on Mat slices and numpy float32 scalars, from the
+    oracle's Hamming-stage result: pins the SAD slide, parabola, clamp and median cut of the C++ oracle."""
+    f32 = np.float32
+    for t0, tr in ((0, None), (2, 34)):
+        left = S.make_frames("C2", 1, t0=t0)[0]
+        right = S.make_frames("C2", 1, t0=t0, right=True)[0] if tr is None else S.make_frames("C2", 1, t0=tr)[0]
+        el, er = oracle_mod.Extractor(1200), oracle_mod.Extractor(1200)
+        kl, dl, _ = el.extract(left, (0, 0))
+        kr, dr, _ = er.extract(right, (0, 0))
+        pl = [np.ascontiguousarray(el.pyramid(l)) for l in range(8)]
+        pr = [np.ascontiguousarray(er.pyramid(l)) for l in range(8)]
+        mbf = f32(47.90639384423901)
+        mb = f32(mbf / f32(458.654))
+        sf, isf = el.scale_factors, el.inv_scale_factors
+        bi, bd, ur, dp, kept = oracle_mod.stereo_matches(kl, dl, kr, dr, sf, isf, pl, pr, mb, mbf)
+        maxD = mbf / mb
+        ur2 = np.full(len(kl), -1, f32)
+        dp2 = np.full(len(kl), -1, f32)
+        vdist = []
+        rnd = lambda v: f32(np.floor(v + f32(0.5)) if v >= 0 else np.ceil(v - f32(0.5)))  # C round(): half away
+        for iL in range(len(kl)):
+            if bd[iL] >= 75 or bi[iL] < 0:
+                continue
+            o = int(kl["octave"][iL])
+            uL = f32(kl["x"][iL])
+            su, sv, sr = rnd(uL * isf[o]), rnd(f32(kl["y"][iL]) * isf[o]), rnd(f32(kr["x"][bi[iL]]) * isf[o])
+            w = L = 5
+            if sr + L - w < 0 or sr + L + w + 1 >= pl[o].shape[1]:
+                continue
+            su, sv, sr = int(su), int(sv), int(sr)
+            IL = pl[o][sv - w:sv + w + 1, su - w:su + w + 1]
+            best, binc, dists = 2 ** 31 - 1, 0, []
+            for inc in range(-L, L + 1):
+                IR = pr[o][sv - w:sv + w + 1, sr + inc - w:sr + inc + w + 1]
+                d = f32(cv2.norm(IL, IR, cv2.NORM_L1))
+                if d < best:
+                    best, binc = int(d), inc
+                dists.append(d)
+            if binc in (-L, L):
+                continue
+            d1, d2, d3 = dists[L + binc - 1], dists[L + binc], dists[L + binc + 1]
+            with np.errstate(all="ignore"):
+                delta = (d1 - d3) / (f32(2.0) * (d1 + d3 - f32(2.0) * d2))
+            if delta < -1 or delta > 1:
+                continue
+            bu = sf[o] * (f32(sr) + f32(binc) + delta)
+            disp = uL - bu
+            if disp >= 0 and disp < maxD:
+                if disp <= 0:
+                    disp = f32(0.01)
+                    bu = f32(np.float64(uL) - 0.01)
+                dp2[iL] = mbf / disp
+                ur2[iL] = bu
+                vdist.append((best, iL))
+        vdist.sort()
+        th = f32(1.5) * f32(1.4) * f32(vdist[len(vdist) // 2][0])
+        for d, i in reversed(vdist):
+            if d < th:
+                break
+            ur2[i] = dp2[i] = -1
+        assert np.array_equal(ur.view(np.uint32), ur2.view(np.uint32))
+        assert np.array_equal(dp.view(np.uint32), dp2.view(np.uint32))
+        assert kept == int((ur2 > 0).sum()) > 100

@@ -10,8 +10,9 @@ from orb_slam3_vio_fixes_b200.matcher import ORBmatcher
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+blur_mode = sys.argv[3] if len(sys.argv) > 3 else None
 frames = torch.from_numpy(S.make_frames("C1", B)).cuda()
-ex = ORBextractor(1000, 1.2, 8, 20, 7, max_batch=B).plan(752, 480)
+ex = ORBextractor(1000, 1.2, 8, 20, 7, max_batch=B, blur_mode=blur_mode).plan(752, 480)
 out = ex.alloc_outputs(B, frames.device)
 sf = ex.GetScaleFactors()
 shift = torch.from_numpy(shifts_for(0, B)).cuda()
