@@ -61,7 +61,9 @@ struct orbx_extractor_s {
   // orbx_extract_batch_host pipeline: copy-in / two compute / copy-out streams, one event pair per chunk
   cudaStream_t s_in = nullptr, s_out = nullptr, s_cmp[2] = {nullptr, nullptr};
   std::vector<cudaEvent_t> ev_in, ev_done;
+  cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
   int host_chunk = 64;
+  int dev_split = 2;  // sub-batches of orbx_extract_batch_device (ORBX_DEVICE_SPLIT)
 };
 
 static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
@@ -96,6 +98,9 @@ void orbx_destroy(orbx_handle h) {
     if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
   for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  for (int i = 0; i < 2; i++)
+    if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]);
   if (h->s_in) cudaStreamDestroy(h->s_in);
   if (h->s_out) cudaStreamDestroy(h->s_out);
   for (int i = 0; i < 2; i++)
@@ -220,6 +225,20 @@ int orbx_max_keypoints(orbx_handle h) { return h ? h->plan.max_keypoints : ORBX_
 // Runs the launch sequence for `batch` frames whose per-frame scratch (pyramid arena, candidate
 // slots, selections) starts at frame slot f0 of the handle; l0 and the outputs point at the first
 // of those frames.
+static int ensure_streams(orbx_handle h) {
+  if (h->s_in) return ORBX_OK;
+  CU(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&h->s_cmp[0], cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&h->s_cmp[1], cudaStreamNonBlocking));
+  CU(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&h->ev_join[0], cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&h->ev_join[1], cudaEventDisableTiming));
+  if (const char* e = getenv("ORBX_HOST_CHUNK")) { const int v = atoi(e); if (v > 0) h->host_chunk = v; }
+  if (const char* e = getenv("ORBX_DEVICE_SPLIT")) { const int v = atoi(e); if (v > 0) h->dev_split = v; }
+  return ORBX_OK;
+}
+
 static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1, OrbxKeyPointDev* d_kps,
                         uint8_t* d_desc, int capacity, int32_t* d_n, int32_t* d_mono, cudaStream_t st,
                         int f0 = 0, bool allow_timing = true) {
@@ -272,8 +291,38 @@ int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch
   CU(cudaSetDevice(h->device));
   Level0 l0;
   l0.base = d_imgs; l0.frame_stride = (long long)frame_stride; l0.pitch = (int)pitch;
-  return run_pipeline(h, l0, batch, lap0, lap1, (OrbxKeyPointDev*)d_kps, d_desc, capacity, d_n_out, d_mono_index,
-                      (cudaStream_t)stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  // Large batches are cut into sub-batches that alternate between two internal streams (forked from and
+  // joined back into the caller's stream): the latency-bound octree of one sub-batch then shares the SMs
+  // with the issue-bound FAST / describe kernels of its neighbour instead of running alone.  Sub-batches
+  // own disjoint frame slots of the scratch buffers.  Off while per-stage events are being recorded.
+  int rc = ensure_streams(h);
+  if (rc) return rc;
+  int nsplit = h->dev_split;
+  if ((h->cfg.flags & ORBX_FLAG_STAGE_TIMING) || batch < 64 * nsplit) nsplit = 1;
+  if (nsplit <= 1)
+    return run_pipeline(h, l0, batch, lap0, lap1, (OrbxKeyPointDev*)d_kps, d_desc, capacity, d_n_out, d_mono_index, st);
+  CU(cudaEventRecord(h->ev_fork, st));
+  CU(cudaStreamWaitEvent(h->s_cmp[0], h->ev_fork, 0));
+  CU(cudaStreamWaitEvent(h->s_cmp[1], h->ev_fork, 0));
+  const int chunk = (batch + nsplit - 1) / nsplit;
+  for (int c = 0, f0 = 0; f0 < batch; c++, f0 += chunk) {
+    const int nb = (batch - f0) < chunk ? (batch - f0) : chunk;
+    Level0 l = l0;
+    l.base = l0.base + (long long)f0 * l0.frame_stride;
+    rc = run_pipeline(h, l, nb, lap0, lap1, (OrbxKeyPointDev*)d_kps + (long long)f0 * capacity,
+                      d_desc + (long long)f0 * capacity * 32, capacity, d_n_out + f0, d_mono_index + f0,
+                      h->s_cmp[c & 1], f0, false);
+    if (rc) return rc;
+  }
+  for (int i = 0; i < 2; i++) {
+    CU(cudaEventRecord(h->ev_join[i], h->s_cmp[i]));
+    CU(cudaStreamWaitEvent(st, h->ev_join[i], 0));
+  }
+  h->last_l0 = l0;
+  h->last_batch = batch;
+  h->timed = false;
+  return ORBX_OK;
 }
 
 int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int lap0, int lap1,
@@ -288,13 +337,7 @@ int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int l
   // Chunked pipeline: while chunk c is being extracted, chunk c+1 is on its way in and chunk c-1 on its
   // way out (PCIe is full duplex).  Chunks own disjoint frame slots of the handle's scratch, so two
   // compute streams may run neighbouring chunks concurrently and fill each other's kernel tails.
-  if (!h->s_in) {
-    CU(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&h->s_cmp[0], cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&h->s_cmp[1], cudaStreamNonBlocking));
-    if (const char* e = getenv("ORBX_HOST_CHUNK")) { const int v = atoi(e); if (v > 0) h->host_chunk = v; }
-  }
+  { int rc_ = ensure_streams(h); if (rc_) return rc_; }
   if (!h->stage) {
     cudaError_t e_ = cudaMalloc((void**)&h->stage, (size_t)h->cfg.max_batch * W * H + 512);
     if (e_ != cudaSuccess) { set_err("cudaMalloc stage", e_); return e_ == cudaErrorMemoryAllocation ? ORBX_E_NOMEM : ORBX_E_CUDA; }
