@@ -239,8 +239,6 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
 // per row, two dp4a per word against constant column weights) and 512 samples from the blurred level.
 // No shared memory.
 // ------------------------------------------------------------------------------------------------
-// c_mom_mask[|v|][j]: bytes of word j (patch columns u = 4j-15 .. 4j-12) with |u| <= umax[|v|]
-__device__ uint32_t c_mom_mask[16 * 8];
 
 __device__ __forceinline__ int dp4a_us(uint32_t a_u8x4, uint32_t b_s8x4, int c) {
   int d;
@@ -248,12 +246,23 @@ __device__ __forceinline__ int dp4a_us(uint32_t a_u8x4, uint32_t b_s8x4, int c) 
   return d;
 }
 
+// Moment weights for the coalesced patch read: the 31x36-byte window (9 aligned words per patch row) is
+// word i = 9*r + j, lane-strided.  For alignment offset sh = (kx-15)&3, byte b of word i is patch column
+// u = 4j + b - sh - 15 of row v = r - 15; g_mom_wu holds u and g_mom_wv holds v (signed bytes) where
+// |u| <= umax[|v|] and 0 elsewhere, so m10 += dp4a(px, wu), m01 += dp4a(px, wv) (ORBextractor.cc:76-103).
+#define MOM_WORDS 279
+#define MOM_STRIDE 288
+__device__ uint32_t g_mom_wu[4 * MOM_STRIDE];
+__device__ uint32_t g_mom_wv[4 * MOM_STRIDE];
+#define LITE_WORDS (BL * BW)  // 429 words: the 39 x 44-byte blurred window around the keypoint
+
 template <bool STRICT_FP>
 __global__ void __launch_bounds__(DESC_WARPS * 32)
 k_describe_lite(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
                 const uint8_t* __restrict__ blur, const uint32_t* __restrict__ sel,
                 const int32_t* __restrict__ sel_cnt, const int32_t* __restrict__ dst,
                 OrbxKeyPointDev* __restrict__ kps, uint8_t* __restrict__ desc, int capacity) {
+  __shared__ __align__(16) uint32_t s_win[DESC_WARPS][LITE_WORDS + 3];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int frame = blockIdx.y;
   const int slot = blockIdx.x * DESC_WARPS + warp;
@@ -272,37 +281,56 @@ k_describe_lite(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __r
   if (level == 0) { pitch = l0.pitch; img = l0.base + (long long)frame * l0.frame_stride; }
   else { pitch = L.pitch; img = arena + (long long)frame * P.arena_bytes + L.offset; }
 
-  // ---- IC_Angle: integer moments over the circular patch of radius 15 (rows v = lane - 15)
+  // ---- blurred 39x39 window -> shared memory, coalesced: word i = 11*r + j of the window that starts at
+  // the aligned column (kx-19)&~3 (the blurred levels live in the library's own pitched buffer: always
+  // 4-byte aligned, and the <= 5 bytes read past column w-1 stay inside the row pitch / the slack)
+  const int bp = L.pitch;
+  const int xb = kx - 19, shb = xb & 3;
+  const uint8_t* bwin = blur + (long long)frame * P.arena_bytes + L.offset + (long long)(ky - 19) * bp + (xb - shb);
+  uint32_t bw[14];
+#pragma unroll
+  for (int t = 0; t < 14; t++) {
+    const int i = lane + 32 * t;
+    const int r = (i * 745) >> 13, j = i - r * BW;  // i / 11 for i < 448
+    bw[t] = 0;
+    if (t < 13 || i < LITE_WORDS) bw[t] = __ldg(reinterpret_cast<const uint32_t*>(bwin + r * bp) + j);
+  }
+
+  // ---- IC_Angle: integer moments over the circular patch of radius 15
   int m01 = 0, m10 = 0;
-  if (lane < 31) {
+  if ((pitch & 3) == 0 && ((uintptr_t)img & 3) == 0) {
+    // rows ky-15..ky+15 never include the last image row, so the <= 1 byte read past column w-1 is in-bounds
+    const int xa = kx - ORBX_HALF_PATCH, sh = xa & 3;
+    const uint8_t* pwin = img + (long long)(ky - ORBX_HALF_PATCH) * pitch + (xa - sh);
+    const uint32_t* wu = g_mom_wu + sh * MOM_STRIDE;
+    const uint32_t* wv = g_mom_wv + sh * MOM_STRIDE;
+#pragma unroll
+    for (int t = 0; t < 9; t++) {
+      const int i = lane + 32 * t;
+      if (t < 8 || i < MOM_WORDS) {
+        const int r = (i * 57) >> 9, j = i - r * 9;  // i / 9 for i < 288
+        const uint32_t px = __ldg(reinterpret_cast<const uint32_t*>(pwin + r * pitch) + j);
+        m10 = dp4a_us(px, __ldg(wu + i), m10);
+        m01 = dp4a_us(px, __ldg(wv + i), m01);
+      }
+    }
+  } else if (lane < 31) {
     const int v = lane - ORBX_HALF_PATCH, av = v < 0 ? -v : v;
-    const uint8_t* rowp = img + (long long)(ky + v) * pitch + (kx - ORBX_HALF_PATCH);  // u = -15
+    const uint8_t* rowp = img + (long long)(ky + v) * pitch + kx;
+    const int d = P.umax[av];
     int s = 0, su = 0;
-    if ((pitch & 3) == 0 && ((uintptr_t)img & 3) == 0 && kx + ORBX_HALF_PATCH + 8 < L.w) {
-      const int sh = 8 * (int)((uintptr_t)rowp & 3);
-      const uint32_t* wp = reinterpret_cast<const uint32_t*>(rowp - ((uintptr_t)rowp & 3));
-      uint32_t w[9];
-#pragma unroll
-      for (int j = 0; j < 9; j++) w[j] = __ldg(wp + j);
-#pragma unroll
-      for (int j = 0; j < 8; j++) {
-        const uint32_t px = __funnelshift_r(w[j], w[j + 1], sh) & c_mom_mask[av * 8 + j];  // u = 4j-15 .. 4j-12
-        const int u0 = 4 * j - 15;
-        const uint32_t wt = (uint32_t)(u0 & 0xff) | ((uint32_t)((u0 + 1) & 0xff) << 8) |
-                            ((uint32_t)((u0 + 2) & 0xff) << 16) | ((uint32_t)((u0 + 3) & 0xff) << 24);
-        s = dp4a_us(px, 0x01010101u, s);
-        su = dp4a_us(px, wt, su);
-      }
-    } else {
-      const int d = P.umax[av];
-      for (int u = -d; u <= d; u++) {
-        const int val = rowp[ORBX_HALF_PATCH + u];
-        s += val;
-        su += u * val;
-      }
+    for (int u = -d; u <= d; u++) {
+      const int val = rowp[u];
+      s += val;
+      su += u * val;
     }
     m10 = su;
     m01 = v * s;
+  }
+#pragma unroll
+  for (int t = 0; t < 14; t++) {
+    const int i = lane + 32 * t;
+    if (t < 13 || i < LITE_WORDS) s_win[warp][i] = bw[t];
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -310,15 +338,15 @@ k_describe_lite(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __r
     m10 += __shfl_xor_sync(0xffffffffu, m10, o);
   }
   const float angle = orbx_fast_atan2((float)m01, (float)m10);
+  __syncwarp();
 
-  // ---- rotated BRIEF on the blurred level: test t = 32*j + lane -> bit `lane` of descriptor word j
+  // ---- rotated BRIEF on the staged window: test t = 32*j + lane -> bit `lane` of descriptor word j
   const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
   float a, b;
   orbx_sincosf(f_mul(angle, factorPI), &b, &a);
-  const uint8_t* centre = blur + (long long)frame * P.arena_bytes + L.offset + (long long)ky * L.pitch + kx;
+  const uint8_t* centre = reinterpret_cast<const uint8_t*>(s_win[warp]) + 19 * (BW * 4) + 19 + shb;
   const float kMagic = 12582912.0f;  // cvRound through the mantissa, see k_describe
-  const int bp = L.pitch;
-  const uint32_t kBias = 0x4B400000u * (uint32_t)(bp + 1);
+  const uint32_t kBias = 0x4B400000u * (uint32_t)(BW * 4 + 1);
   uint32_t word_mine = 0;
 #pragma unroll
   for (int j = 0; j < 8; j++) {
@@ -331,9 +359,9 @@ k_describe_lite(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __r
       fy0 = f_fma(pt.x, b, f_mul(pt.y, a)); fx0 = f_fma(pt.x, a, -f_mul(pt.y, b));
       fy1 = f_fma(pt.z, b, f_mul(pt.w, a)); fx1 = f_fma(pt.z, a, -f_mul(pt.w, b));
     }
-    const uint32_t i0 = __float_as_uint(f_add(fy0, kMagic)) * (uint32_t)bp + __float_as_uint(f_add(fx0, kMagic)) - kBias;
-    const uint32_t i1 = __float_as_uint(f_add(fy1, kMagic)) * (uint32_t)bp + __float_as_uint(f_add(fx1, kMagic)) - kBias;
-    const int v0 = __ldg(centre + (int)i0), v1 = __ldg(centre + (int)i1);
+    const uint32_t i0 = __float_as_uint(f_add(fy0, kMagic)) * (uint32_t)(BW * 4) + __float_as_uint(f_add(fx0, kMagic)) - kBias;
+    const uint32_t i1 = __float_as_uint(f_add(fy1, kMagic)) * (uint32_t)(BW * 4) + __float_as_uint(f_add(fx1, kMagic)) - kBias;
+    const int v0 = centre[(int)i0], v1 = centre[(int)i1];
     const uint32_t wd = __ballot_sync(0xffffffffu, v0 < v1);
     if (lane == j) word_mine = wd;
   }
@@ -356,7 +384,7 @@ k_describe_lite(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __r
   }
 }
 
-// Fills c_mom_mask from the plan's umax table (once per process; the table is a constant of the
+// Fills the row-task and moment-weight tables from the plan's umax table (once per process; the table is a constant of the
 // algorithm, ORBextractor.cc:453-468).
 static const float h_patf[1024] = {
 #include "orb_pattern.inc"
@@ -387,17 +415,20 @@ cudaError_t orbx_describe_init_tables(const int* umax) {
     e = cudaMemcpyToSymbol(c_row_ntasks, cnt, sizeof(cnt));
     if (e != cudaSuccess) return e;
   }
-  uint32_t m[16 * 8];
-  for (int av = 0; av < 16; av++)
-    for (int j = 0; j < 8; j++) {
-      uint32_t w = 0;
-      for (int k = 0; k < 4; k++) {
-        const int u = 4 * j - 15 + k;
-        if ((u < 0 ? -u : u) <= umax[av]) w |= 0xffu << (8 * k);
+  std::vector<uint32_t> wu(4 * MOM_STRIDE, 0), wv(4 * MOM_STRIDE, 0);
+  for (int sh = 0; sh < 4; sh++)
+    for (int i = 0; i < MOM_WORDS; i++) {
+      const int r = i / 9, j = i % 9, v = r - 15, av = v < 0 ? -v : v;
+      for (int b = 0; b < 4; b++) {
+        const int u = 4 * j + b - sh - 15;
+        if ((u < 0 ? -u : u) > umax[av]) continue;
+        wu[sh * MOM_STRIDE + i] |= (uint32_t)(uint8_t)(int8_t)u << (8 * b);
+        wv[sh * MOM_STRIDE + i] |= (uint32_t)(uint8_t)(int8_t)v << (8 * b);
       }
-      m[av * 8 + j] = w;
     }
-  return cudaMemcpyToSymbol(c_mom_mask, m, sizeof(m));
+  cudaError_t e2 = cudaMemcpyToSymbol(g_mom_wu, wu.data(), wu.size() * sizeof(uint32_t));
+  if (e2 != cudaSuccess) return e2;
+  return cudaMemcpyToSymbol(g_mom_wv, wv.data(), wv.size() * sizeof(uint32_t));
 }
 
 cudaError_t orbx_launch_describe_lite(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint8_t* blur,
