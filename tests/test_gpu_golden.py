@@ -59,8 +59,9 @@ def test_match_and_stereo_match_golden():
         assert np.array_equal(res[f, :len(ref)], ref)
     s = np.load(G / "c2_stereo.npz")
     exl, exr = ORBextractor(1200, 1.2, 8, 20, 7), ORBextractor(1200, 1.2, 8, 20, 7)
-    ol = exl.extract_batch_device(_t(s["left"]), (0, 0))
-    orr = exr.extract_batch_device(_t(s["right"]), (0, 0))
+    left_t, right_t = _t(s["left"]), _t(s["right"])  # level 0 of the device pyramids IS the caller's buffer: keep alive
+    ol = exl.extract_batch_device(left_t, (0, 0))
+    orr = exr.extract_batch_device(right_t, (0, 0))
     bi, bd = ORBmatcher.stereo_rowband(ol["kps"], ol["desc"], ol["n"], orr["kps"], orr["desc"], orr["n"],
                                        s["scale_factors"], np.float32(s["bf"]) / np.float32(s["mb"]))
     n = int(ol["n"][0])
