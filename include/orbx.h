@@ -202,6 +202,37 @@ int orbm_queries_shift(const orbx_keypoint* d_kps, const uint8_t* d_desc, const 
                        int8_t* d_qmin_level, int8_t* d_qmax_level, uint8_t* d_qdesc, int32_t* d_nq,
                        void* stream);
 
+/* ORBmatcher::SearchByProjection as a whole function, single-camera case (Nleft == -1), batched over
+ * `batch` current frames:
+ *   ORBM_PROJ_MAPPOINTS  (Frame&, const vector<MapPoint*>&, th, ...)  ORBmatcher.cc:43-142: best and second
+ *                        best with their levels, TH_HIGH, ratio test nn_ratio when both are on one level;
+ *   ORBM_PROJ_LASTFRAME  (Frame& Current, const Frame& Last, th, bMono) ORBmatcher.cc:1676-1887: best only,
+ *                        TH_HIGH, rotation histogram + ComputeThreeMaxima when check_orientation.
+ * The pose / camera projection stays on the host and arrives per query: (d_qx,d_qy) projected pixel,
+ * d_qr search radius, [d_qmin_level, d_qmax_level] the octave band passed to GetFeaturesInArea (max < 0 =
+ * open), d_q_ur projected right coordinate (NULL with d_u_right NULL: no stereo check), d_q_flags bit 0 =
+ * query takes part (mbTrackInView / a non-outlier MapPoint), bit 1 = its MapPoint has Observations()>0, so
+ * the feature it is written to is skipped by all later queries (NULL = 3 for all), d_q_angle = kpLF.angle.
+ * d_feat_locked[j] != 0: F.mvpMapPoints[j] holds a point with Observations()>0 on entry (NULL = none).
+ * The grid is orbm_grid_build's.  The sequential "already matched" dependence of the reference loop is
+ * reproduced exactly (queries are committed in index order).  Outputs: d_match[i] = feature that query i
+ * was written to (-1 none / erased by the rotation check), d_feat_query[j] = query whose MapPoint
+ * F.mvpMapPoints[j] holds on return (-1 = untouched or erased), d_nmatches[f] = the return value.
+ * d_scratch: batch * q_stride * 32 bytes. */
+#define ORBM_PROJ_MAPPOINTS 0
+#define ORBM_PROJ_LASTFRAME 1
+int orbm_search_by_projection(const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n,
+                              int kp_stride, int batch, const int32_t* d_cell_off,
+                              const int32_t* d_cell_idx, float min_x, float max_x, float min_y,
+                              float max_y, const float* d_u_right, const uint8_t* d_feat_locked,
+                              const float* d_qx, const float* d_qy, const float* d_qr,
+                              const int8_t* d_qmin_level, const int8_t* d_qmax_level,
+                              const uint8_t* d_qdesc, const int32_t* d_nq, int q_stride,
+                              const float* d_q_ur, const uint8_t* d_q_flags, const float* d_q_angle,
+                              int mode, float nn_ratio, int check_orientation, void* d_scratch,
+                              int32_t* d_match, int32_t* d_feat_query, int32_t* d_nmatches,
+                              void* stream);
+
 /* Hamming stage of Frame::ComputeStereoMatches (Frame.cc:811-894): per left keypoint the best
  * right keypoint in its row band (|dy| within 2*scale[octR], |octave diff|<=1,
  * uL-max_d <= uR <= uL), first minimum below TH_HIGH=100 wins, candidates visited in

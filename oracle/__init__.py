@@ -261,6 +261,35 @@ def stereo_matches(kps_l, desc_l, kps_r, desc_r, scale_factors, inv_scale_factor
     return bi, bd, ur, dp, kept
 
 
+def search_by_projection(kps, desc, bounds, qx, qy, qr, qmin, qmax, qdesc, mode, nn_ratio=0.6,
+                         check_orientation=True, u_right=None, feat_locked=None, q_ur=None, q_flags=None,
+                         q_angle=None):
+    """ORBmatcher::SearchByProjection (mode 0: MapPoints variant, mode 1: last-frame variant), one frame.
+    Returns (match [nq], feat_query [n], nmatches)."""
+    kps = np.ascontiguousarray(kps)
+    n, nq = kps.size, len(qx)
+    f32 = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+    u8 = lambda a: None if a is None else np.ascontiguousarray(a, np.uint8)
+    i8 = lambda a: np.ascontiguousarray(a, np.int8)
+    args = dict(desc=u8(desc), u_right=f32(u_right), feat_locked=u8(feat_locked), qx=f32(qx), qy=f32(qy), qr=f32(qr),
+                qmin=i8(qmin), qmax=i8(qmax), qdesc=u8(qdesc), q_ur=f32(q_ur), q_flags=u8(q_flags),
+                q_angle=f32(q_angle))
+    pp = lambda a: None if a is None else _p(a)
+    match = np.zeros(nq, np.int32)
+    fq = np.zeros(n, np.int32)
+    L = lib()
+    L.oracle_search_by_projection.restype = C.c_int
+    L.oracle_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float,
+                                              C.c_float] + [C.c_void_p] * 8 + [C.c_int] + [C.c_void_p] * 3 + \
+                                             [C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+    nm = L.oracle_search_by_projection(_p(kps), pp(args["desc"]), n, bounds[0], bounds[1], bounds[2], bounds[3],
+                                       pp(args["u_right"]), pp(args["feat_locked"]), pp(args["qx"]), pp(args["qy"]),
+                                       pp(args["qr"]), pp(args["qmin"]), pp(args["qmax"]), pp(args["qdesc"]), nq,
+                                       pp(args["q_ur"]), pp(args["q_flags"]), pp(args["q_angle"]), int(mode),
+                                       float(nn_ratio), int(bool(check_orientation)), _p(match), _p(fq))
+    return match, fq, nm
+
+
 def rgbd_depth(kps, kps_un, depth_img, mbf):
     """Frame::ComputeStereoFromRGBD.  Returns (uRight, depth)."""
     kps = np.ascontiguousarray(kps)

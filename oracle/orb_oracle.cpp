@@ -929,6 +929,130 @@ int oracle_stereo_matches(const void* kpsL_v, const uint8_t* descL, int nL, cons
   return kept;
 }
 
+// ORBmatcher::SearchByProjection, whole function, single-camera case (Nleft == -1), on flat arrays.
+//   mode 0 = (Frame&, const vector<MapPoint*>&, th, ...)      ORBmatcher.cc:43-142  (best + second, ratio test)
+//   mode 1 = (Frame& CurrentFrame, const Frame& LastFrame...) ORBmatcher.cc:1676-1887 (best only, rotation histogram)
+// The projection itself (pose * point, camera model) is host geometry and arrives precomputed per query:
+// qx,qy = projected pixel, qr = search radius, [qmin,qmax] = octave band handed to GetFeaturesInArea,
+// q_ur = projected right coordinate, q_flags bit0 = query takes part, bit1 = its MapPoint has
+// Observations()>0 (so a feature it is written to becomes invisible to later queries, :88-90 / :1741-1743),
+// q_angle = kpLF.angle.  feat_locked[j] != 0: F.mvpMapPoints[j] holds such a point on entry.
+// Outputs: match[i] = feature written by query i (-1 none; for mode 1 also -1 when the rotation check
+// erased it), feat_query[j] = query whose MapPoint F.mvpMapPoints[j] holds on return (-1 = untouched /
+// erased).  Returns nmatches.
+static void ComputeThreeMaxima(const std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3) {
+  int max1 = 0, max2 = 0, max3 = 0;  // ORBmatcher.cc:2012-2053
+  for (int i = 0; i < L; i++) {
+    const int s = (int)histo[i].size();
+    if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+    else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+    else if (s > max3) { max3 = s; ind3 = i; }
+  }
+  if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+  else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+int oracle_search_by_projection(const void* kps_v, const uint8_t* desc, int n, float mnMinX, float mnMaxX,
+                                float mnMinY, float mnMaxY, const float* u_right, const uint8_t* feat_locked,
+                                const float* qx, const float* qy, const float* qr, const int8_t* qmin,
+                                const int8_t* qmax, const uint8_t* qdesc, int nq, const float* q_ur,
+                                const uint8_t* q_flags, const float* q_angle, int mode, float nnratio,
+                                int check_orientation, int* match, int* feat_query) {
+  const KeyPoint* kps = (const KeyPoint*)kps_v;
+  const int COLS = 64, ROWS = 48, TH_HIGH = 100, HISTO_LENGTH = 30;
+  const float wInv = static_cast<float>(COLS) / static_cast<float>(mnMaxX - mnMinX);
+  const float hInv = static_cast<float>(ROWS) / static_cast<float>(mnMaxY - mnMinY);
+  std::vector<std::vector<int>> grid(COLS * ROWS);
+  for (int i = 0; i < n; i++) {
+    int px = (int)std::round((kps[i].x - mnMinX) * wInv), py = (int)std::round((kps[i].y - mnMinY) * hInv);
+    if (px < 0 || px >= COLS || py < 0 || py >= ROWS) continue;
+    grid[px * ROWS + py].push_back(i);
+  }
+  std::vector<uint8_t> locked(n, 0);  // F.mvpMapPoints[j] && F.mvpMapPoints[j]->Observations()>0
+  for (int j = 0; j < n; j++) { locked[j] = feat_locked ? (feat_locked[j] != 0) : 0; feat_query[j] = -1; }
+  std::vector<int> rotHist[30];
+  const float factor = 1.0f / HISTO_LENGTH;
+  int nmatches = 0;
+  for (int i = 0; i < nq; i++) {
+    match[i] = -1;
+    const int fl = q_flags ? q_flags[i] : 3;
+    if (!(fl & 1)) continue;
+    const float x = qx[i], y = qy[i], r = qr[i];
+    const int minLevel = qmin[i], maxLevel = qmax[i];
+    // GetFeaturesInArea (Frame.cc:657-723)
+    std::vector<int> vIndices;
+    do {
+      const int nMinCellX = std::max(0, (int)std::floor((x - mnMinX - r) * wInv));
+      if (nMinCellX >= COLS) break;
+      const int nMaxCellX = std::min(COLS - 1, (int)std::ceil((x - mnMinX + r) * wInv));
+      if (nMaxCellX < 0) break;
+      const int nMinCellY = std::max(0, (int)std::floor((y - mnMinY - r) * hInv));
+      if (nMinCellY >= ROWS) break;
+      const int nMaxCellY = std::min(ROWS - 1, (int)std::ceil((y - mnMinY + r) * hInv));
+      if (nMaxCellY < 0) break;
+      const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+      for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+        for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+          for (int j : grid[ix * ROWS + iy]) {
+            const KeyPoint& kp = kps[j];
+            if (bCheckLevels) {
+              if (kp.octave < minLevel) continue;
+              if (maxLevel >= 0 && kp.octave > maxLevel) continue;
+            }
+            if (std::fabs(kp.x - x) < r && std::fabs(kp.y - y) < r) vIndices.push_back(j);
+          }
+    } while (0);
+    if (vIndices.empty()) continue;
+    int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+    for (int idx : vIndices) {
+      if (locked[idx]) continue;
+      if (u_right && q_ur && u_right[idx] > 0) {
+        const float er = std::fabs(q_ur[i] - u_right[idx]);
+        if (er > r) continue;
+      }
+      const int dist = DescriptorDistance(qdesc + (size_t)i * 32, desc + (size_t)idx * 32);
+      if (mode == 0) {
+        if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = kps[idx].octave; bestIdx = idx; }
+        else if (dist < bestDist2) { bestLevel2 = kps[idx].octave; bestDist2 = dist; }
+      } else {
+        if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+      }
+    }
+    if (bestDist <= TH_HIGH) {
+      if (mode == 0 && bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+      feat_query[bestIdx] = i;
+      if (fl & 2) locked[bestIdx] = 1; else locked[bestIdx] = 0;  // the feature now holds this query's point
+      match[i] = bestIdx;
+      nmatches++;
+      if (mode == 1 && check_orientation) {
+        float rot = q_angle[i] - kps[bestIdx].angle;
+        if (rot < 0.0) rot += 360.0f;
+        int bin = (int)std::round(rot * factor);
+        if (bin == HISTO_LENGTH) bin = 0;
+        rotHist[bin].push_back(bestIdx);
+      }
+    }
+  }
+  if (mode == 1 && check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int b = 0; b < HISTO_LENGTH; b++) {
+      if (b == ind1 || b == ind2 || b == ind3) continue;
+      for (int j : rotHist[b]) { feat_query[j] = -1; nmatches--; }  // pointer nulled, :1870-1876
+    }
+    // match[i] = -1 where query i's own histogram entry was erased
+    for (int i = 0; i < nq; i++)
+      if (match[i] >= 0) {
+        float rot = q_angle[i] - kps[match[i]].angle;
+        if (rot < 0.0) rot += 360.0f;
+        int bin = (int)std::round(rot * factor);
+        if (bin == HISTO_LENGTH) bin = 0;
+        if (!(bin == ind1 || bin == ind2 || bin == ind3)) match[i] = -1;
+      }
+  }
+  return nmatches;
+}
+
 // Frame::ComputeStereoFromRGBD (Frame.cc:984-1005).  depth_img is float32 [h][w]; kps_un are the
 // undistorted keypoints (mvKeysUn).
 void oracle_rgbd_depth(const void* kps_v, const void* kps_un_v, int n, const float* depth_img, int w, int h,

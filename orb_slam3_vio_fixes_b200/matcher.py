@@ -109,6 +109,32 @@ class ORBmatcher:
         return out
 
     @staticmethod
+    def search_by_projection(kps, desc, n, grid, bounds, q, mode, nn_ratio=0.6, check_orientation=True,
+                             u_right=None, feat_locked=None):
+        """ORBmatcher::SearchByProjection as a whole function (ORBmatcher.cc:43-142 / :1676-1887, Nleft == -1).
+        q: dict of CUDA tensors qx,qy,qr [B,Q] f32, qmin,qmax [B,Q] i8, qdesc [B,Q,32] u8, nq [B] i32 and
+        optionally q_ur [B,Q] f32, flags [B,Q] u8 (bit0 takes part, bit1 MapPoint has observations),
+        angle [B,Q] f32.  Returns dict(match [B,Q] i32, feat_query [B,cap] i32, nmatches [B] i32)."""
+        import torch
+        b, cap = kps.shape[0], kps.shape[1]
+        qs = q["qx"].shape[1]
+        dev = kps.device
+        scratch = torch.empty((b, qs, 8), dtype=torch.int32, device=dev)
+        out = {"match": torch.empty((b, qs), dtype=torch.int32, device=dev),
+               "feat_query": torch.empty((b, cap), dtype=torch.int32, device=dev),
+               "nmatches": torch.empty((b,), dtype=torch.int32, device=dev)}
+        p = lambda t: t.data_ptr() if t is not None else None
+        rc = _lib.lib().orbm_search_by_projection(
+            kps.data_ptr(), desc.data_ptr(), n.data_ptr(), cap, b, grid[0].data_ptr(), grid[1].data_ptr(),
+            float(bounds[0]), float(bounds[1]), float(bounds[2]), float(bounds[3]), p(u_right), p(feat_locked),
+            q["qx"].data_ptr(), q["qy"].data_ptr(), q["qr"].data_ptr(), q["qmin"].data_ptr(), q["qmax"].data_ptr(),
+            q["qdesc"].data_ptr(), q["nq"].data_ptr(), qs, p(q.get("q_ur")), p(q.get("flags")), p(q.get("angle")),
+            int(mode), float(nn_ratio), int(bool(check_orientation)), scratch.data_ptr(), out["match"].data_ptr(),
+            out["feat_query"].data_ptr(), out["nmatches"].data_ptr(), _stream(dev))
+        _lib.check(rc, "orbm_search_by_projection")
+        return out
+
+    @staticmethod
     def stereo_rowband(kps_l, desc_l, n_l, kps_r, desc_r, n_r, scale_factors, max_d):
         """Hamming stage of Frame::ComputeStereoMatches.  Returns (best_idx_r [B,cap] i32, best_dist [B,cap] i32)."""
         import torch

@@ -258,3 +258,119 @@ def test_rgbd_depth(oracle_mod):
         rur, rdp = oracle_mod.rgbd_depth(k[f, :n[f]], kun_np[f, :n[f]], depth[f], mbf)
         assert np.array_equal(ur2[f, :n[f]].cpu().numpy().view(np.uint32), rur.view(np.uint32))
         assert np.array_equal(dp2[f, :n[f]].cpu().numpy().view(np.uint32), rdp.view(np.uint32))
+
+
+def _proj_queries(kq, dq, shift, th, sf, band, rng, dup=1, drop=0.0, unlocked=0.0, cap=None):
+    """Host-built SearchByProjection queries: keypoints kq of another frame moved by `shift`."""
+    k = np.concatenate([kq] * dup)
+    d = np.concatenate([dq] * dup)
+    nq = len(k)
+    q = {"qx": (k["x"] + np.float32(shift[0])).astype(np.float32), "qy": (k["y"] + np.float32(shift[1])).astype(np.float32),
+         "qr": (np.float32(th) * sf[k["octave"]]).astype(np.float32),
+         "qmin": (k["octave"] + band[0]).astype(np.int8), "qmax": (k["octave"] + band[1]).astype(np.int8),
+         "qdesc": d, "angle": k["angle"].astype(np.float32)}
+    fl = np.full(nq, 3, np.uint8)
+    fl[rng.random(nq) < unlocked] = 1
+    fl[rng.random(nq) < drop] &= 2
+    q["flags"] = fl
+    q["q_ur"] = (q["qx"] - np.float32(24.0) + rng.normal(0, 3, nq)).astype(np.float32)
+    return q
+
+
+def _proj_run(oracle_mod, out, q_list, bounds, mode, nn_ratio, check_ori, u_right=None, feat_locked=None):
+    import torch
+    B, cap = out["kps"].shape[0], out["kps"].shape[1]
+    Q = max(len(q["qx"]) for q in q_list)
+    dev = out["kps"].device
+    qt = {"qx": torch.zeros((B, Q), dtype=torch.float32), "qy": torch.zeros((B, Q), dtype=torch.float32),
+          "qr": torch.zeros((B, Q), dtype=torch.float32), "qmin": torch.zeros((B, Q), dtype=torch.int8),
+          "qmax": torch.zeros((B, Q), dtype=torch.int8), "qdesc": torch.zeros((B, Q, 32), dtype=torch.uint8),
+          "angle": torch.zeros((B, Q), dtype=torch.float32), "flags": torch.zeros((B, Q), dtype=torch.uint8),
+          "q_ur": torch.zeros((B, Q), dtype=torch.float32), "nq": torch.zeros(B, dtype=torch.int32)}
+    for f, q in enumerate(q_list):
+        m = len(q["qx"])
+        for key in ("qx", "qy", "qr", "qmin", "qmax", "qdesc", "angle", "flags", "q_ur"):
+            qt[key][f, :m] = torch.from_numpy(np.ascontiguousarray(q[key]))
+        qt["nq"][f] = m
+    qt = {k_: v.to(dev) for k_, v in qt.items()}
+    if u_right is None:
+        qt.pop("q_ur")
+    grid = ORBmatcher.grid_build(out["kps"], out["n"], bounds)
+    res = ORBmatcher.search_by_projection(out["kps"], out["desc"], out["n"], grid, bounds, qt, mode, nn_ratio, check_ori,
+                                          u_right=None if u_right is None else _t(u_right),
+                                          feat_locked=None if feat_locked is None else _t(feat_locked))
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    n = out["n"].cpu().numpy()
+    mt, fq, nm = res["match"].cpu().numpy(), res["feat_query"].cpu().numpy(), res["nmatches"].cpu().numpy()
+    tot = 0
+    for f, q in enumerate(q_list):
+        rm, rfq, rnm = oracle_mod.search_by_projection(
+            kps[f, :n[f]], desc[f, :n[f]], bounds, q["qx"], q["qy"], q["qr"], q["qmin"], q["qmax"], q["qdesc"], mode,
+            nn_ratio, check_ori, u_right=None if u_right is None else u_right[f, :n[f]],
+            feat_locked=None if feat_locked is None else feat_locked[f, :n[f]],
+            q_ur=q["q_ur"] if u_right is not None else None, q_flags=q["flags"], q_angle=q["angle"])
+        m = len(q["qx"])
+        assert np.array_equal(mt[f, :m], rm), (f, np.nonzero(mt[f, :m] != rm)[0][:10])
+        assert np.array_equal(fq[f, :n[f]], rfq)
+        assert nm[f] == rnm
+        tot += rnm
+    return tot, mt, fq
+
+
+@pytest.mark.parametrize("check_ori", [True, False])
+def test_search_by_projection_lastframe(oracle_mod, check_ori):
+    """ORBmatcher.cc:1676-1887 (mono shape): last-frame keypoints projected by the known shift, th=15."""
+    from bench import shifts_for, MATCH_TH
+    B = 4
+    frames = S.make_frames("C1", B)
+    ex = ORBextractor(1000, max_batch=B, **ORB)
+    out = _extract_batch(ex, frames, (0, 1000))
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    n = out["n"].cpu().numpy()
+    sf = ex.GetScaleFactors()
+    sh = shifts_for(0, B)
+    rng = np.random.default_rng(3)
+    bounds = (0.0, 752.0, 0.0, 480.0)
+    # plain; duplicated queries (every second copy finds its best locked -> rescans); mixed flags
+    for dup, drop, unl in ((1, 0.0, 0.0), (2, 0.0, 0.0), (3, 0.1, 0.4)):
+        ql = []
+        for f in range(B):
+            s = (f - 1) % B
+            ql.append(_proj_queries(kps[s, :n[s]], desc[s, :n[s]], sh[f], MATCH_TH, sf, (-1, 1), rng, dup, drop, unl))
+        tot, mt, fq = _proj_run(oracle_mod, out, ql, bounds, 1, 0.9, check_ori)
+        assert tot > B * 500 * (1 if dup == 1 else 1.2)
+
+
+def test_search_by_projection_mappoints(oracle_mod):
+    """ORBmatcher.cc:43-142 (C3 shape): 'map points' = keypoints of the 3 other frames, levels [l-1,l], ratio 0.8,
+    some features already matched on entry, stereo consistency against mvuRight."""
+    from bench import shifts_for
+    B = 4
+    frames = S.make_frames("C3", B)
+    ex = ORBextractor(1000, max_batch=B, **ORB)
+    out = _extract_batch(ex, frames, (0, 0))
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    n = out["n"].cpu().numpy()
+    cap = out["kps"].shape[1]
+    sf = ex.GetScaleFactors()
+    rng = np.random.default_rng(9)
+    bounds = (0.0, 640.0, 0.0, 480.0)
+    pos = np.array([S.frame_shift(t) for t in range(B)], np.float32)
+    ql = []
+    for f in range(B):
+        parts = []
+        for s in range(B):
+            if s == f:
+                continue
+            parts.append(_proj_queries(kps[s, :n[s]], desc[s, :n[s]], pos[s] - pos[f], 12.0, sf, (-1, 0), rng, 1, 0.05, 0.2))
+        ql.append({k_: np.concatenate([p[k_] for p in parts]) for k_ in parts[0]})
+    locked = (rng.random((B, cap)) < 0.15).astype(np.uint8)
+    u_right = np.where(rng.random((B, cap)) < 0.7, kps["x"] - np.float32(24.0), np.float32(-1)).astype(np.float32)
+    for nn in (0.8, 0.6):
+        tot, mt, fq = _proj_run(oracle_mod, out, ql, bounds, 0, nn, False, u_right=u_right, feat_locked=locked)
+        assert tot > B * 300
+    tot2, _, _ = _proj_run(oracle_mod, out, ql, bounds, 0, 0.8, False)
+    assert tot2 > tot

@@ -92,3 +92,33 @@ def test_argmin2_semantics(oracle_mod):
     assert (res["best_idx"], res["best_dist"]) == (2, 1)
     res = oracle_mod.argmin2_csr(q, r, np.array([0, 0], np.int32), idx, lv, 0)[0]
     assert (res["best_idx"], res["best_dist"], res["second_dist"], res["best_level"]) == (-1, 256, 256, -1)
+
+
+def test_search_by_projection_lock_semantics(oracle_mod):
+    """ORBmatcher.cc:1741-1743 / :88-90: a feature written by a MapPoint with Observations()>0 is invisible to
+    later queries; one written by an unobserved point can be overwritten (both matches still count)."""
+    from orb_slam3_vio_fixes_b200 import _lib
+    k = np.zeros(3, _lib.KP_DTYPE)
+    k["x"], k["y"], k["octave"], k["angle"] = [100, 101, 102], [50, 50, 50], 0, [10, 10, 10]
+    d = np.zeros((3, 32), np.uint8)
+    d[1, 0] = 0x01          # distance 1 to the zero descriptor
+    d[2, 0] = 0x07          # distance 3
+    qd = np.zeros((2, 32), np.uint8)
+    common = dict(qx=[101, 101], qy=[50, 50], qr=[5, 5], qmin=[0, 0], qmax=[-1, -1], qdesc=qd,
+                  q_angle=[10, 10], check_orientation=True)
+    bounds = (0.0, 640.0, 0.0, 480.0)
+    m, fq, nm = oracle_mod.search_by_projection(k, d, bounds, mode=1, q_flags=[3, 3], **common)
+    assert list(m) == [0, 1] and list(fq) == [0, 1, -1] and nm == 2
+    m, fq, nm = oracle_mod.search_by_projection(k, d, bounds, mode=1, q_flags=[1, 3], **common)
+    assert list(m) == [0, 0] and list(fq) == [1, -1, -1] and nm == 2
+    m, fq, nm = oracle_mod.search_by_projection(k, d, bounds, mode=1, q_flags=[3, 0], **common)
+    assert list(m) == [0, -1] and nm == 1
+    # mode 0: ratio test uses the second best AFTER the lock: q1 sees {1 (d=1), 2 (d=3)}: 1 > 0.3*3 -> rejected
+    m, fq, nm = oracle_mod.search_by_projection(k, d, bounds, mode=0, nn_ratio=0.3, q_flags=[3, 3], **common)
+    assert list(m) == [0, -1] and nm == 1          # q0: best 0 (d=0), 0 > 0.3*1 is false -> accepted
+    m, fq, nm = oracle_mod.search_by_projection(k, d, bounds, mode=0, nn_ratio=0.4, q_flags=[3, 3], **common)
+    assert list(m) == [0, 1] and nm == 2
+    # rotation histogram: a lone match in another bin than the dominant ones survives only if >= 10 % of max
+    m, fq, nm = oracle_mod.search_by_projection(k, d, bounds, mode=1, q_flags=[3, 3], feat_locked=[0, 0, 1],
+                                                **{**common, "q_angle": [10, 100]})
+    assert nm == 2 and list(m) == [0, 1]           # bins 0 and 3, one entry each: both within the top three
