@@ -192,13 +192,20 @@ def main():
     shift = torch.from_numpy(shifts_for(t0, B)).to(dev)
     src_frame = torch.from_numpy(((np.arange(B) - 1) % B).astype(np.int32)).to(dev)
 
-    ex = ORBextractor(nf, ORB["scale"], ORB["nlevels"], ORB["ini"], ORB["mn"], max_batch=B, device=local_rank,
-                      stage_timing=True).plan(w, h)
+    # `ex` runs the timed steps; `ex_t` records per-stage CUDA events (which switches the sub-batch
+    # stream overlap off) and only serves the per-kernel breakdown below
+    ex = ORBextractor(nf, ORB["scale"], ORB["nlevels"], ORB["ini"], ORB["mn"], max_batch=B, device=local_rank).plan(w, h)
+    ex_t = ORBextractor(nf, ORB["scale"], ORB["nlevels"], ORB["ini"], ORB["mn"], max_batch=B, device=local_rank,
+                        stage_timing=True).plan(w, h)
     sf = ex.GetScaleFactors()
     bounds = (0.0, float(w), 0.0, float(h))
     out = ex.alloc_outputs(B, dev)
     qbuf = None
-    launches_per_step = (ORB["nlevels"] - 1) + 4 + 3  # resize x7, fast, octree, order, describe, grid, queries, search
+    # resize x7, fast, octree, order, describe per sub-batch (orbx_extract_batch_device cuts batches >= 128 frames
+    # in two, one per internal stream; ORBX_DEVICE_SPLIT) + grid, queries, search
+    nsplit = int(os.environ.get("ORBX_DEVICE_SPLIT", "2"))
+    nsplit = nsplit if B >= 64 * nsplit else 1
+    launches_per_step = nsplit * ((ORB["nlevels"] - 1) + 4) + 3
 
     def step(src):
         nonlocal qbuf
@@ -232,14 +239,14 @@ def main():
     m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     match_ms = 0.0
     for _ in range(args.steps):
-        ex.extract_batch_device(frames, lap, out)
+        ex_t.extract_batch_device(frames, lap, out)
         m0.record()
         grid = ORBmatcher.grid_build(out["kps"], out["n"], bounds)
         qbuf = ORBmatcher.queries_shift(out["kps"], out["desc"], out["n"], src_frame, shift, MATCH_TH, sf, (-1, 1), qbuf)
         res = ORBmatcher.search_area(out["kps"], out["desc"], out["n"], grid, bounds, qbuf["qx"], qbuf["qy"],
                                      qbuf["qr"], qbuf["qmin"], qbuf["qmax"], qbuf["qdesc"], qbuf["nq"])
         m1.record()
-        for k, v in ex.stage_times().items():
+        for k, v in ex_t.stage_times().items():
             stage_ms[k] += v / args.steps
         torch.cuda.synchronize()
         match_ms += m0.elapsed_time(m1) / args.steps

@@ -283,6 +283,93 @@ k_stereo_rowband(const OrbxKeyPointDev* __restrict__ kl, const uint8_t* __restri
 }
 
 
+// Same result with the right keypoints bucketed by image row first (the reference's vRowIndices, Frame.cc:820-838,
+// at 16-row granularity): one CTA = one slice of the left keypoints of one pair; it builds the buckets in shared
+// memory (count, scan, fill), then each warp takes left keypoints and scans only the bucket of their row.  The
+// visiting order inside a bucket is irrelevant: ties are decided by the packed key (dist << 20 | iR).
+#define RB_SHIFT 4
+#define RB_BINS 256          // rows < 4096
+#define RB_THREADS 256
+#define RB_SPAN 3            // a right keypoint's band (<= 2*2*scale+2 rows) touches at most 3 buckets up to scale 7.5
+__global__ void __launch_bounds__(RB_THREADS)
+k_stereo_rowband_binned(const OrbxKeyPointDev* __restrict__ kl, const uint8_t* __restrict__ dl,
+                        const int32_t* __restrict__ nl_arr, const OrbxKeyPointDev* __restrict__ kr,
+                        const uint8_t* __restrict__ dr, const int32_t* __restrict__ nr_arr, int kp_stride,
+                        ScaleTab scales, float max_d, int32_t* __restrict__ best_idx, int32_t* __restrict__ best_dist) {
+  extern __shared__ uint16_t rb_list[];  // RB_SPAN * kp_stride entries
+  __shared__ int cnt[RB_BINS + 1];
+  __shared__ int cur[RB_BINS];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, f = blockIdx.y;
+  const size_t base = (size_t)f * kp_stride;
+  const int nL = nl_arr[f], nR = nr_arr[f];
+  for (int i = tid; i <= RB_BINS; i += RB_THREADS) cnt[i] = 0;
+  __syncthreads();
+  for (int iR = tid; iR < nR; iR += RB_THREADS) {
+    const OrbxKeyPointDev kpR = kr[base + iR];
+    const float rr = f_mul(2.0f, scales.s[kpR.octave]);
+    const int maxr = (int)ceilf(f_add(kpR.y, rr)), minr = (int)floorf(f_sub(kpR.y, rr));
+    const int b0 = max(minr, 0) >> RB_SHIFT, b1 = min(maxr >> RB_SHIFT, RB_BINS - 1);
+    for (int b = b0; b <= b1 && b < b0 + RB_SPAN; b++) atomicAdd(&cnt[b], 1);
+  }
+  __syncthreads();
+  if (warp == 0) {  // exclusive scan of 256 counts
+    int carry = 0;
+    for (int c = 0; c < RB_BINS; c += 32) {
+      const int v = cnt[c + lane];
+      int inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+      }
+      cnt[c + lane] = carry + inc - v;
+      cur[c + lane] = carry + inc - v;
+      carry += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) cnt[RB_BINS] = carry;
+  }
+  __syncthreads();
+  for (int iR = tid; iR < nR; iR += RB_THREADS) {
+    const OrbxKeyPointDev kpR = kr[base + iR];
+    const float rr = f_mul(2.0f, scales.s[kpR.octave]);
+    const int maxr = (int)ceilf(f_add(kpR.y, rr)), minr = (int)floorf(f_sub(kpR.y, rr));
+    const int b0 = max(minr, 0) >> RB_SHIFT, b1 = min(maxr >> RB_SHIFT, RB_BINS - 1);
+    for (int b = b0; b <= b1 && b < b0 + RB_SPAN; b++) rb_list[atomicAdd(&cur[b], 1)] = (uint16_t)iR;
+  }
+  __syncthreads();
+  // left keypoints of this slice, one per warp at a time
+  const int per = (nL + gridDim.x - 1) / gridDim.x;
+  const int l0 = blockIdx.x * per, l1 = min(nL, l0 + per);
+  for (int iL = l0 + warp; iL < l1; iL += RB_THREADS / 32) {
+    const OrbxKeyPointDev kpL = kl[base + iL];
+    const int rowL = (int)kpL.y;  // vRowIndices[vL] (:852)
+    const float minU = f_sub(kpL.x, max_d), maxU = kpL.x;  // minD = 0
+    uint32_t bestk = KEY_NONE;
+    if (!(maxU < 0) && rowL >= 0 && (rowL >> RB_SHIFT) < RB_BINS) {
+      const Desc256 dq = load_desc(dl + (base + iL) * 32);
+      const int b = rowL >> RB_SHIFT;
+      for (int e = cnt[b] + lane; e < cnt[b + 1]; e += 32) {
+        const int iR = rb_list[e];
+        const OrbxKeyPointDev kpR = kr[base + iR];
+        const float rr = f_mul(2.0f, scales.s[kpR.octave]);
+        const int maxr = (int)ceilf(f_add(kpR.y, rr)), minr = (int)floorf(f_sub(kpR.y, rr));
+        if (rowL < minr || rowL > maxr) continue;
+        if (kpR.octave < kpL.octave - 1 || kpR.octave > kpL.octave + 1) continue;
+        if (!(kpR.x >= minU && kpR.x <= maxU)) continue;
+        const int d = hamming(dq, load_desc(dr + (base + iR) * 32));
+        bestk = min(bestk, ((uint32_t)d << 20) | (uint32_t)iR);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) bestk = min(bestk, __shfl_xor_sync(0xffffffffu, bestk, o));
+    if (lane == 0) {
+      const int d = bestk == KEY_NONE ? 256 : (int)(bestk >> 20);
+      if (d < 100) { best_idx[base + iL] = (int)(bestk & 0xFFFFF); best_dist[base + iL] = d; }
+      else { best_idx[base + iL] = -1; best_dist[base + iL] = 100; }
+    }
+  }
+}
+
 // ---- window queries for SearchByProjection(Frame&, const Frame&) under a pure image shift ------------
 // The reference projects last-frame map points with the current pose (host geometry, out of scope)
 // and then searches radius th*scale[octave] in the octave band [o+lo, o+hi] (ORBmatcher.cc:1725-1733).
@@ -385,10 +472,26 @@ int orbm_stereo_rowband(const orbx_keypoint* d_kps_l, const uint8_t* d_desc_l, c
     return ORBX_E_INVALID;
   ScaleTab st;
   for (int i = 0; i < ORBX_MAX_LEVELS; i++) st.s[i] = i < nlevels ? scale_factors_host[i] : 1.0f;
-  dim3 grd((kp_stride + M_WARPS - 1) / M_WARPS, batch);
-  k_stereo_rowband<<<grd, M_WARPS * 32, 0, (cudaStream_t)stream>>>(
-      (const OrbxKeyPointDev*)d_kps_l, d_desc_l, d_n_l, (const OrbxKeyPointDev*)d_kps_r, d_desc_r, d_n_r, kp_stride, st,
-      max_d, d_best_idx_r, d_best_dist);
+  float smax = 0;
+  for (int i = 0; i < nlevels; i++) smax = scale_factors_host[i] > smax ? scale_factors_host[i] : smax;
+  const size_t smem = (size_t)RB_SPAN * kp_stride * sizeof(uint16_t);
+  if (kp_stride < 65536 && smem <= 160 * 1024 && 4.0f * smax + 3.0f <= (float)((RB_SPAN - 1) << RB_SHIFT)) {
+    // bucketed by row: a band of <= 4*scale+3 rows touches at most RB_SPAN buckets
+    static bool attr_set = false;
+    if (smem > 48 * 1024 && !attr_set) {
+      CUM(cudaFuncSetAttribute(k_stereo_rowband_binned, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+      attr_set = true;
+    }
+    dim3 grd(4, batch);
+    k_stereo_rowband_binned<<<grd, RB_THREADS, smem, (cudaStream_t)stream>>>(
+        (const OrbxKeyPointDev*)d_kps_l, d_desc_l, d_n_l, (const OrbxKeyPointDev*)d_kps_r, d_desc_r, d_n_r, kp_stride,
+        st, max_d, d_best_idx_r, d_best_dist);
+  } else {
+    dim3 grd((kp_stride + M_WARPS - 1) / M_WARPS, batch);
+    k_stereo_rowband<<<grd, M_WARPS * 32, 0, (cudaStream_t)stream>>>(
+        (const OrbxKeyPointDev*)d_kps_l, d_desc_l, d_n_l, (const OrbxKeyPointDev*)d_kps_r, d_desc_r, d_n_r, kp_stride,
+        st, max_d, d_best_idx_r, d_best_dist);
+  }
   CUM(cudaGetLastError());
   return ORBX_OK;
 }
