@@ -8,12 +8,12 @@
 // Two kernels:
 //   k_proj_score    one thread per query: GetFeaturesInArea fused with scoring under all the gates that
 //                   are known on entry (octave band, window, features already holding a point, stereo
-//                   consistency) -> best and second best (index + distance).
-//   k_proj_resolve  one warp per frame walks the queries in order.  A query's scored result is final
-//                   unless its best (or, with the ratio test, its second best) has been locked by an
-//                   earlier query in the meantime — removing any other candidate cannot change it; only
-//                   then the warp rescans that query's window with the current lock bitmap.  The rotation
-//                   histogram, ComputeThreeMaxima (:2012-2053) and the erasure pass follow in the same warp.
+//                   consistency) -> the 4 best candidates (index + distance), sorted.
+//   k_proj_resolve  one warp per frame commits the queries in order.  A query's result is the first (two)
+//                   entries of its list that no earlier query has locked — removing any other candidate
+//                   cannot change it; only when a full list runs out the warp rescans that query's window
+//                   with the current lock bitmap.  The rotation histogram, ComputeThreeMaxima (:2012-2053)
+//                   and the erasure pass follow in the same warp.
 #include "match_core.cuh"
 
 struct ProjArgs {
