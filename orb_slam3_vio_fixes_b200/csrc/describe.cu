@@ -178,11 +178,28 @@ k_describe(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restri
       const int r = tk >> 4, w = tk & 15, q = r * BW + w;
       const uint2* tp = sm.t + r * PW + w;
       const uint2 a = tp[0], b = tp[1], c = tp[2];
-      const uint32_t t0 = a.x & 0xffffu, t1 = a.y & 0xffffu, t2 = a.x >> 16, t3 = a.y >> 16;
-      const uint32_t t4 = b.x & 0xffffu, t5 = b.y & 0xffffu, t6 = b.x >> 16, t7 = b.y >> 16;
-      const uint32_t t8 = c.x & 0xffffu, t9 = c.y & 0xffffu;
-      bw[q] = blur_out(t0, t1, t2, t3, t4, t5, t6) | (blur_out(t1, t2, t3, t4, t5, t6, t7) << 8) |
-              (blur_out(t2, t3, t4, t5, t6, t7, t8) << 16) | (blur_out(t3, t4, t5, t6, t7, t8, t9) << 24);
+      // a.x = {T0,T2}, a.y = {T1,T3}, b.x = {T4,T6}, b.y = {T5,T7}, c.x = {T8,..}, c.y = {T9,..}: each output is a
+      // 7-tap dot product over 16-bit sums = 4-5 dp2a (u16 x u8) on the packed pairs, no unpacking; the rounded
+      // byte (acc + 2^15) >> 16 is byte 2 of the accumulator (acc < 2^24)
+      uint32_t o0 = __dp2a_lo(a.x, 0x00003012u, 32768u);   // 18 T0 + 48 T2
+      o0 = __dp2a_lo(a.y, 0x00003822u, o0);                // 34 T1 + 56 T3
+      o0 = __dp2a_lo(b.x, 0x00001230u, o0);                // 48 T4 + 18 T6
+      o0 = __dp2a_lo(b.y, 0x00000022u, o0);                // 34 T5
+      uint32_t o1 = __dp2a_lo(a.y, 0x00003012u, 32768u);   // 18 T1 + 48 T3
+      o1 = __dp2a_lo(a.x, 0x00002200u, o1);                // 34 T2
+      o1 = __dp2a_lo(b.x, 0x00002238u, o1);                // 56 T4 + 34 T6
+      o1 = __dp2a_lo(b.y, 0x00001230u, o1);                // 48 T5 + 18 T7
+      uint32_t o2 = __dp2a_lo(a.x, 0x00001200u, 32768u);   // 18 T2
+      o2 = __dp2a_lo(a.y, 0x00002200u, o2);                // 34 T3
+      o2 = __dp2a_lo(b.x, 0x00003030u, o2);                // 48 T4 + 48 T6
+      o2 = __dp2a_lo(b.y, 0x00002238u, o2);                // 56 T5 + 34 T7
+      o2 = __dp2a_lo(c.x, 0x00000012u, o2);                // 18 T8
+      uint32_t o3 = __dp2a_lo(a.y, 0x00001200u, 32768u);   // 18 T3
+      o3 = __dp2a_lo(b.x, 0x00003822u, o3);                // 34 T4 + 56 T6
+      o3 = __dp2a_lo(b.y, 0x00003030u, o3);                // 48 T5 + 48 T7
+      o3 = __dp2a_lo(c.x, 0x00000022u, o3);                // 34 T8
+      o3 = __dp2a_lo(c.y, 0x00000012u, o3);                // 18 T9
+      bw[q] = __byte_perm(__byte_perm(o0, o1, 0x0062), __byte_perm(o2, o3, 0x0062), 0x5410);
     }
   }
   __syncwarp();
