@@ -374,3 +374,37 @@ def test_search_by_projection_mappoints(oracle_mod):
         assert tot > B * 300
     tot2, _, _ = _proj_run(oracle_mod, out, ql, bounds, 0, 0.8, False)
     assert tot2 > tot
+
+
+def test_degenerate_inputs_new_entry_points(oracle_mod):
+    """Flat frames (0 keypoints) and empty query sets through the stereo / projection / RGB-D entry points."""
+    import torch
+    from orb_slam3_vio_fixes_b200 import _lib
+    B = 2
+    flat = np.full((B, 480, 752), 90, np.uint8)
+    mixed = np.stack([S.make_frames("C2", 1)[0], flat[0]])
+    exl = ORBextractor(1200, max_batch=B, **ORB)
+    exr = ORBextractor(1200, max_batch=B, **ORB)
+    ol = _extract_batch(exl, mixed, (0, 0))
+    orr = _extract_batch(exr, flat, (0, 0))
+    assert int(ol["n"][1]) == 0 and int(orr["n"].sum()) == 0
+    sf = exl.GetScaleFactors()
+    bi, bd = ORBmatcher.stereo_rowband(ol["kps"], ol["desc"], ol["n"], orr["kps"], orr["desc"], orr["n"], sf, 458.0)
+    res = ORBmatcher.stereo_refine(exl, exr, ol["kps"], ol["n"], orr["kps"], bi, bd, 47.9, 458.0)
+    n0 = int(ol["n"][0])
+    assert (bi[0, :n0] == -1).all() and (res["u_right"][0, :n0] == -1).all() and res["kept"].tolist() == [0, 0]
+    # projection search: no queries, then queries against a frame without features
+    bounds = (0.0, 752.0, 0.0, 480.0)
+    grid = ORBmatcher.grid_build(ol["kps"], ol["n"], bounds)
+    Q = 64
+    dev = ol["kps"].device
+    q = {"qx": torch.full((B, Q), 300.0, device=dev), "qy": torch.full((B, Q), 200.0, device=dev),
+         "qr": torch.full((B, Q), 20.0, device=dev), "qmin": torch.zeros((B, Q), dtype=torch.int8, device=dev),
+         "qmax": torch.full((B, Q), -1, dtype=torch.int8, device=dev),
+         "qdesc": torch.zeros((B, Q, 32), dtype=torch.uint8, device=dev),
+         "angle": torch.zeros((B, Q), device=dev), "nq": torch.tensor([0, Q], dtype=torch.int32, device=dev)}
+    for mode in (_lib.PROJ_MAPPOINTS, _lib.PROJ_LASTFRAME):
+        r = ORBmatcher.search_by_projection(ol["kps"], ol["desc"], ol["n"], grid, bounds, q, mode, 0.8, True)
+        assert r["nmatches"].tolist() == [0, 0] and (r["match"][1] == -1).all() and (r["feat_query"][0, :n0] == -1).all()
+    ur, dp = ORBmatcher.rgbd_depth(ol["kps"], ol["n"], torch.ones((B, 480, 752), device=dev), 40.0)
+    assert (dp[0, :n0] == 1).all()
