@@ -92,6 +92,10 @@ class ORBextractor {
   std::vector<float> inline GetScaleSigmaSquares() { return mvLevelSigma2; }
   std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
 
+  // The C-ABI handle behind this instance (device-resident outputs and pyramid of the last call), for the
+  // matcher-side entry points that run on them without a second upload (orbx_compat/StereoMatcher.h).
+  orbx_handle handle() const { return h_; }
+
   // "GetPyramid": level image of the last call (same object mvImagePyramid[level] holds).
   const cv::Mat& GetPyramid(int level) const { return mvImagePyramid[level]; }
 

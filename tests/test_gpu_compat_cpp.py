@@ -12,12 +12,12 @@ pytestmark = pytest.mark.gpu
 ROOT = Path(__file__).resolve().parents[1]
 
 
-def _build_exe(tmp):
+def _build_exe(tmp, name="compat_main"):
     B.build()
-    exe = tmp / "compat_main"
+    exe = tmp / name
     pkg = ROOT / "orb_slam3_vio_fixes_b200"
     subprocess.check_call(["nvcc", "-O2", "-std=c++17", "-DORBX_NO_OPENCV", f"-I{ROOT / 'include'}",
-                           str(ROOT / "tests" / "cpp" / "compat_main.cpp"), "-o", str(exe), f"-L{pkg}", "-lorbx",
+                           str(ROOT / "tests" / "cpp" / f"{name}.cpp"), "-o", str(exe), f"-L{pkg}", "-lorbx",
                            "-Xlinker", f"-rpath={pkg}"])
     return exe
 
@@ -45,3 +45,25 @@ def test_cpp_dropin_matches_oracle(oracle_mod, tmp_path, lap):
     idx = ((np.arange(n)[:, None] + np.arange(1, 9)[None, :]) % n).astype(np.int32).ravel()
     ref = oracle_mod.argmin2_csr(odesc, odesc, off, idx, okps["octave"].astype(np.int8), 0)
     assert np.array_equal(res, ref)
+
+
+def test_cpp_stereo_dropin_matches_oracle(oracle_mod, tmp_path):
+    """Frame::ComputeStereoMatches replaced by ORB_SLAM3::ComputeStereoMatches(left, right, mb, mbf, ...)."""
+    exe = _build_exe(tmp_path, "compat_stereo")
+    left, right = S.make_frames("C2", 1)[0], S.make_frames("C2", 1, right=True)[0]
+    left.tofile(tmp_path / "l.raw")
+    right.tofile(tmp_path / "r.raw")
+    mbf = np.float32(47.90639384423901)
+    mb = np.float32(mbf / np.float32(458.654))
+    out = subprocess.check_output([str(exe), str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), "752", "480", "1200",
+                                   repr(float(mb)), repr(float(mbf)), str(tmp_path / "o")], text=True)
+    nl, nr, kept = [int(v) for v in out.split()]
+    el, er = oracle_mod.Extractor(1200), oracle_mod.Extractor(1200)
+    kl, dl, _ = el.extract(left, (0, 0))
+    kr, dr, _ = er.extract(right, (0, 0))
+    pl = [el.pyramid(l) for l in range(8)]
+    pr = [er.pyramid(l) for l in range(8)]
+    bi, bd, ur, dp, rkept = oracle_mod.stereo_matches(kl, dl, kr, dr, el.scale_factors, el.inv_scale_factors, pl, pr, mb, mbf)
+    assert (nl, nr, kept) == (len(kl), len(kr), rkept) and kept > 100
+    assert np.array_equal(np.fromfile(tmp_path / "o.ur", dtype=np.uint32), ur.view(np.uint32))
+    assert np.array_equal(np.fromfile(tmp_path / "o.depth", dtype=np.uint32), dp.view(np.uint32))
