@@ -113,7 +113,8 @@ class Extractor:
         """operator(): returns (keypoints[KP_DTYPE], descriptors[n,32] u8, monoIndex)."""
         img = np.ascontiguousarray(img, np.uint8)
         hgt, w = img.shape
-        cap = self.nfeatures + 3 * self.nlevels + 64
+        # a level returns up to max(N+3, 4*nIni) keypoints, nIni = round(width/height) root nodes (ORBextractor.cc:559)
+        cap = self.nfeatures + self.nlevels * (3 + 4 * (w // max(hgt, 1) + 2)) + 64
         kps = np.zeros(cap, KP_DTYPE)
         desc = np.zeros((cap, 32), np.uint8)
         n = C.c_int(0)
