@@ -269,6 +269,83 @@ int orbm_rgbd_depth(const orbx_keypoint* d_kps, const orbx_keypoint* d_kps_un, c
 int orbm_knn2_dense(const uint8_t* d_q, int nq, const uint8_t* d_r, int nr, int32_t* d_idx2,
                     int32_t* d_dist2, void* stream);
 
+/* --------------------------------------------------------------------------------------
+ * Vocabulary-node matching (§8(f).2-4).
+ * A DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>, Thirdparty/DBoW2/DBoW2/
+ * FeatureVector.h) is a CSR per frame: d_node[f][node_stride] ascending node ids,
+ * d_off[f][node_stride+1], d_idx[f][kp_stride] feature indices (ascending inside a node),
+ * d_nn[f] nodes in use.
+ * -------------------------------------------------------------------------------------- */
+typedef struct orbm_feature_vector {
+  int32_t* d_node;
+  int32_t* d_off;
+  int32_t* d_idx;
+  int32_t* d_nn;
+} orbm_feature_vector;
+
+/* ORBmatcher::SearchByBoW, whole function, single-camera case, batched over `batch` pairs:
+ *   ORBM_BOW_KF_FRAME  (KeyFrame*, Frame&, vector<MapPoint*>&)      ORBmatcher.cc:223-425   best <= TH_LOW
+ *   ORBM_BOW_KF_KF     (KeyFrame*, KeyFrame*, vector<MapPoint*>&)   ORBmatcher.cc:765-905   best <  TH_LOW
+ * side 1 = the (first) keyframe, side 2 = the frame / second keyframe.  d_valid1[i] != 0: feature i
+ * of side 1 holds a MapPoint that is not bad (NULL = all); d_valid2 likewise (KF_KF only).
+ * d_match12[i] = side-2 feature matched to side-1 feature i (vpMatches12 of KF_KF), d_match21 the
+ * inverse (vpMapPointMatches of KF_FRAME); -1 = none or erased by the rotation check.
+ * The reference's "already matched" skip is reproduced exactly. */
+#define ORBM_BOW_KF_FRAME 0
+#define ORBM_BOW_KF_KF 1
+int orbm_search_by_bow(int mode, const orbx_keypoint* d_kps1, const uint8_t* d_desc1, const int32_t* d_n1,
+                       const uint8_t* d_valid1, const orbm_feature_vector* fv1,
+                       const orbx_keypoint* d_kps2, const uint8_t* d_desc2, const int32_t* d_n2,
+                       const uint8_t* d_valid2, const orbm_feature_vector* fv2, int kp_stride,
+                       int node_stride, int batch, float nn_ratio, int check_orientation,
+                       int32_t* d_match12, int32_t* d_match21, int32_t* d_nmatches, void* stream);
+
+/* ORBmatcher::SearchForTriangulation (ORBmatcher.cc:907-1146), pinhole single-camera case, with
+ * Pinhole::epipolarConstrain (CameraModels/Pinhole.cpp:107-129), batched over keyframe pairs.
+ * Host geometry per pair: d_F12[p][9] = K1^-T [t12]x R12 K2^-1 (row-major), d_ep[p][2] = epipole.
+ * d_has_mp*[i] != 0: GetMapPoint(i) != NULL (skipped); d_u_right* = mvuRight (NULL = monocular).
+ * scale_factors2 / level_sigma2_2 = pKF2->mvScaleFactors / mvLevelSigma2 (host arrays).
+ * d_match12[i] = vMatches12[i] after the rotation check; d_nmatches[p] = the return value. */
+int orbm_search_for_triangulation(
+    const orbx_keypoint* d_kps1, const uint8_t* d_desc1, const int32_t* d_n1, const uint8_t* d_has_mp1,
+    const float* d_u_right1, const orbm_feature_vector* fv1, const orbx_keypoint* d_kps2,
+    const uint8_t* d_desc2, const int32_t* d_n2, const uint8_t* d_has_mp2, const float* d_u_right2,
+    const orbm_feature_vector* fv2, int kp_stride, int node_stride, int batch, const float* d_F12,
+    const float* d_ep, const float* scale_factors2_host, const float* level_sigma2_2_host, int nlevels,
+    int only_stereo, int coarse, int check_orientation, int32_t* d_match12, int32_t* d_nmatches,
+    void* stream);
+
+/* DBoW2 vocabulary tree, flat, device-resident (TemplatedVocabulary.h m_nodes): node i has children
+ * d_child_idx[d_child_off[i] .. d_child_off[i+1]) (none = leaf), descriptor d_node_desc[i*32],
+ * word id d_node_word[i] and weight d_node_weight[i] (leaves).  Node 0 is the root. */
+typedef struct orbm_vocabulary {
+  const int32_t* d_child_off;
+  const int32_t* d_child_idx;
+  const uint8_t* d_node_desc;
+  const int32_t* d_node_word;
+  const double* d_node_weight;
+  int n_nodes, L;
+} orbm_vocabulary;
+
+/* TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup)
+ * (TemplatedVocabulary.h:1127-1259; Frame.cc:738-745 calls it with levelsup = 4), TF_IDF + L1.
+ * Per feature: word id, node id at level L-levelsup, weight.  Per frame: the FeatureVector CSR
+ * (fv_out; d_nn < 0 = node_stride too small, -needed) and the BowVector (d_bow_word ascending,
+ * d_bow_val normalised, d_bow_n entries; rows of kp_stride).  kp_stride <= 8192. */
+int orbm_bow_transform(const orbm_vocabulary* voc, const uint8_t* d_desc, const int32_t* d_n,
+                       int kp_stride, int batch, int levelsup, int32_t* d_feat_word,
+                       int32_t* d_feat_node, double* d_feat_weight, const orbm_feature_vector* fv_out,
+                       int node_stride, int32_t* d_bow_word, double* d_bow_val, int32_t* d_bow_n,
+                       void* stream);
+
+/* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:367-401), batched over map points: point m
+ * observes descriptors d_desc_pool[d_obs_idx[d_obs_off[m] .. d_obs_off[m+1])]; d_best[m] = position
+ * (in that list) of the descriptor with the least median distance to the rest, d_median[m] its
+ * median (may be NULL). */
+int orbm_distinctive_descriptors(const uint8_t* d_desc_pool, const int32_t* d_obs_off,
+                                 const int32_t* d_obs_idx, int n_points, int32_t* d_best,
+                                 int32_t* d_median, void* stream);
+
 /* Library / build identification. */
 const char* orbx_version(void);
 const char* orbx_last_error(void);

@@ -315,6 +315,135 @@ def knn2_dense(q, r):
     return idx, dist
 
 
+def _fv_args(fv):
+    node = np.ascontiguousarray(fv[0], np.int32)
+    off = np.ascontiguousarray(fv[1], np.int32)
+    idx = np.ascontiguousarray(fv[2], np.int32)
+    return node, off, idx
+
+
+def search_by_bow(mode, kps1, desc1, fv1, kps2, desc2, fv2, nn_ratio=0.6, check_orientation=True, valid1=None,
+                  valid2=None):
+    """ORBmatcher::SearchByBoW (mode 0: KeyFrame x Frame :223-425, mode 1: KeyFrame x KeyFrame :765-905).
+    fv = (node ids ascending, off, idx).  Returns (match12, match21, nmatches)."""
+    kps1, kps2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+    d1, d2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    a, b = _fv_args(fv1), _fv_args(fv2)
+    v1 = None if valid1 is None else np.ascontiguousarray(valid1, np.uint8)
+    v2 = None if valid2 is None else np.ascontiguousarray(valid2, np.uint8)
+    pp = lambda x: None if x is None else _p(x)
+    m12 = np.zeros(kps1.size, np.int32)
+    m21 = np.zeros(kps2.size, np.int32)
+    L = lib()
+    L.oracle_search_by_bow.restype = C.c_int
+    L.oracle_search_by_bow.argtypes = [C.c_int] + ([C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                                    C.c_void_p, C.c_void_p, C.c_int] * 2) + \
+                                      [C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+    nm = L.oracle_search_by_bow(int(mode), _p(kps1), _p(d1), kps1.size, pp(v1), _p(a[0]), _p(a[1]), _p(a[2]),
+                                a[0].size, _p(kps2), _p(d2), kps2.size, pp(v2), _p(b[0]), _p(b[1]), _p(b[2]),
+                                b[0].size, float(nn_ratio), int(bool(check_orientation)), _p(m12), _p(m21))
+    return m12, m21, nm
+
+
+def search_for_triangulation(kps1, desc1, fv1, kps2, desc2, fv2, F12, ep, scale2, sigma2_2, only_stereo=False,
+                             coarse=False, check_orientation=True, has_mp1=None, has_mp2=None, u_right1=None,
+                             u_right2=None):
+    """ORBmatcher::SearchForTriangulation (:907-1146), pinhole single camera.  Returns (match12, nmatches)."""
+    kps1, kps2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+    d1, d2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    a, b = _fv_args(fv1), _fv_args(fv2)
+    u8 = lambda x: None if x is None else np.ascontiguousarray(x, np.uint8)
+    f32 = lambda x: None if x is None else np.ascontiguousarray(x, np.float32)
+    h1, h2, u1, u2 = u8(has_mp1), u8(has_mp2), f32(u_right1), f32(u_right2)
+    F, e, sc, sg = f32(np.zeros(9) if F12 is None else F12), f32(ep), f32(scale2), f32(sigma2_2)
+    pp = lambda x: None if x is None else _p(x)
+    m12 = np.zeros(kps1.size, np.int32)
+    L = lib()
+    L.oracle_search_for_triangulation.restype = C.c_int
+    side = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    L.oracle_search_for_triangulation.argtypes = side * 2 + [C.c_void_p] * 4 + [C.c_int] * 3 + [C.c_void_p]
+    nm = L.oracle_search_for_triangulation(_p(kps1), _p(d1), kps1.size, pp(h1), pp(u1), _p(a[0]), _p(a[1]), _p(a[2]),
+                                           a[0].size, _p(kps2), _p(d2), kps2.size, pp(h2), pp(u2), _p(b[0]),
+                                           _p(b[1]), _p(b[2]), b[0].size, _p(F), _p(e), _p(sc), _p(sg),
+                                           int(bool(only_stereo)), int(bool(coarse)), int(bool(check_orientation)),
+                                           _p(m12))
+    return m12, nm
+
+
+def bow_transform(desc, voc, levelsup=4):
+    """DBoW2 transform.  voc = dict(child_off, child_idx, node_desc, node_word, node_weight, L).
+    Returns dict(feat_word, feat_node, feat_weight, bow_word, bow_val, fv=(node, off, idx))."""
+    d = np.ascontiguousarray(desc, np.uint8)
+    n = d.shape[0]
+    co = np.ascontiguousarray(voc["child_off"], np.int32)
+    ci = np.ascontiguousarray(voc["child_idx"], np.int32)
+    nd = np.ascontiguousarray(voc["node_desc"], np.uint8)
+    nw = np.ascontiguousarray(voc["node_word"], np.int32)
+    wt = np.ascontiguousarray(voc["node_weight"], np.float64)
+    fw, fn, fwt = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.float64)
+    bw, bv = np.zeros(n, np.int32), np.zeros(n, np.float64)
+    node, off, idx = np.zeros(n, np.int32), np.zeros(n + 1, np.int32), np.zeros(n, np.int32)
+    nn = C.c_int(0)
+    L = lib()
+    L.oracle_bow_transform.restype = C.c_int
+    L.oracle_bow_transform.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_int] + \
+                                      [C.c_void_p] * 8 + [C.POINTER(C.c_int)]
+    k = L.oracle_bow_transform(_p(d), n, _p(co), _p(ci), _p(nd), _p(nw), _p(wt), int(voc["L"]), int(levelsup),
+                               _p(fw), _p(fn), _p(fwt), _p(bw), _p(bv), _p(node), _p(off), _p(idx), C.byref(nn))
+    nn = nn.value
+    return {"feat_word": fw, "feat_node": fn, "feat_weight": fwt, "bow_word": bw[:k].copy(), "bow_val": bv[:k].copy(),
+            "fv": (node[:nn].copy(), off[:nn + 1].copy(), idx[:off[nn]].copy())}
+
+
+def distinctive_descriptor(desc):
+    """MapPoint::ComputeDistinctiveDescriptors core: index of the least-median row."""
+    d = np.ascontiguousarray(desc, np.uint8)
+    L = lib()
+    L.oracle_distinctive_descriptor.restype = C.c_int
+    L.oracle_distinctive_descriptor.argtypes = [C.c_void_p, C.c_int]
+    return L.oracle_distinctive_descriptor(_p(d), d.shape[0])
+
+
+def make_vocabulary(k, L, seed=0, stop_fraction=0.02, desc_pool=None):
+    """A synthetic DBoW2-shaped vocabulary (k-ary, depth L, random 256-bit node descriptors, idf-like positive
+    weights, a few stopped words with weight 0) in the flat layout, node ids in the breadth-first creation order
+    of TemplatedVocabulary::HKmeansStep.  ORBvoc.txt itself is not in the image."""
+    rng = np.random.default_rng(seed)
+    child_off, child_idx = [0], []
+    levels = [[0]]
+    nid = 1
+    parents = [0]
+    children_of = {0: []}
+    for lvl in range(1, L + 1):
+        cur = []
+        for pnode in parents:
+            ids = list(range(nid, nid + k))
+            nid += k
+            children_of[pnode] = ids
+            for c in ids:
+                children_of[c] = []
+            cur += ids
+        parents = cur
+    nnodes = nid
+    for i in range(nnodes):
+        child_idx += children_of[i]
+        child_off.append(len(child_idx))
+    if desc_pool is None:
+        node_desc = rng.integers(0, 256, (nnodes, 32), dtype=np.uint8)
+    else:  # node centres drawn from real descriptors: features of neighbouring frames share nodes
+        pool = np.ascontiguousarray(desc_pool, np.uint8).reshape(-1, 32)
+        node_desc = pool[rng.integers(0, pool.shape[0], nnodes)].copy()
+    node_word = np.full(nnodes, -1, np.int32)
+    leaves = [i for i in range(nnodes) if not children_of[i]]
+    node_word[leaves] = np.arange(len(leaves), dtype=np.int32)
+    node_weight = np.zeros(nnodes, np.float64)
+    w = np.log(rng.uniform(1.5, 400.0, len(leaves)))
+    w[rng.random(len(leaves)) < stop_fraction] = 0.0
+    node_weight[leaves] = w
+    return {"child_off": np.array(child_off, np.int32), "child_idx": np.array(child_idx, np.int32),
+            "node_desc": node_desc, "node_word": node_word, "node_weight": node_weight, "L": L}
+
+
 def bench_extract(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, lap, threads, flags=0):
     """Times the oracle over frames[n,h,w]; returns (seconds, total keypoints)."""
     frames = np.ascontiguousarray(frames, np.uint8)

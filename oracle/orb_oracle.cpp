@@ -39,6 +39,7 @@
 #include <list>
 #include <thread>
 #include <utility>
+#include <map>
 #include <vector>
 
 namespace {
@@ -1082,6 +1083,219 @@ void oracle_knn2_dense(const uint8_t* q, int nq, const uint8_t* r, int nr, int* 
     idx2[2 * i] = i0; idx2[2 * i + 1] = i1;
     dist2[2 * i] = i0 < 0 ? -1 : b0; dist2[2 * i + 1] = i1 < 0 ? -1 : b1;
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Vocabulary-node matching: ORBmatcher::SearchByBoW ×2 and SearchForTriangulation on flat arrays.
+// A DBoW2::FeatureVector (std::map<NodeId, vector<unsigned>>) is a CSR: fv_node[nn] ascending node
+// ids, fv_off[nn+1], fv_idx[] feature indices of each node in insertion (= ascending) order.
+// The merge walk with lower_bound (ORBmatcher.cc:244-379) visits exactly the node ids present in
+// both maps, in ascending order.
+// ---------------------------------------------------------------------------------------------
+static inline int rot_bin(float a1, float a2) {  // ORBmatcher.cc:332-338 and twins
+  const float factor = 1.0f / 30;
+  float rot = a1 - a2;
+  if (rot < 0.0) rot += 360.0f;
+  int bin = (int)std::round(rot * factor);
+  if (bin == 30) bin = 0;
+  return bin;
+}
+
+// mode 0: SearchByBoW(KeyFrame*, Frame&, ...) single-camera (F.Nleft == -1), ORBmatcher.cc:223-425.
+//         side 1 = keyframe (valid1[i] = pMP && !pMP->isBad()), side 2 = frame; best <= TH_LOW.
+// mode 1: SearchByBoW(KeyFrame*, KeyFrame*, ...) (NLeft == -1), ORBmatcher.cc:765-905; valid2[j] =
+//         pMP2 && !pMP2->isBad(); best < TH_LOW.
+// match12[i] = side-2 feature matched to side-1 feature i (-1 none / erased by the rotation check),
+// match21[j] = the inverse (mode 0: this is vpMapPointMatches; mode 1: match12 is vpMatches12).
+int oracle_search_by_bow(int mode, const void* kps1_v, const uint8_t* desc1, int n1, const uint8_t* valid1,
+                         const int* fv1_node, const int* fv1_off, const int* fv1_idx, int nn1,
+                         const void* kps2_v, const uint8_t* desc2, int n2, const uint8_t* valid2,
+                         const int* fv2_node, const int* fv2_off, const int* fv2_idx, int nn2, float nnratio,
+                         int check_orientation, int* match12, int* match21) {
+  const KeyPoint* kps1 = (const KeyPoint*)kps1_v;
+  const KeyPoint* kps2 = (const KeyPoint*)kps2_v;
+  const int TH_LOW = 50, HISTO_LENGTH = 30;
+  for (int i = 0; i < n1; i++) match12[i] = -1;
+  for (int j = 0; j < n2; j++) match21[j] = -1;
+  std::vector<int> rotHist[30];
+  int nmatches = 0, a = 0, b = 0;
+  while (a < nn1 && b < nn2) {
+    if (fv1_node[a] == fv2_node[b]) {
+      for (int i1 = fv1_off[a]; i1 < fv1_off[a + 1]; i1++) {
+        const int idx1 = fv1_idx[i1];
+        if (valid1 && !valid1[idx1]) continue;
+        int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+        for (int i2 = fv2_off[b]; i2 < fv2_off[b + 1]; i2++) {
+          const int idx2 = fv2_idx[i2];
+          if (match21[idx2] >= 0) continue;            // vpMapPointMatches[realIdxF] / vbMatched2[idx2]
+          if (mode == 1 && valid2 && !valid2[idx2]) continue;
+          const int dist = DescriptorDistance(desc1 + (size_t)idx1 * 32, desc2 + (size_t)idx2 * 32);
+          if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+          else if (dist < bestDist2) { bestDist2 = dist; }
+        }
+        const bool pass = mode == 0 ? bestDist1 <= TH_LOW : bestDist1 < TH_LOW;
+        if (pass && static_cast<float>(bestDist1) < nnratio * static_cast<float>(bestDist2)) {
+          match12[idx1] = bestIdx2; match21[bestIdx2] = idx1;
+          if (check_orientation) rotHist[rot_bin(kps1[idx1].angle, kps2[bestIdx2].angle)].push_back(idx1);
+          nmatches++;
+        }
+      }
+      a++; b++;
+    } else if (fv1_node[a] < fv2_node[b]) {
+      a = (int)(std::lower_bound(fv1_node, fv1_node + nn1, fv2_node[b]) - fv1_node);
+    } else {
+      b = (int)(std::lower_bound(fv2_node, fv2_node + nn2, fv1_node[a]) - fv2_node);
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int idx1 : rotHist[i]) { match21[match12[idx1]] = -1; match12[idx1] = -1; nmatches--; }
+    }
+  }
+  return nmatches;
+}
+
+// ORBmatcher::SearchForTriangulation, pinhole single-camera case (mpCamera2 == NULL, NLeft == -1),
+// ORBmatcher.cc:907-1146 with Pinhole::epipolarConstrain (CameraModels/Pinhole.cpp:107-129).
+// Host geometry arrives precomputed per keyframe pair: F12 = K1^-T [t12]x R12 K2^-1 (row-major 3x3),
+// ep = epipole of KF1's centre in KF2.  has_mp*[i] = GetMapPoint(i) != NULL, u_right* = mvuRight (NULL:
+// monocular, every value < 0).  scale2 / sigma2_2 = pKF2->mvScaleFactors / mvLevelSigma2.
+// match12[i] = vMatches12 after the rotation check.  Returns nmatches.
+int oracle_search_for_triangulation(const void* kps1_v, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
+                                    const float* u_right1, const int* fv1_node, const int* fv1_off,
+                                    const int* fv1_idx, int nn1, const void* kps2_v, const uint8_t* desc2, int n2,
+                                    const uint8_t* has_mp2, const float* u_right2, const int* fv2_node,
+                                    const int* fv2_off, const int* fv2_idx, int nn2, const float* F12,
+                                    const float* ep, const float* scale2, const float* sigma2_2, int only_stereo,
+                                    int coarse, int check_orientation, int* match12) {
+  const KeyPoint* kps1 = (const KeyPoint*)kps1_v;
+  const KeyPoint* kps2 = (const KeyPoint*)kps2_v;
+  const int TH_LOW = 50, HISTO_LENGTH = 30;
+  for (int i = 0; i < n1; i++) match12[i] = -1;
+  std::vector<int> rotHist[30];
+  int nmatches = 0, a = 0, b = 0;
+  while (a < nn1 && b < nn2) {
+    if (fv1_node[a] == fv2_node[b]) {
+      for (int i1 = fv1_off[a]; i1 < fv1_off[a + 1]; i1++) {
+        const int idx1 = fv1_idx[i1];
+        if (has_mp1 && has_mp1[idx1]) continue;
+        const bool bStereo1 = u_right1 && u_right1[idx1] >= 0;
+        if (only_stereo && !bStereo1) continue;
+        const KeyPoint& kp1 = kps1[idx1];
+        int bestDist = TH_LOW, bestIdx2 = -1;
+        for (int i2 = fv2_off[b]; i2 < fv2_off[b + 1]; i2++) {
+          const int idx2 = fv2_idx[i2];
+          if (has_mp2 && has_mp2[idx2]) continue;       // vbMatched2 is never set in the reference
+          const bool bStereo2 = u_right2 && u_right2[idx2] >= 0;
+          if (only_stereo && !bStereo2) continue;
+          const int dist = DescriptorDistance(desc1 + (size_t)idx1 * 32, desc2 + (size_t)idx2 * 32);
+          if (dist > TH_LOW || dist > bestDist) continue;
+          const KeyPoint& kp2 = kps2[idx2];
+          if (!bStereo1 && !bStereo2) {
+            const float distex = ep[0] - kp2.x;
+            const float distey = ep[1] - kp2.y;
+            if (distex * distex + distey * distey < 100 * scale2[kp2.octave]) continue;
+          }
+          bool ok = coarse != 0;
+          if (!ok) {  // Pinhole::epipolarConstrain
+            const float la = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+            const float lb = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+            const float lc = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+            const float num = la * kp2.x + lb * kp2.y + lc;
+            const float den = la * la + lb * lb;
+            if (den == 0) ok = false;
+            else { const float dsqr = num * num / den; ok = dsqr < 3.84 * sigma2_2[kp2.octave]; }
+          }
+          if (ok) { bestIdx2 = idx2; bestDist = dist; }
+        }
+        if (bestIdx2 >= 0) {
+          match12[idx1] = bestIdx2; nmatches++;
+          if (check_orientation) rotHist[rot_bin(kp1.angle, kps2[bestIdx2].angle)].push_back(idx1);
+        }
+      }
+      a++; b++;
+    } else if (fv1_node[a] < fv2_node[b]) {
+      a = (int)(std::lower_bound(fv1_node, fv1_node + nn1, fv2_node[b]) - fv1_node);
+    } else {
+      b = (int)(std::lower_bound(fv2_node, fv2_node + nn2, fv1_node[a]) - fv2_node);
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int idx1 : rotHist[i]) { match12[idx1] = -1; nmatches--; }
+    }
+  }
+  return nmatches;
+}
+
+// DBoW2::TemplatedVocabulary<FORB::TDescriptor,FORB>::transform(features, BowVector&, FeatureVector&, levelsup)
+// (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1127-1259; FORB::distance FORB.cpp:82-100; BowVector.cpp:33-88;
+// FeatureVector.cpp:31-45) for TF_IDF weighting + L1 norm (the ORBvoc.txt header "10 6 0 0").  The tree is flat:
+// node i has children child_idx[child_off[i] .. child_off[i+1]) (a leaf has none), descriptor node_desc[i*32],
+// word id node_word[i] and weight node_weight[i] (leaves).  Outputs per feature: word / node / weight; the
+// BowVector as (bow_word ascending, bow_val normalised), and the FeatureVector CSR.  Returns the number of
+// BowVector entries; *fv_nn = number of FeatureVector nodes.
+int oracle_bow_transform(const uint8_t* desc, int n, const int* child_off, const int* child_idx,
+                         const uint8_t* node_desc, const int* node_word, const double* node_weight, int L,
+                         int levelsup, int* feat_word, int* feat_node, double* feat_weight, int* bow_word,
+                         double* bow_val, int* fv_node, int* fv_off, int* fv_idx, int* fv_nn) {
+  std::map<unsigned, double> v;
+  std::map<unsigned, std::vector<unsigned>> fv;
+  const int nid_level = L - levelsup;
+  for (int f = 0; f < n; f++) {
+    unsigned nid = 0, final_id = 0;
+    int current_level = 0;
+    do {
+      ++current_level;
+      const int c0 = child_off[final_id], c1 = child_off[final_id + 1];
+      final_id = child_idx[c0];
+      double best_d = DescriptorDistance(desc + (size_t)f * 32, node_desc + (size_t)final_id * 32);
+      for (int c = c0 + 1; c < c1; c++) {
+        const unsigned id = child_idx[c];
+        const double d = DescriptorDistance(desc + (size_t)f * 32, node_desc + (size_t)id * 32);
+        if (d < best_d) { best_d = d; final_id = id; }
+      }
+      if (current_level == nid_level) nid = final_id;
+    } while (child_off[final_id] != child_off[final_id + 1]);
+    const double w = node_weight[final_id];
+    feat_word[f] = node_word[final_id]; feat_node[f] = (int)nid; feat_weight[f] = w;
+    if (w > 0) { v[(unsigned)node_word[final_id]] += w; fv[nid].push_back((unsigned)f); }
+  }
+  double norm = 0.0;
+  for (auto& kv : v) norm += fabs(kv.second);
+  if (norm > 0.0) for (auto& kv : v) kv.second /= norm;
+  int k = 0;
+  for (auto& kv : v) { bow_word[k] = (int)kv.first; bow_val[k] = kv.second; k++; }
+  int nn = 0, pos = 0;
+  for (auto& kv : fv) {
+    fv_node[nn] = (int)kv.first; fv_off[nn] = pos;
+    for (unsigned i : kv.second) fv_idx[pos++] = (int)i;
+    nn++;
+  }
+  fv_off[nn] = pos; *fv_nn = nn;
+  return k;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors core (MapPoint.cc:367-401): all-pairs distances, per row the
+// median = sorted[0.5*(N-1)], pick the row with the least median (first wins).  Returns the index.
+int oracle_distinctive_descriptor(const uint8_t* desc, int n) {
+  std::vector<std::vector<int>> D(n, std::vector<int>(n, 0));
+  for (int i = 0; i < n; i++)
+    for (int j = i + 1; j < n; j++) { int d = DescriptorDistance(desc + (size_t)i * 32, desc + (size_t)j * 32); D[i][j] = d; D[j][i] = d; }
+  int BestMedian = INT_MAX, BestIdx = 0;
+  for (int i = 0; i < n; i++) {
+    std::vector<int> vDists(D[i].begin(), D[i].end());
+    std::sort(vDists.begin(), vDists.end());
+    int median = vDists[(size_t)(0.5 * (n - 1))];
+    if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+  }
+  return BestIdx;
 }
 
 // Multithreaded CPU baseline: runs `extract` over n_frames frames (one frame per task, T

@@ -21,6 +21,7 @@ FLAG_LEVEL_BLUR = 8
 STAGES = ("pyramid", "fast", "octree", "order", "describe")
 TIE_FIRST_MIN, TIE_LAST_MIN = 0, 1
 PROJ_MAPPOINTS, PROJ_LASTFRAME = 0, 1
+BOW_KF_FRAME, BOW_KF_KF = 0, 1
 MAX_LEVELS = 12
 GRID_COLS, GRID_ROWS = 64, 48
 
@@ -36,7 +37,9 @@ SYMBOLS = [
     "orbx_create", "orbx_destroy", "orbx_max_keypoints", "orbx_extract", "orbx_extract_batch_device",
     "orbx_extract_batch_host", "orbx_last_outputs_device", "orbx_get_pyramid", "orbx_pyramid_device", "orbx_level_size",
     "orbx_get_scale_tables", "orbx_stage_times", "orbx_debug_level_keypoints", "orbx_debug_octree", "orbm_argmin2_csr", "orbm_grid_build",
-    "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense", "orbx_version", "orbx_last_error",
+    "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
+    "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
+    "orbx_version", "orbx_last_error",
 ]
 
 
@@ -45,6 +48,16 @@ class OrbxConfig(C.Structure):
                 ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32), ("width", C.c_int32),
                 ("height", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32),
                 ("flags", C.c_uint32)]
+
+
+class OrbmFeatureVector(C.Structure):  # orbm_feature_vector
+    _fields_ = [("d_node", C.c_void_p), ("d_off", C.c_void_p), ("d_idx", C.c_void_p), ("d_nn", C.c_void_p)]
+
+
+class OrbmVocabulary(C.Structure):  # orbm_vocabulary
+    _fields_ = [("d_child_off", C.c_void_p), ("d_child_idx", C.c_void_p), ("d_node_desc", C.c_void_p),
+                ("d_node_word", C.c_void_p), ("d_node_weight", C.c_void_p), ("n_nodes", C.c_int32),
+                ("L", C.c_int32)]
 
 
 class OrbxError(RuntimeError):
@@ -98,6 +111,13 @@ def lib():
     L.orbm_stereo_refine.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp, vp, f32, f32, vp, vp, vp, vp, vp]
     L.orbm_rgbd_depth.argtypes = [vp, vp, vp, i32, i32, vp, sz, sz, i32, i32, f32, vp, vp, vp]
     L.orbm_knn2_dense.argtypes = [vp, i32, vp, i32, vp, vp, vp]
+    pfv, pvoc = C.POINTER(OrbmFeatureVector), C.POINTER(OrbmVocabulary)
+    L.orbm_search_by_bow.argtypes = [i32, vp, vp, vp, vp, pfv, vp, vp, vp, vp, pfv, i32, i32, i32, f32, i32, vp, vp,
+                                     vp, vp]
+    L.orbm_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, pfv, vp, vp, vp, vp, vp, pfv, i32, i32, i32, vp,
+                                                vp, vp, vp, i32, i32, i32, i32, vp, vp, vp]
+    L.orbm_bow_transform.argtypes = [pvoc, vp, vp, i32, i32, i32, vp, vp, vp, pfv, i32, vp, vp, vp, vp]
+    L.orbm_distinctive_descriptors.argtypes = [vp, vp, vp, i32, vp, vp, vp]
     L.orbx_version.restype = C.c_char_p
     L.orbx_last_error.restype = C.c_char_p
     _lib = L

@@ -194,3 +194,118 @@ class ORBmatcher:
                                         dist.data_ptr(), _stream(q.device))
         _lib.check(rc, "orbm_knn2_dense")
         return idx, dist
+
+    # ---- vocabulary-node matching (SearchByBoW / SearchForTriangulation / DBoW2 transform) -----------
+    @staticmethod
+    def _fv_struct(fv):
+        return _lib.OrbmFeatureVector(fv["node"].data_ptr(), fv["off"].data_ptr(), fv["idx"].data_ptr(),
+                                      fv["nn"].data_ptr())
+
+    @staticmethod
+    def feature_vector_alloc(batch, cap, node_stride, dev):
+        """Empty FeatureVector CSR tensors: node [B,S], off [B,S+1], idx [B,cap], nn [B] (all i32)."""
+        import torch
+        z = lambda *s: torch.zeros(s, dtype=torch.int32, device=dev)
+        return {"node": z(batch, node_stride), "off": z(batch, node_stride + 1), "idx": z(batch, cap), "nn": z(batch)}
+
+    @staticmethod
+    def search_by_bow(mode, kps1, desc1, n1, fv1, kps2, desc2, n2, fv2, nn_ratio=0.6, check_orientation=True,
+                      valid1=None, valid2=None):
+        """ORBmatcher::SearchByBoW (mode _lib.BOW_KF_FRAME: ORBmatcher.cc:223-425; BOW_KF_KF: :765-905).
+        kps* [B,cap,7] f32, desc* [B,cap,32] u8, n* [B] i32, fv* dicts from feature_vector_alloc / bow_transform,
+        valid* [B,cap] u8 or None.  Returns dict(match12, match21 [B,cap] i32, nmatches [B] i32)."""
+        import torch
+        b, cap = kps1.shape[0], kps1.shape[1]
+        dev = kps1.device
+        ns = fv1["node"].shape[1]
+        assert fv2["node"].shape[1] == ns and kps2.shape[1] == cap
+        out = {"match12": torch.empty((b, cap), dtype=torch.int32, device=dev),
+               "match21": torch.empty((b, cap), dtype=torch.int32, device=dev),
+               "nmatches": torch.empty((b,), dtype=torch.int32, device=dev)}
+        p = lambda t: t.data_ptr() if t is not None else None
+        s1, s2 = ORBmatcher._fv_struct(fv1), ORBmatcher._fv_struct(fv2)
+        rc = _lib.lib().orbm_search_by_bow(int(mode), kps1.data_ptr(), desc1.data_ptr(), n1.data_ptr(), p(valid1), s1,
+                                           kps2.data_ptr(), desc2.data_ptr(), n2.data_ptr(), p(valid2), s2, cap, ns,
+                                           b, float(nn_ratio), int(bool(check_orientation)),
+                                           out["match12"].data_ptr(), out["match21"].data_ptr(),
+                                           out["nmatches"].data_ptr(), _stream(dev))
+        _lib.check(rc, "orbm_search_by_bow")
+        return out
+
+    @staticmethod
+    def search_for_triangulation(kps1, desc1, n1, fv1, kps2, desc2, n2, fv2, F12, ep, scale_factors2, level_sigma2_2,
+                                 only_stereo=False, coarse=False, check_orientation=True, has_mp1=None,
+                                 has_mp2=None, u_right1=None, u_right2=None):
+        """ORBmatcher::SearchForTriangulation (ORBmatcher.cc:907-1146), pinhole single camera.  F12 [B,9] f32,
+        ep [B,2] f32 (CUDA).  Returns dict(match12 [B,cap] i32, nmatches [B] i32)."""
+        import torch
+        b, cap = kps1.shape[0], kps1.shape[1]
+        dev = kps1.device
+        ns = fv1["node"].shape[1]
+        assert fv2["node"].shape[1] == ns and kps2.shape[1] == cap
+        out = {"match12": torch.empty((b, cap), dtype=torch.int32, device=dev),
+               "nmatches": torch.empty((b,), dtype=torch.int32, device=dev)}
+        p = lambda t: t.data_ptr() if t is not None else None
+        sf = np.ascontiguousarray(scale_factors2, np.float32)
+        sg = np.ascontiguousarray(level_sigma2_2, np.float32)
+        s1, s2 = ORBmatcher._fv_struct(fv1), ORBmatcher._fv_struct(fv2)
+        rc = _lib.lib().orbm_search_for_triangulation(
+            kps1.data_ptr(), desc1.data_ptr(), n1.data_ptr(), p(has_mp1), p(u_right1), s1, kps2.data_ptr(),
+            desc2.data_ptr(), n2.data_ptr(), p(has_mp2), p(u_right2), s2, cap, ns, b, p(F12), ep.data_ptr(),
+            sf.ctypes.data, sg.ctypes.data, sf.size, int(bool(only_stereo)), int(bool(coarse)),
+            int(bool(check_orientation)), out["match12"].data_ptr(), out["nmatches"].data_ptr(), _stream(dev))
+        _lib.check(rc, "orbm_search_for_triangulation")
+        return out
+
+    @staticmethod
+    def distinctive_descriptors(pool, obs_off, obs_idx):
+        """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:367-401) batched.  pool [R,32] u8, obs_off [M+1] i32,
+        obs_idx [total] i32.  Returns (best [M] i32, median [M] i32)."""
+        import torch
+        m = obs_off.shape[0] - 1
+        best = torch.empty((m,), dtype=torch.int32, device=pool.device)
+        med = torch.empty((m,), dtype=torch.int32, device=pool.device)
+        rc = _lib.lib().orbm_distinctive_descriptors(pool.data_ptr(), obs_off.data_ptr(), obs_idx.data_ptr(), m,
+                                                     best.data_ptr(), med.data_ptr(), _stream(pool.device))
+        _lib.check(rc, "orbm_distinctive_descriptors")
+        return best, med
+
+
+class ORBVocabulary:
+    """Device-resident DBoW2 vocabulary tree (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h) as flat arrays and its
+    transform() (:1127-1259).  Arrays: child_off [nnodes+1] i32, child_idx i32, node_desc [nnodes,32] u8,
+    node_word [nnodes] i32, node_weight [nnodes] f64; node 0 is the root; L = tree depth."""
+
+    def __init__(self, child_off, child_idx, node_desc, node_word, node_weight, L, device="cuda:0"):
+        import torch
+        t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a, dt)).to(device)
+        self.child_off, self.child_idx = t(child_off, np.int32), t(child_idx, np.int32)
+        self.node_desc, self.node_word = t(node_desc, np.uint8), t(node_word, np.int32)
+        self.node_weight = t(node_weight, np.float64)
+        self.L, self.device = int(L), device
+        self._s = _lib.OrbmVocabulary(self.child_off.data_ptr(), self.child_idx.data_ptr(), self.node_desc.data_ptr(),
+                                      self.node_word.data_ptr(), self.node_weight.data_ptr(),
+                                      self.node_word.shape[0], self.L)
+
+    def transform(self, desc, n, levelsup=4, node_stride=None):
+        """desc [B,cap,32] u8, n [B] i32 (CUDA).  Returns dict(feat_word, feat_node [B,cap] i32, feat_weight
+        [B,cap] f64, fv (FeatureVector CSR dict), bow_word [B,cap] i32, bow_val [B,cap] f64, bow_n [B] i32)."""
+        import torch
+        b, cap = desc.shape[0], desc.shape[1]
+        dev = desc.device
+        ns = cap if node_stride is None else int(node_stride)
+        fv = ORBmatcher.feature_vector_alloc(b, cap, ns, dev)
+        out = {"feat_word": torch.zeros((b, cap), dtype=torch.int32, device=dev),
+               "feat_node": torch.zeros((b, cap), dtype=torch.int32, device=dev),
+               "feat_weight": torch.zeros((b, cap), dtype=torch.float64, device=dev),
+               "fv": fv,
+               "bow_word": torch.zeros((b, cap), dtype=torch.int32, device=dev),
+               "bow_val": torch.zeros((b, cap), dtype=torch.float64, device=dev),
+               "bow_n": torch.zeros((b,), dtype=torch.int32, device=dev)}
+        rc = _lib.lib().orbm_bow_transform(self._s, desc.data_ptr(), n.data_ptr(), cap, b, int(levelsup),
+                                           out["feat_word"].data_ptr(), out["feat_node"].data_ptr(),
+                                           out["feat_weight"].data_ptr(), ORBmatcher._fv_struct(fv), ns,
+                                           out["bow_word"].data_ptr(), out["bow_val"].data_ptr(),
+                                           out["bow_n"].data_ptr(), _stream(dev))
+        _lib.check(rc, "orbm_bow_transform")
+        return out
