@@ -233,6 +233,23 @@ int orbm_search_by_projection(const orbx_keypoint* d_kps, const uint8_t* d_desc,
                               int32_t* d_match, int32_t* d_feat_query, int32_t* d_nmatches,
                               void* stream);
 
+/* The same with the acceptance threshold as a parameter (th_dist replaces TH_HIGH = 100).  With
+ * ORBM_PROJ_LASTFRAME, every query flagged 3, d_feat_locked = "CurrentFrame.mvpMapPoints[j] != NULL" and
+ * no stereo inputs this is SearchByProjection(Frame&, KeyFrame*, const set<MapPoint*>&, th, ORBdist)
+ * (ORBmatcher.cc:1889-2010, relocalisation: octave band [l-1, l+1], best <= ORBdist = 100 or 64); queries
+ * the host drops (bad point, in sAlreadyFound, outside the image or the distance range) clear bit 0. */
+int orbm_search_by_projection_th(const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n,
+                                 int kp_stride, int batch, const int32_t* d_cell_off,
+                                 const int32_t* d_cell_idx, float min_x, float max_x, float min_y,
+                                 float max_y, const float* d_u_right, const uint8_t* d_feat_locked,
+                                 const float* d_qx, const float* d_qy, const float* d_qr,
+                                 const int8_t* d_qmin_level, const int8_t* d_qmax_level,
+                                 const uint8_t* d_qdesc, const int32_t* d_nq, int q_stride,
+                                 const float* d_q_ur, const uint8_t* d_q_flags, const float* d_q_angle,
+                                 int mode, float nn_ratio, int check_orientation, int th_dist,
+                                 void* d_scratch, int32_t* d_match, int32_t* d_feat_query,
+                                 int32_t* d_nmatches, void* stream);
+
 /* Hamming stage of Frame::ComputeStereoMatches (Frame.cc:811-894): per left keypoint the best
  * right keypoint in its row band (|dy| within 2*scale[octR], |octave diff|<=1,
  * uL-max_d <= uR <= uL), first minimum below TH_HIGH=100 wins, candidates visited in

@@ -264,7 +264,7 @@ def stereo_matches(kps_l, desc_l, kps_r, desc_r, scale_factors, inv_scale_factor
 
 def search_by_projection(kps, desc, bounds, qx, qy, qr, qmin, qmax, qdesc, mode, nn_ratio=0.6,
                          check_orientation=True, u_right=None, feat_locked=None, q_ur=None, q_flags=None,
-                         q_angle=None):
+                         q_angle=None, th_dist=100):
     """ORBmatcher::SearchByProjection (mode 0: MapPoints variant, mode 1: last-frame variant), one frame.
     Returns (match [nq], feat_query [n], nmatches)."""
     kps = np.ascontiguousarray(kps)
@@ -282,12 +282,12 @@ def search_by_projection(kps, desc, bounds, qx, qy, qr, qmin, qmax, qdesc, mode,
     L.oracle_search_by_projection.restype = C.c_int
     L.oracle_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float,
                                               C.c_float] + [C.c_void_p] * 8 + [C.c_int] + [C.c_void_p] * 3 + \
-                                             [C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+                                             [C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     nm = L.oracle_search_by_projection(_p(kps), pp(args["desc"]), n, bounds[0], bounds[1], bounds[2], bounds[3],
                                        pp(args["u_right"]), pp(args["feat_locked"]), pp(args["qx"]), pp(args["qy"]),
                                        pp(args["qr"]), pp(args["qmin"]), pp(args["qmax"]), pp(args["qdesc"]), nq,
                                        pp(args["q_ur"]), pp(args["q_flags"]), pp(args["q_angle"]), int(mode),
-                                       float(nn_ratio), int(bool(check_orientation)), _p(match), _p(fq))
+                                       float(nn_ratio), int(bool(check_orientation)), int(th_dist), _p(match), _p(fq))
     return match, fq, nm
 
 

@@ -958,9 +958,10 @@ int oracle_search_by_projection(const void* kps_v, const uint8_t* desc, int n, f
                                 const float* qx, const float* qy, const float* qr, const int8_t* qmin,
                                 const int8_t* qmax, const uint8_t* qdesc, int nq, const float* q_ur,
                                 const uint8_t* q_flags, const float* q_angle, int mode, float nnratio,
-                                int check_orientation, int* match, int* feat_query) {
+                                int check_orientation, int th_dist, int* match, int* feat_query) {
   const KeyPoint* kps = (const KeyPoint*)kps_v;
-  const int COLS = 64, ROWS = 48, TH_HIGH = 100, HISTO_LENGTH = 30;
+  const int COLS = 64, ROWS = 48, HISTO_LENGTH = 30;
+  const int TH_HIGH = th_dist;  // 100, or ORBdist in the relocalisation variant (ORBmatcher.cc:1961)
   const float wInv = static_cast<float>(COLS) / static_cast<float>(mnMaxX - mnMinX);
   const float hInv = static_cast<float>(ROWS) / static_cast<float>(mnMaxY - mnMinY);
   std::vector<std::vector<int>> grid(COLS * ROWS);

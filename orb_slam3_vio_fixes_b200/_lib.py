@@ -37,7 +37,7 @@ SYMBOLS = [
     "orbx_create", "orbx_destroy", "orbx_max_keypoints", "orbx_extract", "orbx_extract_batch_device",
     "orbx_extract_batch_host", "orbx_last_outputs_device", "orbx_get_pyramid", "orbx_pyramid_device", "orbx_level_size",
     "orbx_get_scale_tables", "orbx_stage_times", "orbx_debug_level_keypoints", "orbx_debug_octree", "orbm_argmin2_csr", "orbm_grid_build",
-    "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
+    "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_search_by_projection_th", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
     "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
     "orbx_version", "orbx_last_error",
 ]
@@ -108,6 +108,8 @@ def lib():
     L.orbm_stereo_rowband.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, vp, i32, f32, vp, vp, vp]
     L.orbm_search_by_projection.argtypes = [vp, vp, vp, i32, i32, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp, vp,
                                             vp, vp, i32, vp, vp, vp, i32, f32, i32, vp, vp, vp, vp, vp]
+    L.orbm_search_by_projection_th.argtypes = [vp, vp, vp, i32, i32, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp,
+                                               vp, vp, vp, i32, vp, vp, vp, i32, f32, i32, i32, vp, vp, vp, vp, vp]
     L.orbm_stereo_refine.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp, vp, f32, f32, vp, vp, vp, vp, vp]
     L.orbm_rgbd_depth.argtypes = [vp, vp, vp, i32, i32, vp, sz, sz, i32, i32, f32, vp, vp, vp]
     L.orbm_knn2_dense.argtypes = [vp, i32, vp, i32, vp, vp, vp]

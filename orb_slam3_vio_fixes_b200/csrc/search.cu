@@ -23,7 +23,7 @@ struct ProjArgs {
   const float* u_right; const uint8_t* feat_locked;
   const float *qx, *qy, *qr; const int8_t *qmin, *qmax; const uint8_t* qdesc; const int32_t* nq; int q_stride;
   const float* q_ur; const uint8_t* q_flags; const float* q_angle;
-  int mode; float nnratio; int check_orientation;
+  int mode; float nnratio; int check_orientation; int th_dist;
 };
 
 struct ProjQuery {
@@ -196,7 +196,7 @@ k_proj_resolve(const ProjArgs A, const ProjCand* __restrict__ cand, int32_t* __r
     };
     // acceptance of the scored result (re-evaluated after a rescan)
     auto accept_of = [&](int a1, int a2, int e1, int e2) {
-      bool acc = a1 >= 0 && e1 <= 100;  // TH_HIGH
+      bool acc = a1 >= 0 && e1 <= A.th_dist;  // TH_HIGH (or ORBdist, ORBmatcher.cc:1961)
       if (acc && ratio_mode) {
         // bestLevel==bestLevel2 && bestDist > mfNNratio*bestDist2 -> rejected (:123-127); no second: levels differ
         const int lv1 = k[a1].octave, lv2 = a2 >= 0 ? k[a2].octave : -1;
@@ -316,19 +316,20 @@ k_proj_resolve(const ProjArgs A, const ProjCand* __restrict__ cand, int32_t* __r
   if (lane == 0) nmatches[f] = total;
 }
 
-extern "C" int orbm_search_by_projection(
+extern "C" int orbm_search_by_projection_th(
     const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n, int kp_stride, int batch,
     const int32_t* d_cell_off, const int32_t* d_cell_idx, float min_x, float max_x, float min_y, float max_y,
     const float* d_u_right, const uint8_t* d_feat_locked, const float* d_qx, const float* d_qy, const float* d_qr,
     const int8_t* d_qmin_level, const int8_t* d_qmax_level, const uint8_t* d_qdesc, const int32_t* d_nq,
     int q_stride, const float* d_q_ur, const uint8_t* d_q_flags, const float* d_q_angle, int mode, float nn_ratio,
-    int check_orientation, void* d_scratch, int32_t* d_match, int32_t* d_feat_query, int32_t* d_nmatches,
+    int check_orientation, int th_dist, void* d_scratch, int32_t* d_match, int32_t* d_feat_query, int32_t* d_nmatches,
     void* stream) {
   if (!d_kps || !d_desc || !d_n || !d_cell_off || !d_cell_idx || !d_qx || !d_qy || !d_qr || !d_qmin_level ||
       !d_qmax_level || !d_qdesc || !d_nq || !d_scratch || !d_match || !d_feat_query || !d_nmatches || batch < 1 ||
       kp_stride < 1 || q_stride < 1 || !(max_x > min_x) || !(max_y > min_y))
     return ORBX_E_INVALID;
   if (mode != ORBM_PROJ_MAPPOINTS && mode != ORBM_PROJ_LASTFRAME) return ORBX_E_INVALID;
+  if (th_dist < 0 || th_dist > 256) return ORBX_E_INVALID;
   if (mode == ORBM_PROJ_LASTFRAME && check_orientation && !d_q_angle) return ORBX_E_INVALID;
   const size_t smem = 2 * (size_t)((kp_stride + 31) / 32) * sizeof(uint32_t);
   if (smem > 40 * 1024) return ORBX_E_INVALID;  // > 160k features per frame
@@ -340,10 +341,25 @@ extern "C" int orbm_search_by_projection(
   A.u_right = d_u_right; A.feat_locked = d_feat_locked;
   A.qx = d_qx; A.qy = d_qy; A.qr = d_qr; A.qmin = d_qmin_level; A.qmax = d_qmax_level; A.qdesc = d_qdesc;
   A.nq = d_nq; A.q_stride = q_stride; A.q_ur = d_q_ur; A.q_flags = d_q_flags; A.q_angle = d_q_angle;
-  A.mode = mode; A.nnratio = nn_ratio; A.check_orientation = check_orientation;
+  A.mode = mode; A.nnratio = nn_ratio; A.check_orientation = check_orientation; A.th_dist = th_dist;
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grd((q_stride + PS_THREADS - 1) / PS_THREADS, batch);
   k_proj_score<<<grd, PS_THREADS, 0, st>>>(A, (ProjCand*)d_scratch);
   k_proj_resolve<<<batch, 32, smem, st>>>(A, (const ProjCand*)d_scratch, d_match, d_feat_query, d_nmatches);
   return cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
+}
+
+extern "C" int orbm_search_by_projection(
+    const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n, int kp_stride, int batch,
+    const int32_t* d_cell_off, const int32_t* d_cell_idx, float min_x, float max_x, float min_y, float max_y,
+    const float* d_u_right, const uint8_t* d_feat_locked, const float* d_qx, const float* d_qy, const float* d_qr,
+    const int8_t* d_qmin_level, const int8_t* d_qmax_level, const uint8_t* d_qdesc, const int32_t* d_nq,
+    int q_stride, const float* d_q_ur, const uint8_t* d_q_flags, const float* d_q_angle, int mode, float nn_ratio,
+    int check_orientation, void* d_scratch, int32_t* d_match, int32_t* d_feat_query, int32_t* d_nmatches,
+    void* stream) {
+  return orbm_search_by_projection_th(d_kps, d_desc, d_n, kp_stride, batch, d_cell_off, d_cell_idx, min_x, max_x,
+                                      min_y, max_y, d_u_right, d_feat_locked, d_qx, d_qy, d_qr, d_qmin_level,
+                                      d_qmax_level, d_qdesc, d_nq, q_stride, d_q_ur, d_q_flags, d_q_angle, mode,
+                                      nn_ratio, check_orientation, 100 /* TH_HIGH */, d_scratch, d_match,
+                                      d_feat_query, d_nmatches, stream);
 }

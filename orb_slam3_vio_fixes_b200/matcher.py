@@ -110,10 +110,10 @@ class ORBmatcher:
 
     @staticmethod
     def search_by_projection(kps, desc, n, grid, bounds, q, mode, nn_ratio=0.6, check_orientation=True,
-                             u_right=None, feat_locked=None):
+                             u_right=None, feat_locked=None, th_dist=100):
         """ORBmatcher::SearchByProjection as a whole function (ORBmatcher.cc:43-142 / :1676-1887, Nleft == -1).
         q: dict of CUDA tensors qx,qy,qr [B,Q] f32, qmin,qmax [B,Q] i8, qdesc [B,Q,32] u8, nq [B] i32 and
-        optionally q_ur [B,Q] f32, flags [B,Q] u8 (bit0 takes part, bit1 MapPoint has observations),
+        th_dist = TH_HIGH, or ORBdist of the relocalisation variant (ORBmatcher.cc:1889-2010); optionally q_ur [B,Q] f32, flags [B,Q] u8 (bit0 takes part, bit1 MapPoint has observations),
         angle [B,Q] f32.  Returns dict(match [B,Q] i32, feat_query [B,cap] i32, nmatches [B] i32)."""
         import torch
         b, cap = kps.shape[0], kps.shape[1]
@@ -124,12 +124,13 @@ class ORBmatcher:
                "feat_query": torch.empty((b, cap), dtype=torch.int32, device=dev),
                "nmatches": torch.empty((b,), dtype=torch.int32, device=dev)}
         p = lambda t: t.data_ptr() if t is not None else None
-        rc = _lib.lib().orbm_search_by_projection(
+        rc = _lib.lib().orbm_search_by_projection_th(
             kps.data_ptr(), desc.data_ptr(), n.data_ptr(), cap, b, grid[0].data_ptr(), grid[1].data_ptr(),
             float(bounds[0]), float(bounds[1]), float(bounds[2]), float(bounds[3]), p(u_right), p(feat_locked),
             q["qx"].data_ptr(), q["qy"].data_ptr(), q["qr"].data_ptr(), q["qmin"].data_ptr(), q["qmax"].data_ptr(),
             q["qdesc"].data_ptr(), q["nq"].data_ptr(), qs, p(q.get("q_ur")), p(q.get("flags")), p(q.get("angle")),
-            int(mode), float(nn_ratio), int(bool(check_orientation)), scratch.data_ptr(), out["match"].data_ptr(),
+            int(mode), float(nn_ratio), int(bool(check_orientation)), int(th_dist), scratch.data_ptr(),
+            out["match"].data_ptr(),
             out["feat_query"].data_ptr(), out["nmatches"].data_ptr(), _stream(dev))
         _lib.check(rc, "orbm_search_by_projection")
         return out

@@ -277,7 +277,7 @@ def _proj_queries(kq, dq, shift, th, sf, band, rng, dup=1, drop=0.0, unlocked=0.
     return q
 
 
-def _proj_run(oracle_mod, out, q_list, bounds, mode, nn_ratio, check_ori, u_right=None, feat_locked=None):
+def _proj_run(oracle_mod, out, q_list, bounds, mode, nn_ratio, check_ori, u_right=None, feat_locked=None, th_dist=100):
     import torch
     B, cap = out["kps"].shape[0], out["kps"].shape[1]
     Q = max(len(q["qx"]) for q in q_list)
@@ -298,7 +298,7 @@ def _proj_run(oracle_mod, out, q_list, bounds, mode, nn_ratio, check_ori, u_righ
     grid = ORBmatcher.grid_build(out["kps"], out["n"], bounds)
     res = ORBmatcher.search_by_projection(out["kps"], out["desc"], out["n"], grid, bounds, qt, mode, nn_ratio, check_ori,
                                           u_right=None if u_right is None else _t(u_right),
-                                          feat_locked=None if feat_locked is None else _t(feat_locked))
+                                          feat_locked=None if feat_locked is None else _t(feat_locked), th_dist=th_dist)
     kps = ORBextractor.kps_from_tensor(out["kps"])
     desc = out["desc"].cpu().numpy()
     n = out["n"].cpu().numpy()
@@ -309,13 +309,46 @@ def _proj_run(oracle_mod, out, q_list, bounds, mode, nn_ratio, check_ori, u_righ
             kps[f, :n[f]], desc[f, :n[f]], bounds, q["qx"], q["qy"], q["qr"], q["qmin"], q["qmax"], q["qdesc"], mode,
             nn_ratio, check_ori, u_right=None if u_right is None else u_right[f, :n[f]],
             feat_locked=None if feat_locked is None else feat_locked[f, :n[f]],
-            q_ur=q["q_ur"] if u_right is not None else None, q_flags=q["flags"], q_angle=q["angle"])
+            q_ur=q["q_ur"] if u_right is not None else None, q_flags=q["flags"], q_angle=q["angle"], th_dist=th_dist)
         m = len(q["qx"])
         assert np.array_equal(mt[f, :m], rm), (f, np.nonzero(mt[f, :m] != rm)[0][:10])
         assert np.array_equal(fq[f, :n[f]], rfq)
         assert nm[f] == rnm
         tot += rnm
     return tot, mt, fq
+
+
+@pytest.mark.parametrize("orb_dist", [100, 64, 30])
+def test_search_by_projection_keyframe_relocalisation(oracle_mod, orb_dist):
+    """SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (ORBmatcher.cc:1889-2010): keyframe
+    MapPoints projected into the current frame, band [l-1,l+1], every non-null mvpMapPoints entry blocks its
+    feature, best <= ORBdist, rotation histogram.  th = 10 / 3 as Tracking::Relocalization uses them."""
+    from bench import shifts_for
+    B = 3
+    frames = S.make_frames("C1", B)
+    ex = ORBextractor(1000, max_batch=B, **ORB)
+    out = _extract_batch(ex, frames, (0, 1000))
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    n = out["n"].cpu().numpy()
+    sf = ex.GetScaleFactors()
+    sh = shifts_for(0, B)
+    rng = np.random.default_rng(13)
+    bounds = (0.0, 752.0, 0.0, 480.0)
+    cap = out["kps"].shape[1]
+    for th in (10, 3):
+        ql = []
+        for f in range(B):
+            s = (f - 1) % B
+            # dup=2: the second copy of every MapPoint finds its best feature taken; drop = in sAlreadyFound / bad
+            q = _proj_queries(kps[s, :n[s]], desc[s, :n[s]], sh[f], th, sf, (-1, 1), rng, dup=2, drop=0.2)
+            q["flags"] = (q["flags"] | 2).astype(np.uint8) & np.where(q["flags"] & 1, 3, 2).astype(np.uint8)
+            ql.append(q)
+        locked = (rng.random((B, cap)) < 0.25).astype(np.uint8)   # features already holding a MapPoint
+        tot, mt, fq = _proj_run(oracle_mod, out, ql, bounds, 1, 0.9, True, feat_locked=locked, th_dist=orb_dist)
+        assert tot > (100 if orb_dist == 30 else 600)
+        for f in range(B):  # nothing is ever written to a feature that was occupied on entry
+            assert np.all(fq[f, :n[f]][locked[f, :n[f]] != 0] == -1)
 
 
 @pytest.mark.parametrize("check_ori", [True, False])
