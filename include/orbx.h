@@ -191,6 +191,20 @@ int orbm_search_area(const orbx_keypoint* d_kps, const uint8_t* d_desc, const in
                      const int8_t* d_qmax_level, const uint8_t* d_qdesc, const int32_t* d_nq,
                      int q_stride, int batch, int tie_rule, orbm_result* d_out, void* stream);
 
+/* Candidate scoring of ORBmatcher::Fuse (ORBmatcher.cc:1148-1338 and the Sim3 twin :1340-1455): per
+ * projected MapPoint (d_qx,d_qy = uv, d_q_ur = ur, d_qr = th*scale[l], d_qlevel = nPredictedLevel,
+ * descriptor) KeyFrame::GetFeaturesInArea (KeyFrame.cc:704-748) on the orbm_grid_build CSR, octave in
+ * [l-1, l], chi-square gate e2*invLevelSigma2[octave] <= 5.99 (7.8 with d_u_right[j] >= 0), first
+ * minimum.  d_out[q].best_idx/best_dist feed the host's `bestDist<=TH_LOW` replace-or-add bookkeeping,
+ * which mutates the map and stays on the host.  Queries are independent. */
+int orbm_fuse_candidates(const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n,
+                         int kp_stride, const int32_t* d_cell_off, const int32_t* d_cell_idx,
+                         float min_x, float max_x, float min_y, float max_y, const float* d_u_right,
+                         const float* inv_level_sigma2_host, int nlevels, const float* d_qx,
+                         const float* d_qy, const float* d_qr, const float* d_q_ur,
+                         const int8_t* d_qlevel, const uint8_t* d_qdesc, const int32_t* d_nq,
+                         int q_stride, int batch, orbm_result* d_out, void* stream);
+
 /* Window queries of SearchByProjection(Frame&, const Frame&, th, bMono) (ORBmatcher.cc:1676-1768)
  * for a pure image-plane shift: query i of frame f is keypoint i of frame d_src_frame[f] moved by
  * d_shift_xy[f] = (dx,dy), radius th*scale[octave], octave band [octave+band_lo, octave+band_hi],
@@ -362,6 +376,19 @@ int orbm_bow_transform(const orbm_vocabulary* voc, const uint8_t* d_desc, const 
 int orbm_distinctive_descriptors(const uint8_t* d_desc_pool, const int32_t* d_obs_off,
                                  const int32_t* d_obs_idx, int n_points, int32_t* d_best,
                                  int32_t* d_median, void* stream);
+
+/* ORBmatcher::SearchForInitialization (ORBmatcher.cc:648-763), batched over frame pairs (F1, F2):
+ * level-0 keypoints of F1, window `window_size` around d_prev_matched[i] (vbPrevMatched, [batch]
+ * [kp_stride][2], updated in place like the reference does at :757-759) on F2's orbm_grid_build CSR,
+ * vMatchedDistance / vnMatches21 stealing rule, TH_LOW, ratio, rotation histogram (stale entries of
+ * stolen matches keep counting, as in the reference).  d_match12 = vnMatches12; d_scratch: 2 * batch *
+ * kp_stride int32. */
+int orbm_search_for_initialization(
+    const orbx_keypoint* d_kps1, const uint8_t* d_desc1, const int32_t* d_n1, const orbx_keypoint* d_kps2,
+    const uint8_t* d_desc2, const int32_t* d_n2, int kp_stride, int batch, const int32_t* d_cell_off2,
+    const int32_t* d_cell_idx2, float min_x, float max_x, float min_y, float max_y, float* d_prev_matched,
+    int window_size, float nn_ratio, int check_orientation, int32_t* d_match12, int32_t* d_scratch,
+    int32_t* d_nmatches, void* stream);
 
 /* Library / build identification. */
 const char* orbx_version(void);

@@ -291,6 +291,43 @@ def search_by_projection(kps, desc, bounds, qx, qy, qr, qmin, qmax, qdesc, mode,
     return match, fq, nm
 
 
+def fuse_candidates(kps, desc, bounds, inv_sigma2, qx, qy, qr, qlevel, qdesc, u_right=None, q_ur=None):
+    """Candidate scoring of ORBmatcher::Fuse, one keyframe.  Returns (best_idx, best_dist)."""
+    kps = np.ascontiguousarray(kps)
+    f32 = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+    d, qd = np.ascontiguousarray(desc, np.uint8), np.ascontiguousarray(qdesc, np.uint8)
+    ur, sg, x, y, r, qu = f32(u_right), f32(inv_sigma2), f32(qx), f32(qy), f32(qr), f32(q_ur)
+    lv = np.ascontiguousarray(qlevel, np.int8)
+    pp = lambda a: None if a is None else _p(a)
+    nq = len(x)
+    bi, bd = np.zeros(nq, np.int32), np.zeros(nq, np.int32)
+    L = lib()
+    L.oracle_fuse_candidates.restype = None
+    L.oracle_fuse_candidates.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float] + \
+                                        [C.c_void_p] * 8 + [C.c_int, C.c_void_p, C.c_void_p]
+    L.oracle_fuse_candidates(_p(kps), _p(d), kps.size, bounds[0], bounds[1], bounds[2], bounds[3], pp(ur), _p(sg),
+                             _p(x), _p(y), _p(r), pp(qu), _p(lv), _p(qd), nq, _p(bi), _p(bd))
+    return bi, bd
+
+
+def search_for_initialization(kps1, desc1, kps2, desc2, bounds, prev_matched, window_size=100, nn_ratio=0.9,
+                              check_orientation=True):
+    """ORBmatcher::SearchForInitialization.  Returns (match12, nmatches, updated prev_matched)."""
+    kps1, kps2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+    d1, d2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    pm = np.array(prev_matched, np.float32, copy=True).reshape(-1, 2)
+    m12 = np.zeros(kps1.size, np.int32)
+    L = lib()
+    L.oracle_search_for_initialization.restype = C.c_int
+    L.oracle_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                                   C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_int,
+                                                   C.c_float, C.c_int, C.c_void_p]
+    nm = L.oracle_search_for_initialization(_p(kps1), _p(d1), kps1.size, _p(kps2), _p(d2), kps2.size, bounds[0],
+                                            bounds[1], bounds[2], bounds[3], _p(pm), int(window_size),
+                                            float(nn_ratio), int(bool(check_orientation)), _p(m12))
+    return m12, nm, pm
+
+
 def rgbd_depth(kps, kps_un, depth_img, mbf):
     """Frame::ComputeStereoFromRGBD.  Returns (uRight, depth)."""
     kps = np.ascontiguousarray(kps)

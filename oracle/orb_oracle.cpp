@@ -930,6 +930,98 @@ int oracle_stereo_matches(const void* kpsL_v, const uint8_t* descL, int nL, cons
   return kept;
 }
 
+// Candidate scoring of ORBmatcher::Fuse (ORBmatcher.cc:1148-1338): KeyFrame::GetFeaturesInArea
+// (KeyFrame.cc:704-748) then the loop :1258-1308 (octave in [l-1,l], chi-square gate, first minimum).
+// best_idx/best_dist per query (-1 / 256 when no candidate passes).
+void oracle_fuse_candidates(const void* kps_v, const uint8_t* desc, int n, float mnMinX, float mnMaxX,
+                            float mnMinY, float mnMaxY, const float* u_right, const float* invLevelSigma2,
+                            const float* qx, const float* qy, const float* qr, const float* q_ur,
+                            const int8_t* qlevel, const uint8_t* qdesc, int nq, int* best_idx, int* best_dist) {
+  const KeyPoint* kps = (const KeyPoint*)kps_v;
+  std::vector<int> none(nq, -1), off(nq + 1), idx;
+  int tot = oracle_grid_queries(kps_v, n, mnMinX, mnMaxX, mnMinY, mnMaxY, qx, qy, qr, none.data(), none.data(), nq,
+                                off.data(), nullptr, 0);
+  idx.resize(tot + 1);
+  oracle_grid_queries(kps_v, n, mnMinX, mnMaxX, mnMinY, mnMaxY, qx, qy, qr, none.data(), none.data(), nq, off.data(),
+                      idx.data(), tot);
+  for (int q = 0; q < nq; q++) {
+    const int nPredictedLevel = qlevel[q];
+    int bestDist = 256, bestIdx = -1;
+    for (int c = off[q]; c < off[q + 1]; c++) {
+      const int i = idx[c];
+      const KeyPoint& kp = kps[i];
+      const int kpLevel = kp.octave;
+      if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+      if (u_right && u_right[i] >= 0) {
+        const float ex = qx[q] - kp.x, ey = qy[q] - kp.y, er = q_ur[q] - u_right[i];
+        const float e2 = ex * ex + ey * ey + er * er;
+        if (e2 * invLevelSigma2[kpLevel] > 7.8) continue;
+      } else {
+        const float ex = qx[q] - kp.x, ey = qy[q] - kp.y;
+        const float e2 = ex * ex + ey * ey;
+        if (e2 * invLevelSigma2[kpLevel] > 5.99) continue;
+      }
+      const int dist = DescriptorDistance(qdesc + (size_t)q * 32, desc + (size_t)i * 32);
+      if (dist < bestDist) { bestDist = dist; bestIdx = i; }
+    }
+    best_idx[q] = bestIdx; best_dist[q] = bestDist;
+  }
+}
+
+static inline int rot_bin(float a1, float a2);
+static void ComputeThreeMaxima(const std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
+// ORBmatcher::SearchForInitialization (ORBmatcher.cc:648-763) on flat arrays; prev_matched ([n1][2]) is
+// vbPrevMatched and is updated in place.  Returns nmatches; match12 = vnMatches12.
+int oracle_search_for_initialization(const void* kps1_v, const uint8_t* desc1, int n1, const void* kps2_v,
+                                     const uint8_t* desc2, int n2, float mnMinX, float mnMaxX, float mnMinY,
+                                     float mnMaxY, float* prev_matched, int windowSize, float nnratio,
+                                     int check_orientation, int* match12) {
+  const KeyPoint* kps1 = (const KeyPoint*)kps1_v;
+  const KeyPoint* kps2 = (const KeyPoint*)kps2_v;
+  const int TH_LOW = 50, HISTO_LENGTH = 30;
+  int nmatches = 0;
+  for (int i = 0; i < n1; i++) match12[i] = -1;
+  std::vector<int> rotHist[30];
+  std::vector<int> vMatchedDistance(n2, INT_MAX), vnMatches21(n2, -1);
+  std::vector<int> off(2), idx(n2 + 1);
+  for (int i1 = 0; i1 < n1; i1++) {
+    const int level1 = kps1[i1].octave;
+    if (level1 > 0) continue;
+    const float x = prev_matched[2 * i1], y = prev_matched[2 * i1 + 1], r = (float)windowSize;
+    const int tot = oracle_grid_queries(kps2_v, n2, mnMinX, mnMaxX, mnMinY, mnMaxY, &x, &y, &r, &level1, &level1, 1,
+                                        off.data(), idx.data(), n2);
+    if (tot == 0) continue;
+    int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+    for (int c = 0; c < tot; c++) {
+      const int i2 = idx[c];
+      const int dist = DescriptorDistance(desc1 + (size_t)i1 * 32, desc2 + (size_t)i2 * 32);
+      if (vMatchedDistance[i2] <= dist) continue;
+      if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+      else if (dist < bestDist2) { bestDist2 = dist; }
+    }
+    if (bestDist <= TH_LOW) {
+      if (bestDist < (float)bestDist2 * nnratio) {
+        if (vnMatches21[bestIdx2] >= 0) { match12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+        match12[i1] = bestIdx2; vnMatches21[bestIdx2] = i1; vMatchedDistance[bestIdx2] = bestDist;
+        nmatches++;
+        if (check_orientation) rotHist[rot_bin(kps1[i1].angle, kps2[bestIdx2].angle)].push_back(i1);
+      }
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int idx1 : rotHist[i])
+        if (match12[idx1] >= 0) { match12[idx1] = -1; nmatches--; }
+    }
+  }
+  for (int i1 = 0; i1 < n1; i1++)
+    if (match12[i1] >= 0) { prev_matched[2 * i1] = kps2[match12[i1]].x; prev_matched[2 * i1 + 1] = kps2[match12[i1]].y; }
+  return nmatches;
+}
+
 // ORBmatcher::SearchByProjection, whole function, single-camera case (Nleft == -1), on flat arrays.
 //   mode 0 = (Frame&, const vector<MapPoint*>&, th, ...)      ORBmatcher.cc:43-142  (best + second, ratio test)
 //   mode 1 = (Frame& CurrentFrame, const Frame& LastFrame...) ORBmatcher.cc:1676-1887 (best only, rotation histogram)

@@ -522,3 +522,124 @@ extern "C" int orbm_distinctive_descriptors(const uint8_t* d_desc_pool, const in
       d_desc_pool, d_obs_off, d_obs_idx, n_points, d_best, d_median);
   return cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// ORBmatcher::SearchForInitialization (ORBmatcher.cc:648-763).  The loop is sequential through
+// vMatchedDistance / vnMatches21 (a later query may steal a feature from an earlier one), and it only runs
+// while the monocular map is being initialised, so one warp walks the level-0 keypoints of F1 in order and
+// spreads each query's window candidates over its lanes.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32)
+k_search_init(const OrbxKeyPointDev* __restrict__ k1, const uint8_t* __restrict__ d1,
+              const int32_t* __restrict__ n1_arr, const OrbxKeyPointDev* __restrict__ k2,
+              const uint8_t* __restrict__ d2, const int32_t* __restrict__ n2_arr, int kp_stride,
+              const int32_t* __restrict__ cell_off, const int32_t* __restrict__ cell_idx, float min_x, float min_y,
+              float winv, float hinv, float* __restrict__ prev_matched, float window, float nnratio,
+              int check_orientation, int32_t* __restrict__ match12, int32_t* __restrict__ match21,
+              int32_t* __restrict__ matched_dist, int32_t* __restrict__ nmatches_out) {
+  __shared__ int hist[30];
+  const int lane = threadIdx.x, p = blockIdx.x;
+  const size_t fb = (size_t)p * kp_stride;
+  const int n1 = n1_arr[p], n2 = n2_arr[p];
+  const int32_t* off = cell_off + (size_t)p * (GRID_CELLS + 1);
+  const int32_t* idx = cell_idx + fb;
+  volatile int32_t* m12 = match12 + fb;
+  volatile int32_t* m21 = match21 + fb;
+  volatile int32_t* md = matched_dist + fb;
+  if (lane < 30) hist[lane] = 0;
+  for (int i = lane; i < n1; i += 32) m12[i] = -1;
+  for (int i = lane; i < n2; i += 32) { m21[i] = -1; md[i] = 0x7fffffff; }
+  __syncwarp();
+  const float r = window;
+  for (int i1 = 0; i1 < n1; i1++) {
+    const OrbxKeyPointDev kp1 = k1[fb + i1];
+    if (kp1.octave > 0) continue;
+    const float x = prev_matched[(fb + i1) * 2], y = prev_matched[(fb + i1) * 2 + 1];
+    const int nMinCellX = max(0, (int)floorf(f_mul(f_sub(f_sub(x, min_x), r), winv)));
+    const int nMaxCellX = min(FRAME_GRID_COLS - 1, (int)ceilf(f_mul(f_add(f_sub(x, min_x), r), winv)));
+    const int nMinCellY = max(0, (int)floorf(f_mul(f_sub(f_sub(y, min_y), r), hinv)));
+    const int nMaxCellY = min(FRAME_GRID_ROWS - 1, (int)ceilf(f_mul(f_add(f_sub(y, min_y), r), hinv)));
+    if (!(nMinCellX < FRAME_GRID_COLS && nMaxCellX >= 0 && nMinCellY < FRAME_GRID_ROWS && nMaxCellY >= 0)) continue;
+    const Desc256 dq = load_desc(d1 + (fb + i1) * 32);
+    Top2 t;
+    int seq = 0;
+    for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
+      const int e0 = off[ix * FRAME_GRID_ROWS + nMinCellY], e1 = off[ix * FRAME_GRID_ROWS + nMaxCellY + 1];
+      for (int e = e0 + lane; e < e1; e += 32) {
+        const int j = idx[e];
+        const OrbxKeyPointDev kp2 = k2[fb + j];
+        if (kp2.octave != 0) continue;  // GetFeaturesInArea(..., level1, level1) with level1 == 0
+        if (!(fabsf(f_sub(kp2.x, x)) < r && fabsf(f_sub(kp2.y, y)) < r)) continue;
+        const int dist = hamming(dq, load_desc(d2 + (fb + j) * 32));
+        if (md[j] <= dist) continue;    // :689
+        t.push(make_key(dist, (seq + e - e0) & 0xFFFFF, ORBM_TIE_FIRST_MIN), j);
+      }
+      seq += e1 - e0;
+    }
+    warp_top2(t);
+    if (t.i1 < 0) continue;
+    const int bestDist = (int)(t.k1 >> 20);
+    const float second = t.i2 >= 0 ? (float)(int)(t.k2 >> 20) : 2147483648.0f;  // (float)INT_MAX
+    if (bestDist <= 50 && (float)bestDist < f_mul(second, nnratio)) {
+      const int j = t.i1;
+      if (lane == 0) {
+        const int old = m21[j];
+        if (old >= 0) m12[old] = -1;  // a stolen feature: the earlier match is dropped (:709-713)
+        m12[i1] = j; m21[j] = i1; md[j] = bestDist;
+        if (check_orientation) hist[bow_rot_bin(kp1.angle, k2[fb + j].angle)]++;
+      }
+    }
+    __syncwarp();
+  }
+  // nmatches bookkeeping: count what is live now (every steal did nmatches-- and nmatches++)
+  __syncwarp();
+  int live = 0;
+  for (int i = lane; i < n1; i += 32) live += m12[i] >= 0;
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    {
+      int max1 = 0, max2 = 0, max3 = 0;
+      for (int i = 0; i < 30; i++) {
+        const int s = hist[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+      }
+      if ((float)max2 < f_mul(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+      else if ((float)max3 < f_mul(0.1f, (float)max1)) { ind3 = -1; }
+    }
+    for (int i = lane; i < n1; i += 32) {
+      const int m = m12[i];
+      if (m < 0) continue;
+      const int bin = bow_rot_bin(k1[fb + i].angle, k2[fb + m].angle);
+      if (bin != ind1 && bin != ind2 && bin != ind3) { m12[i] = -1; live--; }
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) live += __shfl_xor_sync(FULLMASK, live, o);
+  if (lane == 0) nmatches_out[p] = live;
+  // Update prev matched (:757-759)
+  for (int i = lane; i < n1; i += 32) {
+    const int m = m12[i];
+    if (m >= 0) { prev_matched[(fb + i) * 2] = k2[fb + m].x; prev_matched[(fb + i) * 2 + 1] = k2[fb + m].y; }
+  }
+}
+
+extern "C" int orbm_search_for_initialization(
+    const orbx_keypoint* d_kps1, const uint8_t* d_desc1, const int32_t* d_n1, const orbx_keypoint* d_kps2,
+    const uint8_t* d_desc2, const int32_t* d_n2, int kp_stride, int batch, const int32_t* d_cell_off2,
+    const int32_t* d_cell_idx2, float min_x, float max_x, float min_y, float max_y, float* d_prev_matched,
+    int window_size, float nn_ratio, int check_orientation, int32_t* d_match12, int32_t* d_scratch,
+    int32_t* d_nmatches, void* stream) {
+  if (!d_kps1 || !d_desc1 || !d_n1 || !d_kps2 || !d_desc2 || !d_n2 || kp_stride < 1 || batch < 1 || !d_cell_off2 ||
+      !d_cell_idx2 || !(max_x > min_x) || !(max_y > min_y) || !d_prev_matched || !d_match12 || !d_scratch ||
+      !d_nmatches)
+    return ORBX_E_INVALID;
+  const float winv = (float)FRAME_GRID_COLS / (max_x - min_x), hinv = (float)FRAME_GRID_ROWS / (max_y - min_y);
+  k_search_init<<<batch, 32, 0, (cudaStream_t)stream>>>(
+      (const OrbxKeyPointDev*)d_kps1, d_desc1, d_n1, (const OrbxKeyPointDev*)d_kps2, d_desc2, d_n2, kp_stride,
+      d_cell_off2, d_cell_idx2, min_x, min_y, winv, hinv, d_prev_matched, (float)window_size, nn_ratio,
+      check_orientation, d_match12, d_scratch, d_scratch + (size_t)batch * kp_stride, d_nmatches);
+  return cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
+}

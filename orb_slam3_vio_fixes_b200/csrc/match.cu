@@ -240,6 +240,79 @@ k_search_area_tq(const OrbxKeyPointDev* __restrict__ kps, const uint8_t* __restr
   out[qo] = res;
 }
 
+// ---- candidate scoring of ORBmatcher::Fuse (ORBmatcher.cc:1148-1338, :1340-1455) ---------------------
+// KeyFrame::GetFeaturesInArea (KeyFrame.cc:704-748, no octave band) + the in-loop gates: octave in
+// [l-1, l], chi-square reprojection gate (5.99 mono, 7.8 with a stereo coordinate), first minimum.
+struct InvSigmaTab { float s[ORBX_MAX_LEVELS]; };
+
+__global__ void __launch_bounds__(SA_THREADS)
+k_fuse_tq(const OrbxKeyPointDev* __restrict__ kps, const uint8_t* __restrict__ desc,
+          const int32_t* __restrict__ n_arr, int kp_stride, const int32_t* __restrict__ cell_off,
+          const int32_t* __restrict__ cell_idx, float min_x, float min_y, float winv, float hinv,
+          const float* __restrict__ u_right, InvSigmaTab inv_sigma2, const float* __restrict__ qx,
+          const float* __restrict__ qy, const float* __restrict__ qr, const float* __restrict__ q_ur,
+          const int8_t* __restrict__ qlevel, const uint8_t* __restrict__ qdesc,
+          const int32_t* __restrict__ nq_arr, int q_stride, orbm_result* __restrict__ out) {
+  const int f = blockIdx.y;
+  const int qi = blockIdx.x * SA_THREADS + threadIdx.x;
+  if (qi >= nq_arr[f]) return;
+  const size_t qo = (size_t)f * q_stride + qi;
+  const float x = qx[qo], y = qy[qo], r = qr[qo];
+  const float ur = q_ur ? q_ur[qo] : 0.0f;
+  const int level = qlevel[qo];
+  const OrbxKeyPointDev* k = kps + (size_t)f * kp_stride;
+  const uint8_t* dsc = desc + (size_t)f * kp_stride * 32;
+  const float* urk = u_right ? u_right + (size_t)f * kp_stride : nullptr;
+  const int32_t* off = cell_off + (size_t)f * (GRID_CELLS + 1);
+  const int32_t* idx = cell_idx + (size_t)f * kp_stride;
+  const int nMinCellX = max(0, (int)floorf(f_mul(f_sub(f_sub(x, min_x), r), winv)));
+  const int nMaxCellX = min(FRAME_GRID_COLS - 1, (int)ceilf(f_mul(f_add(f_sub(x, min_x), r), winv)));
+  const int nMinCellY = max(0, (int)floorf(f_mul(f_sub(f_sub(y, min_y), r), hinv)));
+  const int nMaxCellY = min(FRAME_GRID_ROWS - 1, (int)ceilf(f_mul(f_add(f_sub(y, min_y), r), hinv)));
+  const bool ok = nMinCellX < FRAME_GRID_COLS && nMaxCellX >= 0 && nMinCellY < FRAME_GRID_ROWS && nMaxCellY >= 0;
+  uint32_t best = KEY_NONE;
+  int best_i = -1;
+  if (ok) {
+    const Desc256 dq = load_desc(qdesc + qo * 32);
+    int seq = 0, ix = nMinCellX, e = 0, e1 = 0;
+    while (true) {
+      if (e >= e1) {
+        if (ix > nMaxCellX) break;
+        e = off[ix * FRAME_GRID_ROWS + nMinCellY];
+        e1 = off[ix * FRAME_GRID_ROWS + nMaxCellY + 1];
+        ix++;
+        continue;
+      }
+      const int j = idx[e];
+      e++;
+      const float kx = k[j].x, ky = k[j].y;
+      const int oct = k[j].octave;
+      if (!(fabsf(f_sub(kx, x)) < r && fabsf(f_sub(ky, y)) < r)) continue;  // GetFeaturesInArea
+      const int pos = seq++;
+      if (oct < level - 1 || oct > level) continue;                            // :1269
+      const float ex = f_sub(x, kx), ey = f_sub(y, ky);
+      float e2 = f_add(f_mul(ex, ex), f_mul(ey, ey));
+      const float kr = urk ? urk[j] : -1.0f;
+      double lim = 5.99;
+      if (kr >= 0.0f) {                                                        // :1272-1285
+        const float er = f_sub(ur, kr);
+        e2 = f_add(e2, f_mul(er, er));
+        lim = 7.8;
+      }
+      if ((double)f_mul(e2, inv_sigma2.s[oct]) > lim) continue;
+      const int d = hamming(dq, load_desc(dsc + (size_t)j * 32));
+      const uint32_t key = make_key(d, pos & 0xFFFFF, ORBM_TIE_FIRST_MIN);
+      if (key < best) { best = key; best_i = j; }
+    }
+  }
+  orbm_result res;
+  res.best_idx = best_i;
+  res.best_dist = best_i >= 0 ? (int16_t)(best >> 20) : (int16_t)256;
+  res.best_level = best_i >= 0 ? (int8_t)k[best_i].octave : (int8_t)-1;
+  res.second_dist = 256; res.second_level = -1; res.pad = 0;
+  out[qo] = res;
+}
+
 // ---- Hamming stage of Frame::ComputeStereoMatches (Frame.cc:811-894) -------------------------------
 struct ScaleTab { float s[ORBX_MAX_LEVELS]; };
 
@@ -459,6 +532,27 @@ int orbm_search_area(const orbx_keypoint* d_kps, const uint8_t* d_desc, const in
   k_search_area_tq<<<grd, SA_THREADS, 0, (cudaStream_t)stream>>>(
       (const OrbxKeyPointDev*)d_kps, d_desc, d_n, kp_stride, d_cell_off, d_cell_idx, min_x, min_y, winv, hinv, d_qx,
       d_qy, d_qr, d_qmin_level, d_qmax_level, d_qdesc, d_nq, q_stride, tie_rule, d_out);
+  CUM(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbm_fuse_candidates(const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n, int kp_stride,
+                         const int32_t* d_cell_off, const int32_t* d_cell_idx, float min_x, float max_x, float min_y,
+                         float max_y, const float* d_u_right, const float* inv_level_sigma2_host, int nlevels,
+                         const float* d_qx, const float* d_qy, const float* d_qr, const float* d_q_ur,
+                         const int8_t* d_qlevel, const uint8_t* d_qdesc, const int32_t* d_nq, int q_stride,
+                         int batch, orbm_result* d_out, void* stream) {
+  if (!d_kps || !d_desc || !d_n || !d_cell_off || !d_cell_idx || !inv_level_sigma2_host || !d_qx || !d_qy ||
+      !d_qr || !d_qlevel || !d_qdesc || !d_nq || !d_out || batch < 1 || kp_stride < 1 || q_stride < 1 ||
+      nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !(max_x > min_x) || !(max_y > min_y) || (d_u_right && !d_q_ur))
+    return ORBX_E_INVALID;
+  InvSigmaTab tab;
+  for (int i = 0; i < ORBX_MAX_LEVELS; i++) tab.s[i] = i < nlevels ? inv_level_sigma2_host[i] : 0.0f;
+  const float winv = (float)FRAME_GRID_COLS / (max_x - min_x), hinv = (float)FRAME_GRID_ROWS / (max_y - min_y);
+  dim3 grd((q_stride + SA_THREADS - 1) / SA_THREADS, batch);
+  k_fuse_tq<<<grd, SA_THREADS, 0, (cudaStream_t)stream>>>(
+      (const OrbxKeyPointDev*)d_kps, d_desc, d_n, kp_stride, d_cell_off, d_cell_idx, min_x, min_y, winv, hinv,
+      d_u_right, tab, d_qx, d_qy, d_qr, d_q_ur, d_qlevel, d_qdesc, d_nq, q_stride, d_out);
   CUM(cudaGetLastError());
   return ORBX_OK;
 }

@@ -84,6 +84,25 @@ class ORBmatcher:
         return out
 
     @staticmethod
+    def fuse_candidates(kps, desc, n, grid, bounds, inv_level_sigma2, qx, qy, qr, qlevel, qdesc, nq, u_right=None,
+                        q_ur=None):
+        """Candidate scoring of ORBmatcher::Fuse (ORBmatcher.cc:1148-1338).  Queries [B,Q]: qx,qy,qr (,q_ur) f32,
+        qlevel i8 (predicted level), qdesc [B,Q,32] u8, nq [B] i32; u_right [B,cap] f32 = mvuRight or None.
+        Returns [B,Q,12] uint8 orbm_result records (best_idx, best_dist)."""
+        b, cap = kps.shape[0], kps.shape[1]
+        qs = qx.shape[1]
+        out = _res_tensor(b * qs, kps.device).view(b, qs, RES_DTYPE.itemsize)
+        sg = np.ascontiguousarray(inv_level_sigma2, np.float32)
+        p = lambda t: t.data_ptr() if t is not None else None
+        rc = _lib.lib().orbm_fuse_candidates(kps.data_ptr(), desc.data_ptr(), n.data_ptr(), cap, grid[0].data_ptr(),
+                                             grid[1].data_ptr(), *[float(v) for v in bounds], p(u_right),
+                                             sg.ctypes.data, sg.size, qx.data_ptr(), qy.data_ptr(), qr.data_ptr(),
+                                             p(q_ur), qlevel.data_ptr(), qdesc.data_ptr(), nq.data_ptr(), qs, b,
+                                             out.data_ptr(), _stream(kps.device))
+        _lib.check(rc, "orbm_fuse_candidates")
+        return out
+
+    @staticmethod
     def queries_shift(kps, desc, n, src_frame, shift_xy, th, scale_factors, band=(-1, 1), out=None):
         """Window queries of SearchByProjection(Frame, Frame) for a per-frame image shift.
         src_frame [B] i32, shift_xy [B,2] f32.  Returns dict(qx,qy,qr,qmin,qmax,qdesc,nq)."""
@@ -256,6 +275,25 @@ class ORBmatcher:
             sf.ctypes.data, sg.ctypes.data, sf.size, int(bool(only_stereo)), int(bool(coarse)),
             int(bool(check_orientation)), out["match12"].data_ptr(), out["nmatches"].data_ptr(), _stream(dev))
         _lib.check(rc, "orbm_search_for_triangulation")
+        return out
+
+    @staticmethod
+    def search_for_initialization(kps1, desc1, n1, kps2, desc2, n2, grid2, bounds, prev_matched, window_size=100,
+                                  nn_ratio=0.9, check_orientation=True):
+        """ORBmatcher::SearchForInitialization (ORBmatcher.cc:648-763).  prev_matched [B,cap,2] f32 is updated in
+        place (vbPrevMatched).  Returns dict(match12 [B,cap] i32, nmatches [B] i32)."""
+        import torch
+        b, cap = kps1.shape[0], kps1.shape[1]
+        dev = kps1.device
+        out = {"match12": torch.empty((b, cap), dtype=torch.int32, device=dev),
+               "nmatches": torch.empty((b,), dtype=torch.int32, device=dev)}
+        scratch = torch.empty((2, b, cap), dtype=torch.int32, device=dev)
+        rc = _lib.lib().orbm_search_for_initialization(
+            kps1.data_ptr(), desc1.data_ptr(), n1.data_ptr(), kps2.data_ptr(), desc2.data_ptr(), n2.data_ptr(), cap, b,
+            grid2[0].data_ptr(), grid2[1].data_ptr(), *[float(v) for v in bounds], prev_matched.data_ptr(),
+            int(window_size), float(nn_ratio), int(bool(check_orientation)), out["match12"].data_ptr(),
+            scratch.data_ptr(), out["nmatches"].data_ptr(), _stream(dev))
+        _lib.check(rc, "orbm_search_for_initialization")
         return out
 
     @staticmethod

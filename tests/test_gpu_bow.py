@@ -233,3 +233,81 @@ def test_distinctive_descriptors_match_oracle(oracle_mod, frames_feats):
     best = best.cpu().numpy()
     for m in range(len(sizes)):
         assert best[m] == oracle_mod.distinctive_descriptor(pool[idx[off[m]:off[m + 1]]]), m
+
+
+def test_fuse_candidates_match_oracle(oracle_mod, frames_feats):
+    """Candidate scoring of ORBmatcher::Fuse: MapPoints = keypoints of neighbouring frames projected with noise."""
+    import torch
+    from orb_slam3_vio_fixes_b200.matcher import results_to_numpy
+    feats, _, sf = frames_feats
+    rng = np.random.default_rng(41)
+    cap = 1100
+    B = 4
+    kps, desc, n = _pad_batch(feats[:B], cap)
+    bounds = (0.0, 752.0, 0.0, 480.0)
+    inv = (1.0 / (sf * sf)).astype(np.float32)
+    Q = 2200
+    qx, qy, qr, qur = (np.zeros((B, Q), np.float32) for _ in range(4))
+    ql = np.zeros((B, Q), np.int8)
+    qd = np.zeros((B, Q, 32), np.uint8)
+    nq = np.zeros(B, np.int32)
+    ur = np.where(rng.random((B, cap)) < 0.5, kps["x"] - 24.0 + rng.normal(0, 0.5, (B, cap)), -1.0).astype(np.float32)
+    for f in range(B):
+        src = [feats[(f + 1) % len(feats)], feats[(f + 2) % len(feats)]]
+        k = np.concatenate([s[0] for s in src])
+        d = np.concatenate([s[1] for s in src])
+        m = len(k)
+        shift = np.repeat(np.array([[-2.0, -1.0], [-4.0, -2.0]], np.float32), [len(src[0][0]), len(src[1][0])], 0)
+        qx[f, :m] = k["x"] + shift[:, 0] + rng.normal(0, 1.0, m)
+        qy[f, :m] = k["y"] + shift[:, 1] + rng.normal(0, 1.0, m)
+        ql[f, :m] = np.clip(k["octave"] + rng.integers(-1, 2, m), 0, 7)
+        qr[f, :m] = 3.0 * sf[ql[f, :m]]
+        qur[f, :m] = qx[f, :m] - 24.0
+        qd[f, :m] = d
+        nq[f] = m
+    grid = ORBmatcher.grid_build(_kt(kps), _t(n), bounds)
+    for with_stereo in (False, True):
+        out = ORBmatcher.fuse_candidates(_kt(kps), _t(desc), _t(n), grid, bounds, inv, _t(qx), _t(qy), _t(qr), _t(ql),
+                                         _t(qd), _t(nq), _t(ur) if with_stereo else None,
+                                         _t(qur) if with_stereo else None)
+        torch.cuda.synchronize()
+        res = results_to_numpy(out)
+        hits = 0
+        for f in range(B):
+            m = nq[f]
+            bi, bd = oracle_mod.fuse_candidates(kps[f, :n[f]], desc[f, :n[f]], bounds, inv, qx[f, :m], qy[f, :m], qr[f, :m],
+                                                ql[f, :m], qd[f, :m], ur[f, :n[f]] if with_stereo else None,
+                                                qur[f, :m] if with_stereo else None)
+            assert np.array_equal(res["best_idx"][f, :m], bi)
+            assert np.array_equal(res["best_dist"][f, :m], bd)
+            hits += int(np.sum(bd <= 50))
+        assert hits > 500
+
+
+@pytest.mark.parametrize("check_ori", [True, False])
+def test_search_for_initialization_matches_oracle(oracle_mod, frames_feats, check_ori):
+    import torch
+    feats, _, _ = frames_feats
+    cap = 1100
+    pairs = [(0, 1), (0, 3), (2, 5), (4, 4)]
+    f1 = [feats[a] for a, _ in pairs]
+    f2 = [feats[b] for _, b in pairs]
+    k1, d1, n1 = _pad_batch(f1, cap)
+    k2, d2, n2 = _pad_batch(f2, cap)
+    bounds = (0.0, 752.0, 0.0, 480.0)
+    pm = np.stack([k1["x"], k1["y"]], -1).astype(np.float32)   # vbPrevMatched starts at F1's own keypoints
+    grid2 = ORBmatcher.grid_build(_kt(k2), _t(n2), bounds)
+    for window, ratio in ((100, 0.9), (30, 0.7)):
+        pm_t = _t(pm.copy())
+        out = ORBmatcher.search_for_initialization(_kt(k1), _t(d1), _t(n1), _kt(k2), _t(d2), _t(n2), grid2, bounds, pm_t,
+                                                   window, ratio, check_ori)
+        torch.cuda.synchronize()
+        tot = 0
+        for p in range(len(pairs)):
+            m12, nm, pm2 = oracle_mod.search_for_initialization(f1[p][0], f1[p][1], f2[p][0], f2[p][1], bounds,
+                                                                pm[p, :n1[p]], window, ratio, check_ori)
+            assert int(out["nmatches"][p]) == nm
+            assert np.array_equal(out["match12"][p, :n1[p]].cpu().numpy(), m12)
+            assert np.array_equal(pm_t[p, :n1[p]].cpu().numpy(), pm2)
+            tot += nm
+        assert tot > 150

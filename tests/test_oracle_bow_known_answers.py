@@ -147,3 +147,45 @@ def test_distinctive_descriptor_median_rule(oracle_mod):
     # rows: 30 ; [30,0,10,70] -> 10 ; [40,10,0,60] -> 10 ; 60 -> first of the two 10s
     assert oracle_mod.distinctive_descriptor(d) == 1
     assert oracle_mod.distinctive_descriptor(d[:1]) == 0
+
+
+def test_fuse_candidates_gates(oracle_mod):
+    # three level-1 keypoints near the projection (100,100): at 1 px, 2 px and 3 px; invSigma2[1] = 1/1.44
+    xy = np.array([[101, 100], [102, 100], [103, 100], [100.5, 100]], np.float32)
+    k = _kps(4, octave=1, xy=xy)
+    k["octave"][3] = 3                      # closest, but outside [l-1, l]
+    d = _desc_with_bits([30, 10, 5, 0])
+    inv = (1.0 / (np.array([1.2 ** i for i in range(8)], np.float32) ** 2)).astype(np.float32)
+    q = dict(qx=[100.0], qy=[100.0], qr=[10.0], qlevel=[1], qdesc=_desc_with_bits([0]))
+    # mono: e2*inv = 1/1.44, 4/1.44 = 2.78, 9/1.44 = 6.25 > 5.99 -> third dropped -> best = index 1 (dist 10)
+    bi, bd = oracle_mod.fuse_candidates(k, d, (0, 752, 0, 480), inv, **q)
+    assert bi[0] == 1 and bd[0] == 10
+    # stereo coordinate on index 1 with er = 3: (4+9)/1.44 = 9.03 > 7.8 -> dropped -> index 0
+    ur = np.array([-1, 50, -1, -1], np.float32)
+    bi, bd = oracle_mod.fuse_candidates(k, d, (0, 752, 0, 480), inv, u_right=ur, q_ur=[53.0], **q)
+    assert bi[0] == 0 and bd[0] == 30
+    # predicted level 2 accepts octave 1 and 2; level 3 accepts the octave-3 keypoint only
+    q["qlevel"] = [3]
+    bi, bd = oracle_mod.fuse_candidates(k, d, (0, 752, 0, 480), inv, **q)
+    assert bi[0] == 3 and bd[0] == 0
+
+
+def test_search_for_initialization_stealing(oracle_mod):
+    # two F1 keypoints compete for one F2 feature: the second (closer descriptor) steals it, the first ends unmatched
+    k1 = _kps(2, xy=np.array([[100, 100], [105, 100]], np.float32))
+    k2 = _kps(1, xy=np.array([[102, 100]], np.float32))
+    d1 = _desc_with_bits([20, 5])
+    d2 = _desc_with_bits([0])
+    pm = np.stack([k1["x"], k1["y"]], 1)
+    m12, nm, pm2 = oracle_mod.search_for_initialization(k1, d1, k2, d2, (0, 752, 0, 480), pm, 100, 0.9, False)
+    assert list(m12) == [-1, 0] and nm == 1
+    assert np.array_equal(pm2, np.array([[100, 100], [102, 100]], np.float32))
+    # reversed descriptor quality: the later, worse one does not steal (vMatchedDistance <= dist)
+    m12, nm, _ = oracle_mod.search_for_initialization(k1, d1[::-1].copy(), k2, d2, (0, 752, 0, 480), pm, 100, 0.9, False)
+    assert list(m12) == [0, -1] and nm == 1
+    # only level-0 keypoints of F1 take part, only level-0 features of F2 are candidates
+    k1b = k1.copy(); k1b["octave"][1] = 1
+    m12, nm, _ = oracle_mod.search_for_initialization(k1b, d1, k2, d2, (0, 752, 0, 480), pm, 100, 0.9, False)
+    assert list(m12) == [0, -1]
+    k2b = k2.copy(); k2b["octave"][0] = 1
+    assert oracle_mod.search_for_initialization(k1, d1, k2b, d2, (0, 752, 0, 480), pm, 100, 0.9, False)[1] == 0
