@@ -338,7 +338,11 @@ def main():
         if caps:
             kern = json.loads(caps[-1].read_text())["kernels"].get("k_" + top["kernel"])
             if kern:
-                traffic = int(kern[0]["dram_read_bytes"] + kern[0]["dram_write_bytes"])
+                # the capture's launches may cover a sub-batch (grid.y = frames in the launch): scale to the B
+                # frames that `alg_bytes_per_launch` and the stage time refer to
+                per = [(k_["dram_read_bytes"] + k_["dram_write_bytes"]) / max(1, int(k_["grid"].strip("()").split(",")[1]))
+                       for k_ in kern]
+                traffic = int(sum(per) / len(per) * B)
     except Exception:
         traffic = None
     total_bytes = sum(ext_bytes.values()) + match_bytes

@@ -441,44 +441,7 @@ def distinctive_descriptor(desc):
     return L.oracle_distinctive_descriptor(_p(d), d.shape[0])
 
 
-def make_vocabulary(k, L, seed=0, stop_fraction=0.02, desc_pool=None):
-    """A synthetic DBoW2-shaped vocabulary (k-ary, depth L, random 256-bit node descriptors, idf-like positive
-    weights, a few stopped words with weight 0) in the flat layout, node ids in the breadth-first creation order
-    of TemplatedVocabulary::HKmeansStep.  ORBvoc.txt itself is not in the image."""
-    rng = np.random.default_rng(seed)
-    child_off, child_idx = [0], []
-    levels = [[0]]
-    nid = 1
-    parents = [0]
-    children_of = {0: []}
-    for lvl in range(1, L + 1):
-        cur = []
-        for pnode in parents:
-            ids = list(range(nid, nid + k))
-            nid += k
-            children_of[pnode] = ids
-            for c in ids:
-                children_of[c] = []
-            cur += ids
-        parents = cur
-    nnodes = nid
-    for i in range(nnodes):
-        child_idx += children_of[i]
-        child_off.append(len(child_idx))
-    if desc_pool is None:
-        node_desc = rng.integers(0, 256, (nnodes, 32), dtype=np.uint8)
-    else:  # node centres drawn from real descriptors: features of neighbouring frames share nodes
-        pool = np.ascontiguousarray(desc_pool, np.uint8).reshape(-1, 32)
-        node_desc = pool[rng.integers(0, pool.shape[0], nnodes)].copy()
-    node_word = np.full(nnodes, -1, np.int32)
-    leaves = [i for i in range(nnodes) if not children_of[i]]
-    node_word[leaves] = np.arange(len(leaves), dtype=np.int32)
-    node_weight = np.zeros(nnodes, np.float64)
-    w = np.log(rng.uniform(1.5, 400.0, len(leaves)))
-    w[rng.random(len(leaves)) < stop_fraction] = 0.0
-    node_weight[leaves] = w
-    return {"child_off": np.array(child_off, np.int32), "child_idx": np.array(child_idx, np.int32),
-            "node_desc": node_desc, "node_word": node_word, "node_weight": node_weight, "L": L}
+from orb_slam3_vio_fixes_b200.synthetic import make_vocabulary  # noqa: E402,F401  (synthetic input, not a checker)
 
 
 def bench_extract(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, lap, threads, flags=0):

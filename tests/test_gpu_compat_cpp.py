@@ -67,3 +67,47 @@ def test_cpp_stereo_dropin_matches_oracle(oracle_mod, tmp_path):
     assert (nl, nr, kept) == (len(kl), len(kr), rkept) and kept > 100
     assert np.array_equal(np.fromfile(tmp_path / "o.ur", dtype=np.uint32), ur.view(np.uint32))
     assert np.array_equal(np.fromfile(tmp_path / "o.depth", dtype=np.uint32), dp.view(np.uint32))
+
+
+def test_cpp_bow_helpers_match_oracle(oracle_mod, tmp_path):
+    """include/orbx_compat/BowMatcher.h (SearchByBoW x2, SearchForTriangulation on std:: containers) vs the oracle."""
+    exe = _build_exe(tmp_path, "compat_bow")
+    frames = S.make_frames("C1", 2)
+    orc = oracle_mod.Extractor(1000)
+    (k1, d1, _), (k2, d2, _) = [orc.extract(f, (0, 0)) for f in frames]
+    voc = S.make_vocabulary(10, 4, seed=5, desc_pool=np.concatenate([d1, d2]))
+    fv1 = oracle_mod.bow_transform(d1, voc, 2)["fv"]
+    fv2 = oracle_mod.bow_transform(d2, voc, 2)["fv"]
+    rng = np.random.default_rng(9)
+    v1 = (rng.random(len(k1)) < 0.7).astype(np.uint8)
+    v2 = (rng.random(len(k2)) < 0.7).astype(np.uint8)
+    u1 = np.where(rng.random(len(k1)) < 0.5, 100.0, -1.0).astype(np.float32)
+    u2 = np.where(rng.random(len(k2)) < 0.5, 100.0, -1.0).astype(np.float32)
+    F = np.array([0, -0.01, 0.447, 0.01, 0, -0.894, -0.447, 0.894, 0], np.float32)
+    ep = np.array([500.0, 300.0], np.float32)
+    sf = np.array([1.2 ** i for i in range(8)], np.float32)
+    sg = (sf * sf).astype(np.float32)
+    with open(tmp_path / "in.bin", "wb") as f:
+        f.write(np.array([len(k1), len(k2), len(fv1[0]), len(fv2[0])], np.int32).tobytes())
+        for k, d, v, u, fv in ((k1, d1, v1, u1, fv1), (k2, d2, v2, u2, fv2)):
+            idx = np.zeros(len(k), np.int32)
+            idx[:len(fv[2])] = fv[2]
+            for a in (k, d, v, u, fv[0], fv[1], idx):
+                f.write(np.ascontiguousarray(a).tobytes())
+        for a in (F, ep, sf, sg):
+            f.write(a.tobytes())
+    out = subprocess.check_output([str(exe), str(tmp_path / "in.bin"), str(tmp_path / "o")], text=True)
+    n0, n1, n2, npairs = [int(v) for v in out.split()]
+    m12, m21, r0 = oracle_mod.search_by_bow(0, k1, d1, fv1, k2, d2, fv2, 0.7, True, v1, v2)
+    assert n0 == r0 > 50
+    assert np.array_equal(np.fromfile(tmp_path / "o.bow0_m12", np.int32), m12)
+    assert np.array_equal(np.fromfile(tmp_path / "o.bow0_m21", np.int32), m21)
+    m12, _, r1 = oracle_mod.search_by_bow(1, k1, d1, fv1, k2, d2, fv2, 0.8, True, v1, v2)
+    assert n1 == r1 > 50
+    assert np.array_equal(np.fromfile(tmp_path / "o.bow1_m12", np.int32), m12)
+    t12, r2 = oracle_mod.search_for_triangulation(k1, d1, fv1, k2, d2, fv2, F, ep, sf, sg, False, False, True,
+                                                  1 - v1, 1 - v2, u1, u2)
+    assert n2 == r2 == npairs
+    pairs = np.fromfile(tmp_path / "o.tri_pairs", np.int32).reshape(-1, 2)
+    ref = np.stack([np.nonzero(t12 >= 0)[0], t12[t12 >= 0]], 1)
+    assert np.array_equal(pairs, ref)
