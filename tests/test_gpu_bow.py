@@ -282,6 +282,21 @@ def test_fuse_candidates_match_oracle(oracle_mod, frames_feats):
             assert np.array_equal(res["best_dist"][f, :m], bd)
             hits += int(np.sum(bd <= 50))
         assert hits > 500
+    # SearchBySim3's scoring loops (ORBmatcher.cc:1543-1580, 1623-1660): same walk and level band, no chi-square
+    # gate (an all-zero invLevelSigma2 disables it), accept best <= TH_HIGH, then mutual agreement on the host
+    zero = np.zeros(8, np.float32)
+    out = ORBmatcher.fuse_candidates(_kt(kps), _t(desc), _t(n), grid, bounds, zero, _t(qx), _t(qy), _t(qr), _t(ql), _t(qd),
+                                     _t(nq))
+    torch.cuda.synchronize()
+    res = results_to_numpy(out)
+    more = 0
+    for f in range(B):
+        m = nq[f]
+        bi, bd = oracle_mod.fuse_candidates(kps[f, :n[f]], desc[f, :n[f]], bounds, zero, qx[f, :m], qy[f, :m], qr[f, :m],
+                                            ql[f, :m], qd[f, :m])
+        assert np.array_equal(res["best_idx"][f, :m], bi) and np.array_equal(res["best_dist"][f, :m], bd)
+        more += int(np.sum(bd <= 100))
+    assert more > hits
 
 
 @pytest.mark.parametrize("check_ori", [True, False])

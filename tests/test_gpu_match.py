@@ -351,6 +351,34 @@ def test_search_by_projection_keyframe_relocalisation(oracle_mod, orb_dist):
             assert np.all(fq[f, :n[f]][locked[f, :n[f]] != 0] == -1)
 
 
+@pytest.mark.parametrize("ratio_hamming", [1.0, 0.75])
+def test_search_by_projection_sim3_keyframe(oracle_mod, ratio_hamming):
+    """SearchByProjection(KeyFrame*, Sim3, vpPoints, vpMatched, th, ratioHamming) (ORBmatcher.cc:427-532, 534-646):
+    candidates on levels [l-1, l] only, features already in vpMatched are skipped, best <= TH_LOW*ratioHamming,
+    no rotation check.  Served by the threshold-parameter entry point."""
+    from bench import shifts_for
+    B = 3
+    frames = S.make_frames("C1", B)
+    ex = ORBextractor(1000, max_batch=B, **ORB)
+    out = _extract_batch(ex, frames, (0, 1000))
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    n = out["n"].cpu().numpy()
+    sf = ex.GetScaleFactors()
+    sh = shifts_for(0, B)
+    rng = np.random.default_rng(17)
+    bounds = (0.0, 752.0, 0.0, 480.0)
+    cap = out["kps"].shape[1]
+    ql = []
+    for f in range(B):
+        s = (f - 1) % B
+        ql.append(_proj_queries(kps[s, :n[s]], desc[s, :n[s]], sh[f], 4, sf, (-1, 0), rng, dup=2, drop=0.15))
+    matched = (rng.random((B, cap)) < 0.3).astype(np.uint8)     # vpMatched[idx] != NULL on entry
+    th_dist = int(np.floor(50 * ratio_hamming))                 # bestDist <= TH_LOW*ratioHamming, integer distances
+    tot, mt, fq = _proj_run(oracle_mod, out, ql, bounds, 1, 0.9, False, feat_locked=matched, th_dist=th_dist)
+    assert tot > 300
+
+
 @pytest.mark.parametrize("check_ori", [True, False])
 def test_search_by_projection_lastframe(oracle_mod, check_ori):
     """ORBmatcher.cc:1676-1887 (mono shape): last-frame keypoints projected by the known shift, th=15."""
