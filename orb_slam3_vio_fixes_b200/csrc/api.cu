@@ -63,6 +63,7 @@ struct orbx_extractor_s {
   std::vector<cudaEvent_t> ev_in, ev_done;
   cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
   int host_chunk = 64;
+  int host_edge = 0;   // length of the first and last chunk of a long host batch (ORBX_HOST_EDGE, 0 = off)
   int dev_split = 2;  // sub-batches of orbx_extract_batch_device (ORBX_DEVICE_SPLIT)
 };
 
@@ -235,6 +236,7 @@ static int ensure_streams(orbx_handle h) {
   CU(cudaEventCreateWithFlags(&h->ev_join[0], cudaEventDisableTiming));
   CU(cudaEventCreateWithFlags(&h->ev_join[1], cudaEventDisableTiming));
   if (const char* e = getenv("ORBX_HOST_CHUNK")) { const int v = atoi(e); if (v > 0) h->host_chunk = v; }
+  if (const char* e = getenv("ORBX_HOST_EDGE")) { const int v = atoi(e); if (v >= 0) h->host_edge = v; }
   if (const char* e = getenv("ORBX_DEVICE_SPLIT")) { const int v = atoi(e); if (v > 0) h->dev_split = v; }
   return ORBX_OK;
 }
@@ -343,7 +345,17 @@ int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int l
     if (e_ != cudaSuccess) { set_err("cudaMalloc stage", e_); return e_ == cudaErrorMemoryAllocation ? ORBX_E_NOMEM : ORBX_E_CUDA; }
   }
   const int chunk = h->host_chunk < batch ? h->host_chunk : batch;
-  const int nchunks = (batch + chunk - 1) / chunk;
+  // Chunk schedule: full chunks in the middle, a shorter first chunk (the kernels start sooner) and a shorter
+  // last one (less work left once the last frame has arrived), when the batch is long enough to afford it.
+  std::vector<int> sched;
+  {
+    const int edge = h->host_edge > 0 && h->host_edge < chunk && batch >= 4 * chunk ? h->host_edge : 0;
+    int left = batch;
+    if (edge) { sched.push_back(edge); left -= 2 * edge; }
+    while (left > 0) { const int c_ = left < chunk ? left : chunk; sched.push_back(c_); left -= c_; }
+    if (edge) sched.push_back(edge);
+  }
+  const int nchunks = (int)sched.size();
   while ((int)h->ev_in.size() < nchunks) {
     cudaEvent_t a, b;
     CU(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
@@ -352,8 +364,10 @@ int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int l
   }
   // anything still running on the handle's own stream (single-frame API) must be done first
   CU(cudaStreamSynchronize(h->stream));
+  int f_next = 0;
   for (int c = 0; c < nchunks; c++) {
-    const int f0 = c * chunk, nb = (batch - f0) < chunk ? (batch - f0) : chunk;
+    const int f0 = f_next, nb = sched[c];
+    f_next += nb;
     cudaStream_t cs = h->s_cmp[c & 1];
     // One contiguous H2D per chunk into the tightly packed staging frames, which then serve as
     // level 0 directly (row pitch = W): strided 2-D copies of 752-byte rows run far below PCIe rate.
