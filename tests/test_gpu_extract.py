@@ -185,3 +185,25 @@ def test_full_size_configs(oracle_mod, cfg, lap, nframes):
     for right in eyes:
         for img in S.make_frames(cfg, nframes, right=right):
             _compare_frame(oracle_mod, ex, orc, img, lap)
+
+
+@pytest.mark.parametrize("chunk,edge", [(4, 0), (4, 2), (5, 3), (64, 0)])
+def test_host_batch_chunk_schedules_give_identical_bytes(monkeypatch, chunk, edge):
+    """orbx_extract_batch_host: any chunk schedule (ORBX_HOST_CHUNK, shorter first/last chunk ORBX_HOST_EDGE, ragged
+    tail) returns the bytes of the device-resident path."""
+    import torch
+    monkeypatch.setenv("ORBX_HOST_CHUNK", str(chunk))
+    monkeypatch.setenv("ORBX_HOST_EDGE", str(edge))
+    B = 23
+    frames = S.make_frames("C3", B, width=400, height=300)
+    ex = ORBextractor(500, max_batch=B, **ORB)
+    out = ex.extract_batch_device(torch.from_numpy(frames).cuda(), (0, 0))
+    torch.cuda.synchronize()
+    n = out["n"].cpu().numpy()
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    k2, d2, n2, m2 = ex.extract_batch_host(frames, (0, 0))
+    assert np.array_equal(n2, n) and n.min() > 100
+    assert np.array_equal(m2, out["mono"].cpu().numpy())
+    for f in range(B):
+        assert np.array_equal(k2[f, :n[f]], kps[f, :n[f]]) and np.array_equal(d2[f, :n[f]], desc[f, :n[f]])
