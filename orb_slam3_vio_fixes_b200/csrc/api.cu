@@ -59,7 +59,8 @@ struct orbx_extractor_s {
   cudaEvent_t ev[ORBX_NUM_STAGES + 1] = {};
   bool timed = false;
   // orbx_extract_batch_host pipeline: copy-in / two compute / copy-out streams, one event pair per chunk
-  cudaStream_t s_in = nullptr, s_out = nullptr, s_cmp[2] = {nullptr, nullptr};
+  cudaStream_t s_in = nullptr, s_out = nullptr, s_cmp[4] = {nullptr, nullptr, nullptr, nullptr};
+  int host_streams = 2;  // compute streams the host batch pipeline rotates its chunks over (ORBX_HOST_STREAMS, 1..4)
   std::vector<cudaEvent_t> ev_in, ev_done;
   cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
   int host_chunk = 64;
@@ -104,7 +105,7 @@ void orbx_destroy(orbx_handle h) {
     if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]);
   if (h->s_in) cudaStreamDestroy(h->s_in);
   if (h->s_out) cudaStreamDestroy(h->s_out);
-  for (int i = 0; i < 2; i++)
+  for (int i = 0; i < 4; i++)
     if (h->s_cmp[i]) cudaStreamDestroy(h->s_cmp[i]);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
@@ -232,10 +233,13 @@ static int ensure_streams(orbx_handle h) {
   CU(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&h->s_cmp[0], cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&h->s_cmp[1], cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&h->s_cmp[2], cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&h->s_cmp[3], cudaStreamNonBlocking));
   CU(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
   CU(cudaEventCreateWithFlags(&h->ev_join[0], cudaEventDisableTiming));
   CU(cudaEventCreateWithFlags(&h->ev_join[1], cudaEventDisableTiming));
   if (const char* e = getenv("ORBX_HOST_CHUNK")) { const int v = atoi(e); if (v > 0) h->host_chunk = v; }
+  if (const char* e = getenv("ORBX_HOST_STREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 4) h->host_streams = v; }
   if (const char* e = getenv("ORBX_HOST_EDGE")) { const int v = atoi(e); if (v >= 0) h->host_edge = v; }
   if (const char* e = getenv("ORBX_DEVICE_SPLIT")) { const int v = atoi(e); if (v > 0) h->dev_split = v; }
   return ORBX_OK;
@@ -368,7 +372,7 @@ int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int l
   for (int c = 0; c < nchunks; c++) {
     const int f0 = f_next, nb = sched[c];
     f_next += nb;
-    cudaStream_t cs = h->s_cmp[c & 1];
+    cudaStream_t cs = h->s_cmp[c % h->host_streams];
     // One contiguous H2D per chunk into the tightly packed staging frames, which then serve as
     // level 0 directly (row pitch = W): strided 2-D copies of 752-byte rows run far below PCIe rate.
     CU(cudaMemcpyAsync(h->stage + (size_t)f0 * W * H, imgs + (size_t)f0 * W * H, (size_t)nb * W * H,
@@ -393,8 +397,7 @@ int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int l
   h->last_l0.base = h->stage; h->last_l0.frame_stride = (long long)W * H; h->last_l0.pitch = W;
   h->last_batch = batch;
   CU(cudaStreamSynchronize(h->s_out));
-  CU(cudaStreamSynchronize(h->s_cmp[0]));
-  CU(cudaStreamSynchronize(h->s_cmp[1]));
+  for (int i = 0; i < h->host_streams; i++) CU(cudaStreamSynchronize(h->s_cmp[i]));
   return ORBX_OK;
 }
 
