@@ -73,3 +73,57 @@ def test_match_and_stereo_match_golden():
     assert np.array_equal(res["u_right"][0, :n].cpu().numpy().view(np.uint32), s["u_right"].view(np.uint32))
     assert np.array_equal(res["depth"][0, :n].cpu().numpy().view(np.uint32), s["depth"].view(np.uint32))
     assert int(res["kept"][0]) == int(s["kept"])
+
+
+def test_bow_functions_match_golden():
+    """CUDA path vs tests/golden/bow_c1.npz: DBoW2 transform (fp64 BowVector bits), SearchByBoW x2,
+    SearchForTriangulation, ComputeDistinctiveDescriptors — no oracle involved."""
+    import torch
+    from orb_slam3_vio_fixes_b200 import synthetic as S
+    from orb_slam3_vio_fixes_b200 import _lib
+    from orb_slam3_vio_fixes_b200.matcher import ORBVocabulary
+    g, b = np.load(G / "c1_mono.npz"), np.load(G / "bow_c1.npz")
+    feats = [(g["kps0"], g["desc0"]), (g["kps1"], g["desc1"])]
+    cap = max(len(k) for k, _ in feats) + 8
+    voc = S.make_vocabulary(int(b["voc_k"]), int(b["voc_L"]), seed=int(b["voc_seed"]),
+                            desc_pool=np.concatenate([feats[0][1], feats[1][1]]))
+    V = ORBVocabulary(voc["child_off"], voc["child_idx"], voc["node_desc"], voc["node_word"], voc["node_weight"], voc["L"])
+    kps = np.zeros((2, cap), _lib.KP_DTYPE)
+    desc = np.zeros((2, cap, 32), np.uint8)
+    n = np.array([len(k) for k, _ in feats], np.int32)
+    flags = np.zeros((2, cap), np.uint8)
+    ur = np.full((2, cap), -1, np.float32)
+    for i, (k, d) in enumerate(feats):
+        kps[i, :n[i]], desc[i, :n[i]] = k, d
+    flags[0, :n[0]], flags[1, :n[1]] = b["valid_a"], b["valid_b"]
+    ur[0, :n[0]], ur[1, :n[1]] = b["uright_a"], b["uright_b"]
+    kt = _t(kps.view(np.float32).reshape(2, cap, 7))
+    tr = {}
+    for levelsup in (2, 3):
+        tr[levelsup] = V.transform(_t(desc), _t(n), levelsup=levelsup)
+        torch.cuda.synchronize()
+        for i, tag in enumerate("ab"):
+            o = tr[levelsup]
+            assert np.array_equal(o["feat_word"][i, :n[i]].cpu().numpy(), b[f"word_{tag}_{levelsup}"])
+            assert np.array_equal(o["feat_node"][i, :n[i]].cpu().numpy(), b[f"node_{tag}_{levelsup}"])
+            nb = int(o["bow_n"][i])
+            assert np.array_equal(o["bow_word"][i, :nb].cpu().numpy(), b[f"bow_word_{tag}_{levelsup}"])
+            assert np.array_equal(o["bow_val"][i, :nb].cpu().numpy(), b[f"bow_val_{tag}_{levelsup}"])
+    fv = tr[2]["fv"]
+    side = lambda i: (kt[i:i + 1], _t(desc[i:i + 1]), _t(n[i:i + 1]), {k_: v[i:i + 1].contiguous() for k_, v in fv.items()})
+    (ka, da, na, fa), (kb, db, nb_, fb) = side(0), side(1)
+    for mode in (0, 1):
+        for ratio, ori in ((0.6, True), (0.9, False)):
+            key = f"bow{mode}_{int(ratio * 100)}_{int(ori)}"
+            r = ORBmatcher.search_by_bow(mode, ka, da, na, fa, kb, db, nb_, fb, ratio, ori, _t(flags[0:1]), _t(flags[1:2]))
+            assert int(r["nmatches"][0]) == int(b[key + "_n"])
+            assert np.array_equal(r["match12"][0, :n[0]].cpu().numpy(), b[key + "_m12"])
+            assert np.array_equal(r["match21"][0, :n[1]].cpu().numpy(), b[key + "_m21"])
+    for only_stereo, coarse in ((0, 0), (1, 0), (0, 1)):
+        r = ORBmatcher.search_for_triangulation(ka, da, na, fa, kb, db, nb_, fb, _t(b["F12"][None]), _t(b["ep"][None]),
+                                                b["scale"], b["sigma2"], only_stereo, coarse, True, _t(1 - flags[0:1]),
+                                                _t(1 - flags[1:2]), _t(ur[0:1]), _t(ur[1:2]))
+        assert int(r["nmatches"][0]) == int(b[f"tri_{only_stereo}{coarse}_n"])
+        assert np.array_equal(r["match12"][0, :n[0]].cpu().numpy(), b[f"tri_{only_stereo}{coarse}_m12"])
+    best, _ = ORBmatcher.distinctive_descriptors(_t(feats[0][1]), _t(b["dd_off"]), _t(b["dd_idx"]))
+    assert np.array_equal(best.cpu().numpy(), b["dd_best"])
