@@ -164,6 +164,12 @@ typedef struct orbm_result {
 #define ORBM_TIE_FIRST_MIN 0 /* `dist<bestDist` loops: ORBmatcher.cc:84-120, 273-325, 1743-1768 */
 #define ORBM_TIE_LAST_MIN 1  /* `dist<=bestDist`: SearchForTriangulation, ORBmatcher.cc:1017     */
 
+/* ORBmatcher::DescriptorDistance (ORBmatcher.cc:2058-2074) for n_pairs explicit pairs in one launch:
+ * d_dist[i] = Hamming(d_a[d_idx_a[i]], d_b[d_idx_b[i]]) (index arrays may be NULL = row i).  For callers
+ * that hold many pairs at once (e.g. re-scoring accepted matches); a single pair stays the host inline. */
+int orbm_descriptor_distance_pairs(const uint8_t* d_a, const uint8_t* d_b, const int32_t* d_idx_a,
+                                   const int32_t* d_idx_b, int n_pairs, int32_t* d_dist, void* stream);
+
 /* Scores explicit candidate lists (CSR: d_cand_off[nq+1], d_cand_idx in the order the
  * reference loop visits them).  d_ref_level[nr] = octave of each reference keypoint (may be
  * NULL).  Result per query as the reference's bestDist/bestIdx/bestLevel/bestDist2/

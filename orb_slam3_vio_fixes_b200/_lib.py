@@ -38,7 +38,7 @@ SYMBOLS = [
     "orbx_extract_batch_host", "orbx_last_outputs_device", "orbx_get_pyramid", "orbx_pyramid_device", "orbx_level_size",
     "orbx_get_scale_tables", "orbx_stage_times", "orbx_debug_level_keypoints", "orbx_debug_octree", "orbm_argmin2_csr", "orbm_grid_build",
     "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_search_by_projection_th", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
-    "orbm_fuse_candidates", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
+    "orbm_fuse_candidates", "orbm_descriptor_distance_pairs", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
     "orbx_version", "orbx_last_error",
 ]
 
@@ -103,6 +103,7 @@ def lib():
     L.orbm_grid_build.argtypes = [vp, vp, i32, i32, f32, f32, f32, f32, vp, vp, vp]
     L.orbm_search_area.argtypes = [vp, vp, vp, i32, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp, vp,
                                    i32, i32, i32, vp, vp]
+    L.orbm_descriptor_distance_pairs.argtypes = [vp, vp, vp, vp, i32, vp, vp]
     L.orbm_fuse_candidates.argtypes = [vp, vp, vp, i32, vp, vp, f32, f32, f32, f32, vp, vp, i32, vp, vp, vp, vp, vp,
                                        vp, vp, i32, i32, vp, vp]
     L.orbm_queries_shift.argtypes = [vp, vp, vp, i32, i32, vp, vp, f32, vp, i32, i32, i32, vp, vp, vp, vp, vp, vp,

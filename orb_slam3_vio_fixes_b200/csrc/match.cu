@@ -313,6 +313,16 @@ k_fuse_tq(const OrbxKeyPointDev* __restrict__ kps, const uint8_t* __restrict__ d
   out[qo] = res;
 }
 
+// ---- ORBmatcher::DescriptorDistance (ORBmatcher.cc:2058-2074) over explicit index pairs ----------------
+__global__ void __launch_bounds__(256)
+k_distance_pairs(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const int32_t* __restrict__ ia,
+                 const int32_t* __restrict__ ib, int n, int32_t* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const size_t ra = ia ? (size_t)ia[i] : (size_t)i, rb = ib ? (size_t)ib[i] : (size_t)i;
+  out[i] = hamming(load_desc(a + ra * 32), load_desc(b + rb * 32));
+}
+
 // ---- Hamming stage of Frame::ComputeStereoMatches (Frame.cc:811-894) -------------------------------
 struct ScaleTab { float s[ORBX_MAX_LEVELS]; };
 
@@ -532,6 +542,15 @@ int orbm_search_area(const orbx_keypoint* d_kps, const uint8_t* d_desc, const in
   k_search_area_tq<<<grd, SA_THREADS, 0, (cudaStream_t)stream>>>(
       (const OrbxKeyPointDev*)d_kps, d_desc, d_n, kp_stride, d_cell_off, d_cell_idx, min_x, min_y, winv, hinv, d_qx,
       d_qy, d_qr, d_qmin_level, d_qmax_level, d_qdesc, d_nq, q_stride, tie_rule, d_out);
+  CUM(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbm_descriptor_distance_pairs(const uint8_t* d_a, const uint8_t* d_b, const int32_t* d_idx_a,
+                                   const int32_t* d_idx_b, int n_pairs, int32_t* d_dist, void* stream) {
+  if (!d_a || !d_b || !d_dist || n_pairs < 0) return ORBX_E_INVALID;
+  if (n_pairs == 0) return ORBX_OK;
+  k_distance_pairs<<<(n_pairs + 255) / 256, 256, 0, (cudaStream_t)stream>>>(d_a, d_b, d_idx_a, d_idx_b, n_pairs, d_dist);
   CUM(cudaGetLastError());
   return ORBX_OK;
 }

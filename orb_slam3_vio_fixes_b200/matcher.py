@@ -44,6 +44,19 @@ class ORBmatcher:
 
     # ---- batched cores ---------------------------------------------------------------------
     @staticmethod
+    def descriptor_distance_pairs(a, b, idx_a=None, idx_b=None):
+        """DescriptorDistance for many pairs: a [na,32], b [nb,32] u8 CUDA tensors, optional i32 index tensors.
+        Returns an i32 tensor of Hamming distances."""
+        import torch
+        n = (idx_a if idx_a is not None else a).shape[0]
+        out = torch.empty((n,), dtype=torch.int32, device=a.device)
+        p = lambda t: t.data_ptr() if t is not None else None
+        rc = _lib.lib().orbm_descriptor_distance_pairs(a.data_ptr(), b.data_ptr(), p(idx_a), p(idx_b), n,
+                                                       out.data_ptr(), _stream(a.device))
+        _lib.check(rc, "orbm_descriptor_distance_pairs")
+        return out
+
+    @staticmethod
     def argmin2_csr(q, r, cand_off, cand_idx, ref_level=None, tie_rule=TIE_FIRST_MIN):
         """q [nq,32] u8, r [nr,32] u8, cand_off [nq+1] i32, cand_idx [total] i32 (CUDA tensors).
         Returns a [nq,12] uint8 tensor of orbm_result records."""

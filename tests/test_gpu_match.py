@@ -48,6 +48,22 @@ def test_argmin2_csr_random_with_ties(oracle_mod, tie_rule):
     _same_results(got, ref, with_second=(tie_rule == TIE_FIRST_MIN))
 
 
+def test_descriptor_distance_pairs(oracle_mod):
+    rng = np.random.default_rng(12)
+    a = rng.integers(0, 256, (500, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (700, 32), dtype=np.uint8)
+    b[3] = a[9]
+    ia = rng.integers(0, 500, 4000).astype(np.int32)
+    ib = rng.integers(0, 700, 4000).astype(np.int32)
+    ia[0], ib[0] = 9, 3
+    got = ORBmatcher.descriptor_distance_pairs(_t(a), _t(b), _t(ia), _t(ib)).cpu().numpy()
+    ref = np.array([oracle_mod.descriptor_distance(a[i], b[j]) for i, j in zip(ia, ib)], np.int32)
+    assert np.array_equal(got, ref) and got[0] == 0
+    assert all(ORBmatcher.DescriptorDistance(a[i], b[j]) == r for i, j, r in zip(ia[:50], ib[:50], ref[:50]))
+    got = ORBmatcher.descriptor_distance_pairs(_t(a), _t(b[:500])).cpu().numpy()      # row i against row i
+    assert np.array_equal(got, [oracle_mod.descriptor_distance(a[i], b[i]) for i in range(500)])
+
+
 def test_knn2_dense(oracle_mod):
     rng = np.random.default_rng(8)
     q = rng.integers(0, 256, (333, 32), dtype=np.uint8)
