@@ -8,8 +8,8 @@
 //                   list.  Features of a node only ever meet features of the same node, hence the reference's
 //                   sequential "already matched" skip (:278-279, :823) is a dependence INSIDE one warp: side-1
 //                   features of the node are taken in order, lanes score the node's side-2 features.
-//   k_tri_nodes     same partition for SearchForTriangulation; vbMatched2 is never set there, so the queries are
-//                   independent: lanes score candidates, `dist<=bestDist` (last minimum wins, :1017) is a min over
+//   k_tri_nodes     same partition for SearchForTriangulation (one CTA per node, its warps share the node's
+//                   queries); vbMatched2 is never set there, so the queries are independent: lanes score candidates, `dist<=bestDist` (last minimum wins, :1017) is a min over
 //                   (dist, ~position) among the candidates that pass the epipole and epipolar-line gates.
 //   k_bow_rot       one CTA per pair: rotation histogram, ComputeThreeMaxima (:2012-2053), erasure, nmatches.
 //   k_bow_descend   one thread per feature: 10-ary tree descent with first-minimum child (FORB::distance).
@@ -114,7 +114,7 @@ struct TriGeom {       // per pair, host geometry
 __global__ void __launch_bounds__(BOW_WARPS * 32)
 k_tri_nodes(BowSide S1, BowSide S2, TriGeom G, int kp_stride, int node_stride, int32_t* __restrict__ match12) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, p = blockIdx.y;
-  const int a = blockIdx.x * BOW_WARPS + warp;
+  const int a = blockIdx.x;  // one CTA per node: the queries are independent, its warps take them round-robin
   if (a >= S1.fv_nn[p]) return;
   const size_t nb = (size_t)p * node_stride, fb = (size_t)p * kp_stride;
   const int node = S1.fv_node[nb + a];
@@ -129,7 +129,7 @@ k_tri_nodes(BowSide S1, BowSide S2, TriGeom G, int kp_stride, int node_stride, i
   for (int i = 0; i < 9; i++) F[i] = G.coarse ? 0.f : __ldg(G.F12 + (size_t)p * 9 + i);
   const float epx = __ldg(G.ep + 2 * p), epy = __ldg(G.ep + 2 * p + 1);
   const int TH_LOW = 50;
-  for (int i1 = o1; i1 < e1; i1++) {
+  for (int i1 = o1 + warp; i1 < e1; i1 += BOW_WARPS) {
     const int idx1 = idx1s[i1];
     if (S1.flag && S1.flag[fb + idx1]) continue;
     const bool st1 = S1.u_right && S1.u_right[fb + idx1] >= 0.0f;
@@ -476,7 +476,7 @@ extern "C" int orbm_search_for_triangulation(
     G.scale2[l] = l < nlevels ? scale_factors2_host[l] : 0.f;
     G.sigma2_2[l] = l < nlevels ? level_sigma2_2_host[l] : 0.f;
   }
-  dim3 grd((node_stride + BOW_WARPS - 1) / BOW_WARPS, batch);
+  dim3 grd(node_stride, batch);
   k_tri_nodes<<<grd, BOW_WARPS * 32, 0, st>>>(S1, S2, G, kp_stride, node_stride, d_match12);
   k_bow_rot<<<batch, 256, 0, st>>>(S1.kps, S2.kps, d_n1, kp_stride, check_orientation, d_match12, nullptr,
                                    d_nmatches);

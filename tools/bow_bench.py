@@ -43,7 +43,7 @@ def report(name, ms, units, unit_name, alg_bytes):
           f"{alg_bytes / ms / 1e6:8.1f} GB/s")
 
 
-ms, tr = timed(lambda: V.transform(desc, n, levelsup=4))
+ms, tr = timed(lambda: V.transform(desc, n, levelsup=4, node_stride=128))
 # per feature: its descriptor + L levels x 10 children x 32 B node descriptors + 16 B of outputs
 report("bow_transform (L=6,k=10)", ms, nk, "features", nk * (32 + 6 * 10 * 32 + 16))
 fv = tr["fv"]
