@@ -1,5 +1,7 @@
 """Randomised GPU-vs-oracle sweep of the vocabulary-node functions: ragged sizes (including empty sides and empty
 nodes lists), heavy distance ties, nodes larger than a warp, random object-state flags and geometry."""
+import os
+
 import numpy as np
 import pytest
 
@@ -59,7 +61,7 @@ def _batch(sides, cap, ns):
     return kt, _t(desc), _t(n), {k_: _t(v) for k_, v in fv.items()}, _t(flag), _t(ur)
 
 
-@pytest.mark.parametrize("seed", range(6))
+@pytest.mark.parametrize("seed", range(int(os.environ.get("ORBX_STRESS_SEEDS", "6"))))  # more seeds: stress run
 def test_random_bow_and_triangulation(oracle_mod, seed):
     import torch
     rng = np.random.default_rng(1000 + seed)
