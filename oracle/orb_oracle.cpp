@@ -10,13 +10,20 @@
 //                         :907-1146 last-min rule, :1676-1887 best-only)
 //   src/Frame.cc         (:385-416, :657-735 grid; :811-981 stereo matching)
 // with the OpenCV primitives the reference calls (resize, copyMakeBorder, FAST,
-// GaussianBlur, fastAtan2, cvRound) restated as exact integer / fp32 code.  The
-// reference itself cannot be compiled here (needs OpenCV/Eigen C++ headers that the
-// image lacks — see DESIGN.md), so this restatement is pinned instead against the
-// real OpenCV 4.13 binary (cv2) primitive by primitive and end to end
-// (tests/test_oracle_vs_cv2.py, oracle/cv2_pipeline.py) and against committed golden
-// vectors (tests/golden/).  The reference ships no tests / golden vectors for this
-// path ("parity unpinned" by the reference's own fixtures; pinned by cv2 here).
+// GaussianBlur, fastAtan2, cvRound) restated as exact integer / fp32 code.
+//
+// PINNED (extractor, rows a1-a11): oracle/_ref compiles the reference's own
+// src/ORBextractor.cc UNMODIFIED (recipe: oracle/Makefile target `ref`, over the OpenCV
+// header shim oracle/ref_shim/) and tests/test_ref_extractor.py asserts array_equal between
+// that build and this file on C1-C5, the threshold/fallback cases and the committed goldens,
+// with the five image primitives taken (a) from this file's exports and (b) from the real
+// OpenCV 4.13 binary (cv2 callbacks).  The primitives themselves are pinned against cv2 one
+// by one (tests/test_oracle_vs_cv2.py).  The reference ships no tests / golden vectors of
+// its own for this path.
+// UNPINNED by any executable reference (matcher rows m2-m12): ORBmatcher.cc / Frame.cc need
+// Eigen + Sophus + the Frame/KeyFrame/MapPoint graph, absent from the image; those
+// restatements are checked by hand-derived known answers and a second independent Python
+// restatement (tests/golden/make_golden_bow.py) only.
 //
 // Floating-point contract:
 //   * cos/sin: libm sincosf, exactly what the reference's `cos(float)`/`sin(float)`
@@ -1259,7 +1266,7 @@ int oracle_search_by_bow(int mode, const void* kps1_v, const uint8_t* desc1, int
 // match12[i] = vMatches12 after the rotation check.  Returns nmatches.
 int oracle_search_for_triangulation(const void* kps1_v, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
                                     const float* u_right1, const int* fv1_node, const int* fv1_off,
-                                    const int* fv1_idx, int nn1, const void* kps2_v, const uint8_t* desc2, int n2,
+                                    const int* fv1_idx, int nn1, const void* kps2_v, const uint8_t* desc2, int /*n2*/,
                                     const uint8_t* has_mp2, const float* u_right2, const int* fv2_node,
                                     const int* fv2_off, const int* fv2_idx, int nn2, const float* F12,
                                     const float* ep, const float* scale2, const float* sigma2_2, int only_stereo,

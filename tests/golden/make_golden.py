@@ -2,8 +2,10 @@
 """Generates tests/golden/*.npz — input frames plus the expected outputs of the hot path.
 
 Run in the BUILD container (needs cv2): every golden is written only after the C++ oracle and the
-independent cv2-based pipeline (real OpenCV primitives, oracle/cv2_pipeline.py) produced identical
-keypoints and descriptors for it, which is recorded in the file (`pinned_by_cv2`).  The GPU box
+independent cv2-based pipeline (real OpenCV primitives, oracle/cv2_pipeline.py) AND the reference's own
+ORBextractor.cc compiled here (oracle/_ref) running over the real cv2 primitives produced identical
+keypoints and descriptors for it, which is recorded in the file (`pinned_by_cv2`,
+`pinned_by_reference_build`).  The GPU box
 needs neither cv2 nor /root/reference to check against these.
 """
 import sys
@@ -23,11 +25,19 @@ OUT = Path(__file__).resolve().parent
 
 def extract_case(name, frames, nf, lap, cv2_check=True):
     from oracle.cv2_pipeline import Cv2Extractor
+    from oracle import ref as R
     orc = oracle.Extractor(nf)
     cvx = Cv2Extractor(nf)
-    d = {"frames": frames, "nfeatures": nf, "lap": np.array(lap, np.int32), "pinned_by_cv2": np.array(cv2_check)}
+    # the reference's own ORBextractor.cc (oracle/_ref) running over the real OpenCV binary
+    R.build()
+    R.use_cv2_primitives()
+    refx = R.RefExtractor(nf)
+    d = {"frames": frames, "nfeatures": nf, "lap": np.array(lap, np.int32), "pinned_by_cv2": np.array(cv2_check),
+         "pinned_by_reference_build": np.array(True)}
     for i, img in enumerate(frames):
         k, de, m = orc.extract(img, lap)
+        k3, d3, m3 = refx.extract(img, lap)
+        assert m == m3 and np.array_equal(k, k3) and np.array_equal(de, d3), (name, i, "reference build")
         if cv2_check:
             k2, d2, m2 = cvx.extract(img, lap)
             assert m == m2 and np.array_equal(k, k2) and np.array_equal(de, d2), (name, i)
@@ -78,7 +88,7 @@ def main():
     np.savez_compressed(OUT / "c2_stereo.npz", left=left, right=right, kps_l=dl["kps0"], desc_l=dl["desc0"],
                         kps_r=dr["kps0"], desc_r=dr["desc0"], best_idx_r=bi, best_dist=bd, u_right=ur, depth=dp,
                         kept=np.array(kept), mb=mb, bf=bf, scale_factors=ol.scale_factors,
-                        pinned_by_cv2=np.array(True))
+                        pinned_by_cv2=np.array(True), pinned_by_reference_build=np.array(True))
     for p in sorted(OUT.glob("*.npz")):
         print(p.name, p.stat().st_size)
 
