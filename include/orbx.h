@@ -32,6 +32,8 @@ extern "C" {
 #define ORBX_E_NOMEM (-4)       /* device allocation failed                                 */
 #define ORBX_E_EMPTY (-5)       /* empty image: operator() returns -1 (ORBextractor.cc:1090) */
 #define ORBX_E_NODEVICE (-6)    /* no CUDA device / driver: there is no CPU fallback        */
+#define ORBX_E_INTERNAL (-7)    /* an internal capacity bound was violated on the device (octree
+                                   node pool): the call's output is incomplete, never silently    */
 
 #define ORBX_MAX_LEVELS 12
 
@@ -99,6 +101,11 @@ int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch
                               orbx_keypoint* d_kps, uint8_t* d_desc, int capacity,
                               int32_t* d_n_out, int32_t* d_mono_index, void* stream);
 
+/* For the asynchronous device path: waits for `stream`, then reads and clears the handle's device-side
+ * status word.  ORBX_OK, or ORBX_E_INTERNAL if a kernel of an earlier orbx_extract_batch_device call hit
+ * an internal bound (the synchronous entry points check this themselves before returning). */
+int orbx_check_status(orbx_handle h, void* stream);
+
 /* Same through HOST buffers (pinned for full speed): copies the batch in, runs, copies the
  * results out, synchronises.  Frames are tightly packed width*height. */
 int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int lap0, int lap1,
@@ -134,6 +141,12 @@ int orbx_get_scale_tables(orbx_handle h, float* scale, float* inv_scale, float* 
  * finish.  ms[ORBX_NUM_STAGES] = {pyramid (all level launches), fast, octree, order, describe}. */
 int orbx_stage_times(orbx_handle h, float* ms);
 
+/* Introspection for the parity tests: order-independent 64-bit checksums (one per `chunk` patterns) of the device
+ * build of the glibc-exact sincosf (ORBextractor.cc:112) over `count` consecutive float bit patterns from `lo`. */
+int orbx_debug_sincos_checksum(int device, uint32_t lo, uint64_t count, uint32_t chunk, uint64_t* out, int n_out);
+/* Introspection for the parity tests: the GaussianBlur'ed level (ORBextractor.cc:1131-1133) the descriptor
+ * stage sampled for frame `frame` of the last call (level-blur mode only), border-free, row stride dst_stride. */
+int orbx_debug_blur_level(orbx_handle h, int frame, int level, uint8_t* dst, size_t dst_stride);
 /* Introspection for the parity tests: per-level intermediate keypoint lists of frame `frame`
  * of the last call.  stage 0 = FAST candidates in DistributeOctTree input order (x,y relative
  * to (16,16), response); stage 1 = after the octree, in list order (level coordinates).

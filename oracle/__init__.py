@@ -205,6 +205,15 @@ def sincos_bits(lo, count, stride=1):
     return c, s
 
 
+def sincos_checksum(lo, count, chunk=1 << 22, threads=None):
+    """Per-chunk checksums of glibc sincosf over `count` float bit patterns from `lo` (see orb_oracle.cpp)."""
+    L = lib()
+    L.oracle_sincos_checksum.argtypes = [C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p, C.c_int]
+    out = np.zeros((count + chunk - 1) // chunk, np.uint64)
+    L.oracle_sincos_checksum(lo, count, chunk, _p(out), threads or host_threads())
+    return out
+
+
 def descriptor_distance(a, b):
     a = np.ascontiguousarray(a, np.uint8)
     b = np.ascontiguousarray(b, np.uint8)

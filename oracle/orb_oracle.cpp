@@ -745,6 +745,32 @@ void oracle_sincos_deg(const float* angle_deg, float* cos_out, float* sin_out, l
   for (long i = 0; i < n; i++) { float a = angle_deg[i] * factorPI; sincosf(a, &sin_out[i], &cos_out[i]); }
 }
 // libm sincosf over raw float bit patterns [lo, hi] with a stride (exhaustive sweeps).
+// Per-chunk, order-independent 64-bit checksums of libm sincosf over `count` consecutive float bit patterns from
+// `lo` (the device test hook orbx_debug_sincos_checksum computes the same function of its own sincosf).
+void oracle_sincos_checksum(uint32_t lo, uint64_t count, uint32_t chunk, uint64_t* out, int threads) {
+  const uint64_t nchunks = (count + chunk - 1) / chunk;
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; t++)
+    pool.emplace_back([=]() {
+      for (uint64_t k = t; k < nchunks; k += threads) {
+        uint64_t acc = 0;
+        const uint64_t i1 = std::min<uint64_t>(count, (k + 1) * chunk);
+        for (uint64_t i = k * chunk; i < i1; i++) {
+          const uint32_t bits = lo + (uint32_t)i;
+          float y, s, c;
+          memcpy(&y, &bits, 4);
+          sincosf(y, &s, &c);
+          uint32_t sb, cb;
+          memcpy(&sb, &s, 4); memcpy(&cb, &c, 4);
+          uint64_t h = ((uint64_t)cb << 32) | sb;
+          h = h * 0x9E3779B97F4A7C15ull + bits;
+          acc += h ^ (h >> 29);
+        }
+        out[k] = acc;
+      }
+    });
+  for (auto& th : pool) th.join();
+}
 void oracle_sincos_bits(uint32_t lo, uint32_t count, uint32_t stride, float* cos_out, float* sin_out) {
   for (uint32_t i = 0; i < count; i++) {
     uint32_t u = lo + i * stride; float a; memcpy(&a, &u, 4);

@@ -13,7 +13,7 @@ SO = PKG / "liborbx.so"
 
 ORBX_OK = 0
 ERRORS = {-1: "ORBX_E_INVALID", -2: "ORBX_E_CUDA", -3: "ORBX_E_CAPACITY", -4: "ORBX_E_NOMEM",
-          -5: "ORBX_E_EMPTY", -6: "ORBX_E_NODEVICE"}
+          -5: "ORBX_E_EMPTY", -6: "ORBX_E_NODEVICE", -7: "ORBX_E_INTERNAL"}
 FLAG_STRICT_FP = 1
 FLAG_STAGE_TIMING = 2
 FLAG_FUSED_BLUR = 4
@@ -36,7 +36,7 @@ RES_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i2"), ("second_dist",
 SYMBOLS = [
     "orbx_create", "orbx_destroy", "orbx_max_keypoints", "orbx_extract", "orbx_extract_batch_device",
     "orbx_extract_batch_host", "orbx_last_outputs_device", "orbx_get_pyramid", "orbx_pyramid_device", "orbx_level_size",
-    "orbx_get_scale_tables", "orbx_stage_times", "orbx_debug_level_keypoints", "orbx_debug_octree", "orbm_argmin2_csr", "orbm_grid_build",
+    "orbx_get_scale_tables", "orbx_stage_times", "orbx_check_status", "orbx_debug_blur_level", "orbx_debug_sincos_checksum", "orbx_debug_level_keypoints", "orbx_debug_octree", "orbm_argmin2_csr", "orbm_grid_build",
     "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_search_by_projection_th", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
     "orbm_fuse_candidates", "orbm_descriptor_distance_pairs", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
     "orbx_version", "orbx_last_error",
@@ -97,6 +97,9 @@ def lib():
     L.orbx_level_size.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32)]
     L.orbx_get_scale_tables.argtypes = [vp, vp, vp, vp, vp, vp]
     L.orbx_stage_times.argtypes = [vp, vp]
+    L.orbx_check_status.argtypes = [vp, vp]
+    L.orbx_debug_sincos_checksum.argtypes = [i32, C.c_uint32, C.c_uint64, C.c_uint32, vp, i32]
+    L.orbx_debug_blur_level.argtypes = [vp, i32, i32, vp, C.c_size_t]
     L.orbx_debug_level_keypoints.argtypes = [vp, i32, i32, i32, vp, i32, C.POINTER(i32)]
     L.orbx_debug_octree.argtypes = [vp, i32, vp, i32, vp, i32, C.POINTER(i32)]
     L.orbm_argmin2_csr.argtypes = [vp, i32, vp, i32, vp, vp, vp, i32, vp, vp]

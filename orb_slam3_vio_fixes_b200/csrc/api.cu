@@ -10,6 +10,7 @@
 
 #include "../../include/orbx.h"
 #include "orbx_kernels.cuh"
+#include "orbx_core.h"
 
 static thread_local char g_err[256] = "";
 static void set_err(const char* what, cudaError_t e) {
@@ -62,7 +63,8 @@ struct orbx_extractor_s {
   cudaStream_t s_in = nullptr, s_out = nullptr, s_cmp[4] = {nullptr, nullptr, nullptr, nullptr};
   int host_streams = 2;  // compute streams the host batch pipeline rotates its chunks over (ORBX_HOST_STREAMS, 1..4)
   std::vector<cudaEvent_t> ev_in, ev_done;
-  cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
+  cudaEvent_t ev_fork = nullptr, ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
+  bool streams_ready = false;
   int host_chunk = 64;
   int host_edge = 0;   // length of the first and last chunk of a long host batch (ORBX_HOST_EDGE, 0 = off)
   int dev_split = 2;  // sub-batches of orbx_extract_batch_device (ORBX_DEVICE_SPLIT)
@@ -84,6 +86,47 @@ static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
   }
 }
 
+// Test hook kernel: order-independent 64-bit checksum per chunk of the device build of orbx_sincosf over the
+// float bit patterns lo, lo+1, ... (the nvcc compile of the glibc-exact sincosf the descriptor stage uses).
+__device__ __forceinline__ unsigned long long sincos_mix(uint32_t bits, float s, float c) {
+  unsigned long long h = ((unsigned long long)__float_as_uint(c) << 32) | __float_as_uint(s);
+  h = h * 0x9E3779B97F4A7C15ull + bits;
+  return h ^ (h >> 29);
+}
+__global__ void k_sincos_checksum(uint32_t lo, unsigned long long count, uint32_t chunk, unsigned long long* out) {
+  const unsigned long long c0 = (unsigned long long)blockIdx.x * chunk;
+  unsigned long long acc = 0;
+  for (unsigned long long i = c0 + threadIdx.x; i < c0 + chunk && i < count; i += blockDim.x) {
+    const uint32_t bits = lo + (uint32_t)i;
+    float s, c;
+    orbx_sincosf(__uint_as_float(bits), &s, &c);
+    acc += sincos_mix(bits, s, c);
+  }
+  atomicAdd(out + blockIdx.x, acc);
+}
+
+// Waits for everything the handle's internal streams still have in flight (error paths: no D2H copy
+// into the caller's buffers may outlive the call, and forked streams must not be left unjoined).
+static void drain_streams(orbx_extractor_s* h) {
+  if (h->s_in) cudaStreamSynchronize(h->s_in);
+  for (int i = 0; i < 4; i++)
+    if (h->s_cmp[i]) cudaStreamSynchronize(h->s_cmp[i]);
+  if (h->s_out) cudaStreamSynchronize(h->s_out);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+}
+
+// Reads and clears the device-side status word (bit 0: k_octree ran out of node pool and returned an
+// empty level).  The work that could set it must have completed.
+static int consume_status(orbx_extractor_s* h) {
+  int32_t st = 0;
+  cudaError_t e = cudaMemcpy(&st, h->status, sizeof(int32_t), cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) { set_err("status readback", e); return ORBX_E_CUDA; }
+  if (st == 0) return ORBX_OK;
+  cudaMemset(h->status, 0, sizeof(int32_t));
+  set_err("internal bound violated (octree node pool overflow): this call's keypoints are incomplete", cudaSuccess);
+  return ORBX_E_INTERNAL;
+}
+
 extern "C" {
 
 const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }
@@ -101,7 +144,7 @@ void orbx_destroy(orbx_handle h) {
   for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
   for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
-  for (int i = 0; i < 2; i++)
+  for (int i = 0; i < 4; i++)
     if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]);
   if (h->s_in) cudaStreamDestroy(h->s_in);
   if (h->s_out) cudaStreamDestroy(h->s_out);
@@ -200,23 +243,29 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   }
   ALLOC(h->border_tmp, (size_t)(P.lv[0].w + 2 * ORBX_EDGE) * (P.lv[0].h + 2 * ORBX_EDGE));
 #undef ALLOC
+  // from here on a failure must release the handle and its device buffers
+#define CUH(call)                                                     \
+  do {                                                                \
+    cudaError_t e_ = (call);                                          \
+    if (e_ != cudaSuccess) { set_err(#call, e_); orbx_destroy(h); return ORBX_E_CUDA; } \
+  } while (0)
   if (!xt.empty()) {
-    CU(cudaMemcpy(h->xtaps, xt.data(), xt.size() * sizeof(OrbxTap), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(h->ytaps, yt.data(), yt.size() * sizeof(OrbxTap), cudaMemcpyHostToDevice));
+    CUH(cudaMemcpy(h->xtaps, xt.data(), xt.size() * sizeof(OrbxTap), cudaMemcpyHostToDevice));
+    CUH(cudaMemcpy(h->ytaps, yt.data(), yt.size() * sizeof(OrbxTap), cudaMemcpyHostToDevice));
   }
   {
     std::vector<uint32_t> tab(P.total_cells);
     for (int l = 0; l < P.nlevels; l++)
       for (int c = 0; c < P.lv[l].nCols * P.lv[l].nRows; c++)
         tab[P.lv[l].cell_base + c] = ((uint32_t)l << 24) | ((uint32_t)(c / P.lv[l].nCols) << 12) | (uint32_t)(c % P.lv[l].nCols);
-    CU(cudaMemcpy(h->cell_tab, tab.data(), tab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    CUH(cudaMemcpy(h->cell_tab, tab.data(), tab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
   }
-  CU(cudaMemset(h->status, 0, sizeof(int32_t)));
-  CU(cudaMemset(h->arena, 0, B * P.arena_bytes + 512));
-  CU(orbx_octree_set_smem(h->oct_smem));
-  CU(orbx_describe_init_tables(P.umax));
+  CUH(cudaMemset(h->status, 0, sizeof(int32_t)));
+  CUH(cudaMemset(h->arena, 0, B * P.arena_bytes + 512));
+  CUH(orbx_describe_init_tables(P.umax));
   if (cfg->flags & ORBX_FLAG_STAGE_TIMING)
-    for (int i = 0; i <= ORBX_NUM_STAGES; i++) CU(cudaEventCreate(&h->ev[i]));
+    for (int i = 0; i <= ORBX_NUM_STAGES; i++) CUH(cudaEventCreate(&h->ev[i]));
+#undef CUH
   h->last_l0.base = h->arena; h->last_l0.frame_stride = P.arena_bytes; h->last_l0.pitch = P.lv[0].pitch;
   *out = h;
   return ORBX_OK;
@@ -228,16 +277,20 @@ int orbx_max_keypoints(orbx_handle h) { return h ? h->plan.max_keypoints : ORBX_
 // slots, selections) starts at frame slot f0 of the handle; l0 and the outputs point at the first
 // of those frames.
 static int ensure_streams(orbx_handle h) {
-  if (h->s_in) return ORBX_OK;
-  CU(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
-  CU(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
-  CU(cudaStreamCreateWithFlags(&h->s_cmp[0], cudaStreamNonBlocking));
-  CU(cudaStreamCreateWithFlags(&h->s_cmp[1], cudaStreamNonBlocking));
-  CU(cudaStreamCreateWithFlags(&h->s_cmp[2], cudaStreamNonBlocking));
-  CU(cudaStreamCreateWithFlags(&h->s_cmp[3], cudaStreamNonBlocking));
-  CU(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
-  CU(cudaEventCreateWithFlags(&h->ev_join[0], cudaEventDisableTiming));
-  CU(cudaEventCreateWithFlags(&h->ev_join[1], cudaEventDisableTiming));
+  if (h->streams_ready) return ORBX_OK;
+  // all or nothing: a partial failure releases what was created, so a later call starts over
+  cudaError_t e = cudaSuccess;
+  cudaStream_t* ss[6] = {&h->s_in, &h->s_out, &h->s_cmp[0], &h->s_cmp[1], &h->s_cmp[2], &h->s_cmp[3]};
+  cudaEvent_t* es[5] = {&h->ev_fork, &h->ev_join[0], &h->ev_join[1], &h->ev_join[2], &h->ev_join[3]};
+  for (int i = 0; i < 6 && e == cudaSuccess; i++) e = cudaStreamCreateWithFlags(ss[i], cudaStreamNonBlocking);
+  for (int i = 0; i < 5 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(es[i], cudaEventDisableTiming);
+  if (e != cudaSuccess) {
+    set_err("creating the handle's internal streams", e);
+    for (int i = 0; i < 6; i++) if (*ss[i]) { cudaStreamDestroy(*ss[i]); *ss[i] = nullptr; }
+    for (int i = 0; i < 5; i++) if (*es[i]) { cudaEventDestroy(*es[i]); *es[i] = nullptr; }
+    return ORBX_E_CUDA;
+  }
+  h->streams_ready = true;
   if (const char* e = getenv("ORBX_HOST_CHUNK")) { const int v = atoi(e); if (v > 0) h->host_chunk = v; }
   if (const char* e = getenv("ORBX_HOST_STREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 4) h->host_streams = v; }
   if (const char* e = getenv("ORBX_HOST_EDGE")) { const int v = atoi(e); if (v >= 0) h->host_edge = v; }
@@ -319,7 +372,7 @@ int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch
     rc = run_pipeline(h, l, nb, lap0, lap1, (OrbxKeyPointDev*)d_kps + (long long)f0 * capacity,
                       d_desc + (long long)f0 * capacity * 32, capacity, d_n_out + f0, d_mono_index + f0,
                       h->s_cmp[c & 1], f0, false);
-    if (rc) return rc;
+    if (rc) break;  // still join the forked streams back into the caller's stream below
   }
   for (int i = 0; i < 2; i++) {
     CU(cudaEventRecord(h->ev_join[i], h->s_cmp[i]));
@@ -328,7 +381,14 @@ int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch
   h->last_l0 = l0;
   h->last_batch = batch;
   h->timed = false;
-  return ORBX_OK;
+  return rc;
+}
+
+int orbx_check_status(orbx_handle h, void* stream) {
+  if (!h) return ORBX_E_INVALID;
+  CU(cudaSetDevice(h->device));
+  CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return consume_status(h);
 }
 
 int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int lap0, int lap1,
@@ -383,7 +443,7 @@ int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int l
     l0.base = h->stage + (size_t)f0 * W * H; l0.frame_stride = (long long)W * H; l0.pitch = W;
     int rc = run_pipeline(h, l0, nb, lap0, lap1, h->o_kps + (long long)f0 * mk, h->o_desc + (long long)f0 * mk * 32, mk,
                           h->o_n + f0, h->o_mono + f0, cs, f0, false);
-    if (rc) return rc;
+    if (rc) { drain_streams(h); return rc; }
     CU(cudaEventRecord(h->ev_done[c], cs));
     CU(cudaStreamWaitEvent(h->s_out, h->ev_done[c], 0));
     CU(cudaMemcpyAsync(n_out + f0, h->o_n + f0, nb * sizeof(int32_t), cudaMemcpyDeviceToHost, h->s_out));
@@ -398,7 +458,7 @@ int orbx_extract_batch_host(orbx_handle h, const uint8_t* imgs, int batch, int l
   h->last_batch = batch;
   CU(cudaStreamSynchronize(h->s_out));
   for (int i = 0; i < h->host_streams; i++) CU(cudaStreamSynchronize(h->s_cmp[i]));
-  return ORBX_OK;
+  return consume_status(h);
 }
 
 /* Device copies of what the last orbx_extract / orbx_extract_batch_host call returned (so that the
@@ -433,6 +493,7 @@ int orbx_extract(orbx_handle h, const uint8_t* img, int width, int height, size_
   CU(cudaStreamSynchronize(st));
   *n_out = nm[0];
   *mono_index = nm[1];
+  { const int rs = consume_status(h); if (rs) return rs; }
   if (nm[0] > capacity) { set_err("keypoint buffer too small", cudaSuccess); return ORBX_E_CAPACITY; }
   if (nm[0] > 0) {
     CU(cudaMemcpyAsync(kps, h->o_kps, (size_t)nm[0] * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st));
@@ -553,6 +614,39 @@ int orbx_stage_times(orbx_handle h, float* ms) {
   CU(cudaSetDevice(h->device));
   CU(cudaEventSynchronize(h->ev[ORBX_NUM_STAGES]));
   for (int i = 0; i < ORBX_NUM_STAGES; i++) CU(cudaEventElapsedTime(&ms[i], h->ev[i], h->ev[i + 1]));
+  return ORBX_OK;
+}
+
+/* Test hook: per-chunk checksums of the DEVICE orbx_sincosf over `count` consecutive float bit patterns from `lo`
+ * (chunk patterns per output word); tests compare them with the same checksum of glibc's sincosf. */
+int orbx_debug_sincos_checksum(int device, uint32_t lo, uint64_t count, uint32_t chunk, uint64_t* out, int n_out) {
+  if (!out || chunk == 0 || count == 0) return ORBX_E_INVALID;
+  const int nchunks = (int)((count + chunk - 1) / chunk);
+  if (n_out < nchunks) return ORBX_E_CAPACITY;
+  CU(cudaSetDevice(device));
+  unsigned long long* d = nullptr;
+  CU(cudaMalloc((void**)&d, (size_t)nchunks * 8));
+  cudaError_t e = cudaMemset(d, 0, (size_t)nchunks * 8);
+  if (e == cudaSuccess) {
+    k_sincos_checksum<<<nchunks, 256>>>(lo, count, chunk, d);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(out, d, (size_t)nchunks * 8, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) { set_err("orbx_debug_sincos_checksum", e); return ORBX_E_CUDA; }
+  return ORBX_OK;
+}
+
+/* Test hook: the blurred level the descriptor stage sampled (level-blur mode only), border-free. */
+int orbx_debug_blur_level(orbx_handle h, int frame, int level, uint8_t* dst, size_t dst_stride) {
+  if (!h || !dst || level < 0 || level >= h->plan.nlevels || frame < 0 || frame >= h->cfg.max_batch) return ORBX_E_INVALID;
+  if (!h->level_blur || !h->blur) { set_err("handle is not in level-blur mode", cudaSuccess); return ORBX_E_INVALID; }
+  const OrbxLevel& L = h->plan.lv[level];
+  if (dst_stride < (size_t)L.w) return ORBX_E_INVALID;
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpy2D(dst, dst_stride, h->blur + (long long)frame * h->plan.arena_bytes + L.offset, L.pitch, L.w, L.h,
+                  cudaMemcpyDeviceToHost));
   return ORBX_OK;
 }
 

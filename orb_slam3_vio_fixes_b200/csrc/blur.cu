@@ -7,175 +7,145 @@
 // the half taps t' = 9,17,24,28,24,17,9:  out = (sum_ij t'_i t'_j I + 2^13) >> 14  (the same integer).
 //
 // No shared memory, no barriers.  A thread owns one 32-bit word column (4 pixels) and walks BL_RB rows
-// down it; a warp = 32 adjacent word columns, so every load and store is one coalesced 128-byte access:
-//   row pass     the 12-byte window (x-4 .. x+7) of the new row is three L1-resident word loads; the four
-//                7-tap row sums are 6 funnel shifts + 8 dp4a against the packed half taps;
-//   column pass  the last 7 rows of row sums (4 x 7 registers) are combined with the symmetric form
-//                36(a0+a6) + 68(a1+a5) + 96(a2+a4) + 112 a3 + 2^15 (half taps x4: the result byte lands in
-//                bits 16..23), packed with PRMT and stored as one word.
-// BORDER_REFLECT_101: rows are reflected through the row index; at the left/right level edge the window
-// words of the (at most two) affected lanes are rebuilt from the loaded words with per-lane PRMT
-// selectors computed once before the walk (warps that touch no edge run the plain path).
+// down it; a warp = 32 adjacent word columns (lanes 1..30 produce output, lanes 0 and 31 carry the
+// horizontal halo), so every load and store is one coalesced access and each pixel is loaded ONCE:
+//   column pass  first, on the raw bytes: the word is split into its even / odd bytes (two pixels per
+//                register in 16-bit lanes); with the half taps the 7-row sum of a pixel is <= 255*128 =
+//                32640, so 9(a0+a6) + 17(a1+a5) + 24(a2+a4) + 28 a3 runs on two pixels per IADD / IMAD;
+//   row pass     the neighbours' column sums come from the adjacent lanes (4 SHFL); the 7-tap row sums of
+//                the four pixels are 18 dp2a (u16x2 . u8x2) against the half taps x4 (36,68,96,112: the
+//                rounded result byte then lands in bits 16..23), packed with PRMT and stored as one word.
+// Loads run four rows ahead of the arithmetic (the kernel was latency-bound on its row loads
+// with a one-row prefetch: profiles/r2a_*).
+// BORDER_REFLECT_101: rows are reflected through the row index; a lane whose word is not entirely inside [0,w)
+// rebuilds it from the two aligned words that hold its four reflected columns (one PRMT, selector per lane).
 #include "orbx_kernels.cuh"
 
-#define BL_RB ORBX_BLUR_ROWS  // 35 output rows per thread (a multiple of 7: the row-sum window is indexed statically)
+#define BL_RB ORBX_BLUR_ROWS  // 35 output rows per thread (a multiple of 7: the row window is indexed statically)
 #define BL_WARPS 4
-#define BL_TA 0x1c181109u  // half taps 9,17,24,28 on window bytes x-3 .. x
-#define BL_TB 0x00091118u  // half taps 24,17,9,0  on window bytes x+1 .. x+4
+#define BL_TW ORBX_BLUR_TILE_WORDS  // 30 output words per warp row
 
-struct BlurEdge {  // per-lane fix-ups of the window words at the level's left / right edge
-  uint32_t s0, s1, s2a, s2b;
-  bool has_l, has_r, w2_from_01;
-};
+// even / odd bytes of a word as two 16-bit lanes each
+#define BL_EVEN(w) __byte_perm((w), 0u, 0x4240)
+#define BL_ODD(w) __byte_perm((w), 0u, 0x4341)
 
-// selector nibble source: window byte si (0..11 = columns x-4 .. x+7) relative to the register pair
-// (R0,R1) -> si, or (R1,R2) -> si-4
-__device__ __forceinline__ BlurEdge blur_edge_setup(int x, int w, int pitch) {
-  BlurEdge e;
-  e.has_l = x >= 4;
-  e.has_r = x + 8 <= pitch;
-  int si[12];
-#pragma unroll
-  for (int i = 0; i < 12; i++) {
-    int c = x - 4 + i;
-    if (c < 0) c = -c;
-    if (c >= w) c = 2 * (w - 1) - c;
-    int s = c - (x - 4);
-    si[i] = s < 0 ? 0 : (s > 11 ? 11 : s);
-  }
-  // when R0 / R2 cannot be loaded they are replaced by R1; bytes that would come from them are unused
-  e.s0 = (uint32_t)(si[0] & 7) | ((uint32_t)(si[1] & 7) << 4) | ((uint32_t)(si[2] & 7) << 8) | ((uint32_t)(si[3] & 7) << 12);
-  e.s1 = (uint32_t)(si[4] & 7) | ((uint32_t)(si[5] & 7) << 4) | ((uint32_t)(si[6] & 7) << 8) | ((uint32_t)(si[7] & 7) << 12);
-  // W2: sources either all in (R1,R2) (si >= 4) or, when the level ends inside this lane's word, in (R0,R1)
-  e.w2_from_01 = (w - 1) < x + 3;
-  e.s2a = e.s2b = 0;
-#pragma unroll
-  for (int j = 0; j < 4; j++) {
-    const int s = si[8 + j];
-    e.s2a |= (uint32_t)(s & 7) << (4 * j);                        // from (R0,R1): valid when s < 8
-    e.s2b |= (uint32_t)((s >= 4 ? s - 4 : 0) & 7) << (4 * j);      // from (R1,R2): valid when s >= 4
-  }
-  return e;
+__device__ __forceinline__ uint32_t blur_vsum(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t a4,
+                                              uint32_t a5, uint32_t a6) {
+  return 9u * (a0 + a6) + 17u * (a1 + a5) + 24u * (a2 + a4) + 28u * a3;
 }
 
-// The three raw window words of one image row (next row is fetched while the current one is being filtered).
-struct BlurRaw { uint32_t r0, r1, r2; };
-
-template <bool EDGE>
-__device__ __forceinline__ BlurRaw blur_load(const uint8_t* __restrict__ rowp, bool active, const BlurEdge& e) {
-  BlurRaw v;
-  const uint32_t* p = reinterpret_cast<const uint32_t*>(rowp);
-  if (!EDGE) {
-    v.r0 = __ldg(p - 1); v.r1 = __ldg(p); v.r2 = __ldg(p + 1);
-  } else {
-    v.r0 = v.r1 = v.r2 = 0;
-    if (active) {
-      v.r1 = __ldg(p);
-      v.r0 = e.has_l ? __ldg(p - 1) : v.r1;
-      v.r2 = e.has_r ? __ldg(p + 1) : v.r1;
-    }
-  }
-  return v;
+// Row pass + pack for this lane's 4 pixels from the column sums of pixels -4..7 around it:
+// Le=(V-4,V-2) Lo=(V-3,V-1) Ce=(V0,V2) Co=(V1,V3) Re=(V4,V6) Ro=(V5,V7), 16-bit lanes (low, high).
+#define BL_K(lo, hi) ((uint32_t)(lo) | ((uint32_t)(hi) << 8))
+__device__ __forceinline__ uint32_t blur_hsum(uint32_t Le, uint32_t Lo, uint32_t Ce, uint32_t Co, uint32_t Re,
+                                              uint32_t Ro) {
+  uint32_t a0 = __dp2a_lo(Lo, BL_K(36, 96), 32768u);   // 36 V-3 + 96 V-1
+  a0 = __dp2a_lo(Le, BL_K(0, 68), a0);                 // 68 V-2
+  a0 = __dp2a_lo(Ce, BL_K(112, 68), a0);               // 112 V0 + 68 V2
+  a0 = __dp2a_lo(Co, BL_K(96, 36), a0);                // 96 V1 + 36 V3
+  uint32_t a1 = __dp2a_lo(Le, BL_K(0, 36), 32768u);    // 36 V-2
+  a1 = __dp2a_lo(Lo, BL_K(0, 68), a1);                 // 68 V-1
+  a1 = __dp2a_lo(Ce, BL_K(96, 96), a1);                // 96 V0 + 96 V2
+  a1 = __dp2a_lo(Co, BL_K(112, 68), a1);               // 112 V1 + 68 V3
+  a1 = __dp2a_lo(Re, BL_K(36, 0), a1);                 // 36 V4
+  uint32_t a2 = __dp2a_lo(Lo, BL_K(0, 36), 32768u);    // 36 V-1
+  a2 = __dp2a_lo(Ce, BL_K(68, 112), a2);               // 68 V0 + 112 V2
+  a2 = __dp2a_lo(Co, BL_K(96, 96), a2);                // 96 V1 + 96 V3
+  a2 = __dp2a_lo(Re, BL_K(68, 0), a2);                 // 68 V4
+  a2 = __dp2a_lo(Ro, BL_K(36, 0), a2);                 // 36 V5
+  uint32_t a3 = __dp2a_lo(Ce, BL_K(36, 96), 32768u);   // 36 V0 + 96 V2
+  a3 = __dp2a_lo(Co, BL_K(68, 112), a3);               // 68 V1 + 112 V3
+  a3 = __dp2a_lo(Re, BL_K(96, 36), a3);                // 96 V4 + 36 V6
+  a3 = __dp2a_lo(Ro, BL_K(68, 0), a3);                 // 68 V5
+  return __byte_perm(__byte_perm(a0, a1, 0x0062), __byte_perm(a2, a3, 0x0062), 0x5410);
 }
 
-// Row sums for this lane's 4 pixels.  EDGE: lanes at the level border rebuild their window first.
-template <bool EDGE>
-__device__ __forceinline__ void blur_row_sums(const BlurRaw& v, const BlurEdge& e, uint32_t (&H)[4]) {
-  uint32_t w0 = v.r0, w1 = v.r1, w2 = v.r2;
+// EDGE  = some lane of the warp has a word that is not entirely inside [0,w) (warp-uniform);
+// VEDGE = the tile touches the first / last rows of the level or is shorter than BL_RB rows.
+template <bool EDGE, bool VEDGE>
+__device__ __forceinline__ void blur_walk(const uint8_t* __restrict__ img, int pitch, int w, int h, int wq, int y0,
+                                          uint8_t* __restrict__ out, int opitch, int lane) {
+  const int c = 4 * wq;
+  // EDGE: the lane's four columns reflected into [0,w) are 4 consecutive-ish columns, so they always lie in two
+  // adjacent aligned words: two word loads (byte offsets qa, qb) and one PRMT with a per-lane selector rebuild the
+  // lane's word; interior lanes of the same warp get the identity selector.  No divergence, no byte loads.
+  int qa = c, qb = c;
+  uint32_t sel = 0x3210u;
   if (EDGE) {
-    w0 = __byte_perm(v.r0, v.r1, e.s0);
-    w1 = __byte_perm(v.r0, v.r1, e.s1);
-    const uint32_t ua = __byte_perm(v.r0, v.r1, e.s2a), ub = __byte_perm(v.r1, v.r2, e.s2b);
-    w2 = e.w2_from_01 ? ua : ub;
-  }
-  H[0] = __dp4a(__funnelshift_r(w0, w1, 8), BL_TA, __dp4a(__funnelshift_r(w1, w2, 8), BL_TB, 0u));
-  H[1] = __dp4a(__funnelshift_r(w0, w1, 16), BL_TA, __dp4a(__funnelshift_r(w1, w2, 16), BL_TB, 0u));
-  H[2] = __dp4a(__funnelshift_r(w0, w1, 24), BL_TA, __dp4a(__funnelshift_r(w1, w2, 24), BL_TB, 0u));
-  H[3] = __dp4a(w1, BL_TA, __dp4a(w2, BL_TB, 0u));
-}
-
-// Column pass for one output row: H rows oldest..newest = a0..a6.  The column taps are the half taps x4, so
-// the rounded result byte sits in bits 16..23 of the accumulator and PRMT packs four of them.
-__device__ __forceinline__ uint32_t blur_col(const uint32_t (&a0)[4], const uint32_t (&a1)[4], const uint32_t (&a2)[4],
-                                             const uint32_t (&a3)[4], const uint32_t (&a4)[4], const uint32_t (&a5)[4],
-                                             const uint32_t (&a6)[4]) {
-  uint32_t acc[4];
+    int xs[4], lo = 1 << 30;
 #pragma unroll
-  for (int k = 0; k < 4; k++)
-    acc[k] = 36u * (a0[k] + a6[k]) + 68u * (a1[k] + a5[k]) + 96u * (a2[k] + a4[k]) + 112u * a3[k] + 32768u;
-  return __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
-}
-
-// ROWS: VEDGE = the tile touches the first / last rows of the level (row index reflected per row);
-// FULL = the tile has all BL_RB output rows (static trip counts).
-template <bool EDGE, bool VEDGE, bool FULL>
-__device__ __forceinline__ void blur_walk(const uint8_t* __restrict__ img, int pitch, int w, int h, int x, int y0,
-                                          bool active, uint8_t* __restrict__ out, int opitch) {
-  BlurEdge e = {};
-  if (EDGE) e = blur_edge_setup(x, w, pitch);
-  else active = true;
-  const int nout = FULL ? BL_RB : min(BL_RB, h - y0);
-  uint32_t H[7][4];
-  const uint8_t* colp = img + x;
-  const uint8_t* rowp = colp + (long long)(y0 - 3) * pitch;  // !VEDGE: rows y0-3 .. y0+nout+3 are all inside
-  uint8_t* op = out + (long long)y0 * opitch + x;
+    for (int j = 0; j < 4; j++) {
+      int x = c + j;
+      x = x < 0 ? -x : x;
+      x = x >= w ? 2 * (w - 1) - x : x;
+      xs[j] = x < 0 ? 0 : (x >= w ? w - 1 : x);  // lanes further out are never used: any valid column will do
+      lo = min(lo, xs[j]);
+    }
+    qa = lo & ~3;
+    qb = qa;
+    sel = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      if (xs[j] >= qa + 4) qb = qa + 4;
+      sel |= (uint32_t)(xs[j] - qa) << (4 * j);
+    }
+  }
+  const int nout = VEDGE ? min(BL_RB, h - y0) : BL_RB;
+  auto fetch = [&](int yy) -> uint32_t {
+    int sy = yy;
+    if (VEDGE) {
+      sy = sy < 0 ? -sy : sy;
+      sy = sy >= h ? 2 * (h - 1) - sy : sy;
+      sy = sy < 0 ? 0 : (sy >= h ? h - 1 : sy);  // rows past the reflected band are never used
+    }
+    const uint8_t* rp = img + (long long)sy * pitch;
+    if (!EDGE) return __ldg(reinterpret_cast<const uint32_t*>(rp + c));
+    return __byte_perm(__ldg(reinterpret_cast<const uint32_t*>(rp + qa)), __ldg(reinterpret_cast<const uint32_t*>(rp + qb)),
+                       sel);
+  };
+  const bool writer = lane >= 1 && lane <= BL_TW && c < w;  // c >= 0 for lanes >= 1
+  uint8_t* op = out + (long long)y0 * opitch + c;
+  // E/O: the last 7 source rows (even / odd bytes), slot = source row mod 7; q0..q3: raw words of the next four
+  // source rows, already on their way (the loads run 4 rows ahead of the arithmetic).  Source row r of the walk
+  // is level row y0 - 3 + r; output row o needs source rows o .. o+6.
+  uint32_t E[7], O[7];
   int yy = y0 - 3;
-  const int ylast = y0 + nout + 2;  // last source row (unreflected index) this tile needs
-  if (VEDGE) {
-    int sy = yy < 0 ? -yy : yy;
-    sy = sy >= h ? 2 * (h - 1) - sy : sy;
-    rowp = colp + (long long)sy * pitch;
-  }
-  BlurRaw nxt = blur_load<EDGE>(rowp, active, e);
-  // filter the prefetched row into H[slot] after issuing the loads of the row below it
-#define BLUR_ROW(slot)                                                            \
-  do {                                                                            \
-    const BlurRaw cur = nxt;                                                      \
-    yy++;                                                                         \
-    if (VEDGE) {                                                                  \
-      int sy = yy < 0 ? -yy : yy;                                                 \
-      sy = sy >= h ? 2 * (h - 1) - sy : sy;                                       \
-      rowp = colp + (long long)sy * pitch;                                        \
-    } else {                                                                      \
-      rowp += pitch;                                                              \
-    }                                                                             \
-    if (FULL || yy <= ylast) nxt = blur_load<EDGE>(rowp, active, e);              \
-    blur_row_sums<EDGE>(cur, e, H[slot]);                                         \
+  uint32_t q0 = fetch(yy), q1 = fetch(yy + 1), q2 = fetch(yy + 2), q3 = fetch(yy + 3);
+  yy += 4;
+#define BL_ROW(s)                                    \
+  do {                                               \
+    const uint32_t raw = q0;                         \
+    q0 = q1; q1 = q2; q2 = q3; q3 = fetch(yy); yy++; \
+    E[s] = BL_EVEN(raw); O[s] = BL_ODD(raw);         \
   } while (0)
-#define BLUR_OUT(s)                                                                                           \
-  do {                                                                                                        \
-    const uint32_t v = blur_col(H[(s + 1) % 7], H[(s + 2) % 7], H[(s + 3) % 7], H[(s + 4) % 7], H[(s + 5) % 7], \
-                                H[(s + 6) % 7], H[s]);                                                        \
-    if (active) *reinterpret_cast<uint32_t*>(op) = v;                                                         \
-    op += opitch;                                                                                             \
+#define BL_OUT(s)                                                                                                  \
+  do {                                                                                                             \
+    const uint32_t Ce = blur_vsum(E[(s + 1) % 7], E[(s + 2) % 7], E[(s + 3) % 7], E[(s + 4) % 7], E[(s + 5) % 7],   \
+                                  E[(s + 6) % 7], E[s]);                                                           \
+    const uint32_t Co = blur_vsum(O[(s + 1) % 7], O[(s + 2) % 7], O[(s + 3) % 7], O[(s + 4) % 7], O[(s + 5) % 7],   \
+                                  O[(s + 6) % 7], O[s]);                                                           \
+    const uint32_t Le = __shfl_up_sync(0xffffffffu, Ce, 1), Lo = __shfl_up_sync(0xffffffffu, Co, 1);               \
+    const uint32_t Re = __shfl_down_sync(0xffffffffu, Ce, 1), Ro = __shfl_down_sync(0xffffffffu, Co, 1);           \
+    const uint32_t v = blur_hsum(Le, Lo, Ce, Co, Re, Ro);                                                          \
+    if (writer && (!VEDGE || left > 0)) *reinterpret_cast<uint32_t*>(op) = v;                                      \
+    op += opitch;                                                                                                  \
+    if (VEDGE) left--;                                                                                             \
   } while (0)
-  BLUR_ROW(0); BLUR_ROW(1); BLUR_ROW(2); BLUR_ROW(3); BLUR_ROW(4); BLUR_ROW(5);
-  if (FULL) {
+  int left = nout;
+  BL_ROW(0); BL_ROW(1); BL_ROW(2); BL_ROW(3); BL_ROW(4); BL_ROW(5);
+  // (the queue runs up to 4 source rows past the last one used: in range for !VEDGE tiles, clamped otherwise)
 #pragma unroll 1
-    for (int g = 0; g < BL_RB / 7; g++) {
-      BLUR_ROW(6); BLUR_OUT(6);
-      BLUR_ROW(0); BLUR_OUT(0);
-      BLUR_ROW(1); BLUR_OUT(1);
-      BLUR_ROW(2); BLUR_OUT(2);
-      BLUR_ROW(3); BLUR_OUT(3);
-      BLUR_ROW(4); BLUR_OUT(4);
-      BLUR_ROW(5); BLUR_OUT(5);
-    }
-  } else {
-    int left = nout;
-#pragma unroll 1
-    while (left > 0) {
-      BLUR_ROW(6); BLUR_OUT(6); if (--left == 0) break;
-      BLUR_ROW(0); BLUR_OUT(0); if (--left == 0) break;
-      BLUR_ROW(1); BLUR_OUT(1); if (--left == 0) break;
-      BLUR_ROW(2); BLUR_OUT(2); if (--left == 0) break;
-      BLUR_ROW(3); BLUR_OUT(3); if (--left == 0) break;
-      BLUR_ROW(4); BLUR_OUT(4); if (--left == 0) break;
-      BLUR_ROW(5); BLUR_OUT(5); --left;
-    }
+  for (int g = 0; g < BL_RB / 7; g++) {
+    BL_ROW(6); BL_OUT(6);
+    BL_ROW(0); BL_OUT(0);
+    BL_ROW(1); BL_OUT(1);
+    BL_ROW(2); BL_OUT(2);
+    BL_ROW(3); BL_OUT(3);
+    BL_ROW(4); BL_OUT(4);
+    BL_ROW(5); BL_OUT(5);
   }
-#undef BLUR_ROW
-#undef BLUR_OUT
+#undef BL_ROW
+#undef BL_OUT
 }
 
 // Unaligned level-0 input (caller's buffer with an odd pitch or base): same arithmetic from byte loads.
@@ -208,7 +178,7 @@ __device__ __forceinline__ void blur_walk_bytes(const uint8_t* __restrict__ img,
 
 __global__ void __launch_bounds__(BL_WARPS * 32)
 k_blur_levels(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
-              uint8_t* __restrict__ blur) {
+              uint8_t* __restrict__ blur, int l0_bytes) {
   const int lane = threadIdx.x & 31, frame = blockIdx.y;
   int tile = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
   if (tile >= P.total_btiles) return;
@@ -220,32 +190,50 @@ k_blur_levels(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __res
   tile -= L.btile_base;
   const int ty = tile / L.btiles_x, tx = tile - ty * L.btiles_x;
   const int w = L.w, h = L.h;
-  const int x = 4 * (tx * 32 + lane), y0 = ty * BL_RB;
+  const int y0 = ty * BL_RB;
   int pitch;
   const uint8_t* img;
   if (level == 0) { pitch = l0.pitch; img = l0.base + (long long)frame * l0.frame_stride; }
   else { pitch = L.pitch; img = arena + (long long)frame * P.arena_bytes + L.offset; }
   uint8_t* out = blur + (long long)frame * P.arena_bytes + L.offset;
-  const bool active = x < w;
-  if ((pitch & 3) != 0 || ((uintptr_t)img & 3) != 0) {
-    blur_walk_bytes(img, pitch, w, h, x, y0, active, out, L.pitch);
-    return;
-  }
-  // warp-uniform: does any lane's 12-byte window leave [0, w)?
-  const bool edge = tx == 0 || 4 * (tx * 32 + 33) > w;
-  const bool full = y0 + BL_RB <= h;
-  const bool vedge = y0 < 3 || y0 + BL_RB + 4 > h;  // FULL tiles also fetch one row past their last
-  if (full && !vedge) {
-    if (edge) blur_walk<true, false, true>(img, pitch, w, h, x, y0, active, out, L.pitch);
-    else blur_walk<false, false, true>(img, pitch, w, h, x, y0, active, out, L.pitch);
+  if (level == 0 && l0_bytes) return;  // unaligned caller buffer: k_blur_level0_bytes does level 0
+  const int wq = tx * BL_TW + lane - 1;  // word column of this lane; lanes 0 and 31 are halo
+  // warp-uniform: is any lane's word (word columns tx*BL_TW-1 .. tx*BL_TW+30) not entirely inside [0,w)?
+  const bool edge = tx == 0 || 4 * (tx * BL_TW + BL_TW + 1) > w;
+  // the walk fetches source rows y0-3 .. y0+BL_RB+2
+  const bool vedge = y0 < 3 || y0 + BL_RB + 7 > h;  // (the load queue runs 4 rows past the last row it uses)
+  if (!vedge) {
+    if (edge) blur_walk<true, false>(img, pitch, w, h, wq, y0, out, L.pitch, lane);
+    else blur_walk<false, false>(img, pitch, w, h, wq, y0, out, L.pitch, lane);
   } else {  // first / last tile rows of a level: one generic variant (keeps the code footprint small)
-    blur_walk<true, true, false>(img, pitch, w, h, x, y0, active, out, L.pitch);
+    blur_walk<true, true>(img, pitch, w, h, wq, y0, out, L.pitch, lane);
   }
+}
+
+// Level 0 of a caller-owned buffer whose pitch or base is not a multiple of 4: the same arithmetic from byte loads.
+__global__ void __launch_bounds__(BL_WARPS * 32)
+k_blur_level0_bytes(const __grid_constant__ DevPlan P, Level0 l0, uint8_t* __restrict__ blur) {
+  const int lane = threadIdx.x & 31, frame = blockIdx.y;
+  const int tile = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
+  const DevLevel& L = P.lv[0];
+  const int ntiles = P.nlevels > 1 ? P.lv[1].btile_base : P.total_btiles;
+  if (tile >= ntiles) return;
+  const int ty = tile / L.btiles_x, tx = tile - ty * L.btiles_x;
+  const int x = 4 * (tx * BL_TW + lane);
+  if (lane < BL_TW)
+    blur_walk_bytes(l0.base + (long long)frame * l0.frame_stride, l0.pitch, L.w, L.h, x, ty * BL_RB, x < L.w,
+                    blur + (long long)frame * P.arena_bytes + L.offset, L.pitch);
 }
 
 cudaError_t orbx_launch_blur(const DevPlan& P, Level0 l0, const uint8_t* arena, uint8_t* blur, int batch,
                              cudaStream_t st) {
+  const int l0_bytes = ((l0.pitch & 3) != 0 || ((uintptr_t)l0.base & 3) != 0 || (l0.frame_stride & 3) != 0) ? 1 : 0;
   dim3 grd((P.total_btiles + BL_WARPS - 1) / BL_WARPS, batch);
-  k_blur_levels<<<grd, BL_WARPS * 32, 0, st>>>(P, l0, arena, blur);
+  k_blur_levels<<<grd, BL_WARPS * 32, 0, st>>>(P, l0, arena, blur, l0_bytes);
+  if (l0_bytes) {
+    const int nt0 = P.nlevels > 1 ? P.lv[1].btile_base : P.total_btiles;
+    dim3 g0((nt0 + BL_WARPS - 1) / BL_WARPS, batch);
+    k_blur_level0_bytes<<<g0, BL_WARPS * 32, 0, st>>>(P, l0, blur);
+  }
   return cudaGetLastError();
 }

@@ -502,12 +502,7 @@ extern "C" int orbm_bow_transform(const orbm_vocabulary* voc, const uint8_t* d_d
   int np2 = BV_THREADS;
   while (np2 < kp_stride) np2 <<= 1;
   const size_t smem = (size_t)np2 * sizeof(unsigned long long);
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(k_bow_vectors, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8) != cudaSuccess)
-      return ORBX_E_CUDA;
-    attr_set = true;
-  }
+  if (orbx_ensure_dyn_smem(ORBX_SMEM_BOW_VECTORS, (const void*)k_bow_vectors, smem) != cudaSuccess) return ORBX_E_CUDA;
   k_bow_vectors<<<batch, BV_THREADS, smem, st>>>(d_n, kp_stride, node_stride, np2, d_feat_word, d_feat_node,
                                                  d_feat_weight, fv_out->d_node, fv_out->d_off, fv_out->d_idx,
                                                  fv_out->d_nn, d_bow_word, d_bow_val, d_bow_n);

@@ -420,8 +420,6 @@ k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__
   if (lane == 0) *cnt_out = total;
 }
 
-static int g_fast_smem_set = 0;
-
 cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* cell_tab,
                              int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st) {
   // shared-memory geometry from the largest cell of the plan
@@ -434,11 +432,8 @@ cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, 
   }
   cap = (cap + 8 + 15) & ~15;  // quads per cell (bytes of qm) + one spare uint2, regions stay 8-byte aligned
   const size_t smem = (size_t)FAST_WARPS * (2 * pw * rows + FAST_LIST_CAP / 2 + (cap >> 2)) * sizeof(uint32_t);
-  if ((int)smem > g_fast_smem_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    g_fast_smem_set = (int)smem;
-  }
+  cudaError_t e = orbx_ensure_dyn_smem(ORBX_SMEM_FAST, (const void*)k_fast, smem);
+  if (e != cudaSuccess) return e;
   dim3 grd((P.total_cells + FAST_WARPS - 1) / FAST_WARPS, batch);
   k_fast<<<grd, FAST_THREADS, smem, st>>>(P, l0, arena, cell_tab, cell_cnt, cand, pw, rows, cap);
   return cudaGetLastError();

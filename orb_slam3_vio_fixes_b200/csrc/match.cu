@@ -590,11 +590,7 @@ int orbm_stereo_rowband(const orbx_keypoint* d_kps_l, const uint8_t* d_desc_l, c
   const size_t smem = (size_t)RB_SPAN * kp_stride * sizeof(uint16_t);
   if (kp_stride < 65536 && smem <= 160 * 1024 && 4.0f * smax + 3.0f <= (float)((RB_SPAN - 1) << RB_SHIFT)) {
     // bucketed by row: a band of <= 4*scale+3 rows touches at most RB_SPAN buckets
-    static bool attr_set = false;
-    if (smem > 48 * 1024 && !attr_set) {
-      CUM(cudaFuncSetAttribute(k_stereo_rowband_binned, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-      attr_set = true;
-    }
+    CUM(orbx_ensure_dyn_smem(ORBX_SMEM_ROWBAND, (const void*)k_stereo_rowband_binned, smem));
     dim3 grd(4, batch);
     k_stereo_rowband_binned<<<grd, RB_THREADS, smem, (cudaStream_t)stream>>>(
         (const OrbxKeyPointDev*)d_kps_l, d_desc_l, d_n_l, (const OrbxKeyPointDev*)d_kps_r, d_desc_r, d_n_r, kp_stride,

@@ -301,14 +301,29 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
   }
 }
 
-cudaError_t orbx_octree_set_smem(size_t bytes) {
-  return cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+#include <mutex>
+cudaError_t orbx_ensure_dyn_smem(OrbxSmemSlot slot, const void* func, size_t bytes) {
+  static std::mutex mu;
+  static int have[64][ORBX_SMEM_SLOTS];  // zero-initialised; 48 KB needs no opt-in
+  if (bytes <= 48 * 1024) return cudaSuccess;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lk(mu);
+  if (dev < 0 || dev >= 64) return cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if ((int)bytes <= have[dev][slot]) return cudaSuccess;
+  e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e == cudaSuccess) have[dev][slot] = (int)bytes;
+  return e;
 }
 
 cudaError_t orbx_launch_octree(const DevPlan& P, const int32_t* cell_cnt, const uint32_t* cand,
                                uint32_t* gkeys, int16_t* glabels, uint32_t* sel, int32_t* sel_cnt,
                                int32_t* status, int batch, size_t smem_bytes, int smem_keys, int node_cap,
                                int max_cells, cudaStream_t st) {
+  // the opt-in is per (function, device) and is only ever raised (a smaller handle created later must not lower it)
+  cudaError_t e = orbx_ensure_dyn_smem(ORBX_SMEM_OCTREE, (const void*)k_octree, smem_bytes);
+  if (e != cudaSuccess) return e;
   dim3 grd(P.nlevels, batch);
   k_octree<<<grd, OCT_THREADS, smem_bytes, st>>>(P, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, status,
                                                  smem_keys, node_cap, max_cells);

@@ -92,4 +92,9 @@ cudaError_t orbx_describe_init_tables(const int* umax);
 cudaError_t orbx_launch_border(const uint8_t* src, int pitch, int w, int h, uint8_t* dst, int dst_pitch,
                                cudaStream_t st);
 size_t orbx_octree_smem_bytes(int smem_keys, int node_cap, int max_cells);
-cudaError_t orbx_octree_set_smem(size_t bytes);
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to (function, device), not to a handle: this keeps a
+// per-device, monotone (only ever raised) cache per kernel slot, under a mutex, so handles of different sizes,
+// on different devices, created from different threads never lower or miss each other's opt-in.
+enum OrbxSmemSlot { ORBX_SMEM_FAST = 0, ORBX_SMEM_OCTREE, ORBX_SMEM_BOW_VECTORS, ORBX_SMEM_ROWBAND, ORBX_SMEM_SLOTS };
+cudaError_t orbx_ensure_dyn_smem(OrbxSmemSlot slot, const void* func, size_t bytes);

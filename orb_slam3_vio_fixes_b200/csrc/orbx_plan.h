@@ -13,6 +13,7 @@
 
 #define ORBX_PLAN_MAX_LEVELS 12
 #define ORBX_BLUR_ROWS 35  // rows per warp tile of k_blur_levels (blur.cu BL_RB)
+#define ORBX_BLUR_TILE_WORDS 30  // output words (4 px) per warp tile row: lanes 1..30, lanes 0/31 are halo
 
 struct OrbxLevel {
   int w, h;          // level size (cvRound(cols*inv), cvRound(rows*inv))
@@ -34,7 +35,7 @@ struct OrbxLevel {
   int xtab, ytab;  // offsets into the resize tables (entries), level>=1
   int fast_resize;  // the 4-column tap windows of k_resize_walk hold for every column group
   int tile_resize;  // every 128x64 output tile fits k_resize_tile's shared-memory source window
-  int btile_base, btiles_x;  // warp tiles (32 words x ORBX_BLUR_ROWS rows) of k_blur_levels: first tile of this level, tiles per row
+  int btile_base, btiles_x;  // warp tiles (ORBX_BLUR_TILE_WORDS words x ORBX_BLUR_ROWS rows) of k_blur_levels: first tile of this level, tiles per row
 };
 
 struct OrbxPlan {
@@ -116,7 +117,7 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
     L.offset = offset;
     offset += (long long)L.pitch * L.h;
     L.btile_base = btiles;
-    L.btiles_x = (L.w + 127) / 128;
+    L.btiles_x = ((L.w + 3) / 4 + ORBX_BLUR_TILE_WORDS - 1) / ORBX_BLUR_TILE_WORDS;
     btiles += L.btiles_x * ((L.h + ORBX_BLUR_ROWS - 1) / ORBX_BLUR_ROWS);
     L.scale = P->scale[l];
     L.patch_size = (float)(int)(31 * P->scale[l]);

@@ -233,6 +233,13 @@ class ORBextractor:
                                                 C.byref(n)), "orbx_debug_octree")
         return out[:n.value].copy()
 
+    def debug_blur_level(self, level, frame=0):
+        """The blurred level the descriptor stage sampled (level-blur mode), as an [h,w] array."""
+        w, h = self.level_size(level)
+        out = np.zeros((h, w), np.uint8)
+        _lib.check(_lib.lib().orbx_debug_blur_level(self._h, frame, level, out.ctypes.data, w), "orbx_debug_blur_level")
+        return out
+
     def debug_level_keypoints(self, level, stage, frame=0):
         cap = 1 << 16
         while True:

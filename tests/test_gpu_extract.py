@@ -207,3 +207,56 @@ def test_host_batch_chunk_schedules_give_identical_bytes(monkeypatch, chunk, edg
     assert np.array_equal(m2, out["mono"].cpu().numpy())
     for f in range(B):
         assert np.array_equal(k2[f, :n[f]], kps[f, :n[f]]) and np.array_equal(d2[f, :n[f]], desc[f, :n[f]])
+
+
+@pytest.mark.parametrize("size", [(752, 480), (640, 480), (501, 317), (502, 300), (503, 301), (500, 299), (1241, 376)])
+def test_blur_levels_match_oracle(oracle_mod, size):
+    """Level-blur mode: every blurred pyramid level == GaussianBlur(7x7, sigma 2, REFLECT_101) of that level
+    (ORBextractor.cc:1131-1133), all pixels including the 3-px reflected frame, for level widths of every residue
+    mod 4 (the last word of a row is partial) and tile edges in both directions."""
+    w, h = size
+    frames = S.make_frames("C1", 2, width=w, height=h)
+    ex = ORBextractor(800, max_batch=2, blur_mode="level", **ORB).plan(w, h)
+    import torch
+    ex.extract_batch_device(torch.from_numpy(frames).cuda(), (0, 0))
+    torch.cuda.synchronize()
+    orc = oracle_mod.Extractor(800, 1.2, 8, 20, 7)
+    for f in (0, 1):
+        orc.extract(frames[f], (0, 0))
+        for level in range(8):
+            got = ex.debug_blur_level(level, frame=f)
+            ref = oracle_mod.gaussian_blur7(orc.pyramid(level))
+            bad = np.argwhere(got != ref)
+            assert len(bad) == 0, f"{size} frame {f} level {level} {got.shape}: {len(bad)} px differ, first {bad[:4].tolist()}"
+
+
+def test_handles_of_different_sizes_coexist(oracle_mod):
+    """the octree's dynamic-shared-memory opt-in belongs to (function, device), not to a handle.  The mono
+    initialisation extractor (5*nFeatures, Tracking.cc:595-601) is created first, the regular one afterwards; the
+    big handle must still run."""
+    img = S.make_frames("C3", 1)[0]
+    big = ORBextractor(5000, **ORB)
+    mono_b, k_b, d_b = big(img, None, (0, 1000))
+    small = ORBextractor(1000, **ORB)
+    mono_s, k_s, d_s = small(img, None, (0, 0))
+    mono_b2, k_b2, d_b2 = big(img, None, (0, 1000))
+    assert mono_b2 == mono_b and np.array_equal(k_b2, k_b) and np.array_equal(d_b2, d_b)
+    ok, od, om = oracle_mod.Extractor(5000, 1.2, 8, 20, 7).extract(img, (0, 1000))
+    assert om == mono_b and np.array_equal(ok, k_b) and np.array_equal(od, d_b)
+    ok, od, om = oracle_mod.Extractor(1000, 1.2, 8, 20, 7).extract(img, (0, 0))
+    assert om == mono_s and np.array_equal(ok, k_s) and np.array_equal(od, d_s)
+
+
+def test_device_sincosf_exhaustive(oracle_mod):
+    """The nvcc build of orbx_sincosf == glibc sincosf for every float in [0, 6.3] (1.09 G bit patterns): chunked
+    order-independent checksums of (sin, cos) bits, device vs libm."""
+    import ctypes as C
+    from orb_slam3_vio_fixes_b200 import _lib
+    hi = int(np.float32(6.3).view(np.uint32))
+    count, chunk = hi + 1, 1 << 22
+    n = (count + chunk - 1) // chunk
+    got = np.zeros(n, np.uint64)
+    _lib.check(_lib.lib().orbx_debug_sincos_checksum(0, 0, count, chunk, got.ctypes.data, n), "sincos checksum")
+    ref = oracle_mod.sincos_checksum(0, count, chunk)
+    bad = np.nonzero(got != ref)[0]
+    assert len(bad) == 0, f"{len(bad)} of {n} chunks differ, first chunk {bad[:3]}"

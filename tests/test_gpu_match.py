@@ -185,7 +185,7 @@ def test_stereo_rowband(oracle_mod):
         assert np.median(kl[f, :nl[f]]["x"][ok] - ur[ok]) == pytest.approx(24.0, abs=0.5)
 
 
-def _stereo_case(oracle_mod, left, right, nfeat=1200):
+def _stereo_case(oracle_mod, left, right, nfeat=1200, fx=458.654, bf=47.90639384423901):
     """Full ComputeStereoMatches on the device (rowband -> refine -> median cut) vs the oracle, bit for bit."""
     B = left.shape[0]
     exl = ORBextractor(nfeat, max_batch=B, **ORB)
@@ -193,7 +193,6 @@ def _stereo_case(oracle_mod, left, right, nfeat=1200):
     ol = _extract_batch(exl, left, (0, 0))
     orr = _extract_batch(exr, right, (0, 0))
     sf, isf = exl.GetScaleFactors(), exl.GetInverseScaleFactors()
-    fx, bf = 458.654, 47.90639384423901
     mb = np.float32(bf / fx)
     mbf = np.float32(bf)
     max_d = mbf / mb
@@ -225,6 +224,18 @@ def test_stereo_refine_constant_disparity(oracle_mod):
         d = kl["x"][ok] - ur[ok]
         assert np.median(d) == pytest.approx(24.0, abs=0.5)
         assert len(np.unique(ur[ok] - np.floor(ur[ok]))) > 20  # the parabola really moves things off the grid
+
+
+def test_stereo_c4_kitti_shape(oracle_mod):
+    """BASELINE config C4: 1241x376 pairs, K=2000/eye, maxD = mbf/mb = fx = 718.856 (Stereo/KITTI00-02.yaml:
+    Camera1.fx 718.856, Stereo.b 0.53716): both eyes + the whole ComputeStereoMatches against the oracle."""
+    left = S.make_frames("C4", 2)
+    right = S.make_frames("C4", 2, right=True)
+    fx = 718.856
+    for kl, ur, dp, kept in _stereo_case(oracle_mod, left, right, nfeat=2000, fx=fx, bf=fx * 0.53716):
+        ok = ur > 0
+        assert len(kl) >= 2000 and kept > 300
+        assert np.median(kl["x"][ok] - ur[ok]) == pytest.approx(24.0, abs=0.5)
 
 
 def test_stereo_refine_zero_and_mixed_disparity(oracle_mod):
@@ -451,6 +462,62 @@ def test_search_by_projection_mappoints(oracle_mod):
         assert tot > B * 300
     tot2, _, _ = _proj_run(oracle_mod, out, ql, bounds, 0, 0.8, False)
     assert tot2 > tot
+
+
+def test_search_by_projection_c3_survey_shape(oracle_mod):
+    """SURVEY §8(d) C3 exactly: 640x480, K=1000; the 'local map' of frame t is the keypoints + descriptors of frames
+    t-4..t-1 (M ~ 4000), projected by the known shifts; th=3, r=4.0 -> radius 12*scale[l]; levels [l-1,l]; best + second
+    with levels; nnratio 0.8 (Tracking.cc:3390-3393 -> ORBmatcher.cc:43-142)."""
+    B = 6
+    frames = S.make_frames("C3", B)
+    ex = ORBextractor(1000, max_batch=B, **ORB)
+    out = _extract_batch(ex, frames, (0, 0))
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    n = out["n"].cpu().numpy()
+    sf = ex.GetScaleFactors()
+    rng = np.random.default_rng(19)
+    bounds = (0.0, 640.0, 0.0, 480.0)
+    pos = np.array([S.frame_shift(t) for t in range(B)], np.float32)
+    ql = []
+    for f in range(B):
+        parts = [_proj_queries(kps[s % B, :n[s % B]], desc[s % B, :n[s % B]], pos[s % B] - pos[f], 4.0 * 3.0, sf, (-1, 0), rng,
+                               1, 0.0, 0.0) for s in range(f - 4, f)]
+        ql.append({k_: np.concatenate([p[k_] for p in parts]) for k_ in parts[0]})
+        assert 3900 < len(ql[-1]["qx"]) < 4200
+    tot, mt, fq = _proj_run(oracle_mod, out, ql, bounds, 0, 0.8, False)
+    assert tot > B * 500
+
+
+def test_search_area_c5_frame_to_frame(oracle_mod):
+    """BASELINE config C5 matcher leg: 3840x2160, K=5000, frame t-1 keypoints shifted into frame t, window
+    15*scale[octave], octave band [o-1,o+1], 64x48 grid over the 4K bounds -> fused GetFeaturesInArea + scoring."""
+    from bench import shifts_for
+    B = 2
+    frames = S.make_frames("C5", B)
+    ex = ORBextractor(5000, max_batch=B, **ORB)
+    out = _extract_batch(ex, frames, (0, 1000))
+    sf = ex.GetScaleFactors()
+    bounds = (0.0, 3840.0, 0.0, 2160.0)
+    shift = shifts_for(0, B)
+    src = ((np.arange(B) - 1) % B).astype(np.int32)
+    grid = ORBmatcher.grid_build(out["kps"], out["n"], bounds)
+    qb = ORBmatcher.queries_shift(out["kps"], out["desc"], out["n"], _t(src), _t(shift), 15.0, sf, (-1, 1))
+    kps = ORBextractor.kps_from_tensor(out["kps"])
+    desc = out["desc"].cpu().numpy()
+    n = out["n"].cpu().numpy()
+    res = results_to_numpy(ORBmatcher.search_area(out["kps"], out["desc"], out["n"], grid, bounds, qb["qx"], qb["qy"],
+                                                  qb["qr"], qb["qmin"], qb["qmax"], qb["qdesc"], qb["nq"], TIE_FIRST_MIN))
+    for f in range(B):
+        s_ = src[f]
+        k_ref, k_q = kps[f, :n[f]], kps[s_, :n[s_]]
+        assert n[f] >= 5000
+        qx, qy = k_q["x"] + shift[f, 0], k_q["y"] + shift[f, 1]
+        qr = (np.float32(15.0) * sf[k_q["octave"]]).astype(np.float32)
+        off, idx = oracle_mod.grid_queries(k_ref, bounds, qx, qy, qr, k_q["octave"] - 1, k_q["octave"] + 1)
+        ref = oracle_mod.argmin2_csr(desc[s_, :n[s_]], desc[f, :n[f]], off, idx, k_ref["octave"].astype(np.int8), TIE_FIRST_MIN)
+        _same_results(res[f, :n[s_]], ref)
+    assert (res[1, :n[0]]["best_dist"] <= 100).mean() > 0.6
 
 
 def test_degenerate_inputs_new_entry_points(oracle_mod):
