@@ -68,6 +68,7 @@ struct orbx_extractor_s {
   int host_chunk = 64;
   int host_edge = 0;   // length of the first and last chunk of a long host batch (ORBX_HOST_EDGE, 0 = off)
   int dev_split = 2;  // sub-batches of orbx_extract_batch_device (ORBX_DEVICE_SPLIT)
+  int dev_streams = 2;  // internal streams the sub-batches rotate over (ORBX_DEVICE_STREAMS, 1..4)
 };
 
 static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
@@ -295,6 +296,7 @@ static int ensure_streams(orbx_handle h) {
   if (const char* e = getenv("ORBX_HOST_STREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 4) h->host_streams = v; }
   if (const char* e = getenv("ORBX_HOST_EDGE")) { const int v = atoi(e); if (v >= 0) h->host_edge = v; }
   if (const char* e = getenv("ORBX_DEVICE_SPLIT")) { const int v = atoi(e); if (v > 0) h->dev_split = v; }
+  if (const char* e = getenv("ORBX_DEVICE_STREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 4) h->dev_streams = v; }
   return ORBX_OK;
 }
 
@@ -358,12 +360,13 @@ int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch
   int rc = ensure_streams(h);
   if (rc) return rc;
   int nsplit = h->dev_split;
-  if ((h->cfg.flags & ORBX_FLAG_STAGE_TIMING) || batch < 64 * nsplit) nsplit = 1;
+  while (nsplit > 1 && batch < 64 * nsplit) nsplit >>= 1;
+  if (h->cfg.flags & ORBX_FLAG_STAGE_TIMING) nsplit = 1;
+  const int nstreams = h->dev_streams < nsplit ? h->dev_streams : nsplit;
   if (nsplit <= 1)
     return run_pipeline(h, l0, batch, lap0, lap1, (OrbxKeyPointDev*)d_kps, d_desc, capacity, d_n_out, d_mono_index, st);
   CU(cudaEventRecord(h->ev_fork, st));
-  CU(cudaStreamWaitEvent(h->s_cmp[0], h->ev_fork, 0));
-  CU(cudaStreamWaitEvent(h->s_cmp[1], h->ev_fork, 0));
+  for (int i = 0; i < nstreams; i++) CU(cudaStreamWaitEvent(h->s_cmp[i], h->ev_fork, 0));
   const int chunk = (batch + nsplit - 1) / nsplit;
   for (int c = 0, f0 = 0; f0 < batch; c++, f0 += chunk) {
     const int nb = (batch - f0) < chunk ? (batch - f0) : chunk;
@@ -371,10 +374,10 @@ int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch
     l.base = l0.base + (long long)f0 * l0.frame_stride;
     rc = run_pipeline(h, l, nb, lap0, lap1, (OrbxKeyPointDev*)d_kps + (long long)f0 * capacity,
                       d_desc + (long long)f0 * capacity * 32, capacity, d_n_out + f0, d_mono_index + f0,
-                      h->s_cmp[c & 1], f0, false);
+                      h->s_cmp[c % nstreams], f0, false);
     if (rc) break;  // still join the forked streams back into the caller's stream below
   }
-  for (int i = 0; i < 2; i++) {
+  for (int i = 0; i < nstreams; i++) {
     CU(cudaEventRecord(h->ev_join[i], h->s_cmp[i]));
     CU(cudaStreamWaitEvent(st, h->ev_join[i], 0));
   }

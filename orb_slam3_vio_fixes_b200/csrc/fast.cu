@@ -22,10 +22,18 @@
 //   5. NMS over the listed pairs;
 //   6. if nothing survives at iniThFAST the cell is redone at minThFAST (:843-859), else
 //   7. ordered (row-major) emission into the cell's slot array.
+#include <stdlib.h>
+
 #include "orbx_kernels.cuh"
 
 #define FAST_WARPS 4
 #define FAST_THREADS (FAST_WARPS * 32)
+// Opposite ring pairs the quick test checks: 4 = (0,8)(4,12)(2,10)(6,14); 2 = the axial pairs only.  On the
+// SURVEY frames the diagonal pairs reject only 14 % of what the axial pairs let through (8.1 % -> 7.0 % of the
+// pixels) but cost half of the quick test's ALU-pipe instructions, so 2 is faster (measured: DESIGN.md §4).
+#ifndef FAST_QUICK_PAIRS
+#define FAST_QUICK_PAIRS 2
+#endif
 #define FAST_LIST_CAP 512  // pair tasks scored per band of rows (a cell is one band unless it is corner-dense)
 
 // 16-bit lanes {w[A], w[A+1]} out of the 12-byte window w0|w1|w2 (A compile-time, 1..9)
@@ -92,31 +100,36 @@ __device__ __forceinline__ uint32_t nms_pair(uint32_t w0, uint32_t w1, uint32_t 
 // One step of the quick test for the quad column a lane walks down.  C/L2/R2/L3/R3 hold, per
 // staged row (slot = row mod 7), the centre word and the words shifted by -2, +2, -3, +3 pixels
 // (7-bit pixels).  Slot NEW receives tile row `row`; the quad under test sits 3 rows above it.
+template <int QP>
 struct QuickWin {
-  uint32_t C[7], L2[7], R2[7], L3[7], R3[7];
+  uint32_t C[7], L2[QP == 4 ? 7 : 1], R2[QP == 4 ? 7 : 1], L3[7], R3[7];
 };
 
-template <int NEW>
-__device__ __forceinline__ void quick_load(QuickWin& W, const uint32_t* hrow) {
+template <int NEW, int QP>
+__device__ __forceinline__ void quick_load(QuickWin<QP>& W, const uint32_t* hrow) {
   const uint32_t n0 = hrow[-1], n1 = hrow[0], n2 = hrow[1];
   W.C[NEW] = n1;
-  W.L2[NEW] = __byte_perm(n0, n1, 0x5432);
-  W.R2[NEW] = __byte_perm(n1, n2, 0x5432);
+  if (QP == 4) {
+    W.L2[QP == 4 ? NEW : 0] = __byte_perm(n0, n1, 0x5432);
+    W.R2[QP == 4 ? NEW : 0] = __byte_perm(n1, n2, 0x5432);
+  }
   W.L3[NEW] = __byte_perm(n0, n1, 0x4321);
   W.R3[NEW] = __byte_perm(n1, n2, 0x6543);
 }
 
 // PH = slot of the oldest row (tile row yy); the centre row is slot PH+3, the newest PH+6.
 // Returns the 4-bit mask of pixels that pass.
-template <int PH>
-__device__ __forceinline__ uint32_t quick_test(const QuickWin& W, uint32_t cadd) {
+template <int PH, int QP>
+__device__ __forceinline__ uint32_t quick_test(const QuickWin<QP>& W, uint32_t cadd) {
   constexpr int S0 = PH % 7, S1 = (PH + 1) % 7, S3 = (PH + 3) % 7, S5 = (PH + 5) % 7, S6 = (PH + 6) % 7;
   const uint32_t v = W.C[S3];
 #define QT(x) (__vabsdiffu4(v, (x)) + cadd)
   uint32_t g = QT(W.C[S6]) | QT(W.C[S0]);     // ring 0 (0,+3) | ring 8 (0,-3)
   g &= QT(W.R3[S3]) | QT(W.L3[S3]);           // ring 4 (+3,0) | ring 12 (-3,0)
-  g &= QT(W.R2[S5]) | QT(W.L2[S1]);           // ring 2 (+2,+2) | ring 10 (-2,-2)
-  g &= QT(W.R2[S1]) | QT(W.L2[S5]);           // ring 6 (+2,-2) | ring 14 (-2,+2)
+  if (QP == 4) {
+    g &= QT(W.R2[QP == 4 ? S5 : 0]) | QT(W.L2[QP == 4 ? S1 : 0]);  // ring 2 (+2,+2) | ring 10 (-2,-2)
+    g &= QT(W.R2[QP == 4 ? S1 : 0]) | QT(W.L2[QP == 4 ? S5 : 0]);  // ring 6 (+2,-2) | ring 14 (-2,+2)
+  }
 #undef QT
   return ((g & 0x80808080u) * 0x00204081u) >> 28;  // bits 7,15,23,31 -> 0..3
 }
@@ -263,6 +276,7 @@ __device__ __forceinline__ int fast_sweep(const FastCell& c, int nquads, int th,
   return total;
 }
 
+template <int QP>
 __global__ void __launch_bounds__(FAST_THREADS, 8)
 k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
        const uint32_t* __restrict__ cell_tab, int32_t* __restrict__ cell_cnt, uint32_t* __restrict__ cand,
@@ -381,18 +395,18 @@ k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__
       const int hlast = (zh + 5) * pw;  // last staged row
       int hp = y0 * pw;
       uint8_t* qp = c.qm + y0 * nqr + cg + (active ? qi : 0);
-      QuickWin W;
-      quick_load<0>(W, hcol + hp); hp = min(hp + pw, hlast);
-      quick_load<1>(W, hcol + hp); hp = min(hp + pw, hlast);
-      quick_load<2>(W, hcol + hp); hp = min(hp + pw, hlast);
-      quick_load<3>(W, hcol + hp); hp = min(hp + pw, hlast);
-      quick_load<4>(W, hcol + hp); hp = min(hp + pw, hlast);
-      quick_load<5>(W, hcol + hp); hp = min(hp + pw, hlast);
+      QuickWin<QP> W;
+      quick_load<0, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
+      quick_load<1, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
+      quick_load<2, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
+      quick_load<3, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
+      quick_load<4, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
+      quick_load<5, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
 #define QSTEP(PH)                                       \
   {                                                     \
-    quick_load<(PH + 6) % 7>(W, hcol + hp);                  \
+    quick_load<(PH + 6) % 7, QP>(W, hcol + hp);                  \
     hp = min(hp + pw, hlast);                           \
-    const uint32_t m = quick_test<PH>(W, cadd);         \
+    const uint32_t m = quick_test<PH, QP>(W, cadd);         \
     if (base + PH < nrow) qp[PH * nqr] = (uint8_t)m;    \
   }
 #pragma unroll 1
@@ -432,9 +446,12 @@ cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, 
   }
   cap = (cap + 8 + 15) & ~15;  // quads per cell (bytes of qm) + one spare uint2, regions stay 8-byte aligned
   const size_t smem = (size_t)FAST_WARPS * (2 * pw * rows + FAST_LIST_CAP / 2 + (cap >> 2)) * sizeof(uint32_t);
-  cudaError_t e = orbx_ensure_dyn_smem(ORBX_SMEM_FAST, (const void*)k_fast, smem);
+  static const int qp = [] { const char* e = getenv("ORBX_FAST_PAIRS"); return e && atoi(e) == 4 ? 4 : FAST_QUICK_PAIRS; }();
+  const void* fn = qp == 4 ? (const void*)k_fast<4> : (const void*)k_fast<2>;
+  cudaError_t e = orbx_ensure_dyn_smem(qp == 4 ? ORBX_SMEM_FAST4 : ORBX_SMEM_FAST, fn, smem);
   if (e != cudaSuccess) return e;
   dim3 grd((P.total_cells + FAST_WARPS - 1) / FAST_WARPS, batch);
-  k_fast<<<grd, FAST_THREADS, smem, st>>>(P, l0, arena, cell_tab, cell_cnt, cand, pw, rows, cap);
+  if (qp == 4) k_fast<4><<<grd, FAST_THREADS, smem, st>>>(P, l0, arena, cell_tab, cell_cnt, cand, pw, rows, cap);
+  else k_fast<2><<<grd, FAST_THREADS, smem, st>>>(P, l0, arena, cell_tab, cell_cnt, cand, pw, rows, cap);
   return cudaGetLastError();
 }

@@ -180,24 +180,12 @@ __device__ __forceinline__ void rs_row_smem(const uint8_t* p, const RsTapRegs& T
   }
 }
 
-template <int P>
-__device__ __forceinline__ uint32_t rs_out_row_smem(const uint8_t* base, int sy0, int sy1, uint32_t b0, uint32_t b1,
-                                                    const RsTapRegs& T, uint32_t (&H)[2][4], int (&held)[2]) {
-  if (held[P] != sy0) {
-    rs_row_smem(base + sy0 * RT_SPITCH, T, H[P]);
-    held[P] = sy0;
-  }
-  if (held[P ^ 1] != sy1) {
-    rs_row_smem(base + sy1 * RT_SPITCH, T, H[P ^ 1]);
-    held[P ^ 1] = sy1;
-  }
-  uint32_t out = 0;
+// Vertical taps + pack of one output word from the H rows of source rows sy0 (A) and sy0+1 (B).
+__device__ __forceinline__ uint32_t rs_vert(const uint32_t (&A)[4], const uint32_t (&B)[4], uint32_t b0, uint32_t b1) {
+  uint32_t v[4];
 #pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const uint32_t v = (__umulhi(b0, H[P][i]) + __umulhi(b1, H[P ^ 1][i]) + 2u) >> 2;  // <= 255
-    out |= v << (8 * i);
-  }
-  return out;
+  for (int i = 0; i < 4; i++) v[i] = (__umulhi(b0, A[i]) + __umulhi(b1, B[i]) + 2u) >> 2;  // <= 255
+  return __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
 }
 
 __global__ void __launch_bounds__(RS_WARPS * 32)
@@ -256,19 +244,26 @@ k_resize_tile(const uint8_t* __restrict__ src, int spitch, long long sframe, int
   if (!live) return;
   const uint8_t* base = tile + ((o0 & ~3) - xs0) - sy_first * RT_SPITCH;
   uint8_t* out = dst + (long long)blockIdx.z * dframe + (long long)dy0 * dpitch + x4;
-  uint32_t H[2][4];
-  int held[2] = {-1, -1};
+  // Row schedule (warp-uniform): consecutive output rows use source rows (sy0, sy0+1) with sy0 advancing by 1
+  // or 2 (the scale is between 1 and 2), so the H row of sy0 is either the previous output row's second row
+  // or a new one; the second row is always new.  HA/HB swap roles instead of moving.
+  uint32_t HA[4], HB[4];
+  int sy_b = -1 << 20;  // source row held in HB
   const int dy1 = min(dy0 + RS_ROWS, dh);
 #pragma unroll 1
   for (int dy = dy0; dy < dy1; dy++, out += dpitch) {
     const OrbxTap ty = yt[dy];
     const int sy0 = min(max(ty.ofs, 0), sh - 1), sy1 = min(max(ty.ofs + 1, 0), sh - 1);
-    const uint32_t b0 = (uint32_t)ty.c0, b1 = (uint32_t)ty.c1;
-    uint32_t v;
-    if (sy0 & 1) v = rs_out_row_smem<1>(base, sy0, sy1, b0, b1, T, H, held);
-    else v = rs_out_row_smem<0>(base, sy0, sy1, b0, b1, T, H, held);
+    if (sy0 == sy_b) {
+#pragma unroll
+      for (int i = 0; i < 4; i++) HA[i] = HB[i];
+    } else {
+      rs_row_smem(base + sy0 * RT_SPITCH, T, HA);
+    }
+    rs_row_smem(base + sy1 * RT_SPITCH, T, HB);
+    sy_b = sy1;
     // rows are 128-byte aligned and padded, so the full word store stays inside the row
-    *reinterpret_cast<uint32_t*>(out) = v;
+    *reinterpret_cast<uint32_t*>(out) = rs_vert(HA, HB, (uint32_t)ty.c0, (uint32_t)ty.c1);
   }
 }
 
