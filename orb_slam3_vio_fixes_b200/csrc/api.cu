@@ -36,6 +36,7 @@ struct orbx_extractor_s {
   OrbxTap *xtaps = nullptr, *ytaps = nullptr;
   int32_t* cell_cnt = nullptr;
   uint32_t* cell_tab = nullptr;  // per cell: level << 24 | row << 12 | column
+  uint32_t* strip_tab = nullptr;  // per FAST strip: level << 24 | cell row << 12 | first cell column
   uint32_t* cand = nullptr;
   uint32_t* gkeys = nullptr;
   int16_t* glabels = nullptr;
@@ -74,7 +75,7 @@ struct orbx_extractor_s {
 static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
   memset(D, 0, sizeof(*D));
   D->nlevels = P.nlevels; D->total_cells = P.total_cells; D->kp_total_cap = P.kp_total_cap;
-  D->ini_th = P.ini_th; D->min_th = P.min_th; D->total_btiles = P.total_btiles; D->cand_total = P.cand_total; D->arena_bytes = P.arena_bytes;
+  D->ini_th = P.ini_th; D->min_th = P.min_th; D->total_btiles = P.total_btiles; D->total_strips = P.total_strips; D->cand_total = P.cand_total; D->arena_bytes = P.arena_bytes;
   for (int i = 0; i < 16; i++) D->umax[i] = P.umax[i];
   for (int l = 0; l < P.nlevels; l++) {
     const OrbxLevel& s = P.lv[l];
@@ -83,7 +84,7 @@ static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
     d.hCell = s.hCell; d.cell_base = s.cell_base; d.cell_cap = s.cell_cap; d.nfeat = s.nfeat;
     d.kp_base = s.kp_base; d.kp_cap = s.kp_cap; d.kp_max = s.kp_max; d.nIni = s.nIni; d.hX = s.hX;
     d.scale = s.scale; d.patch_size = s.patch_size; d.xtab = s.xtab; d.ytab = s.ytab; d.fast_resize = s.fast_resize; d.tile_resize = s.tile_resize; d.btile_base = s.btile_base; d.btiles_x = s.btiles_x; d.offset = s.offset;
-    d.cand_base = s.cand_base;
+    d.cand_base = s.cand_base; d.strip_k = s.strip_k;
   }
 }
 
@@ -136,7 +137,7 @@ const char* orbx_last_error(void) { return g_err; }
 void orbx_destroy(orbx_handle h) {
   if (!h) return;
   cudaSetDevice(h->device);
-  cudaFree(h->arena); cudaFree(h->xtaps); cudaFree(h->ytaps); cudaFree(h->cell_cnt); cudaFree(h->cell_tab); cudaFree(h->cand);
+  cudaFree(h->arena); cudaFree(h->xtaps); cudaFree(h->ytaps); cudaFree(h->cell_cnt); cudaFree(h->cell_tab); cudaFree(h->strip_tab); cudaFree(h->cand);
   cudaFree(h->gkeys); cudaFree(h->glabels); cudaFree(h->sel); cudaFree(h->sel_cnt); cudaFree(h->dst);
   cudaFree(h->status); cudaFree(h->o_kps); cudaFree(h->o_desc); cudaFree(h->o_n); cudaFree(h->o_mono);
   cudaFree(h->border_tmp); cudaFree(h->stage); cudaFree(h->blur);
@@ -218,6 +219,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   ALLOC(h->ytaps, (yt.size() + 1) * sizeof(OrbxTap));
   ALLOC(h->cell_cnt, B * P.total_cells * sizeof(int32_t));
   ALLOC(h->cell_tab, (size_t)P.total_cells * sizeof(uint32_t));
+  ALLOC(h->strip_tab, (size_t)P.total_strips * sizeof(uint32_t));
   ALLOC(h->cand, B * P.cand_total * sizeof(uint32_t));
   ALLOC(h->gkeys, B * P.cand_total * sizeof(uint32_t));
   ALLOC(h->glabels, B * P.cand_total * sizeof(int16_t));
@@ -260,6 +262,13 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
       for (int c = 0; c < P.lv[l].nCols * P.lv[l].nRows; c++)
         tab[P.lv[l].cell_base + c] = ((uint32_t)l << 24) | ((uint32_t)(c / P.lv[l].nCols) << 12) | (uint32_t)(c % P.lv[l].nCols);
     CUH(cudaMemcpy(h->cell_tab, tab.data(), tab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    std::vector<uint32_t> stab(P.total_strips);
+    for (int l = 0; l < P.nlevels; l++)
+      for (int i = 0; i < P.lv[l].nRows; i++)
+        for (int sj = 0; sj < P.lv[l].strips_per_row; sj++)
+          stab[P.lv[l].strip_base + i * P.lv[l].strips_per_row + sj] =
+              ((uint32_t)l << 24) | ((uint32_t)i << 12) | (uint32_t)(sj * P.lv[l].strip_k);
+    CUH(cudaMemcpy(h->strip_tab, stab.data(), stab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
   }
   CUH(cudaMemset(h->status, 0, sizeof(int32_t)));
   CUH(cudaMemset(h->arena, 0, B * P.arena_bytes + 512));
@@ -317,7 +326,7 @@ static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1,
   STAGE_MARK(0);
   CU(orbx_launch_pyramid(D, l0, arena, h->xtaps, h->ytaps, batch, st));
   STAGE_MARK(1);
-  CU(orbx_launch_fast(D, l0, arena, h->cell_tab, cell_cnt, cand, batch, st));
+  CU(orbx_launch_fast(D, l0, arena, h->cell_tab, h->strip_tab, cell_cnt, cand, batch, st));
   STAGE_MARK(2);
   CU(orbx_launch_octree(D, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, h->status, batch,
                         h->oct_smem, h->oct_smem_keys, h->oct_node_cap, h->oct_max_cells, st));

@@ -1,457 +1,430 @@
-// fast.cu — per-cell FAST-9/16 detection with non-max suppression and the per-cell threshold
-// fallback (cell loop of ORBextractor::ComputeKeyPointsOctTree, src/ORBextractor.cc:781-872;
-// cv::FAST TYPE_9_16 + cornerScore) for sm_100a.
+// fast.cu — per-cell FAST-9/16 detection with non-max suppression and the per-cell threshold fallback
+// (cell loop of ORBextractor::ComputeKeyPointsOctTree, src/ORBextractor.cc:781-872; cv::FAST TYPE_9_16 +
+// cornerScore) for sm_100a: the strip kernel.
 //
 // The reference runs cv::FAST on each ~35-px cell ROI (6 px overlap).  cv::FAST tests ROI pixels
-// [3,W-3)x[3,H-3), so the tested zones of the cells tile [19,w-19)x[19,h-19) exactly on a
-// (wCell,hCell) lattice, and the NMS of a cell only sees that cell's own zone (outside = 0).
+// [3,W-3)x[3,H-3), so the tested zones of the cells tile [19,w-19)x[19,h-19) exactly on a (wCell,hCell)
+// lattice; the NMS of a cell only sees that cell's own zone (outside = 0), and a cell that is empty after NMS
+// at iniThFAST is redone at minThFAST (:843-859).  The arc strength A of a pixel depends on neither the cell
+// nor the threshold (corner(th) <=> A > th, cornerScore == A-1), so only NMS and emission are per cell.
 //
-// One WARP = one cell (no block-level synchronisation at all; a CTA is just 4 independent warps):
-//   1. stage the zone + 3-px halo in the warp's shared-memory slice with 32-bit loads, plus a
-//      copy with every byte halved (7-bit pixels) for the quick test;
-//   2. quick test at threshold t, four pixels (one 32-bit word, a "quad") per lane per step with
-//      packed-byte arithmetic (VABSDIFF4): a 9/16 corner needs |v-ring| > t on at least one pixel
-//      of each opposite ring pair (0,8)(4,12)(2,10)(6,14).  On 7-bit pixels the test
-//      |v'-r'| >= ceil(t/2) is implied by |v-r| > t (never rejects a corner) and the compare is one
-//      add whose carry lands in bit 7.  A lane walks down one quad column keeping the last 7 rows
-//      in registers, so a step costs 3 shared loads; the pass masks go to a byte map;
-//   3. the byte map is compacted, in row-major order, into a list of pixel PAIRS to score;
-//   4. arc strength A of the listed pairs only, with packed 16-bit SIMD (VIMNMX3.U16x2: the 16
-//      sliding windows of 9 ring pixels are two rounds of 3-input min/max); corner(t) <=> A > t and
-//      cornerScore == A-1;
-//   5. NMS over the listed pairs;
-//   6. if nothing survives at iniThFAST the cell is redone at minThFAST (:843-859), else
-//   7. ordered (row-major) emission into the cell's slot array.
+// One WARP = one STRIP = strip_k consecutive cells of one cell row (<= 120 tested columns), no block-level
+// synchronisation (a CTA is FS_WARPS independent warps):
+//   1. the strip's pixels (+3 px halo, 16-byte aligned columns) go to shared memory with cp.async (16 B per
+//      lane, three rows per step) while the A map and the keep bitmap are being cleared;
+//   2. quick test, dense: lane = one 4-pixel word column, walking down the rows with the last 7 rows (7-bit
+//      pixels) in registers and the horizontal neighbours taken from the adjacent lanes (SHFL); packed-byte
+//      arithmetic (VABSDIFF4): a 9/16 corner needs |v-ring| > t on at least one pixel of each of the axial
+//      ring pairs (0,8) and (4,12).  Two pass bits (one per pixel pair) per row accumulate in a register;
+//   3. the pass bits are compacted into a task list (pixel pairs, any order);
+//   4. arc strength of the listed pairs with packed 16-bit SIMD (fast_arc.cuh) into the A map (u8, 0 where
+//      A <= th or outside the zone); pairs with a corner are kept in the list;
+//   5. NMS of the kept pairs against the A map, with the columns where a new cell starts masked out, sets one
+//      bit per surviving corner in the keep bitmap;
+//   6. per cell: lanes own rows, count their bits, one warp scan, ordered (row-major) emission into the cell's
+//      slot array — the order the reference's per-cell cv::FAST returns;
+//   7. cells that stayed empty are redone from step 2 at minThFAST with the zone restricted to their columns.
 #include <stdlib.h>
 
+#include "fast_arc.cuh"
 #include "orbx_kernels.cuh"
 
-#define FAST_WARPS 4
-#define FAST_THREADS (FAST_WARPS * 32)
-// Opposite ring pairs the quick test checks: 4 = (0,8)(4,12)(2,10)(6,14); 2 = the axial pairs only.  On the
-// SURVEY frames the diagonal pairs reject only 14 % of what the axial pairs let through (8.1 % -> 7.0 % of the
-// pixels) but cost half of the quick test's ALU-pipe instructions, so 2 is faster (measured: DESIGN.md §4).
-#ifndef FAST_QUICK_PAIRS
-#define FAST_QUICK_PAIRS 2
-#endif
-#define FAST_LIST_CAP 512  // pair tasks scored per band of rows (a cell is one band unless it is corner-dense)
+#define FS_WARPS 2
+#define FS_THREADS (FS_WARPS * 32)
+#define FS_TP 144            // tile row pitch in bytes: 9 vectors of 16 B cover lane words 0..31 at word offset <= 3
+#define FS_TPW (FS_TP / 4)   // 36 words
+#define FS_AP 132            // A-map row pitch in bytes: 4 (pad) + 120 (columns) + 8 (pad), odd word count
+#define FS_APW (FS_AP / 4)   // 33 words
+#define FS_KBP 5             // keep-bitmap words per row (4 used: 120 columns)
+#define FS_CAP 512           // pair tasks per chunk of the list
+#define FS_MAXB2 5           // pass-bit words per lane: 14 rows each (zh <= 69)
 
-// 16-bit lanes {w[A], w[A+1]} out of the 12-byte window w0|w1|w2 (A compile-time, 1..9)
-template <int A>
-__device__ __forceinline__ uint32_t pick2(uint32_t w0, uint32_t w1, uint32_t w2) {
-  if (A <= 2) return __byte_perm(w0, 0, A | 0x40 | ((A + 1) << 8) | 0x4000);
-  if (A == 3) return __byte_perm(w0, w1, 0x0403) & 0x00ff00ffu;
-  if (A <= 6) return __byte_perm(w1, 0, (A - 4) | 0x40 | ((A - 3) << 8) | 0x4000);
-  if (A == 7) return __byte_perm(w1, w2, 0x0403) & 0x00ff00ffu;
-  return __byte_perm(w2, 0, (A - 8) | 0x40 | ((A - 7) << 8) | 0x4000);
+__device__ __forceinline__ uint32_t fs_halve(uint32_t v) { return (v >> 1) & 0x7f7f7f7fu; }
+
+__device__ __forceinline__ void fs_cp_async16(uint32_t saddr, const void* g, uint32_t nbytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(saddr), "l"(g), "r"(nbytes) : "memory");
 }
 
-// Arc strength of the two pixels at window bytes 4+J and 5+J.  rw[d] = the three words (q-1,q,q+1)
-// of tile row (r-3+d).  Returns A0 | A1<<8.
-template <int J>
-__device__ __forceinline__ uint32_t arc_pair(const uint32_t (&rw)[7][3]) {
-  uint32_t r[16];
-#define RING(k, dx, dy) r[k] = pick2<4 + J + (dx)>(rw[(dy) + 3][0], rw[(dy) + 3][1], rw[(dy) + 3][2])
-  // OpenCV ring order (features2d/fast_score.cpp makeOffsets, patternSize 16)
-  RING(0, 0, 3);   RING(1, 1, 3);    RING(2, 2, 2);    RING(3, 3, 1);
-  RING(4, 3, 0);   RING(5, 3, -1);   RING(6, 2, -2);   RING(7, 1, -3);
-  RING(8, 0, -3);  RING(9, -1, -3);  RING(10, -2, -2); RING(11, -3, -1);
-  RING(12, -3, 0); RING(13, -3, 1);  RING(14, -2, 2);  RING(15, -1, 3);
-#undef RING
-  const uint32_t vv = pick2<4 + J>(rw[3][0], rw[3][1], rw[3][2]);
-  uint32_t mn3[16], mx3[16];
-#pragma unroll
-  for (int k = 0; k < 16; k++) {
-    mn3[k] = __vimin3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
-    mx3[k] = __vimax3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
+// NMS of the pixel pair in bytes 1,2 of w1.  w0,w1,w2 = rows above / at / below with the A values of columns
+// c-1..c+2 (bytes 0..3); e3 bit i = a cell starts at column c+i (its left neighbour belongs to another cell,
+// whose corners the reference's per-cell cv::FAST never sees).  cv::FAST keeps a corner when its score A-1 is
+// strictly greater than all 8 neighbouring scores (0 for non-corners): keep <=> A > max(1, neighbours' A).
+__device__ __forceinline__ uint32_t fs_nms_pair(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t e3) {
+  uint32_t mA = 0x00ffffffu, mB = 0xffffff00u;
+  if (e3 & 1u) mA &= 0xffffff00u;
+  if (e3 & 2u) { mA &= 0xff00ffffu; mB &= 0xffff00ffu; }
+  if (e3 & 4u) mB &= 0x00ffffffu;
+  uint32_t keep = 0;
+  {
+    const uint32_t x0 = w0 & mA, x1 = w1 & mA & 0xffff00ffu, x2 = w2 & mA;
+    const uint32_t ve = __vimax3_u16x2(x0 & 0x00ff00ffu, x1 & 0x00ff00ffu, x2 & 0x00ff00ffu);
+    const uint32_t vo = __vimax3_u16x2((x0 >> 8) & 0x00ff00ffu, (x1 >> 8) & 0x00ff00ffu, (x2 >> 8) & 0x00ff00ffu);
+    const uint32_t t = __vmaxu2(ve, vo);
+    const uint32_t m = max(max(t & 0xffffu, t >> 16), 1u);
+    if (((w1 >> 8) & 0xffu) > m) keep |= 1u;
   }
-  // windows of 9 = three consecutive windows of 3; keep only the extreme over the 16 arcs:
-  //   bright-centre strength = v - min_k max9[k],  dark-centre strength = max_k min9[k] - v
-  uint32_t lo = 0xffffffffu, hi = 0;
-#pragma unroll
-  for (int k = 0; k < 16; k++) {
-    const uint32_t mx9 = __vimax3_u16x2(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]);
-    const uint32_t mn9 = __vimin3_u16x2(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
-    lo = __vminu2(lo, mx9);
-    hi = __vmaxu2(hi, mn9);
+  {
+    const uint32_t x0 = w0 & mB, x1 = w1 & mB & 0xff00ffffu, x2 = w2 & mB;
+    const uint32_t ve = __vimax3_u16x2(x0 & 0x00ff00ffu, x1 & 0x00ff00ffu, x2 & 0x00ff00ffu);
+    const uint32_t vo = __vimax3_u16x2((x0 >> 8) & 0x00ff00ffu, (x1 >> 8) & 0x00ff00ffu, (x2 >> 8) & 0x00ff00ffu);
+    const uint32_t t = __vmaxu2(ve, vo);
+    const uint32_t m = max(max(t & 0xffffu, t >> 16), 1u);
+    if (((w1 >> 16) & 0xffu) > m) keep |= 2u;
   }
-  const int v0 = (int)(vv & 0xffffu), v1 = (int)(vv >> 16);
-  const int a0 = max(max(v0 - (int)(lo & 0xffffu), (int)(hi & 0xffffu) - v0), 0);
-  const int a1 = max(max(v1 - (int)(lo >> 16), (int)(hi >> 16) - v1), 0);
-  return (uint32_t)a0 | ((uint32_t)a1 << 8);
+  return keep;
 }
 
-// NMS for the two pixels of a pair.  w0,w1,w2 = the rows above / at / below, each holding the A
-// values (0 where A <= th) of columns c-1, c, c+1, c+2 with the pair at c, c+1.  cv::FAST_t keeps a
-// corner when its score A-1 is strictly greater than all 8 neighbouring scores (0 for non-corners):
-//   keep <=> A != 0 && A > max(1, max of the 8 neighbours' A).
-// Returns bit0 / bit1 for the left / right pixel.
-__device__ __forceinline__ uint32_t nms_pair(uint32_t w0, uint32_t w1, uint32_t w2) {
-  const uint32_t e0 = w0 & 0x00ff00ffu, e1 = w1 & 0x00ff00ffu, e2 = w2 & 0x00ff00ffu;  // columns 0,2
-  const uint32_t o0 = (w0 >> 8) & 0x00ff00ffu, o1 = (w1 >> 8) & 0x00ff00ffu, o2 = (w2 >> 8) & 0x00ff00ffu;  // 1,3
-  const uint32_t ve = __vimax3_u16x2(e0, e1, e2), vo = __vimax3_u16x2(o0, o1, o2);  // column maxima
-  const uint32_t te = __vmaxu2(e0, e2), to = __vmaxu2(o0, o2);                      // without the centre row
-  const uint32_t ma = max(max(ve & 0xffffu, ve >> 16), max(to & 0xffffu, 1u));  // around column 1
-  const uint32_t mb = max(max(vo & 0xffffu, vo >> 16), max(te >> 16, 1u));      // around column 2
-  const uint32_t a = o1 & 0xffffu, b = e1 >> 16;
-  return (a > ma ? 1u : 0u) | (b > mb ? 2u : 0u);
-}
-
-// One step of the quick test for the quad column a lane walks down.  C/L2/R2/L3/R3 hold, per
-// staged row (slot = row mod 7), the centre word and the words shifted by -2, +2, -3, +3 pixels
-// (7-bit pixels).  Slot NEW receives tile row `row`; the quad under test sits 3 rows above it.
-template <int QP>
-struct QuickWin {
-  uint32_t C[7], L2[QP == 4 ? 7 : 1], R2[QP == 4 ? 7 : 1], L3[7], R3[7];
-};
-
-template <int NEW, int QP>
-__device__ __forceinline__ void quick_load(QuickWin<QP>& W, const uint32_t* hrow) {
-  const uint32_t n0 = hrow[-1], n1 = hrow[0], n2 = hrow[1];
-  W.C[NEW] = n1;
-  if (QP == 4) {
-    W.L2[QP == 4 ? NEW : 0] = __byte_perm(n0, n1, 0x5432);
-    W.R2[QP == 4 ? NEW : 0] = __byte_perm(n1, n2, 0x5432);
-  }
-  W.L3[NEW] = __byte_perm(n0, n1, 0x4321);
-  W.R3[NEW] = __byte_perm(n1, n2, 0x6543);
-}
-
-// PH = slot of the oldest row (tile row yy); the centre row is slot PH+3, the newest PH+6.
-// Returns the 4-bit mask of pixels that pass.
-template <int PH, int QP>
-__device__ __forceinline__ uint32_t quick_test(const QuickWin<QP>& W, uint32_t cadd) {
-  constexpr int S0 = PH % 7, S1 = (PH + 1) % 7, S3 = (PH + 3) % 7, S5 = (PH + 5) % 7, S6 = (PH + 6) % 7;
-  const uint32_t v = W.C[S3];
-#define QT(x) (__vabsdiffu4(v, (x)) + cadd)
-  uint32_t g = QT(W.C[S6]) | QT(W.C[S0]);     // ring 0 (0,+3) | ring 8 (0,-3)
-  g &= QT(W.R3[S3]) | QT(W.L3[S3]);           // ring 4 (+3,0) | ring 12 (-3,0)
-  if (QP == 4) {
-    g &= QT(W.R2[QP == 4 ? S5 : 0]) | QT(W.L2[QP == 4 ? S1 : 0]);  // ring 2 (+2,+2) | ring 10 (-2,-2)
-    g &= QT(W.R2[QP == 4 ? S1 : 0]) | QT(W.L2[QP == 4 ? S5 : 0]);  // ring 6 (+2,-2) | ring 14 (-2,+2)
-  }
-#undef QT
-  return ((g & 0x80808080u) * 0x00204081u) >> 28;  // bits 7,15,23,31 -> 0..3
-}
-
-// Shared memory of one warp, in 32-bit words:
-//   px[pw*rows]   staged pixels: tile row r (= zone row r-3), zone column x at byte r*4*pw + 7+sh + x
-//   hm[pw*rows]   the same tile with 7-bit pixels during the quick test; afterwards the arc-strength
-//                 map A (u8, 0 where A <= th or outside the zone), same geometry
-//   list[FAST_LIST_CAP] u16 tasks (quad*2 + pair), row-major, for the current band of rows
-//   qm[qcap]      u8 per quad: quick-test mask of its 4 pixels
-struct FastCell {
-  uint32_t *px, *hm;
+// Shared memory of one warp (32-bit words):
+//   tile[FS_TPW * (hmax+6)]   staged pixels: tile row r = level row Y0-3+r, tile byte b = level column xt+b
+//   amap[FS_APW * (hmax+2)]   arc strengths: row r+1 = zone row r, byte 4+c = strip column c (level column xs+c)
+//   kb[FS_KBP * hmax]         keep bitmap: bit c of row r
+//   pb[32 * FS_MAXB2]         pass bits: word b of lane l = rows 14b..14b+13 (two 7-row halves, see below)
+//   list[FS_CAP] u16          tasks: row << 6 | lane << 1 | pair
+//   misc[12]                  zbits[4] (zone columns), ledge[5] (columns where a cell starts / the zone ends)
+struct FsStrip {
+  uint32_t *tile, *amap, *kb, *pb, *misc;
   uint16_t* list;
-  uint8_t* qm;
-  int pw, nqr, q_first, colbase, zw, zh;
-  uint32_t rcq;
+  int wq0;  // tile word of lane 0
+  int zh;
 };
 
-// Arc strength of the listed pairs (dense: the warp stays converged) into the A map.
-__device__ __forceinline__ void fast_score_list(const FastCell& c, int nlist, int th, int lane) {
-  for (int e = lane; e < nlist; e += 32) {
-    const int tk = c.list[e];
-    const int ql = tk >> 1, pr = tk & 1;
-    const int yy = (int)(((uint32_t)ql * c.rcq) >> 20), q = c.q_first + ql - yy * c.nqr;
-    const int fs = 16 * pr;
+// Task list of chunk [cb, cb+FS_CAP) of the pass bits pw[] (lane-private), off = this lane's first index.
+__device__ __forceinline__ void fs_fill(const FsStrip& s, const uint32_t (&pw)[FS_MAXB2], int off, int cb, int lane) {
+  int pos = off - cb;
+#pragma unroll
+  for (int b = 0; b < FS_MAXB2; b++) {
+    uint32_t w = pw[b];
+    while (w) {
+      const int bit = __ffs(w) - 1;
+      w &= w - 1;
+      // low half: rows 0..6 at bits 2+2j, high half: rows 7..13 at bits 18+2(j-7); even bit = pair 0
+      const int row = 14 * b + 7 * (bit >> 4) + (((bit & 15) - 2) >> 1);
+      if ((unsigned)pos < (unsigned)FS_CAP) s.list[pos] = (uint16_t)((row << 6) | (lane << 1) | (bit & 1));
+      pos++;
+    }
+  }
+  __syncwarp();
+}
+
+// Arc strength of the n listed pairs into the A map; with COMPACT the pairs that hold a corner move to the
+// front of the list (returns their number), otherwise returns n.
+template <bool COMPACT>
+__device__ __forceinline__ int fs_score(const FsStrip& s, int n, int th, int lane) {
+  int nkeep = 0;
+  for (int base = 0; base < n; base += 32) {
+    const int e = base + lane;
+    const bool act = e < n;
+    const uint32_t tk = act ? (uint32_t)s.list[e] : 2u;  // idle lanes score the pair of lane 1, row 0 (discarded)
+    const int r = (int)(tk >> 6), ql = (int)((tk >> 1) & 31u), p = (int)(tk & 1u);
+    const uint32_t* tp = s.tile + r * FS_TPW + s.wq0 + ql - 1;
+    const int fs = 16 * p;
     uint32_t rw[7][3];
 #pragma unroll
     for (int d = 0; d < 7; d++) {
-      const uint32_t* p = c.px + (yy + d) * c.pw + q - 1;
-      const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+      const uint32_t w0 = tp[d * FS_TPW], w1 = tp[d * FS_TPW + 1], w2 = tp[d * FS_TPW + 2];
       rw[d][0] = __funnelshift_r(w0, w1, fs);
       rw[d][1] = __funnelshift_r(w1, w2, fs);
       rw[d][2] = w2 >> fs;
     }
-    const uint32_t a = arc_pair<0>(rw);  // A of zone columns x0, x0+1
-    const int x0 = 4 * q - c.colbase + 2 * pr;
-    const int A0 = (int)(a & 0xffu), A1 = (int)(a >> 8);
+    const uint32_t a = arc_pair<0>(rw);
+    const int c0 = 4 * (ql - 1) + 2 * p;  // strip column of the left pixel
+    const uint32_t zz = (s.misc[c0 >> 5] >> (c0 & 31)) & 3u;
     uint32_t keep = 0;
-    if (A0 > th && (unsigned)x0 < (unsigned)c.zw) keep |= 0x00ffu;
-    if (A1 > th && (unsigned)(x0 + 1) < (unsigned)c.zw) keep |= 0xff00u;
-    reinterpret_cast<uint16_t*>(c.hm + (yy + 3) * c.pw + q)[pr] = (uint16_t)(a & keep);
+    if ((int)(a & 0xffu) > th && (zz & 1u)) keep |= 0x00ffu;
+    if ((int)(a >> 8) > th && (zz & 2u)) keep |= 0xff00u;
+    const uint32_t av = a & keep;
+    if (act) *reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(s.amap) + (r + 1) * FS_AP + 4 + c0) = (uint16_t)av;
+    if (COMPACT) {
+      const bool sv = act && av != 0;
+      const unsigned bal = __ballot_sync(0xffffffffu, sv);
+      if (sv) s.list[nkeep + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)tk;
+      nkeep += __popc(bal);
+    }
+  }
+  __syncwarp();
+  return COMPACT ? nkeep : n;
+}
+
+// NMS of the n listed pairs (pairs without a corner are skipped) into the keep bitmap.
+__device__ __forceinline__ void fs_nms(const FsStrip& s, int n, int lane) {
+  const uint32_t* ledge = s.misc + 4;
+  for (int e = lane; e < n; e += 32) {
+    const uint32_t tk = s.list[e];
+    const int r = (int)(tk >> 6), ql = (int)((tk >> 1) & 31u), p = (int)(tk & 1u);
+    const int c0 = 4 * (ql - 1) + 2 * p;
+    const uint32_t a = *reinterpret_cast<const uint16_t*>(reinterpret_cast<const uint8_t*>(s.amap) + (r + 1) * FS_AP + 4 + c0);
+    if (a == 0) continue;
+    // columns c0-1..c0+2 = bytes 3+c0..6+c0 of the A-map row; rows r, r+1, r+2 = zone rows r-1, r, r+1
+    const uint32_t* wp = s.amap + r * FS_APW + ((3 + c0) >> 2);
+    const int fs = p ? 8 : 24;
+    const uint32_t w0 = __funnelshift_r(wp[0], wp[1], fs);
+    const uint32_t w1 = __funnelshift_r(wp[FS_APW], wp[FS_APW + 1], fs);
+    const uint32_t w2 = __funnelshift_r(wp[2 * FS_APW], wp[2 * FS_APW + 1], fs);
+    const uint32_t e3 = __funnelshift_r(ledge[c0 >> 5], ledge[(c0 >> 5) + 1], c0 & 31) & 7u;
+    const uint32_t f = fs_nms_pair(w0, w1, w2, e3);
+    if (f) atomicOr(s.kb + r * FS_KBP + (c0 >> 5), f << (c0 & 31));
   }
   __syncwarp();
 }
 
-// NMS over the listed pairs and ordered emission (list order == row-major, pairs and their pixels
-// left to right).  Returns the new running total of the cell.
-__device__ __forceinline__ int fast_nms_emit(const FastCell& c, int nlist, int total, uint32_t* out, int kx0,
-                                             int ky0, int lane) {
-  for (int base = 0; base < nlist; base += 32) {
-    const int e = base + lane;
-    uint32_t f = 0, a = 0;
-    int yy = 0, q = 0, pr = 0;
-    if (e < nlist) {
-      const int tk = c.list[e];
-      const int ql = tk >> 1;
-      pr = tk & 1;
-      yy = (int)(((uint32_t)ql * c.rcq) >> 20);
-      q = c.q_first + ql - yy * c.nqr;
-      const uint32_t* p = c.hm + (yy + 2) * c.pw + q - 1;
-      a = reinterpret_cast<const uint16_t*>(p + c.pw + 1)[pr];
-      if (a != 0) {
-        // columns c-1..c+2 around the pair at c = 2*pr of word q
-        const int fs = pr ? 8 : 24;
-        uint32_t w[3];
-#pragma unroll
-        for (int d = 0; d < 3; d++) {
-          const uint32_t lo = pr ? p[d * c.pw + 1] : p[d * c.pw], hi = pr ? p[d * c.pw + 2] : p[d * c.pw + 1];
-          w[d] = __funnelshift_r(lo, hi, fs);
-        }
-        f = nms_pair(w[0], w[1], w[2]);
-      }
-    }
-    const unsigned b = __ballot_sync(0xffffffffu, f != 0);
-    if (b == 0) continue;
-    const int cnt = __popc(f);
-    int inc = cnt;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += t;
-    }
-    if (f) {
-      int pos = total + inc - cnt;
-      // coordinates relative to (minBorderX,minBorderY)=(16,16), as DistributeOctTree sees them
-      const int x = kx0 + 4 * q + 2 * pr, y = ky0 + yy;
-      if (f & 1u) out[pos++] = orbx_pack_key(x, y, (int)(a & 0xffu) - 1);
-      if (f & 2u) out[pos] = orbx_pack_key(x + 1, y, (int)(a >> 8) - 1);
-    }
-    total += __shfl_sync(0xffffffffu, inc, 31);
-  }
-  return total;
-}
-
-// Walks the quick-test byte map in row-major order, 256 quads (two words of qm per lane) at a time,
-// compacting the pixel pairs that passed into the task list.  The list is handed to the scoring
-// stage (MODE 0) or to NMS + emission (MODE 1) whenever the next 256 quads might not fit, and at the
-// end; *bands counts the hand-overs.  Returns the running emission total (MODE 1).
-template <int MODE>
-__device__ __forceinline__ int fast_sweep(const FastCell& c, int nquads, int th, int lane, int* nlist_out,
-                                          int* bands, int total, uint32_t* out, int kx0, int ky0) {
-  int nlist = 0, nb = 0;
-  for (int base = 0; base < nquads; base += 256) {
-    const int i4 = (base >> 2) + 2 * lane;  // this lane's two words of qm = 8 quads
-    uint32_t bits = 0;
-    if (4 * i4 < nquads) {
-      const uint2 mm = *reinterpret_cast<const uint2*>(c.qm + 4 * i4);
-      uint32_t x = (mm.x | (mm.x >> 1)) & 0x05050505u;  // per quad: bit0 = left pair, bit2 = right pair
-      uint32_t y = (mm.y | (mm.y >> 1)) & 0x05050505u;
-      x = (x | (x >> 1)) & 0x03030303u;                 // -> bits 0,1
-      y = (y | (y >> 1)) & 0x03030303u;
-      bits = (x | (x >> 6) | (x >> 12) | (x >> 18)) & 0xffu;
-      if (4 * i4 + 4 < nquads) bits |= ((y | (y >> 6) | (y >> 12) | (y >> 18)) & 0xffu) << 8;
-    }
-    const int cnt = __popc(bits);
-    int inc = cnt;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += t;
-    }
-    const int chunk = __shfl_sync(0xffffffffu, inc, 31);
-    if (nlist + chunk > FAST_LIST_CAP) {
-      __syncwarp();
-      if (MODE == 0) fast_score_list(c, nlist, th, lane);
-      else total = fast_nms_emit(c, nlist, total, out, kx0, ky0, lane);
-      __syncwarp();
-      nlist = 0;
-      nb++;
-    }
-    int pos = nlist + inc - cnt;
-    while (bits) {
-      const int b = __ffs(bits) - 1;
-      bits &= bits - 1;
-      c.list[pos++] = (uint16_t)(8 * i4 + b);  // (4*i4 + b/2)*2 + (b&1), b < 16 spans both words
-    }
-    nlist += chunk;
-  }
-  __syncwarp();
-  if (MODE == 0) fast_score_list(c, nlist, th, lane);
-  else total = fast_nms_emit(c, nlist, total, out, kx0, ky0, lane);
-  *nlist_out = nlist;
-  *bands = nb;
-  return total;
-}
-
-template <int QP>
-__global__ void __launch_bounds__(FAST_THREADS, 8)
-k_fast(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
-       const uint32_t* __restrict__ cell_tab, int32_t* __restrict__ cell_cnt, uint32_t* __restrict__ cand,
-       int pw, int rows_max, int qcap) {
-  extern __shared__ uint32_t fast_smem[];
+__global__ void __launch_bounds__(FS_THREADS, 7)
+k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
+             const uint32_t* __restrict__ strip_tab, int32_t* __restrict__ cell_cnt, uint32_t* __restrict__ cand,
+             int hmax, int region_words) {
+  extern __shared__ __align__(16) uint32_t fs_smem[];
   const int frame = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int cell = blockIdx.x * FAST_WARPS + warp;
-  if (cell >= P.total_cells) return;
-  const int region = 2 * pw * rows_max + FAST_LIST_CAP / 2 + (qcap >> 2);
-  FastCell c;
-  c.px = fast_smem + warp * region;
-  c.hm = c.px + pw * rows_max;
-  c.list = reinterpret_cast<uint16_t*>(c.hm + pw * rows_max);
-  c.qm = reinterpret_cast<uint8_t*>(c.hm + pw * rows_max + FAST_LIST_CAP / 2);
-  c.pw = pw;
+  const int strip = blockIdx.x * FS_WARPS + warp;
+  if (strip >= P.total_strips) return;
+  const int amap_words = (FS_APW * (hmax + 2) + 3) & ~3, kb_words = (FS_KBP * hmax + 3) & ~3;
+  FsStrip s;
+  s.tile = fs_smem + warp * region_words;
+  s.amap = s.tile + FS_TPW * (hmax + 6);
+  s.kb = s.amap + amap_words;
+  s.pb = s.kb + kb_words;
+  s.list = reinterpret_cast<uint16_t*>(s.pb + 32 * FS_MAXB2);
+  s.misc = s.pb + 32 * FS_MAXB2 + FS_CAP / 2;
 
-  // cell_tab: level << 24 | cell row << 12 | cell column (built with the plan)
-  const uint32_t ct = __ldg(cell_tab + cell);
-  const int level = (int)(ct >> 24), ci = (int)((ct >> 12) & 0xfff), cj = (int)(ct & 0xfff);
+  // strip_tab: level << 24 | cell row << 12 | first cell column (built with the plan)
+  const uint32_t stt = __ldg(strip_tab + strip);
+  const int level = (int)(stt >> 24), ci = (int)((stt >> 12) & 0xfff), cj0 = (int)(stt & 0xfff);
   const DevLevel& L = P.lv[level];
-  cell -= L.cell_base;
-  // tested zone of this cell, level coordinates
-  const int zx0 = ORBX_EDGE + cj * L.wCell, zy0 = ORBX_EDGE + ci * L.hCell;
-  const int zx1 = min(zx0 + L.wCell, L.w - ORBX_EDGE), zy1 = min(zy0 + L.hCell, L.h - ORBX_EDGE);
-  const int zw = zx1 - zx0, zh = zy1 - zy0;
-  int32_t* cnt_out = cell_cnt + (long long)frame * P.total_cells + L.cell_base + cell;
-  if (zw <= 0 || zh <= 0) {  // cell skipped / empty in the reference (:810,:819)
-    if (lane == 0) *cnt_out = 0;
+  const int k = min(L.strip_k, L.nCols - cj0);
+  const int Y0 = ORBX_EDGE + ci * L.hCell, Y1 = min(Y0 + L.hCell, L.h - ORBX_EDGE), zh = Y1 - Y0;
+  const int X0 = ORBX_EDGE + cj0 * L.wCell, X1 = min(X0 + k * L.wCell, L.w - ORBX_EDGE);
+  const int cell0 = L.cell_base + ci * L.nCols + cj0;
+  int32_t* cnt_out = cell_cnt + (long long)frame * P.total_cells + cell0;
+  if (zh <= 0 || X1 <= X0) {  // cells skipped / empty in the reference (:810,:819)
+    if (lane < k) cnt_out[lane] = 0;
     return;
   }
+  s.zh = zh;
   int pitch;
   const uint8_t* img;
   if (level == 0) { pitch = l0.pitch; img = l0.base + (long long)frame * l0.frame_stride; }
   else { pitch = L.pitch; img = arena + (long long)frame * P.arena_bytes + L.offset; }
 
-  // 1. stage pixels [zx0-3, zx1+3) x [zy0-3, zy1+3)
-  const uint8_t* tile0 = img + (long long)(zy0 - 3) * pitch + (zx0 - 3);
-  int sh;
-  const bool aligned = (pitch & 3) == 0;
-  if (aligned) {
-    sh = (int)((uintptr_t)tile0 & 3);
-    const int nw = (sh + zw + 6 + 3) >> 2;  // data words per row
-    const uint32_t* a0 = reinterpret_cast<const uint32_t*>(tile0 - sh);
-    const int wpitch = pitch >> 2;
-    if (nw <= 16) {
-      // half a warp per row: lane = (row parity, word)
-      const int col = lane & 15;
-      if (col < nw) {
-        const uint32_t* g = a0 + (lane >> 4) * wpitch + col;
-        int o = (lane >> 4) * pw + 1 + col;
-#pragma unroll 4
-        for (int r = lane >> 4; r < zh + 6; r += 2, g += 2 * wpitch, o += 2 * pw) {
-          const uint32_t v = __ldg(g);
-          c.px[o] = v;
-          c.hm[o] = (v >> 1) & 0x7f7f7f7fu;
-        }
-      }
-    } else {
-      const uint32_t rcw = ((1u << 20) + nw - 1) / nw;
-      const int nwords = nw * (zh + 6);
-#pragma unroll 4
-      for (int i = lane; i < nwords; i += 32) {
-        const int r = (int)(((uint32_t)i * rcw) >> 20), col = i - r * nw;
-        const uint32_t v = __ldg(a0 + r * wpitch + col);
-        const int o = r * pw + 1 + col;
-        c.px[o] = v;
-        c.hm[o] = (v >> 1) & 0x7f7f7f7fu;
-      }
+  // 1. stage level rows [Y0-3, Y1+3), columns [xt, xt+144)
+  const int xs = X0 & ~3;           // level column of lane 1's first pixel (strip column 0)
+  const int xt = (xs - 4) & ~15;    // level column of tile byte 0
+  s.wq0 = (xs - 4 - xt) >> 2;
+  const int trows = zh + 6;
+  const uint8_t* src0 = img + (long long)(Y0 - 3) * pitch + xt;
+  const bool al16 = ((reinterpret_cast<uintptr_t>(img) | (uintptr_t)(unsigned)pitch) & 15u) == 0;
+  if (al16) {
+    const int v = lane % 9, ro = lane / 9;
+    if (ro < 3) {
+      const bool inb = xt + 16 * v + 16 <= pitch;  // columns past the row's allocation are never needed: zero-fill
+      const uint8_t* g = src0 + (inb ? 16 * v : 0) + (long long)ro * pitch;
+      uint32_t sa = (uint32_t)__cvta_generic_to_shared(s.tile) + ro * FS_TP + 16 * v;
+      const uint32_t nb = inb ? 16u : 0u;
+      for (int r = ro; r < trows; r += 3, g += 3LL * pitch, sa += 3 * FS_TP) fs_cp_async16(sa, g, nb);
     }
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
   } else {
-    sh = 0;
-    uint8_t* pb = reinterpret_cast<uint8_t*>(c.px);
-    for (int i = lane; i < (zw + 6) * (zh + 6); i += 32) {
-      const int r = i / (zw + 6), col = i - r * (zw + 6);
-      pb[r * (pw * 4) + 4 + col] = tile0[(long long)r * pitch + col];
+    for (int i = lane; i < trows * FS_TPW; i += 32) {
+      const int r = i / FS_TPW, wq = i - r * FS_TPW, col = xt + 4 * wq;
+      const uint8_t* g = src0 + (long long)r * pitch + 4 * wq;
+      uint32_t v = 0;
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (col + j < L.w) v |= (uint32_t)g[j] << (8 * j);
+      s.tile[i] = v;
     }
   }
-  // Quads: word q of tile row r holds smem columns 4q..4q+3 = zone x 4q-(7+sh)+j, j=0..3.
-  c.colbase = 7 + sh;  // smem column of zone x = 0
-  c.q_first = c.colbase >> 2;
-  c.nqr = ((c.colbase + zw - 1) >> 2) - c.q_first + 1;  // quads per zone row
-  c.zw = zw;
-  c.zh = zh;
-  c.rcq = ((1u << 20) + c.nqr - 1) / c.nqr;
-  const int nqr = c.nqr, nquads = nqr * zh;
-  uint32_t* out = cand + (long long)frame * P.cand_total + L.cand_base + (long long)cell * L.cell_cap;
-  const int kx0 = zx0 - c.colbase - ORBX_MIN_BORDER, ky0 = zy0 - ORBX_MIN_BORDER;
+  // clear the A map (rows 0..zh+1) and the keep bitmap while the copies are in flight
+  {
+    uint4* z = reinterpret_cast<uint4*>(s.amap);
+    const int nz = (FS_APW * (zh + 2) + 3) >> 2;
+    for (int i = lane; i < nz; i += 32) z[i] = make_uint4(0, 0, 0, 0);
+    uint4* zk = reinterpret_cast<uint4*>(s.kb);
+    const int nk = (FS_KBP * zh + 3) >> 2;
+    for (int i = lane; i < nk; i += 32) zk[i] = make_uint4(0, 0, 0, 0);
+  }
+  // zone columns / cell starts as bit masks over the strip's columns
+  const int cx0 = X0 - xs, cx1 = X1 - xs;  // strip columns of the zone, cx1 <= 120
+  if (lane < 4) {
+    const int lo = max(cx0 - 32 * lane, 0), hi = min(cx1 - 32 * lane, 32);
+    s.misc[lane] = hi > lo ? ((hi - lo == 32) ? 0xffffffffu : (((1u << (hi - lo)) - 1u) << lo)) : 0u;
+  } else if (lane < 9) {
+    const int w = lane - 4;
+    uint32_t m = 0;
+    for (int j = 0; j <= k; j++) {
+      const int c = j < k ? cx0 + j * L.wCell : cx1;
+      if ((c >> 5) == w) m |= 1u << (c & 31);
+    }
+    if ((cx1 >> 5) == w) m |= 1u << (cx1 & 31);
+    s.misc[4 + w] = m;
+  }
+  if (al16) asm volatile("cp.async.wait_all;\n" ::: "memory");
+  __syncwarp();
 
-  int th = P.ini_th, total = 0;
-  bool restage = !aligned;  // hm does not hold the 7-bit tile yet
+  uint32_t* out0 = cand + (long long)frame * P.cand_total + L.cand_base + (long long)(ci * L.nCols + cj0) * L.cell_cap;
+  int th = P.ini_th;
+  uint32_t todo = (1u << k) - 1u;  // cells this attempt covers
 #pragma unroll 1
   for (int attempt = 0; attempt < 2; attempt++) {
-    __syncwarp();
-    if (restage) {
-      for (int i = lane; i < pw * (zh + 6); i += 32) c.hm[i] = (c.px[i] >> 1) & 0x7f7f7f7fu;
-      __syncwarp();
+    // 2. quick test
+    uint32_t zm = 0;
+    if (lane >= 1 && lane <= 30) {
+      const int c = 4 * (lane - 1);
+      const uint32_t nib = (s.misc[c >> 5] >> (c & 31)) & 15u;
+      zm = ((nib * 0x00204081u) & 0x01010101u) << 7;
     }
-    if (lane == 0) reinterpret_cast<uint32_t*>(c.qm)[(nquads - 1) >> 2] = 0;  // tail bytes of the last word
-    __syncwarp();
-
-    // 2. quick test: lane = (segment of rows, quad column)
     const uint32_t cadd = (uint32_t)(128 - ((th + 1) >> 1)) * 0x01010101u;
+    const int nblk = (zh + 6) / 7;
+    {
+      const uint32_t* trow = s.tile + s.wq0 + lane;
+      uint32_t C[7];
+#pragma unroll
+      for (int i = 0; i < 6; i++) C[i] = fs_halve(trow[i * FS_TPW]);
+      trow += 6 * FS_TPW;
+      uint16_t* pb16 = reinterpret_cast<uint16_t*>(s.pb + lane);
 #pragma unroll 1
-    for (int cg = 0; cg < nqr; cg += 32) {
-      const int ncols = min(32, nqr - cg);
-      const int nseg = ncols <= 10 ? 3 : (ncols <= 16 ? 2 : 1);
-      const int rps = (zh + nseg - 1) / nseg;
-      int seg = lane >= 2 * ncols ? 2 : (lane >= ncols ? 1 : 0);
-      const int qi = lane - seg * ncols;
-      const bool active = seg < nseg && qi < ncols;
-      if (!active) seg = 0;
-      const int y0 = seg * rps;
-      const int nrow = active ? min(zh, y0 + rps) - y0 : 0;  // rows this lane reports
-      const uint32_t* hcol = c.hm + c.q_first + cg + (active ? qi : 0);
-      const int hlast = (zh + 5) * pw;  // last staged row
-      int hp = y0 * pw;
-      uint8_t* qp = c.qm + y0 * nqr + cg + (active ? qi : 0);
-      QuickWin<QP> W;
-      quick_load<0, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
-      quick_load<1, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
-      quick_load<2, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
-      quick_load<3, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
-      quick_load<4, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
-      quick_load<5, QP>(W, hcol + hp); hp = min(hp + pw, hlast);
-#define QSTEP(PH)                                       \
-  {                                                     \
-    quick_load<(PH + 6) % 7, QP>(W, hcol + hp);                  \
-    hp = min(hp + pw, hlast);                           \
-    const uint32_t m = quick_test<PH, QP>(W, cadd);         \
-    if (base + PH < nrow) qp[PH * nqr] = (uint8_t)m;    \
-  }
-#pragma unroll 1
-      for (int base = 0; base < rps; base += 7) {
-        QSTEP(0) QSTEP(1) QSTEP(2) QSTEP(3) QSTEP(4) QSTEP(5) QSTEP(6)
-        qp += 7 * nqr;
+      for (int blk = 0; blk < nblk; blk++, trow += 7 * FS_TPW) {
+        uint32_t acc = 0;
+#pragma unroll
+        for (int ph = 0; ph < 7; ph++) {
+          C[(ph + 6) % 7] = fs_halve(trow[ph * FS_TPW]);
+          const uint32_t v = C[(ph + 3) % 7];
+          const uint32_t lw = __shfl_up_sync(0xffffffffu, v, 1), rw = __shfl_down_sync(0xffffffffu, v, 1);
+          const uint32_t l3 = __byte_perm(lw, v, 0x4321), r3 = __byte_perm(v, rw, 0x6543);
+#define QT(x) (__vabsdiffu4(v, (x)) + cadd)
+          uint32_t g = (QT(C[(ph + 6) % 7]) | QT(C[ph % 7])) & zm;  // ring 0 (0,+3) | ring 8 (0,-3)
+          g &= QT(r3) | QT(l3);                                     // ring 4 (+3,0) | ring 12 (-3,0)
+#undef QT
+          // bit 7 / 23 of t: a pixel of pair 0 / 1 passed -> bits 30 / 31
+          const uint32_t t = (g | (g >> 8)) & 0x00800080u;
+          acc = (acc >> 2) | ((t * 0x00800100u) & 0xC0000000u);
+        }
+        // rows 7blk..7blk+6 sit at bits 18..31: keep them as the low/high half of the lane's word blk/2
+        pb16[((blk >> 1) * 32) * 2 + (blk & 1)] = (uint16_t)(acc >> 16);
       }
-#undef QSTEP
     }
     __syncwarp();
-    // hm becomes the A map: clear the rows NMS can read (tile rows 2 .. zh+3)
-    for (int i = 2 * pw + lane; i < (zh + 4) * pw; i += 32) c.hm[i] = 0;
-    __syncwarp();
-
-    // 3.-5. list the pixel pairs that passed, score them, then NMS + ordered emission
-    int nlist, bands;
-    fast_sweep<0>(c, nquads, th, lane, &nlist, &bands, 0, out, kx0, ky0);
-    if (bands == 0) total = fast_nms_emit(c, nlist, 0, out, kx0, ky0, lane);
-    else total = fast_sweep<1>(c, nquads, th, lane, &nlist, &bands, 0, out, kx0, ky0);
-    if (total > 0 || th == P.min_th) break;
-    // 6. nothing at iniThFAST: the reference runs FAST again on the cell with minThFAST
+    // 3. this lane's pass bits, rows past the zone masked off
+    uint32_t pw[FS_MAXB2];
+    int cnt = 0;
+#pragma unroll
+    for (int b = 0; b < FS_MAXB2; b++) {
+      const int nv = min(max(zh - 14 * b, 0), 14);
+      const int nlo = min(nv, 7), nhi = nv - nlo;
+      const uint32_t m = (((1u << (2 * nlo)) - 1u) << 2) | (((1u << (2 * nhi)) - 1u) << 18);
+      pw[b] = nv > 0 ? (s.pb[b * 32 + lane] & m) : 0u;
+      cnt += __popc(pw[b]);
+    }
+    int inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    const int total_tasks = __shfl_sync(0xffffffffu, inc, 31), off = inc - cnt;
+    // 4./5. score, then NMS
+    if (total_tasks <= FS_CAP) {
+      fs_fill(s, pw, off, 0, lane);
+      const int nk = fs_score<true>(s, total_tasks, th, lane);
+      fs_nms(s, nk, lane);
+    } else {
+      for (int cb = 0; cb < total_tasks; cb += FS_CAP) {
+        fs_fill(s, pw, off, cb, lane);
+        fs_score<false>(s, min(FS_CAP, total_tasks - cb), th, lane);
+      }
+      for (int cb = 0; cb < total_tasks; cb += FS_CAP) {
+        fs_fill(s, pw, off, cb, lane);
+        fs_nms(s, min(FS_CAP, total_tasks - cb), lane);
+      }
+    }
+    // 6. per cell: ordered emission
+    uint32_t redo = 0;
+    const uint8_t* ab = reinterpret_cast<const uint8_t*>(s.amap);
+#pragma unroll 1
+    for (int j = 0; j < k; j++) {
+      if (!((todo >> j) & 1u)) continue;
+      const int cs = cx0 + j * L.wCell, ce = min(cs + L.wCell, cx1);
+      int total = 0;
+      if (ce > cs) {
+        const int wlo = cs >> 5, whi = (ce - 1) >> 5;
+        const uint32_t mlo = 0xffffffffu << (cs & 31), mhi = 0xffffffffu >> (31 - ((ce - 1) & 31));
+        uint32_t* out = out0 + (long long)j * L.cell_cap;
+        for (int rb = 0; rb < zh; rb += 64) {
+          const int r0 = rb + 2 * lane;
+          int c0n = 0, c1n = 0;
+          for (int w = wlo; w <= whi; w++) {
+            const uint32_t m = (w == wlo ? mlo : 0xffffffffu) & (w == whi ? mhi : 0xffffffffu);
+            if (r0 < zh) c0n += __popc(s.kb[r0 * FS_KBP + w] & m);
+            if (r0 + 1 < zh) c1n += __popc(s.kb[(r0 + 1) * FS_KBP + w] & m);
+          }
+          int inc2 = c0n + c1n;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc2, o);
+            if (lane >= o) inc2 += t;
+          }
+          int pos = total + inc2 - (c0n + c1n);
+          total += __shfl_sync(0xffffffffu, inc2, 31);
+          if (c0n + c1n) {
+            for (int rr = r0; rr < r0 + 2; rr++) {
+              if (rr >= zh) break;
+              for (int w = wlo; w <= whi; w++) {
+                uint32_t bits = s.kb[rr * FS_KBP + w] & (w == wlo ? mlo : 0xffffffffu) & (w == whi ? mhi : 0xffffffffu);
+                while (bits) {
+                  const int c = 32 * w + __ffs(bits) - 1;
+                  bits &= bits - 1;
+                  const int a = ab[(rr + 1) * FS_AP + 4 + c];
+                  // coordinates relative to (minBorderX,minBorderY)=(16,16), as DistributeOctTree sees them
+                  out[pos++] = orbx_pack_key(xs + c - ORBX_MIN_BORDER, Y0 + rr - ORBX_MIN_BORDER, a - 1);
+                }
+              }
+            }
+          }
+        }
+        if (total == 0) redo |= 1u << j;
+      }
+      if (lane == 0) cnt_out[j] = total;
+    }
+    // 7. nothing at iniThFAST: the reference runs FAST again on the cell with minThFAST
+    if (redo == 0 || th == P.min_th) break;
     th = P.min_th;
-    restage = true;
+    todo = redo;
+    __syncwarp();
+    if (lane < 4) {
+      uint32_t m = 0;
+      for (int j = 0; j < k; j++) {
+        if (!((redo >> j) & 1u)) continue;
+        const int cs = cx0 + j * L.wCell, ce = min(cs + L.wCell, cx1);
+        const int lo = max(cs - 32 * lane, 0), hi = min(ce - 32 * lane, 32);
+        if (hi > lo) m |= (hi - lo == 32) ? 0xffffffffu : (((1u << (hi - lo)) - 1u) << lo);
+      }
+      s.misc[lane] = m;
+    }
+    __syncwarp();
   }
-  if (lane == 0) *cnt_out = total;
+}
+
+static size_t fs_region_words(int hmax) {
+  const int amap_words = (FS_APW * (hmax + 2) + 3) & ~3, kb_words = (FS_KBP * hmax + 3) & ~3;
+  return (size_t)FS_TPW * (hmax + 6) + amap_words + kb_words + 32 * FS_MAXB2 + FS_CAP / 2 + 12;
+}
+
+cudaError_t orbx_launch_fast_strip(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* strip_tab,
+                                   int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st) {
+  int hmax = 0;
+  for (int l = 0; l < P.nlevels; l++) hmax = max(hmax, P.lv[l].hCell);
+  if (hmax > 14 * FS_MAXB2) return cudaErrorInvalidValue;
+  const size_t region = (fs_region_words(hmax) + 3) & ~(size_t)3;
+  const size_t smem = FS_WARPS * region * sizeof(uint32_t);
+  cudaError_t e = orbx_ensure_dyn_smem(ORBX_SMEM_FAST_STRIP, (const void*)k_fast_strip, smem);
+  if (e != cudaSuccess) return e;
+  dim3 grd((P.total_strips + FS_WARPS - 1) / FS_WARPS, batch);
+  k_fast_strip<<<grd, FS_THREADS, smem, st>>>(P, l0, arena, strip_tab, cell_cnt, cand, hmax, (int)region);
+  return cudaGetLastError();
 }
 
 cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* cell_tab,
-                             int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st) {
-  // shared-memory geometry from the largest cell of the plan
-  int pw = 0, rows = 0, cap = 0;
-  for (int l = 0; l < P.nlevels; l++) {
-    const int nw = (3 + P.lv[l].wCell + 6 + 3) >> 2;
-    pw = max(pw, nw + 2);
-    rows = max(rows, P.lv[l].hCell + 6);
-    cap = max(cap, ((P.lv[l].wCell + 3 + 3) / 4 + 2) * P.lv[l].hCell);
-  }
-  cap = (cap + 8 + 15) & ~15;  // quads per cell (bytes of qm) + one spare uint2, regions stay 8-byte aligned
-  const size_t smem = (size_t)FAST_WARPS * (2 * pw * rows + FAST_LIST_CAP / 2 + (cap >> 2)) * sizeof(uint32_t);
-  static const int qp = [] { const char* e = getenv("ORBX_FAST_PAIRS"); return e && atoi(e) == 4 ? 4 : FAST_QUICK_PAIRS; }();
-  const void* fn = qp == 4 ? (const void*)k_fast<4> : (const void*)k_fast<2>;
-  cudaError_t e = orbx_ensure_dyn_smem(qp == 4 ? ORBX_SMEM_FAST4 : ORBX_SMEM_FAST, fn, smem);
-  if (e != cudaSuccess) return e;
-  dim3 grd((P.total_cells + FAST_WARPS - 1) / FAST_WARPS, batch);
-  if (qp == 4) k_fast<4><<<grd, FAST_THREADS, smem, st>>>(P, l0, arena, cell_tab, cell_cnt, cand, pw, rows, cap);
-  else k_fast<2><<<grd, FAST_THREADS, smem, st>>>(P, l0, arena, cell_tab, cell_cnt, cand, pw, rows, cap);
-  return cudaGetLastError();
+                             const uint32_t* strip_tab, int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st) {
+  // ORBX_FAST_IMPL=cell selects the first-generation cell-per-warp kernel (A/B measurements)
+  static const bool cell = [] { const char* e = getenv("ORBX_FAST_IMPL"); return e && e[0] == 'c'; }();
+  if (cell) return orbx_launch_fast_cell(P, l0, arena, cell_tab, cell_cnt, cand, batch, st);
+  return orbx_launch_fast_strip(P, l0, arena, strip_tab, cell_cnt, cand, batch, st);
 }

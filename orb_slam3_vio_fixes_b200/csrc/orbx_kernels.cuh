@@ -16,13 +16,14 @@ struct DevLevel {
   float hX, scale, patch_size;
   int xtab, ytab, fast_resize, tile_resize;
   int btile_base, btiles_x;
+  int strip_k;
   long long offset;     // bytes, inside a frame's pyramid arena
   long long cand_base;  // uint32 units, inside a frame's candidate arena
 };
 
 struct DevPlan {
   DevLevel lv[ORBX_PLAN_MAX_LEVELS];
-  int nlevels, total_cells, kp_total_cap, ini_th, min_th, total_btiles;
+  int nlevels, total_cells, kp_total_cap, ini_th, min_th, total_btiles, total_strips;
   long long cand_total;   // uint32 per frame
   long long arena_bytes;  // per frame
   int umax[16];
@@ -63,7 +64,11 @@ struct OrbxStereoPyr {
 cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, const OrbxTap* xtaps,
                                 const OrbxTap* ytaps, int batch, cudaStream_t st);
 cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* cell_tab,
-                             int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st);
+                             const uint32_t* strip_tab, int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st);
+cudaError_t orbx_launch_fast_cell(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* cell_tab,
+                                  int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st);
+cudaError_t orbx_launch_fast_strip(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* strip_tab,
+                                   int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st);
 cudaError_t orbx_launch_octree(const DevPlan& P, const int32_t* cell_cnt, const uint32_t* cand,
                                uint32_t* gkeys, int16_t* glabels, uint32_t* sel, int32_t* sel_cnt,
                                int32_t* status, int batch, size_t smem_bytes, int smem_keys, int node_cap,
@@ -96,5 +101,5 @@ size_t orbx_octree_smem_bytes(int smem_keys, int node_cap, int max_cells);
 // cudaFuncAttributeMaxDynamicSharedMemorySize belongs to (function, device), not to a handle: this keeps a
 // per-device, monotone (only ever raised) cache per kernel slot, under a mutex, so handles of different sizes,
 // on different devices, created from different threads never lower or miss each other's opt-in.
-enum OrbxSmemSlot { ORBX_SMEM_FAST = 0, ORBX_SMEM_FAST4, ORBX_SMEM_OCTREE, ORBX_SMEM_BOW_VECTORS, ORBX_SMEM_ROWBAND, ORBX_SMEM_SLOTS };
+enum OrbxSmemSlot { ORBX_SMEM_FAST = 0, ORBX_SMEM_FAST4, ORBX_SMEM_FAST_STRIP, ORBX_SMEM_OCTREE, ORBX_SMEM_BOW_VECTORS, ORBX_SMEM_ROWBAND, ORBX_SMEM_SLOTS };
 cudaError_t orbx_ensure_dyn_smem(OrbxSmemSlot slot, const void* func, size_t bytes);

@@ -13,6 +13,7 @@
 
 #define ORBX_PLAN_MAX_LEVELS 12
 #define ORBX_BLUR_ROWS 35  // rows per warp tile of k_blur_levels (blur.cu BL_RB)
+#define ORBX_FAST_STRIP_PX 120  // columns a FAST strip can test per row (lanes 1..30 x 4 px)
 #define ORBX_BLUR_TILE_WORDS 30  // output words (4 px) per warp tile row: lanes 1..30, lanes 0/31 are halo
 
 struct OrbxLevel {
@@ -36,6 +37,8 @@ struct OrbxLevel {
   int fast_resize;  // the 4-column tap windows of k_resize_walk hold for every column group
   int tile_resize;  // every 128x64 output tile fits k_resize_tile's shared-memory source window
   int btile_base, btiles_x;  // warp tiles (ORBX_BLUR_TILE_WORDS words x ORBX_BLUR_ROWS rows) of k_blur_levels: first tile of this level, tiles per row
+  // FAST strips (k_fast_strip): a strip = strip_k consecutive cells of one cell row, one warp each
+  int strip_k, strips_per_row, strip_base;
 };
 
 struct OrbxPlan {
@@ -46,6 +49,7 @@ struct OrbxPlan {
   long long arena_bytes;     // pyramid bytes per frame (all levels)
   int kp_total_cap;          // Σ kp_cap
   int total_btiles;          // Σ blur tiles per frame
+  int total_strips;          // Σ FAST strips per frame
   int max_keypoints;         // Σ kp_max (what one frame can return; nfeatures+3*nlevels normally)
   float scale[ORBX_PLAN_MAX_LEVELS], inv_scale[ORBX_PLAN_MAX_LEVELS];
   float sigma2[ORBX_PLAN_MAX_LEVELS], inv_sigma2[ORBX_PLAN_MAX_LEVELS];
@@ -107,7 +111,7 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
     }
   }
   long long offset = 0, cand = 0;
-  int cells = 0, kpb = 0, maxk = 0, btiles = 0;
+  int cells = 0, kpb = 0, maxk = 0, btiles = 0, strips = 0;
   xtaps->clear(); ytaps->clear();
   for (int l = 0; l < nlevels; l++) {
     OrbxLevel& L = P->lv[l];
@@ -132,6 +136,13 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
     L.hCell = (int)ceilf(fh / L.nRows);
     L.cell_base = cells;
     cells += L.nCols * L.nRows;
+    // strips: as many whole cells as fit the 120 tested columns after the <= 3 px of word alignment slack
+    L.strip_k = (ORBX_FAST_STRIP_PX - 3) / L.wCell;
+    if (L.strip_k < 1) return -1;
+    if (L.strip_k > L.nCols) L.strip_k = L.nCols;
+    L.strips_per_row = (L.nCols + L.strip_k - 1) / L.strip_k;
+    L.strip_base = strips;
+    strips += L.strips_per_row * L.nRows;
     L.cell_cap = ((L.wCell + 1) / 2) * ((L.hCell + 1) / 2);
     L.cand_base = cand;
     L.cand_cap = (long long)L.nCols * L.nRows * L.cell_cap;
@@ -204,6 +215,7 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
   P->arena_bytes = (offset + 255) & ~255LL;
   P->kp_total_cap = kpb;
   P->total_btiles = btiles;
+  P->total_strips = strips;
   P->max_keypoints = maxk;
   return 0;
 }
