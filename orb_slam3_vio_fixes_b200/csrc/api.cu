@@ -75,7 +75,7 @@ struct orbx_extractor_s {
 static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
   memset(D, 0, sizeof(*D));
   D->nlevels = P.nlevels; D->total_cells = P.total_cells; D->kp_total_cap = P.kp_total_cap;
-  D->ini_th = P.ini_th; D->min_th = P.min_th; D->total_btiles = P.total_btiles; D->total_strips = P.total_strips; D->cand_total = P.cand_total; D->arena_bytes = P.arena_bytes;
+  D->ini_th = P.ini_th; D->min_th = P.min_th; D->total_btiles = P.total_btiles; D->total_strips = P.total_strips; D->strips_a = P.strips_a; D->hmax_a = P.hmax_a; D->hmax_b = P.hmax_b; D->cand_total = P.cand_total; D->arena_bytes = P.arena_bytes;
   for (int i = 0; i < 16; i++) D->umax[i] = P.umax[i];
   for (int l = 0; l < P.nlevels; l++) {
     const OrbxLevel& s = P.lv[l];

@@ -29,15 +29,15 @@
 #include "fast_arc.cuh"
 #include "orbx_kernels.cuh"
 
+#ifndef FS_WARPS
 #define FS_WARPS 2
+#endif
 #define FS_THREADS (FS_WARPS * 32)
 #define FS_TP 144            // tile row pitch in bytes: 9 vectors of 16 B cover lane words 0..31 at word offset <= 3
 #define FS_TPW (FS_TP / 4)   // 36 words
-#define FS_AP 132            // A-map row pitch in bytes: 4 (pad) + 120 (columns) + 8 (pad), odd word count
-#define FS_APW (FS_AP / 4)   // 33 words
-#define FS_KBP 5             // keep-bitmap words per row (4 used: 120 columns)
-#define FS_CAP 512           // pair tasks per chunk of the list
-#define FS_MAXB2 5           // pass-bit words per lane: 14 rows each (zh <= 69)
+#define FS_APW 32            // A-map row pitch in words: word 0 = pad, words 1..30 = strip columns 0..119, word 31 = pad
+#define FS_KBW 4             // keep-bitmap words per row (120 columns)
+#define FS_MAXH 96           // tallest zone: three rows per lane in the emission scan
 
 __device__ __forceinline__ uint32_t fs_halve(uint32_t v) { return (v >> 1) & 0x7f7f7f7fu; }
 
@@ -45,145 +45,170 @@ __device__ __forceinline__ void fs_cp_async16(uint32_t saddr, const void* g, uin
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(saddr), "l"(g), "r"(nbytes) : "memory");
 }
 
-// NMS of the pixel pair in bytes 1,2 of w1.  w0,w1,w2 = rows above / at / below with the A values of columns
-// c-1..c+2 (bytes 0..3); e3 bit i = a cell starts at column c+i (its left neighbour belongs to another cell,
-// whose corners the reference's per-cell cv::FAST never sees).  cv::FAST keeps a corner when its score A-1 is
-// strictly greater than all 8 neighbouring scores (0 for non-corners): keep <=> A > max(1, neighbours' A).
-__device__ __forceinline__ uint32_t fs_nms_pair(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t e3) {
-  uint32_t mA = 0x00ffffffu, mB = 0xffffff00u;
-  if (e3 & 1u) mA &= 0xffffff00u;
-  if (e3 & 2u) { mA &= 0xff00ffffu; mB &= 0xffff00ffu; }
-  if (e3 & 4u) mB &= 0x00ffffffu;
-  uint32_t keep = 0;
-  {
-    const uint32_t x0 = w0 & mA, x1 = w1 & mA & 0xffff00ffu, x2 = w2 & mA;
-    const uint32_t ve = __vimax3_u16x2(x0 & 0x00ff00ffu, x1 & 0x00ff00ffu, x2 & 0x00ff00ffu);
-    const uint32_t vo = __vimax3_u16x2((x0 >> 8) & 0x00ff00ffu, (x1 >> 8) & 0x00ff00ffu, (x2 >> 8) & 0x00ff00ffu);
-    const uint32_t t = __vmaxu2(ve, vo);
-    const uint32_t m = max(max(t & 0xffffu, t >> 16), 1u);
-    if (((w1 >> 8) & 0xffu) > m) keep |= 1u;
-  }
-  {
-    const uint32_t x0 = w0 & mB, x1 = w1 & mB & 0xff00ffffu, x2 = w2 & mB;
-    const uint32_t ve = __vimax3_u16x2(x0 & 0x00ff00ffu, x1 & 0x00ff00ffu, x2 & 0x00ff00ffu);
-    const uint32_t vo = __vimax3_u16x2((x0 >> 8) & 0x00ff00ffu, (x1 >> 8) & 0x00ff00ffu, (x2 >> 8) & 0x00ff00ffu);
-    const uint32_t t = __vmaxu2(ve, vo);
-    const uint32_t m = max(max(t & 0xffffu, t >> 16), 1u);
-    if (((w1 >> 16) & 0xffu) > m) keep |= 2u;
-  }
-  return keep;
-}
-
 // Shared memory of one warp (32-bit words):
 //   tile[FS_TPW * (hmax+6)]   staged pixels: tile row r = level row Y0-3+r, tile byte b = level column xt+b
 //   amap[FS_APW * (hmax+2)]   arc strengths: row r+1 = zone row r, byte 4+c = strip column c (level column xs+c)
-//   kb[FS_KBP * hmax]         keep bitmap: bit c of row r
-//   pb[32 * FS_MAXB2]         pass bits: word b of lane l = rows 14b..14b+13 (two 7-row halves, see below)
-//   list[FS_CAP] u16          tasks: row << 6 | lane << 1 | pair
+//   kb[FS_KBW * hmax]         keep bitmap: bit c of row r
+//   rowpre[hmax]              per zone row: corners kept in the rows above, per cell (11 | 11 | 10 bits)
+//   list[30 * (hmax+6)] u16   quad tasks, row-major: row << 5 | lane
 //   misc[12]                  zbits[4] (zone columns), ledge[5] (columns where a cell starts / the zone ends)
 struct FsStrip {
-  uint32_t *tile, *amap, *kb, *pb, *misc;
+  uint32_t *tile, *amap, *kb, *rowpre, *misc;
   uint16_t* list;
   int wq0;  // tile word of lane 0
   int zh;
 };
 
-// Task list of chunk [cb, cb+FS_CAP) of the pass bits pw[] (lane-private), off = this lane's first index.
-__device__ __forceinline__ void fs_fill(const FsStrip& s, const uint32_t (&pw)[FS_MAXB2], int off, int cb, int lane) {
-  int pos = off - cb;
+// Quick test over the whole strip, compacted on the fly: lane = one 4-pixel word column (a "quad" per row),
+// walking down the rows with the last 7 rows (7-bit pixels) in registers.  A quad passes when one of its
+// pixels has |v-ring| > t on at least one pixel of each axial ring pair; every row's passing quads are
+// appended to the task list with one ballot (row-major order).  Returns the number of tasks in rows < zh.
+__device__ __forceinline__ int fs_quick(const FsStrip& s, int th, uint32_t zm, int lane) {
+  const uint32_t cadd = (uint32_t)(128 - ((th + 1) >> 1)) * 0x01010101u;
+  const int zh = s.zh, nblk = (zh + 6) / 7;
+  const uint32_t ltm = (1u << lane) - 1u;
+  const uint32_t* trow = s.tile + s.wq0 + lane;
+  uint32_t C[7];
 #pragma unroll
-  for (int b = 0; b < FS_MAXB2; b++) {
-    uint32_t w = pw[b];
-    while (w) {
-      const int bit = __ffs(w) - 1;
-      w &= w - 1;
-      // low half: rows 0..6 at bits 2+2j, high half: rows 7..13 at bits 18+2(j-7); even bit = pair 0
-      const int row = 14 * b + 7 * (bit >> 4) + (((bit & 15) - 2) >> 1);
-      if ((unsigned)pos < (unsigned)FS_CAP) s.list[pos] = (uint16_t)((row << 6) | (lane << 1) | (bit & 1));
-      pos++;
+  for (int i = 0; i < 6; i++) C[i] = fs_halve(trow[i * FS_TPW]);
+  trow += 6 * FS_TPW;
+  int base = 0, nv = 0;
+  uint32_t code = (uint32_t)lane;
+#pragma unroll 1
+  for (int blk = 0; blk < nblk; blk++, trow += 7 * FS_TPW) {
+#pragma unroll
+    for (int ph = 0; ph < 7; ph++) {
+      C[(ph + 6) % 7] = fs_halve(trow[ph * FS_TPW]);
+      const uint32_t v = C[(ph + 3) % 7];
+      const uint32_t lw = __shfl_up_sync(0xffffffffu, v, 1), rw = __shfl_down_sync(0xffffffffu, v, 1);
+      const uint32_t l3 = __byte_perm(lw, v, 0x4321), r3 = __byte_perm(v, rw, 0x6543);
+#define QT(x) (__vabsdiffu4(v, (x)) + cadd)
+      uint32_t g = (QT(C[(ph + 6) % 7]) | QT(C[ph % 7])) & zm;  // ring 0 (0,+3) | ring 8 (0,-3); zm keeps bit 7 of zone bytes
+      g &= QT(r3) | QT(l3);                                     // ring 4 (+3,0) | ring 12 (-3,0)
+#undef QT
+      const bool pass = g != 0;
+      const unsigned bal = __ballot_sync(0xffffffffu, pass);
+      if (pass) s.list[base + __popc(bal & ltm)] = (uint16_t)(code + 32u * ph);
+      base += __popc(bal);
+      if (7 * blk + ph < zh) nv = base;
     }
+    code += 7u * 32u;
   }
   __syncwarp();
+  return nv;
 }
 
-// Arc strength of the n listed pairs into the A map; with COMPACT the pairs that hold a corner move to the
-// front of the list (returns their number), otherwise returns n.
-template <bool COMPACT>
+// Arc strength of the n listed quads into the A map (0 where A <= th or outside the zone); the quads that
+// hold a corner move to the front of the list (order kept); returns their number.
 __device__ __forceinline__ int fs_score(const FsStrip& s, int n, int th, int lane) {
+  const uint32_t th4 = (uint32_t)th * 0x01010101u;
   int nkeep = 0;
   for (int base = 0; base < n; base += 32) {
     const int e = base + lane;
     const bool act = e < n;
-    const uint32_t tk = act ? (uint32_t)s.list[e] : 2u;  // idle lanes score the pair of lane 1, row 0 (discarded)
-    const int r = (int)(tk >> 6), ql = (int)((tk >> 1) & 31u), p = (int)(tk & 1u);
+    const uint32_t tk = act ? (uint32_t)s.list[e] : 1u;  // idle lanes score the quad of lane 1, row 0 (discarded)
+    const int r = (int)(tk >> 5), ql = (int)(tk & 31u);
     const uint32_t* tp = s.tile + r * FS_TPW + s.wq0 + ql - 1;
-    const int fs = 16 * p;
     uint32_t rw[7][3];
 #pragma unroll
     for (int d = 0; d < 7; d++) {
-      const uint32_t w0 = tp[d * FS_TPW], w1 = tp[d * FS_TPW + 1], w2 = tp[d * FS_TPW + 2];
-      rw[d][0] = __funnelshift_r(w0, w1, fs);
-      rw[d][1] = __funnelshift_r(w1, w2, fs);
-      rw[d][2] = w2 >> fs;
+      rw[d][0] = tp[d * FS_TPW];
+      rw[d][1] = tp[d * FS_TPW + 1];
+      rw[d][2] = tp[d * FS_TPW + 2];
     }
-    const uint32_t a = arc_pair<0>(rw);
-    const int c0 = 4 * (ql - 1) + 2 * p;  // strip column of the left pixel
-    const uint32_t zz = (s.misc[c0 >> 5] >> (c0 & 31)) & 3u;
-    uint32_t keep = 0;
-    if ((int)(a & 0xffu) > th && (zz & 1u)) keep |= 0x00ffu;
-    if ((int)(a >> 8) > th && (zz & 2u)) keep |= 0xff00u;
-    const uint32_t av = a & keep;
-    if (act) *reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(s.amap) + (r + 1) * FS_AP + 4 + c0) = (uint16_t)av;
-    if (COMPACT) {
-      const bool sv = act && av != 0;
-      const unsigned bal = __ballot_sync(0xffffffffu, sv);
-      if (sv) s.list[nkeep + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)tk;
-      nkeep += __popc(bal);
-    }
+    const uint32_t a = arc_pair<0>(rw) | (arc_pair<2>(rw) << 16);
+    const int c0 = 4 * (ql - 1);  // strip column of the quad's first pixel
+    const uint32_t nib = (s.misc[c0 >> 5] >> (c0 & 31)) & 15u;
+    const uint32_t zmask = ((nib * 0x00204081u) & 0x01010101u) * 0xffu;
+    const uint32_t av = a & __vcmpgtu4(a, th4) & zmask;
+    if (act) s.amap[(r + 1) * FS_APW + ql] = av;
+    const bool sv = act && av != 0;
+    const unsigned bal = __ballot_sync(0xffffffffu, sv);
+    __syncwarp();  // every lane has read its entry of this batch before the compacted entries land
+    if (sv) s.list[nkeep + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)tk;
+    nkeep += __popc(bal);
   }
   __syncwarp();
-  return COMPACT ? nkeep : n;
+  return nkeep;
 }
 
-// NMS of the n listed pairs (pairs without a corner are skipped) into the keep bitmap.
+// NMS of a quad.  w[j][0..2] = A-map words ql-1, ql, ql+1 of the rows above / at / below; e5 bit i = a cell
+// starts at the quad's column i (i = 4: the next quad's first column): the column to its left belongs to
+// another cell, whose corners the reference's per-cell cv::FAST never sees.  cv::FAST keeps a corner when its
+// score A-1 is strictly greater than all 8 neighbouring scores (0 for non-corners): keep <=> A > max(1,
+// neighbours' A).  Returns one bit per pixel.
+__device__ __forceinline__ uint32_t fs_nms_quad(const uint32_t (&w)[3][3], uint32_t e5) {
+  uint32_t p02[3], p13[3], p24[3], p35[3];
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    const uint32_t X = __funnelshift_r(w[j][0], w[j][1], 24);  // columns -1..2 of the quad
+    const uint32_t Y = __funnelshift_r(w[j][1], w[j][2], 8);   // columns 1..4
+    p02[j] = X & 0x00ff00ffu; p13[j] = (X >> 8) & 0x00ff00ffu;
+    p24[j] = Y & 0x00ff00ffu; p35[j] = (Y >> 8) & 0x00ff00ffu;
+  }
+  // window position p = column p-1; pixel i sits at position i+1, its neighbours at i and i+2
+  uint32_t m02 = __vimax3_u16x2(p02[0], p02[1], p02[2]), m13 = __vimax3_u16x2(p13[0], p13[1], p13[2]);
+  uint32_t m24 = __vimax3_u16x2(p24[0], p24[1], p24[2]), m35 = __vimax3_u16x2(p35[0], p35[1], p35[2]);
+  const uint32_t c13 = __vmaxu2(p13[0], p13[2]), c24 = __vmaxu2(p24[0], p24[2]);
+  uint32_t r24 = m24, l13 = m13;
+  if (e5) {
+    // pixel i: left column out when a cell starts at i, right column out when one starts at i+1
+    const uint32_t k0 = (e5 & 1u) ? 0u : 0xffffu, k1 = (e5 & 2u) ? 0u : 0xffffu, k2 = (e5 & 4u) ? 0u : 0xffffu,
+                   k3 = (e5 & 8u) ? 0u : 0xffffu, k4 = (e5 & 16u) ? 0u : 0xffffu;
+    m02 &= k0 | (k2 << 16);  // left of pixels 0,2
+    r24 &= k1 | (k3 << 16);  // right of pixels 0,2
+    l13 &= k1 | (k3 << 16);  // left of pixels 1,3
+    m35 &= k2 | (k4 << 16);  // right of pixels 1,3
+  }
+  const uint32_t n02 = __vmaxu2(__vimax3_u16x2(m02, r24, c13), 0x00010001u);
+  const uint32_t n13 = __vmaxu2(__vimax3_u16x2(l13, m35, c24), 0x00010001u);
+  // own > n  <=>  bit 8 of (256 + n - own) clear, per 16-bit lane (no borrow crosses lanes)
+  const uint32_t k02 = ~((n02 | 0x01000100u) - p13[1]) & 0x01000100u;
+  const uint32_t k13 = ~((n13 | 0x01000100u) - p24[1]) & 0x01000100u;
+  return ((k02 >> 8) & 1u) | ((k13 >> 7) & 2u) | ((k02 >> 22) & 4u) | ((k13 >> 21) & 8u);
+}
+
+// NMS of the n listed quads (all hold a corner) into the keep bitmap.
 __device__ __forceinline__ void fs_nms(const FsStrip& s, int n, int lane) {
   const uint32_t* ledge = s.misc + 4;
   for (int e = lane; e < n; e += 32) {
     const uint32_t tk = s.list[e];
-    const int r = (int)(tk >> 6), ql = (int)((tk >> 1) & 31u), p = (int)(tk & 1u);
-    const int c0 = 4 * (ql - 1) + 2 * p;
-    const uint32_t a = *reinterpret_cast<const uint16_t*>(reinterpret_cast<const uint8_t*>(s.amap) + (r + 1) * FS_AP + 4 + c0);
-    if (a == 0) continue;
-    // columns c0-1..c0+2 = bytes 3+c0..6+c0 of the A-map row; rows r, r+1, r+2 = zone rows r-1, r, r+1
-    const uint32_t* wp = s.amap + r * FS_APW + ((3 + c0) >> 2);
-    const int fs = p ? 8 : 24;
-    const uint32_t w0 = __funnelshift_r(wp[0], wp[1], fs);
-    const uint32_t w1 = __funnelshift_r(wp[FS_APW], wp[FS_APW + 1], fs);
-    const uint32_t w2 = __funnelshift_r(wp[2 * FS_APW], wp[2 * FS_APW + 1], fs);
-    const uint32_t e3 = __funnelshift_r(ledge[c0 >> 5], ledge[(c0 >> 5) + 1], c0 & 31) & 7u;
-    const uint32_t f = fs_nms_pair(w0, w1, w2, e3);
-    if (f) atomicOr(s.kb + r * FS_KBP + (c0 >> 5), f << (c0 & 31));
+    const int r = (int)(tk >> 5), ql = (int)(tk & 31u);
+    const int c0 = 4 * (ql - 1);
+    const uint32_t* wp = s.amap + r * FS_APW + ql - 1;  // rows r, r+1, r+2 = zone rows r-1, r, r+1
+    uint32_t w[3][3];
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      w[j][0] = wp[j * FS_APW]; w[j][1] = wp[j * FS_APW + 1]; w[j][2] = wp[j * FS_APW + 2];
+    }
+    const uint32_t e5 = __funnelshift_r(ledge[c0 >> 5], ledge[(c0 >> 5) + 1], c0 & 31) & 31u;
+    const uint32_t f = fs_nms_quad(w, e5);
+    if (f) atomicOr(s.kb + r * FS_KBW + (c0 >> 5), f << (c0 & 31));
   }
   __syncwarp();
 }
 
-__global__ void __launch_bounds__(FS_THREADS, 7)
+__device__ __forceinline__ uint32_t fs_below(int c, int w) {  // bits of bitmap word w that lie below column c
+  const int n = c - 32 * w;
+  return n <= 0 ? 0u : (n >= 32 ? 0xffffffffu : ((1u << n) - 1u));
+}
+
+__global__ void __launch_bounds__(FS_THREADS, 14 / FS_WARPS)
 k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
              const uint32_t* __restrict__ strip_tab, int32_t* __restrict__ cell_cnt, uint32_t* __restrict__ cand,
-             int hmax, int region_words) {
+             int strip0, int strip1, int hmax, int region_words) {
   extern __shared__ __align__(16) uint32_t fs_smem[];
   const int frame = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int strip = blockIdx.x * FS_WARPS + warp;
-  if (strip >= P.total_strips) return;
-  const int amap_words = (FS_APW * (hmax + 2) + 3) & ~3, kb_words = (FS_KBP * hmax + 3) & ~3;
+  const int strip = strip0 + blockIdx.x * FS_WARPS + warp;
+  if (strip >= strip1) return;
   FsStrip s;
   s.tile = fs_smem + warp * region_words;
   s.amap = s.tile + FS_TPW * (hmax + 6);
-  s.kb = s.amap + amap_words;
-  s.pb = s.kb + kb_words;
-  s.list = reinterpret_cast<uint16_t*>(s.pb + 32 * FS_MAXB2);
-  s.misc = s.pb + 32 * FS_MAXB2 + FS_CAP / 2;
+  s.kb = s.amap + FS_APW * (hmax + 2);
+  s.rowpre = s.kb + FS_KBW * hmax;
+  s.misc = s.rowpre + ((hmax + 3) & ~3);
+  s.list = reinterpret_cast<uint16_t*>(s.misc + 12);
 
   // strip_tab: level << 24 | cell row << 12 | first cell column (built with the plan)
   const uint32_t stt = __ldg(strip_tab + strip);
@@ -235,27 +260,31 @@ k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __rest
   // clear the A map (rows 0..zh+1) and the keep bitmap while the copies are in flight
   {
     uint4* z = reinterpret_cast<uint4*>(s.amap);
-    const int nz = (FS_APW * (zh + 2) + 3) >> 2;
+    const int nz = (FS_APW * (zh + 2)) >> 2;
     for (int i = lane; i < nz; i += 32) z[i] = make_uint4(0, 0, 0, 0);
     uint4* zk = reinterpret_cast<uint4*>(s.kb);
-    const int nk = (FS_KBP * zh + 3) >> 2;
-    for (int i = lane; i < nk; i += 32) zk[i] = make_uint4(0, 0, 0, 0);
+    for (int i = lane; i < zh; i += 32) zk[i] = make_uint4(0, 0, 0, 0);
   }
   // zone columns / cell starts as bit masks over the strip's columns
   const int cx0 = X0 - xs, cx1 = X1 - xs;  // strip columns of the zone, cx1 <= 120
+  const int wc = L.wCell;
   if (lane < 4) {
-    const int lo = max(cx0 - 32 * lane, 0), hi = min(cx1 - 32 * lane, 32);
-    s.misc[lane] = hi > lo ? ((hi - lo == 32) ? 0xffffffffu : (((1u << (hi - lo)) - 1u) << lo)) : 0u;
+    s.misc[lane] = fs_below(cx1, lane) & ~fs_below(cx0, lane);
   } else if (lane < 9) {
     const int w = lane - 4;
     uint32_t m = 0;
     for (int j = 0; j <= k; j++) {
-      const int c = j < k ? cx0 + j * L.wCell : cx1;
+      const int c = j < k ? min(cx0 + j * wc, cx1) : cx1;
       if ((c >> 5) == w) m |= 1u << (c & 31);
     }
-    if ((cx1 >> 5) == w) m |= 1u << (cx1 & 31);
     s.misc[4 + w] = m;
   }
+  // cells: [cs1, cs2) is cell 1, [cs2, ..) cell 2; cells that start past the zone are empty in the reference (:819)
+  const int cs1 = k > 1 ? cx0 + wc : 128, cs2 = k > 2 ? cx0 + 2 * wc : 128;
+  uint32_t valid = 1u;
+  if (k > 1 && cs1 < cx1) valid |= 2u;
+  if (k > 2 && cs2 < cx1) valid |= 4u;
+  const int R = (zh + 31) >> 5;  // zone rows per lane in the emission scan
   if (al16) asm volatile("cp.async.wait_all;\n" ::: "memory");
   __syncwarp();
 
@@ -264,124 +293,92 @@ k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __rest
   uint32_t todo = (1u << k) - 1u;  // cells this attempt covers
 #pragma unroll 1
   for (int attempt = 0; attempt < 2; attempt++) {
-    // 2. quick test
+    // 2./3. quick test -> task list
     uint32_t zm = 0;
     if (lane >= 1 && lane <= 30) {
       const int c = 4 * (lane - 1);
       const uint32_t nib = (s.misc[c >> 5] >> (c & 31)) & 15u;
       zm = ((nib * 0x00204081u) & 0x01010101u) << 7;
     }
-    const uint32_t cadd = (uint32_t)(128 - ((th + 1) >> 1)) * 0x01010101u;
-    const int nblk = (zh + 6) / 7;
-    {
-      const uint32_t* trow = s.tile + s.wq0 + lane;
-      uint32_t C[7];
-#pragma unroll
-      for (int i = 0; i < 6; i++) C[i] = fs_halve(trow[i * FS_TPW]);
-      trow += 6 * FS_TPW;
-      uint16_t* pb16 = reinterpret_cast<uint16_t*>(s.pb + lane);
-#pragma unroll 1
-      for (int blk = 0; blk < nblk; blk++, trow += 7 * FS_TPW) {
-        uint32_t acc = 0;
-#pragma unroll
-        for (int ph = 0; ph < 7; ph++) {
-          C[(ph + 6) % 7] = fs_halve(trow[ph * FS_TPW]);
-          const uint32_t v = C[(ph + 3) % 7];
-          const uint32_t lw = __shfl_up_sync(0xffffffffu, v, 1), rw = __shfl_down_sync(0xffffffffu, v, 1);
-          const uint32_t l3 = __byte_perm(lw, v, 0x4321), r3 = __byte_perm(v, rw, 0x6543);
-#define QT(x) (__vabsdiffu4(v, (x)) + cadd)
-          uint32_t g = (QT(C[(ph + 6) % 7]) | QT(C[ph % 7])) & zm;  // ring 0 (0,+3) | ring 8 (0,-3)
-          g &= QT(r3) | QT(l3);                                     // ring 4 (+3,0) | ring 12 (-3,0)
-#undef QT
-          // bit 7 / 23 of t: a pixel of pair 0 / 1 passed -> bits 30 / 31
-          const uint32_t t = (g | (g >> 8)) & 0x00800080u;
-          acc = (acc >> 2) | ((t * 0x00800100u) & 0xC0000000u);
+    const int ntask = fs_quick(s, th, zm, lane);
+    // 4./5. arc strength, then NMS of the quads that hold a corner
+    const int nk = fs_score(s, ntask, th, lane);
+    fs_nms(s, nk, lane);
+    // 6a. corners kept per zone row and cell -> exclusive prefix over the rows (lanes own R consecutive rows)
+    uint32_t lsum = 0;
+    for (int rr = 0; rr < R; rr++) {
+      const int row = lane * R + rr;
+      if (row < zh) {
+        const uint4 kw = reinterpret_cast<const uint4*>(s.kb)[row];
+        uint32_t pk = 0;
+        if (kw.x | kw.y | kw.z | kw.w) {
+          const int t = __popc(kw.x) + __popc(kw.y) + __popc(kw.z) + __popc(kw.w);
+          const int b1 = __popc(kw.x & fs_below(cs1, 0)) + __popc(kw.y & fs_below(cs1, 1)) +
+                         __popc(kw.z & fs_below(cs1, 2)) + __popc(kw.w & fs_below(cs1, 3));
+          const int b2 = __popc(kw.x & fs_below(cs2, 0)) + __popc(kw.y & fs_below(cs2, 1)) +
+                         __popc(kw.z & fs_below(cs2, 2)) + __popc(kw.w & fs_below(cs2, 3));
+          pk = (uint32_t)b1 | ((uint32_t)(b2 - b1) << 11) | ((uint32_t)(t - b2) << 22);
         }
-        // rows 7blk..7blk+6 sit at bits 18..31: keep them as the low/high half of the lane's word blk/2
-        pb16[((blk >> 1) * 32) * 2 + (blk & 1)] = (uint16_t)(acc >> 16);
+        s.rowpre[row] = pk;
+        lsum += pk;
       }
     }
-    __syncwarp();
-    // 3. this lane's pass bits, rows past the zone masked off
-    uint32_t pw[FS_MAXB2];
-    int cnt = 0;
-#pragma unroll
-    for (int b = 0; b < FS_MAXB2; b++) {
-      const int nv = min(max(zh - 14 * b, 0), 14);
-      const int nlo = min(nv, 7), nhi = nv - nlo;
-      const uint32_t m = (((1u << (2 * nlo)) - 1u) << 2) | (((1u << (2 * nhi)) - 1u) << 18);
-      pw[b] = nv > 0 ? (s.pb[b * 32 + lane] & m) : 0u;
-      cnt += __popc(pw[b]);
-    }
-    int inc = cnt;
+    uint32_t inc = lsum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, inc, o);
+      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
       if (lane >= o) inc += t;
     }
-    const int total_tasks = __shfl_sync(0xffffffffu, inc, 31), off = inc - cnt;
-    // 4./5. score, then NMS
-    if (total_tasks <= FS_CAP) {
-      fs_fill(s, pw, off, 0, lane);
-      const int nk = fs_score<true>(s, total_tasks, th, lane);
-      fs_nms(s, nk, lane);
-    } else {
-      for (int cb = 0; cb < total_tasks; cb += FS_CAP) {
-        fs_fill(s, pw, off, cb, lane);
-        fs_score<false>(s, min(FS_CAP, total_tasks - cb), th, lane);
-      }
-      for (int cb = 0; cb < total_tasks; cb += FS_CAP) {
-        fs_fill(s, pw, off, cb, lane);
-        fs_nms(s, min(FS_CAP, total_tasks - cb), lane);
+    const uint32_t tot = __shfl_sync(0xffffffffu, inc, 31);
+    {
+      uint32_t run = inc - lsum;
+      for (int rr = 0; rr < R; rr++) {
+        const int row = lane * R + rr;
+        if (row < zh) {
+          const uint32_t t = s.rowpre[row];
+          s.rowpre[row] = run;
+          run += t;
+        }
       }
     }
-    // 6. per cell: ordered emission
     uint32_t redo = 0;
-    const uint8_t* ab = reinterpret_cast<const uint8_t*>(s.amap);
-#pragma unroll 1
-    for (int j = 0; j < k; j++) {
-      if (!((todo >> j) & 1u)) continue;
-      const int cs = cx0 + j * L.wCell, ce = min(cs + L.wCell, cx1);
-      int total = 0;
-      if (ce > cs) {
-        const int wlo = cs >> 5, whi = (ce - 1) >> 5;
-        const uint32_t mlo = 0xffffffffu << (cs & 31), mhi = 0xffffffffu >> (31 - ((ce - 1) & 31));
-        uint32_t* out = out0 + (long long)j * L.cell_cap;
-        for (int rb = 0; rb < zh; rb += 64) {
-          const int r0 = rb + 2 * lane;
-          int c0n = 0, c1n = 0;
-          for (int w = wlo; w <= whi; w++) {
-            const uint32_t m = (w == wlo ? mlo : 0xffffffffu) & (w == whi ? mhi : 0xffffffffu);
-            if (r0 < zh) c0n += __popc(s.kb[r0 * FS_KBP + w] & m);
-            if (r0 + 1 < zh) c1n += __popc(s.kb[(r0 + 1) * FS_KBP + w] & m);
-          }
-          int inc2 = c0n + c1n;
 #pragma unroll
-          for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc2, o);
-            if (lane >= o) inc2 += t;
-          }
-          int pos = total + inc2 - (c0n + c1n);
-          total += __shfl_sync(0xffffffffu, inc2, 31);
-          if (c0n + c1n) {
-            for (int rr = r0; rr < r0 + 2; rr++) {
-              if (rr >= zh) break;
-              for (int w = wlo; w <= whi; w++) {
-                uint32_t bits = s.kb[rr * FS_KBP + w] & (w == wlo ? mlo : 0xffffffffu) & (w == whi ? mhi : 0xffffffffu);
-                while (bits) {
-                  const int c = 32 * w + __ffs(bits) - 1;
-                  bits &= bits - 1;
-                  const int a = ab[(rr + 1) * FS_AP + 4 + c];
-                  // coordinates relative to (minBorderX,minBorderY)=(16,16), as DistributeOctTree sees them
-                  out[pos++] = orbx_pack_key(xs + c - ORBX_MIN_BORDER, Y0 + rr - ORBX_MIN_BORDER, a - 1);
-                }
-              }
-            }
-          }
-        }
-        if (total == 0) redo |= 1u << j;
+    for (int j = 0; j < 3; j++) {
+      const int tj = (int)((tot >> (11 * j)) & (j == 2 ? 0x3ffu : 0x7ffu));
+      if ((todo >> j) & 1u) {
+        if (lane == 0) cnt_out[j] = tj;
+        if (tj == 0) redo |= 1u << j;
       }
-      if (lane == 0) cnt_out[j] = total;
+    }
+    redo &= valid;
+    __syncwarp();
+    // 6b. ordered emission: position = corners of the cell in the rows above + those to the left in the row
+    if (tot) {
+      const uint8_t* ab = reinterpret_cast<const uint8_t*>(s.amap);
+      for (int e = lane; e < nk; e += 32) {
+        const uint32_t tk = s.list[e];
+        const int r = (int)(tk >> 5), ql = (int)(tk & 31u);
+        const int c0 = 4 * (ql - 1);
+        const uint4 kw = reinterpret_cast<const uint4*>(s.kb)[r];
+        const uint32_t kword = (c0 >> 5) == 0 ? kw.x : ((c0 >> 5) == 1 ? kw.y : ((c0 >> 5) == 2 ? kw.z : kw.w));
+        uint32_t f = (kword >> (c0 & 31)) & 15u;
+        if (!f) continue;
+        const uint32_t pre = s.rowpre[r];
+        while (f) {
+          const int i = __ffs(f) - 1;
+          f &= f - 1;
+          const int c = c0 + i;
+          const int j = (c >= cs1) + (c >= cs2);
+          if (!((todo >> j) & 1u)) continue;
+          const int csj = j == 0 ? 0 : (j == 1 ? cs1 : cs2);
+          const int inrow = __popc(kw.x & fs_below(c, 0) & ~fs_below(csj, 0)) + __popc(kw.y & fs_below(c, 1) & ~fs_below(csj, 1)) +
+                            __popc(kw.z & fs_below(c, 2) & ~fs_below(csj, 2)) + __popc(kw.w & fs_below(c, 3) & ~fs_below(csj, 3));
+          const int pos = (int)((pre >> (11 * j)) & (j == 2 ? 0x3ffu : 0x7ffu)) + inrow;
+          const int a = ab[(r + 1) * (FS_APW * 4) + 4 + c];
+          // coordinates relative to (minBorderX,minBorderY)=(16,16), as DistributeOctTree sees them
+          out0[(long long)j * L.cell_cap + pos] = orbx_pack_key(xs + c - ORBX_MIN_BORDER, Y0 + r - ORBX_MIN_BORDER, a - 1);
+        }
+      }
     }
     // 7. nothing at iniThFAST: the reference runs FAST again on the cell with minThFAST
     if (redo == 0 || th == P.min_th) break;
@@ -392,9 +389,8 @@ k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __rest
       uint32_t m = 0;
       for (int j = 0; j < k; j++) {
         if (!((redo >> j) & 1u)) continue;
-        const int cs = cx0 + j * L.wCell, ce = min(cs + L.wCell, cx1);
-        const int lo = max(cs - 32 * lane, 0), hi = min(ce - 32 * lane, 32);
-        if (hi > lo) m |= (hi - lo == 32) ? 0xffffffffu : (((1u << (hi - lo)) - 1u) << lo);
+        const int cs = cx0 + j * wc, ce = min(cs + wc, cx1);
+        m |= fs_below(ce, lane) & ~fs_below(cs, lane);
       }
       s.misc[lane] = m;
     }
@@ -403,22 +399,30 @@ k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __rest
 }
 
 static size_t fs_region_words(int hmax) {
-  const int amap_words = (FS_APW * (hmax + 2) + 3) & ~3, kb_words = (FS_KBP * hmax + 3) & ~3;
-  return (size_t)FS_TPW * (hmax + 6) + amap_words + kb_words + 32 * FS_MAXB2 + FS_CAP / 2 + 12;
+  const size_t w = (size_t)FS_TPW * (hmax + 6) + (size_t)FS_APW * (hmax + 2) + (size_t)FS_KBW * hmax + ((hmax + 3) & ~3) + 12 +
+                   (30 * (size_t)(hmax + 6) + 1) / 2;
+  return (w + 3) & ~(size_t)3;
 }
 
 cudaError_t orbx_launch_fast_strip(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* strip_tab,
                                    int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st) {
-  int hmax = 0;
-  for (int l = 0; l < P.nlevels; l++) hmax = max(hmax, P.lv[l].hCell);
-  if (hmax > 14 * FS_MAXB2) return cudaErrorInvalidValue;
-  const size_t region = (fs_region_words(hmax) + 3) & ~(size_t)3;
-  const size_t smem = FS_WARPS * region * sizeof(uint32_t);
-  cudaError_t e = orbx_ensure_dyn_smem(ORBX_SMEM_FAST_STRIP, (const void*)k_fast_strip, smem);
-  if (e != cudaSuccess) return e;
-  dim3 grd((P.total_strips + FS_WARPS - 1) / FS_WARPS, batch);
-  k_fast_strip<<<grd, FS_THREADS, smem, st>>>(P, l0, arena, strip_tab, cell_cnt, cand, hmax, (int)region);
-  return cudaGetLastError();
+  // two launches: the strips of the levels with ordinary cell heights, then those of the (small) levels whose
+  // few cell rows are tall — shared memory per warp follows the tallest zone of the launch
+  for (int g = 0; g < 2; g++) {
+    const int s0 = g == 0 ? 0 : P.strips_a, s1 = g == 0 ? P.strips_a : P.total_strips;
+    const int hmax = g == 0 ? P.hmax_a : P.hmax_b;
+    if (s1 <= s0) continue;
+    if (hmax > FS_MAXH) return cudaErrorInvalidValue;
+    const size_t region = fs_region_words(hmax);
+    const size_t smem = FS_WARPS * region * sizeof(uint32_t);
+    cudaError_t e = orbx_ensure_dyn_smem(ORBX_SMEM_FAST_STRIP, (const void*)k_fast_strip, smem);
+    if (e != cudaSuccess) return e;
+    dim3 grd((s1 - s0 + FS_WARPS - 1) / FS_WARPS, batch);
+    k_fast_strip<<<grd, FS_THREADS, smem, st>>>(P, l0, arena, strip_tab, cell_cnt, cand, s0, s1, hmax, (int)region);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* cell_tab,

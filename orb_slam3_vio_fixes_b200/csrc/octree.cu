@@ -305,15 +305,16 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
 cudaError_t orbx_ensure_dyn_smem(OrbxSmemSlot slot, const void* func, size_t bytes) {
   static std::mutex mu;
   static int have[64][ORBX_SMEM_SLOTS];  // zero-initialised; 48 KB needs no opt-in
-  if (bytes <= 48 * 1024 && slot != ORBX_SMEM_FAST && slot != ORBX_SMEM_FAST4) return cudaSuccess;
+  const bool fast = slot == ORBX_SMEM_FAST || slot == ORBX_SMEM_FAST4 || slot == ORBX_SMEM_FAST_STRIP;
+  if (bytes <= 48 * 1024 && !fast) return cudaSuccess;
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   std::lock_guard<std::mutex> lk(mu);
   if (dev < 0 || dev >= 64) return cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
   if ((int)bytes <= have[dev][slot]) return cudaSuccess;
-  // k_fast is limited by shared memory per SM (8 CTAs x ~26 KB): ask for the largest carveout
-  if (slot == ORBX_SMEM_FAST || slot == ORBX_SMEM_FAST4)
+  // the FAST kernels are limited by shared memory per SM: ask for the largest carveout
+  if (fast)
     cudaFuncSetAttribute(func, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
   if (e == cudaSuccess) have[dev][slot] = (int)bytes;

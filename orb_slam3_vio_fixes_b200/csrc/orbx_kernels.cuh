@@ -23,7 +23,7 @@ struct DevLevel {
 
 struct DevPlan {
   DevLevel lv[ORBX_PLAN_MAX_LEVELS];
-  int nlevels, total_cells, kp_total_cap, ini_th, min_th, total_btiles, total_strips;
+  int nlevels, total_cells, kp_total_cap, ini_th, min_th, total_btiles, total_strips, strips_a, hmax_a, hmax_b;
   long long cand_total;   // uint32 per frame
   long long arena_bytes;  // per frame
   int umax[16];

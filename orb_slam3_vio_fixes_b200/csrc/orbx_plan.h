@@ -50,6 +50,7 @@ struct OrbxPlan {
   int kp_total_cap;          // Σ kp_cap
   int total_btiles;          // Σ blur tiles per frame
   int total_strips;          // Σ FAST strips per frame
+  int strips_a, hmax_a, hmax_b;  // strips [0, strips_a): levels with ordinary cell heights (<= hmax_a), the rest: tall cells (<= hmax_b)
   int max_keypoints;         // Σ kp_max (what one frame can return; nfeatures+3*nlevels normally)
   float scale[ORBX_PLAN_MAX_LEVELS], inv_scale[ORBX_PLAN_MAX_LEVELS];
   float sigma2[ORBX_PLAN_MAX_LEVELS], inv_sigma2[ORBX_PLAN_MAX_LEVELS];
@@ -141,8 +142,6 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
     if (L.strip_k < 1) return -1;
     if (L.strip_k > L.nCols) L.strip_k = L.nCols;
     L.strips_per_row = (L.nCols + L.strip_k - 1) / L.strip_k;
-    L.strip_base = strips;
-    strips += L.strips_per_row * L.nRows;
     L.cell_cap = ((L.wCell + 1) / 2) * ((L.hCell + 1) / 2);
     L.cand_base = cand;
     L.cand_cap = (long long)L.nCols * L.nRows * L.cell_cap;
@@ -215,6 +214,20 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
   P->arena_bytes = (offset + 255) & ~255LL;
   P->kp_total_cap = kpb;
   P->total_btiles = btiles;
+  // strip order: the levels whose cells are about as tall as level 0's first, then the levels with tall cells
+  // (the small levels with few cell rows) — k_fast_strip sizes a warp's shared memory by the tallest zone of a launch
+  P->hmax_a = P->hmax_b = 0;
+  for (int g = 0; g < 2; g++) {
+    for (int l = 0; l < nlevels; l++) {
+      OrbxLevel& L = P->lv[l];
+      if ((L.hCell <= P->lv[0].hCell + 2) != (g == 0)) continue;
+      L.strip_base = strips;
+      strips += L.strips_per_row * L.nRows;
+      if (g == 0) { if (L.hCell > P->hmax_a) P->hmax_a = L.hCell; }
+      else if (L.hCell > P->hmax_b) P->hmax_b = L.hCell;
+    }
+    if (g == 0) P->strips_a = strips;
+  }
   P->total_strips = strips;
   P->max_keypoints = maxk;
   return 0;
