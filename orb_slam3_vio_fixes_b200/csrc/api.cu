@@ -36,6 +36,7 @@ struct orbx_extractor_s {
   OrbxTap *xtaps = nullptr, *ytaps = nullptr;
   int32_t* cell_cnt = nullptr;
   uint32_t* cell_tab = nullptr;  // per cell: level << 24 | row << 12 | column
+  OrbxFastMaps fast_maps;         // tensor maps of arena levels 1.. for k_fast_strip (level 0 is encoded per call)
   uint32_t* strip_tab = nullptr;  // per FAST strip: level << 24 | cell row << 12 | first cell column
   uint32_t* cand = nullptr;
   uint32_t* gkeys = nullptr;
@@ -272,6 +273,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   }
   CUH(cudaMemset(h->status, 0, sizeof(int32_t)));
   CUH(cudaMemset(h->arena, 0, B * P.arena_bytes + 512));
+  orbx_fast_maps_init(h->dplan, h->arena, cfg->max_batch, &h->fast_maps);
   CUH(orbx_describe_init_tables(P.umax));
   if (cfg->flags & ORBX_FLAG_STAGE_TIMING)
     for (int i = 0; i <= ORBX_NUM_STAGES; i++) CUH(cudaEventCreate(&h->ev[i]));
@@ -326,7 +328,7 @@ static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1,
   STAGE_MARK(0);
   CU(orbx_launch_pyramid(D, l0, arena, h->xtaps, h->ytaps, batch, st));
   STAGE_MARK(1);
-  CU(orbx_launch_fast(D, l0, arena, h->cell_tab, h->strip_tab, cell_cnt, cand, batch, st));
+  CU(orbx_launch_fast(D, h->fast_maps, l0, arena, h->cell_tab, h->strip_tab, cell_cnt, cand, batch, f0, st));
   STAGE_MARK(2);
   CU(orbx_launch_octree(D, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, h->status, batch,
                         h->oct_smem, h->oct_smem_keys, h->oct_node_cap, h->oct_max_cells, st));

@@ -24,6 +24,7 @@
 //   6. per cell: lanes own rows, count their bits, one warp scan, ordered (row-major) emission into the cell's
 //      slot array — the order the reference's per-cell cv::FAST returns;
 //   7. cells that stayed empty are redone from step 2 at minThFAST with the zone restricted to their columns.
+#include <cuda.h>
 #include <stdlib.h>
 
 #include "fast_arc.cuh"
@@ -36,24 +37,17 @@
 #define FS_TP 144            // tile row pitch in bytes: 9 vectors of 16 B cover lane words 0..31 at word offset <= 3
 #define FS_TPW (FS_TP / 4)   // 36 words
 #define FS_APW 32            // A-map row pitch in words: word 0 = pad, words 1..30 = strip columns 0..119, word 31 = pad
-#define FS_KBW 4             // keep-bitmap words per row (120 columns)
-#define FS_MAXH 96           // tallest zone: three rows per lane in the emission scan
+#define FS_MAXH 120          // tallest zone (list codes hold 7 bits of row: rows + 6 < 128)
 
 __device__ __forceinline__ uint32_t fs_halve(uint32_t v) { return (v >> 1) & 0x7f7f7f7fu; }
-
-__device__ __forceinline__ void fs_cp_async16(uint32_t saddr, const void* g, uint32_t nbytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(saddr), "l"(g), "r"(nbytes) : "memory");
-}
 
 // Shared memory of one warp (32-bit words):
 //   tile[FS_TPW * (hmax+6)]   staged pixels: tile row r = level row Y0-3+r, tile byte b = level column xt+b
 //   amap[FS_APW * (hmax+2)]   arc strengths: row r+1 = zone row r, byte 4+c = strip column c (level column xs+c)
-//   kb[FS_KBW * hmax]         keep bitmap: bit c of row r
-//   rowpre[hmax]              per zone row: corners kept in the rows above, per cell (11 | 11 | 10 bits)
 //   list[30 * (hmax+6)] u16   quad tasks, row-major: row << 5 | lane
 //   misc[12]                  zbits[4] (zone columns), ledge[5] (columns where a cell starts / the zone ends)
 struct FsStrip {
-  uint32_t *tile, *amap, *kb, *rowpre, *misc;
+  uint32_t *tile, *amap, *misc;
   uint16_t* list;
   int wq0;  // tile word of lane 0
   int zh;
@@ -72,12 +66,14 @@ __device__ __forceinline__ int fs_quick(const FsStrip& s, int th, uint32_t zm, i
 #pragma unroll
   for (int i = 0; i < 6; i++) C[i] = fs_halve(trow[i * FS_TPW]);
   trow += 6 * FS_TPW;
-  int base = 0, nv = 0;
+  int base = 0;
   uint32_t code = (uint32_t)lane;
+  int rows_left = zh;
 #pragma unroll 1
-  for (int blk = 0; blk < nblk; blk++, trow += 7 * FS_TPW) {
+  for (int blk = 0; blk < nblk; blk++, trow += 7 * FS_TPW, rows_left -= 7) {
 #pragma unroll
     for (int ph = 0; ph < 7; ph++) {
+      if (ph >= rows_left) break;  // warp-uniform: the last block of rows may be short
       C[(ph + 6) % 7] = fs_halve(trow[ph * FS_TPW]);
       const uint32_t v = C[(ph + 3) % 7];
       const uint32_t lw = __shfl_up_sync(0xffffffffu, v, 1), rw = __shfl_down_sync(0xffffffffu, v, 1);
@@ -90,12 +86,11 @@ __device__ __forceinline__ int fs_quick(const FsStrip& s, int th, uint32_t zm, i
       const unsigned bal = __ballot_sync(0xffffffffu, pass);
       if (pass) s.list[base + __popc(bal & ltm)] = (uint16_t)(code + 32u * ph);
       base += __popc(bal);
-      if (7 * blk + ph < zh) nv = base;
     }
     code += 7u * 32u;
   }
   __syncwarp();
-  return nv;
+  return base;
 }
 
 // Arc strength of the n listed quads into the A map (0 where A <= th or outside the zone); the quads that
@@ -168,36 +163,16 @@ __device__ __forceinline__ uint32_t fs_nms_quad(const uint32_t (&w)[3][3], uint3
   return ((k02 >> 8) & 1u) | ((k13 >> 7) & 2u) | ((k02 >> 22) & 4u) | ((k13 >> 21) & 8u);
 }
 
-// NMS of the n listed quads (all hold a corner) into the keep bitmap.
-__device__ __forceinline__ void fs_nms(const FsStrip& s, int n, int lane) {
-  const uint32_t* ledge = s.misc + 4;
-  for (int e = lane; e < n; e += 32) {
-    const uint32_t tk = s.list[e];
-    const int r = (int)(tk >> 5), ql = (int)(tk & 31u);
-    const int c0 = 4 * (ql - 1);
-    const uint32_t* wp = s.amap + r * FS_APW + ql - 1;  // rows r, r+1, r+2 = zone rows r-1, r, r+1
-    uint32_t w[3][3];
-#pragma unroll
-    for (int j = 0; j < 3; j++) {
-      w[j][0] = wp[j * FS_APW]; w[j][1] = wp[j * FS_APW + 1]; w[j][2] = wp[j * FS_APW + 2];
-    }
-    const uint32_t e5 = __funnelshift_r(ledge[c0 >> 5], ledge[(c0 >> 5) + 1], c0 & 31) & 31u;
-    const uint32_t f = fs_nms_quad(w, e5);
-    if (f) atomicOr(s.kb + r * FS_KBW + (c0 >> 5), f << (c0 & 31));
-  }
-  __syncwarp();
-}
-
 __device__ __forceinline__ uint32_t fs_below(int c, int w) {  // bits of bitmap word w that lie below column c
   const int n = c - 32 * w;
   return n <= 0 ? 0u : (n >= 32 ? 0xffffffffu : ((1u << n) - 1u));
 }
 
 __global__ void __launch_bounds__(FS_THREADS, 14 / FS_WARPS)
-k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
-             const uint32_t* __restrict__ strip_tab, int32_t* __restrict__ cell_cnt, uint32_t* __restrict__ cand,
-             int strip0, int strip1, int hmax, int region_words) {
-  extern __shared__ __align__(16) uint32_t fs_smem[];
+k_fast_strip(const __grid_constant__ DevPlan P, const __grid_constant__ OrbxFastMaps M, Level0 l0,
+             const uint8_t* __restrict__ arena, const uint32_t* __restrict__ strip_tab, int32_t* __restrict__ cell_cnt,
+             uint32_t* __restrict__ cand, int strip0, int strip1, int hmax, int region_words, int f0) {
+  extern __shared__ __align__(128) uint32_t fs_smem[];
   const int frame = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int strip = strip0 + blockIdx.x * FS_WARPS + warp;
@@ -205,10 +180,8 @@ k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __rest
   FsStrip s;
   s.tile = fs_smem + warp * region_words;
   s.amap = s.tile + FS_TPW * (hmax + 6);
-  s.kb = s.amap + FS_APW * (hmax + 2);
-  s.rowpre = s.kb + FS_KBW * hmax;
-  s.misc = s.rowpre + ((hmax + 3) & ~3);
-  s.list = reinterpret_cast<uint16_t*>(s.misc + 12);
+  s.misc = s.amap + FS_APW * (hmax + 2);
+  s.list = reinterpret_cast<uint16_t*>(s.misc + 12);  // misc[10..11] = the warp's mbarrier (8-byte aligned)
 
   // strip_tab: level << 24 | cell row << 12 | first cell column (built with the plan)
   const uint32_t stt = __ldg(strip_tab + strip);
@@ -235,17 +208,22 @@ k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __rest
   s.wq0 = (xs - 4 - xt) >> 2;
   const int trows = zh + 6;
   const uint8_t* src0 = img + (long long)(Y0 - 3) * pitch + xt;
-  const bool al16 = ((reinterpret_cast<uintptr_t>(img) | (uintptr_t)(unsigned)pitch) & 15u) == 0;
-  if (al16) {
-    const int v = lane % 9, ro = lane / 9;
-    if (ro < 3) {
-      const bool inb = xt + 16 * v + 16 <= pitch;  // columns past the row's allocation are never needed: zero-fill
-      const uint8_t* g = src0 + (inb ? 16 * v : 0) + (long long)ro * pitch;
-      uint32_t sa = (uint32_t)__cvta_generic_to_shared(s.tile) + ro * FS_TP + 16 * v;
-      const uint32_t nb = inb ? 16u : 0u;
-      for (int r = ro; r < trows; r += 3, g += 3LL * pitch, sa += 3 * FS_TP) fs_cp_async16(sa, g, nb);
+  // One 2-D box of the level's tensor map (144 columns x hCell+6 rows of frame f0+frame), fetched by the TMA
+  // engine on behalf of the warp; columns / rows outside the level read as zeros (never used).  Levels whose
+  // base or pitch is not 16-byte aligned (a caller's odd-width level 0) are staged with plain loads.
+  const bool tma = (M.mask >> level) & 1u;
+  const uint32_t bar_a = (uint32_t)__cvta_generic_to_shared(s.misc + 10);
+  if (tma) {
+    if (lane == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(FS_TP * (L.hCell + 6)) : "memory");
+      asm volatile(
+          "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+          ::"r"((uint32_t)__cvta_generic_to_shared(s.tile)), "l"(reinterpret_cast<const void*>(&M.m[level])), "r"(xt),
+          "r"(Y0 - 3), "r"(f0 + frame), "r"(bar_a)
+          : "memory");
     }
-    asm volatile("cp.async.commit_group;\n" ::: "memory");
   } else {
     for (int i = lane; i < trows * FS_TPW; i += 32) {
       const int r = i / FS_TPW, wq = i - r * FS_TPW, col = xt + 4 * wq;
@@ -257,13 +235,11 @@ k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __rest
       s.tile[i] = v;
     }
   }
-  // clear the A map (rows 0..zh+1) and the keep bitmap while the copies are in flight
+  // clear the A map (rows 0..zh+1) while the copies are in flight
   {
     uint4* z = reinterpret_cast<uint4*>(s.amap);
     const int nz = (FS_APW * (zh + 2)) >> 2;
     for (int i = lane; i < nz; i += 32) z[i] = make_uint4(0, 0, 0, 0);
-    uint4* zk = reinterpret_cast<uint4*>(s.kb);
-    for (int i = lane; i < zh; i += 32) zk[i] = make_uint4(0, 0, 0, 0);
   }
   // zone columns / cell starts as bit masks over the strip's columns
   const int cx0 = X0 - xs, cx1 = X1 - xs;  // strip columns of the zone, cx1 <= 120
@@ -284,8 +260,12 @@ k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __rest
   uint32_t valid = 1u;
   if (k > 1 && cs1 < cx1) valid |= 2u;
   if (k > 2 && cs2 < cx1) valid |= 4u;
-  const int R = (zh + 31) >> 5;  // zone rows per lane in the emission scan
-  if (al16) asm volatile("cp.async.wait_all;\n" ::: "memory");
+  if (tma) {
+    uint32_t done = 0;
+    while (!done)
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                   : "=r"(done) : "r"(bar_a) : "memory");
+  }
   __syncwarp();
 
   uint32_t* out0 = cand + (long long)frame * P.cand_total + L.cand_base + (long long)(ci * L.nCols + cj0) * L.cell_cap;
@@ -301,85 +281,68 @@ k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __rest
       zm = ((nib * 0x00204081u) & 0x01010101u) << 7;
     }
     const int ntask = fs_quick(s, th, zm, lane);
-    // 4./5. arc strength, then NMS of the quads that hold a corner
+    // 4. arc strength; the quads that hold a corner stay listed (row-major)
     const int nk = fs_score(s, ntask, th, lane);
-    fs_nms(s, nk, lane);
-    // 6a. corners kept per zone row and cell -> exclusive prefix over the rows (lanes own R consecutive rows)
-    uint32_t lsum = 0;
-    for (int rr = 0; rr < R; rr++) {
-      const int row = lane * R + rr;
-      if (row < zh) {
-        const uint4 kw = reinterpret_cast<const uint4*>(s.kb)[row];
-        uint32_t pk = 0;
-        if (kw.x | kw.y | kw.z | kw.w) {
-          const int t = __popc(kw.x) + __popc(kw.y) + __popc(kw.z) + __popc(kw.w);
-          const int b1 = __popc(kw.x & fs_below(cs1, 0)) + __popc(kw.y & fs_below(cs1, 1)) +
-                         __popc(kw.z & fs_below(cs1, 2)) + __popc(kw.w & fs_below(cs1, 3));
-          const int b2 = __popc(kw.x & fs_below(cs2, 0)) + __popc(kw.y & fs_below(cs2, 1)) +
-                         __popc(kw.z & fs_below(cs2, 2)) + __popc(kw.w & fs_below(cs2, 3));
-          pk = (uint32_t)b1 | ((uint32_t)(b2 - b1) << 11) | ((uint32_t)(t - b2) << 22);
-        }
-        s.rowpre[row] = pk;
-        lsum += pk;
-      }
-    }
-    uint32_t inc = lsum;
+    // 5./6. NMS and ordered emission in one sweep over the kept quads, 32 at a time: the position of a corner in
+    // its cell's slot array is the number of corners the cell kept before it in row-major order, i.e. a running
+    // per-cell count (11 | 11 | 10 bits) + a warp prefix over the batch + its rank inside the quad
+    uint32_t run = 0;
+    const uint32_t* ledge = s.misc + 4;
+    const uint8_t* ab = reinterpret_cast<const uint8_t*>(s.amap);
+    for (int base = 0; base < nk; base += 32) {
+      const int e = base + lane;
+      uint32_t f = 0;
+      int r = 0, c0 = 0;
+      if (e < nk) {
+        const uint32_t tk = s.list[e];
+        r = (int)(tk >> 5);
+        const int ql = (int)(tk & 31u);
+        c0 = 4 * (ql - 1);
+        const uint32_t* wp = s.amap + r * FS_APW + ql - 1;  // rows r, r+1, r+2 = zone rows r-1, r, r+1
+        uint32_t w[3][3];
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += t;
-    }
-    const uint32_t tot = __shfl_sync(0xffffffffu, inc, 31);
-    {
-      uint32_t run = inc - lsum;
-      for (int rr = 0; rr < R; rr++) {
-        const int row = lane * R + rr;
-        if (row < zh) {
-          const uint32_t t = s.rowpre[row];
-          s.rowpre[row] = run;
-          run += t;
+        for (int j = 0; j < 3; j++) {
+          w[j][0] = wp[j * FS_APW]; w[j][1] = wp[j * FS_APW + 1]; w[j][2] = wp[j * FS_APW + 2];
         }
+        const uint32_t e5 = __funnelshift_r(ledge[c0 >> 5], ledge[(c0 >> 5) + 1], c0 & 31) & 31u;
+        f = fs_nms_quad(w, e5);
+      }
+      // the quad's pixels by cell: columns below cs1 are cell 0, below cs2 cell 1, the rest cell 2
+      const uint32_t m1 = (1u << min(max(cs1 - c0, 0), 4)) - 1u, m2 = (1u << min(max(cs2 - c0, 0), 4)) - 1u;
+      const uint32_t f0 = f & m1, f1 = f & m2 & ~m1, f2 = f & ~m2;
+      const uint32_t pk = (uint32_t)__popc(f0) | ((uint32_t)__popc(f1) << 11) | ((uint32_t)__popc(f2) << 22);
+      uint32_t inc = pk;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+      }
+      const uint32_t exc = run + inc - pk;
+      run += __shfl_sync(0xffffffffu, inc, 31);
+      while (f) {
+        const int i = __ffs(f) - 1;
+        const uint32_t below = (1u << i) - 1u;
+        f &= f - 1;
+        const int j = (int)(((m1 >> i) & 1u) ^ 1u) + (int)(((m2 >> i) & 1u) ^ 1u);
+        if (!((todo >> j) & 1u)) continue;
+        const uint32_t fj = j == 0 ? f0 : (j == 1 ? f1 : f2);
+        const int pos = (int)((exc >> (11 * j)) & (j == 2 ? 0x3ffu : 0x7ffu)) + __popc(fj & below);
+        const int c = c0 + i;
+        const int a = ab[(r + 1) * (FS_APW * 4) + 4 + c];
+        // coordinates relative to (minBorderX,minBorderY)=(16,16), as DistributeOctTree sees them
+        out0[(long long)j * L.cell_cap + pos] = orbx_pack_key(xs + c - ORBX_MIN_BORDER, Y0 + r - ORBX_MIN_BORDER, a - 1);
       }
     }
     uint32_t redo = 0;
 #pragma unroll
     for (int j = 0; j < 3; j++) {
-      const int tj = (int)((tot >> (11 * j)) & (j == 2 ? 0x3ffu : 0x7ffu));
+      const int tj = (int)((run >> (11 * j)) & (j == 2 ? 0x3ffu : 0x7ffu));
       if ((todo >> j) & 1u) {
         if (lane == 0) cnt_out[j] = tj;
         if (tj == 0) redo |= 1u << j;
       }
     }
     redo &= valid;
-    __syncwarp();
-    // 6b. ordered emission: position = corners of the cell in the rows above + those to the left in the row
-    if (tot) {
-      const uint8_t* ab = reinterpret_cast<const uint8_t*>(s.amap);
-      for (int e = lane; e < nk; e += 32) {
-        const uint32_t tk = s.list[e];
-        const int r = (int)(tk >> 5), ql = (int)(tk & 31u);
-        const int c0 = 4 * (ql - 1);
-        const uint4 kw = reinterpret_cast<const uint4*>(s.kb)[r];
-        const uint32_t kword = (c0 >> 5) == 0 ? kw.x : ((c0 >> 5) == 1 ? kw.y : ((c0 >> 5) == 2 ? kw.z : kw.w));
-        uint32_t f = (kword >> (c0 & 31)) & 15u;
-        if (!f) continue;
-        const uint32_t pre = s.rowpre[r];
-        while (f) {
-          const int i = __ffs(f) - 1;
-          f &= f - 1;
-          const int c = c0 + i;
-          const int j = (c >= cs1) + (c >= cs2);
-          if (!((todo >> j) & 1u)) continue;
-          const int csj = j == 0 ? 0 : (j == 1 ? cs1 : cs2);
-          const int inrow = __popc(kw.x & fs_below(c, 0) & ~fs_below(csj, 0)) + __popc(kw.y & fs_below(c, 1) & ~fs_below(csj, 1)) +
-                            __popc(kw.z & fs_below(c, 2) & ~fs_below(csj, 2)) + __popc(kw.w & fs_below(c, 3) & ~fs_below(csj, 3));
-          const int pos = (int)((pre >> (11 * j)) & (j == 2 ? 0x3ffu : 0x7ffu)) + inrow;
-          const int a = ab[(r + 1) * (FS_APW * 4) + 4 + c];
-          // coordinates relative to (minBorderX,minBorderY)=(16,16), as DistributeOctTree sees them
-          out0[(long long)j * L.cell_cap + pos] = orbx_pack_key(xs + c - ORBX_MIN_BORDER, Y0 + r - ORBX_MIN_BORDER, a - 1);
-        }
-      }
-    }
     // 7. nothing at iniThFAST: the reference runs FAST again on the cell with minThFAST
     if (redo == 0 || th == P.min_th) break;
     th = P.min_th;
@@ -399,13 +362,59 @@ k_fast_strip(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __rest
 }
 
 static size_t fs_region_words(int hmax) {
-  const size_t w = (size_t)FS_TPW * (hmax + 6) + (size_t)FS_APW * (hmax + 2) + (size_t)FS_KBW * hmax + ((hmax + 3) & ~3) + 12 +
-                   (30 * (size_t)(hmax + 6) + 1) / 2;
-  return (w + 3) & ~(size_t)3;
+  const size_t w = (size_t)FS_TPW * (hmax + 6) + (size_t)FS_APW * (hmax + 2) + 12 + (30 * (size_t)(hmax + 6) + 1) / 2;
+  return (w + 31) & ~(size_t)31;  // the TMA destination (the tile, first in the region) is 128-byte aligned
 }
 
-cudaError_t orbx_launch_fast_strip(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* strip_tab,
-                                   int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st) {
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*FsEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static FsEncodeFn fs_encode_fn() {
+  static FsEncodeFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (FsEncodeFn)p;
+  }();
+  return fn;
+}
+
+// Tensor map of one level: bytes [w] x rows [h] x frames [n], box = FS_TP columns x box_rows rows x 1 frame.
+static bool fs_encode_level(CUtensorMap* m, const uint8_t* base, int w, int h, long long nframes, long long pitch,
+                            long long frame_stride, int box_rows) {
+  FsEncodeFn enc = fs_encode_fn();
+  if (!enc || box_rows > 256) return false;
+  if ((reinterpret_cast<uintptr_t>(base) & 15u) || (pitch & 15) || (frame_stride & 15) || nframes < 1) return false;
+  const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)nframes};
+  const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frame_stride};
+  const cuuint32_t box[3] = {FS_TP, (cuuint32_t)box_rows, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(base), dims, strides, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+void orbx_fast_maps_init(const DevPlan& P, const uint8_t* arena, int max_batch, OrbxFastMaps* M) {
+  memset(M, 0, sizeof(*M));
+  for (int l = 1; l < P.nlevels; l++) {
+    const DevLevel& L = P.lv[l];
+    if (fs_encode_level(reinterpret_cast<CUtensorMap*>(&M->m[l]), arena + L.offset, L.w, L.h, max_batch, L.pitch, P.arena_bytes, L.hCell + 6)) M->mask |= 1u << l;
+  }
+}
+
+cudaError_t orbx_launch_fast_strip(const DevPlan& P, const OrbxFastMaps& maps, Level0 l0, const uint8_t* arena,
+                                   const uint32_t* strip_tab, int32_t* cell_cnt, uint32_t* cand, int batch, int f0,
+                                   cudaStream_t st) {
+  // level 0 is the caller's buffer: its map is encoded per call (frame 0 of the map = l0.base)
+  OrbxFastMaps M = maps;
+  M.mask &= ~1u;
+  static const bool no_tma = [] { const char* e = getenv("ORBX_FAST_TMA"); return e && e[0] == '0'; }();
+  if (no_tma) M.mask = 0;
+  else if (fs_encode_level(reinterpret_cast<CUtensorMap*>(&M.m[0]), l0.base - (long long)f0 * l0.frame_stride, P.lv[0].w, P.lv[0].h, (long long)f0 + batch, l0.pitch,
+                           l0.frame_stride ? l0.frame_stride : 16, P.lv[0].hCell + 6))
+    M.mask |= 1u;
   // two launches: the strips of the levels with ordinary cell heights, then those of the (small) levels whose
   // few cell rows are tall — shared memory per warp follows the tallest zone of the launch
   for (int g = 0; g < 2; g++) {
@@ -418,17 +427,18 @@ cudaError_t orbx_launch_fast_strip(const DevPlan& P, Level0 l0, const uint8_t* a
     cudaError_t e = orbx_ensure_dyn_smem(ORBX_SMEM_FAST_STRIP, (const void*)k_fast_strip, smem);
     if (e != cudaSuccess) return e;
     dim3 grd((s1 - s0 + FS_WARPS - 1) / FS_WARPS, batch);
-    k_fast_strip<<<grd, FS_THREADS, smem, st>>>(P, l0, arena, strip_tab, cell_cnt, cand, s0, s1, hmax, (int)region);
+    k_fast_strip<<<grd, FS_THREADS, smem, st>>>(P, M, l0, arena, strip_tab, cell_cnt, cand, s0, s1, hmax, (int)region, f0);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
 }
 
-cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* cell_tab,
-                             const uint32_t* strip_tab, int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st) {
+cudaError_t orbx_launch_fast(const DevPlan& P, const OrbxFastMaps& maps, Level0 l0, const uint8_t* arena,
+                             const uint32_t* cell_tab, const uint32_t* strip_tab, int32_t* cell_cnt, uint32_t* cand,
+                             int batch, int f0, cudaStream_t st) {
   // ORBX_FAST_IMPL=cell selects the first-generation cell-per-warp kernel (A/B measurements)
   static const bool cell = [] { const char* e = getenv("ORBX_FAST_IMPL"); return e && e[0] == 'c'; }();
   if (cell) return orbx_launch_fast_cell(P, l0, arena, cell_tab, cell_cnt, cand, batch, st);
-  return orbx_launch_fast_strip(P, l0, arena, strip_tab, cell_cnt, cand, batch, st);
+  return orbx_launch_fast_strip(P, maps, l0, arena, strip_tab, cell_cnt, cand, batch, f0, st);
 }

@@ -38,11 +38,13 @@ __device__ __forceinline__ uint32_t arc_pair(const uint32_t (&rw)[7][3]) {
   //   bright-centre strength = v - min_k max9[k],  dark-centre strength = max_k min9[k] - v
   uint32_t lo = 0xffffffffu, hi = 0;
 #pragma unroll
-  for (int k = 0; k < 16; k++) {
-    const uint32_t mx9 = __vimax3_u16x2(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]);
-    const uint32_t mn9 = __vimin3_u16x2(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
-    lo = __vminu2(lo, mx9);
-    hi = __vmaxu2(hi, mn9);
+  for (int k = 0; k < 16; k += 2) {
+    const uint32_t mx9a = __vimax3_u16x2(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]);
+    const uint32_t mx9b = __vimax3_u16x2(mx3[k + 1], mx3[(k + 4) & 15], mx3[(k + 7) & 15]);
+    const uint32_t mn9a = __vimin3_u16x2(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
+    const uint32_t mn9b = __vimin3_u16x2(mn3[k + 1], mn3[(k + 4) & 15], mn3[(k + 7) & 15]);
+    lo = __vimin3_u16x2(lo, mx9a, mx9b);
+    hi = __vimax3_u16x2(hi, mn9a, mn9b);
   }
   const int v0 = (int)(vv & 0xffffu), v1 = (int)(vv >> 16);
   const int a0 = max(max(v0 - (int)(lo & 0xffffu), (int)(hi & 0xffffu) - v0), 0);

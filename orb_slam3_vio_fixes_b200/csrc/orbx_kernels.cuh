@@ -63,12 +63,22 @@ struct OrbxStereoPyr {
 // --- launches (each returns cudaGetLastError()) -------------------------------------------------
 cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, const OrbxTap* xtaps,
                                 const OrbxTap* ytaps, int batch, cudaStream_t st);
-cudaError_t orbx_launch_fast(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* cell_tab,
-                             const uint32_t* strip_tab, int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st);
+// Tensor maps of the pyramid levels for k_fast_strip's TMA staging: one CUtensorMap (128 bytes, 64-byte aligned)
+// per level over (columns, rows, frames); mask bit l = level l has a map.  Kept opaque here so that only fast.cu
+// needs <cuda.h>.
+struct alignas(64) OrbxFastMaps {
+  unsigned long long m[ORBX_PLAN_MAX_LEVELS][16];
+  unsigned mask;
+};
+void orbx_fast_maps_init(const DevPlan& P, const uint8_t* arena, int max_batch, OrbxFastMaps* M);
+cudaError_t orbx_launch_fast(const DevPlan& P, const OrbxFastMaps& maps, Level0 l0, const uint8_t* arena,
+                             const uint32_t* cell_tab, const uint32_t* strip_tab, int32_t* cell_cnt, uint32_t* cand,
+                             int batch, int f0, cudaStream_t st);
 cudaError_t orbx_launch_fast_cell(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* cell_tab,
                                   int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st);
-cudaError_t orbx_launch_fast_strip(const DevPlan& P, Level0 l0, const uint8_t* arena, const uint32_t* strip_tab,
-                                   int32_t* cell_cnt, uint32_t* cand, int batch, cudaStream_t st);
+cudaError_t orbx_launch_fast_strip(const DevPlan& P, const OrbxFastMaps& maps, Level0 l0, const uint8_t* arena,
+                                   const uint32_t* strip_tab, int32_t* cell_cnt, uint32_t* cand, int batch, int f0,
+                                   cudaStream_t st);
 cudaError_t orbx_launch_octree(const DevPlan& P, const int32_t* cell_cnt, const uint32_t* cand,
                                uint32_t* gkeys, int16_t* glabels, uint32_t* sel, int32_t* sel_cnt,
                                int32_t* status, int batch, size_t smem_bytes, int smem_keys, int node_cap,
