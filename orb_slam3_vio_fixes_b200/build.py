@@ -1,4 +1,6 @@
 """Builds liborbx.so (the C-ABI CUDA library) in-tree with nvcc for sm_100a."""
+import os
+import shlex
 import subprocess
 import sys
 from pathlib import Path
@@ -26,7 +28,8 @@ def needs_build():
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return SO
-    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+    extra = shlex.split(os.environ.get("ORBX_NVCC_EXTRA", ""))  # experiments: -DFS_WARPS=1 ...
+    cmd = ["nvcc"] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + \
         ["-o", str(SO)] + [str(CSRC / s) for s in SOURCES if (CSRC / s).exists()]
     subprocess.check_call(cmd)
     return SO

@@ -9,21 +9,23 @@
 // nor the threshold (corner(th) <=> A > th, cornerScore == A-1), so only NMS and emission are per cell.
 //
 // One WARP = one STRIP = strip_k consecutive cells of one cell row (<= 120 tested columns), no block-level
-// synchronisation (a CTA is FS_WARPS independent warps):
-//   1. the strip's pixels (+3 px halo, 16-byte aligned columns) go to shared memory with cp.async (16 B per
-//      lane, three rows per step) while the A map and the keep bitmap are being cleared;
-//   2. quick test, dense: lane = one 4-pixel word column, walking down the rows with the last 7 rows (7-bit
-//      pixels) in registers and the horizontal neighbours taken from the adjacent lanes (SHFL); packed-byte
-//      arithmetic (VABSDIFF4): a 9/16 corner needs |v-ring| > t on at least one pixel of each of the axial
-//      ring pairs (0,8) and (4,12).  Two pass bits (one per pixel pair) per row accumulate in a register;
-//   3. the pass bits are compacted into a task list (pixel pairs, any order);
-//   4. arc strength of the listed pairs with packed 16-bit SIMD (fast_arc.cuh) into the A map (u8, 0 where
-//      A <= th or outside the zone); pairs with a corner are kept in the list;
-//   5. NMS of the kept pairs against the A map, with the columns where a new cell starts masked out, sets one
-//      bit per surviving corner in the keep bitmap;
-//   6. per cell: lanes own rows, count their bits, one warp scan, ordered (row-major) emission into the cell's
-//      slot array — the order the reference's per-cell cv::FAST returns;
-//   7. cells that stayed empty are redone from step 2 at minThFAST with the zone restricted to their columns.
+// synchronisation (a CTA is FS_WARPS independent warps; 1 by default so shared memory packs the SM tightly):
+//   1. the strip's pixels (+3 px halo, 16-byte aligned columns) are fetched by the TMA engine: one 3-D
+//      tensor-map box (144 columns x hCell+6 rows of one frame) per strip, completion on the warp's mbarrier,
+//      while the A map is being cleared;
+//   2. quick test, dense: lane = one 4-pixel word column (a "quad" per row), walking down the rows with the last
+//      7 rows (7-bit pixels) in registers and the horizontal neighbours taken from the adjacent lanes (SHFL);
+//      packed-byte arithmetic (VABSDIFF4): a 9/16 corner needs |v-ring| > t on at least one pixel of each of the
+//      axial ring pairs (0,8) and (4,12).  Each row's passing quads are appended to a task list with one ballot,
+//      so the list is in row-major order;
+//   3. arc strength of the listed quads with packed 16-bit SIMD (fast_arc.cuh, two pixel pairs per quad) into the
+//      A map (u8, 0 where A <= th or outside the zone); quads with a corner stay listed;
+//   4. NMS of the kept quads against the A map (columns where a new cell starts masked out) and, in the same
+//      sweep, ordered emission: a corner's slot in its cell is a running per-cell count + a warp prefix over the
+//      batch of 32 quads + its rank inside the quad — the row-major order the reference's per-cell cv::FAST returns;
+//   5. cells that stayed empty are redone from step 2 at minThFAST with the zone restricted to their columns.
+// The kernel is bound by the integer ALU pipe (VABSDIFF4 / LOP3 / PRMT / VIMNMX3 issue at one warp instruction
+// per two cycles per scheduler), not by memory: see DESIGN.md §4 for the instruction budget per pixel.
 #include <cuda.h>
 #include <stdlib.h>
 
@@ -31,13 +33,13 @@
 #include "orbx_kernels.cuh"
 
 #ifndef FS_WARPS
-#define FS_WARPS 2
+#define FS_WARPS 1
 #endif
 #define FS_THREADS (FS_WARPS * 32)
 #define FS_TP 144            // tile row pitch in bytes: 9 vectors of 16 B cover lane words 0..31 at word offset <= 3
 #define FS_TPW (FS_TP / 4)   // 36 words
 #define FS_APW 32            // A-map row pitch in words: word 0 = pad, words 1..30 = strip columns 0..119, word 31 = pad
-#define FS_MAXH 120          // tallest zone (list codes hold 7 bits of row: rows + 6 < 128)
+#define FS_MAXH 250          // tallest zone: a TMA box holds at most 256 rows
 
 __device__ __forceinline__ uint32_t fs_halve(uint32_t v) { return (v >> 1) & 0x7f7f7f7fu; }
 
