@@ -468,18 +468,21 @@ def host_threads():
 
 
 def bench_pipeline(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, lap, shift_xy, th, threads,
-                   do_match=True, flags=0):
+                   do_match=True, flags=0, stages=None):
     """CPU baseline of bench.py's step (extract all frames + frame-to-frame window matching).
-    Returns (seconds, total keypoints, total matches)."""
+    Returns (seconds, total keypoints, total matches).  `stages`: optional float64[8] that receives the per-stage
+    seconds summed over the workers (pyramid, FAST, octree, orientation, blur, descriptors) and the wall seconds of
+    the extract and match phases."""
     L = lib()
     L.oracle_bench_pipeline.restype = C.c_double
     L.oracle_bench_pipeline.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int,
                                         C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float, C.c_int, C.c_int,
-                                        C.POINTER(C.c_long), C.POINTER(C.c_long)]
+                                        C.POINTER(C.c_long), C.POINTER(C.c_long), C.c_void_p]
     frames = np.ascontiguousarray(frames, np.uint8)
     shift_xy = np.ascontiguousarray(shift_xy, np.float32)
     n, h, w = frames.shape
     tk, tm = C.c_long(0), C.c_long(0)
     sec = L.oracle_bench_pipeline(nfeatures, scale_factor, nlevels, ini_th, min_th, flags, _p(frames), n, w, h,
-                                  lap[0], lap[1], _p(shift_xy), th, threads, int(do_match), C.byref(tk), C.byref(tm))
+                                  lap[0], lap[1], _p(shift_xy), th, threads, int(do_match), C.byref(tk), C.byref(tm),
+                                  stages.ctypes.data if stages is not None else None)
     return sec, tk.value, tm.value

@@ -47,6 +47,7 @@
 #include <thread>
 #include <utility>
 #include <map>
+#include <memory>
 #include <vector>
 
 namespace {
@@ -449,6 +450,10 @@ struct Extractor {
   std::vector<Image> pyrB;      // with the 19-px REFLECT_101 border (mvImagePyramid parents)
   std::vector<std::vector<KeyPoint>> candidates;  // per level, before the octree (debug/tests)
   std::vector<std::vector<KeyPoint>> perLevel;    // per level after octree+orientation
+  // wall seconds spent per stage, accumulated over extract() calls (bench only):
+  // 0 pyramid, 1 per-cell FAST, 2 octree (+fix-up), 3 orientation, 4 blur, 5 descriptors (+ordering)
+  double stage_sec[6] = {0, 0, 0, 0, 0, 0};
+  static double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
   Extractor(int nf, float sf, int nl, int ini, int mn, int fl)
       : nfeatures(nf), nlevels(nl), iniThFAST(ini), minThFAST(mn), flags(fl), scaleFactor(sf) {
@@ -537,6 +542,7 @@ struct Extractor {
       const int nCols = (int)(width / W), nRows = (int)(height / W);
       const int wCell = (int)std::ceil(width / nCols), hCell = (int)std::ceil(height / nRows);
       std::vector<Corner> cell;
+      const double t_fast0 = now_s();
       for (int i = 0; i < nRows; i++) {
         const float iniY = (float)(minBorderY + i * hCell);
         float maxY = iniY + hCell + 6;
@@ -556,6 +562,7 @@ struct Extractor {
           }
         }
       }
+      const double t_fast1 = now_s();
       std::vector<KeyPoint>& keypoints = perLevel[level];
       keypoints = DistributeOctTree(vToDistributeKeys, minBorderX, maxBorderX, minBorderY, maxBorderY,
                                     mnFeaturesPerLevel[level]);
@@ -563,9 +570,13 @@ struct Extractor {
       for (KeyPoint& kp : keypoints) {
         kp.x += minBorderX; kp.y += minBorderY; kp.octave = level; kp.size = (float)scaledPatchSize;
       }
+      const double t_oct1 = now_s();
+      stage_sec[1] += t_fast1 - t_fast0; stage_sec[2] += t_oct1 - t_fast1;
     }
+    const double t_or0 = now_s();
     for (int level = 0; level < nlevels; ++level)
       for (KeyPoint& kp : perLevel[level]) kp.angle = IC_Angle(pyr[level], cvRound(kp.x), cvRound(kp.y));
+    stage_sec[3] += now_s() - t_or0;
   }
 
   void computeOrbDescriptor(const KeyPoint& kpt, const Image& img, uint8_t* desc) const {  // :107-146
@@ -598,7 +609,9 @@ struct Extractor {
   int extract(const uint8_t* img, int w, int h, size_t stride, int lap0, int lap1, KeyPoint* out_kps,
               uint8_t* out_desc, int capacity, int* n_out) {
     if (!img || w <= 0 || h <= 0) return -1;
+    const double t_p0 = now_s();
     ComputePyramid(img, w, h, stride);
+    stage_sec[0] += now_s() - t_p0;
     ComputeKeyPointsOctTree();
     int nkeypoints = 0;
     for (int level = 0; level < nlevels; ++level) nkeypoints += (int)perLevel[level].size();
@@ -609,7 +622,10 @@ struct Extractor {
     for (int level = 0; level < nlevels; ++level) {
       std::vector<KeyPoint>& keypoints = perLevel[level];
       if (keypoints.empty()) continue;
+      const double t_b0 = now_s();
       gaussian_blur7(pyr[level], working);
+      const double t_b1 = now_s();
+      stage_sec[4] += t_b1 - t_b0;
       float scale = mvScaleFactor[level];
       for (KeyPoint kp : keypoints) {
         uint8_t d[32];
@@ -620,6 +636,7 @@ struct Extractor {
         out_kps[dst] = kp;
         memcpy(out_desc + (size_t)dst * 32, d, 32);
       }
+      stage_sec[5] += now_s() - t_b1;
     }
     return monoIndex;
   }
@@ -1463,20 +1480,25 @@ double oracle_bench_extract(int nfeatures, float scaleFactor, int nlevels, int i
 extern "C" double oracle_bench_pipeline(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh,
                                         int flags, const uint8_t* frames, int n_frames, int w, int h, int lap0,
                                         int lap1, const float* shift_xy, float th, int threads, int do_match,
-                                        long* total_kps, long* total_matches) {
+                                        long* total_kps, long* total_matches, double* stage_out) {
   const int cap = nfeatures + 3 * nlevels + 64;
   std::vector<std::vector<KeyPoint>> K(n_frames);
   std::vector<std::vector<uint8_t>> D(n_frames);
   std::vector<float> sf(nlevels);
+  // one Extractor per worker and the output buffers, built outside the timed region (the reference keeps its
+  // extractors for the whole run, Tracking.cc:ParseORBParamFile)
+  std::vector<std::unique_ptr<Extractor>> ex;
+  for (int t = 0; t < threads; t++) ex.emplace_back(new Extractor(nfeatures, scaleFactor, nlevels, iniTh, minTh, flags));
+  for (int l = 0; l < nlevels; l++) sf[l] = ex[0]->mvScaleFactor[l];
+  for (int f = 0; f < n_frames; f++) { K[f].resize(cap); D[f].resize((size_t)cap * 32); }
   auto t0 = std::chrono::steady_clock::now();
   {
     std::vector<std::thread> pool;
     for (int t = 0; t < threads; t++)
       pool.emplace_back([&, t]() {
-        Extractor e(nfeatures, scaleFactor, nlevels, iniTh, minTh, flags);
-        if (t == 0) for (int l = 0; l < nlevels; l++) sf[l] = e.mvScaleFactor[l];
+        Extractor& e = *ex[t];
         for (int f = t; f < n_frames; f += threads) {
-          K[f].resize(cap); D[f].resize((size_t)cap * 32);
+          K[f].resize(cap);
           int n = 0;
           e.extract(frames + (size_t)f * w * h, w, h, w, lap0, lap1, K[f].data(), D[f].data(), cap, &n);
           K[f].resize(n);
@@ -1484,6 +1506,7 @@ extern "C" double oracle_bench_pipeline(int nfeatures, float scaleFactor, int nl
       });
     for (auto& th_ : pool) th_.join();
   }
+  auto t_mid = std::chrono::steady_clock::now();
   std::vector<long> matches(threads, 0);
   if (do_match) {
     std::vector<std::thread> pool;
@@ -1522,5 +1545,10 @@ extern "C" double oracle_bench_pipeline(int nfeatures, float scaleFactor, int nl
   for (long m : matches) tm += m;
   if (total_kps) *total_kps = tk;
   if (total_matches) *total_matches = tm;
+  if (stage_out) {  // [0..5] per-stage seconds summed over the workers, [6] extract phase wall, [7] match phase wall
+    for (int i = 0; i < 6; i++) { stage_out[i] = 0; for (auto& e : ex) stage_out[i] += e->stage_sec[i]; }
+    stage_out[6] = std::chrono::duration<double>(t_mid - t0).count();
+    stage_out[7] = std::chrono::duration<double>(t1 - t_mid).count();
+  }
   return std::chrono::duration<double>(t1 - t0).count();
 }

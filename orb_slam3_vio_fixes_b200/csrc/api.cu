@@ -233,14 +233,13 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   ALLOC(h->o_n, B * sizeof(int32_t));
   ALLOC(h->o_mono, B * sizeof(int32_t));
   {
-    // Descriptor stage mode.  Measured on B200 (profiles/): blurring whole levels costs ~55 instructions
-    // per level pixel plus a per-keypoint sampler that is L1-bound on its scattered byte reads; blurring
-    // each keypoint's own 45x45 neighbourhood in shared memory costs ~2100 warp instructions per keypoint
-    // and nothing per pixel (and writes no blurred level).  The level mode only pays off when keypoints
-    // are dense (< ~600 level pixels per keypoint); EuRoC-shaped frames at 1000 kp are not.
+    // Descriptor stage mode.  Blurring whole levels (k_blur_levels, then a light per-keypoint sampler) costs per
+    // level pixel; blurring each keypoint's own 45x45 neighbourhood in shared memory (fused k_describe) costs per
+    // keypoint and writes no blurred level.  Measured on B200 at 752x480 / 1000 kp (1078 level pixels per keypoint)
+    // the level mode is 3 % faster per step; at 4K / 5000 kp (5000 px per keypoint) the fused mode wins clearly.
     long long px = 0;
     for (int l = 0; l < P.nlevels; l++) px += (long long)P.lv[l].w * P.lv[l].h;
-    h->level_blur = px < 600LL * P.max_keypoints;
+    h->level_blur = px < 1200LL * P.max_keypoints;
     if (cfg->flags & ORBX_FLAG_LEVEL_BLUR) h->level_blur = true;
     if (cfg->flags & ORBX_FLAG_FUSED_BLUR) h->level_blur = false;
     if (h->level_blur) ALLOC(h->blur, B * P.arena_bytes + 512);
@@ -326,6 +325,11 @@ static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1,
   int32_t* dst = h->dst + (long long)f0 * D.kp_total_cap;
 #define STAGE_MARK(i) do { if (tm) CU(cudaEventRecord(h->ev[i], st)); } while (0)
   STAGE_MARK(0);
+  if (((uintptr_t)l0.base | (uintptr_t)(unsigned)l0.pitch | (uintptr_t)l0.frame_stride) & 15u) {
+    // unaligned caller buffer: one pass into the arena's (unused in batch mode) level-0 slot, see pyramid.cu
+    CU(orbx_launch_repack_level0(D, l0, arena, batch, st));
+    l0.base = arena + D.lv[0].offset; l0.pitch = D.lv[0].pitch; l0.frame_stride = D.arena_bytes;
+  }
   CU(orbx_launch_pyramid(D, l0, arena, h->xtaps, h->ytaps, batch, st));
   STAGE_MARK(1);
   CU(orbx_launch_fast(D, h->fast_maps, l0, arena, h->cell_tab, h->strip_tab, cell_cnt, cand, batch, f0, st));

@@ -535,7 +535,7 @@ int orbm_search_area(const orbx_keypoint* d_kps, const uint8_t* d_desc, const in
                      const int8_t* d_qmin_level, const int8_t* d_qmax_level, const uint8_t* d_qdesc,
                      const int32_t* d_nq, int q_stride, int batch, int tie_rule, orbm_result* d_out, void* stream) {
   if (!d_kps || !d_desc || !d_n || !d_cell_off || !d_cell_idx || !d_qx || !d_qy || !d_qr || !d_qmin_level ||
-      !d_qmax_level || !d_qdesc || !d_nq || !d_out || batch < 1 || q_stride < 1)
+      !d_qmax_level || !d_qdesc || !d_nq || !d_out || batch < 1 || q_stride < 1 || !(max_x > min_x) || !(max_y > min_y))
     return ORBX_E_INVALID;
   const float winv = (float)FRAME_GRID_COLS / (max_x - min_x), hinv = (float)FRAME_GRID_ROWS / (max_y - min_y);
   dim3 grd((q_stride + SA_THREADS - 1) / SA_THREADS, batch);

@@ -61,6 +61,7 @@ struct OrbxStereoPyr {
 };
 
 // --- launches (each returns cudaGetLastError()) -------------------------------------------------
+cudaError_t orbx_launch_repack_level0(const DevPlan& P, Level0 l0, uint8_t* arena, int batch, cudaStream_t st);
 cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, const OrbxTap* xtaps,
                                 const OrbxTap* ytaps, int batch, cudaStream_t st);
 // Tensor maps of the pyramid levels for k_fast_strip's TMA staging: one CUtensorMap (128 bytes, 64-byte aligned)

@@ -305,6 +305,32 @@ cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, con
 }
 
 // ------------------------------------------------------------------------------------------------
+// A caller's level 0 whose base, pitch or frame stride is not 16-byte aligned (e.g. tightly packed 1241-px
+// KITTI rows) is copied once into the arena's level-0 slot (pitch a multiple of 128): every later kernel
+// then takes its aligned path (TMA boxes in k_fast_strip, bulk copies in k_resize_tile).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_repack_level0(const uint8_t* __restrict__ src, long long sframe, int spitch, uint8_t* __restrict__ dst,
+                long long dframe, int dpitch, int w, int h) {
+  const int y = blockIdx.y, frame = blockIdx.z;
+  const int x4 = (blockIdx.x * 256 + threadIdx.x) * 4;
+  if (x4 >= w) return;
+  const uint8_t* g = src + (long long)frame * sframe + (long long)y * spitch + x4;
+  uint32_t v = 0;
+#pragma unroll
+  for (int j = 0; j < 4; j++)
+    if (x4 + j < w) v |= (uint32_t)g[j] << (8 * j);
+  *reinterpret_cast<uint32_t*>(dst + (long long)frame * dframe + (long long)y * dpitch + x4) = v;
+}
+
+cudaError_t orbx_launch_repack_level0(const DevPlan& P, Level0 l0, uint8_t* arena, int batch, cudaStream_t st) {
+  const DevLevel& L = P.lv[0];
+  dim3 grd((L.w + 1023) / 1024, L.h, batch);
+  k_repack_level0<<<grd, 256, 0, st>>>(l0.base, l0.frame_stride, l0.pitch, arena + L.offset, P.arena_bytes, L.pitch, L.w, L.h);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
 // copyMakeBorder(BORDER_REFLECT_101, 19 px) — only for orbx_get_pyramid(with_border=1); the
 // compute kernels never read the border.
 // ------------------------------------------------------------------------------------------------

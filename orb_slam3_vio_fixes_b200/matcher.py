@@ -68,25 +68,31 @@ class ORBmatcher:
         return out
 
     @staticmethod
-    def grid_build(kps, n, bounds):
+    def grid_build(kps, n, bounds, out=None):
         """kps [B,cap,7] f32 (cv::KeyPoint records), n [B] i32; bounds = (minX, maxX, minY, maxY).
-        Returns (cell_off [B, 64*48+1] i32, cell_idx [B,cap] i32)."""
+        Returns (cell_off [B, 64*48+1] i32, cell_idx [B,cap] i32); `out` = a previous return value to refill
+        (no allocation, no fill kernel on the per-frame path)."""
         import torch
         b, cap = kps.shape[0], kps.shape[1]
-        cell_off = torch.zeros((b, _lib.GRID_COLS * _lib.GRID_ROWS + 1), dtype=torch.int32, device=kps.device)
-        cell_idx = torch.zeros((b, cap), dtype=torch.int32, device=kps.device)
+        if out is not None:
+            cell_off, cell_idx = out
+        else:
+            cell_off = torch.zeros((b, _lib.GRID_COLS * _lib.GRID_ROWS + 1), dtype=torch.int32, device=kps.device)
+            cell_idx = torch.zeros((b, cap), dtype=torch.int32, device=kps.device)
         rc = _lib.lib().orbm_grid_build(kps.data_ptr(), n.data_ptr(), cap, b, *[float(v) for v in bounds],
                                         cell_off.data_ptr(), cell_idx.data_ptr(), _stream(kps.device))
         _lib.check(rc, "orbm_grid_build")
         return cell_off, cell_idx
 
     @staticmethod
-    def search_area(kps, desc, n, grid, bounds, qx, qy, qr, qmin, qmax, qdesc, nq, tie_rule=TIE_FIRST_MIN):
+    def search_area(kps, desc, n, grid, bounds, qx, qy, qr, qmin, qmax, qdesc, nq, tie_rule=TIE_FIRST_MIN, out=None):
         """Fused GetFeaturesInArea + best/second scoring.  Queries [B,Q] (qx,qy,qr f32; qmin,qmax i8;
-        qdesc [B,Q,32] u8; nq [B] i32).  Returns [B,Q,12] uint8 orbm_result records."""
+        qdesc [B,Q,32] u8; nq [B] i32).  Returns [B,Q,12] uint8 orbm_result records (`out` = a previous return
+        value to refill; records of queries >= nq keep what they held)."""
         b, cap = kps.shape[0], kps.shape[1]
         qs = qx.shape[1]
-        out = _res_tensor(b * qs, kps.device).view(b, qs, RES_DTYPE.itemsize)
+        if out is None:
+            out = _res_tensor(b * qs, kps.device).view(b, qs, RES_DTYPE.itemsize)
         cell_off, cell_idx = grid
         rc = _lib.lib().orbm_search_area(kps.data_ptr(), desc.data_ptr(), n.data_ptr(), cap, cell_off.data_ptr(),
                                          cell_idx.data_ptr(), *[float(v) for v in bounds], qx.data_ptr(),
