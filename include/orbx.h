@@ -409,6 +409,50 @@ int orbm_search_for_initialization(
     int window_size, float nn_ratio, int check_orientation, int32_t* d_match12, int32_t* d_scratch,
     int32_t* d_nmatches, void* stream);
 
+/* --------------------------------------------------------------------------------------
+ * Per-point Frame geometry.
+ * -------------------------------------------------------------------------------------- */
+
+/* Frame::UndistortKeyPoints (Frame.cc:747-781): mvKeysUn = cv::undistortPoints(mvKeys, K, mDistCoef,
+ * R = I, P = K) — 5 fixed-point iterations in double, bit-exact against OpenCV 4.13; every other
+ * cv::KeyPoint field is copied.  dist_coef_host = mDistCoef (k1,k2,p1,p2[,k3[,k4,k5,k6[,s1..s4]]],
+ * n_coef <= 12; dist_coef_host[0] == 0 -> mvKeysUn = mvKeys as the reference does).  The same call on
+ * the four image corners is Frame::ComputeImageBounds (Frame.cc:783-809). */
+int orbm_undistort_keypoints(const orbx_keypoint* d_kps, const int32_t* d_n, int kp_stride, int batch,
+                             float fx, float fy, float cx, float cy, const float* dist_coef_host,
+                             int n_coef, orbx_keypoint* d_kps_un, void* stream);
+
+/* GeometricCamera parameters (CameraModels/Pinhole.h, KannalaBrandt8.h: mvParameters). */
+typedef struct orbm_camera {
+  int32_t model;          /* 0 = Pinhole, 1 = KannalaBrandt8 */
+  float fx, fy, cx, cy;
+  float k[4];             /* KannalaBrandt8 k0..k3 */
+} orbm_camera;
+
+/* Frame::isInFrustum (Frame.cc:512-586, Nleft == -1; fisheye_rig = 0) and Frame::isInFrustumChecks
+ * (Frame.cc:1168-1242; fisheye_rig = 1, one call per camera of the rig) with MapPoint::PredictScale
+ * (MapPoint.cc:531-546), batched: frame f tests its d_nmp[f] MapPoints (rows of mp_stride).
+ * d_pos / d_normal = GetWorldPos / GetNormal ([..][3]); d_min_dist / d_max_dist = the raw
+ * mfMinDistance / mfMaxDistance members (the 0.8 / 1.2 factors of the getters are applied here).
+ * d_pose[f][15] = R (row-major 3x3), t, camera centre: (mRcw, mtcw, mOw) for the left camera,
+ * (Rrl*mRcw, Rrl*mtcw+trl, mRwc*tlr+mOw) for the right one (:1174-1184, host geometry).
+ * Outputs: d_in_view = the return value; d_proj_x/y = mTrackProjX/Y (fisheye_rig = 0: also set when
+ * only the distance / viewing-angle gates fail, like the reference; else -1), d_proj_xr =
+ * mTrackProjXR (u - mbf/z; fisheye_rig = 0), d_depth = mTrackDepth, d_view_cos, d_level =
+ * mnTrackScaleLevel (-1 when not in view).  d_proj_xr, d_depth, d_view_cos may be NULL.
+ * Optional (d_qr != NULL): the search window of SearchByProjection(Frame&, vector<MapPoint*>&, th)
+ * (ORBmatcher.cc:62-71): d_qr = RadiusByViewingCos(viewCos) [* th if th != 1] * scale[level],
+ * d_qmin = level-1, d_qmax = level — the (qr, qmin, qmax) inputs of orbm_search_by_projection.
+ * fp32 contract: uncontracted, Eigen's fixed-size evaluation order. */
+int orbm_is_in_frustum(const float* d_pos, const float* d_normal, const float* d_min_dist,
+                       const float* d_max_dist, const int32_t* d_nmp, int mp_stride, int batch,
+                       const float* d_pose, const orbm_camera* cam, float mbf, float min_x, float max_x,
+                       float min_y, float max_y, float viewing_cos_limit, float log_scale_factor,
+                       int n_levels, int fisheye_rig, uint8_t* d_in_view, float* d_proj_x,
+                       float* d_proj_y, float* d_proj_xr, float* d_depth, float* d_view_cos,
+                       int8_t* d_level, float th, const float* scale_factors_host, float* d_qr,
+                       int8_t* d_qmin, int8_t* d_qmax, void* stream);
+
 /* Library / build identification. */
 const char* orbx_version(void);
 const char* orbx_last_error(void);

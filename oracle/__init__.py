@@ -27,8 +27,8 @@ STRICT_FP = 1
 
 
 def build(force=False):
-    src = _DIR / "orb_oracle.cpp"
-    if force or not _SO.exists() or _SO.stat().st_mtime < src.stat().st_mtime:
+    srcs = [_DIR / "orb_oracle.cpp", _DIR / "frame_oracle.cpp"]
+    if force or not _SO.exists() or any(_SO.stat().st_mtime < s.stat().st_mtime for s in srcs):
         subprocess.check_call(["make", "-C", str(_DIR), "-B" if force else "-s"],
                               stdout=subprocess.DEVNULL)
     return _SO
@@ -451,6 +451,43 @@ def distinctive_descriptor(desc):
 
 
 from orb_slam3_vio_fixes_b200.synthetic import make_vocabulary  # noqa: E402,F401  (synthetic input, not a checker)
+
+
+def undistort_keypoints(kps, fx, fy, cx, cy, dist_coef):
+    """Frame::UndistortKeyPoints (cv::undistortPoints, R = I, P = K), one frame.  Returns mvKeysUn."""
+    kps = np.ascontiguousarray(kps)
+    d = np.ascontiguousarray(dist_coef, np.float32)
+    out = np.zeros_like(kps)
+    L = lib()
+    L.oracle_undistort_keypoints.restype = None
+    L.oracle_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
+                                             C.c_void_p, C.c_int, C.c_void_p]
+    L.oracle_undistort_keypoints(_p(kps), kps.size, fx, fy, cx, cy, _p(d), d.size, _p(out))
+    return out
+
+
+def is_in_frustum(pos, normal, min_dist, max_dist, pose, cam, mbf, bounds, cos_limit, log_sf, n_levels,
+                  fisheye_rig=False, f64=False):
+    """Frame::isInFrustum / isInFrustumChecks + PredictScale for one camera pose.
+    pose = 15 floats (R row-major, t, centre); cam = (model, fx, fy, cx, cy, k0..k3).
+    Returns dict(in_view, proj_x, proj_y, proj_xr, depth, view_cos, level)."""
+    pos = np.ascontiguousarray(pos, np.float32); normal = np.ascontiguousarray(normal, np.float32)
+    mn = np.ascontiguousarray(min_dist, np.float32); mx = np.ascontiguousarray(max_dist, np.float32)
+    pose = np.ascontiguousarray(pose, np.float32)
+    camf = np.ascontiguousarray(list(cam[1:]) + [0.0] * (9 - len(cam)), np.float32)
+    n = mn.size
+    o = dict(in_view=np.zeros(n, np.uint8), proj_x=np.zeros(n, np.float32), proj_y=np.zeros(n, np.float32),
+             proj_xr=np.zeros(n, np.float32), depth=np.zeros(n, np.float32), view_cos=np.zeros(n, np.float32),
+             level=np.zeros(n, np.int8))
+    L = lib()
+    L.oracle_is_in_frustum.restype = None
+    L.oracle_is_in_frustum.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_void_p, C.c_int, C.c_void_p] + \
+        [C.c_float] * 7 + [C.c_int] * 3 + [C.c_void_p] * 7
+    L.oracle_is_in_frustum(_p(pos), _p(normal), _p(mn), _p(mx), n, _p(pose), int(cam[0]), _p(camf), mbf, bounds[0],
+                           bounds[1], bounds[2], bounds[3], cos_limit, log_sf, n_levels, int(bool(fisheye_rig)),
+                           int(bool(f64)), _p(o["in_view"]), _p(o["proj_x"]), _p(o["proj_y"]), _p(o["proj_xr"]),
+                           _p(o["depth"]), _p(o["view_cos"]), _p(o["level"]))
+    return o
 
 
 def bench_extract(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, lap, threads, flags=0):

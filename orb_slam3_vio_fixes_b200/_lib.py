@@ -39,6 +39,7 @@ SYMBOLS = [
     "orbx_get_scale_tables", "orbx_stage_times", "orbx_check_status", "orbx_debug_blur_level", "orbx_debug_sincos_checksum", "orbx_debug_level_keypoints", "orbx_debug_octree", "orbm_argmin2_csr", "orbm_grid_build",
     "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_search_by_projection_th", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
     "orbm_fuse_candidates", "orbm_descriptor_distance_pairs", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
+    "orbm_undistort_keypoints", "orbm_is_in_frustum",
     "orbx_version", "orbx_last_error",
 ]
 
@@ -58,6 +59,11 @@ class OrbmVocabulary(C.Structure):  # orbm_vocabulary
     _fields_ = [("d_child_off", C.c_void_p), ("d_child_idx", C.c_void_p), ("d_node_desc", C.c_void_p),
                 ("d_node_word", C.c_void_p), ("d_node_weight", C.c_void_p), ("n_nodes", C.c_int32),
                 ("L", C.c_int32)]
+
+
+class OrbmCamera(C.Structure):  # orbm_camera
+    _fields_ = [("model", C.c_int32), ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("k", C.c_float * 4)]
 
 
 class OrbxError(RuntimeError):
@@ -128,6 +134,9 @@ def lib():
     L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, vp, vp, f32, f32, f32, f32, vp, i32,
                                                  f32, i32, vp, vp, vp, vp]
     L.orbm_distinctive_descriptors.argtypes = [vp, vp, vp, i32, vp, vp, vp]
+    L.orbm_undistort_keypoints.argtypes = [vp, vp, i32, i32, f32, f32, f32, f32, vp, i32, vp, vp]
+    L.orbm_is_in_frustum.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp, C.POINTER(OrbmCamera), f32, f32, f32, f32, f32,
+                                     f32, f32, i32, i32, vp, vp, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]
     L.orbx_version.restype = C.c_char_p
     L.orbx_last_error.restype = C.c_char_p
     _lib = L

@@ -164,3 +164,39 @@ ORBX_HD int orbx_reflect101(int p, int len) {
   if (p >= len) p = 2 * (len - 1) - p;
   return p;
 }
+
+// ---- logf, bit-identical to glibc 2.39's logf for positive normal floats ------------------------
+// MapPoint::PredictScale (src/MapPoint.cc:531-546) takes `log(ratio)` of a float with std::log(float)
+// in scope (TemplatedVocabulary.h's global `using namespace std`), i.e. libm logf.  Same algorithm
+// (16-entry table, degree-3 polynomial in double) in explicit uncontracted double operations; the
+// sweep over all 2,130,706,432 positive normal floats against libm shows zero differences
+// (tests/test_harness.py::test_logf_matches_libm_exhaustively).
+ORBX_HD float orbx_logf(float xf) {
+  const double T[16][2] = {
+      {0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2}, {0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2},
+      {0x1.49539f0f010bp+0, -0x1.01eae7f513a67p-2},  {0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3},
+      {0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3}, {0x1.25e227b0b8eap+0, -0x1.1aa2bc79c81p-3},
+      {0x1.1bb4a4a1a343fp+0, -0x1.a4e76ce8c0e5ep-4}, {0x1.12358f08ae5bap+0, -0x1.1973c5a611cccp-4},
+      {0x1.0953f419900a7p+0, -0x1.252f438e10c1ep-5}, {0x1p+0, 0x0p+0},
+      {0x1.e608cfd9a47acp-1, 0x1.aa5aa5df25984p-5},  {0x1.ca4b31f026aap-1, 0x1.c5e53aa362eb4p-4},
+      {0x1.b2036576afce6p-1, 0x1.526e57720db08p-3},  {0x1.9c2d163a1aa2dp-1, 0x1.bc2860d22477p-3},
+      {0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2},  {0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2}};
+  const double Ln2 = 0x1.62e42fefa39efp-1;
+  const double A0 = -0x1.00ea348b88334p-2, A1 = 0x1.5575b0be00b6ap-2, A2 = -0x1.ffffef20a4123p-2;
+  union { float f; uint32_t u; } cvt;
+  cvt.f = xf;
+  const uint32_t ix = cvt.u;
+  if (ix == 0x3f800000u) return 0.0f;
+  const uint32_t tmp = ix - 0x3f330000u;
+  const int i = (int)((tmp >> 19) & 15u);
+  const int k = (int32_t)tmp >> 23;
+  cvt.u = ix - (tmp & 0xff800000u);
+  const double z = (double)cvt.f;
+  const double r = d_add(d_mul(z, T[i][0]), -1.0);
+  const double y0 = d_add(T[i][1], d_mul((double)k, Ln2));
+  const double r2 = d_mul(r, r);
+  double y = d_add(d_mul(A1, r), A2);
+  y = d_add(d_mul(A0, r2), y);
+  y = d_add(d_mul(y, r2), d_add(y0, r));
+  return (float)y;
+}

@@ -34,6 +34,8 @@ def harness():
     H = C.CDLL(str(so))
     H.h_sincos_mismatches.restype = C.c_long
     H.h_sincos_mismatches.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
+    H.h_logf_mismatches.restype = C.c_long
+    H.h_logf_mismatches.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
     return H
 
 

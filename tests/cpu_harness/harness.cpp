@@ -10,6 +10,7 @@
 #include "octree_core.h"
 #include "orbx_core.h"
 #include "orbx_plan.h"
+#include "frame_core.h"
 
 extern "C" {
 
@@ -147,6 +148,40 @@ long h_sincos_mismatches(uint32_t lo, uint32_t hi, uint32_t stride) {
     if (memcmp(&s, &s2, 4) || memcmp(&c, &c2, 4)) bad++;
   }
   return bad;
+}
+
+// counts positive normal float bit patterns in [lo,hi] where orbx_logf differs from libm logf
+long h_logf_mismatches(uint32_t lo, uint32_t hi, uint32_t stride) {
+  long bad = 0;
+  for (uint64_t u = lo; u <= hi; u += stride) {
+    float x, a, b; uint32_t uu = (uint32_t)u; memcpy(&x, &uu, 4);
+    a = logf(x); b = orbx_logf(x);
+    if (memcmp(&a, &b, 4)) bad++;
+  }
+  return bad;
+}
+
+// frame_core.h compiled for the host: cv::undistortPoints on (x,y) pairs, isInFrustum on n MapPoints
+void h_undistort(const float* xy, int n, float fx, float fy, float cx, float cy, const float* dist, int n_coef,
+                 float* out_xy) {
+  double k[12];
+  for (int i = 0; i < 12; i++) k[i] = i < n_coef ? (double)dist[i] : 0.0;
+  for (int i = 0; i < n; i++) orbx_undistort_point(xy[2 * i], xy[2 * i + 1], fx, fy, cx, cy, k, out_xy + 2 * i, out_xy + 2 * i + 1);
+}
+
+void h_in_frustum(const float* pos, const float* normal, const float* min_dist, const float* max_dist, int n,
+                  const float* pose, int model, const float* cam, float mbf, float min_x, float max_x, float min_y,
+                  float max_y, float cos_limit, float log_sf, int n_levels, int fisheye_rig, uint8_t* in_view,
+                  float* proj_x, float* proj_y, float* proj_xr, float* depth, float* view_cos, int8_t* level) {
+  OrbxFrustumPose T; memcpy(&T, pose, sizeof(T));
+  OrbxFrustumCam C; C.model = model; C.fx = cam[0]; C.fy = cam[1]; C.cx = cam[2]; C.cy = cam[3];
+  for (int i = 0; i < 4; i++) C.k[i] = cam[4 + i];
+  for (int i = 0; i < n; i++) {
+    const OrbxFrustumOut o = orbx_in_frustum(pos + 3 * i, normal + 3 * i, min_dist[i], max_dist[i], T, C, mbf, min_x,
+                                             max_x, min_y, max_y, cos_limit, log_sf, n_levels, fisheye_rig);
+    in_view[i] = (uint8_t)o.in_view; proj_x[i] = o.proj_x; proj_y[i] = o.proj_y; proj_xr[i] = o.proj_xr;
+    depth[i] = o.depth; view_cos[i] = o.view_cos; level[i] = (int8_t)o.level;
+  }
 }
 
 void h_fast_atan2(const float* y, const float* x, float* out, int n) {
