@@ -377,6 +377,34 @@ typedef struct orbm_vocabulary {
   int n_nodes, L;
 } orbm_vocabulary;
 
+/* The same tree in host memory, as TemplatedVocabulary::loadFromTextFile builds it
+ * (TemplatedVocabulary.h:1338-1423): node ids in file order, children in push_back order, word ids in
+ * file order of the leaves (-1 for inner nodes); k, L, scoring (ScoringType), weighting (WeightingType)
+ * from the first line. */
+typedef struct orbm_vocabulary_host {
+  int32_t k, L, scoring, weighting, n_nodes, n_words;
+  int32_t* child_off;   /* [n_nodes+1] */
+  int32_t* child_idx;   /* [n_nodes-1] */
+  uint8_t* node_desc;   /* [n_nodes][32] */
+  int32_t* node_word;   /* [n_nodes] */
+  double* node_weight;  /* [n_nodes] */
+  int32_t* node_parent; /* [n_nodes] */
+} orbm_vocabulary_host;
+
+/* ORBVocabulary::loadFromTextFile (System.cc:118 loads ORBvoc.txt with it): parses the reference's text
+ * format ("k L scoring weighting", then "parent isLeaf d0..d31 weight" per node) on the host; needs no
+ * GPU.  ORBX_E_INVALID for an unreadable / malformed file (the reference returns false).  Blank lines
+ * are skipped (the reference turns the trailing newline into a node of uninitialised memory). */
+int orbm_vocabulary_parse_text(const char* path, orbm_vocabulary_host* out);
+/* TemplatedVocabulary::saveToTextFile (TemplatedVocabulary.h:1427-1464); weights written losslessly. */
+int orbm_vocabulary_save_text(const char* path, const orbm_vocabulary_host* voc);
+void orbm_vocabulary_host_free(orbm_vocabulary_host* voc);
+/* Host tree -> device arrays for orbm_bow_transform; orbm_vocabulary_release frees them. */
+int orbm_vocabulary_upload(const orbm_vocabulary_host* voc, orbm_vocabulary* out);
+void orbm_vocabulary_release(orbm_vocabulary* voc);
+/* parse + upload in one call; k / n_words may be NULL. */
+int orbm_vocabulary_load_text(const char* path, orbm_vocabulary* out, int32_t* k, int32_t* n_words);
+
 /* TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup)
  * (TemplatedVocabulary.h:1127-1259; Frame.cc:738-745 calls it with levelsup = 4), TF_IDF + L1.
  * Per feature: word id, node id at level L-levelsup, weight.  Per frame: the FeatureVector CSR

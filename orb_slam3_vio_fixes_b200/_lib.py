@@ -40,6 +40,8 @@ SYMBOLS = [
     "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_search_by_projection_th", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
     "orbm_fuse_candidates", "orbm_descriptor_distance_pairs", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
     "orbm_undistort_keypoints", "orbm_is_in_frustum",
+    "orbm_vocabulary_parse_text", "orbm_vocabulary_save_text", "orbm_vocabulary_host_free", "orbm_vocabulary_upload",
+    "orbm_vocabulary_release", "orbm_vocabulary_load_text",
     "orbx_version", "orbx_last_error",
 ]
 
@@ -59,6 +61,14 @@ class OrbmVocabulary(C.Structure):  # orbm_vocabulary
     _fields_ = [("d_child_off", C.c_void_p), ("d_child_idx", C.c_void_p), ("d_node_desc", C.c_void_p),
                 ("d_node_word", C.c_void_p), ("d_node_weight", C.c_void_p), ("n_nodes", C.c_int32),
                 ("L", C.c_int32)]
+
+
+class OrbmVocabularyHost(C.Structure):  # orbm_vocabulary_host
+    _fields_ = [("k", C.c_int32), ("L", C.c_int32), ("scoring", C.c_int32), ("weighting", C.c_int32),
+                ("n_nodes", C.c_int32), ("n_words", C.c_int32), ("child_off", C.POINTER(C.c_int32)),
+                ("child_idx", C.POINTER(C.c_int32)), ("node_desc", C.POINTER(C.c_uint8)),
+                ("node_word", C.POINTER(C.c_int32)), ("node_weight", C.POINTER(C.c_double)),
+                ("node_parent", C.POINTER(C.c_int32))]
 
 
 class OrbmCamera(C.Structure):  # orbm_camera
@@ -137,6 +147,15 @@ def lib():
     L.orbm_undistort_keypoints.argtypes = [vp, vp, i32, i32, f32, f32, f32, f32, vp, i32, vp, vp]
     L.orbm_is_in_frustum.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp, C.POINTER(OrbmCamera), f32, f32, f32, f32, f32,
                                      f32, f32, i32, i32, vp, vp, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]
+    pvh = C.POINTER(OrbmVocabularyHost)
+    L.orbm_vocabulary_parse_text.argtypes = [C.c_char_p, pvh]
+    L.orbm_vocabulary_save_text.argtypes = [C.c_char_p, pvh]
+    L.orbm_vocabulary_host_free.argtypes = [pvh]
+    L.orbm_vocabulary_host_free.restype = None
+    L.orbm_vocabulary_upload.argtypes = [pvh, pvoc]
+    L.orbm_vocabulary_release.argtypes = [pvoc]
+    L.orbm_vocabulary_release.restype = None
+    L.orbm_vocabulary_load_text.argtypes = [C.c_char_p, pvoc, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.orbx_version.restype = C.c_char_p
     L.orbx_last_error.restype = C.c_char_p
     _lib = L

@@ -8,7 +8,7 @@ from pathlib import Path
 PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 SO = PKG / "liborbx.so"
-SOURCES = ["api.cu", "pyramid.cu", "fast.cu", "fast_cell.cu", "octree.cu", "describe.cu", "blur.cu", "match.cu", "stereo.cu", "search.cu", "bow.cu", "frame.cu"]
+SOURCES = ["api.cu", "pyramid.cu", "fast.cu", "fast_cell.cu", "octree.cu", "describe.cu", "blur.cu", "match.cu", "stereo.cu", "search.cu", "bow.cu", "frame.cu", "voc.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     # parity contract: no implicit FMA contraction anywhere (explicit __fmaf_rn where wanted)

@@ -345,6 +345,31 @@ class ORBVocabulary:
                                       self.node_word.data_ptr(), self.node_weight.data_ptr(),
                                       self.node_word.shape[0], self.L)
 
+    @staticmethod
+    def parse_text_file(path):
+        """TemplatedVocabulary::loadFromTextFile (TemplatedVocabulary.h:1338-1423) on the host, through the C ABI
+        (no GPU needed).  Returns the flat tree as a dict of numpy arrays + k, L, scoring, weighting, n_words."""
+        import ctypes as C
+        h = _lib.OrbmVocabularyHost()
+        rc = _lib.lib().orbm_vocabulary_parse_text(str(path).encode(), C.byref(h))
+        _lib.check(rc, "orbm_vocabulary_parse_text")
+        try:
+            n = h.n_nodes
+            arr = lambda p, cnt, dt: np.ctypeslib.as_array(p, shape=(cnt,)).astype(dt).copy()
+            return {"k": h.k, "L": h.L, "scoring": h.scoring, "weighting": h.weighting, "n_words": h.n_words,
+                    "child_off": arr(h.child_off, n + 1, np.int32), "child_idx": arr(h.child_idx, n - 1, np.int32),
+                    "node_desc": arr(h.node_desc, n * 32, np.uint8).reshape(n, 32),
+                    "node_word": arr(h.node_word, n, np.int32), "node_weight": arr(h.node_weight, n, np.float64),
+                    "node_parent": arr(h.node_parent, n, np.int32)}
+        finally:
+            _lib.lib().orbm_vocabulary_host_free(C.byref(h))
+
+    @classmethod
+    def loadFromTextFile(cls, path, device="cuda:0"):
+        """ORBVocabulary::loadFromTextFile + upload (src/System.cc:118)."""
+        v = cls.parse_text_file(path)
+        return cls(v["child_off"], v["child_idx"], v["node_desc"], v["node_word"], v["node_weight"], v["L"], device)
+
     def transform(self, desc, n, levelsup=4, node_stride=None):
         """desc [B,cap,32] u8, n [B] i32 (CUDA).  Returns dict(feat_word, feat_node [B,cap] i32, feat_weight
         [B,cap] f64, fv (FeatureVector CSR dict), bow_word [B,cap] i32, bow_val [B,cap] f64, bow_n [B] i32)."""
