@@ -481,6 +481,64 @@ int orbm_is_in_frustum(const float* d_pos, const float* d_normal, const float* d
                        int8_t* d_level, float th, const float* scale_factors_host, float* d_qr,
                        int8_t* d_qmin, int8_t* d_qmax, void* stream);
 
+/* --------------------------------------------------------------------------------------
+ * Two-camera rig (fisheye stereo: F.Nleft != -1, KeyFrame::mpCamera2 != NULL) twins of the matcher
+ * functions.  The reference numbers the rig's features left camera
+ * first, right camera from Nleft on; mGrid / mGridRight are per camera (Frame.cc:385-416).
+ * -------------------------------------------------------------------------------------- */
+
+/* One camera of a rig as the projection search sees it: that camera's own keypoints / descriptors
+ * (LOCAL numbering — the right camera's global index is local + Nleft), its orbm_grid_build CSR,
+ * d_feat_locked[j] != 0: mvpMapPoints[j] holds a point with Observations()>0 on entry (NULL = none),
+ * d_partner[j] = mvLeftToRightMatch[j] (left camera) / mvRightToLeftMatch[j] (right camera): local
+ * index of the paired feature in the other camera or -1 (NULL = no pairs). */
+typedef struct orbm_rig_camera {
+  const orbx_keypoint* d_kps;
+  const uint8_t* d_desc;
+  const int32_t* d_n;
+  int32_t kp_stride;
+  const int32_t* d_cell_off;
+  const int32_t* d_cell_idx;
+  const uint8_t* d_feat_locked;
+  const int32_t* d_partner;
+} orbm_rig_camera;
+
+/* ORBmatcher::SearchByProjection on a two-camera Frame, whole function, batched over frames:
+ *   ORBM_PROJ_MAPPOINTS  ORBmatcher.cc:43-213  left block :59-142 + right block :144-210, with the
+ *                        pair propagation (:131-135, :197-201) and the reference's `continue`s (a
+ *                        failed left ratio test skips the right search of that MapPoint)
+ *   ORBM_PROJ_LASTFRAME  ORBmatcher.cc:1676-1887  left :1716-1792 + right :1794-1862 (searched only
+ *                        when the left window was not empty), one rotation histogram for both
+ * Per query (MapPoint): the left window (d_qx, d_qy, d_qr, level band) and the right window (*_r),
+ * one descriptor, d_q_flags bit0 = left query takes part, bit1 = Observations()>0, bit2 = right
+ * query takes part (MAPPOINTS: mbTrackInViewR && mnTrackScaleLevelR != -1), d_q_angle (LASTFRAME).
+ * d_scratch: batch * q_stride * 65 bytes.  Outputs in local numbering: d_match_l/r[q] = feature the
+ * query itself was matched to, d_feat_query_l/r[j] = last query written into feature j (including
+ * pair propagation; -1 none / erased), d_nmatches[f] = the return value. */
+int orbm_search_by_projection_rig(
+    int mode, const orbm_rig_camera* left, const orbm_rig_camera* right, int batch, float min_x,
+    float max_x, float min_y, float max_y, const float* d_qx, const float* d_qy, const float* d_qr,
+    const int8_t* d_qmin_level, const int8_t* d_qmax_level, const float* d_qx_r, const float* d_qy_r,
+    const float* d_qr_r, const int8_t* d_qmin_level_r, const int8_t* d_qmax_level_r,
+    const uint8_t* d_qdesc, const int32_t* d_nq, int q_stride, const uint8_t* d_q_flags,
+    const float* d_q_angle, float nn_ratio, int check_orientation, void* d_scratch,
+    int32_t* d_match_l, int32_t* d_match_r, int32_t* d_feat_query_l, int32_t* d_feat_query_r,
+    int32_t* d_nmatches, void* stream);
+
+/* ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) with F.Nleft != -1 (ORBmatcher.cc:295-323,
+ * 356-380): side 2 = the frame's left|right features in the reference's concatenated numbering,
+ * d_nleft2[p] = F.Nleft; side 1 = the keyframe (its left|right keypoints concatenated likewise when
+ * it has mpCamera2).  Separate best pairs per camera; d_match12_left / d_match12_right = the left /
+ * right feature written for keyframe feature i, d_match21 = vpMapPointMatches (keyframe feature
+ * whose MapPoint frame feature j received); the rotation histogram runs over the written features. */
+int orbm_search_by_bow_rig(const orbx_keypoint* d_kps1, const uint8_t* d_desc1, const int32_t* d_n1,
+                           const uint8_t* d_valid1, const orbm_feature_vector* fv1,
+                           const orbx_keypoint* d_kps2, const uint8_t* d_desc2, const int32_t* d_n2,
+                           const int32_t* d_nleft2, const orbm_feature_vector* fv2, int kp_stride,
+                           int node_stride, int batch, float nn_ratio, int check_orientation,
+                           int32_t* d_match12_left, int32_t* d_match12_right, int32_t* d_match21,
+                           int32_t* d_nmatches, void* stream);
+
 /* Library / build identification. */
 const char* orbx_version(void);
 const char* orbx_last_error(void);

@@ -490,6 +490,60 @@ def is_in_frustum(pos, normal, min_dist, max_dist, pose, cam, mbf, bounds, cos_l
     return o
 
 
+def search_by_bow_rig(kps1, desc1, fv1, kps2, desc2, nleft2, fv2, nn_ratio=0.6, check_orientation=True, valid1=None):
+    """SearchByBoW(KeyFrame*, Frame&) with F.Nleft != -1.  Returns (match12_left, match12_right, match21, nmatches)."""
+    kps1, kps2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+    d1, d2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    a, b = _fv_args(fv1), _fv_args(fv2)
+    v1 = None if valid1 is None else np.ascontiguousarray(valid1, np.uint8)
+    m12l, m12r = np.zeros(kps1.size, np.int32), np.zeros(kps1.size, np.int32)
+    m21 = np.zeros(kps2.size, np.int32)
+    L = lib()
+    L.oracle_search_by_bow_fisheye.restype = C.c_int
+    L.oracle_search_by_bow_fisheye.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int,
+                                               C.c_void_p, C.c_void_p, C.c_void_p]
+    nm = L.oracle_search_by_bow_fisheye(_p(kps1), _p(d1), kps1.size, None if v1 is None else _p(v1), _p(a[0]), _p(a[1]),
+                                        _p(a[2]), a[0].size, _p(kps2), _p(d2), kps2.size, int(nleft2), _p(b[0]), _p(b[1]),
+                                        _p(b[2]), b[0].size, float(nn_ratio), int(bool(check_orientation)), _p(m12l),
+                                        _p(m12r), _p(m21))
+    return m12l, m12r, m21, nm
+
+
+def search_by_projection_rig(mode, kps_l, desc_l, kps_r, desc_r, bounds, q, nn_ratio=0.6, check_orientation=True,
+                             locked_l=None, locked_r=None, l2r=None, r2l=None):
+    """SearchByProjection on a two-camera Frame, one frame (local numbering per camera).  q: dict of numpy arrays
+    qx,qy,qr,qmin,qmax,qx_r,qy_r,qr_r,qmin_r,qmax_r,qdesc and optional flags, angle.
+    Returns dict(match_l, match_r, feat_query_l, feat_query_r, nmatches)."""
+    kps_l, kps_r = np.ascontiguousarray(kps_l), np.ascontiguousarray(kps_r)
+    nl, nr, nq = kps_l.size, kps_r.size, len(q["qx"])
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    i8 = lambda a: np.ascontiguousarray(a, np.int8)
+    u8 = lambda a: None if a is None else np.ascontiguousarray(a, np.uint8)
+    i32 = lambda a, n: np.full(n, -1, np.int32) if a is None else np.ascontiguousarray(a, np.int32)
+    pp = lambda a: None if a is None else _p(a)
+    hold = dict(dl=u8(desc_l), dr=u8(desc_r), ll=u8(locked_l), lr=u8(locked_r), l2r=i32(l2r, nl), r2l=i32(r2l, nr),
+                qx=f32(q["qx"]), qy=f32(q["qy"]), qr=f32(q["qr"]), qmin=i8(q["qmin"]), qmax=i8(q["qmax"]),
+                qxr=f32(q["qx_r"]), qyr=f32(q["qy_r"]), qrr=f32(q["qr_r"]), qminr=i8(q["qmin_r"]), qmaxr=i8(q["qmax_r"]),
+                qd=u8(q["qdesc"]), fl=u8(q.get("flags")), ang=None if q.get("angle") is None else f32(q["angle"]))
+    o = dict(match_l=np.zeros(nq, np.int32), match_r=np.zeros(nq, np.int32), feat_query_l=np.zeros(nl, np.int32),
+             feat_query_r=np.zeros(nr, np.int32))
+    L = lib()
+    L.oracle_search_by_projection_rig.restype = C.c_int
+    L.oracle_search_by_projection_rig.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                                  C.c_int] + [C.c_float] * 4 + [C.c_void_p] * 15 + [C.c_int] + \
+        [C.c_void_p] * 2 + [C.c_float, C.c_int] + [C.c_void_p] * 4
+    o["nmatches"] = L.oracle_search_by_projection_rig(
+        int(mode), _p(kps_l), pp(hold["dl"]), nl, _p(kps_r), pp(hold["dr"]), nr, bounds[0], bounds[1], bounds[2],
+        bounds[3], pp(hold["ll"]), pp(hold["lr"]), _p(hold["l2r"]), _p(hold["r2l"]), _p(hold["qx"]), _p(hold["qy"]),
+        _p(hold["qr"]), _p(hold["qmin"]), _p(hold["qmax"]), _p(hold["qxr"]), _p(hold["qyr"]), _p(hold["qrr"]),
+        _p(hold["qminr"]), _p(hold["qmaxr"]), _p(hold["qd"]), nq, pp(hold["fl"]), pp(hold["ang"]), float(nn_ratio),
+        int(bool(check_orientation)), _p(o["match_l"]), _p(o["match_r"]), _p(o["feat_query_l"]),
+        _p(o["feat_query_r"]))
+    return o
+
+
 def bench_extract(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, lap, threads, flags=0):
     """Times the oracle over frames[n,h,w]; returns (seconds, total keypoints)."""
     frames = np.ascontiguousarray(frames, np.uint8)

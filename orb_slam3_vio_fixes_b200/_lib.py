@@ -40,6 +40,7 @@ SYMBOLS = [
     "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_search_by_projection_th", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
     "orbm_fuse_candidates", "orbm_descriptor_distance_pairs", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
     "orbm_undistort_keypoints", "orbm_is_in_frustum",
+    "orbm_search_by_projection_rig", "orbm_search_by_bow_rig",
     "orbm_vocabulary_parse_text", "orbm_vocabulary_save_text", "orbm_vocabulary_host_free", "orbm_vocabulary_upload",
     "orbm_vocabulary_release", "orbm_vocabulary_load_text",
     "orbx_version", "orbx_last_error",
@@ -69,6 +70,12 @@ class OrbmVocabularyHost(C.Structure):  # orbm_vocabulary_host
                 ("child_idx", C.POINTER(C.c_int32)), ("node_desc", C.POINTER(C.c_uint8)),
                 ("node_word", C.POINTER(C.c_int32)), ("node_weight", C.POINTER(C.c_double)),
                 ("node_parent", C.POINTER(C.c_int32))]
+
+
+class OrbmRigCamera(C.Structure):  # orbm_rig_camera
+    _fields_ = [("d_kps", C.c_void_p), ("d_desc", C.c_void_p), ("d_n", C.c_void_p), ("kp_stride", C.c_int32),
+                ("d_cell_off", C.c_void_p), ("d_cell_idx", C.c_void_p), ("d_feat_locked", C.c_void_p),
+                ("d_partner", C.c_void_p)]
 
 
 class OrbmCamera(C.Structure):  # orbm_camera
@@ -147,6 +154,11 @@ def lib():
     L.orbm_undistort_keypoints.argtypes = [vp, vp, i32, i32, f32, f32, f32, f32, vp, i32, vp, vp]
     L.orbm_is_in_frustum.argtypes = [vp, vp, vp, vp, vp, i32, i32, vp, C.POINTER(OrbmCamera), f32, f32, f32, f32, f32,
                                      f32, f32, i32, i32, vp, vp, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]
+    prc = C.POINTER(OrbmRigCamera)
+    L.orbm_search_by_projection_rig.argtypes = [i32, prc, prc, i32, f32, f32, f32, f32] + [vp] * 12 + [i32, vp, vp, f32,
+                                                                                                   i32] + [vp] * 7
+    L.orbm_search_by_bow_rig.argtypes = [vp, vp, vp, vp, pfv, vp, vp, vp, vp, pfv, i32, i32, i32, f32, i32, vp, vp, vp,
+                                         vp, vp]
     pvh = C.POINTER(OrbmVocabularyHost)
     L.orbm_vocabulary_parse_text.argtypes = [C.c_char_p, pvh]
     L.orbm_vocabulary_save_text.argtypes = [C.c_char_p, pvh]

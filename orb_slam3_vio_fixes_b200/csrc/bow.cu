@@ -104,6 +104,125 @@ k_bow_nodes(BowSide S1, BowSide S2, int kp_stride, int node_stride, int mode, fl
   }
 }
 
+// SearchByBoW(KeyFrame*, Frame&) on a two-camera Frame (F.Nleft != -1; ORBmatcher.cc:295-323, 356-380): side 2 holds
+// the left features [0, Nleft) and the right features [Nleft, N) in one numbering; every side-1 feature keeps a
+// separate (best, second) pair per camera.  The left match needs bestDist1 <= TH_LOW and the ratio test; the right
+// match is taken whenever bestDist1 <= TH_LOW and bestDist1R <= TH_LOW (`|| true` at :358).
+__global__ void __launch_bounds__(BOW_WARPS * 32)
+k_bow_nodes_rig(BowSide S1, BowSide S2, const int32_t* __restrict__ nleft2, int kp_stride, int node_stride,
+                float nnratio, int32_t* __restrict__ match12l, int32_t* __restrict__ match12r,
+                int32_t* __restrict__ match21) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, p = blockIdx.y;
+  const int a = blockIdx.x * BOW_WARPS + warp;
+  if (a >= S1.fv_nn[p]) return;
+  const size_t nb = (size_t)p * node_stride, fb = (size_t)p * kp_stride;
+  const int node = S1.fv_node[nb + a];
+  const int b = bow_find_node(S2.fv_node + nb, S2.fv_nn[p], node);
+  if (b < 0) return;
+  const int o1 = S1.fv_off[nb + p + a], e1 = S1.fv_off[nb + p + a + 1];
+  const int o2 = S2.fv_off[nb + p + b], e2 = S2.fv_off[nb + p + b + 1];
+  const int32_t* idx1s = S1.fv_idx + fb;
+  const int32_t* idx2s = S2.fv_idx + fb;
+  volatile int32_t* m21 = match21 + fb;
+  const int nleft = nleft2[p];
+  const int TH_LOW = 50;
+  for (int i1 = o1; i1 < e1; i1++) {
+    const int idx1 = idx1s[i1];
+    if (S1.flag && !S1.flag[fb + idx1]) continue;
+    const Desc256 d1 = load_desc(S1.desc + (fb + idx1) * 32);
+    uint32_t kL = KEY_NONE, kR = KEY_NONE; int sL = 256, sR = 256;  // lane-local best key / second distance per camera
+    for (int c = o2 + lane; c < e2; c += 32) {
+      const int idx2 = idx2s[c];
+      if (m21[idx2] >= 0) continue;
+      const int dist = hamming(d1, load_desc(S2.desc + (fb + idx2) * 32));
+      const uint32_t key = ((uint32_t)dist << 16) | (uint32_t)((c - o2) & 0xffff);
+      if (idx2 < nleft) {
+        if (key < kL) { sL = min(sL, (int)(kL >> 16)); kL = key; } else sL = min(sL, dist);
+      } else {
+        if (key < kR) { sR = min(sR, (int)(kR >> 16)); kR = key; } else sR = min(sR, dist);
+      }
+    }
+    if (kL == KEY_NONE) sL = 256; else sL = min(sL, 256);
+    if (kR == KEY_NONE) sR = 256; else sR = min(sR, 256);
+    uint32_t bestL = kL, bestR = kR;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      bestL = min(bestL, __shfl_xor_sync(FULLMASK, bestL, o));
+      bestR = min(bestR, __shfl_xor_sync(FULLMASK, bestR, o));
+    }
+    if (bestL == KEY_NONE) { __syncwarp(); continue; }  // bestDist1 = 256 > TH_LOW: neither camera is written (:327)
+    int secL = (kL == bestL) ? sL : (kL == KEY_NONE ? 256 : (int)(kL >> 16));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) secL = min(secL, __shfl_xor_sync(FULLMASK, secL, o));
+    const int bestDist1 = (int)(bestL >> 16), bestDist2 = secL;
+    if (bestDist1 <= TH_LOW) {
+      if ((float)bestDist1 < f_mul(nnratio, (float)bestDist2)) {
+        const int idx2 = idx2s[o2 + (int)(bestL & 0xffff)];
+        if (lane == 0) { match12l[fb + idx1] = idx2; m21[idx2] = idx1; }
+      }
+      if (bestR != KEY_NONE && (int)(bestR >> 16) <= TH_LOW) {
+        const int idx2 = idx2s[o2 + (int)(bestR & 0xffff)];
+        if (lane == 0) { match12r[fb + idx1] = idx2; m21[idx2] = idx1; }
+      }
+    }
+    __syncwarp();
+  }
+}
+
+// Rotation histogram of the rig variant: the entries are the written side-2 features (rotHist[bin].push_back(
+// bestIdxF / bestIdxFR), :352, :376), so the sweep runs over match21.
+__global__ void __launch_bounds__(256)
+k_bow_rot_rig(const OrbxKeyPointDev* __restrict__ k1, const OrbxKeyPointDev* __restrict__ k2,
+              const int32_t* __restrict__ n2_arr, int kp_stride, int check_orientation, int32_t* __restrict__ match12l,
+              int32_t* __restrict__ match12r, int32_t* __restrict__ match21, int32_t* __restrict__ nmatches) {
+  __shared__ int hist[30];
+  __shared__ int s_ind[3];
+  __shared__ int s_cnt;
+  const int p = blockIdx.x, n2 = n2_arr[p];
+  const size_t fb = (size_t)p * kp_stride;
+  if (threadIdx.x < 30) hist[threadIdx.x] = 0;
+  if (threadIdx.x == 0) s_cnt = 0;
+  __syncthreads();
+  int cnt = 0;
+  for (int j = threadIdx.x; j < n2; j += blockDim.x) {
+    const int m = match21[fb + j];
+    if (m < 0) continue;
+    cnt++;
+    if (check_orientation) atomicAdd(&hist[bow_rot_bin(k1[fb + m].angle, k2[fb + j].angle)], 1);
+  }
+  __syncthreads();
+  if (check_orientation) {
+    if (threadIdx.x == 0) {
+      int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+      for (int i = 0; i < 30; i++) {
+        const int s = hist[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+      }
+      if ((float)max2 < f_mul(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+      else if ((float)max3 < f_mul(0.1f, (float)max1)) { ind3 = -1; }
+      s_ind[0] = ind1; s_ind[1] = ind2; s_ind[2] = ind3;
+    }
+    __syncthreads();
+    const int ind1 = s_ind[0], ind2 = s_ind[1], ind3 = s_ind[2];
+    for (int j = threadIdx.x; j < n2; j += blockDim.x) {
+      const int m = match21[fb + j];
+      if (m < 0) continue;
+      const int bin = bow_rot_bin(k1[fb + m].angle, k2[fb + j].angle);
+      if (bin != ind1 && bin != ind2 && bin != ind3) {
+        match21[fb + j] = -1;
+        if (match12l[fb + m] == j) match12l[fb + m] = -1;  // the left and the right entry of m are distinct features
+        if (match12r[fb + m] == j) match12r[fb + m] = -1;
+        cnt--;
+      }
+    }
+  }
+  atomicAdd(&s_cnt, cnt);
+  __syncthreads();
+  if (threadIdx.x == 0) nmatches[p] = s_cnt;
+}
+
 struct TriGeom {       // per pair, host geometry
   const float* F12;    // [batch][9] row-major
   const float* ep;     // [batch][2]
@@ -452,6 +571,30 @@ extern "C" int orbm_search_by_bow(int mode, const orbx_keypoint* d_kps1, const u
   k_bow_nodes<<<grd, BOW_WARPS * 32, 0, st>>>(S1, S2, kp_stride, node_stride, mode, nn_ratio, d_match12, d_match21);
   k_bow_rot<<<batch, 256, 0, st>>>(S1.kps, S2.kps, d_n1, kp_stride, check_orientation, d_match12, d_match21,
                                    d_nmatches);
+  return cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
+}
+
+extern "C" int orbm_search_by_bow_rig(const orbx_keypoint* d_kps1, const uint8_t* d_desc1, const int32_t* d_n1,
+                                      const uint8_t* d_valid1, const orbm_feature_vector* fv1,
+                                      const orbx_keypoint* d_kps2, const uint8_t* d_desc2, const int32_t* d_n2,
+                                      const int32_t* d_nleft2, const orbm_feature_vector* fv2, int kp_stride,
+                                      int node_stride, int batch, float nn_ratio, int check_orientation,
+                                      int32_t* d_match12_left, int32_t* d_match12_right, int32_t* d_match21,
+                                      int32_t* d_nmatches, void* stream) {
+  if (!d_kps1 || !d_desc1 || !d_n1 || !fv_ok(fv1) || !d_kps2 || !d_desc2 || !d_n2 || !d_nleft2 || !fv_ok(fv2) ||
+      kp_stride < 1 || node_stride < 1 || batch < 1 || !d_match12_left || !d_match12_right || !d_match21 || !d_nmatches)
+    return ORBX_E_INVALID;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(d_match12_left, 0xff, (size_t)batch * kp_stride * sizeof(int32_t), st);
+  cudaMemsetAsync(d_match12_right, 0xff, (size_t)batch * kp_stride * sizeof(int32_t), st);
+  cudaMemsetAsync(d_match21, 0xff, (size_t)batch * kp_stride * sizeof(int32_t), st);
+  const BowSide S1 = make_side(d_kps1, d_desc1, d_n1, d_valid1, nullptr, fv1);
+  const BowSide S2 = make_side(d_kps2, d_desc2, d_n2, nullptr, nullptr, fv2);
+  dim3 grd((node_stride + BOW_WARPS - 1) / BOW_WARPS, batch);
+  k_bow_nodes_rig<<<grd, BOW_WARPS * 32, 0, st>>>(S1, S2, d_nleft2, kp_stride, node_stride, nn_ratio, d_match12_left,
+                                                 d_match12_right, d_match21);
+  k_bow_rot_rig<<<batch, 256, 0, st>>>(S1.kps, S2.kps, d_n2, kp_stride, check_orientation, d_match12_left,
+                                       d_match12_right, d_match21, d_nmatches);
   return cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
 }
 

@@ -24,6 +24,7 @@ struct ProjArgs {
   const float *qx, *qy, *qr; const int8_t *qmin, *qmax; const uint8_t* qdesc; const int32_t* nq; int q_stride;
   const float* q_ur; const uint8_t* q_flags; const float* q_angle;
   int mode; float nnratio; int check_orientation; int th_dist;
+  int flag_bit;  // bit of q_flags that enables the query in k_proj_score (1; 4 for the right camera of a rig)
 };
 
 struct ProjQuery {
@@ -49,12 +50,17 @@ __device__ __forceinline__ ProjQuery proj_query(const ProjArgs& A, size_t qo) {
   return q;
 }
 
+// GetFeaturesInArea membership (Frame.cc:689-712): octave band and window
+__device__ __forceinline__ bool proj_gate_area(const ProjQuery& q, const OrbxKeyPointDev* k, int j) {
+  const float kx = k[j].x, ky = k[j].y;
+  const int oct = k[j].octave;
+  return oct >= q.lo && oct <= q.hi && fabsf(f_sub(kx, q.x)) < q.r && fabsf(f_sub(ky, q.y)) < q.r;
+}
+
 // every gate of the candidate loops that does not depend on earlier queries
 __device__ __forceinline__ bool proj_gate(const ProjArgs& A, const ProjQuery& q, const OrbxKeyPointDev* k,
                                           size_t fbase, int j) {
-  const float kx = k[j].x, ky = k[j].y;
-  const int oct = k[j].octave;
-  if (!(oct >= q.lo && oct <= q.hi && fabsf(f_sub(kx, q.x)) < q.r && fabsf(f_sub(ky, q.y)) < q.r)) return false;
+  if (!proj_gate_area(q, k, j)) return false;
   if (A.feat_locked && A.feat_locked[fbase + j]) return false;       // :88-90 / :1741-1743 (state on entry)
   if (A.u_right && A.q_ur) {                                         // :92-97 / :1745-1751
     const float ur = A.u_right[fbase + j];
@@ -89,13 +95,14 @@ struct TopK {
 
 #define PS_THREADS 128
 __global__ void __launch_bounds__(PS_THREADS)
-k_proj_score(const ProjArgs A, ProjCand* __restrict__ cand) {
+k_proj_score(const ProjArgs A, ProjCand* __restrict__ cand, uint8_t* __restrict__ area_any = nullptr) {
   const int f = blockIdx.y;
   const int qi = blockIdx.x * PS_THREADS + threadIdx.x;
   if (qi >= A.nq[f]) return;
   const size_t qo = (size_t)f * A.q_stride + qi;
   TopK t;
-  if (!A.q_flags || (A.q_flags[qo] & 1)) {
+  bool any = false;  // vIndices non-empty (before the lock / stereo gates)
+  if (!A.q_flags || (A.q_flags[qo] & A.flag_bit)) {
     const size_t fbase = (size_t)f * A.kp_stride;
     const OrbxKeyPointDev* k = A.kps + fbase;
     const uint8_t* dsc = A.desc + fbase * 32;
@@ -114,6 +121,7 @@ k_proj_score(const ProjArgs A, ProjCand* __restrict__ cand) {
           continue;
         }
         const int j = idx[e];
+        if (area_any && !any && proj_gate_area(q, k, j)) any = true;
         if (proj_gate(A, q, k, fbase, j)) {
           const int d = hamming(dq, load_desc(dsc + (size_t)j * 32));
           t.push(make_key(d, seq & 0xFFFFF, ORBM_TIE_FIRST_MIN), j);
@@ -123,6 +131,7 @@ k_proj_score(const ProjArgs A, ProjCand* __restrict__ cand) {
       }
     }
   }
+  if (area_any) area_any[qo] = any ? 1 : 0;
   ProjCand c;
 #pragma unroll
   for (int j = 0; j < PROJ_K; j++) { c.key[j] = t.k[j]; c.idx[j] = t.i[j]; }
@@ -342,6 +351,7 @@ extern "C" int orbm_search_by_projection_th(
   A.qx = d_qx; A.qy = d_qy; A.qr = d_qr; A.qmin = d_qmin_level; A.qmax = d_qmax_level; A.qdesc = d_qdesc;
   A.nq = d_nq; A.q_stride = q_stride; A.q_ur = d_q_ur; A.q_flags = d_q_flags; A.q_angle = d_q_angle;
   A.mode = mode; A.nnratio = nn_ratio; A.check_orientation = check_orientation; A.th_dist = th_dist;
+  A.flag_bit = 1;
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grd((q_stride + PS_THREADS - 1) / PS_THREADS, batch);
   k_proj_score<<<grd, PS_THREADS, 0, st>>>(A, (ProjCand*)d_scratch);
@@ -362,4 +372,265 @@ extern "C" int orbm_search_by_projection(
                                       d_qmax_level, d_qdesc, d_nq, q_stride, d_q_ur, d_q_flags, d_q_angle, mode,
                                       nn_ratio, check_orientation, 100 /* TH_HIGH */, d_scratch, d_match,
                                       d_feat_query, d_nmatches, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Two-camera rig (F.Nleft != -1): the fisheye twins of the two functions above.
+//   mode ORBM_PROJ_MAPPOINTS  src/ORBmatcher.cc:43-213  (right block :144-210, pair propagation :131-135, :197-201)
+//   mode ORBM_PROJ_LASTFRAME  src/ORBmatcher.cc:1676-1887 (right block :1794-1862, one rotation histogram)
+// Each camera keeps its own features, grid, lock bitmap and top-4 lists (k_proj_score, once per camera).  The commit
+// is one warp per frame walking the MapPoints IN ORDER (left query, then right query): the two cameras are coupled
+// through mvLeftToRightMatch / mvRightToLeftMatch (a match also writes — and re-locks or UNLOCKS — the paired feature
+// of the other camera) and through the reference's `continue`s (a failed left ratio test, or an empty left window in
+// the last-frame variant, skips the right search of that point), so the parallel prefix commit of k_proj_resolve
+// does not apply; a query costs a broadcast list read and a few ballots.  Lists were built under the locks known on
+// entry; if a paired write ever unlocks a feature that was locked on entry, that camera's lists are no longer
+// supersets and every later query of it rescans its window (flag `dirty`).
+// ---------------------------------------------------------------------------------------------------------
+struct RigSide {
+  ProjArgs A;                 // that camera's features, grid, window queries
+  const ProjCand* cand;       // [batch][q_stride]
+  const int32_t* partner;     // mvLeftToRightMatch / mvRightToLeftMatch [batch][kp_stride] (local index of the other camera, -1)
+  int32_t* match;             // [batch][q_stride]
+  int32_t* feat_query;        // [batch][kp_stride]
+};
+
+struct RigPick { int i1, i2, d1, d2; };
+
+// best / second best of query qo on one camera under the CURRENT lock bitmap (warp-uniform result)
+__device__ __forceinline__ RigPick rig_pick(const RigSide& S, const uint32_t* lockbits, bool dirty, bool want_second,
+                                            int f, size_t qo, int lane) {
+#define RBIT(bm, j) (((bm)[(j) >> 5] >> ((j) & 31)) & 1u)
+  RigPick r;
+  r.i1 = r.i2 = -1; r.d1 = r.d2 = 256;
+  bool ok = false;
+  if (!dirty) {
+    const ProjCand c = S.cand[qo];
+#pragma unroll
+    for (int j = 0; j < PROJ_K; j++) {
+      const int x = c.idx[j];
+      if (x < 0 || RBIT(lockbits, x)) continue;
+      if (r.i1 < 0) { r.i1 = x; r.d1 = (int)(c.key[j] >> 20); }
+      else if (r.i2 < 0) { r.i2 = x; r.d2 = (int)(c.key[j] >> 20); }
+    }
+    const bool full = c.idx[PROJ_K - 1] >= 0;
+    ok = !full || (r.i1 >= 0 && (!want_second || r.i2 >= 0));
+  }
+  if (!ok) {  // warp-cooperative rescan of the window under the current locks (entry locks are in the bitmap)
+    const ProjArgs& A = S.A;
+    const size_t fbase = (size_t)f * A.kp_stride;
+    const OrbxKeyPointDev* k = A.kps + fbase;
+    const uint8_t* dsc = A.desc + fbase * 32;
+    const int32_t* off = A.cell_off + (size_t)f * (GRID_CELLS + 1);
+    const int32_t* idx = A.cell_idx + fbase;
+    const ProjQuery q = proj_query(A, qo);
+    Top2 t;
+    if (q.ok) {
+      const Desc256 dq = load_desc(A.qdesc + qo * 32);
+      int seq = 0;
+      for (int ix = q.cx0; ix <= q.cx1; ix++) {
+        const int e0 = off[ix * FRAME_GRID_ROWS + q.cy0], e1 = off[ix * FRAME_GRID_ROWS + q.cy1 + 1];
+        for (int e = e0 + lane; e < e1; e += 32) {
+          const int j = idx[e];
+          if (proj_gate_area(q, k, j) && !RBIT(lockbits, j)) {
+            const int d = hamming(dq, load_desc(dsc + (size_t)j * 32));
+            t.push(make_key(d, (seq + e - e0) & 0xFFFFF, ORBM_TIE_FIRST_MIN), j);
+          }
+        }
+        seq += e1 - e0;
+      }
+    }
+    warp_top2(t);
+    r.i1 = t.i1; r.i2 = t.i2;
+    r.d1 = t.i1 >= 0 ? (int)(t.k1 >> 20) : 256;
+    r.d2 = t.i2 >= 0 ? (int)(t.k2 >> 20) : 256;
+  }
+  return r;
+#undef RBIT
+}
+
+__global__ void __launch_bounds__(32)
+k_proj_resolve_rig(const RigSide L, const RigSide R, const uint8_t* __restrict__ area_any_l, int mode, float nnratio,
+                   int check_orientation, int th_dist, int32_t* __restrict__ nmatches) {
+  extern __shared__ uint32_t s_bits[];
+  __shared__ int hist[30];
+  __shared__ int s_ind[3];
+  const int lane = threadIdx.x, f = blockIdx.x;
+  const int nwl = (L.A.kp_stride + 31) / 32, nwr = (R.A.kp_stride + 31) / 32;
+  uint32_t* lockL = s_bits;
+  uint32_t* lockR = s_bits + nwl;
+  const size_t fbl = (size_t)f * L.A.kp_stride, fbr = (size_t)f * R.A.kp_stride, qbase = (size_t)f * L.A.q_stride;
+  const int nl = L.A.n[f], nr = R.A.n[f], nq = L.A.nq[f];
+  // lock bitmaps = the state on entry; feat_query = -1
+  for (int w = lane; w < nwl; w += 32) {
+    uint32_t m = 0;
+    if (L.A.feat_locked)
+      for (int b = 0; b < 32; b++) { const int j = 32 * w + b; if (j < nl && L.A.feat_locked[fbl + j]) m |= 1u << b; }
+    lockL[w] = m;
+  }
+  for (int w = lane; w < nwr; w += 32) {
+    uint32_t m = 0;
+    if (R.A.feat_locked)
+      for (int b = 0; b < 32; b++) { const int j = 32 * w + b; if (j < nr && R.A.feat_locked[fbr + j]) m |= 1u << b; }
+    lockR[w] = m;
+  }
+  for (int j = lane; j < nl; j += 32) L.feat_query[fbl + j] = -1;
+  for (int j = lane; j < nr; j += 32) R.feat_query[fbr + j] = -1;
+  if (lane < 30) hist[lane] = 0;
+  __syncwarp();
+  const bool ratio_mode = mode == ORBM_PROJ_MAPPOINTS;
+  const bool rot_check = mode == ORBM_PROJ_LASTFRAME && check_orientation;
+  const OrbxKeyPointDev* kl = L.A.kps + fbl;
+  const OrbxKeyPointDev* kr = R.A.kps + fbr;
+  bool dirtyL = false, dirtyR = false;
+  int total = 0;
+  // writes a MapPoint into a feature of one camera: holder, lock bit (set or cleared), "dirty" on an entry lock lost
+  auto write_feat = [&](const RigSide& S, uint32_t* bits, bool& dirty, size_t fb, int j, int qi, bool locker) {
+    if (lane == 0) {
+      S.feat_query[fb + j] = qi;
+      if (locker) bits[j >> 5] |= 1u << (j & 31); else bits[j >> 5] &= ~(1u << (j & 31));
+    }
+    if (!locker && S.A.feat_locked && S.A.feat_locked[fb + j]) dirty = true;
+    __syncwarp();
+  };
+  auto accept = [&](const RigPick& p, const OrbxKeyPointDev* k, bool& ratio_failed) {
+    ratio_failed = false;
+    if (!(p.i1 >= 0 && p.d1 <= th_dist)) return false;
+    if (ratio_mode) {
+      const int lv1 = k[p.i1].octave, lv2 = p.i2 >= 0 ? k[p.i2].octave : -1;
+      if (lv1 == lv2 && (float)p.d1 > f_mul(nnratio, (float)p.d2)) { ratio_failed = true; return false; }
+    }
+    return true;
+  };
+  for (int qi = 0; qi < nq; qi++) {
+    const size_t qo = qbase + qi;
+    const int fl = L.A.q_flags ? L.A.q_flags[qo] : 7;
+    const bool locker = (fl & 2) != 0;
+    int ml = -1, mr = -1;
+    bool skip_right = false;
+    if (fl & 1) {
+      const RigPick p = rig_pick(L, lockL, dirtyL, ratio_mode, f, qo, lane);
+      bool rf;
+      if (accept(p, kl, rf)) {
+        ml = p.i1;
+        write_feat(L, lockL, dirtyL, fbl, p.i1, qi, locker);
+        total++;
+        if (ratio_mode) {
+          const int pr = L.partner ? L.partner[fbl + p.i1] : -1;   // :131-135
+          if (pr >= 0) { write_feat(R, lockR, dirtyR, fbr, pr, qi, locker); total++; }
+        } else if (rot_check && lane == 0) {
+          hist[proj_rot_bin(L.A.q_angle[qo], kl[p.i1].angle)]++;
+        }
+      } else if (rf) {
+        skip_right = true;                                          // `continue` at :126-127
+      }
+      if (!ratio_mode && !area_any_l[qo]) skip_right = true;        // `continue` at :1737-1738
+    } else if (!ratio_mode) {
+      skip_right = true;                                            // the projection gates failed (:1706-1714)
+    }
+    const bool right_on = ratio_mode ? (fl & 4) != 0 : true;
+    if (!skip_right && right_on) {
+      const RigPick p = rig_pick(R, lockR, dirtyR, ratio_mode, f, qo, lane);
+      bool rf;
+      if (accept(p, kr, rf)) {
+        mr = p.i1;
+        if (ratio_mode) {
+          const int pl = R.partner ? R.partner[fbr + p.i1] : -1;    // :197-201
+          if (pl >= 0) { write_feat(L, lockL, dirtyL, fbl, pl, qi, locker); total++; }
+        }
+        write_feat(R, lockR, dirtyR, fbr, p.i1, qi, locker);
+        total++;
+        if (rot_check && lane == 0) hist[proj_rot_bin(L.A.q_angle[qo], kr[p.i1].angle)]++;
+      }
+    }
+    if (lane == 0) { L.match[qo] = ml; R.match[qo] = mr; }
+  }
+  __syncwarp();
+  int erased = 0;
+  if (rot_check) {
+    if (lane == 0) {  // ComputeThreeMaxima (:2012-2053)
+      int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+      for (int i = 0; i < 30; i++) {
+        const int s = hist[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+      }
+      if ((float)max2 < f_mul(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+      else if ((float)max3 < f_mul(0.1f, (float)max1)) { ind3 = -1; }
+      s_ind[0] = ind1; s_ind[1] = ind2; s_ind[2] = ind3;
+    }
+    __syncwarp();
+    const int ind1 = s_ind[0], ind2 = s_ind[1], ind3 = s_ind[2];
+    for (int qi = lane; qi < nq; qi += 32) {
+      const size_t qo = qbase + qi;
+      const int a = L.match[qo], b = R.match[qo];
+      if (a >= 0) {
+        const int bin = proj_rot_bin(L.A.q_angle[qo], kl[a].angle);
+        if (bin != ind1 && bin != ind2 && bin != ind3) { L.match[qo] = -1; L.feat_query[fbl + a] = -1; erased++; }
+      }
+      if (b >= 0) {
+        const int bin = proj_rot_bin(L.A.q_angle[qo], kr[b].angle);
+        if (bin != ind1 && bin != ind2 && bin != ind3) { R.match[qo] = -1; R.feat_query[fbr + b] = -1; erased++; }
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) erased += __shfl_xor_sync(0xffffffffu, erased, o);
+  if (lane == 0) nmatches[f] = total - erased;
+}
+
+static ProjArgs rig_args(const orbm_rig_camera* c, float min_x, float max_x, float min_y, float max_y,
+                         const float* qx, const float* qy, const float* qr, const int8_t* qmin, const int8_t* qmax,
+                         const uint8_t* qdesc, const int32_t* nq, int q_stride, const uint8_t* q_flags,
+                         const float* q_angle, int mode, float nn_ratio, int check_orientation, int flag_bit) {
+  ProjArgs A;
+  A.kps = (const OrbxKeyPointDev*)c->d_kps; A.desc = c->d_desc; A.n = c->d_n; A.kp_stride = c->kp_stride;
+  A.cell_off = c->d_cell_off; A.cell_idx = c->d_cell_idx;
+  A.min_x = min_x; A.min_y = min_y;
+  A.winv = (float)FRAME_GRID_COLS / (max_x - min_x); A.hinv = (float)FRAME_GRID_ROWS / (max_y - min_y);
+  A.u_right = nullptr; A.feat_locked = c->d_feat_locked;
+  A.qx = qx; A.qy = qy; A.qr = qr; A.qmin = qmin; A.qmax = qmax; A.qdesc = qdesc; A.nq = nq; A.q_stride = q_stride;
+  A.q_ur = nullptr; A.q_flags = q_flags; A.q_angle = q_angle;
+  A.mode = mode; A.nnratio = nn_ratio; A.check_orientation = check_orientation; A.th_dist = 100; A.flag_bit = flag_bit;
+  return A;
+}
+
+extern "C" int orbm_search_by_projection_rig(
+    int mode, const orbm_rig_camera* left, const orbm_rig_camera* right, int batch, float min_x, float max_x,
+    float min_y, float max_y, const float* d_qx, const float* d_qy, const float* d_qr, const int8_t* d_qmin_level,
+    const int8_t* d_qmax_level, const float* d_qx_r, const float* d_qy_r, const float* d_qr_r,
+    const int8_t* d_qmin_level_r, const int8_t* d_qmax_level_r, const uint8_t* d_qdesc, const int32_t* d_nq,
+    int q_stride, const uint8_t* d_q_flags, const float* d_q_angle, float nn_ratio, int check_orientation,
+    void* d_scratch, int32_t* d_match_l, int32_t* d_match_r, int32_t* d_feat_query_l, int32_t* d_feat_query_r,
+    int32_t* d_nmatches, void* stream) {
+  if ((mode != ORBM_PROJ_MAPPOINTS && mode != ORBM_PROJ_LASTFRAME) || !left || !right || batch < 1 || q_stride < 1 ||
+      !(max_x > min_x) || !(max_y > min_y) || !d_qx || !d_qy || !d_qr || !d_qmin_level || !d_qmax_level || !d_qx_r ||
+      !d_qy_r || !d_qr_r || !d_qmin_level_r || !d_qmax_level_r || !d_qdesc || !d_nq || !d_scratch || !d_match_l ||
+      !d_match_r || !d_feat_query_l || !d_feat_query_r || !d_nmatches)
+    return ORBX_E_INVALID;
+  for (const orbm_rig_camera* c : {left, right})
+    if (!c->d_kps || !c->d_desc || !c->d_n || !c->d_cell_off || !c->d_cell_idx || c->kp_stride < 1) return ORBX_E_INVALID;
+  if (mode == ORBM_PROJ_LASTFRAME && check_orientation && !d_q_angle) return ORBX_E_INVALID;
+  const size_t smem = ((size_t)(left->kp_stride + 31) / 32 + (size_t)(right->kp_stride + 31) / 32) * sizeof(uint32_t);
+  if (smem > 40 * 1024) return ORBX_E_INVALID;
+  RigSide L, R;
+  L.A = rig_args(left, min_x, max_x, min_y, max_y, d_qx, d_qy, d_qr, d_qmin_level, d_qmax_level, d_qdesc, d_nq, q_stride,
+                 d_q_flags, d_q_angle, mode, nn_ratio, check_orientation, 1);
+  R.A = rig_args(right, min_x, max_x, min_y, max_y, d_qx_r, d_qy_r, d_qr_r, d_qmin_level_r, d_qmax_level_r, d_qdesc,
+                 d_nq, q_stride, d_q_flags, d_q_angle, mode, nn_ratio, check_orientation,
+                 mode == ORBM_PROJ_MAPPOINTS ? 4 : 1);
+  // scratch: two candidate arrays [batch][q_stride] + the left camera's "window not empty" bytes
+  ProjCand* cand_l = (ProjCand*)d_scratch;
+  ProjCand* cand_r = cand_l + (size_t)batch * q_stride;
+  uint8_t* any_l = (uint8_t*)(cand_r + (size_t)batch * q_stride);
+  L.cand = cand_l; R.cand = cand_r;
+  L.partner = left->d_partner; R.partner = right->d_partner;
+  L.match = d_match_l; R.match = d_match_r; L.feat_query = d_feat_query_l; R.feat_query = d_feat_query_r;
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grd((q_stride + PS_THREADS - 1) / PS_THREADS, batch);
+  k_proj_score<<<grd, PS_THREADS, 0, st>>>(L.A, cand_l, any_l);
+  k_proj_score<<<grd, PS_THREADS, 0, st>>>(R.A, cand_r, nullptr);
+  k_proj_resolve_rig<<<batch, 32, smem, st>>>(L, R, any_l, mode, nn_ratio, check_orientation, 100, d_nmatches);
+  return cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
 }

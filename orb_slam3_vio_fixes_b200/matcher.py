@@ -174,6 +174,48 @@ class ORBmatcher:
         return out
 
     @staticmethod
+    def rig_camera(kps, desc, n, grid, feat_locked=None, partner=None):
+        """One camera of a two-camera Frame (orbm_rig_camera): its own keypoints [B,cap,28] u8, descriptors, counts,
+        orbm_grid_build CSR, optional entry locks [B,cap] u8 and pair table [B,cap] i32 (mvLeftToRightMatch /
+        mvRightToLeftMatch).  Keeps the tensors alive."""
+        c = _lib.OrbmRigCamera()
+        p = lambda t: t.data_ptr() if t is not None else None
+        c.d_kps, c.d_desc, c.d_n, c.kp_stride = kps.data_ptr(), desc.data_ptr(), n.data_ptr(), kps.shape[1]
+        c.d_cell_off, c.d_cell_idx = grid[0].data_ptr(), grid[1].data_ptr()
+        c.d_feat_locked, c.d_partner = p(feat_locked), p(partner)
+        c._keep = (kps, desc, n, grid, feat_locked, partner)
+        return c
+
+    @staticmethod
+    def search_by_projection_rig(mode, left, right, bounds, q, nn_ratio=0.6, check_orientation=True):
+        """ORBmatcher::SearchByProjection on a two-camera (fisheye) Frame, whole function (ORBmatcher.cc:43-213 /
+        :1676-1887 with their right-camera blocks).  left / right = rig_camera(...).  q: dict of CUDA tensors
+        qx,qy,qr,qmin,qmax (left window), qx_r,qy_r,qr_r,qmin_r,qmax_r (right window), qdesc [B,Q,32], nq [B],
+        optional flags [B,Q] u8 (bit0 left, bit1 observations, bit2 right) and angle [B,Q] f32.
+        Returns dict(match_l, match_r [B,Q], feat_query_l, feat_query_r [B,cap], nmatches [B])."""
+        import ctypes as C
+        import torch
+        b, qs = q["qx"].shape
+        dev = q["qx"].device
+        scratch = torch.empty((b, qs, 65), dtype=torch.uint8, device=dev)
+        out = {"match_l": torch.empty((b, qs), dtype=torch.int32, device=dev),
+               "match_r": torch.empty((b, qs), dtype=torch.int32, device=dev),
+               "feat_query_l": torch.empty((b, left.kp_stride), dtype=torch.int32, device=dev),
+               "feat_query_r": torch.empty((b, right.kp_stride), dtype=torch.int32, device=dev),
+               "nmatches": torch.empty((b,), dtype=torch.int32, device=dev)}
+        p = lambda t: t.data_ptr() if t is not None else None
+        rc = _lib.lib().orbm_search_by_projection_rig(
+            int(mode), C.byref(left), C.byref(right), b, float(bounds[0]), float(bounds[1]), float(bounds[2]),
+            float(bounds[3]), q["qx"].data_ptr(), q["qy"].data_ptr(), q["qr"].data_ptr(), q["qmin"].data_ptr(),
+            q["qmax"].data_ptr(), q["qx_r"].data_ptr(), q["qy_r"].data_ptr(), q["qr_r"].data_ptr(),
+            q["qmin_r"].data_ptr(), q["qmax_r"].data_ptr(), q["qdesc"].data_ptr(), q["nq"].data_ptr(), qs,
+            p(q.get("flags")), p(q.get("angle")), float(nn_ratio), int(bool(check_orientation)), scratch.data_ptr(),
+            out["match_l"].data_ptr(), out["match_r"].data_ptr(), out["feat_query_l"].data_ptr(),
+            out["feat_query_r"].data_ptr(), out["nmatches"].data_ptr(), _stream(dev))
+        _lib.check(rc, "orbm_search_by_projection_rig")
+        return out
+
+    @staticmethod
     def stereo_rowband(kps_l, desc_l, n_l, kps_r, desc_r, n_r, scale_factors, max_d):
         """Hamming stage of Frame::ComputeStereoMatches.  Returns (best_idx_r [B,cap] i32, best_dist [B,cap] i32)."""
         import torch
@@ -269,6 +311,29 @@ class ORBmatcher:
                                            out["match12"].data_ptr(), out["match21"].data_ptr(),
                                            out["nmatches"].data_ptr(), _stream(dev))
         _lib.check(rc, "orbm_search_by_bow")
+        return out
+
+    @staticmethod
+    def search_by_bow_rig(kps1, desc1, n1, fv1, kps2, desc2, n2, nleft2, fv2, nn_ratio=0.6, check_orientation=True,
+                          valid1=None):
+        """ORBmatcher::SearchByBoW(KeyFrame*, Frame&) with F.Nleft != -1 (ORBmatcher.cc:295-323, 356-380).  Side 2 =
+        the frame's left|right features in one numbering, nleft2 [B] i32 = F.Nleft.
+        Returns dict(match12_left, match12_right, match21 [B,cap] i32, nmatches [B] i32)."""
+        import torch
+        b, cap = kps1.shape[0], kps1.shape[1]
+        dev = kps1.device
+        ns = fv1["node"].shape[1]
+        assert fv2["node"].shape[1] == ns and kps2.shape[1] == cap
+        out = {k: torch.empty((b, cap), dtype=torch.int32, device=dev) for k in ("match12_left", "match12_right", "match21")}
+        out["nmatches"] = torch.empty((b,), dtype=torch.int32, device=dev)
+        p = lambda t: t.data_ptr() if t is not None else None
+        s1, s2 = ORBmatcher._fv_struct(fv1), ORBmatcher._fv_struct(fv2)
+        rc = _lib.lib().orbm_search_by_bow_rig(kps1.data_ptr(), desc1.data_ptr(), n1.data_ptr(), p(valid1), s1,
+                                               kps2.data_ptr(), desc2.data_ptr(), n2.data_ptr(), nleft2.data_ptr(), s2,
+                                               cap, ns, b, float(nn_ratio), int(bool(check_orientation)),
+                                               out["match12_left"].data_ptr(), out["match12_right"].data_ptr(),
+                                               out["match21"].data_ptr(), out["nmatches"].data_ptr(), _stream(dev))
+        _lib.check(rc, "orbm_search_by_bow_rig")
         return out
 
     @staticmethod
