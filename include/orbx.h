@@ -539,6 +539,39 @@ int orbm_search_by_bow_rig(const orbx_keypoint* d_kps1, const uint8_t* d_desc1, 
                            int32_t* d_match12_left, int32_t* d_match12_right, int32_t* d_match21,
                            int32_t* d_nmatches, void* stream);
 
+/* ORBmatcher::SearchForTriangulation between two keyframes of a two-camera rig (mpCamera2 != NULL;
+ * ORBmatcher.cc:907-1146 with the camera selection :1036-1062), batched over keyframe pairs.  Features
+ * are numbered left camera first (d_nleft* = NLeft).  d_rig_pose[p][4][12] = (R12 row-major, t12) of
+ * (Tll, Tlr, Trl, Trr) (:929-937, host geometry); cams1 / cams2 = {mpCamera, mpCamera2} of KF1 / KF2
+ * (KannalaBrandt8).  No mvuRight stereo and no epipole gate exist in this case (:973, :1022), so
+ * only_stereo != 0 returns no matches; every candidate passes KannalaBrandt8::epipolarConstrain
+ * (KannalaBrandt8.cpp:216-220, 306-375) with level_sigma2_1[kp1.octave] / level_sigma2_2[kp2.octave]
+ * unless `coarse`.  That gate is floating-point triangulation: tolerance contract of DESIGN.md §2
+ * (fp32 rays in source order, fp64 Jacobi null vector), not bit parity. */
+int orbm_search_for_triangulation_rig(
+    const orbx_keypoint* d_kps1, const uint8_t* d_desc1, const int32_t* d_n1, const int32_t* d_nleft1,
+    const uint8_t* d_has_mp1, const orbm_feature_vector* fv1, const orbx_keypoint* d_kps2,
+    const uint8_t* d_desc2, const int32_t* d_n2, const int32_t* d_nleft2, const uint8_t* d_has_mp2,
+    const orbm_feature_vector* fv2, int kp_stride, int node_stride, int batch, const float* d_rig_pose,
+    const orbm_camera* cams1, const orbm_camera* cams2, const float* level_sigma2_1_host,
+    const float* level_sigma2_2_host, int nlevels, int only_stereo, int coarse, int check_orientation,
+    int32_t* d_match12, int32_t* d_nmatches, void* stream);
+
+/* Frame::ComputeStereoFishEyeMatches (Frame.cc:1126-1166), batched over rig frames: knnMatch(k=2) of the
+ * lapping-area keypoints (indices >= d_mono_l / d_mono_r = the monoIndex the two extractors returned,
+ * Frame.cc:1063-1067), Lowe ratio 0.7, KannalaBrandt8::TriangulateMatches with (mRlr, mtlr) and
+ * mvLevelSigma2.  Outputs in each camera's numbering: d_left_to_right = mvLeftToRightMatch,
+ * d_right_to_left = mvRightToLeftMatch (rows of kp_stride, -1 = none), d_depth = mvDepth (-1),
+ * d_p3d[..][3] = mvStereo3Dpoints.  The triangulation carries the tolerance contract of
+ * orbm_search_for_triangulation_rig. */
+int orbm_stereo_fisheye_matches(const orbx_keypoint* d_kps_l, const uint8_t* d_desc_l, const int32_t* d_n_l,
+                                const int32_t* d_mono_l, const orbx_keypoint* d_kps_r,
+                                const uint8_t* d_desc_r, const int32_t* d_n_r, const int32_t* d_mono_r,
+                                int kp_stride, int batch, const orbm_camera* cam_l,
+                                const orbm_camera* cam_r, const float* Rlr_host, const float* tlr_host,
+                                const float* level_sigma2_host, int nlevels, int32_t* d_left_to_right,
+                                int32_t* d_right_to_left, float* d_depth, float* d_p3d, void* stream);
+
 /* Library / build identification. */
 const char* orbx_version(void);
 const char* orbx_last_error(void);

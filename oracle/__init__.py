@@ -544,6 +544,30 @@ def search_by_projection_rig(mode, kps_l, desc_l, kps_r, desc_r, bounds, q, nn_r
     return o
 
 
+def search_for_triangulation_rig(kps1, desc1, fv1, kps2, desc2, fv2, gate, only_stereo=False, coarse=False,
+                                 check_orientation=True, has_mp1=None, has_mp2=None):
+    """SearchForTriangulation on a two-camera rig; gate [n1,n2] u8 = epipolarConstrain outcome per pair (evaluated by
+    the caller).  Returns (match12, nmatches)."""
+    kps1, kps2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+    d1, d2 = np.ascontiguousarray(desc1, np.uint8), np.ascontiguousarray(desc2, np.uint8)
+    a, b = _fv_args(fv1), _fv_args(fv2)
+    g = np.ascontiguousarray(gate, np.uint8)
+    h1 = None if has_mp1 is None else np.ascontiguousarray(has_mp1, np.uint8)
+    h2 = None if has_mp2 is None else np.ascontiguousarray(has_mp2, np.uint8)
+    pp = lambda x: None if x is None else _p(x)
+    m12 = np.zeros(kps1.size, np.int32)
+    L = lib()
+    L.oracle_search_for_triangulation_rig.restype = C.c_int
+    L.oracle_search_for_triangulation_rig.argtypes = ([C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                       C.c_void_p, C.c_int] * 2) + [C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                                                                    C.c_void_p]
+    nm = L.oracle_search_for_triangulation_rig(_p(kps1), _p(d1), kps1.size, pp(h1), _p(a[0]), _p(a[1]), _p(a[2]),
+                                               a[0].size, _p(kps2), _p(d2), kps2.size, pp(h2), _p(b[0]), _p(b[1]),
+                                               _p(b[2]), b[0].size, _p(g), int(bool(only_stereo)), int(bool(coarse)),
+                                               int(bool(check_orientation)), _p(m12))
+    return m12, nm
+
+
 def bench_extract(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, lap, threads, flags=0):
     """Times the oracle over frames[n,h,w]; returns (seconds, total keypoints)."""
     frames = np.ascontiguousarray(frames, np.uint8)

@@ -452,4 +452,62 @@ int oracle_search_by_projection_rig(int mode, const void* kps_l_v, const uint8_t
   return nmatches;
 }
 
+// ORBmatcher::SearchForTriangulation between two keyframes of a two-camera rig (mpCamera2 != NULL), ORBmatcher.cc:907-1146.
+// bStereo1 / bStereo2 are false when mpCamera2 is set (:973, :998), so bOnlyStereo skips every feature and the epipole
+// gate (:1022-1030, needs !pKF1->mpCamera2) never applies.  The geometric gate pCamera1->epipolarConstrain(...) of the
+// camera combination chosen at :1036-1062 is floating-point triangulation (KannalaBrandt8.cpp:306-375, Eigen JacobiSVD)
+// and is NOT restated here: the caller supplies its outcome per (idx1, idx2) in gate[n1][n2] (the tests evaluate it in
+// fp64 numpy), so this function pins the loop logic only — skips, `dist>TH_LOW || dist>bestDist`, last minimum wins,
+// rotation histogram.
+int oracle_search_for_triangulation_rig(const void* kps1_v, const uint8_t* desc1, int n1, const uint8_t* has_mp1,
+                                        const int* fv1_node, const int* fv1_off, const int* fv1_idx, int nn1,
+                                        const void* kps2_v, const uint8_t* desc2, int n2, const uint8_t* has_mp2,
+                                        const int* fv2_node, const int* fv2_off, const int* fv2_idx, int nn2,
+                                        const uint8_t* gate, int only_stereo, int coarse, int check_orientation,
+                                        int* match12) {
+  const KeyPoint* kps1 = (const KeyPoint*)kps1_v;
+  const KeyPoint* kps2 = (const KeyPoint*)kps2_v;
+  const int TH_LOW = 50, HISTO_LENGTH = 30;
+  for (int i = 0; i < n1; i++) match12[i] = -1;
+  std::vector<int> rotHist[30];
+  int nmatches = 0, a = 0, b = 0;
+  while (a < nn1 && b < nn2) {
+    if (fv1_node[a] == fv2_node[b]) {
+      for (int i1 = fv1_off[a]; i1 < fv1_off[a + 1]; i1++) {
+        const int idx1 = fv1_idx[i1];
+        if (has_mp1 && has_mp1[idx1]) continue;
+        const bool bStereo1 = false;
+        if (only_stereo && !bStereo1) continue;
+        int bestDist = TH_LOW, bestIdx2 = -1;
+        for (int i2 = fv2_off[b]; i2 < fv2_off[b + 1]; i2++) {
+          const int idx2 = fv2_idx[i2];
+          if (has_mp2 && has_mp2[idx2]) continue;  // vbMatched2 is never set in the reference
+          const int dist = HammingDistance(desc1 + (size_t)idx1 * 32, desc2 + (size_t)idx2 * 32);
+          if (dist > TH_LOW || dist > bestDist) continue;
+          if (coarse || gate[(size_t)idx1 * n2 + idx2]) { bestIdx2 = idx2; bestDist = dist; }
+        }
+        if (bestIdx2 >= 0) {
+          match12[idx1] = bestIdx2;
+          nmatches++;
+          if (check_orientation) rotHist[RotBin(kps1[idx1].angle, kps2[bestIdx2].angle)].push_back(idx1);
+        }
+      }
+      a++; b++;
+    } else if (fv1_node[a] < fv2_node[b]) {
+      a = (int)(std::lower_bound(fv1_node, fv1_node + nn1, fv2_node[b]) - fv1_node);
+    } else {
+      b = (int)(std::lower_bound(fv2_node, fv2_node + nn2, fv1_node[a]) - fv2_node);
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    ThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int idx1 : rotHist[i]) { match12[idx1] = -1; nmatches--; }
+    }
+  }
+  return nmatches;
+}
+
 }  // extern "C"

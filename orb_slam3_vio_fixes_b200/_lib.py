@@ -40,7 +40,7 @@ SYMBOLS = [
     "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_search_by_projection_th", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
     "orbm_fuse_candidates", "orbm_descriptor_distance_pairs", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
     "orbm_undistort_keypoints", "orbm_is_in_frustum",
-    "orbm_search_by_projection_rig", "orbm_search_by_bow_rig",
+    "orbm_search_by_projection_rig", "orbm_search_by_bow_rig", "orbm_search_for_triangulation_rig", "orbm_stereo_fisheye_matches",
     "orbm_vocabulary_parse_text", "orbm_vocabulary_save_text", "orbm_vocabulary_host_free", "orbm_vocabulary_upload",
     "orbm_vocabulary_release", "orbm_vocabulary_load_text",
     "orbx_version", "orbx_last_error",
@@ -159,6 +159,11 @@ def lib():
                                                                                                    i32] + [vp] * 7
     L.orbm_search_by_bow_rig.argtypes = [vp, vp, vp, vp, pfv, vp, vp, vp, vp, pfv, i32, i32, i32, f32, i32, vp, vp, vp,
                                          vp, vp]
+    pcam = C.POINTER(OrbmCamera)
+    L.orbm_search_for_triangulation_rig.argtypes = [vp, vp, vp, vp, vp, pfv, vp, vp, vp, vp, vp, pfv, i32, i32, i32, vp,
+                                                    pcam, pcam, vp, vp, i32, i32, i32, i32, vp, vp, vp]
+    L.orbm_stereo_fisheye_matches.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, pcam, pcam, vp, vp, vp, i32, vp,
+                                              vp, vp, vp, vp]
     pvh = C.POINTER(OrbmVocabularyHost)
     L.orbm_vocabulary_parse_text.argtypes = [C.c_char_p, pvh]
     L.orbm_vocabulary_save_text.argtypes = [C.c_char_p, pvh]

@@ -21,6 +21,7 @@
 #include "orbx_kernels.cuh"
 #include "orbx_core.h"
 #include "match_core.cuh"
+#include "tri_core.h"
 
 #define BOW_WARPS 4
 #define FULLMASK 0xffffffffu
@@ -281,6 +282,64 @@ k_tri_nodes(BowSide S1, BowSide S2, TriGeom G, int kp_stride, int node_stride, i
       }
       const uint32_t key = ((uint32_t)dist << 16) | (uint32_t)(0xffff - ((c - o2) & 0xffff));
       k1 = min(k1, key);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) k1 = min(k1, __shfl_xor_sync(FULLMASK, k1, o));
+    if (k1 != KEY_NONE && lane == 0) match12[fb + idx1] = idx2s[o2 + (0xffff - (int)(k1 & 0xffff))];
+  }
+}
+
+// SearchForTriangulation between two keyframes of a two-camera rig (pKF->mpCamera2 != NULL; ORBmatcher.cc:907-1146 with
+// the camera selection :1036-1062): features [0, NLeft) belong to the left camera, the rest to the right one; there is
+// no mvuRight stereo (bStereo1/2 = false, :973,:998: with bOnlyStereo every feature is skipped) and no epipole gate
+// (:1022 needs !mpCamera2); each candidate pair picks (R12, t12, camera of KF1, camera of KF2) from the four
+// left/right combinations and passes KannalaBrandt8::epipolarConstrain (tri_core.h) unless bCoarse.
+struct TriRig {
+  const OrbxRigPose* pose;   // [batch][4]: index 2*bRight1 + bRight2 = (Tll, Tlr, Trl, Trr) as (R12, t12)
+  const int32_t *nleft1, *nleft2;
+  OrbxFrustumCam cam1[2], cam2[2];  // [0] = mpCamera, [1] = mpCamera2 of KF1 / KF2
+  float sigma2_1[ORBX_MAX_LEVELS], sigma2_2[ORBX_MAX_LEVELS];
+  int only_stereo, coarse;
+};
+
+__global__ void __launch_bounds__(BOW_WARPS * 32)
+k_tri_nodes_rig(BowSide S1, BowSide S2, const __grid_constant__ TriRig G, int kp_stride, int node_stride,
+                int32_t* __restrict__ match12) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, p = blockIdx.y;
+  const int a = blockIdx.x;
+  if (a >= S1.fv_nn[p] || G.only_stereo) return;
+  const size_t nb = (size_t)p * node_stride, fb = (size_t)p * kp_stride;
+  const int node = S1.fv_node[nb + a];
+  const int b = bow_find_node(S2.fv_node + nb, S2.fv_nn[p], node);
+  if (b < 0) return;
+  const int o1 = S1.fv_off[nb + p + a], e1 = S1.fv_off[nb + p + a + 1];
+  const int o2 = S2.fv_off[nb + p + b], e2 = S2.fv_off[nb + p + b + 1];
+  const int32_t* idx1s = S1.fv_idx + fb;
+  const int32_t* idx2s = S2.fv_idx + fb;
+  const int nl1 = G.nleft1[p], nl2 = G.nleft2[p];
+  const int TH_LOW = 50;
+  for (int i1 = o1 + warp; i1 < e1; i1 += BOW_WARPS) {
+    const int idx1 = idx1s[i1];
+    if (S1.flag && S1.flag[fb + idx1]) continue;
+    const OrbxKeyPointDev kp1 = S1.kps[fb + idx1];
+    const int right1 = idx1 >= nl1 ? 1 : 0;
+    const Desc256 d1 = load_desc(S1.desc + (fb + idx1) * 32);
+    uint32_t k1 = KEY_NONE;
+    for (int c = o2 + lane; c < e2; c += 32) {
+      const int idx2 = idx2s[c];
+      if (S2.flag && S2.flag[fb + idx2]) continue;
+      const int dist = hamming(d1, load_desc(S2.desc + (fb + idx2) * 32));
+      if (dist > TH_LOW) continue;
+      if (!G.coarse) {
+        const OrbxKeyPointDev kp2 = S2.kps[fb + idx2];
+        const int right2 = idx2 >= nl2 ? 1 : 0;
+        if (!orbx_kb8_epipolar_constrain(G.cam1[right1], G.cam2[right2], kp1.x, kp1.y, kp2.x, kp2.y,
+                                         G.pose[(size_t)p * 4 + 2 * right1 + right2], G.sigma2_1[kp1.octave],
+                                         G.sigma2_2[kp2.octave]))
+          continue;
+      }
+      const uint32_t key = ((uint32_t)dist << 16) | (uint32_t)(0xffff - ((c - o2) & 0xffff));
+      k1 = min(k1, key);  // dist <= bestDist: the last minimum wins (:1017)
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) k1 = min(k1, __shfl_xor_sync(FULLMASK, k1, o));
@@ -623,6 +682,48 @@ extern "C" int orbm_search_for_triangulation(
   k_tri_nodes<<<grd, BOW_WARPS * 32, 0, st>>>(S1, S2, G, kp_stride, node_stride, d_match12);
   k_bow_rot<<<batch, 256, 0, st>>>(S1.kps, S2.kps, d_n1, kp_stride, check_orientation, d_match12, nullptr,
                                    d_nmatches);
+  return cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
+}
+
+static OrbxFrustumCam to_cam(const orbm_camera& c) {
+  OrbxFrustumCam o;
+  o.model = c.model; o.fx = c.fx; o.fy = c.fy; o.cx = c.cx; o.cy = c.cy;
+  for (int i = 0; i < 4; i++) o.k[i] = c.k[i];
+  return o;
+}
+
+extern "C" int orbm_search_for_triangulation_rig(
+    const orbx_keypoint* d_kps1, const uint8_t* d_desc1, const int32_t* d_n1, const int32_t* d_nleft1,
+    const uint8_t* d_has_mp1, const orbm_feature_vector* fv1, const orbx_keypoint* d_kps2, const uint8_t* d_desc2,
+    const int32_t* d_n2, const int32_t* d_nleft2, const uint8_t* d_has_mp2, const orbm_feature_vector* fv2,
+    int kp_stride, int node_stride, int batch, const float* d_rig_pose, const orbm_camera* cams1,
+    const orbm_camera* cams2, const float* level_sigma2_1_host, const float* level_sigma2_2_host, int nlevels,
+    int only_stereo, int coarse, int check_orientation, int32_t* d_match12, int32_t* d_nmatches, void* stream) {
+  if (!d_kps1 || !d_desc1 || !d_n1 || !d_nleft1 || !fv_ok(fv1) || !d_kps2 || !d_desc2 || !d_n2 || !d_nleft2 ||
+      !fv_ok(fv2) || kp_stride < 1 || node_stride < 1 || batch < 1 || (!coarse && (!d_rig_pose || !cams1 || !cams2)) ||
+      !level_sigma2_1_host || !level_sigma2_2_host || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !d_match12 ||
+      !d_nmatches)
+    return ORBX_E_INVALID;
+  TriRig G;
+  memset(&G, 0, sizeof(G));
+  if (!coarse)
+    for (int i = 0; i < 2; i++) {
+      if (cams1[i].model != 1 || cams2[i].model != 1) return ORBX_E_INVALID;  // rigs are KannalaBrandt8 pairs (Settings.cc)
+      G.cam1[i] = to_cam(cams1[i]); G.cam2[i] = to_cam(cams2[i]);
+    }
+  G.pose = (const OrbxRigPose*)d_rig_pose; G.nleft1 = d_nleft1; G.nleft2 = d_nleft2;
+  G.only_stereo = only_stereo; G.coarse = coarse;
+  for (int l = 0; l < ORBX_MAX_LEVELS; l++) {
+    G.sigma2_1[l] = l < nlevels ? level_sigma2_1_host[l] : 0.f;
+    G.sigma2_2[l] = l < nlevels ? level_sigma2_2_host[l] : 0.f;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(d_match12, 0xff, (size_t)batch * kp_stride * sizeof(int32_t), st);
+  const BowSide S1 = make_side(d_kps1, d_desc1, d_n1, d_has_mp1, nullptr, fv1);
+  const BowSide S2 = make_side(d_kps2, d_desc2, d_n2, d_has_mp2, nullptr, fv2);
+  dim3 grd(node_stride, batch);
+  k_tri_nodes_rig<<<grd, BOW_WARPS * 32, 0, st>>>(S1, S2, G, kp_stride, node_stride, d_match12);
+  k_bow_rot<<<batch, 256, 0, st>>>(S1.kps, S2.kps, d_n1, kp_stride, check_orientation, d_match12, nullptr, d_nmatches);
   return cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
 }
 

@@ -194,3 +194,94 @@ cudaError_t orbx_launch_rgbd_depth(const OrbxKeyPointDev* kps, const OrbxKeyPoin
                                     depth);
   return cudaGetLastError();
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1126-1166): brute-force knnMatch(k=2) between the lapping-area
+// keypoints of the two fisheye images (cv::BFMatcher(NORM_HAMMING), ties to the lower train index), Lowe ratio 0.7,
+// KannalaBrandt8::TriangulateMatches (tri_core.h) -> mvLeftToRightMatch, mvRightToLeftMatch, mvStereo3Dpoints, mvDepth.
+// One warp per left keypoint; the reference's loop runs in ascending left index and simply overwrites
+// mvRightToLeftMatch[train], so the last (largest) left index wins: atomicMax.
+// ---------------------------------------------------------------------------------------------------------
+#include "match_core.cuh"
+#include "tri_core.h"
+
+struct FishEyeArgs {
+  const OrbxKeyPointDev *kl, *kr;
+  const uint8_t *dl, *dr;
+  const int32_t *nl, *nr, *mono_l, *mono_r;
+  int kp_stride;
+  OrbxFrustumCam cam_l, cam_r;
+  OrbxRigPose Tlr;
+  float sigma2[ORBX_MAX_LEVELS];
+  int32_t *l2r, *r2l;
+  float *depth, *p3d;
+};
+
+__global__ void __launch_bounds__(SR_WARPS * 32)
+k_fisheye_init(const __grid_constant__ FishEyeArgs A) {
+  const int f = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A.kp_stride) return;
+  const size_t o = (size_t)f * A.kp_stride + i;
+  A.l2r[o] = -1; A.r2l[o] = -1; A.depth[o] = -1.0f;
+  A.p3d[3 * o] = 0.f; A.p3d[3 * o + 1] = 0.f; A.p3d[3 * o + 2] = 0.f;
+}
+
+__global__ void __launch_bounds__(SR_WARPS * 32)
+k_fisheye_matches(const __grid_constant__ FishEyeArgs A) {
+  const int lane = threadIdx.x & 31, f = blockIdx.y;
+  const int nl = A.nl[f], nr = A.nr[f], ml = A.mono_l[f], mr = A.mono_r[f];
+  const int qi = ml + blockIdx.x * SR_WARPS + (threadIdx.x >> 5);
+  if (qi >= nl) return;
+  const size_t fb = (size_t)f * A.kp_stride;
+  const Desc256 dq = load_desc(A.dl + (fb + qi) * 32);
+  Top2 t;
+  for (int j = mr + lane; j < nr; j += 32) {
+    const int d = hamming(dq, load_desc(A.dr + (fb + j) * 32));
+    t.push(((uint32_t)d << 20) | (uint32_t)j, j);
+  }
+  warp_top2(t);
+  if (lane != 0 || t.i2 < 0) return;  // (*it).size() >= 2
+  const float d0 = (float)(t.k1 >> 20), d1 = (float)(t.k2 >> 20);
+  if (!((double)d0 < d_mul((double)d1, 0.7))) return;  // float * double literal
+  const OrbxKeyPointDev kl = A.kl[fb + qi], kr = A.kr[fb + t.i1];
+  float p[3];
+  const float depth = orbx_kb8_triangulate_matches(A.cam_l, A.cam_r, kl.x, kl.y, kr.x, kr.y, A.Tlr, A.sigma2[kl.octave],
+                                                   A.sigma2[kr.octave], p);
+  if (depth > 0.0001f) {
+    A.l2r[fb + qi] = t.i1;
+    atomicMax(&A.r2l[fb + t.i1], qi);
+    A.p3d[3 * (fb + qi)] = p[0]; A.p3d[3 * (fb + qi) + 1] = p[1]; A.p3d[3 * (fb + qi) + 2] = p[2];
+    A.depth[fb + qi] = depth;
+  }
+}
+
+extern "C" int orbm_stereo_fisheye_matches(const orbx_keypoint* d_kps_l, const uint8_t* d_desc_l, const int32_t* d_n_l,
+                                           const int32_t* d_mono_l, const orbx_keypoint* d_kps_r,
+                                           const uint8_t* d_desc_r, const int32_t* d_n_r, const int32_t* d_mono_r,
+                                           int kp_stride, int batch, const orbm_camera* cam_l, const orbm_camera* cam_r,
+                                           const float* Rlr_host, const float* tlr_host,
+                                           const float* level_sigma2_host, int nlevels, int32_t* d_left_to_right,
+                                           int32_t* d_right_to_left, float* d_depth, float* d_p3d, void* stream) {
+  if (!d_kps_l || !d_desc_l || !d_n_l || !d_mono_l || !d_kps_r || !d_desc_r || !d_n_r || !d_mono_r || kp_stride < 1 ||
+      batch < 1 || !cam_l || !cam_r || cam_l->model != 1 || cam_r->model != 1 || !Rlr_host || !tlr_host ||
+      !level_sigma2_host || nlevels < 1 || nlevels > ORBX_MAX_LEVELS || !d_left_to_right || !d_right_to_left ||
+      !d_depth || !d_p3d)
+    return ORBX_E_INVALID;
+  FishEyeArgs A;
+  A.kl = (const OrbxKeyPointDev*)d_kps_l; A.kr = (const OrbxKeyPointDev*)d_kps_r; A.dl = d_desc_l; A.dr = d_desc_r;
+  A.nl = d_n_l; A.nr = d_n_r; A.mono_l = d_mono_l; A.mono_r = d_mono_r; A.kp_stride = kp_stride;
+  const orbm_camera* cs[2] = {cam_l, cam_r};
+  OrbxFrustumCam* os[2] = {&A.cam_l, &A.cam_r};
+  for (int c = 0; c < 2; c++) {
+    os[c]->model = 1; os[c]->fx = cs[c]->fx; os[c]->fy = cs[c]->fy; os[c]->cx = cs[c]->cx; os[c]->cy = cs[c]->cy;
+    for (int i = 0; i < 4; i++) os[c]->k[i] = cs[c]->k[i];
+  }
+  for (int i = 0; i < 9; i++) A.Tlr.R[i] = Rlr_host[i];
+  for (int i = 0; i < 3; i++) A.Tlr.t[i] = tlr_host[i];
+  for (int l = 0; l < ORBX_MAX_LEVELS; l++) A.sigma2[l] = l < nlevels ? level_sigma2_host[l] : 0.f;
+  A.l2r = d_left_to_right; A.r2l = d_right_to_left; A.depth = d_depth; A.p3d = d_p3d;
+  cudaStream_t st = (cudaStream_t)stream;
+  k_fisheye_init<<<dim3((kp_stride + SR_WARPS * 32 - 1) / (SR_WARPS * 32), batch), SR_WARPS * 32, 0, st>>>(A);
+  k_fisheye_matches<<<dim3((kp_stride + SR_WARPS - 1) / SR_WARPS, batch), SR_WARPS * 32, 0, st>>>(A);
+  return cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
+}

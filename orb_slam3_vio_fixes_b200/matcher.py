@@ -250,6 +250,30 @@ class ORBmatcher:
         return out
 
     @staticmethod
+    def stereo_fisheye_matches(kps_l, desc_l, n_l, mono_l, kps_r, desc_r, n_r, mono_r, cam_l, cam_r, Rlr, tlr,
+                               level_sigma2):
+        """Frame::ComputeStereoFishEyeMatches (Frame.cc:1126-1166).  mono_* [B] i32 = the extractors' monoIndex.
+        Returns dict(left_to_right, right_to_left [B,cap] i32, depth [B,cap] f32, p3d [B,cap,3] f32)."""
+        import ctypes as C
+        import torch
+        b, cap = kps_l.shape[0], kps_l.shape[1]
+        dev = kps_l.device
+        out = {"left_to_right": torch.empty((b, cap), dtype=torch.int32, device=dev),
+               "right_to_left": torch.empty((b, cap), dtype=torch.int32, device=dev),
+               "depth": torch.empty((b, cap), dtype=torch.float32, device=dev),
+               "p3d": torch.empty((b, cap, 3), dtype=torch.float32, device=dev)}
+        R = np.ascontiguousarray(Rlr, np.float32).reshape(9)
+        t = np.ascontiguousarray(tlr, np.float32).reshape(3)
+        sg = np.ascontiguousarray(level_sigma2, np.float32)
+        rc = _lib.lib().orbm_stereo_fisheye_matches(
+            kps_l.data_ptr(), desc_l.data_ptr(), n_l.data_ptr(), mono_l.data_ptr(), kps_r.data_ptr(), desc_r.data_ptr(),
+            n_r.data_ptr(), mono_r.data_ptr(), cap, b, C.byref(cam_l), C.byref(cam_r), R.ctypes.data, t.ctypes.data,
+            sg.ctypes.data, sg.size, out["left_to_right"].data_ptr(), out["right_to_left"].data_ptr(),
+            out["depth"].data_ptr(), out["p3d"].data_ptr(), _stream(dev))
+        _lib.check(rc, "orbm_stereo_fisheye_matches")
+        return out
+
+    @staticmethod
     def rgbd_depth(kps, n, depth_img, mbf, kps_un=None):
         """Frame::ComputeStereoFromRGBD (Frame.cc:984-1005).  depth_img: float32 CUDA tensor [B,h,w].
         Returns (u_right, depth) [B,cap] f32."""
@@ -334,6 +358,33 @@ class ORBmatcher:
                                                out["match12_left"].data_ptr(), out["match12_right"].data_ptr(),
                                                out["match21"].data_ptr(), out["nmatches"].data_ptr(), _stream(dev))
         _lib.check(rc, "orbm_search_by_bow_rig")
+        return out
+
+    @staticmethod
+    def search_for_triangulation_rig(kps1, desc1, n1, nleft1, fv1, kps2, desc2, n2, nleft2, fv2, rig_pose, cams1, cams2,
+                                     level_sigma2_1, level_sigma2_2, only_stereo=False, coarse=False,
+                                     check_orientation=True, has_mp1=None, has_mp2=None):
+        """ORBmatcher::SearchForTriangulation for keyframes of a two-camera rig (ORBmatcher.cc:907-1146, camera selection
+        :1036-1062, KannalaBrandt8::epipolarConstrain).  rig_pose [B,4,12] f32 CUDA = (R12,t12) of Tll,Tlr,Trl,Trr;
+        cams1 / cams2 = 2-tuples of frame.camera(KANNALA_BRANDT8, ...).  Returns dict(match12 [B,cap], nmatches [B])."""
+        import torch
+        b, cap = kps1.shape[0], kps1.shape[1]
+        dev = kps1.device
+        ns = fv1["node"].shape[1]
+        out = {"match12": torch.empty((b, cap), dtype=torch.int32, device=dev),
+               "nmatches": torch.empty((b,), dtype=torch.int32, device=dev)}
+        p = lambda t: t.data_ptr() if t is not None else None
+        s1, s2 = ORBmatcher._fv_struct(fv1), ORBmatcher._fv_struct(fv2)
+        c1 = (_lib.OrbmCamera * 2)(*cams1)
+        c2 = (_lib.OrbmCamera * 2)(*cams2)
+        g1 = np.ascontiguousarray(level_sigma2_1, np.float32)
+        g2 = np.ascontiguousarray(level_sigma2_2, np.float32)
+        rc = _lib.lib().orbm_search_for_triangulation_rig(
+            kps1.data_ptr(), desc1.data_ptr(), n1.data_ptr(), nleft1.data_ptr(), p(has_mp1), s1, kps2.data_ptr(),
+            desc2.data_ptr(), n2.data_ptr(), nleft2.data_ptr(), p(has_mp2), s2, cap, ns, b, rig_pose.data_ptr(), c1, c2,
+            g1.ctypes.data, g2.ctypes.data, g1.size, int(bool(only_stereo)), int(bool(coarse)),
+            int(bool(check_orientation)), out["match12"].data_ptr(), out["nmatches"].data_ptr(), _stream(dev))
+        _lib.check(rc, "orbm_search_for_triangulation_rig")
         return out
 
     @staticmethod

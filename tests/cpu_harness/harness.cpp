@@ -11,6 +11,7 @@
 #include "orbx_core.h"
 #include "orbx_plan.h"
 #include "frame_core.h"
+#include "tri_core.h"
 
 extern "C" {
 
@@ -182,6 +183,20 @@ void h_in_frustum(const float* pos, const float* normal, const float* min_dist, 
     in_view[i] = (uint8_t)o.in_view; proj_x[i] = o.proj_x; proj_y[i] = o.proj_y; proj_xr[i] = o.proj_xr;
     depth[i] = o.depth; view_cos[i] = o.view_cos; level[i] = (int8_t)o.level;
   }
+}
+
+// tri_core.h for the host: KannalaBrandt8::epipolarConstrain on n keypoint pairs (cam = fx,fy,cx,cy,k0..k3)
+void h_kb8_epipolar(const float* cam1, const float* cam2, const float* uv1, const float* uv2, int n, const float* pose12,
+                    const float* sigma1, const float* sigma2, uint8_t* out) {
+  OrbxFrustumCam C1, C2;
+  C1.model = C2.model = 1;
+  C1.fx = cam1[0]; C1.fy = cam1[1]; C1.cx = cam1[2]; C1.cy = cam1[3];
+  C2.fx = cam2[0]; C2.fy = cam2[1]; C2.cx = cam2[2]; C2.cy = cam2[3];
+  for (int i = 0; i < 4; i++) { C1.k[i] = cam1[4 + i]; C2.k[i] = cam2[4 + i]; }
+  OrbxRigPose T; memcpy(&T, pose12, sizeof(T));
+  for (int i = 0; i < n; i++)
+    out[i] = orbx_kb8_epipolar_constrain(C1, C2, uv1[2 * i], uv1[2 * i + 1], uv2[2 * i], uv2[2 * i + 1], T, sigma1[i],
+                                         sigma2[i]) ? 1 : 0;
 }
 
 void h_fast_atan2(const float* y, const float* x, float* out, int n) {
