@@ -111,3 +111,196 @@ def test_cpp_bow_helpers_match_oracle(oracle_mod, tmp_path):
     pairs = np.fromfile(tmp_path / "o.tri_pairs", np.int32).reshape(-1, 2)
     ref = np.stack([np.nonzero(t12 >= 0)[0], t12[t12 >= 0]], 1)
     assert np.array_equal(pairs, ref)
+
+
+def test_cpp_orbmatcher_class(oracle_mod, tmp_path):
+    """include/orbx_compat/ORBmatcher.h: ORBmatcherT<Frame, KeyFrame, MapPoint> with the reference's method names and
+    arguments (include/ORBmatcher.h:40-87) on stand-in object types (tests/cpp/compat_matcher.cpp), against the oracle:
+    SearchByProjection (MapPoints: single camera and fisheye rig; last frame), SearchByBoW (KF-Frame, KF-rig Frame,
+    KF-KF), SearchForTriangulation, SearchForInitialization."""
+    exe = _build_exe(tmp_path, "compat_matcher")
+    rng = np.random.default_rng(101)
+    f32 = np.float32
+    sf = np.cumprod([1.0] + [1.2] * 7).astype(f32)   # mvScaleFactors as ORBextractor builds them is close enough here:
+    orc = oracle_mod.Extractor(1000)
+    sf = np.asarray(orc.scale_factors, f32)
+    sig = (sf * sf).astype(f32)
+    blob = []
+    w = lambda a, dt: blob.append(np.ascontiguousarray(a, dt).tobytes())
+
+    def w_points(P):
+        M = len(P["inView"])
+        w([M], np.int32)
+        w(np.stack([P["projX"], P["projY"], P["projXR"], P["projYR"], P["viewCos"], P["viewCosR"], P["depth"],
+                    P["pos"][:, 0], P["pos"][:, 1], P["pos"][:, 2]], 1), f32)
+        w(np.stack([P["inView"], P["inViewR"], P["level"], P["levelR"], P["bad"], P["nObs"]], 1), np.int32)
+        w(P["desc"], np.uint8)
+
+    def w_feats(k, d):
+        w([len(k)], np.int32); blob.append(np.ascontiguousarray(k).tobytes()); w(d, np.uint8)
+
+    def w_fv(fv, n):
+        idx = np.zeros(n, np.int32); idx[:len(fv[2])] = fv[2]
+        w([len(fv[0])], np.int32); w(fv[0], np.int32); w(fv[1], np.int32); w(idx, np.int32)
+
+    def points_from(kq, dq, shift, right_dx=None):
+        M = len(kq)
+        P = dict(projX=(kq["x"] + f32(shift[0])).astype(f32), projY=(kq["y"] + f32(shift[1])).astype(f32),
+                 viewCos=np.where(rng.random(M) < 0.5, f32(0.9995), f32(0.9)).astype(f32),
+                 viewCosR=np.where(rng.random(M) < 0.5, f32(0.9995), f32(0.9)).astype(f32),
+                 depth=(rng.random(M) * 50).astype(f32), level=kq["octave"].astype(np.int32),
+                 inView=(rng.random(M) < 0.9).astype(np.int32), bad=(rng.random(M) < 0.05).astype(np.int32),
+                 nObs=rng.integers(0, 3, M).astype(np.int32), desc=dq, pos=np.zeros((M, 3), f32))
+        if right_dx is None:
+            P["projXR"] = (P["projX"] - f32(24.0) + rng.normal(0, 3, M)).astype(f32)
+            P["projYR"] = P["projY"].copy()
+            P["inViewR"] = np.zeros(M, np.int32)
+            P["levelR"] = np.full(M, -1, np.int32)
+        else:
+            P["projXR"] = (P["projX"] + f32(right_dx) + rng.normal(0, 1.5, M)).astype(f32)
+            P["projYR"] = (P["projY"] + rng.normal(0, 1.0, M)).astype(f32)
+            P["inViewR"] = (rng.random(M) < 0.85).astype(np.int32)
+            P["levelR"] = np.where(rng.random(M) < 0.9, kq["octave"], -1).astype(np.int32)
+        return P
+
+    def holders(n, M, frac):
+        return np.where(rng.random(n) < frac, rng.integers(0, M, n), -1).astype(np.int32)
+
+    radius = lambda vc, th: np.where(vc.astype(np.float64) > 0.998, f32(2.5), f32(4.0)).astype(f32) * f32(th)
+
+    w(sf, f32); w(sig, f32)
+    bounds = (0.0, 752.0, 0.0, 480.0)
+    w(bounds, f32)
+    frames = S.make_frames("C1", 4)
+    feats = [oracle_mod.Extractor(1000).extract(f, (0, 0))[:2] for f in frames]
+    pos = np.array([S.frame_shift(t) for t in range(4)], f32)
+    exp = {}
+
+    # 1. SearchByProjection(F, MapPoints, th=3, bFarPoints, thFar=40), single camera
+    kF, dF = feats[0]
+    kq = np.concatenate([feats[s][0] for s in (1, 2, 3)]); dq = np.concatenate([feats[s][1] for s in (1, 2, 3)])
+    shifts = np.concatenate([np.tile(pos[s] - pos[0], (len(feats[s][0]), 1)) for s in (1, 2, 3)])
+    P = points_from(kq, dq, (0, 0)); P["projX"] = (kq["x"] + shifts[:, 0]).astype(f32); P["projY"] = (kq["y"] + shifts[:, 1]).astype(f32)
+    uR = np.where(rng.random(len(kF)) < 0.7, kF["x"] - f32(24.0), f32(-1)).astype(f32)
+    hold = holders(len(kF), len(kq), 0.15)
+    w_points(P); w_feats(kF, dF); w(uR, f32); w(hold, np.int32)
+    part = (P["inView"] > 0) & ~(P["depth"] > f32(40.0)) & (P["bad"] == 0)
+    q = dict(qx=P["projX"], qy=P["projY"], qr=(radius(P["viewCos"], 3.0) * sf[P["level"]]).astype(f32),
+             qmin=(P["level"] - 1).astype(np.int8), qmax=P["level"].astype(np.int8))
+    flags = (part.astype(np.uint8) | ((P["nObs"] > 0).astype(np.uint8) << 1)).astype(np.uint8)
+    locked = ((hold >= 0) & (P["nObs"][np.maximum(hold, 0)] > 0)).astype(np.uint8)
+    _, fq, nm = oracle_mod.search_by_projection(kF, dF, bounds, q["qx"], q["qy"], q["qr"], q["qmin"], q["qmax"], P["desc"], 0,
+                                                0.8, False, u_right=uR, feat_locked=locked, q_ur=P["projXR"], q_flags=flags)
+    exp["proj_mono"] = (np.where(fq >= 0, fq, hold), nm)
+
+    # 2. the same on a rig frame (left / right eye of C2)
+    el, er = oracle_mod.Extractor(1200), oracle_mod.Extractor(1200)
+    kl, dl, _ = el.extract(S.make_frames("C2", 1)[0], (0, 0))
+    kr, dr, _ = er.extract(S.make_frames("C2", 1, right=True)[0], (0, 0))
+    k2, d2, _ = oracle_mod.Extractor(1200).extract(S.make_frames("C2", 2)[1], (0, 0))
+    sh = np.array(S.frame_shift(1), f32) - np.array(S.frame_shift(0), f32)
+    P = points_from(k2, d2, sh, right_dx=-24.0)
+    nl, nr = len(kl), len(kr)
+    hold = holders(nl + nr, len(k2), 0.15)
+    m = int(min(nl, nr) * 0.4)
+    li, ri = rng.permutation(nl)[:m], rng.permutation(nr)[:m]
+    l2r, r2l = np.full(nl, -1, np.int32), np.full(nr, -1, np.int32)
+    l2r[li] = ri; r2l[ri] = li
+    w_points(P); w_feats(kl, dl); w_feats(kr, dr); w(hold, np.int32); w(l2r, np.int32); w(r2l, np.int32)
+    part = ((P["inView"] > 0) | (P["inViewR"] > 0)) & (P["bad"] == 0)
+    flags = ((part & (P["inView"] > 0)).astype(np.uint8) | ((P["nObs"] > 0).astype(np.uint8) << 1) |
+             ((part & (P["inViewR"] > 0) & (P["levelR"] != -1)).astype(np.uint8) << 2)).astype(np.uint8)
+    lvr = np.maximum(P["levelR"], 0)
+    q = dict(qx=P["projX"], qy=P["projY"], qr=(radius(P["viewCos"], 3.0) * sf[P["level"]]).astype(f32),
+             qmin=(P["level"] - 1).astype(np.int8), qmax=P["level"].astype(np.int8),
+             qx_r=P["projXR"], qy_r=P["projYR"], qr_r=(radius(P["viewCosR"], 1.0) * sf[lvr]).astype(f32),
+             qmin_r=(lvr - 1).astype(np.int8), qmax_r=lvr.astype(np.int8), qdesc=P["desc"], flags=flags)
+    locked = ((hold >= 0) & (P["nObs"][np.maximum(hold, 0)] > 0)).astype(np.uint8)
+    o = oracle_mod.search_by_projection_rig(0, kl, dl, kr, dr, bounds, q, 0.8, False, locked_l=locked[:nl],
+                                            locked_r=locked[nl:], l2r=l2r, r2l=r2l)
+    fq = np.concatenate([o["feat_query_l"], o["feat_query_r"]])
+    exp["proj_rig"] = (np.where(fq >= 0, fq, hold), o["nmatches"])
+
+    # 3. SearchByProjection(CurrentFrame, LastFrame, 15, bMono=true): pinhole, identity rotation, z = 1
+    (kL, dL), (kC, dC) = feats[0], feats[1]
+    fx, fy, cx, cy = f32(458.654), f32(457.296), f32(367.215), f32(248.375)
+    M = len(kL)
+    shv = pos[0] - pos[1]
+    Pm = points_from(kL, dL, (0, 0))
+    Pm["pos"] = np.stack([(kL["x"] - cx) / fx, (kL["y"] - cy) / fy, np.ones(M, f32)], 1).astype(f32)
+    t = np.array([shv[0] / fx, shv[1] / fy, 0], f32)
+    X = (Pm["pos"][:, 0] + t[0]).astype(f32); Y = (Pm["pos"][:, 1] + t[1]).astype(f32)
+    u = ((fx * X).astype(f32) + cx).astype(f32); v = ((fy * Y).astype(f32) + cy).astype(f32)
+    holdL = np.where(rng.random(M) < 0.8, np.arange(M), -1).astype(np.int32)
+    outl = (rng.random(M) < 0.05).astype(np.int32)
+    holdC = holders(len(kC), M, 0.1)
+    uRC = np.where(rng.random(len(kC)) < 0.5, kC["x"] - f32(24.0), f32(-1)).astype(f32)
+    mbf = f32(47.9)
+    w_points(Pm); w_feats(kC, dC); w(uRC, f32); w(holdC, np.int32); w_feats(kL, dL); w(holdL, np.int32); w(outl, np.int32)
+    w([fx, fy, cx, cy], f32); w(list(np.eye(3).ravel()) + list(t), f32); w(list(np.eye(3).ravel()) + [0, 0, 0], f32)
+    w([0.1, mbf], f32)
+    sel = np.nonzero((holdL >= 0) & (outl == 0) & (u >= f32(bounds[0])) & (u <= f32(bounds[1])) & (v >= f32(bounds[2])) &
+                     (v <= f32(bounds[3])))[0]
+    q = dict(qx=u[sel], qy=v[sel], qr=(f32(15.0) * sf[kL["octave"][sel]]).astype(f32),
+             qmin=(kL["octave"][sel] - 1).astype(np.int8), qmax=(kL["octave"][sel] + 1).astype(np.int8))
+    q_ur = (u[sel] - (mbf * f32(1.0))).astype(f32)
+    flags = (1 | ((Pm["nObs"][sel] > 0).astype(np.uint8) << 1)).astype(np.uint8)
+    lockedC = ((holdC >= 0) & (Pm["nObs"][np.maximum(holdC, 0)] > 0)).astype(np.uint8)
+    args = (kC, dC, bounds, q["qx"], q["qy"], q["qr"], q["qmin"], q["qmax"], dL[sel], 1, 0.9)
+    kw = dict(u_right=uRC, feat_locked=lockedC, q_ur=q_ur, q_flags=flags, q_angle=kL["angle"][sel])
+    _, fq0, _ = oracle_mod.search_by_projection(*args, False, **kw)
+    _, fq1, nm = oracle_mod.search_by_projection(*args, True, **kw)
+    ids = np.where(fq0 >= 0, np.where(fq1 >= 0, sel[np.maximum(fq1, 0)], -1), holdC)
+    exp["proj_last"] = (ids, nm)
+
+    # 4.-6. SearchByBoW x3, SearchForTriangulation
+    (k1, d1), (k2b, d2b) = feats[0], feats[1]
+    voc = S.make_vocabulary(10, 4, seed=5, desc_pool=np.concatenate([d1, d2b]))
+    fv1 = oracle_mod.bow_transform(d1, voc, 2)["fv"]; fv2 = oracle_mod.bow_transform(d2b, voc, 2)["fv"]
+    Mb = 3000
+    Pb = points_from(np.concatenate([k1, k2b, k1])[:Mb], np.concatenate([d1, d2b, d1])[:Mb], (0, 0))
+    h1, h2 = holders(len(k1), Mb, 0.7), holders(len(k2b), Mb, 0.7)
+    u1 = np.where(rng.random(len(k1)) < 0.5, 100.0, -1.0).astype(f32)
+    u2 = np.where(rng.random(len(k2b)) < 0.5, 100.0, -1.0).astype(f32)
+    Fm = np.array([0, -0.01, 0.447, 0.01, 0, -0.894, -0.447, 0.894, 0], f32); ep = np.array([500.0, 300.0], f32)
+    w_points(Pb)
+    for k_, d_, fv_, h_, u_ in ((k1, d1, fv1, h1, u1), (k2b, d2b, fv2, h2, u2)):
+        w_feats(k_, d_); w_fv(fv_, len(k_)); w(h_, np.int32); w(u_, f32)
+    w(np.concatenate([Fm, ep]), f32)
+    v1 = ((h1 >= 0) & (Pb["bad"][np.maximum(h1, 0)] == 0)).astype(np.uint8)
+    v2 = ((h2 >= 0) & (Pb["bad"][np.maximum(h2, 0)] == 0)).astype(np.uint8)
+    _, m21, nm = oracle_mod.search_by_bow(0, k1, d1, fv1, k2b, d2b, fv2, 0.7, True, v1, None)
+    exp["bow_kf_f"] = (np.where(m21 >= 0, h1[np.maximum(m21, 0)], -1), nm)
+    m12, _, nm = oracle_mod.search_by_bow(1, k1, d1, fv1, k2b, d2b, fv2, 0.7, True, v1, v2)
+    exp["bow_kf_kf"] = (np.where(m12 >= 0, h2[np.maximum(m12, 0)], -1), nm)
+    t12, nm = oracle_mod.search_for_triangulation(k1, d1, fv1, k2b, d2b, fv2, Fm, ep, sf, sig, False, False, True,
+                                                  (h1 >= 0).astype(np.uint8), (h2 >= 0).astype(np.uint8), u1, u2)
+    exp["tri_pairs"] = (np.stack([np.nonzero(t12 >= 0)[0], t12[t12 >= 0]], 1).ravel(), nm)
+    dcat = np.concatenate([dl, dr]); kcat = np.concatenate([kl, kr])
+    voc2 = S.make_vocabulary(10, 4, seed=6, desc_pool=np.concatenate([d1, dcat]))
+    fvk = oracle_mod.bow_transform(d1, voc2, 2)["fv"]
+    # (the keyframe's FeatureVector was written for `voc`; the rig frame must share the keyframe's tree, so the rig
+    # frame is transformed with `voc` as well)
+    fvr = oracle_mod.bow_transform(dcat, voc, 2)["fv"]
+    del fvk, voc2
+    w_feats(kl, dl); w_feats(kr, dr); w_fv(fvr, len(kcat))
+    _, _, m21, nm = oracle_mod.search_by_bow_rig(k1, d1, fv1, kcat, dcat, nl, fvr, 0.7, True, valid1=v1)
+    exp["bow_kf_rig"] = (np.where(m21 >= 0, h1[np.maximum(m21, 0)], -1), nm)
+
+    # 7. SearchForInitialization
+    w_feats(k1, d1); w_feats(k2b, d2b)
+    prev = np.stack([k1["x"], k1["y"]], 1)
+    m12, nm, _ = oracle_mod.search_for_initialization(k1, d1, k2b, d2b, bounds, prev, 100, 0.9, True)
+    exp["init_m12"] = (m12, nm)
+
+    (tmp_path / "in.bin").write_bytes(b"".join(blob))
+    out = subprocess.check_output([str(exe), str(tmp_path / "in.bin"), str(tmp_path / "o")], text=True)
+    rets = [int(v) for v in out.split()]
+    order = ["proj_mono", "proj_rig", "proj_last", "bow_kf_f", "bow_kf_kf", "tri_pairs", "bow_kf_rig", "init_m12"]
+    assert len(rets) == len(order)
+    for name, ret in zip(order, rets):
+        want, nm = exp[name]
+        got = np.fromfile(tmp_path / f"o.{name}", np.int32)
+        assert ret == nm, (name, ret, nm)
+        assert np.array_equal(got, want), (name, np.nonzero(got != want)[0][:10])
+        assert nm > 50, (name, nm)
