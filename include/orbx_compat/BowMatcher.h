@@ -48,6 +48,14 @@ struct DevSide {
     cudaFree(fv.d_node); cudaFree(fv.d_off); cudaFree(fv.d_idx); cudaFree(fv.d_nn);
   }
 };
+struct Buf {  // device scratch that frees itself on every path
+  void* p = nullptr;
+  Buf() {}
+  Buf(const Buf&) = delete;
+  Buf& operator=(const Buf&) = delete;
+  ~Buf() { cudaFree(p); }
+  bool alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 1) == cudaSuccess; }
+};
 template <class T>
 inline bool up(void** d, const T* h, size_t count) {
   if (cudaMalloc(d, (count ? count : 1) * sizeof(T)) != cudaSuccess) return false;
@@ -90,8 +98,9 @@ inline int SearchByBoWDevice(int mode, const BowSide& s1, const BowSide& s2, flo
   const int cap = bowdetail::strides(s1, s2, &ns);
   bowdetail::DevSide d1, d2;
   if (!bowdetail::upload(s1, cap, ns, d1) || !bowdetail::upload(s2, cap, ns, d2)) return ORBX_E_CUDA;
-  int32_t *m12 = nullptr, *m21 = nullptr, *nm = nullptr;
-  if (cudaMalloc(&m12, (size_t)cap * 4) || cudaMalloc(&m21, (size_t)cap * 4) || cudaMalloc(&nm, 4)) return ORBX_E_NOMEM;
+  bowdetail::Buf b12, b21, bnm;
+  if (!b12.alloc((size_t)cap * 4) || !b21.alloc((size_t)cap * 4) || !bnm.alloc(4)) return ORBX_E_NOMEM;
+  int32_t *m12 = (int32_t*)b12.p, *m21 = (int32_t*)b21.p, *nm = (int32_t*)bnm.p;
   int rc = orbm_search_by_bow(mode, (const orbx_keypoint*)d1.kps, (const uint8_t*)d1.desc, (const int32_t*)d1.n,
                               (const uint8_t*)d1.flag, &d1.fv, (const orbx_keypoint*)d2.kps, (const uint8_t*)d2.desc,
                               (const int32_t*)d2.n, (const uint8_t*)d2.flag, &d2.fv, cap, ns, 1, nnratio,
@@ -104,7 +113,6 @@ inline int SearchByBoWDevice(int mode, const BowSide& s1, const BowSide& s2, flo
        cudaMemcpy(match21.data(), m21, match21.size() * 4, cudaMemcpyDeviceToHost) ||
        cudaMemcpy(&nmatches, nm, 4, cudaMemcpyDeviceToHost)))
     rc = ORBX_E_CUDA;
-  cudaFree(m12); cudaFree(m21); cudaFree(nm);
   return rc == ORBX_OK ? nmatches : rc;
 }
 
@@ -118,12 +126,13 @@ inline int SearchForTriangulationDevice(const BowSide& s1, const BowSide& s2, co
   const int cap = bowdetail::strides(s1, s2, &ns);
   bowdetail::DevSide d1, d2;
   if (!bowdetail::upload(s1, cap, ns, d1) || !bowdetail::upload(s2, cap, ns, d2)) return ORBX_E_CUDA;
-  int32_t *m12 = nullptr, *nm = nullptr;
-  float *dF = nullptr, *dep = nullptr;
-  if (cudaMalloc(&m12, (size_t)cap * 4) || cudaMalloc(&nm, 4) || cudaMalloc(&dF, 36) || cudaMalloc(&dep, 8))
-    return ORBX_E_NOMEM;
-  cudaMemcpy(dF, F12, 36, cudaMemcpyHostToDevice);
-  cudaMemcpy(dep, ep, 8, cudaMemcpyHostToDevice);
+  bowdetail::Buf b12, bnm, bF, bep;
+  if (!b12.alloc((size_t)cap * 4) || !bnm.alloc(4) || !bF.alloc(36) || !bep.alloc(8)) return ORBX_E_NOMEM;
+  int32_t *m12 = (int32_t*)b12.p, *nm = (int32_t*)bnm.p;
+  float *dF = (float*)bF.p, *dep = (float*)bep.p;
+  if (cudaMemcpy(dF, F12, 36, cudaMemcpyHostToDevice) != cudaSuccess ||
+      cudaMemcpy(dep, ep, 8, cudaMemcpyHostToDevice) != cudaSuccess)
+    return ORBX_E_CUDA;
   int rc = orbm_search_for_triangulation(
       (const orbx_keypoint*)d1.kps, (const uint8_t*)d1.desc, (const int32_t*)d1.n, (const uint8_t*)d1.flag,
       (const float*)d1.ur, &d1.fv, (const orbx_keypoint*)d2.kps, (const uint8_t*)d2.desc, (const int32_t*)d2.n,
@@ -134,7 +143,6 @@ inline int SearchForTriangulationDevice(const BowSide& s1, const BowSide& s2, co
   if (rc == ORBX_OK && (cudaMemcpy(v12.data(), m12, v12.size() * 4, cudaMemcpyDeviceToHost) ||
                         cudaMemcpy(&nmatches, nm, 4, cudaMemcpyDeviceToHost)))
     rc = ORBX_E_CUDA;
-  cudaFree(m12); cudaFree(nm); cudaFree(dF); cudaFree(dep);
   vMatchedPairs.clear();  // :1133-1143
   for (size_t i = 0; i < v12.size(); i++)
     if (v12[i] >= 0) vMatchedPairs.push_back(std::make_pair(i, (size_t)v12[i]));

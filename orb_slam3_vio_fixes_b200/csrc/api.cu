@@ -374,8 +374,12 @@ int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch
   // own disjoint frame slots of the scratch buffers.  Off while per-stage events are being recorded.
   int rc = ensure_streams(h);
   if (rc) return rc;
+  // a sub-batch should still fill the GPU: >= 64 frames of 752x480, fewer of larger frames (3 at 4K)
   int nsplit = h->dev_split;
-  while (nsplit > 1 && batch < 64 * nsplit) nsplit >>= 1;
+  const long long px = (long long)h->plan.width * h->plan.height;
+  long long min_frames = (64LL * 752 * 480 + px - 1) / px;
+  if (min_frames < 1) min_frames = 1;
+  while (nsplit > 1 && batch < min_frames * nsplit) nsplit >>= 1;
   if (h->cfg.flags & ORBX_FLAG_STAGE_TIMING) nsplit = 1;
   const int nstreams = h->dev_streams < nsplit ? h->dev_streams : nsplit;
   if (nsplit <= 1)

@@ -260,3 +260,40 @@ def test_device_sincosf_exhaustive(oracle_mod):
     ref = oracle_mod.sincos_checksum(0, count, chunk)
     bad = np.nonzero(got != ref)[0]
     assert len(bad) == 0, f"{len(bad)} of {n} chunks differ, first chunk {bad[:3]}"
+
+
+def test_two_handles_from_two_threads(oracle_mod):
+    """Frame.cc:122-125 calls the left and right extractor from two std::threads: two handles driven concurrently from
+    two threads of ONE process give the oracle's bytes.  With >= 2 GPUs the second handle lives on device 1 (SURVEY
+    §8(e): one process, explicit cudaSetDevice, one handle per GPU); the per-device cache of the dynamic shared-memory
+    opt-in (orbx_ensure_dyn_smem) is what this exercises there — 5000 features need > 48 KB in k_octree."""
+    import threading
+    import torch
+    ndev = torch.cuda.device_count()
+    frames = [S.make_frames("C2", 3), S.make_frames("C2", 3, right=True)]
+    res, err = [None, None], [None, None]
+
+    def work(i):
+        try:
+            ex = ORBextractor(5000 if i == 0 else 1200, device=(i if ndev >= 2 else 0), **ORB)
+            out = []
+            for rep in range(4):
+                for f in frames[i]:
+                    mono, k, d = ex(f, None, (0, 0))
+                    out.append((mono, k.copy(), d.copy()))
+            res[i] = out
+        except Exception as e:  # noqa: BLE001
+            err[i] = e
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert err == [None, None], err
+    for i in range(2):
+        orc = oracle_mod.Extractor(5000 if i == 0 else 1200)
+        want = [orc.extract(f, (0, 0)) for f in frames[i]]
+        for j, (mono, k, d) in enumerate(res[i]):
+            wk, wd, wm = want[j % 3]
+            assert mono == wm and np.array_equal(k, wk) and np.array_equal(d, wd), (i, j)
