@@ -4,17 +4,20 @@
 // formulation with plain loops against the oracle); per-key work (root/quadrant labelling,
 // counting, relabelling, best-response selection) is spread over the CTA.  The only serial step
 // left is the libstdc++ std::sort replica that orders the careful phase.
+#include <stdlib.h>
+
 #include "octree_core.h"
 #include "orbx_kernels.cuh"
 
-#define OCT_THREADS 256
-#define OCT_WARPS (OCT_THREADS / 32)
+#define OCT_THREADS 256      // ordinary frames; levels with many keypoints (4K) run OCT_THREADS_BIG threads per CTA:
+#define OCT_THREADS_BIG 1024 // the per-key loops and block scans of a round shrink with the CTA width
+#define OCT_MAX_WARPS 32
 #define OCT_MAX_ROOTS 64
 
 struct OctShared {
   int root_cnt[OCT_MAX_ROOTS];
   int root_pos[OCT_MAX_ROOTS];
-  int wsum[2][OCT_WARPS];  // block-scan scratch
+  int wsum[2][OCT_MAX_WARPS];  // block-scan scratch
   int bcast[4];            // block-wide results (totals, first hit)
 };
 
@@ -38,6 +41,7 @@ size_t orbx_octree_smem_bytes(int smem_keys, int node_cap, int max_cells) {
 }
 
 // Exclusive block scan of two values per thread (a, b), with the block totals.  Two barriers.
+template <int NT>
 __device__ __forceinline__ void block_scan2(OctShared& sh, int a, int b, int& ea, int& eb, int& ta, int& tb) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int ia = a, ib = b;
@@ -51,7 +55,7 @@ __device__ __forceinline__ void block_scan2(OctShared& sh, int a, int b, int& ea
   int oa = 0, ob = 0;
   ta = 0; tb = 0;
 #pragma unroll
-  for (int w = 0; w < OCT_WARPS; w++) {
+  for (int w = 0; w < NT / 32; w++) {
     const int va = sh.wsum[0][w], vb = sh.wsum[1][w];
     if (w < warp) { oa += va; ob += vb; }
     ta += va; tb += vb;
@@ -64,7 +68,8 @@ __device__ __forceinline__ void block_scan2(OctShared& sh, int a, int b, int& ea
 __device__ __forceinline__ int quad_K(const int* c) { return (c[0] > 0) + (c[1] > 0) + (c[2] > 0) + (c[3] > 0); }
 __device__ __forceinline__ int quad_E(const int* c) { return (c[0] > 1) + (c[1] > 1) + (c[2] > 1) + (c[3] > 1); }
 
-__global__ void __launch_bounds__(OCT_THREADS)
+template <int NT>
+__global__ void __launch_bounds__(NT)
 k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt,
          const uint32_t* __restrict__ cand, uint32_t* __restrict__ gkeys, int16_t* __restrict__ glabels,
          uint32_t* __restrict__ sel, int32_t* __restrict__ sel_cnt, int32_t* __restrict__ status,
@@ -108,16 +113,16 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
   const int ncell = L.nCols * L.nRows;
   const int32_t* cc = cell_cnt + (long long)frame * P.total_cells + L.cell_base;
   int n = 0;
-  for (int base = 0; base < ncell; base += OCT_THREADS) {
+  for (int base = 0; base < ncell; base += NT) {
     const int c = base + tid;
     const int v = c < ncell ? cc[c] : 0;
     int ev, e2, tv, t2;
-    block_scan2(sh, v, 0, ev, e2, tv, t2);
+    block_scan2<NT>(sh, v, 0, ev, e2, tv, t2);
     if (c < ncell) cell_off[c] = n + ev;
     n += tv;
   }
   if (tid == 0) cell_off[ncell] = n;
-  for (int i = tid; i < OCT_MAX_ROOTS; i += OCT_THREADS) sh.root_cnt[i] = 0;
+  for (int i = tid; i < OCT_MAX_ROOTS; i += NT) sh.root_cnt[i] = 0;
   __syncthreads();
   int32_t* cnt_out = sel_cnt + frame * P.nlevels + level;
   if (n == 0) {
@@ -130,7 +135,7 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
   uint32_t* keys = n <= smem_keys ? skeys : gkeys + lvl_off;
   int16_t* labels = n <= smem_keys ? slabels : glabels + lvl_off;
   const uint32_t* lc = cand + lvl_off;
-  for (int c = warp; c < ncell; c += OCT_WARPS) {
+  for (int c = warp; c < ncell; c += (NT / 32)) {
     const int o = cell_off[c], m = cell_off[c + 1] - o;
     for (int i = lane; i < m; i += 32) {
       const uint32_t k = lc[(long long)c * L.cell_cap + i];
@@ -148,7 +153,7 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
     const int nIni = L.nIni;  // <= OCT_MAX_ROOTS (checked at plan time)
     const int c = tid < nIni ? sh.root_cnt[tid] : 0;
     int e, e2, tot, t2;
-    block_scan2(sh, c > 0 ? 1 : 0, 0, e, e2, tot, t2);
+    block_scan2<NT>(sh, c > 0 ? 1 : 0, 0, e, e2, tot, t2);
     if (tid < nIni) {
       sh.root_pos[tid] = c > 0 ? e : -1;
       if (c > 0) cur[e] = octp_root(tid, L.hX, L.h - 2 * ORBX_MIN_BORDER, c);
@@ -156,7 +161,7 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
     S = tot;
   }
   __syncthreads();
-  for (int i = tid; i < n; i += OCT_THREADS) labels[i] = (int16_t)sh.root_pos[labels[i]];
+  for (int i = tid; i < n; i += NT) labels[i] = (int16_t)sh.root_pos[labels[i]];
   __syncthreads();
 
   // ---- 3. rounds (octree_core.h, "scan" form)
@@ -164,13 +169,13 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
   bool careful = false, overflow = false;
   while (true) {
     const int prevS = S;
-    for (int q = tid; q < S; q += OCT_THREADS) {
+    for (int q = tid; q < S; q += NT) {
       proc[q] = 0;
       *reinterpret_cast<int4*>(qc + 4 * q) = make_int4(0, 0, 0, 0);
     }
     __syncthreads();
     // (a) keys of nodes that may be divided vote for their quadrant
-    for (int i = tid; i < n; i += OCT_THREADS) {
+    for (int i = tid; i < n; i += NT) {
       const int pl = labels[i];
       const OctPNode nd = cur[pl];
       if (nd.cnt > 1) {
@@ -184,21 +189,21 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
       // (b) every node with more than one key is divided, in list order (:620-676)
       {
         int sk = 0, sd = 0;
-        for (int q = tid; q < S; q += OCT_THREADS)
+        for (int q = tid; q < S; q += NT)
           if (cur[q].cnt > 1) { sk += quad_K(qc + 4 * q); sd++; }
         int e1, e2;
-        block_scan2(sh, sk, sd, e1, e2, totK, nproc);
+        block_scan2<NT>(sh, sk, sd, e1, e2, totK, nproc);
       }
       if (totK + S - nproc > cap) { overflow = true; break; }
       int carryK = 0, carryE = 0;
-      for (int base = 0; base < S; base += OCT_THREADS) {
+      for (int base = 0; base < S; base += NT) {
         const int q = base + tid;
         const bool dv = q < S && cur[q].cnt > 1;
         int c[4] = {0, 0, 0, 0};
         if (dv) { const int4 v = *reinterpret_cast<const int4*>(qc + 4 * q); c[0] = v.x; c[1] = v.y; c[2] = v.z; c[3] = v.w; }
         const int K = quad_K(c), E = quad_E(c);
         int eK, eE, tK, tE;
-        block_scan2(sh, K, E, eK, eE, tK, tE);
+        block_scan2<NT>(sh, K, E, eK, eE, tK, tE);
         if (dv) {
           proc[q] = 1;
           octp_emit(cur[q], c, totK - (carryK + eK) - K, carryE + eE, nxt, vec2);
@@ -214,13 +219,13 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
       __syncthreads();
       int carryK = 0, carryE = 0;
       bool found = false;
-      for (int base = 0; base < nvec; base += OCT_THREADS) {
+      for (int base = 0; base < nvec; base += NT) {
         const int s = base + tid;
         const bool valid = s < nvec;
         int K = 0, E = 0;
         if (valid) { const int* c = qc + 4 * (int)(vec[nvec - 1 - s] & 0xffffu); K = quad_K(c); E = quad_E(c); }
         int eK, eE, tK, tE;
-        block_scan2(sh, K, E, eK, eE, tK, tE);
+        block_scan2<NT>(sh, K, E, eK, eE, tK, tE);
         if (valid) { preKs[s] = (int16_t)(carryK + eK); preEs[s] = (int16_t)(carryE + eE); }
         const bool hit = valid && (S + carryK + eK + K - (s + 1) >= N);
         if (hit) atomicMin(&sh.bcast[0], s);
@@ -237,7 +242,7 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
       }
       if (!found) { totK = carryK; totE = carryE; nproc = nvec; }
       if (totK + S - nproc > cap) { overflow = true; break; }
-      for (int s = tid; s < nproc; s += OCT_THREADS) {
+      for (int s = tid; s < nproc; s += NT) {
         const int q = (int)(vec[nvec - 1 - s] & 0xffffu);
         const int4 v = *reinterpret_cast<const int4*>(qc + 4 * q);
         int c[4] = {v.x, v.y, v.z, v.w};
@@ -249,11 +254,11 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
     __syncthreads();
     // (d) nodes that were not divided keep their relative order behind all the new children
     int stay = 0;
-    for (int base = 0; base < S; base += OCT_THREADS) {
+    for (int base = 0; base < S; base += NT) {
       const int q = base + tid;
       const bool st = q < S && !proc[q];
       int e, e2, t, t2;
-      block_scan2(sh, st ? 1 : 0, 0, e, e2, t, t2);
+      block_scan2<NT>(sh, st ? 1 : 0, 0, e, e2, t, t2);
       if (st) {
         const int pos = totK + stay + e;
         nxt[pos] = cur[q];
@@ -263,7 +268,7 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
     }
     __syncthreads();
     // (e) keys follow their node
-    for (int i = tid; i < n; i += OCT_THREADS) {
+    for (int i = tid; i < n; i += NT) {
       const int pl = labels[i];
       if (proc[pl]) {
         const uint32_t k = keys[i];
@@ -286,14 +291,14 @@ k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt
     if (tid == 0) { *cnt_out = 0; atomicOr(status, 1); }
     return;
   }
-  for (int i = tid; i < S; i += OCT_THREADS) best[i] = 0;
+  for (int i = tid; i < S; i += NT) best[i] = 0;
   __syncthreads();
-  for (int i = tid; i < n; i += OCT_THREADS)
+  for (int i = tid; i < n; i += NT)
     atomicMax(&best[labels[i]], ((uint32_t)ORBX_KEY_S(keys[i]) << 24) | (0xFFFFFFu - (uint32_t)i));
   __syncthreads();
   if (tid == 0) *cnt_out = S;
   uint32_t* out = sel + (long long)frame * P.kp_total_cap + L.kp_base;
-  for (int r = tid; r < S; r += OCT_THREADS) {
+  for (int r = tid; r < S; r += NT) {
     const int i = (int)(0xFFFFFFu - (best[r] & 0xFFFFFFu));
     const uint32_t k = keys[i];
     // back to level coordinates (:883-884)
@@ -326,11 +331,21 @@ cudaError_t orbx_launch_octree(const DevPlan& P, const int32_t* cell_cnt, const 
                                int32_t* status, int batch, size_t smem_bytes, int smem_keys, int node_cap,
                                int max_cells, cudaStream_t st) {
   // the opt-in is per (function, device) and is only ever raised (a smaller handle created later must not lower it)
-  cudaError_t e = orbx_ensure_dyn_smem(ORBX_SMEM_OCTREE, (const void*)k_octree, smem_bytes);
-  if (e != cudaSuccess) return e;
+  static const int force = [] { const char* e = getenv("ORBX_OCTREE_THREADS"); return e ? atoi(e) : 0; }();
+  const bool big = force ? force > OCT_THREADS : node_cap >= 768;  // > ~700 keypoints on the largest level
   dim3 grd(P.nlevels, batch);
-  k_octree<<<grd, OCT_THREADS, smem_bytes, st>>>(P, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, status,
-                                                 smem_keys, node_cap, max_cells);
+  cudaError_t e;
+  if (big) {
+    e = orbx_ensure_dyn_smem(ORBX_SMEM_OCTREE_BIG, (const void*)k_octree<OCT_THREADS_BIG>, smem_bytes);
+    if (e != cudaSuccess) return e;
+    k_octree<OCT_THREADS_BIG><<<grd, OCT_THREADS_BIG, smem_bytes, st>>>(P, cell_cnt, cand, gkeys, glabels, sel, sel_cnt,
+                                                                       status, smem_keys, node_cap, max_cells);
+  } else {
+    e = orbx_ensure_dyn_smem(ORBX_SMEM_OCTREE, (const void*)k_octree<OCT_THREADS>, smem_bytes);
+    if (e != cudaSuccess) return e;
+    k_octree<OCT_THREADS><<<grd, OCT_THREADS, smem_bytes, st>>>(P, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, status,
+                                                               smem_keys, node_cap, max_cells);
+  }
   return cudaGetLastError();
 }
 
