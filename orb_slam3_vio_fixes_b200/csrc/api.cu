@@ -66,6 +66,11 @@ struct orbx_extractor_s {
   int host_streams = 2;  // compute streams the host batch pipeline rotates its chunks over (ORBX_HOST_STREAMS, 1..4)
   std::vector<cudaEvent_t> ev_in, ev_done;
   cudaEvent_t ev_fork = nullptr, ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
+  // level-blur mode: k_blur_levels only needs the pyramid, so it can run beside FAST / octree of the same
+  // sub-batch on a side stream (ORBX_BLUR_SIDE=1): fork after the pyramid, join before the sampler
+  cudaStream_t s_side[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_pyr[4] = {nullptr, nullptr, nullptr, nullptr}, ev_blur[4] = {nullptr, nullptr, nullptr, nullptr};
+  int blur_side = 0;
   bool streams_ready = false;
   int host_chunk = 64;
   int host_edge = 0;   // length of the first and last chunk of a long host batch (ORBX_HOST_EDGE, 0 = off)
@@ -149,6 +154,11 @@ void orbx_destroy(orbx_handle h) {
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   for (int i = 0; i < 4; i++)
     if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]);
+  for (int i = 0; i < 4; i++) {
+    if (h->s_side[i]) { cudaStreamSynchronize(h->s_side[i]); cudaStreamDestroy(h->s_side[i]); }
+    if (h->ev_pyr[i]) cudaEventDestroy(h->ev_pyr[i]);
+    if (h->ev_blur[i]) cudaEventDestroy(h->ev_blur[i]);
+  }
   if (h->s_in) cudaStreamDestroy(h->s_in);
   if (h->s_out) cudaStreamDestroy(h->s_out);
   for (int i = 0; i < 4; i++)
@@ -291,20 +301,24 @@ static int ensure_streams(orbx_handle h) {
   if (h->streams_ready) return ORBX_OK;
   // all or nothing: a partial failure releases what was created, so a later call starts over
   cudaError_t e = cudaSuccess;
-  cudaStream_t* ss[6] = {&h->s_in, &h->s_out, &h->s_cmp[0], &h->s_cmp[1], &h->s_cmp[2], &h->s_cmp[3]};
-  cudaEvent_t* es[5] = {&h->ev_fork, &h->ev_join[0], &h->ev_join[1], &h->ev_join[2], &h->ev_join[3]};
-  for (int i = 0; i < 6 && e == cudaSuccess; i++) e = cudaStreamCreateWithFlags(ss[i], cudaStreamNonBlocking);
-  for (int i = 0; i < 5 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(es[i], cudaEventDisableTiming);
+  cudaStream_t* ss[10] = {&h->s_in, &h->s_out, &h->s_cmp[0], &h->s_cmp[1], &h->s_cmp[2], &h->s_cmp[3],
+                          &h->s_side[0], &h->s_side[1], &h->s_side[2], &h->s_side[3]};
+  cudaEvent_t* es[13] = {&h->ev_fork, &h->ev_join[0], &h->ev_join[1], &h->ev_join[2], &h->ev_join[3],
+                         &h->ev_pyr[0], &h->ev_pyr[1], &h->ev_pyr[2], &h->ev_pyr[3],
+                         &h->ev_blur[0], &h->ev_blur[1], &h->ev_blur[2], &h->ev_blur[3]};
+  for (int i = 0; i < 10 && e == cudaSuccess; i++) e = cudaStreamCreateWithFlags(ss[i], cudaStreamNonBlocking);
+  for (int i = 0; i < 13 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(es[i], cudaEventDisableTiming);
   if (e != cudaSuccess) {
     set_err("creating the handle's internal streams", e);
-    for (int i = 0; i < 6; i++) if (*ss[i]) { cudaStreamDestroy(*ss[i]); *ss[i] = nullptr; }
-    for (int i = 0; i < 5; i++) if (*es[i]) { cudaEventDestroy(*es[i]); *es[i] = nullptr; }
+    for (int i = 0; i < 10; i++) if (*ss[i]) { cudaStreamDestroy(*ss[i]); *ss[i] = nullptr; }
+    for (int i = 0; i < 13; i++) if (*es[i]) { cudaEventDestroy(*es[i]); *es[i] = nullptr; }
     return ORBX_E_CUDA;
   }
   h->streams_ready = true;
   if (const char* e = getenv("ORBX_HOST_CHUNK")) { const int v = atoi(e); if (v > 0) h->host_chunk = v; }
   if (const char* e = getenv("ORBX_HOST_STREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 4) h->host_streams = v; }
   if (const char* e = getenv("ORBX_HOST_EDGE")) { const int v = atoi(e); if (v >= 0) h->host_edge = v; }
+  if (const char* e = getenv("ORBX_BLUR_SIDE")) h->blur_side = atoi(e);
   if (const char* e = getenv("ORBX_DEVICE_SPLIT")) { const int v = atoi(e); if (v > 0) h->dev_split = v; }
   if (const char* e = getenv("ORBX_DEVICE_STREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 4) h->dev_streams = v; }
   return ORBX_OK;
@@ -312,7 +326,7 @@ static int ensure_streams(orbx_handle h) {
 
 static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1, OrbxKeyPointDev* d_kps,
                         uint8_t* d_desc, int capacity, int32_t* d_n, int32_t* d_mono, cudaStream_t st,
-                        int f0 = 0, bool allow_timing = true) {
+                        int f0 = 0, bool allow_timing = true, int side = -1) {
   const DevPlan& D = h->dplan;
   const bool tm = allow_timing && (h->cfg.flags & ORBX_FLAG_STAGE_TIMING) != 0;
   uint8_t* arena = h->arena + (long long)f0 * D.arena_bytes;
@@ -332,6 +346,13 @@ static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1,
   }
   CU(orbx_launch_pyramid(D, l0, arena, h->xtaps, h->ytaps, batch, st));
   STAGE_MARK(1);
+  const bool blur_aside = h->level_blur && side >= 0 && h->blur_side && !tm;
+  if (blur_aside) {
+    CU(cudaEventRecord(h->ev_pyr[side], st));
+    CU(cudaStreamWaitEvent(h->s_side[side], h->ev_pyr[side], 0));
+    CU(orbx_launch_blur(D, l0, arena, h->blur + (long long)f0 * D.arena_bytes, batch, h->s_side[side]));
+    CU(cudaEventRecord(h->ev_blur[side], h->s_side[side]));
+  }
   CU(orbx_launch_fast(D, h->fast_maps, l0, arena, h->cell_tab, h->strip_tab, cell_cnt, cand, batch, f0, st));
   STAGE_MARK(2);
   CU(orbx_launch_octree(D, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, h->status, batch,
@@ -341,7 +362,8 @@ static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1,
   STAGE_MARK(4);
   if (h->level_blur) {
     uint8_t* blur = h->blur + (long long)f0 * D.arena_bytes;
-    CU(orbx_launch_blur(D, l0, arena, blur, batch, st));
+    if (blur_aside) CU(cudaStreamWaitEvent(st, h->ev_blur[side], 0));
+    else CU(orbx_launch_blur(D, l0, arena, blur, batch, st));
     CU(orbx_launch_describe_lite(D, l0, arena, blur, sel, sel_cnt, dst, d_kps, d_desc, capacity,
                                  (h->cfg.flags & ORBX_FLAG_STRICT_FP) ? 1 : 0, batch, st));
   } else {
@@ -393,7 +415,7 @@ int orbx_extract_batch_device(orbx_handle h, const uint8_t* d_imgs, size_t pitch
     l.base = l0.base + (long long)f0 * l0.frame_stride;
     rc = run_pipeline(h, l, nb, lap0, lap1, (OrbxKeyPointDev*)d_kps + (long long)f0 * capacity,
                       d_desc + (long long)f0 * capacity * 32, capacity, d_n_out + f0, d_mono_index + f0,
-                      h->s_cmp[c % nstreams], f0, false);
+                      h->s_cmp[c % nstreams], f0, false, c % nstreams);
     if (rc) break;  // still join the forked streams back into the caller's stream below
   }
   for (int i = 0; i < nstreams; i++) {
