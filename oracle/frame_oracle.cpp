@@ -160,8 +160,10 @@ void oracle_is_in_frustum(const float* pos, const float* normal, const float* mi
 // A two-camera Frame holds its features concatenated: indices [0, Nleft) are mvKeys (left image), [Nleft, N) are
 // mvKeysRight (right image); mDescriptors / mvpMapPoints follow the same numbering; mGrid indexes the left
 // features, mGridRight the right ones by their index minus Nleft (Frame.cc:385-416).
-// UNPINNED by an executable reference (needs Eigen/Sophus + the Frame graph); line-by-line restatements checked
-// by hand-derived known answers (tests/test_oracle_fisheye_known_answers.py).
+// PINNED: SearchByProjection (both variants) and SearchByBoW on a rig frame are compared with the reference's own
+// ORBmatcher.cc compiled unmodified (oracle/_ref/libref_orbmatcher.so, tests/test_ref_matcher.py) and with
+// hand-derived known answers (tests/test_oracle_rig_known_answers.py).  The rig SearchForTriangulation needs
+// KannalaBrandt8::TriangulateMatches (Eigen JacobiSVD) and stays on the tolerance contract.
 // =====================================================================================================================
 #include <algorithm>
 #include <vector>

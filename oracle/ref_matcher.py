@@ -215,3 +215,21 @@ def fuse(kps, desc, holder_flags, u_right, bounds, sf, sigma2, bf, mp_flags, uv,
                     float(bf), a["f"].size, _p(a["f"]), _p(a["uv"]), _p(a["mx"]), _p(a["mn"]), _p(a["q"]), float(th),
                     _p(best))
     return best, nf
+
+
+def search_by_projection_sim3(variant, kps, desc, bounds, sf, matched_init, mp_flags, uv, max_dist, min_dist, qdesc, th,
+                              ratio_hamming):
+    """ORBmatcher::SearchByProjection(KeyFrame*, Sim3, ...) (variant 0: :427-532, 1: :534-646).
+    Returns (matched [N], nmatches)."""
+    k = np.ascontiguousarray(kps)
+    a = dict(d=_u8(desc), b=_f32(bounds), s=_f32(sf), mi=_i32(matched_init), f=_u8(mp_flags), uv=_f32(uv), mx=_f32(max_dist),
+             mn=_f32(min_dist), q=_u8(qdesc))
+    out = np.zeros(k.size, np.int32)
+    L = lib()
+    L.ref_search_by_projection_sim3.restype = C.c_int
+    L.ref_search_by_projection_sim3.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                                C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int, C.c_float, C.c_void_p]
+    nm = L.ref_search_by_projection_sim3(int(variant), _p(k), _p(a["d"]), k.size, _p(a["b"]), _p(a["s"]), a["s"].size,
+                                         _p(a["mi"]), a["f"].size, _p(a["f"]), _p(a["uv"]), _p(a["mx"]), _p(a["mn"]),
+                                         _p(a["q"]), int(th), float(ratio_hamming), _p(out))
+    return out, nm

@@ -559,4 +559,49 @@ int ref_fuse(const void* kps, const uint8_t* desc, int n, const uint8_t* holder_
   return nf;
 }
 
+// SearchByProjection(KeyFrame* pKF, Sophus::Sim3f &Scw, vpPoints, vpMatched, th, ratioHamming)  ORBmatcher.cc:427-532
+// (variant 0) and its twin with vpPointsKFs / vpMatchedKF :534-646 (variant 1).  Scw = identity with scale 1, unit
+// pinhole, point i at world (u_i, v_i, 1) with its normal towards the camera.  matched_init[j] = query point held by
+// keyframe feature j on entry (-1 none, -2 a foreign point); matched[j] = the same after the call.
+int ref_search_by_projection_sim3(int variant, const void* kps, const uint8_t* desc, int n, const float* bounds,
+                                  const float* scale_factors, int nlevels, const int* matched_init, int M,
+                                  const uint8_t* mp_flags, const float* uv, const float* max_dist, const float* min_dist,
+                                  const uint8_t* qdesc, int th, float ratio_hamming, int* matched) {
+  KeyFrame K;
+  std::vector<MapPoint> none;
+  std::vector<float> sig(nlevels, 1.f);
+  std::vector<uint8_t> nohold(n, 0);
+  fill_keyframe(K, none, kps, desc, n, -1, nohold.data(), nullptr, nullptr, nullptr, 0, nullptr, bounds, scale_factors,
+                sig.data(), nlevels);
+  GeometricCamera cam;
+  K.mpCamera = &cam;
+  std::vector<MapPoint> pts(M);
+  std::vector<MapPoint*> vp(M);
+  std::vector<KeyFrame*> vpKFs(M, &K);
+  for (int i = 0; i < M; i++) {
+    pts[i].id = i; pts[i].nObs = 1;
+    pts[i].mbBad = (mp_flags[i] & 2) != 0;
+    pts[i].mWorldPos = Eigen::Vector3f(uv[2 * i], uv[2 * i + 1], 1.f);
+    const float nrm = std::sqrt(uv[2 * i] * uv[2 * i] + uv[2 * i + 1] * uv[2 * i + 1] + 1.f);
+    pts[i].mNormalVector = Eigen::Vector3f(uv[2 * i] / nrm, uv[2 * i + 1] / nrm, 1.f / nrm);
+    pts[i].mfMaxDistance = max_dist[i]; pts[i].mfMinDistance = min_dist[i];
+    pts[i].mDescriptor = desc_row(qdesc + (size_t)i * 32);
+    vp[i] = &pts[i];
+  }
+  MapPoint foreign;
+  foreign.id = -2;
+  std::vector<MapPoint*> vpMatched(n, static_cast<MapPoint*>(NULL));
+  std::vector<KeyFrame*> vpMatchedKF(n, static_cast<KeyFrame*>(NULL));
+  for (int j = 0; j < n; j++) {
+    if (matched_init[j] >= 0) vpMatched[j] = &pts[matched_init[j]];
+    else if (matched_init[j] == -2) vpMatched[j] = &foreign;
+  }
+  Sophus::Sim3f Scw;
+  ORBmatcher matcher(0.75f, true);
+  const int nm = variant == 0 ? matcher.SearchByProjection(&K, Scw, vp, vpMatched, th, ratio_hamming)
+                              : matcher.SearchByProjection(&K, Scw, vp, vpKFs, vpMatched, vpMatchedKF, th, ratio_hamming);
+  for (int j = 0; j < n; j++) matched[j] = vpMatched[j] ? vpMatched[j]->id : -1;
+  return nm;
+}
+
 }  // extern "C"

@@ -340,3 +340,38 @@ def test_fuse_candidates(oracle_mod, RM, data):
     want[sel[ok]] = bi[ok]
     assert nf == int(ok.sum()) > 300
     assert np.array_equal(best, want)
+
+
+@pytest.mark.parametrize("variant,th,ratio", [(0, 8, 1.0), (1, 4, 1.5), (0, 5, 0.8)])
+def test_search_by_projection_sim3(oracle_mod, RM, data, variant, th, ratio):
+    """ORBmatcher.cc:427-532 / :534-646 (loop closing / merging): KeyFrame grid without level filter, band [l-1, l]
+    inside the loop, vpMatched blocks its features, best <= TH_LOW * ratioHamming, already-found points skipped."""
+    rng = np.random.default_rng(20 + variant)
+    sf, pos = data["sf"], data["pos"]
+    (kK, dK), (kQ, dQ) = data["mono"][1], data["mono"][0]
+    shv = pos[0] - pos[1]
+    M, n = len(kQ), len(kK)
+    uv = np.stack([(kQ["x"] + shv[0]).astype(f32), (kQ["y"] + shv[1]).astype(f32)], 1)
+    dist = np.sqrt(uv[:, 0].astype(np.float64) ** 2 + uv[:, 1].astype(np.float64) ** 2 + 1.0)
+    level = kQ["octave"].astype(np.int64)
+    max_dist, min_dist = (dist * 1.2 ** (level - 0.5)).astype(f32), (dist * 0.1).astype(f32)
+    mp_flags = (1 | ((rng.random(M) < 0.05).astype(np.uint8) << 1)).astype(np.uint8)
+    matched_init = np.full(n, -1, np.int32)
+    held = rng.permutation(n)[:n // 4]
+    matched_init[held[:len(held) // 2]] = -2                                  # foreign points
+    found = rng.permutation(M)[:len(held) - len(held) // 2]                   # query points already found
+    matched_init[held[len(held) // 2:]] = found
+    matched, nm = RM.search_by_projection_sim3(variant, kK, dK, BOUNDS, sf, matched_init, mp_flags, uv, max_dist, min_dist,
+                                               dQ, th, ratio)
+    inimg = (uv[:, 0] >= BOUNDS[0]) & (uv[:, 0] < BOUNDS[1]) & (uv[:, 1] >= BOUNDS[2]) & (uv[:, 1] < BOUNDS[3])
+    already = np.zeros(M, bool); already[found] = True
+    sel = np.nonzero(((mp_flags & 2) == 0) & ~already & inimg)[0]
+    lv = level[sel]
+    th_dist = int(np.floor(f32(50) * f32(ratio)))
+    _, fq, onm = oracle_mod.search_by_projection(kK, dK, BOUNDS, uv[sel, 0], uv[sel, 1], (f32(th) * sf[lv]).astype(f32),
+                                                 lv - 1, lv, dQ[sel], 1, 0.75, False,
+                                                 feat_locked=(matched_init != -1).astype(np.uint8),
+                                                 q_flags=np.full(len(sel), 3, np.uint8), th_dist=th_dist)
+    want = np.where(fq >= 0, sel[np.maximum(fq, 0)], matched_init)
+    assert nm == onm > 100
+    assert np.array_equal(matched, want)
