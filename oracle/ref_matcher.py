@@ -233,3 +233,44 @@ def search_by_projection_sim3(variant, kps, desc, bounds, sf, matched_init, mp_f
                                          _p(a["mi"]), a["f"].size, _p(a["f"]), _p(a["uv"]), _p(a["mx"]), _p(a["mn"]),
                                          _p(a["q"]), int(th), float(ratio_hamming), _p(out))
     return out, nm
+
+
+def search_by_sim3(kps1, desc1, hf1, uv1, maxd1, mind1, kps2, desc2, hf2, uv2, maxd2, mind2, bounds, sf, init12, th):
+    """ORBmatcher::SearchBySim3 (ORBmatcher.cc:1457-1674).  Returns (match12 [n1], nFound)."""
+    k1, k2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+    a = [_u8(desc1), _u8(hf1), _f32(uv1), _f32(maxd1), _f32(mind1), _u8(desc2), _u8(hf2), _f32(uv2), _f32(maxd2),
+         _f32(mind2), _f32(bounds), _f32(sf), _i32(init12)]
+    out = np.zeros(k1.size, np.int32)
+    L = lib()
+    L.ref_search_by_sim3.restype = C.c_int
+    L.ref_search_by_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_void_p]
+    nf = L.ref_search_by_sim3(_p(k1), _p(a[0]), k1.size, _p(a[1]), _p(a[2]), _p(a[3]), _p(a[4]), _p(k2), _p(a[5]), k2.size,
+                              _p(a[6]), _p(a[7]), _p(a[8]), _p(a[9]), _p(a[10]), _p(a[11]), a[11].size, _p(a[12]),
+                              float(th), _p(out))
+    return out, nf
+
+
+def search_for_triangulation_rig(kps1, desc1, nleft1, hf1, fv1, kps2, desc2, nleft2, hf2, fv2, sf, pose1, pose2, pose_rl,
+                                 gate, only_stereo, coarse, check_ori):
+    """ORBmatcher::SearchForTriangulation on rig keyframes; the geometric gate comes from gate [n1,n2] u8 (table cameras
+    that also verify the camera / pose combination they are called with).  Returns (match12, nmatches, bad_calls)."""
+    k1, k2 = np.ascontiguousarray(kps1), np.ascontiguousarray(kps2)
+    a, b = _fv_args(fv1), _fv_args(fv2)
+    d1, d2, h1, h2, s = _u8(desc1), _u8(desc2), _u8(hf1), _u8(hf2), _f32(sf)
+    p1, p2, prl, g = _f32(pose1), _f32(pose2), _f32(pose_rl), _u8(gate)
+    m12 = np.zeros(k1.size, np.int32)
+    bad = C.c_int(0)
+    L = lib()
+    L.ref_search_for_triangulation_rig.restype = C.c_int
+    L.ref_search_for_triangulation_rig.argtypes = ([C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                                    C.c_void_p, C.c_void_p, C.c_int] * 2) + \
+        [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+         C.POINTER(C.c_int)]
+    nm = L.ref_search_for_triangulation_rig(_p(k1), _p(d1), k1.size, int(nleft1), _pp(h1), _p(a[0]), _p(a[1]), _p(a[2]),
+                                            a[0].size, _p(k2), _p(d2), k2.size, int(nleft2), _pp(h2), _p(b[0]), _p(b[1]),
+                                            _p(b[2]), b[0].size, _p(s), s.size, _p(p1), _p(p2), _p(prl), _p(g),
+                                            int(bool(only_stereo)), int(bool(coarse)), int(bool(check_ori)), _p(m12),
+                                            C.byref(bad))
+    return m12, nm, bad.value

@@ -604,4 +604,105 @@ int ref_search_by_projection_sim3(int variant, const void* kps, const uint8_t* d
   return nm;
 }
 
+// SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12, S12, th)  ORBmatcher.cc:1457-1674.  Identity poses,
+// S12 = identity, fx = fy = 1, cx = cy = 0: MapPoint i of keyframe 1 sits at (uv1_i, 1) — where the reference's code
+// projects it into keyframe 2 — and MapPoint j of keyframe 2 at (uv2_j, 1).  hf*: bit0 point present, bit1 isBad.
+// init12[i] = feature of keyframe 2 whose point vpMatches12[i] holds on entry (-1 none).
+// match12[i] = feature of keyframe 2 whose point vpMatches12[i] holds after the call.
+int ref_search_by_sim3(const void* kps1, const uint8_t* desc1, int n1, const uint8_t* hf1, const float* uv1,
+                       const float* maxd1, const float* mind1, const void* kps2, const uint8_t* desc2, int n2,
+                       const uint8_t* hf2, const float* uv2, const float* maxd2, const float* mind2, const float* bounds,
+                       const float* scale_factors, int nlevels, const int* init12, float th, int* match12) {
+  KeyFrame K1, K2;
+  std::vector<MapPoint> p1, p2;
+  std::vector<float> sig(nlevels, 1.f);
+  fill_keyframe(K1, p1, kps1, desc1, n1, -1, hf1, nullptr, nullptr, nullptr, 0, nullptr, bounds, scale_factors, sig.data(), nlevels);
+  fill_keyframe(K2, p2, kps2, desc2, n2, -1, hf2, nullptr, nullptr, nullptr, 0, nullptr, bounds, scale_factors, sig.data(), nlevels);
+  for (int i = 0; i < n1; i++) {
+    p1[i].mWorldPos = Eigen::Vector3f(uv1[2 * i], uv1[2 * i + 1], 1.f);
+    p1[i].mfMaxDistance = maxd1[i]; p1[i].mfMinDistance = mind1[i];
+    p1[i].mDescriptor = desc_row(desc1 + (size_t)i * 32);
+    p1[i].mObservations[&K1] = std::tuple<int, int>(i, -1);
+  }
+  for (int j = 0; j < n2; j++) {
+    p2[j].mWorldPos = Eigen::Vector3f(uv2[2 * j], uv2[2 * j + 1], 1.f);
+    p2[j].mfMaxDistance = maxd2[j]; p2[j].mfMinDistance = mind2[j];
+    p2[j].mDescriptor = desc_row(desc2 + (size_t)j * 32);
+    p2[j].mObservations[&K2] = std::tuple<int, int>(j, -1);
+  }
+  std::vector<MapPoint*> vpMatches12(n1, static_cast<MapPoint*>(NULL));
+  for (int i = 0; i < n1; i++)
+    if (init12[i] >= 0) vpMatches12[i] = &p2[init12[i]];
+  Sophus::Sim3f S12;
+  ORBmatcher matcher(0.75f, true);
+  const int nf = matcher.SearchBySim3(&K1, &K2, vpMatches12, S12, th);
+  for (int i = 0; i < n1; i++) match12[i] = vpMatches12[i] ? vpMatches12[i]->id : -1;
+  return nf;
+}
+
+// SearchForTriangulation between keyframes of a two-camera rig (mpCamera2 != NULL), ORBmatcher.cc:907-1146 with the
+// camera selection :1036-1062.  The geometric gate is KannalaBrandt8::TriangulateMatches (Eigen JacobiSVD): not
+// compilable here, so the rig's cameras are table cameras whose epipolarConstrain looks the outcome up in
+// gate[n1][n2] (keypoints carry their index in class_id) — and check that the reference handed them the camera pair and
+// the (R12, t12) of the combination (left/right of KF1) x (left/right of KF2); *bad_calls counts violations.
+namespace {
+struct TableCamera : GeometricCamera {
+  const uint8_t* gate; int n2, nleft1, nleft2; bool right;  // which camera of its keyframe this object is
+  TableCamera* peer1[2]; TableCamera* peer2[2];
+  Sophus::SE3f T[4]; int* bad;
+  bool epipolarConstrain(GeometricCamera* pCamera2, const cv::KeyPoint& kp1, const cv::KeyPoint& kp2,
+                         const Eigen::Matrix3f& R12, const Eigen::Vector3f& t12, const float, const float) override {
+    const int r1 = kp1.class_id >= nleft1, r2 = kp2.class_id >= nleft2;
+    const Sophus::SE3f& E = T[2 * r1 + r2];
+    bool ok = this == peer1[r1] && pCamera2 == peer2[r2];
+    // (the reference's translation unit may contract the pose products to FMAs, this file does not: compare to 1e-5;
+    //  the four combinations differ by the 10 cm baseline)
+    for (int i = 0; i < 9; i++) ok = ok && std::fabs(R12.m[i] - E.R.m[i]) < 1e-5f;
+    for (int i = 0; i < 3; i++) ok = ok && std::fabs(t12(i) - E.t(i)) < 1e-5f;
+    if (!ok) (*bad)++;
+    return gate[(size_t)kp1.class_id * n2 + kp2.class_id] != 0;
+  }
+};
+}  // namespace
+
+int ref_search_for_triangulation_rig(const void* kps1, const uint8_t* desc1, int n1, int nleft1, const uint8_t* hf1,
+                                     const int* node1, const int* off1, const int* idx1, int nn1, const void* kps2,
+                                     const uint8_t* desc2, int n2, int nleft2, const uint8_t* hf2, const int* node2,
+                                     const int* off2, const int* idx2, int nn2, const float* scale_factors, int nlevels,
+                                     const float* pose1, const float* pose2, const float* pose_rl, const uint8_t* gate,
+                                     int only_stereo, int coarse, int check_ori, int* match12, int* bad_calls) {
+  KeyFrame K1, K2;
+  std::vector<MapPoint> p1, p2;
+  std::vector<float> sig(nlevels, 1.f);
+  fill_keyframe(K1, p1, kps1, desc1, n1, nleft1, hf1, node1, off1, idx1, nn1, nullptr, nullptr, scale_factors, sig.data(), nlevels);
+  fill_keyframe(K2, p2, kps2, desc2, n2, nleft2, hf2, node2, off2, idx2, nn2, nullptr, nullptr, scale_factors, sig.data(), nlevels);
+  // keypoints carry their (global) feature index
+  for (int i = 0; i < nleft1; i++) K1.mvKeys[i].class_id = i;
+  for (int i = nleft1; i < n1; i++) K1.mvKeysRight[i - nleft1].class_id = i;
+  for (int i = 0; i < nleft2; i++) K2.mvKeys[i].class_id = i;
+  for (int i = nleft2; i < n2; i++) K2.mvKeysRight[i - nleft2].class_id = i;
+  auto set_pose = [](Sophus::SE3f& T, const float* p) {
+    for (int i = 0; i < 9; i++) T.R.m[i] = p[i];
+    for (int i = 0; i < 3; i++) T.t(i) = p[9 + i];
+  };
+  set_pose(K1.mTcw, pose1); set_pose(K2.mTcw, pose2); set_pose(K1.mTrl, pose_rl); set_pose(K2.mTrl, pose_rl);
+  TableCamera c1[2], c2[2];
+  *bad_calls = 0;
+  // the four combinations exactly as ORBmatcher.cc:934-939 forms them
+  const Sophus::SE3f T1w = K1.GetPose(), Tw2 = K2.GetPoseInverse(), Tr1w = K1.GetRightPose(), Twr2 = K2.GetRightPoseInverse();
+  const Sophus::SE3f Tc[4] = {T1w * Tw2, T1w * Twr2, Tr1w * Tw2, Tr1w * Twr2};
+  for (TableCamera* c : {&c1[0], &c1[1], &c2[0], &c2[1]}) {
+    c->gate = gate; c->n2 = n2; c->nleft1 = nleft1; c->nleft2 = nleft2; c->bad = bad_calls;
+    c->peer1[0] = &c1[0]; c->peer1[1] = &c1[1]; c->peer2[0] = &c2[0]; c->peer2[1] = &c2[1];
+    for (int i = 0; i < 4; i++) c->T[i] = Tc[i];
+  }
+  K1.mpCamera = &c1[0]; K1.mpCamera2 = &c1[1]; K2.mpCamera = &c2[0]; K2.mpCamera2 = &c2[1];
+  std::vector<std::pair<size_t, size_t> > pairs;
+  ORBmatcher matcher(0.6f, check_ori != 0);
+  const int nm = matcher.SearchForTriangulation(&K1, &K2, pairs, only_stereo != 0, coarse != 0);
+  for (int i = 0; i < n1; i++) match12[i] = -1;
+  for (auto& pr : pairs) match12[pr.first] = (int)pr.second;
+  return nm;
+}
+
 }  // extern "C"

@@ -375,3 +375,79 @@ def test_search_by_projection_sim3(oracle_mod, RM, data, variant, th, ratio):
     want = np.where(fq >= 0, sel[np.maximum(fq, 0)], matched_init)
     assert nm == onm > 100
     assert np.array_equal(matched, want)
+
+
+def test_search_by_sim3(oracle_mod, RM, data):
+    """ORBmatcher::SearchBySim3 (ORBmatcher.cc:1457-1674): both directions scored like Fuse without the chi-square gate
+    (best <= TH_HIGH, band [l-1, l]), then the two-way agreement; points matched on entry are skipped on both sides."""
+    rng = np.random.default_rng(23)
+    sf, pos = data["sf"], data["pos"]
+    (k1, d1), (k2, d2) = data["mono"][0], data["mono"][1]
+    n1, n2 = len(k1), len(k2)
+    s12 = pos[0] - pos[1]          # keyframe-1 points seen in keyframe 2
+    uv1 = np.stack([(k1["x"] + s12[0]).astype(f32), (k1["y"] + s12[1]).astype(f32)], 1)
+    uv2 = np.stack([(k2["x"] - s12[0]).astype(f32), (k2["y"] - s12[1]).astype(f32)], 1)
+
+    def ranges(uv, k):
+        dist = np.sqrt(uv[:, 0].astype(np.float64) ** 2 + uv[:, 1].astype(np.float64) ** 2 + 1.0)
+        return (dist * 1.2 ** (k["octave"].astype(np.int64) - 0.5)).astype(f32), (dist * 0.1).astype(f32)
+
+    mx1, mn1 = ranges(uv1, k1)
+    mx2, mn2 = ranges(uv2, k2)
+    hf1 = ((rng.random(n1) < 0.85).astype(np.uint8) | ((rng.random(n1) < 0.05).astype(np.uint8) << 1)).astype(np.uint8)
+    hf2 = ((rng.random(n2) < 0.85).astype(np.uint8) | ((rng.random(n2) < 0.05).astype(np.uint8) << 1)).astype(np.uint8)
+    init12 = np.full(n1, -1, np.int32)
+    pre = rng.permutation(n1)[:60]
+    init12[pre] = rng.permutation(np.nonzero(hf2 & 1)[0])[:60]
+    th = 7.5
+    match12, nf = RM.search_by_sim3(k1, d1, hf1, uv1, mx1, mn1, k2, d2, hf2, uv2, mx2, mn2, BOUNDS, sf, init12, th)
+
+    def direction(kq, dq, hfq, uv, skip, kt, dt):
+        inimg = (uv[:, 0] >= BOUNDS[0]) & (uv[:, 0] < BOUNDS[1]) & (uv[:, 1] >= BOUNDS[2]) & (uv[:, 1] < BOUNDS[3])
+        sel = np.nonzero(((hfq & 1) > 0) & ((hfq & 2) == 0) & ~skip & inimg)[0]
+        lv = kq["octave"][sel].astype(np.int64)
+        bi, bd = oracle_mod.fuse_candidates(kt, dt, BOUNDS, np.zeros(8, f32), uv[sel, 0], uv[sel, 1],
+                                            (f32(th) * sf[lv]).astype(f32), lv, dq[sel])
+        out = np.full(len(kq), -1, np.int64)
+        ok = (bi >= 0) & (bd <= 100)
+        out[sel[ok]] = bi[ok]
+        return out
+
+    skip1 = init12 >= 0
+    skip2 = np.zeros(n2, bool); skip2[init12[init12 >= 0]] = True
+    m1 = direction(k1, d1, hf1, uv1, skip1, k2, d2)
+    m2 = direction(k2, d2, hf2, uv2, skip2, k1, d1)
+    want = init12.astype(np.int64).copy()
+    agree = (m1 >= 0) & (m2[np.maximum(m1, 0)] == np.arange(n1))
+    want[agree] = m1[agree]
+    assert nf == int(agree.sum()) > 300
+    assert np.array_equal(match12, want)
+
+
+@pytest.mark.parametrize("only_stereo,coarse", [(False, False), (False, True), (True, False)])
+def test_search_for_triangulation_rig_loop(oracle_mod, RM, data, only_stereo, coarse):
+    """ORBmatcher.cc:907-1146 with mpCamera2 (rig keyframes): skips, no stereo / epipole gates, the camera and
+    (R12, t12) selection :1036-1062 (verified call by call by the table cameras), last minimum wins.  The outcome of
+    KannalaBrandt8::epipolarConstrain is an input (random table) on both sides."""
+    rng = np.random.default_rng(24)
+    (kl1, dl1), (kr1, dr1) = data["left"][0], data["right"][0]
+    (kl2, dl2), (kr2, dr2) = data["left"][1], data["right"][1]
+    k1, d1 = np.concatenate([kl1, kr1]), np.concatenate([dl1, dr1])
+    k2, d2 = np.concatenate([kl2, kr2]), np.concatenate([dl2, dr2])
+    voc = S.make_vocabulary(10, 4, seed=7, desc_pool=np.concatenate([d1, d2]))
+    fv1 = oracle_mod.bow_transform(d1, voc, 2)["fv"]
+    fv2 = oracle_mod.bow_transform(d2, voc, 2)["fv"]
+    hf1 = (rng.random(len(k1)) < 0.3).astype(np.uint8)
+    hf2 = (rng.random(len(k2)) < 0.3).astype(np.uint8)
+    gate = (rng.random((len(k1), len(k2))) < 0.5).astype(np.uint8)
+    ang = 0.03
+    R2 = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+    pose1 = np.concatenate([np.eye(3).ravel(), [0.01, 0.02, 0.03]]).astype(f32)
+    pose2 = np.concatenate([R2.ravel(), [-0.3, 0.04, 0.08]]).astype(f32)
+    pose_rl = np.concatenate([np.eye(3).ravel(), [-0.101, 0.002, 0.001]]).astype(f32)
+    m12, nm, bad = RM.search_for_triangulation_rig(k1, d1, len(kl1), hf1, fv1, k2, d2, len(kl2), hf2, fv2, data["sf"], pose1,
+                                                   pose2, pose_rl, gate, only_stereo, coarse, True)
+    o12, onm = oracle_mod.search_for_triangulation_rig(k1, d1, fv1, k2, d2, fv2, gate, only_stereo, coarse, True, hf1, hf2)
+    assert bad == 0
+    assert nm == onm and np.array_equal(m12, o12)
+    assert nm == 0 if only_stereo else nm > 100
