@@ -11,6 +11,8 @@
 
 #define OCT_THREADS 256      // ordinary frames; levels with many keypoints (4K) run OCT_THREADS_BIG threads per CTA:
 #define OCT_THREADS_BIG 1024 // the per-key loops and block scans of a round shrink with the CTA width
+#define OCT_THREADS_SMALL 128
+#define OCT_SMALL_CAP 300     // node lists below this (<= ~290 keypoints on the largest level) use the narrow CTA
 #define OCT_MAX_WARPS 32
 #define OCT_MAX_ROOTS 64
 
@@ -331,21 +333,23 @@ cudaError_t orbx_launch_octree(const DevPlan& P, const int32_t* cell_cnt, const 
                                int32_t* status, int batch, size_t smem_bytes, int smem_keys, int node_cap,
                                int max_cells, cudaStream_t st) {
   // the opt-in is per (function, device) and is only ever raised (a smaller handle created later must not lower it)
+  // CTA width by the size of the largest level's node list: the rounds are barrier-bound, so narrow CTAs win while the
+  // per-key loops are short (C1: 0.30 -> 0.26 ms / 512 frames at 128 threads) and wide ones once they are long (4K)
   static const int force = [] { const char* e = getenv("ORBX_OCTREE_THREADS"); return e ? atoi(e) : 0; }();
-  const bool big = force ? force > OCT_THREADS : node_cap >= 768;  // > ~700 keypoints on the largest level
+  const int nt = force ? force : (node_cap >= 768 ? OCT_THREADS_BIG : (node_cap >= OCT_SMALL_CAP ? OCT_THREADS : OCT_THREADS_SMALL));
   dim3 grd(P.nlevels, batch);
   cudaError_t e;
-  if (big) {
-    e = orbx_ensure_dyn_smem(ORBX_SMEM_OCTREE_BIG, (const void*)k_octree<OCT_THREADS_BIG>, smem_bytes);
-    if (e != cudaSuccess) return e;
-    k_octree<OCT_THREADS_BIG><<<grd, OCT_THREADS_BIG, smem_bytes, st>>>(P, cell_cnt, cand, gkeys, glabels, sel, sel_cnt,
-                                                                       status, smem_keys, node_cap, max_cells);
-  } else {
-    e = orbx_ensure_dyn_smem(ORBX_SMEM_OCTREE, (const void*)k_octree<OCT_THREADS>, smem_bytes);
-    if (e != cudaSuccess) return e;
-    k_octree<OCT_THREADS><<<grd, OCT_THREADS, smem_bytes, st>>>(P, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, status,
-                                                               smem_keys, node_cap, max_cells);
-  }
+#define OCT_LAUNCH(NT, SLOT)                                                                                       \
+  do {                                                                                                             \
+    e = orbx_ensure_dyn_smem(SLOT, (const void*)k_octree<NT>, smem_bytes);                                         \
+    if (e != cudaSuccess) return e;                                                                                \
+    k_octree<NT><<<grd, NT, smem_bytes, st>>>(P, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, status, smem_keys,   \
+                                              node_cap, max_cells);                                                \
+  } while (0)
+  if (nt >= OCT_THREADS_BIG) OCT_LAUNCH(OCT_THREADS_BIG, ORBX_SMEM_OCTREE_BIG);
+  else if (nt >= OCT_THREADS) OCT_LAUNCH(OCT_THREADS, ORBX_SMEM_OCTREE);
+  else OCT_LAUNCH(OCT_THREADS_SMALL, ORBX_SMEM_OCTREE_X);
+#undef OCT_LAUNCH
   return cudaGetLastError();
 }
 

@@ -112,5 +112,5 @@ size_t orbx_octree_smem_bytes(int smem_keys, int node_cap, int max_cells);
 // cudaFuncAttributeMaxDynamicSharedMemorySize belongs to (function, device), not to a handle: this keeps a
 // per-device, monotone (only ever raised) cache per kernel slot, under a mutex, so handles of different sizes,
 // on different devices, created from different threads never lower or miss each other's opt-in.
-enum OrbxSmemSlot { ORBX_SMEM_FAST = 0, ORBX_SMEM_FAST4, ORBX_SMEM_FAST_STRIP, ORBX_SMEM_OCTREE, ORBX_SMEM_OCTREE_BIG, ORBX_SMEM_BOW_VECTORS, ORBX_SMEM_ROWBAND, ORBX_SMEM_SLOTS };
+enum OrbxSmemSlot { ORBX_SMEM_FAST = 0, ORBX_SMEM_FAST4, ORBX_SMEM_FAST_STRIP, ORBX_SMEM_OCTREE, ORBX_SMEM_OCTREE_BIG, ORBX_SMEM_OCTREE_X, ORBX_SMEM_BOW_VECTORS, ORBX_SMEM_ROWBAND, ORBX_SMEM_SLOTS };
 cudaError_t orbx_ensure_dyn_smem(OrbxSmemSlot slot, const void* func, size_t bytes);

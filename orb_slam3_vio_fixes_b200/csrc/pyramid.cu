@@ -188,6 +188,34 @@ __device__ __forceinline__ uint32_t rs_vert(const uint32_t (&A)[4], const uint32
   return __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
 }
 
+// dp2a form of the horizontal taps (RS_DP2A, default): one PRMT puts the two source bytes of a column into bytes 0 / 1,
+// IDP.2A against the packed coefficients (c0 | c1 << 16) gives h = r0*c0 + r1*c1 (< 2^19); the row keeps h & ~15 and the
+// vertical blend uses umulhi(b << 12, h & ~15) = (b * (h >> 4)) >> 16 — the same integers as cv::resize.
+#ifndef RS_DP2A
+#define RS_DP2A 1
+#endif
+struct RsTapRegs2 {
+  uint32_t sel[4];   // PRMT selector: bytes (d, d+1) of the window -> bytes 0, 1; rest zero
+  uint32_t coef[4];  // c0 | c1 << 16
+  int sa;
+};
+__device__ __forceinline__ void rs_row_smem2(const uint8_t* p, const RsTapRegs2& T, uint32_t (&H)[4]) {
+  const uint32_t w0 = *reinterpret_cast<const uint32_t*>(p);
+  const uint32_t w1 = *reinterpret_cast<const uint32_t*>(p + 4);
+  const uint32_t w2 = *reinterpret_cast<const uint32_t*>(p + 8);
+  const uint32_t lo = __funnelshift_r(w0, w1, T.sa);
+  const uint32_t hi = __funnelshift_r(w1, w2, T.sa);
+  const uint32_t mid = __funnelshift_r(lo, hi, 16);
+#pragma unroll
+  for (int i = 0; i < 4; i++) H[i] = __dp2a_lo(T.coef[i], __byte_perm(i < 2 ? lo : mid, 0, T.sel[i]), 0u) & ~15u;
+}
+__device__ __forceinline__ uint32_t rs_vert2(const uint32_t (&A)[4], const uint32_t (&B)[4], uint32_t b0s, uint32_t b1s) {
+  uint32_t v[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) v[i] = (__umulhi(b0s, A[i]) + __umulhi(b1s, B[i]) + 2u) >> 2;  // <= 255
+  return __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+}
+
 __global__ void __launch_bounds__(RS_WARPS * 32)
 k_resize_tile(const uint8_t* __restrict__ src, int spitch, long long sframe, int sw, int sh,
               uint8_t* __restrict__ dst, int dpitch, long long dframe, int dw, int dh,
@@ -219,7 +247,11 @@ k_resize_tile(const uint8_t* __restrict__ src, int spitch, long long sframe, int
   const int x4 = x0c + (tid & 31) * 4;
   const int dy0 = dy0c + (tid >> 5) * RS_ROWS;
   const bool live = x4 < dw && dy0 < dh;
+#if RS_DP2A
+  RsTapRegs2 T;
+#else
   RsTapRegs T;
+#endif
   int o0 = 0;
   if (live) {
     o0 = xt[x4].ofs;
@@ -229,10 +261,15 @@ k_resize_tile(const uint8_t* __restrict__ src, int spitch, long long sframe, int
       const OrbxTap t = xt[min(x4 + i, dw - 1)];
       int d = t.ofs - o0 - (i < 2 ? 0 : 2);
       d = min(max(d, 0), 2);  // only the padding columns beyond dw can fall outside
+#if RS_DP2A
+      T.sel[i] = 0x4400u | ((uint32_t)(d + 1) << 4) | (uint32_t)d;
+      T.coef[i] = (uint32_t)(uint16_t)t.c0 | ((uint32_t)(uint16_t)t.c1 << 16);
+#else
       T.selA[i] = 0x4440u | (uint32_t)d;
       T.selB[i] = 0x4404u | ((uint32_t)(d + 1) << 4);
       T.C0[i] = (uint32_t)t.c0 << 12;
       T.C1[i] = (uint32_t)t.c1 << 4;
+#endif
     }
   }
   {  // wait for the tile
@@ -248,8 +285,27 @@ k_resize_tile(const uint8_t* __restrict__ src, int spitch, long long sframe, int
   // or 2 (the scale is between 1 and 2), so the H row of sy0 is either the previous output row's second row
   // or a new one; the second row is always new.  HA/HB swap roles instead of moving.
   uint32_t HA[4], HB[4];
-  int sy_b = -1 << 20;  // source row held in HB
+  int sy_b = -1 << 20;  // source row held in the buffer that was the second row of the previous output row
   const int dy1 = min(dy0 + RS_ROWS, dh);
+#if RS_DP2A
+  // two output rows per trip; the buffers swap roles (P = holds the previous second row, Q = receives the new one)
+#define RS_STEP(P, Q, DY)                                                                         \
+  do {                                                                                            \
+    const OrbxTap ty = yt[DY];                                                                    \
+    const int sy0 = min(max(ty.ofs, 0), sh - 1), sy1 = min(max(ty.ofs + 1, 0), sh - 1);           \
+    if (sy0 != sy_b) rs_row_smem2(base + sy0 * RT_SPITCH, T, P);                                  \
+    rs_row_smem2(base + sy1 * RT_SPITCH, T, Q);                                                   \
+    sy_b = sy1;                                                                                   \
+    *reinterpret_cast<uint32_t*>(out) = rs_vert2(P, Q, (uint32_t)ty.c0 << 12, (uint32_t)ty.c1 << 12); \
+    out += dpitch;                                                                                \
+  } while (0)
+#pragma unroll 1
+  for (int dy = dy0; dy < dy1; dy += 2) {
+    RS_STEP(HA, HB, dy);
+    if (dy + 1 < dy1) RS_STEP(HB, HA, dy + 1);
+  }
+#undef RS_STEP
+#else
 #pragma unroll 1
   for (int dy = dy0; dy < dy1; dy++, out += dpitch) {
     const OrbxTap ty = yt[dy];
@@ -265,6 +321,7 @@ k_resize_tile(const uint8_t* __restrict__ src, int spitch, long long sframe, int
     // rows are 128-byte aligned and padded, so the full word store stays inside the row
     *reinterpret_cast<uint32_t*>(out) = rs_vert(HA, HB, (uint32_t)ty.c0, (uint32_t)ty.c1);
   }
+#endif
 }
 
 cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, const OrbxTap* xtaps,
