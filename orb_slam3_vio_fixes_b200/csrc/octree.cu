@@ -348,7 +348,7 @@ cudaError_t orbx_launch_octree(const DevPlan& P, const int32_t* cell_cnt, const 
   } while (0)
   if (nt >= OCT_THREADS_BIG) OCT_LAUNCH(OCT_THREADS_BIG, ORBX_SMEM_OCTREE_BIG);
   else if (nt >= OCT_THREADS) OCT_LAUNCH(OCT_THREADS, ORBX_SMEM_OCTREE);
-  else OCT_LAUNCH(OCT_THREADS_SMALL, ORBX_SMEM_OCTREE_X);
+  else OCT_LAUNCH(OCT_THREADS_SMALL, ORBX_SMEM_OCTREE_X);  // (64 threads: 0.35 ms, slower again)
 #undef OCT_LAUNCH
   return cudaGetLastError();
 }
