@@ -424,6 +424,8 @@ cudaError_t orbx_launch_fast_strip(const DevPlan& P, const OrbxFastMaps& maps, L
     const int hmax = g == 0 ? P.hmax_a : P.hmax_b;
     if (s1 <= s0) continue;
     if (hmax > FS_MAXH) return cudaErrorInvalidValue;
+    // (occupancy is not the lever here: padding the region by 2 / 4 / 8 KB, i.e. 13 / 11 / 9 instead of 15 strips per
+    //  SM, costs 3.6 / 12.8 / 26.5 % — the ALU pipe is 65 % busy at 15 strips, so the 2.6 KB task list could buy ~3 %)
     const size_t region = fs_region_words(hmax);
     const size_t smem = FS_WARPS * region * sizeof(uint32_t);
     cudaError_t e = orbx_ensure_dyn_smem(ORBX_SMEM_FAST_STRIP, (const void*)k_fast_strip, smem);
