@@ -316,12 +316,15 @@ def sum_candidates(kps_q, kps_r, shift, sf, w, h):
     return int(ok[inside].sum())
 
 
-def run_threads(workers, steps):
+def run_threads(workers, steps, device=None):
     """Runs `steps` calls spread round-robin over the worker callables, one host thread each; returns wall seconds."""
     errs = []
 
     def body(j):
         try:
+            if device is not None:  # a new host thread starts on cuda:0: put it on this rank's GPU
+                import torch
+                torch.cuda.set_device(device)
             for _ in range(j, steps, len(workers)):
                 workers[j]()
         except Exception as e:  # noqa: BLE001
@@ -419,12 +422,20 @@ def main():
     numa = "unset"
     all_cpus = os.sched_getaffinity(0)
     try:
+        if os.environ.get("ORBX_BENCH_NO_AFFINITY"):
+            raise RuntimeError("affinity off")
         import pynvml
         pynvml.nvmlInit()
         pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
         numa = "gpu-local"
+        # a VM may report a GPU-local set that is far smaller than the rank's fair share of the host (seen: a
+        # handful of CPUs for 2 ranks on a 24-CPU box, e2e 30 k instead of 280 k frames/s): then keep every CPU
+        if len(os.sched_getaffinity(0)) < max(4, len(all_cpus) // (2 * max(world, 1))):
+            os.sched_setaffinity(0, all_cpus)
+            numa = "all (gpu-local set too small)"
     except Exception:
         pass
+    host_cpus = len(os.sched_getaffinity(0))
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
@@ -602,7 +613,9 @@ def main():
         wk()
         wk()
     barrier()
-    e2e_s = run_threads(workers, args.steps)
+    e2e_s = run_threads(workers, args.steps, dev)
+    if os.environ.get("ORBX_BENCH_VERBOSE"):
+        print(f"[rank {rank}] e2e {args.steps} steps in {e2e_s * 1e3:.1f} ms", file=sys.stderr, flush=True)
     barrier()
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
@@ -686,7 +699,7 @@ def main():
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": workload, "frames_per_step_per_gpu": B, **extra,
                    "l2_policy": f"inputs {eyes * B * w * h / 1e6:.0f} MB + intermediates exceed the 126 MB L2 every step",
-                   "sharding": "independent frame batches per GPU, no collective", "host_affinity": numa,
+                   "sharding": "independent frame batches per GPU, no collective", "host_affinity": numa, "host_cpus": host_cpus,
                    "e2e_host_threads": T},
         "e2e": {"value": world * B * args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h},
