@@ -17,13 +17,24 @@
 //   SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&)                        ORBmatcher.cc:765-905
 //   SearchForInitialization(Frame&, Frame&, vbPrevMatched, vnMatches12, window)  ORBmatcher.cc:648-763
 //   SearchForTriangulation(KeyFrame*, KeyFrame*, vMatchedPairs, bOnlyStereo, bCoarse)   ORBmatcher.cc:907-1146 (pinhole)
+//   SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist)            ORBmatcher.cc:1889-2010 (relocalisation)
+//   SearchByProjection(KeyFrame*, Sim3&, vpPoints, vpMatched, th, ratioHamming)  ORBmatcher.cc:427-532
+//   SearchByProjection(KeyFrame*, Sim3&, vpPoints, vpPointsKFs, vpMatched, vpMatchedKF, th, ratioHamming)   :534-646
+//        all three -> orbm_search_by_projection_th (ORBdist / floor(TH_LOW*ratioHamming) as the threshold)
+//   Fuse(KeyFrame*, vpMapPoints, th, bRight), Fuse(KeyFrame*, Sim3&, vpPoints, th, vpReplacePoint)   :1148-1338, :1340-1455
+//   SearchBySim3(KeyFrame*, KeyFrame*, vpMatches12, S12, th)                     ORBmatcher.cc:1457-1674
+//        -> orbm_fuse_candidates for the scoring; the Replace / AddObservation / AddMapPoint calls and the two-way
+//           agreement run on the host exactly as the reference orders them
+// i.e. every method of include/ORBmatcher.h:40-87.  The Sim3 argument is a template parameter (Sophus::Sim3f in the
+// reference: rotationMatrix(), translation(), scale(), inverse(), operator*).
 // Members read (all reference names): Frame: N, Nleft, mvKeys, mvKeysRight, mvKeysUn, mDescriptors (.data, 32-byte
 // rows), mvuRight, mvpMapPoints, mvbOutlier, mvScaleFactors, mnMinX/mnMaxX/mnMinY/mnMaxY, mFeatVec, mvLeftToRightMatch,
-// mvRightToLeftMatch, mb, mbf, mpCamera->project(), GetPose();  KeyFrame: N, mvKeysUn, mDescriptors, mFeatVec,
-// mvuRight, mvScaleFactors, mvLevelSigma2, GetMapPointMatches(), GetMapPoint(i);  MapPoint: mbTrackInView(R),
-// mTrackProjX/Y/XR/YR, mTrackViewCos(R), mnTrackScaleLevel(R), mTrackDepth, isBad(), Observations(), GetDescriptor(),
-// GetWorldPos().  The Sim3 / Fuse / relocalisation variants keep their map-mutating bodies on the host and call
-// orbm_search_by_projection_th / orbm_fuse_candidates for the scoring.
+// mvRightToLeftMatch, mb, mbf, mpCamera->project(), GetPose();  KeyFrame: N, NLeft, mvKeys, mvKeysRight, mvKeysUn,
+// mDescriptors, mFeatVec, mvuRight, mvScaleFactors, mvLevelSigma2, mvInvLevelSigma2, mnMinX.., fx, fy, cx, cy, mbf,
+// mpCamera(2), GetPose(), GetRightPose(), GetCameraCenter(), GetRightCameraCenter(), IsInImage(), GetMapPointMatches(),
+// GetMapPoint(i), GetMapPoints(), AddMapPoint();  MapPoint: mbTrackInView(R), mTrackProjX/Y/XR/YR, mTrackViewCos(R),
+// mnTrackScaleLevel(R), mTrackDepth, isBad(), Observations(), GetDescriptor(), GetWorldPos(), GetNormal(),
+// GetMin/MaxDistanceInvariance(), PredictScale(), IsInKeyFrame(), GetIndexInKeyFrame(), AddObservation(), Replace().
 // Synchronous: every call uploads what it needs and downloads the result (a resident pipeline calls orbm_* directly).
 #ifndef ORBX_COMPAT_ORBMATCHER_H
 #define ORBX_COMPAT_ORBMATCHER_H
@@ -202,35 +213,7 @@ class ORBmatcherT {
     const int rc = RunProjection(CurrentFrame, q, m, locked, ORBM_PROJ_LASTFRAME, 0 /* rotation check below */, match,
                                  feat_query, nmatches);
     if (rc != ORBX_OK) return rc;
-    // writes in query order (:1772-1792), then the rotation histogram on the host exactly as the reference (:1864-1881)
-    std::vector<int> rotHist[HISTO_LENGTH];
-    const float factor = 1.0f / HISTO_LENGTH;
-    nmatches = 0;
-    for (size_t i = 0; i < m; i++) {
-      const int bestIdx2 = match[i];
-      if (bestIdx2 < 0) continue;
-      CurrentFrame.mvpMapPoints[bestIdx2] = pts[i];
-      nmatches++;
-      if (mbCheckOrientation) {
-        float rot = q.angle[i] - CurrentFrame.mvKeysUn[bestIdx2].angle;
-        if (rot < 0.0) rot += 360.0f;
-        int bin = (int)roundf(rot * factor);
-        if (bin == HISTO_LENGTH) bin = 0;
-        rotHist[bin].push_back(bestIdx2);
-      }
-    }
-    if (mbCheckOrientation) {
-      int ind1 = -1, ind2 = -1, ind3 = -1;
-      ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
-      for (int i = 0; i < HISTO_LENGTH; i++) {
-        if (i == ind1 || i == ind2 || i == ind3) continue;
-        for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
-          CurrentFrame.mvpMapPoints[rotHist[i][j]] = static_cast<MapPointT*>(NULL);
-          nmatches--;
-        }
-      }
-    }
-    return nmatches;
+    return CommitWithRotation(CurrentFrame, pts, q, m, match);
   }
 
   // ---- SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)  ORBmatcher.cc:223-425 ----
@@ -329,6 +312,234 @@ class ORBmatcherT {
                                         mbCheckOrientation, vMatchedPairs);
   }
 
+
+  // ---- SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint*> &sAlreadyFound, th, ORBdist)
+  //      ORBmatcher.cc:1889-2010 (relocalisation) ----
+  int SearchByProjection(FrameT& CurrentFrame, KeyFrameT* pKF, const std::set<MapPointT*>& sAlreadyFound, const float th,
+                         const int ORBdist) {
+    const auto Tcw = CurrentFrame.GetPose();
+    const auto Ow = Tcw.inverse().translation();
+    const std::vector<MapPointT*> vpMPs = pKF->GetMapPointMatches();
+    std::vector<MapPointT*> pts;
+    orbxm::Queries q;
+    q.resize(vpMPs.size());
+    size_t m = 0;
+    for (size_t i = 0, iend = vpMPs.size(); i < iend; i++) {
+      MapPointT* pMP = vpMPs[i];
+      if (!pMP || pMP->isBad() || sAlreadyFound.count(pMP)) continue;
+      const auto x3Dw = pMP->GetWorldPos();
+      const auto x3Dc = Tcw * x3Dw;
+      const auto uv = CurrentFrame.mpCamera->project(x3Dc);
+      if (uv(0) < CurrentFrame.mnMinX || uv(0) > CurrentFrame.mnMaxX) continue;
+      if (uv(1) < CurrentFrame.mnMinY || uv(1) > CurrentFrame.mnMaxY) continue;
+      const auto PO = x3Dw - Ow;
+      float dist3D = PO.norm();
+      const float maxDistance = pMP->GetMaxDistanceInvariance();
+      const float minDistance = pMP->GetMinDistanceInvariance();
+      if (dist3D < minDistance || dist3D > maxDistance) continue;
+      const int nPredictedLevel = pMP->PredictScale(dist3D, &CurrentFrame);
+      q.qx[m] = uv(0); q.qy[m] = uv(1); q.qr[m] = th * CurrentFrame.mvScaleFactors[nPredictedLevel];
+      q.qmin[m] = (int8_t)(nPredictedLevel - 1); q.qmax[m] = (int8_t)(nPredictedLevel + 1);
+      q.angle[m] = pKF->mvKeysUn[i].angle;
+      q.flags[m] = 3;
+      const cv::Mat d = pMP->GetDescriptor();
+      memcpy(&q.desc[m * 32], d.data, 32);
+      pts.push_back(pMP);
+      m++;
+    }
+    q.resize_keep(m);
+    std::vector<unsigned char> locked(CurrentFrame.N, 0);  // any non-null entry blocks its feature (:1951-1952)
+    for (int j = 0; j < CurrentFrame.N; j++) locked[j] = CurrentFrame.mvpMapPoints[j] != NULL;
+    std::vector<int> match, feat_query;
+    int nmatches = 0;
+    std::vector<float> no_uright;
+    const int rc = RunProjection(CurrentFrame, q, m, locked, ORBM_PROJ_LASTFRAME, 0, match, feat_query, nmatches, ORBdist,
+                                 /*stereo_gate=*/false);
+    if (rc != ORBX_OK) return rc;
+    return CommitWithRotation(CurrentFrame, pts, q, m, match);
+  }
+
+  // ---- SearchByProjection(KeyFrame* pKF, Sim3f &Scw, vpPoints, vpMatched, th, ratioHamming)  ORBmatcher.cc:427-532 ----
+  template <class Sim3T>
+  int SearchByProjection(KeyFrameT* pKF, Sim3T& Scw, const std::vector<MapPointT*>& vpPoints,
+                         std::vector<MapPointT*>& vpMatched, int th, float ratioHamming = 1.0) {
+    std::vector<KeyFrameT*> none;
+    return Sim3Projection(pKF, Scw, vpPoints, nullptr, vpMatched, nullptr, th, ratioHamming);
+  }
+
+  // ---- ... with vpPointsKFs / vpMatchedKF  ORBmatcher.cc:534-646 ----
+  template <class Sim3T>
+  int SearchByProjection(KeyFrameT* pKF, Sim3T& Scw, const std::vector<MapPointT*>& vpPoints,
+                         const std::vector<KeyFrameT*>& vpPointsKFs, std::vector<MapPointT*>& vpMatched,
+                         std::vector<KeyFrameT*>& vpMatchedKF, int th, float ratioHamming = 1.0) {
+    return Sim3Projection(pKF, Scw, vpPoints, &vpPointsKFs, vpMatched, &vpMatchedKF, th, ratioHamming);
+  }
+
+  // ---- Fuse(KeyFrame *pKF, const vector<MapPoint*> &vpMapPoints, th, bRight)  ORBmatcher.cc:1148-1338 ----
+  int Fuse(KeyFrameT* pKF, const std::vector<MapPointT*>& vpMapPoints, const float th = 3.0, const bool bRight = false) {
+    const auto Tcw = bRight ? pKF->GetRightPose() : pKF->GetPose();
+    const auto Ow = bRight ? pKF->GetRightCameraCenter() : pKF->GetCameraCenter();
+    auto* pCamera = bRight ? pKF->mpCamera2 : pKF->mpCamera;
+    const float bf = pKF->mbf;
+    const int nMPs = (int)vpMapPoints.size();
+    std::vector<int> who;
+    orbxm::Queries q;
+    q.resize(nMPs);
+    size_t m = 0;
+    for (int i = 0; i < nMPs; i++) {
+      MapPointT* pMP = vpMapPoints[i];
+      if (!pMP || pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+      const auto p3Dw = pMP->GetWorldPos();
+      const auto p3Dc = Tcw * p3Dw;
+      if (p3Dc(2) < 0.0f) continue;
+      const float invz = 1 / p3Dc(2);
+      const auto uv = pCamera->project(p3Dc);
+      if (!pKF->IsInImage(uv(0), uv(1))) continue;
+      const float ur = uv(0) - bf * invz;
+      const float maxDistance = pMP->GetMaxDistanceInvariance();
+      const float minDistance = pMP->GetMinDistanceInvariance();
+      const auto PO = p3Dw - Ow;
+      const float dist3D = PO.norm();
+      if (dist3D < minDistance || dist3D > maxDistance) continue;
+      const auto Pn = pMP->GetNormal();
+      if (PO.dot(Pn) < 0.5 * dist3D) continue;
+      const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
+      q.qx[m] = uv(0); q.qy[m] = uv(1); q.qr[m] = th * pKF->mvScaleFactors[nPredictedLevel];
+      q.qur[m] = ur; q.qmin[m] = (int8_t)nPredictedLevel;
+      const cv::Mat d = pMP->GetDescriptor();
+      memcpy(&q.desc[m * 32], d.data, 32);
+      who.push_back(i);
+      m++;
+    }
+    q.resize_keep(m);
+    std::vector<int> best_idx, best_dist;
+    const int rc = RunFuse(pKF, bRight, q, m, /*chi_gate=*/true, best_idx, best_dist);
+    if (rc != ORBX_OK) return rc;
+    int nFused = 0;
+    for (size_t k = 0; k < m; k++) {  // :1309-1331, in MapPoint order
+      if (best_idx[k] < 0 || best_dist[k] > TH_LOW) continue;
+      MapPointT* pMP = vpMapPoints[who[k]];
+      const int bestIdx = best_idx[k] + (bRight ? pKF->NLeft : 0);
+      MapPointT* pMPinKF = pKF->GetMapPoint(bestIdx);
+      if (pMPinKF) {
+        if (!pMPinKF->isBad()) {
+          if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+          else pMPinKF->Replace(pMP);
+        }
+      } else {
+        pMP->AddObservation(pKF, bestIdx);
+        pKF->AddMapPoint(pMP, bestIdx);
+      }
+      nFused++;
+    }
+    return nFused;
+  }
+
+  // ---- Fuse(KeyFrame *pKF, Sim3f &Scw, vpPoints, th, vpReplacePoint)  ORBmatcher.cc:1340-1455 ----
+  template <class Sim3T>
+  int Fuse(KeyFrameT* pKF, Sim3T& Scw, const std::vector<MapPointT*>& vpPoints, float th,
+           std::vector<MapPointT*>& vpReplacePoint) {
+    decltype(pKF->GetPose()) Tcw(Scw.rotationMatrix(), Scw.translation() / Scw.scale());
+    const auto Ow = Tcw.inverse().translation();
+    const std::set<MapPointT*> spAlreadyFound = pKF->GetMapPoints();
+    const int nPoints = (int)vpPoints.size();
+    std::vector<int> who;
+    orbxm::Queries q;
+    q.resize(nPoints);
+    size_t m = 0;
+    for (int iMP = 0; iMP < nPoints; iMP++) {
+      MapPointT* pMP = vpPoints[iMP];
+      if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+      if (!Sim3Query(pKF, Tcw, Ow, pMP, th, q, m)) continue;
+      q.qmin[m] = q.qmax[m];  // RunFuse takes the predicted level itself (band [l-1, l] is applied by the kernel)
+      who.push_back(iMP);
+      m++;
+    }
+    q.resize_keep(m);
+    std::vector<int> best_idx, best_dist;
+    const int rc = RunFuse(pKF, false, q, m, /*chi_gate=*/false, best_idx, best_dist);
+    if (rc != ORBX_OK) return rc;
+    int nFused = 0;
+    for (size_t k = 0; k < m; k++) {  // :1435-1449
+      if (best_idx[k] < 0 || best_dist[k] > TH_LOW) continue;
+      MapPointT* pMP = vpPoints[who[k]];
+      MapPointT* pMPinKF = pKF->GetMapPoint(best_idx[k]);
+      if (pMPinKF) {
+        if (!pMPinKF->isBad()) vpReplacePoint[who[k]] = pMPinKF;
+      } else {
+        pMP->AddObservation(pKF, best_idx[k]);
+        pKF->AddMapPoint(pMP, best_idx[k]);
+      }
+      nFused++;
+    }
+    return nFused;
+  }
+
+  // ---- SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12, S12, th)  ORBmatcher.cc:1457-1674 ----
+  template <class Sim3T>
+  int SearchBySim3(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12, const Sim3T& S12, const float th) {
+    const float fx = pKF1->fx, fy = pKF1->fy, cx = pKF1->cx, cy = pKF1->cy;  // (the reference uses pKF1's for both)
+    const auto T1w = pKF1->GetPose();
+    const auto T2w = pKF2->GetPose();
+    const auto S21 = S12.inverse();
+    const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches();
+    const std::vector<MapPointT*> vpMapPoints2 = pKF2->GetMapPointMatches();
+    const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
+    std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+    for (int i = 0; i < N1; i++) {
+      MapPointT* pMP = vpMatches12[i];
+      if (pMP) {
+        vbAlreadyMatched1[i] = true;
+        const int idx2 = std::get<0>(pMP->GetIndexInKeyFrame(pKF2));
+        if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+      }
+    }
+    std::vector<int> vnMatch1(N1, -1), vnMatch2(N2, -1);
+    for (int dir = 0; dir < 2; dir++) {  // :1496-1578 KF1 -> KF2, :1580-1660 KF2 -> KF1
+      const std::vector<MapPointT*>& src = dir == 0 ? vpMapPoints1 : vpMapPoints2;
+      const std::vector<bool>& done = dir == 0 ? vbAlreadyMatched1 : vbAlreadyMatched2;
+      KeyFrameT* dst = dir == 0 ? pKF2 : pKF1;
+      std::vector<int> who;
+      orbxm::Queries q;
+      q.resize(src.size());
+      size_t m = 0;
+      for (size_t i = 0; i < src.size(); i++) {
+        MapPointT* pMP = src[i];
+        if (!pMP || done[i] || pMP->isBad()) continue;
+        const auto p3Dw = pMP->GetWorldPos();
+        const auto pa = (dir == 0 ? T1w : T2w) * p3Dw;
+        const auto pb = dir == 0 ? S21 * pa : S12 * pa;
+        if (pb(2) < 0.0) continue;
+        const float invz = 1.0 / pb(2);
+        const float x = pb(0) * invz, y = pb(1) * invz;
+        const float u = fx * x + cx, v = fy * y + cy;
+        if (!dst->IsInImage(u, v)) continue;
+        const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+        const float dist3D = pb.norm();
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        const int nPredictedLevel = pMP->PredictScale(dist3D, dst);
+        q.qx[m] = u; q.qy[m] = v; q.qr[m] = th * dst->mvScaleFactors[nPredictedLevel]; q.qmin[m] = (int8_t)nPredictedLevel;
+        const cv::Mat d = pMP->GetDescriptor();
+        memcpy(&q.desc[m * 32], d.data, 32);
+        who.push_back((int)i);
+        m++;
+      }
+      q.resize_keep(m);
+      std::vector<int> best_idx, best_dist;
+      const int rc = RunFuse(dst, false, q, m, /*chi_gate=*/false, best_idx, best_dist);
+      if (rc != ORBX_OK) return rc;
+      std::vector<int>& out = dir == 0 ? vnMatch1 : vnMatch2;
+      for (size_t k = 0; k < m; k++)
+        if (best_idx[k] >= 0 && best_dist[k] <= TH_HIGH) out[who[k]] = best_idx[k];
+    }
+    int nFound = 0;  // :1662-1677 agreement
+    for (int i1 = 0; i1 < N1; i1++) {
+      const int idx2 = vnMatch1[i1];
+      if (idx2 >= 0 && vnMatch2[idx2] == i1) { vpMatches12[i1] = vpMapPoints2[idx2]; nFound++; }
+    }
+    return nFound;
+  }
+
  protected:
   float RadiusByViewingCos(const float& viewCos) {  // ORBmatcher.cc:215-221
     if (viewCos > 0.998) return 2.5;
@@ -347,36 +558,182 @@ class ORBmatcherT {
     else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
   }
 
-  // one single-camera orbm_search_by_projection_th call on F's features
-  int RunProjection(FrameT& F, const orbxm::Queries& q, size_t M, const std::vector<unsigned char>& locked, int mode,
-                    int check_ori, std::vector<int>& match, std::vector<int>& feat_query, int& nmatches) {
+  // writes in query order (:1772-1792 / :1961-1979), then the rotation histogram on the host exactly as the reference
+  // (:1864-1881 / :1986-2006): the erasure nulls the pointer whoever wrote it last
+  int CommitWithRotation(FrameT& CurrentFrame, const std::vector<MapPointT*>& pts, const orbxm::Queries& q, size_t m,
+                         const std::vector<int>& match) {
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int nmatches = 0;
+    for (size_t i = 0; i < m; i++) {
+      const int bestIdx2 = match[i];
+      if (bestIdx2 < 0) continue;
+      CurrentFrame.mvpMapPoints[bestIdx2] = pts[i];
+      nmatches++;
+      if (mbCheckOrientation) {
+        float rot = q.angle[i] - CurrentFrame.mvKeysUn[bestIdx2].angle;
+        if (rot < 0.0) rot += 360.0f;
+        int bin = (int)roundf(rot * factor);
+        if (bin == HISTO_LENGTH) bin = 0;
+        rotHist[bin].push_back(bestIdx2);
+      }
+    }
+    if (mbCheckOrientation) {
+      int ind1 = -1, ind2 = -1, ind3 = -1;
+      ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+      for (int i = 0; i < HISTO_LENGTH; i++) {
+        if (i == ind1 || i == ind2 || i == ind3) continue;
+        for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) {
+          CurrentFrame.mvpMapPoints[rotHist[i][j]] = static_cast<MapPointT*>(NULL);
+          nmatches--;
+        }
+      }
+    }
+    return nmatches;
+  }
+
+  // one single-camera orbm_search_by_projection_th call on a feature set
+  int RunProjectionRaw(const cv::KeyPoint* keys, const unsigned char* descs, int N, float mnMinX, float mnMaxX,
+                       float mnMinY, float mnMaxY, const std::vector<float>* u_right, const orbxm::Queries& q, size_t M,
+                       const std::vector<unsigned char>& locked, int mode, int check_ori, int th_dist,
+                       std::vector<int>& match, std::vector<int>& feat_query, int& nmatches) {
     match.assign(M, -1);
-    feat_query.assign(F.N, -1);
+    feat_query.assign(N, -1);
     nmatches = 0;
-    if (M == 0 || F.N == 0) return ORBX_OK;
+    if (M == 0 || N == 0) return ORBX_OK;
     orbxm::DevCamera cam;
-    if (!cam.upload(F.mvKeysUn.data(), F.mDescriptors.data, F.N, F.mnMinX, F.mnMaxX, F.mnMinY, F.mnMaxY, &locked, nullptr))
-      return ORBX_E_CUDA;
+    if (!cam.upload(keys, descs, N, mnMinX, mnMaxX, mnMinY, mnMaxY, &locked, nullptr)) return ORBX_E_CUDA;
     orbxm::Dev ur, qx, qy, qr, qmin, qmax, qd, nq, qur, fl, ang, scr, dm, dfq, dnm;
-    std::vector<float> u(F.mvuRight.begin(), F.mvuRight.end());
-    u.resize(cam.cap(), -1.f);
     std::vector<int32_t> nqv(1, (int32_t)M);
-    if (!ur.put(u) || !qx.put(q.qx) || !qy.put(q.qy) || !qr.put(q.qr) || !qmin.put(q.qmin) || !qmax.put(q.qmax) ||
-        !qd.put(q.desc) || !nq.put(nqv) || !qur.put(q.qur) || !fl.put(q.flags) || !ang.put(q.angle) ||
-        !scr.alloc(M * 32) || !dm.alloc(M * 4) || !dfq.alloc((size_t)cam.cap() * 4) || !dnm.alloc(4))
+    if (u_right) {
+      std::vector<float> u(u_right->begin(), u_right->end());
+      u.resize(cam.cap(), -1.f);
+      if (!ur.put(u) || !qur.put(q.qur)) return ORBX_E_CUDA;
+    }
+    if (!qx.put(q.qx) || !qy.put(q.qy) || !qr.put(q.qr) || !qmin.put(q.qmin) || !qmax.put(q.qmax) || !qd.put(q.desc) ||
+        !nq.put(nqv) || !fl.put(q.flags) || !ang.put(q.angle) || !scr.alloc(M * 32) || !dm.alloc(M * 4) ||
+        !dfq.alloc((size_t)cam.cap() * 4) || !dnm.alloc(4))
       return ORBX_E_CUDA;
     const int rc = orbm_search_by_projection_th(
         cam.kps.template as<orbx_keypoint>(), cam.desc.template as<uint8_t>(), cam.n.template as<int32_t>(), cam.cap(), 1,
-        cam.cell_off.template as<int32_t>(), cam.cell_idx.template as<int32_t>(), F.mnMinX, F.mnMaxX, F.mnMinY, F.mnMaxY,
+        cam.cell_off.template as<int32_t>(), cam.cell_idx.template as<int32_t>(), mnMinX, mnMaxX, mnMinY, mnMaxY,
         ur.as<float>(), cam.locked.template as<uint8_t>(), qx.as<float>(), qy.as<float>(), qr.as<float>(), qmin.as<int8_t>(),
         qmax.as<int8_t>(), qd.as<uint8_t>(), nq.as<int32_t>(), (int)M, qur.as<float>(), fl.as<uint8_t>(), ang.as<float>(),
-        mode, mfNNratio, check_ori, TH_HIGH, scr.p, dm.as<int32_t>(), dfq.as<int32_t>(), dnm.as<int32_t>(), nullptr);
+        mode, mfNNratio, check_ori, th_dist, scr.p, dm.as<int32_t>(), dfq.as<int32_t>(), dnm.as<int32_t>(), nullptr);
     if (rc != ORBX_OK) return rc;
     std::vector<int32_t> fq(cam.cap()), nm(1), mt(M);
     if (!dm.get(mt) || !dfq.get(fq) || !dnm.get(nm)) return ORBX_E_CUDA;
     for (size_t i = 0; i < M; i++) match[i] = mt[i];
-    for (int j = 0; j < F.N; j++) feat_query[j] = fq[j];
+    for (int j = 0; j < N; j++) feat_query[j] = fq[j];
     nmatches = nm[0];
+    return ORBX_OK;
+  }
+
+  int RunProjection(FrameT& F, const orbxm::Queries& q, size_t M, const std::vector<unsigned char>& locked, int mode,
+                    int check_ori, std::vector<int>& match, std::vector<int>& feat_query, int& nmatches,
+                    int th_dist = TH_HIGH, bool stereo_gate = true) {
+    return RunProjectionRaw(F.mvKeysUn.data(), F.mDescriptors.data, F.N, F.mnMinX, F.mnMaxX, F.mnMinY, F.mnMaxY,
+                            stereo_gate ? &F.mvuRight : nullptr, q, M, locked, mode, check_ori, th_dist, match, feat_query,
+                            nmatches);
+  }
+
+  // the gates of the two Sim3 functions for one MapPoint (:452-492, :1366-1404): fills query slot m, false = skipped
+  template <class SE3T, class Vec3T>
+  bool Sim3Query(KeyFrameT* pKF, const SE3T& Tcw, const Vec3T& Ow, MapPointT* pMP, float th, orbxm::Queries& q, size_t m) {
+    const auto p3Dw = pMP->GetWorldPos();
+    const auto p3Dc = Tcw * p3Dw;
+    if (p3Dc(2) < 0.0) return false;
+    const auto uv = pKF->mpCamera->project(p3Dc);
+    if (!pKF->IsInImage(uv(0), uv(1))) return false;
+    const float maxDistance = pMP->GetMaxDistanceInvariance();
+    const float minDistance = pMP->GetMinDistanceInvariance();
+    const auto PO = p3Dw - Ow;
+    const float dist = PO.norm();
+    if (dist < minDistance || dist > maxDistance) return false;
+    const auto Pn = pMP->GetNormal();
+    if (PO.dot(Pn) < 0.5 * dist) return false;
+    const int nPredictedLevel = pMP->PredictScale(dist, pKF);
+    q.qx[m] = uv(0); q.qy[m] = uv(1); q.qr[m] = th * pKF->mvScaleFactors[nPredictedLevel];
+    q.qmin[m] = (int8_t)(nPredictedLevel - 1); q.qmax[m] = (int8_t)nPredictedLevel;
+    q.flags[m] = 3;
+    const cv::Mat d = pMP->GetDescriptor();
+    memcpy(&q.desc[m * 32], d.data, 32);
+    return true;
+  }
+
+  template <class Sim3T>
+  int Sim3Projection(KeyFrameT* pKF, Sim3T& Scw, const std::vector<MapPointT*>& vpPoints,
+                     const std::vector<KeyFrameT*>* vpPointsKFs, std::vector<MapPointT*>& vpMatched,
+                     std::vector<KeyFrameT*>* vpMatchedKF, int th, float ratioHamming) {
+    decltype(pKF->GetPose()) Tcw(Scw.rotationMatrix(), Scw.translation() / Scw.scale());
+    const auto Ow = Tcw.inverse().translation();
+    std::set<MapPointT*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+    spAlreadyFound.erase(static_cast<MapPointT*>(NULL));
+    std::vector<int> who;
+    orbxm::Queries q;
+    q.resize(vpPoints.size());
+    size_t m = 0;
+    for (int iMP = 0, iendMP = (int)vpPoints.size(); iMP < iendMP; iMP++) {
+      MapPointT* pMP = vpPoints[iMP];
+      if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+      if (!Sim3Query(pKF, Tcw, Ow, pMP, (float)th, q, m)) continue;
+      who.push_back(iMP);
+      m++;
+    }
+    q.resize_keep(m);
+    const int N = (int)pKF->mvKeysUn.size();
+    std::vector<unsigned char> locked(N, 0);
+    for (int j = 0; j < N; j++) locked[j] = vpMatched[j] != NULL;  // :508-509
+    std::vector<int> match, feat_query;
+    int nmatches = 0;
+    const int th_dist = (int)floorf(TH_LOW * ratioHamming);  // bestDist <= TH_LOW*ratioHamming on integer distances
+    const int rc = RunProjectionRaw(pKF->mvKeysUn.data(), pKF->mDescriptors.data, N, pKF->mnMinX, pKF->mnMaxX, pKF->mnMinY,
+                                    pKF->mnMaxY, nullptr, q, m, locked, ORBM_PROJ_LASTFRAME, 0, th_dist, match, feat_query,
+                                    nmatches);
+    if (rc != ORBX_OK) return rc;
+    for (size_t k = 0; k < m; k++) {
+      if (match[k] < 0) continue;
+      vpMatched[match[k]] = vpPoints[who[k]];
+      if (vpMatchedKF) (*vpMatchedKF)[match[k]] = (*vpPointsKFs)[who[k]];
+    }
+    return nmatches;
+  }
+
+  // candidate scoring of Fuse / SearchBySim3 on a keyframe's features: orbm_fuse_candidates (best index / distance per
+  // query; q.qmin carries the predicted level, q.qur the stereo coordinate)
+  int RunFuse(KeyFrameT* pKF, bool bRight, const orbxm::Queries& q, size_t M, bool chi_gate, std::vector<int>& best_idx,
+              std::vector<int>& best_dist) {
+    best_idx.assign(M, -1);
+    best_dist.assign(M, 256);
+    const std::vector<cv::KeyPoint>& keys = (pKF->NLeft == -1) ? pKF->mvKeysUn : (!bRight ? pKF->mvKeys : pKF->mvKeysRight);
+    const int N = (int)keys.size();
+    if (M == 0 || N == 0) return ORBX_OK;
+    const unsigned char* descs = pKF->mDescriptors.data + (bRight ? (size_t)pKF->NLeft * 32 : 0);
+    orbxm::DevCamera cam;
+    if (!cam.upload(keys.data(), descs, N, pKF->mnMinX, pKF->mnMaxX, pKF->mnMinY, pKF->mnMaxY, nullptr, nullptr)) return ORBX_E_CUDA;
+    const int nlevels = (int)pKF->mvScaleFactors.size();
+    std::vector<float> inv(nlevels, 0.f);
+    if (chi_gate) inv.assign(pKF->mvInvLevelSigma2.begin(), pKF->mvInvLevelSigma2.end());
+    orbxm::Dev ur, qx, qy, qr, qur, ql, qd, nq, out;
+    std::vector<int32_t> nqv(1, (int32_t)M);
+    if (chi_gate) {
+      std::vector<float> u(pKF->mvuRight.begin(), pKF->mvuRight.end());
+      u.resize(cam.cap(), -1.f);
+      if (!ur.put(u) || !qur.put(q.qur)) return ORBX_E_CUDA;
+    }
+    if (!qx.put(q.qx) || !qy.put(q.qy) || !qr.put(q.qr) || !ql.put(q.qmin) || !qd.put(q.desc) || !nq.put(nqv) ||
+        !out.alloc(M * sizeof(orbm_result)))
+      return ORBX_E_CUDA;
+    const int rc = orbm_fuse_candidates(cam.kps.template as<orbx_keypoint>(), cam.desc.template as<uint8_t>(),
+                                        cam.n.template as<int32_t>(), cam.cap(), cam.cell_off.template as<int32_t>(),
+                                        cam.cell_idx.template as<int32_t>(), pKF->mnMinX, pKF->mnMaxX, pKF->mnMinY,
+                                        pKF->mnMaxY, ur.as<float>(), inv.data(), nlevels, qx.as<float>(), qy.as<float>(),
+                                        qr.as<float>(), qur.as<float>(), ql.as<int8_t>(), qd.as<uint8_t>(), nq.as<int32_t>(),
+                                        (int)M, 1, out.as<orbm_result>(), nullptr);
+    if (rc != ORBX_OK) return rc;
+    std::vector<orbm_result> res(M);
+    if (!out.get(res)) return ORBX_E_CUDA;
+    for (size_t i = 0; i < M; i++) { best_idx[i] = res[i].best_idx; best_dist[i] = res[i].best_dist; }
     return ORBX_OK;
   }
 

@@ -117,7 +117,8 @@ def test_cpp_orbmatcher_class(oracle_mod, tmp_path):
     """include/orbx_compat/ORBmatcher.h: ORBmatcherT<Frame, KeyFrame, MapPoint> with the reference's method names and
     arguments (include/ORBmatcher.h:40-87) on stand-in object types (tests/cpp/compat_matcher.cpp), against the oracle:
     SearchByProjection (MapPoints: single camera and fisheye rig; last frame), SearchByBoW (KF-Frame, KF-rig Frame,
-    KF-KF), SearchForTriangulation, SearchForInitialization."""
+    KF-KF), SearchForTriangulation, SearchForInitialization, the relocalisation and Sim3 projections, Fuse x2 (with the
+    reference's Replace / AddObservation rules) and SearchBySim3 — every method of include/ORBmatcher.h:40-87."""
     exe = _build_exe(tmp_path, "compat_matcher")
     rng = np.random.default_rng(101)
     f32 = np.float32
@@ -293,10 +294,132 @@ def test_cpp_orbmatcher_class(oracle_mod, tmp_path):
     m12, nm, _ = oracle_mod.search_for_initialization(k1, d1, k2b, d2b, bounds, prev, 100, 0.9, True)
     exp["init_m12"] = (m12, nm)
 
+    # 8.-11. relocalisation, Sim3 projections x2, Fuse, Fuse(Sim3): keyframe / current frame = frame 1, query points =
+    # frame 0's keypoints at world (u, v, 1) (identity poses, unit pinhole); PredictScale returns the keypoint's octave
+    (kQ, dQ), (kT, dT) = feats[0], feats[1]
+    shv = pos[0] - pos[1]
+    Mq, nT = len(kQ), len(kT)
+    uvq = np.stack([(kQ["x"] + shv[0]).astype(f32), (kQ["y"] + shv[1]).astype(f32)], 1)
+    distq = np.sqrt(uvq[:, 0].astype(np.float64) ** 2 + uvq[:, 1].astype(np.float64) ** 2 + 1.0)
+    lvq = kQ["octave"].astype(np.int64)
+    mxq, mnq = (distq * 1.2 ** (lvq - 0.5)).astype(f32), (distq * 0.1).astype(f32)
+    qf = ((rng.random(Mq) < 0.9).astype(np.int32) | ((rng.random(Mq) < 0.05).astype(np.int32) << 1) |
+          ((rng.random(Mq) < 0.1).astype(np.int32) << 2)).astype(np.int32)
+    hfT = ((rng.random(nT) < 0.5).astype(np.int32) | ((rng.random(nT) < 0.1).astype(np.int32) << 1)).astype(np.int32)
+    uRT = np.where(rng.random(nT) < 0.5, kT["x"] - f32(40.0), f32(-1)).astype(f32)
+    w([Mq], np.int32); w(qf, np.int32); w(uvq, f32); w(mxq, f32); w(mnq, f32); w(kQ["angle"], f32); w(dQ, np.uint8)
+    w_feats(kT, dT); w(hfT, np.int32); w(uRT, f32)
+    held = (hfT & 1) > 0
+    own_ids = np.where(held, -2 - np.arange(nT), -1)
+    inb = (uvq[:, 0] >= 0) & (uvq[:, 0] <= 752) & (uvq[:, 1] >= 0) & (uvq[:, 1] <= 480)
+    inimg = (uvq[:, 0] >= 0) & (uvq[:, 0] < 752) & (uvq[:, 1] >= 0) & (uvq[:, 1] < 480)
+    bad_q, found_q, has_q = (qf & 2) > 0, (qf & 4) > 0, (qf & 1) > 0
+    # 8. relocalisation (th = 10, ORBdist = 100, rotation check)
+    sel = np.nonzero(has_q & ~bad_q & ~found_q & inb)[0]
+    args = (kT, dT, bounds, uvq[sel, 0], uvq[sel, 1], (f32(10.0) * sf[lvq[sel]]).astype(f32), lvq[sel] - 1, lvq[sel] + 1,
+            dQ[sel], 1, 0.9)
+    kw = dict(feat_locked=held.astype(np.uint8), q_flags=np.full(len(sel), 3, np.uint8), q_angle=kQ["angle"][sel], th_dist=100)
+    _, fq0, _ = oracle_mod.search_by_projection(*args, False, **kw)
+    _, fq1, nm = oracle_mod.search_by_projection(*args, True, **kw)
+    exp["reloc"] = (np.where(fq0 >= 0, np.where(fq1 >= 0, sel[np.maximum(fq1, 0)], -1), own_ids), nm)
+    # 9. Sim3 projections: vpMatched = the keyframe's own points, "already found" query i sits at feature i
+    minit = own_ids.copy()
+    placed = np.nonzero(found_q & (np.arange(Mq) < nT))[0]
+    minit[placed] = placed
+    already = np.zeros(Mq, bool); already[placed] = True
+    sel = np.nonzero(~bad_q & ~already & inimg)[0]
+    _, fq, nm = oracle_mod.search_by_projection(kT, dT, bounds, uvq[sel, 0], uvq[sel, 1], (f32(8.0) * sf[lvq[sel]]).astype(f32),
+                                                lvq[sel] - 1, lvq[sel], dQ[sel], 1, 0.75, False,
+                                                feat_locked=(minit != -1).astype(np.uint8),
+                                                q_flags=np.full(len(sel), 3, np.uint8), th_dist=50)
+    exp["sim3_a"] = exp["sim3_b"] = (np.where(fq >= 0, sel[np.maximum(fq, 0)], minit), nm)
+    # 10. Fuse(pKF, vpMapPoints, 3.0): candidate scoring from the oracle, then the reference's Replace / Add rules
+    inv_sig = (f32(1.0) / sig).astype(f32)
+    sel = np.nonzero(has_q & ~bad_q & inimg)[0]
+    bi, bd = oracle_mod.fuse_candidates(kT, dT, bounds, inv_sig, uvq[sel, 0], uvq[sel, 1], (f32(3.0) * sf[lvq[sel]]).astype(f32),
+                                        lvq[sel], dQ[sel], u_right=uRT, q_ur=(uvq[sel, 0] - f32(40.0)).astype(f32))
+    state = {j: ("own", 1, bool(hfT[j] & 2)) for j in range(nT) if held[j]}   # feature -> (who, nObs, bad)
+    where = np.full(Mq, -1, np.int32)
+    nf = 0
+    for k_, i in enumerate(sel):
+        if bi[k_] < 0 or bd[k_] > 50:
+            continue
+        j = int(bi[k_]); nf += 1
+        if j in state:
+            who, nobs, isbad = state[j]
+            if not isbad:
+                if nobs > 1:                     # pMPinKF->Observations() > pMP->Observations(): the new point gives way
+                    where[i] = -3
+                else:                            # the held point is replaced by the new one, which takes its observation
+                    if who != "own":
+                        where[who] = -1          # (cannot happen: a query that holds a feature has 2 observations)
+                    state[j] = (int(i), 2, False); where[i] = j
+        else:
+            state[j] = (int(i), 2, False); where[i] = j
+    exp["fuse"] = (where, nf)
+    # 11. Fuse(pKF, Scw, vpPoints, 4.0, vpReplacePoint)
+    sel = np.nonzero(~bad_q & inimg)[0]
+    bi, bd = oracle_mod.fuse_candidates(kT, dT, bounds, np.zeros(8, f32), uvq[sel, 0], uvq[sel, 1],
+                                        (f32(4.0) * sf[lvq[sel]]).astype(f32), lvq[sel], dQ[sel])
+    holder = {j: (-2 - j, bool(hfT[j] & 2)) for j in range(nT) if held[j]}    # feature -> (id, bad)
+    where = np.full(Mq, -1, np.int32)
+    nf = 0
+    for k_, i in enumerate(sel):
+        if bi[k_] < 0 or bd[k_] > 50:
+            continue
+        j = int(bi[k_]); nf += 1
+        if j in holder:
+            hid, hbad = holder[j]
+            if not hbad:
+                where[i] = -2 - hid              # vpReplacePoint[i] = the holder (own point: its feature; query k: -2-k)
+        else:
+            holder[j] = (int(i), False); where[i] = j
+    exp["fuse_sim3"] = (where, nf)
+    # 12. SearchBySim3: both keyframes' points, scored both ways, agreement
+    (kA, dA), (kB, dB) = feats[0], feats[1]
+    sAB = pos[0] - pos[1]
+    uvA = np.stack([(kA["x"] + sAB[0]).astype(f32), (kA["y"] + sAB[1]).astype(f32)], 1)
+    uvB = np.stack([(kB["x"] - sAB[0]).astype(f32), (kB["y"] - sAB[1]).astype(f32)], 1)
+
+    def rng_of(uv, k):
+        dd = np.sqrt(uv[:, 0].astype(np.float64) ** 2 + uv[:, 1].astype(np.float64) ** 2 + 1.0)
+        return (dd * 1.2 ** (k["octave"].astype(np.int64) - 0.5)).astype(f32), (dd * 0.1).astype(f32)
+
+    mxA, mnA = rng_of(uvA, kA); mxB, mnB = rng_of(uvB, kB)
+    hfA = ((rng.random(len(kA)) < 0.85).astype(np.int32) | ((rng.random(len(kA)) < 0.05).astype(np.int32) << 1)).astype(np.int32)
+    hfB = ((rng.random(len(kB)) < 0.85).astype(np.int32) | ((rng.random(len(kB)) < 0.05).astype(np.int32) << 1)).astype(np.int32)
+    init12 = np.full(len(kA), -1, np.int32)
+    pre = rng.permutation(len(kA))[:60]
+    init12[pre] = rng.permutation(np.nonzero(hfB & 1)[0])[:60]
+    for k_, d_, hf_, uv_, mx_, mn_ in ((kA, dA, hfA, uvA, mxA, mnA), (kB, dB, hfB, uvB, mxB, mnB)):
+        w_feats(k_, d_); w(hf_, np.int32); w(uv_, f32); w(mx_, f32); w(mn_, f32)
+    w(init12, np.int32)
+
+    def direction(kq, dq, hfq, uv, skip, kt, dt):
+        ii = (uv[:, 0] >= 0) & (uv[:, 0] < 752) & (uv[:, 1] >= 0) & (uv[:, 1] < 480)
+        s_ = np.nonzero(((hfq & 1) > 0) & ((hfq & 2) == 0) & ~skip & ii)[0]
+        lv = kq["octave"][s_].astype(np.int64)
+        b_i, b_d = oracle_mod.fuse_candidates(kt, dt, bounds, np.zeros(8, f32), uv[s_, 0], uv[s_, 1],
+                                              (f32(7.5) * sf[lv]).astype(f32), lv, dq[s_])
+        o_ = np.full(len(kq), -1, np.int64)
+        ok_ = (b_i >= 0) & (b_d <= 100)
+        o_[s_[ok_]] = b_i[ok_]
+        return o_
+
+    skipA = init12 >= 0
+    skipB = np.zeros(len(kB), bool); skipB[init12[init12 >= 0]] = True
+    m1 = direction(kA, dA, hfA, uvA, skipA, kB, dB)
+    m2 = direction(kB, dB, hfB, uvB, skipB, kA, dA)
+    want = init12.astype(np.int64).copy()
+    agree = (m1 >= 0) & (m2[np.maximum(m1, 0)] == np.arange(len(kA)))
+    want[agree] = m1[agree]
+    exp["sim3_search"] = (want.astype(np.int32), int(agree.sum()))
+
     (tmp_path / "in.bin").write_bytes(b"".join(blob))
     out = subprocess.check_output([str(exe), str(tmp_path / "in.bin"), str(tmp_path / "o")], text=True)
     rets = [int(v) for v in out.split()]
-    order = ["proj_mono", "proj_rig", "proj_last", "bow_kf_f", "bow_kf_kf", "tri_pairs", "bow_kf_rig", "init_m12"]
+    order = ["proj_mono", "proj_rig", "proj_last", "bow_kf_f", "bow_kf_kf", "tri_pairs", "bow_kf_rig", "init_m12", "reloc",
+             "sim3_a", "sim3_b", "fuse", "fuse_sim3", "sim3_search"]
     assert len(rets) == len(order)
     for name, ret in zip(order, rets):
         want, nm = exp[name]
