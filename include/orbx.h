@@ -124,6 +124,14 @@ int orbx_last_outputs_device(orbx_handle h, const orbx_keypoint** d_kps, const u
  * the reference's ROI (19-px BORDER_REFLECT_101 ring, ORBextractor.cc:1185-1191). */
 int orbx_get_pyramid(orbx_handle h, int frame, int level, uint8_t* dst, size_t dst_stride,
                      int with_border);
+
+/* Every level of frame `frame` in ONE device->host transfer (what the compat operator() needs to
+ * refill mvImagePyramid, ORBextractor.h:83 / ORBextractor.cc:1170-1195): *host_base = a pinned host
+ * buffer owned by the handle and valid until the next call on it; level l starts at offsets[l] with
+ * row stride strides[l] (= w_l + 38 with the 19-px REFLECT_101 ring when with_border, else w_l).
+ * offsets / strides must hold nlevels entries. */
+int orbx_get_pyramid_all(orbx_handle h, int frame, int with_border, const uint8_t** host_base,
+                         size_t* offsets, size_t* strides);
 /* Device view of the same level (border-free). */
 int orbx_pyramid_device(orbx_handle h, int frame, int level, const uint8_t** d_ptr,
                         size_t* pitch, int* width, int* height);

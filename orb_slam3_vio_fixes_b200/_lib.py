@@ -35,7 +35,7 @@ RES_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i2"), ("second_dist",
 # every symbol include/orbx.h declares (tests/test_abi.py checks the library exports them all)
 SYMBOLS = [
     "orbx_create", "orbx_destroy", "orbx_max_keypoints", "orbx_extract", "orbx_extract_batch_device",
-    "orbx_extract_batch_host", "orbx_last_outputs_device", "orbx_get_pyramid", "orbx_pyramid_device", "orbx_level_size",
+    "orbx_extract_batch_host", "orbx_last_outputs_device", "orbx_get_pyramid", "orbx_get_pyramid_all", "orbx_pyramid_device", "orbx_level_size",
     "orbx_get_scale_tables", "orbx_stage_times", "orbx_check_status", "orbx_debug_blur_level", "orbx_debug_sincos_checksum", "orbx_debug_level_keypoints", "orbx_debug_octree", "orbm_argmin2_csr", "orbm_grid_build",
     "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_search_by_projection_th", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
     "orbm_fuse_candidates", "orbm_descriptor_distance_pairs", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
@@ -116,6 +116,7 @@ def lib():
     L.orbx_extract_batch_host.argtypes = [vp, vp, i32, i32, i32, vp, vp, i32, vp, vp]
     L.orbx_last_outputs_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(i32)]
     L.orbx_get_pyramid.argtypes = [vp, i32, i32, vp, sz, i32]
+    L.orbx_get_pyramid_all.argtypes = [vp, i32, i32, C.POINTER(vp), vp, vp]
     L.orbx_pyramid_device.argtypes = [vp, i32, i32, C.POINTER(vp), C.POINTER(sz), C.POINTER(i32), C.POINTER(i32)]
     L.orbx_level_size.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32)]
     L.orbx_get_scale_tables.argtypes = [vp, vp, vp, vp, vp, vp]

@@ -50,6 +50,8 @@ struct orbx_extractor_s {
   uint8_t* o_desc = nullptr;
   int32_t *o_n = nullptr, *o_mono = nullptr;
   uint8_t* border_tmp = nullptr;
+  // orbx_get_pyramid_all: every level of one frame, packed, on the device and in pinned host memory
+  uint8_t* pyr_stage_d = nullptr; uint8_t* pyr_stage_h = nullptr; size_t pyr_stage_bytes = 0;
   uint8_t* stage = nullptr;  // tightly packed level-0 frames of the host batch API (lazy)
   uint8_t* blur = nullptr;   // blurred levels (arena layout) in level-blur mode
   bool level_blur = false;
@@ -147,6 +149,7 @@ void orbx_destroy(orbx_handle h) {
   cudaFree(h->gkeys); cudaFree(h->glabels); cudaFree(h->sel); cudaFree(h->sel_cnt); cudaFree(h->dst);
   cudaFree(h->status); cudaFree(h->o_kps); cudaFree(h->o_desc); cudaFree(h->o_n); cudaFree(h->o_mono);
   cudaFree(h->border_tmp); cudaFree(h->stage); cudaFree(h->blur);
+  cudaFree(h->pyr_stage_d); if (h->pyr_stage_h) cudaFreeHost(h->pyr_stage_h);
   for (int i = 0; i <= ORBX_NUM_STAGES; i++)
     if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
@@ -587,6 +590,52 @@ int orbx_get_pyramid(orbx_handle h, int frame, int level, uint8_t* dst, size_t d
     CU(cudaMemcpy2DAsync(dst, dst_stride, h->border_tmp, bw, bw, bh, cudaMemcpyDeviceToHost, h->stream));
   }
   CU(cudaStreamSynchronize(h->stream));
+  return ORBX_OK;
+}
+
+// All levels of one frame in ONE device->host transfer: the levels (with their 19-px REFLECT_101 ring when
+// with_border) are packed into a device staging buffer by L small kernels / copies and land in a pinned host buffer
+// owned by the handle.  This is what the compat operator() needs after every call (mvImagePyramid, ORBextractor.h:83);
+// eight orbx_get_pyramid calls cost eight synchronisations.
+int orbx_get_pyramid_all(orbx_handle h, int frame, int with_border, const uint8_t** host_base, size_t* offsets,
+                         size_t* strides) {
+  if (!h || !host_base || !offsets || !strides || frame < 0 || frame >= h->cfg.max_batch) return ORBX_E_INVALID;
+  const OrbxPlan& P = h->plan;
+  const int e = with_border ? ORBX_EDGE : 0;
+  size_t total = 0;
+  for (int l = 0; l < P.nlevels; l++) {
+    offsets[l] = total;
+    strides[l] = (size_t)(P.lv[l].w + 2 * e);
+    total += ((strides[l] * (size_t)(P.lv[l].h + 2 * e)) + 63) & ~(size_t)63;
+  }
+  CU(cudaSetDevice(h->device));
+  if (h->pyr_stage_bytes < total) {
+    cudaFree(h->pyr_stage_d); h->pyr_stage_d = nullptr;
+    if (h->pyr_stage_h) { cudaFreeHost(h->pyr_stage_h); h->pyr_stage_h = nullptr; }
+    h->pyr_stage_bytes = 0;
+    // both ring modes fit in the bordered size
+    size_t cap = 0;
+    for (int l = 0; l < P.nlevels; l++)
+      cap += (((size_t)(P.lv[l].w + 2 * ORBX_EDGE) * (size_t)(P.lv[l].h + 2 * ORBX_EDGE)) + 63) & ~(size_t)63;
+    if (cudaMalloc(&h->pyr_stage_d, cap) != cudaSuccess) { cudaGetLastError(); return ORBX_E_NOMEM; }
+    if (cudaHostAlloc((void**)&h->pyr_stage_h, cap, cudaHostAllocDefault) != cudaSuccess) {
+      cudaGetLastError(); cudaFree(h->pyr_stage_d); h->pyr_stage_d = nullptr; return ORBX_E_NOMEM;
+    }
+    h->pyr_stage_bytes = cap;
+  }
+  CU(cudaDeviceSynchronize());  // the last call may have run on a caller stream
+  for (int l = 0; l < P.nlevels; l++) {
+    const uint8_t* p; size_t pitch; int w, hh;
+    const int rc = orbx_pyramid_device(h, frame, l, &p, &pitch, &w, &hh);
+    if (rc) return rc;
+    if (with_border)
+      CU(orbx_launch_border(p, (int)pitch, w, hh, h->pyr_stage_d + offsets[l], (int)strides[l], h->stream));
+    else
+      CU(cudaMemcpy2DAsync(h->pyr_stage_d + offsets[l], strides[l], p, pitch, w, hh, cudaMemcpyDeviceToDevice, h->stream));
+  }
+  CU(cudaMemcpyAsync(h->pyr_stage_h, h->pyr_stage_d, total, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  *host_base = h->pyr_stage_h;
   return ORBX_OK;
 }
 

@@ -208,6 +208,23 @@ class ORBextractor:
                    "orbx_get_pyramid")
         return out
 
+    def GetPyramidAll(self, with_border=True, frame=0):
+        """Every level of the last call in one device->host transfer (orbx_get_pyramid_all): list of level images
+        (copies of the handle's pinned staging buffer)."""
+        L = _lib.lib()
+        base = C.c_void_p()
+        ofs = (C.c_size_t * self.nlevels)()
+        strd = (C.c_size_t * self.nlevels)()
+        _lib.check(L.orbx_get_pyramid_all(self._h, frame, int(with_border), C.byref(base), ofs, strd), "orbx_get_pyramid_all")
+        out = []
+        for level in range(self.nlevels):
+            w, h = self.level_size(level)
+            if with_border:
+                w, h = w + 38, h + 38
+            buf = (C.c_uint8 * (h * strd[level])).from_address(base.value + ofs[level])
+            out.append(np.frombuffer(buf, np.uint8).reshape(h, strd[level])[:, :w].copy())
+        return out
+
     @property
     def mvImagePyramid(self):
         """Level images of the last call, each a view into its bordered parent like the reference's

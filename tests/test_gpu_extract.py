@@ -297,3 +297,19 @@ def test_two_handles_from_two_threads(oracle_mod):
         for j, (mono, k, d) in enumerate(res[i]):
             wk, wd, wm = want[j % 3]
             assert mono == wm and np.array_equal(k, wk) and np.array_equal(d, wd), (i, j)
+
+
+def test_get_pyramid_all_equals_per_level_copies(oracle_mod):
+    """orbx_get_pyramid_all (one device->host transfer for mvImagePyramid) == orbx_get_pyramid level by level == oracle,
+    with and without the 19-px REFLECT_101 ring."""
+    img = S.make_frames("C3", 1)[0]
+    ex = ORBextractor(1000, **ORB)
+    ex(img, None, (0, 0))
+    orc = oracle_mod.Extractor(1000)
+    orc.extract(img, (0, 0))
+    for border in (True, False):
+        levels = ex.GetPyramidAll(with_border=border)
+        assert len(levels) == 8
+        for l, a in enumerate(levels):
+            assert np.array_equal(a, ex.GetPyramid(l, with_border=border))
+            assert np.array_equal(a, orc.pyramid(l, border))
