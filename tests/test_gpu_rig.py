@@ -228,3 +228,37 @@ def test_search_by_bow_rig(rig, oracle_mod):
             tot += nm
             assert (m12r >= 0).sum() > 50 and (m12l >= 0).sum() > 50
         assert tot > P * 150
+
+
+import os  # noqa: E402
+
+
+@pytest.mark.parametrize("seed", range(int(os.environ.get("ORBX_STRESS_SEEDS", "3"))))
+def test_search_by_projection_rig_random_sweep(rig, oracle_mod, seed):
+    """Randomised configurations of the rig projection search (both variants): lock density, pair fraction, duplicated
+    and unobserved MapPoints (the rescan and 'entry lock lost' paths), radius, ratio.  ORBX_STRESS_SEEDS widens it."""
+    rng = np.random.default_rng(1000 + seed)
+    B = rig["B"]
+    cap = rig["ol"]["kps"].shape[1]
+    nl, nr = rig["L"][2], rig["R"][2]
+    th = float(rng.choice([4.0, 8.0, 12.0, 20.0, 30.0]))
+    dup = int(rng.choice([1, 1, 2, 3]))
+    unl = float(rng.choice([0.0, 0.2, 0.6]))
+    lock = float(rng.choice([0.0, 0.15, 0.5]))
+    pf = float(rng.choice([0.0, 0.4, 0.9]))
+    nn = float(rng.choice([0.6, 0.8, 0.95]))
+    qs = [_queries(rig, f, rng, th, (-1, 0), float(rng.choice([0.0, 0.1, 0.4])), float(rng.choice([0.0, 0.15, 0.4])), unl,
+                   dup=dup) for f in range(B)]
+    pairs = [_pairs(nl[f], nr[f], rng, pf) for f in range(B)]
+    locked = ((rng.random((B, cap)) < lock).astype(np.uint8), (rng.random((B, cap)) < lock).astype(np.uint8))
+    tot, _ = _run(rig, oracle_mod, _lib.PROJ_MAPPOINTS, qs, nn, False, locked, pairs)
+    assert tot > 0
+    qs2 = []
+    for f in range(B):
+        q = _queries(rig, f, rng, th, (-1, 1), float(rng.choice([0.0, 0.2])), 0.0, unl, dup=dup)
+        q["flags"] |= 4
+        rot = rng.random(len(q["angle"])) < 0.05
+        q["angle"] = np.where(rot, (q["angle"] + np.float32(95.0)) % np.float32(360.0), q["angle"]).astype(np.float32)
+        qs2.append(q)
+    tot2, _ = _run(rig, oracle_mod, _lib.PROJ_LASTFRAME, qs2, 0.9, bool(rng.integers(0, 2)), locked)
+    assert tot2 > 0
