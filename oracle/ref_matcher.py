@@ -217,6 +217,25 @@ def fuse(kps, desc, holder_flags, u_right, bounds, sf, sigma2, bf, mp_flags, uv,
     return best, nf
 
 
+def fuse_sim3(kps, desc, holder_flags, held_bad, bounds, sf, mp_flags, own_feat, uv, max_dist, min_dist, qdesc, th):
+    """ORBmatcher::Fuse(KeyFrame*, Sim3f&, vpPoints, th, vpReplacePoint) (ORBmatcher.cc:1340-1455).
+    Returns (best_idx [M], replaced [M], nFused).  A point that replaced through a feature taken over by another query
+    point i' reports -3 - i'."""
+    k = np.ascontiguousarray(kps)
+    a = dict(d=_u8(desc), h=_u8(holder_flags), hb=_u8(held_bad), b=_f32(bounds), s=_f32(sf), f=_u8(mp_flags),
+             o=_i32(own_feat), uv=_f32(uv), mx=_f32(max_dist), mn=_f32(min_dist), q=_u8(qdesc))
+    M = a["f"].size
+    best, repl = np.zeros(M, np.int32), np.zeros(M, np.uint8)
+    L = lib()
+    L.ref_fuse_sim3.restype = C.c_int
+    L.ref_fuse_sim3.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                C.c_int] + [C.c_void_p] * 6 + [C.c_float, C.c_void_p, C.c_void_p]
+    nf = L.ref_fuse_sim3(_p(k), _p(a["d"]), k.size, _p(a["h"]), _p(a["hb"]), _p(a["b"]), _p(a["s"]), a["s"].size, M,
+                         _p(a["f"]), _p(a["o"]), _p(a["uv"]), _p(a["mx"]), _p(a["mn"]), _p(a["q"]), float(th), _p(best),
+                         _p(repl))
+    return best, repl, nf
+
+
 def search_by_projection_sim3(variant, kps, desc, bounds, sf, matched_init, mp_flags, uv, max_dist, min_dist, qdesc, th,
                               ratio_hamming):
     """ORBmatcher::SearchByProjection(KeyFrame*, Sim3, ...) (variant 0: :427-532, 1: :534-646).

@@ -559,6 +559,50 @@ int ref_fuse(const void* kps, const uint8_t* desc, int n, const uint8_t* holder_
   return nf;
 }
 
+// Fuse(KeyFrame *pKF, Sophus::Sim3f &Scw, vpPoints, th, vpReplacePoint)  ORBmatcher.cc:1340-1455 (loop closing).
+// Scw = identity; points as in ref_fuse.  mp_flags bit1 = isBad, bit2 = the point is already one of the keyframe's
+// own (it takes over feature own_feat[i] before the call, so spAlreadyFound holds it).  held_bad[j] = the point
+// held by feature j isBad() (then vpReplacePoint stays empty but nFused still counts, :1440-1449).
+// best_idx[i] = feature the point was fused into (-1 none); replaced[i] = 1 when that went through vpReplacePoint.
+int ref_fuse_sim3(const void* kps, const uint8_t* desc, int n, const uint8_t* holder_flags, const uint8_t* held_bad,
+                  const float* bounds, const float* scale_factors, int nlevels, int M, const uint8_t* mp_flags,
+                  const int* own_feat, const float* uv, const float* max_dist, const float* min_dist,
+                  const uint8_t* qdesc, float th, int* best_idx, uint8_t* replaced) {
+  KeyFrame K;
+  std::vector<MapPoint> held;
+  std::vector<float> sig(nlevels, 1.f);
+  fill_keyframe(K, held, kps, desc, n, -1, holder_flags, nullptr, nullptr, nullptr, 0, nullptr, bounds, scale_factors,
+                sig.data(), nlevels);
+  GeometricCamera cam;
+  K.mpCamera = &cam; K.fx = 1; K.fy = 1; K.cx = 0; K.cy = 0;
+  for (int j = 0; j < n; j++) { held[j].id = -2 - j; held[j].mbBad = held_bad && held_bad[j]; }
+  std::vector<MapPoint> pts(M);
+  std::vector<MapPoint*> vp(M), repl(M, static_cast<MapPoint*>(NULL));
+  for (int i = 0; i < M; i++) {
+    pts[i].id = i; pts[i].nObs = 1;
+    pts[i].mbBad = (mp_flags[i] & 2) != 0;
+    pts[i].mWorldPos = Eigen::Vector3f(uv[2 * i], uv[2 * i + 1], 1.f);
+    const float nrm = std::sqrt(uv[2 * i] * uv[2 * i] + uv[2 * i + 1] * uv[2 * i + 1] + 1.f);
+    pts[i].mNormalVector = Eigen::Vector3f(uv[2 * i] / nrm, uv[2 * i + 1] / nrm, 1.f / nrm);
+    pts[i].mfMaxDistance = max_dist[i]; pts[i].mfMinDistance = min_dist[i];
+    pts[i].mDescriptor = desc_row(qdesc + (size_t)i * 32);
+    vp[i] = &pts[i];
+    if ((mp_flags[i] & 4) && own_feat[i] >= 0 && own_feat[i] < n) K.mvpMapPoints[own_feat[i]] = &pts[i];
+    best_idx[i] = -1; replaced[i] = 0;
+  }
+  std::vector<MapPoint::Op> log;
+  MapPoint::oplog = &log;
+  Sophus::Sim3f Scw;
+  ORBmatcher matcher(0.8f);
+  const int nf = matcher.Fuse(&K, Scw, vp, th, repl);
+  MapPoint::oplog = nullptr;
+  for (const MapPoint::Op& op : log)
+    if (op.kind == 1 && op.other >= 0) best_idx[op.other] = op.idx;
+  for (int i = 0; i < M; i++)
+    if (repl[i]) { best_idx[i] = repl[i]->id <= -2 ? -2 - repl[i]->id : -3 - repl[i]->id; replaced[i] = 1; }
+  return nf;
+}
+
 // SearchByProjection(KeyFrame* pKF, Sophus::Sim3f &Scw, vpPoints, vpMatched, th, ratioHamming)  ORBmatcher.cc:427-532
 // (variant 0) and its twin with vpPointsKFs / vpMatchedKF :534-646 (variant 1).  Scw = identity with scale 1, unit
 // pinhole, point i at world (u_i, v_i, 1) with its normal towards the camera.  matched_init[j] = query point held by

@@ -342,6 +342,60 @@ def test_fuse_candidates(oracle_mod, RM, data):
     assert np.array_equal(best, want)
 
 
+@pytest.mark.parametrize("th", [3.0, 6.0])
+def test_fuse_sim3(oracle_mod, RM, data, th):
+    """ORBmatcher::Fuse(KeyFrame*, Sim3f&, vpPoints, th, vpReplacePoint) (ORBmatcher.cc:1340-1455): no chi-square gate,
+    band [l-1, l], best <= TH_LOW; a feature that holds a point answers through vpReplacePoint (nothing recorded when
+    that point is bad, still counted), a free one is taken by the fused point — and later points see it as held."""
+    rng = np.random.default_rng(23)
+    sf, pos = data["sf"], data["pos"]
+    (kK, dK), (kQ, dQ) = data["mono"][1], data["mono"][0]
+    shv = pos[0] - pos[1]
+    M, n = len(kQ), len(kK)
+    # every point twice: the second copy finds the feature its twin has just taken
+    kQ, dQ = np.concatenate([kQ, kQ]), np.concatenate([dQ, dQ])
+    M *= 2
+    uv = np.stack([(kQ["x"] + shv[0]).astype(f32), (kQ["y"] + shv[1]).astype(f32)], 1)
+    dist = np.sqrt(uv[:, 0].astype(np.float64) ** 2 + uv[:, 1].astype(np.float64) ** 2 + 1.0)
+    level = kQ["octave"].astype(np.int64)
+    max_dist, min_dist = (dist * 1.2 ** (level - 0.5)).astype(f32), (dist * 0.1).astype(f32)
+    mp_flags = ((rng.random(M) < 0.05).astype(np.uint8) << 1).astype(np.uint8)
+    own = rng.random(M) < 0.1
+    own_feat = np.full(M, -1, np.int32)
+    own_feat[own] = rng.permutation(n)[:int(own.sum())]
+    mp_flags[own] |= 4
+    holder_flags = (rng.random(n) < 0.4).astype(np.uint8)
+    holder_flags[own_feat[own]] = 0
+    held_bad = ((rng.random(n) < 0.15) & (holder_flags > 0)).astype(np.uint8)
+    best, repl, nf = RM.fuse_sim3(kK, dK, holder_flags, held_bad, BOUNDS, sf, mp_flags, own_feat, uv, max_dist, min_dist,
+                                  dQ, th)
+    bad = (mp_flags & 2) > 0
+    inimg = (uv[:, 0] >= BOUNDS[0]) & (uv[:, 0] < BOUNDS[1]) & (uv[:, 1] >= BOUNDS[2]) & (uv[:, 1] < BOUNDS[3])
+    sel = np.nonzero(~bad & ~(own & ~bad) & inimg)[0]      # spAlreadyFound holds the keyframe's own non-bad points
+    lv = level[sel]
+    bi, bd = oracle_mod.fuse_candidates(kK, dK, BOUNDS, np.zeros(8, f32), uv[sel, 0], uv[sel, 1],
+                                        (f32(th) * sf[lv]).astype(f32), lv, dQ[sel])
+    holder = np.full(n, -1, np.int64)                      # -1 free, -2 held by a foreign point, i >= 0 by query point i
+    holder[holder_flags > 0] = -2
+    holder[own_feat[own]] = np.nonzero(own)[0]
+    want, wrepl, wnf = np.full(M, -1, np.int32), np.zeros(M, np.uint8), 0
+    for i, j, d in zip(sel, bi, bd):
+        if j < 0 or d > 50:
+            continue
+        wnf += 1
+        if holder[j] == -1:
+            holder[j] = i
+            want[i] = j
+        elif holder[j] == -2:
+            if not held_bad[j]:
+                want[i], wrepl[i] = j, 1
+        elif not bad[holder[j]]:
+            want[i], wrepl[i] = -3 - holder[j], 1
+    assert nf == wnf > 400
+    assert np.array_equal(best, want) and np.array_equal(repl, wrepl)
+    assert (wrepl > 0).sum() > 100 and (want <= -3).sum() > 50
+
+
 @pytest.mark.parametrize("variant,th,ratio", [(0, 8, 1.0), (1, 4, 1.5), (0, 5, 0.8)])
 def test_search_by_projection_sim3(oracle_mod, RM, data, variant, th, ratio):
     """ORBmatcher.cc:427-532 / :534-646 (loop closing / merging): KeyFrame grid without level filter, band [l-1, l]
