@@ -401,6 +401,187 @@ k_describe_lite(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __r
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// k_describe_lite4: the same work with LITE_KPW keypoints per warp.  The orientation chain (fastAtan2 + the
+// glibc-exact sincosf, ~225 warp instructions, a quarter of k_describe_lite) is a scalar computation per
+// keypoint: here lane g evaluates it for keypoint g, so one pass of the chain serves LITE_KPW keypoints.  The
+// slot -> level lookup and the result-slot fetch are lane-parallel too; window words are addressed
+// incrementally (i -> i+32 is "three rows down, one word left" on an 11-word row) instead of by a division per
+// load; the blurred window of keypoint g+1 is on its way while keypoint g is being sampled.
+// ------------------------------------------------------------------------------------------------
+#define LITE_KPW 4
+
+template <bool STRICT_FP>
+__global__ void __launch_bounds__(DESC_WARPS * 32)
+k_describe_lite4(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
+                 const uint8_t* __restrict__ blur, const uint32_t* __restrict__ sel,
+                 const int32_t* __restrict__ sel_cnt, const int32_t* __restrict__ dst,
+                 OrbxKeyPointDev* __restrict__ kps, uint8_t* __restrict__ desc, int capacity) {
+  __shared__ __align__(16) uint32_t s_win[DESC_WARPS][LITE_WORDS + 3];
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int frame = blockIdx.y;
+  const int slot0 = (blockIdx.x * DESC_WARPS + warp) * LITE_KPW;
+  if (slot0 >= P.kp_total_cap) return;
+
+  // ---- header, lane-parallel: lane handles keypoint gl = lane % LITE_KPW of the warp's group
+  const int gl = lane & (LITE_KPW - 1);
+  const int slot_l = slot0 + gl;
+  int level_l = 0;
+#pragma unroll
+  for (int l = 1; l < ORBX_PLAN_MAX_LEVELS; l++)
+    if (l < P.nlevels && slot_l >= P.lv[l].kp_base) level_l = l;
+  uint32_t key_l = 0;
+  int dst_l = -1;
+  bool valid_l = slot_l < P.kp_total_cap;
+  if (valid_l) valid_l = slot_l - P.lv[level_l].kp_base < sel_cnt[frame * P.nlevels + level_l];
+  if (valid_l) {
+    key_l = sel[(long long)frame * P.kp_total_cap + slot_l];
+    dst_l = dst[(long long)frame * P.kp_total_cap + slot_l];
+    valid_l = dst_l >= 0 && dst_l < capacity;  // a keypoint without a result slot is never written
+  }
+  const unsigned vmask = __ballot_sync(FULL, valid_l) & ((1u << LITE_KPW) - 1u);
+  if (vmask == 0) return;
+
+  // ---- IC_Angle moments of every keypoint of the group (ORBextractor.cc:76-103)
+  int my01 = 0, my10 = 0;  // the sums of keypoint gl
+#pragma unroll
+  for (int g = 0; g < LITE_KPW; g++) {
+    if (!((vmask >> g) & 1u)) continue;
+    const uint32_t key = __shfl_sync(FULL, key_l, g);
+    const int level = __shfl_sync(FULL, level_l, g);
+    const DevLevel& L = P.lv[level];
+    const int kx = ORBX_KEY_X(key), ky = ORBX_KEY_Y(key);
+    int pitch;
+    const uint8_t* img;
+    if (level == 0) { pitch = l0.pitch; img = l0.base + (long long)frame * l0.frame_stride; }
+    else { pitch = L.pitch; img = arena + (long long)frame * P.arena_bytes + L.offset; }
+    int m01 = 0, m10 = 0;
+    if ((pitch & 3) == 0 && ((uintptr_t)img & 3) == 0) {
+      const int xa = kx - ORBX_HALF_PATCH, sh = xa & 3;
+      // word i = 9 r + j of the 31 x 36-byte window; i -> i + 32: j + 5 (mod 9), three rows down (four on the wrap)
+      const int r0 = (lane * 57) >> 9;
+      int j = lane - 9 * r0;
+      const uint8_t* q = img + (long long)(ky - ORBX_HALF_PATCH + r0) * pitch + (xa - sh) + 4 * j;
+      const int step = 3 * pitch + 20, wrap = pitch - 36;
+      const uint32_t* wu = g_mom_wu + sh * MOM_STRIDE + lane;
+      const uint32_t* wv = g_mom_wv + sh * MOM_STRIDE + lane;
+#pragma unroll
+      for (int t = 0; t < 9; t++) {
+        if (t < 8 || lane + 32 * 8 < MOM_WORDS) {
+          const uint32_t px = __ldg(reinterpret_cast<const uint32_t*>(q));
+          m10 = dp4a_us(px, __ldg(wu + 32 * t), m10);
+          m01 = dp4a_us(px, __ldg(wv + 32 * t), m01);
+        }
+        q += step;
+        j += 5;
+        if (j >= 9) { j -= 9; q += wrap; }
+      }
+    } else if (lane < 31) {
+      const int v = lane - ORBX_HALF_PATCH, av = v < 0 ? -v : v;
+      const uint8_t* rowp = img + (long long)(ky + v) * pitch + kx;
+      const int d = P.umax[av];
+      int s = 0, su = 0;
+      for (int u = -d; u <= d; u++) {
+        const int val = rowp[u];
+        s += val;
+        su += u * val;
+      }
+      m10 = su;
+      m01 = v * s;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      m01 += __shfl_xor_sync(FULL, m01, o);
+      m10 += __shfl_xor_sync(FULL, m10, o);
+    }
+    if (gl == g) { my01 = m01; my10 = m10; }
+  }
+
+  // ---- orientation of keypoint gl on lane gl (lanes >= LITE_KPW repeat it), :103 and the rotation of :107-146
+  const float angle_l = orbx_fast_atan2((float)my01, (float)my10);
+  const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
+  float a_l, b_l;
+  orbx_sincosf(f_mul(angle_l, factorPI), &b_l, &a_l);
+
+  // ---- blurred 39x39 windows -> shared memory -> rotated BRIEF, one keypoint after the other
+  uint32_t bw[14];
+  auto fetch_window = [&](int g) {
+    const uint32_t key = __shfl_sync(FULL, key_l, g);
+    const int level = __shfl_sync(FULL, level_l, g);
+    const DevLevel& L = P.lv[level];
+    const int kx = ORBX_KEY_X(key), ky = ORBX_KEY_Y(key);
+    const int bp = L.pitch, xb = kx - 19, shb = xb & 3;
+    // word i = 11 r + j of the 39 x 44-byte window; i -> i + 32: j - 1 (mod 11), three rows down (two on the wrap)
+    const int r0 = (lane * 745) >> 13;
+    int j = lane - BW * r0;
+    const uint8_t* q = blur + (long long)frame * P.arena_bytes + L.offset + (long long)(ky - 19 + r0) * bp + (xb - shb) + 4 * j;
+    const int step = 3 * bp - 4, wrap = 44 - bp;
+#pragma unroll
+    for (int t = 0; t < 14; t++) {
+      bw[t] = 0;
+      if (t < 13 || lane + 32 * 13 < LITE_WORDS) bw[t] = __ldg(reinterpret_cast<const uint32_t*>(q));
+      q += step;
+      if (--j < 0) { j = BW - 1; q += wrap; }
+    }
+  };
+  const float kMagic = 12582912.0f;  // cvRound through the mantissa, see k_describe
+  const uint32_t kBias = 0x4B400000u * (uint32_t)(BW * 4 + 1);
+  int g = __ffs(vmask) - 1;
+  fetch_window(g);
+  while (g >= 0) {
+    const unsigned rest = vmask & ~((2u << g) - 1u);
+    const int gn = rest ? __ffs(rest) - 1 : -1;
+#pragma unroll
+    for (int t = 0; t < 14; t++)
+      if (t < 13 || lane + 32 * 13 < LITE_WORDS) s_win[warp][lane + 32 * t] = bw[t];
+    __syncwarp();
+    if (gn >= 0) fetch_window(gn);  // in flight while this keypoint is sampled
+    const uint32_t key = __shfl_sync(FULL, key_l, g);
+    const int level = __shfl_sync(FULL, level_l, g);
+    const int d = __shfl_sync(FULL, dst_l, g);
+    const float angle = __shfl_sync(FULL, angle_l, g);
+    const float a = __shfl_sync(FULL, a_l, g), b = __shfl_sync(FULL, b_l, g);
+    const DevLevel& L = P.lv[level];
+    const int kx = ORBX_KEY_X(key), ky = ORBX_KEY_Y(key);
+    const int shb = (kx - 19) & 3;
+    const uint8_t* centre = reinterpret_cast<const uint8_t*>(s_win[warp]) + 19 * (BW * 4) + 19 + shb;
+    uint32_t word_mine = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const float4 pt = __ldg(reinterpret_cast<const float4*>(c_patf) + 32 * j + lane);
+      float fy0, fx0, fy1, fx1;
+      if (STRICT_FP) {
+        fy0 = f_add(f_mul(pt.x, b), f_mul(pt.y, a)); fx0 = f_sub(f_mul(pt.x, a), f_mul(pt.y, b));
+        fy1 = f_add(f_mul(pt.z, b), f_mul(pt.w, a)); fx1 = f_sub(f_mul(pt.z, a), f_mul(pt.w, b));
+      } else {
+        fy0 = f_fma(pt.x, b, f_mul(pt.y, a)); fx0 = f_fma(pt.x, a, -f_mul(pt.y, b));
+        fy1 = f_fma(pt.z, b, f_mul(pt.w, a)); fx1 = f_fma(pt.z, a, -f_mul(pt.w, b));
+      }
+      const uint32_t i0 = __float_as_uint(f_add(fy0, kMagic)) * (uint32_t)(BW * 4) + __float_as_uint(f_add(fx0, kMagic)) - kBias;
+      const uint32_t i1 = __float_as_uint(f_add(fy1, kMagic)) * (uint32_t)(BW * 4) + __float_as_uint(f_add(fx1, kMagic)) - kBias;
+      const int v0 = centre[(int)i0], v1 = centre[(int)i1];
+      const uint32_t wd = __ballot_sync(FULL, v0 < v1);
+      if (lane == j) word_mine = wd;
+    }
+    const long long o = (long long)frame * capacity + d;
+    if (lane < 8) reinterpret_cast<uint32_t*>(desc + o * 32)[lane] = word_mine;
+    if (lane == 8) {
+      OrbxKeyPointDev kp;
+      kp.x = (float)kx; kp.y = (float)ky;
+      if (level != 0) { kp.x = f_mul(kp.x, L.scale); kp.y = f_mul(kp.y, L.scale); }
+      kp.size = L.patch_size;
+      kp.angle = angle;
+      kp.response = (float)ORBX_KEY_S(key);
+      kp.octave = level;
+      kp.class_id = -1;
+      kps[o] = kp;
+    }
+    __syncwarp();  // every lane has sampled before the next window overwrites the buffer
+    g = gn;
+  }
+}
+
 // Fills the row-task and moment-weight tables from the plan's umax table (once per process; the table is a constant of the
 // algorithm, ORBextractor.cc:453-468).
 static const float h_patf[1024] = {
@@ -452,6 +633,13 @@ cudaError_t orbx_launch_describe_lite(const DevPlan& P, Level0 l0, const uint8_t
                                       const uint32_t* sel, const int32_t* sel_cnt, const int32_t* dst,
                                       OrbxKeyPointDev* kps, uint8_t* desc, int capacity, int strict_fp, int batch,
                                       cudaStream_t st) {
+  static const int kpw = [] { const char* e = getenv("ORBX_DESC_KPW"); return e ? atoi(e) : LITE_KPW; }();
+  if (kpw == LITE_KPW) {
+    dim3 grd((P.kp_total_cap + DESC_WARPS * LITE_KPW - 1) / (DESC_WARPS * LITE_KPW), batch);
+    if (strict_fp) k_describe_lite4<true><<<grd, DESC_WARPS * 32, 0, st>>>(P, l0, arena, blur, sel, sel_cnt, dst, kps, desc, capacity);
+    else k_describe_lite4<false><<<grd, DESC_WARPS * 32, 0, st>>>(P, l0, arena, blur, sel, sel_cnt, dst, kps, desc, capacity);
+    return cudaGetLastError();
+  }
   dim3 grd((P.kp_total_cap + DESC_WARPS - 1) / DESC_WARPS, batch);
   if (strict_fp) k_describe_lite<true><<<grd, DESC_WARPS * 32, 0, st>>>(P, l0, arena, blur, sel, sel_cnt, dst, kps, desc, capacity);
   else k_describe_lite<false><<<grd, DESC_WARPS * 32, 0, st>>>(P, l0, arena, blur, sel, sel_cnt, dst, kps, desc, capacity);

@@ -23,8 +23,8 @@ for r in rows:
             key = fname + ':other'
             for nm, (a, b) in regs:
                 if a <= ln <= b: key = nm
-            lines[ln][0] += int(r[iEx]); lines[ln][1] += int(r[iS] or 0); lines[ln][2] = r[hdr.index('Source')]
-        agg[key][0] += int(r[iEx]); agg[key][1] += int(r[iS] or 0)
+            lines[ln][0] += int(r[iEx]); lines[ln][1] += int(r[iS]) if r[iS].strip().isdigit() else 0; lines[ln][2] = r[hdr.index('Source')]
+        agg[key][0] += int(r[iEx]); agg[key][1] += int(r[iS]) if r[iS].strip().isdigit() else 0
 tot = sum(v[0] for v in agg.values()); ts = sum(v[1] for v in agg.values()) or 1
 print("total warp-instructions", tot, "samples", ts)
 for k, v in sorted(agg.items(), key=lambda kv: -kv[1][0]):
