@@ -21,6 +21,14 @@
 // rebuilds it from the two aligned words that hold its four reflected columns (one PRMT, selector per lane).
 #include "orbx_kernels.cuh"
 
+#ifndef BL_PTR
+#define BL_PTR 1   // 1: row-pointer walk in the interior variant, 2: in the edge variant too, 0: off
+#endif
+#ifndef BL_MINB
+#define BL_MINB 8  // 64 registers: unconstrained ptxas takes 94 and the walk loses its latency cover (0.96 -> 0.91 ms describe stage
+                   // at C1 with the cap, the row pointer and the packed tap constants together; profiles/r2ag_blur_variants.txt)
+#endif
+
 #define BL_RB ORBX_BLUR_ROWS  // 35 output rows per thread (a multiple of 7: the row window is indexed statically)
 #define BL_WARPS 4
 #define BL_TW ORBX_BLUR_TILE_WORDS  // 30 output words per warp row
@@ -37,6 +45,12 @@ __device__ __forceinline__ uint32_t blur_vsum(uint32_t a0, uint32_t a1, uint32_t
 // Row pass + pack for this lane's 4 pixels from the column sums of pixels -4..7 around it:
 // Le=(V-4,V-2) Lo=(V-3,V-1) Ce=(V0,V2) Co=(V1,V3) Re=(V4,V6) Ro=(V5,V7), 16-bit lanes (low, high).
 #define BL_K(lo, hi) ((uint32_t)(lo) | ((uint32_t)(hi) << 8))
+// Two tap pairs share one 32-bit constant (dp2a.lo reads bytes 0-1 of the multiplier, dp2a.hi bytes 2-3): five
+// constants instead of nine, so they stay in registers instead of being re-materialised row after row.
+#ifndef BL_PACKK
+#define BL_PACKK 1
+#endif
+#if !BL_PACKK
 __device__ __forceinline__ uint32_t blur_hsum(uint32_t Le, uint32_t Lo, uint32_t Ce, uint32_t Co, uint32_t Re,
                                               uint32_t Ro) {
   uint32_t a0 = __dp2a_lo(Lo, BL_K(36, 96), 32768u);   // 36 V-3 + 96 V-1
@@ -59,6 +73,36 @@ __device__ __forceinline__ uint32_t blur_hsum(uint32_t Le, uint32_t Lo, uint32_t
   a3 = __dp2a_lo(Ro, BL_K(68, 0), a3);                 // 68 V5
   return __byte_perm(__byte_perm(a0, a1, 0x0062), __byte_perm(a2, a3, 0x0062), 0x5410);
 }
+#else
+#define BL_KK(p, q) ((uint32_t)(p) | ((uint32_t)(q) << 16))
+__device__ __forceinline__ uint32_t blur_hsum(uint32_t Le, uint32_t Lo, uint32_t Ce, uint32_t Co, uint32_t Re,
+                                              uint32_t Ro) {
+  const uint32_t KA = BL_KK(BL_K(36, 96), BL_K(0, 68));     // lo: 36,96   hi: 0,68
+  const uint32_t KB = BL_KK(BL_K(112, 68), BL_K(96, 36));   // lo: 112,68  hi: 96,36
+  const uint32_t KC = BL_KK(BL_K(0, 36), BL_K(96, 96));     // lo: 0,36    hi: 96,96
+  const uint32_t KD = BL_KK(BL_K(36, 0), BL_K(68, 112));    // lo: 36,0    hi: 68,112
+  const uint32_t KE = BL_KK(BL_K(68, 0), 0);                // lo: 68,0
+  uint32_t a0 = __dp2a_lo(Lo, KA, 32768u);   // 36 V-3 + 96 V-1
+  a0 = __dp2a_hi(Le, KA, a0);                // 68 V-2
+  a0 = __dp2a_lo(Ce, KB, a0);                // 112 V0 + 68 V2
+  a0 = __dp2a_hi(Co, KB, a0);                // 96 V1 + 36 V3
+  uint32_t a1 = __dp2a_lo(Le, KC, 32768u);   // 36 V-2
+  a1 = __dp2a_hi(Lo, KA, a1);                // 68 V-1
+  a1 = __dp2a_hi(Ce, KC, a1);                // 96 V0 + 96 V2
+  a1 = __dp2a_lo(Co, KB, a1);                // 112 V1 + 68 V3
+  a1 = __dp2a_lo(Re, KD, a1);                // 36 V4
+  uint32_t a2 = __dp2a_lo(Lo, KC, 32768u);   // 36 V-1
+  a2 = __dp2a_hi(Ce, KD, a2);                // 68 V0 + 112 V2
+  a2 = __dp2a_hi(Co, KC, a2);                // 96 V1 + 96 V3
+  a2 = __dp2a_lo(Re, KE, a2);                // 68 V4
+  a2 = __dp2a_lo(Ro, KD, a2);                // 36 V5
+  uint32_t a3 = __dp2a_lo(Ce, KA, 32768u);   // 36 V0 + 96 V2
+  a3 = __dp2a_hi(Co, KD, a3);                // 68 V1 + 112 V3
+  a3 = __dp2a_hi(Re, KB, a3);                // 96 V4 + 36 V6
+  a3 = __dp2a_lo(Ro, KE, a3);                // 68 V5
+  return __byte_perm(__byte_perm(a0, a1, 0x0062), __byte_perm(a2, a3, 0x0062), 0x5410);
+}
+#endif
 
 // EDGE  = some lane of the warp has a word that is not entirely inside [0,w) (warp-uniform);
 // VEDGE = the tile touches the first / last rows of the level or is shorter than BL_RB rows.
@@ -91,7 +135,17 @@ __device__ __forceinline__ void blur_walk(const uint8_t* __restrict__ img, int p
     }
   }
   const int nout = VEDGE ? min(BL_RB, h - y0) : BL_RB;
+  // !VEDGE: the source rows are consecutive, so the walk keeps a row pointer instead of multiplying out every
+  // row's address (5 instructions per row, 3 of them on the fmaheavy pipe)
+  const uint8_t* rpa = img + (long long)(y0 - 3) * pitch + (EDGE ? qa : c);
+  const int qd = qb - qa;
   auto fetch = [&](int yy) -> uint32_t {
+    if (!VEDGE && BL_PTR && (!EDGE || BL_PTR > 1)) {
+      const uint8_t* rp = rpa;
+      rpa += pitch;
+      if (!EDGE) return __ldg(reinterpret_cast<const uint32_t*>(rp));
+      return __byte_perm(__ldg(reinterpret_cast<const uint32_t*>(rp)), __ldg(reinterpret_cast<const uint32_t*>(rp + qd)), sel);
+    }
     int sy = yy;
     if (VEDGE) {
       sy = sy < 0 ? -sy : sy;
@@ -176,7 +230,7 @@ __device__ __forceinline__ void blur_walk_bytes(const uint8_t* __restrict__ img,
   }
 }
 
-__global__ void __launch_bounds__(BL_WARPS * 32)
+__global__ void __launch_bounds__(BL_WARPS * 32, BL_MINB)
 k_blur_levels(const __grid_constant__ DevPlan P, Level0 l0, const uint8_t* __restrict__ arena,
               uint8_t* __restrict__ blur, int l0_bytes) {
   const int lane = threadIdx.x & 31, frame = blockIdx.y;

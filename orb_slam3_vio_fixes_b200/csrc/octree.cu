@@ -75,9 +75,11 @@ __global__ void __launch_bounds__(NT)
 k_octree(const __grid_constant__ DevPlan P, const int32_t* __restrict__ cell_cnt,
          const uint32_t* __restrict__ cand, uint32_t* __restrict__ gkeys, int16_t* __restrict__ glabels,
          uint32_t* __restrict__ sel, int32_t* __restrict__ sel_cnt, int32_t* __restrict__ status,
-         int smem_keys, int node_cap, int max_cells) {
+         int smem_keys, int node_cap, int max_cells, int level_major) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int level = blockIdx.x, frame = blockIdx.y;
+  // all CTAs of level 0 come first in launch order, then level 1, ...: the longest-running CTAs (most candidates)
+  // start first and the short ones fill in behind them (was (level, frame): 0.265 -> see DESIGN.md §4)
+  const int level = level_major ? blockIdx.y : blockIdx.x, frame = level_major ? blockIdx.x : blockIdx.y;
   const DevLevel& L = P.lv[level];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int cap = (node_cap + 7) & ~7;
@@ -337,14 +339,16 @@ cudaError_t orbx_launch_octree(const DevPlan& P, const int32_t* cell_cnt, const 
   // per-key loops are short (C1: 0.30 -> 0.26 ms / 512 frames at 128 threads) and wide ones once they are long (4K)
   static const int force = [] { const char* e = getenv("ORBX_OCTREE_THREADS"); return e ? atoi(e) : 0; }();
   const int nt = force ? force : (node_cap >= 768 ? OCT_THREADS_BIG : (node_cap >= OCT_SMALL_CAP ? OCT_THREADS : OCT_THREADS_SMALL));
+  static const int level_major = [] { const char* e = getenv("ORBX_OCT_LEVEL_MAJOR"); return e ? atoi(e) : 1; }();
   dim3 grd(P.nlevels, batch);
+  if (level_major) grd = dim3(batch, P.nlevels);
   cudaError_t e;
 #define OCT_LAUNCH(NT, SLOT)                                                                                       \
   do {                                                                                                             \
     e = orbx_ensure_dyn_smem(SLOT, (const void*)k_octree<NT>, smem_bytes);                                         \
     if (e != cudaSuccess) return e;                                                                                \
     k_octree<NT><<<grd, NT, smem_bytes, st>>>(P, cell_cnt, cand, gkeys, glabels, sel, sel_cnt, status, smem_keys,   \
-                                              node_cap, max_cells);                                                \
+                                              node_cap, max_cells, level_major);                                                \
   } while (0)
   if (nt >= OCT_THREADS_BIG) OCT_LAUNCH(OCT_THREADS_BIG, ORBX_SMEM_OCTREE_BIG);
   else if (nt >= OCT_THREADS) OCT_LAUNCH(OCT_THREADS, ORBX_SMEM_OCTREE);

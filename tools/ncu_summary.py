@@ -6,7 +6,12 @@ WANT = ['gpu__time_duration.sum', 'launch__grid_size', 'launch__registers_per_th
         'dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed',
         'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'l1tex__throughput.avg.pct_of_peak_sustained_active',
         'lts__throughput.avg.pct_of_peak_sustained_elapsed', 'sm__warps_active.avg.pct_of_peak_sustained_active',
-        'smsp__issue_active.avg.pct', 'smsp__inst_executed.sum',
+        'smsp__issue_active.avg.pct', 'smsp__inst_executed.sum', 'sm__inst_executed.avg.per_cycle_active',
+        'sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_elapsed',
+        'sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_elapsed',
+        'sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed',
+        'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active',
         'launch__occupancy_limit_registers', 'launch__occupancy_limit_shared_mem', 'launch__occupancy_limit_warps',
         'smsp__warp_issue_stalled_barrier_per_warp_active.pct',
         'smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct',
