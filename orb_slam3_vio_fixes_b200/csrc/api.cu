@@ -36,6 +36,7 @@ struct orbx_extractor_s {
   OrbxTap *xtaps = nullptr, *ytaps = nullptr;
   int32_t* cell_cnt = nullptr;
   uint32_t* cell_tab = nullptr;  // per cell: level << 24 | row << 12 | column
+  OrbxResizeMaps resize_maps;     // tensor maps of the source levels for k_resize_tile (level 0 is encoded per call)
   OrbxFastMaps fast_maps;         // tensor maps of arena levels 1.. for k_fast_strip (level 0 is encoded per call)
   uint32_t* strip_tab = nullptr;  // per FAST strip: level << 24 | cell row << 12 | first cell column
   uint32_t* cand = nullptr;
@@ -94,7 +95,7 @@ static void fill_devplan(const OrbxPlan& P, DevPlan* D) {
     d.w = s.w; d.h = s.h; d.pitch = s.pitch; d.nCols = s.nCols; d.nRows = s.nRows; d.wCell = s.wCell;
     d.hCell = s.hCell; d.cell_base = s.cell_base; d.cell_cap = s.cell_cap; d.nfeat = s.nfeat;
     d.kp_base = s.kp_base; d.kp_cap = s.kp_cap; d.kp_max = s.kp_max; d.nIni = s.nIni; d.hX = s.hX;
-    d.scale = s.scale; d.patch_size = s.patch_size; d.xtab = s.xtab; d.ytab = s.ytab; d.fast_resize = s.fast_resize; d.tile_resize = s.tile_resize; d.btile_base = s.btile_base; d.btiles_x = s.btiles_x; d.offset = s.offset;
+    d.scale = s.scale; d.patch_size = s.patch_size; d.xtab = s.xtab; d.ytab = s.ytab; d.fast_resize = s.fast_resize; d.tile_resize = s.tile_resize; d.tile_rows = s.tile_rows; d.btile_base = s.btile_base; d.btiles_x = s.btiles_x; d.offset = s.offset;
     d.cand_base = s.cand_base; d.strip_k = s.strip_k;
   }
 }
@@ -292,6 +293,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
   CUH(cudaMemset(h->status, 0, sizeof(int32_t)));
   CUH(cudaMemset(h->arena, 0, B * P.arena_bytes + 512));
   orbx_fast_maps_init(h->dplan, h->arena, cfg->max_batch, &h->fast_maps);
+  orbx_resize_maps_init(h->dplan, h->arena, cfg->max_batch, &h->resize_maps);
   CUH(orbx_describe_init_tables(P.umax));
   if (cfg->flags & ORBX_FLAG_STAGE_TIMING)
     for (int i = 0; i <= ORBX_NUM_STAGES; i++) CUH(cudaEventCreate(&h->ev[i]));
@@ -367,7 +369,7 @@ static int run_pipeline(orbx_handle h, Level0 l0, int batch, int lap0, int lap1,
     CU(orbx_launch_repack_level0(D, l0, arena, batch, st));
     l0.base = arena + D.lv[0].offset; l0.pitch = D.lv[0].pitch; l0.frame_stride = D.arena_bytes;
   }
-  CU(orbx_launch_pyramid(D, l0, arena, h->xtaps, h->ytaps, batch, st));
+  CU(orbx_launch_pyramid(D, h->resize_maps, l0, arena, h->xtaps, h->ytaps, batch, f0, st));
   STAGE_MARK(1);
   const bool blur_aside = h->level_blur && side >= 0 && h->blur_side && !tm;
   if (blur_aside) {

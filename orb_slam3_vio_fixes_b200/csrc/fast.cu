@@ -383,19 +383,23 @@ static FsEncodeFn fs_encode_fn() {
   return fn;
 }
 
-// Tensor map of one level: bytes [w] x rows [h] x frames [n], box = FS_TP columns x box_rows rows x 1 frame.
-static bool fs_encode_level(CUtensorMap* m, const uint8_t* base, int w, int h, long long nframes, long long pitch,
-                            long long frame_stride, int box_rows) {
+// Tensor map of one level: bytes [w] x rows [h] x frames [n], box = box_cols columns x box_rows rows x 1 frame.
+bool orbx_encode_tmap3(void* m, const uint8_t* base, int w, int h, long long nframes, long long pitch,
+                       long long frame_stride, int box_cols, int box_rows) {
   FsEncodeFn enc = fs_encode_fn();
-  if (!enc || box_rows > 256) return false;
+  if (!enc || box_rows > 256 || box_rows < 1 || box_cols > 256 || (box_cols & 15)) return false;
   if ((reinterpret_cast<uintptr_t>(base) & 15u) || (pitch & 15) || (frame_stride & 15) || nframes < 1) return false;
   const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)nframes};
   const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frame_stride};
-  const cuuint32_t box[3] = {FS_TP, (cuuint32_t)box_rows, 1};
+  const cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1};
   const cuuint32_t estr[3] = {1, 1, 1};
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(base), dims, strides, box, estr,
-             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+  return enc(reinterpret_cast<CUtensorMap*>(m), CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(base), dims, strides,
+             box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+static bool fs_encode_level(CUtensorMap* m, const uint8_t* base, int w, int h, long long nframes, long long pitch,
+                            long long frame_stride, int box_rows) {
+  return orbx_encode_tmap3(m, base, w, h, nframes, pitch, frame_stride, FS_TP, box_rows);
 }
 
 void orbx_fast_maps_init(const DevPlan& P, const uint8_t* arena, int max_batch, OrbxFastMaps* M) {

@@ -14,7 +14,7 @@ struct DevLevel {
   int nfeat, kp_base, kp_cap, kp_max;
   int nIni;
   float hX, scale, patch_size;
-  int xtab, ytab, fast_resize, tile_resize;
+  int xtab, ytab, fast_resize, tile_resize, tile_rows;
   int btile_base, btiles_x;
   int strip_k;
   long long offset;     // bytes, inside a frame's pyramid arena
@@ -62,8 +62,18 @@ struct OrbxStereoPyr {
 
 // --- launches (each returns cudaGetLastError()) -------------------------------------------------
 cudaError_t orbx_launch_repack_level0(const DevPlan& P, Level0 l0, uint8_t* arena, int batch, cudaStream_t st);
-cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, const OrbxTap* xtaps,
-                                const OrbxTap* ytaps, int batch, cudaStream_t st);
+// Tensor maps of the SOURCE levels of the tiled resize (m[l] = level l over (columns, rows, frames), box =
+// 208 columns x lv[l+1].tile_rows rows x 1 frame); mask bit l = level l has a map.  Encoded by fast.cu's helper.
+struct alignas(64) OrbxTmap { unsigned long long v[16]; };
+struct alignas(64) OrbxResizeMaps {
+  OrbxTmap m[ORBX_PLAN_MAX_LEVELS];
+  unsigned mask;
+};
+bool orbx_encode_tmap3(void* m, const uint8_t* base, int w, int h, long long nframes, long long pitch,
+                       long long frame_stride, int box_cols, int box_rows);
+void orbx_resize_maps_init(const DevPlan& P, const uint8_t* arena, int max_batch, OrbxResizeMaps* M);
+cudaError_t orbx_launch_pyramid(const DevPlan& P, const OrbxResizeMaps& maps, Level0 l0, uint8_t* arena,
+                                const OrbxTap* xtaps, const OrbxTap* ytaps, int batch, int f0, cudaStream_t st);
 // Tensor maps of the pyramid levels for k_fast_strip's TMA staging: one CUtensorMap (128 bytes, 64-byte aligned)
 // per level over (columns, rows, frames); mask bit l = level l has a map.  Kept opaque here so that only fast.cu
 // needs <cuda.h>.

@@ -36,6 +36,7 @@ struct OrbxLevel {
   int xtab, ytab;  // offsets into the resize tables (entries), level>=1
   int fast_resize;  // the 4-column tap windows of k_resize_walk hold for every column group
   int tile_resize;  // every 128x64 output tile fits k_resize_tile's shared-memory source window
+  int tile_rows;    // most source rows any of those tiles needs (rows of the TMA box)
   int btile_base, btiles_x;  // warp tiles (ORBX_BLUR_TILE_WORDS words x ORBX_BLUR_ROWS rows) of k_blur_levels: first tile of this level, tiles per row
   // FAST strips (k_fast_strip): a strip = strip_k consecutive cells of one cell row, one warp each
   int strip_k, strips_per_row, strip_base;
@@ -196,6 +197,7 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
       }
       // k_resize_tile: source window of a 128 x 64 output tile (88 rows x 208 bytes of shared memory)
       L.tile_resize = L.fast_resize;
+      L.tile_rows = 0;
       for (int x0 = 0; x0 < L.w; x0 += 128) {
         const int xs0 = (*xtaps)[L.xtab + x0].ofs & ~15;
         const int xl = (*xtaps)[L.xtab + (x0 + 127 < L.w ? x0 + 127 : L.w - 1)].ofs;
@@ -206,6 +208,7 @@ inline int orbx_build_plan(int nfeatures, float scaleFactorF, int nlevels, int i
         a = a < 0 ? 0 : (a > S.h - 1 ? S.h - 1 : a);
         b = b < 0 ? 0 : (b > S.h - 1 ? S.h - 1 : b);
         if (b - a + 1 > 88) L.tile_resize = 0;
+        if (b - a + 1 > L.tile_rows) L.tile_rows = b - a + 1;
       }
     }
   }

@@ -1,4 +1,7 @@
 // pyramid.cu — image pyramid (ORBextractor::ComputePyramid, src/ORBextractor.cc:1170-1195) for sm_100a.
+#include <stdlib.h>
+#include <string.h>
+
 #include "orbx_kernels.cuh"
 
 __device__ __forceinline__ const uint8_t* level_ptr(const DevPlan& P, const Level0& l0, const uint8_t* arena,
@@ -216,8 +219,13 @@ __device__ __forceinline__ uint32_t rs_vert2(const uint32_t (&A)[4], const uint3
   return __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
 }
 
+// TMA = the source window arrives as ONE 3-D tensor-map box (208 columns x box_rows rows of frame zf0 + blockIdx.z,
+// zero-filled outside the level) issued by one thread; otherwise one cp.async.bulk per row (each lane's copy is
+// serialised through the uniform datapath: ~10 % of the kernel's instructions, all before the first output row).
+template <bool TMA>
 __global__ void __launch_bounds__(RS_WARPS * 32)
-k_resize_tile(const uint8_t* __restrict__ src, int spitch, long long sframe, int sw, int sh,
+k_resize_tile(const __grid_constant__ OrbxTmap map, int box_rows, int zf0,
+              const uint8_t* __restrict__ src, int spitch, long long sframe, int sw, int sh,
               uint8_t* __restrict__ dst, int dpitch, long long dframe, int dw, int dh,
               const OrbxTap* __restrict__ xt, const OrbxTap* __restrict__ yt) {
   __shared__ __align__(128) uint8_t tile[RT_SROWS * RT_SPITCH];
@@ -234,10 +242,16 @@ k_resize_tile(const uint8_t* __restrict__ src, int spitch, long long sframe, int
   if (tid == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(nrows * seg) : "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(TMA ? box_rows * RT_SPITCH : nrows * seg) : "memory");
+    if (TMA)
+      asm volatile(
+          "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+          ::"r"(smem_u32(tile)), "l"(reinterpret_cast<const void*>(&map)), "r"(xs0), "r"(sy_first), "r"(zf0 + (int)blockIdx.z),
+          "r"(bar_a)
+          : "memory");
   }
   __syncthreads();
-  {
+  if (!TMA) {
     const uint8_t* g = src + (long long)blockIdx.z * sframe + (long long)sy_first * spitch + xs0;
     for (int r = tid; r < nrows; r += RS_WARPS * 32)
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -324,8 +338,20 @@ k_resize_tile(const uint8_t* __restrict__ src, int spitch, long long sframe, int
 #endif
 }
 
-cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, const OrbxTap* xtaps,
-                                const OrbxTap* ytaps, int batch, cudaStream_t st) {
+// Maps of the arena levels that serve as resize sources (levels 1 .. nlevels-2), over all max_batch frame slots.
+void orbx_resize_maps_init(const DevPlan& P, const uint8_t* arena, int max_batch, OrbxResizeMaps* M) {
+  memset(M, 0, sizeof(*M));
+  for (int l = 1; l + 1 < P.nlevels; l++) {
+    const DevLevel& S = P.lv[l];
+    const DevLevel& D = P.lv[l + 1];
+    if (!D.tile_resize || D.tile_rows < 1 || D.tile_rows > RT_SROWS) continue;
+    if (orbx_encode_tmap3(&M->m[l], arena + S.offset, S.w, S.h, max_batch, S.pitch, P.arena_bytes, RT_SPITCH, D.tile_rows))
+      M->mask |= 1u << l;
+  }
+}
+
+cudaError_t orbx_launch_pyramid(const DevPlan& P, const OrbxResizeMaps& maps, Level0 l0, uint8_t* arena,
+                                const OrbxTap* xtaps, const OrbxTap* ytaps, int batch, int f0, cudaStream_t st) {
   for (int l = 1; l < P.nlevels; l++) {
     const DevLevel& D = P.lv[l];
     const DevLevel& S = P.lv[l - 1];
@@ -338,8 +364,22 @@ cudaError_t orbx_launch_pyramid(const DevPlan& P, Level0 l0, uint8_t* arena, con
     const bool tiled = walk && D.tile_resize && (spitch & 15) == 0 && (sframe & 15) == 0 && ((uintptr_t)src & 15) == 0;
     if (tiled) {
       dim3 grd((D.w + 127) / 128, (D.h + RS_WARPS * RS_ROWS - 1) / (RS_WARPS * RS_ROWS), batch);
-      k_resize_tile<<<grd, RS_WARPS * 32, 0, st>>>(src, spitch, sframe, S.w, S.h, arena + D.offset, D.pitch,
-                                                   P.arena_bytes, D.w, D.h, xtaps + D.xtab, ytaps + D.ytab);
+      static const bool no_tma = [] { const char* e = getenv("ORBX_RESIZE_TMA"); return e && e[0] == '0'; }();
+      OrbxTmap map = maps.m[l - 1];
+      bool tma = !no_tma && D.tile_rows >= 1 && D.tile_rows <= RT_SROWS;
+      int zf0 = f0;
+      if (tma && l == 1) {  // level 0 is the caller's buffer: its map is encoded per call (frame 0 of the map = l0.base)
+        tma = orbx_encode_tmap3(&map, src, S.w, S.h, batch, spitch, sframe ? sframe : 16, RT_SPITCH, D.tile_rows);
+        zf0 = 0;
+      } else if (tma) {
+        tma = (maps.mask >> (l - 1)) & 1u;
+      }
+      if (tma)
+        k_resize_tile<true><<<grd, RS_WARPS * 32, 0, st>>>(map, D.tile_rows, zf0, src, spitch, sframe, S.w, S.h, arena + D.offset,
+                                                           D.pitch, P.arena_bytes, D.w, D.h, xtaps + D.xtab, ytaps + D.ytab);
+      else
+        k_resize_tile<false><<<grd, RS_WARPS * 32, 0, st>>>(map, 0, 0, src, spitch, sframe, S.w, S.h, arena + D.offset,
+                                                            D.pitch, P.arena_bytes, D.w, D.h, xtaps + D.xtab, ytaps + D.ytab);
     } else if (walk) {
       dim3 grd((D.w + 127) / 128, (D.h + RS_WARPS * RS_ROWS - 1) / (RS_WARPS * RS_ROWS), batch);
       // Arena rows are padded (and the arena has slack after its last row), so only a caller-owned
