@@ -48,26 +48,86 @@ __device__ __forceinline__ uint32_t fs_halve(uint32_t v) { return (v >> 1) & 0x7
 //   amap[FS_APW * (hmax+2)]   arc strengths: row r+1 = zone row r, byte 4+c = strip column c (level column xs+c)
 //   list[30 * (hmax+6)] u16   quad tasks, row-major: row << 5 | lane
 //   misc[12]                  zbits[4] (zone columns), ledge[5] (columns where a cell starts / the zone ends)
+//   rowbits[hmax]             per zone row: ballot of the quads that passed the quick test
 struct FsStrip {
-  uint32_t *tile, *amap, *misc;
+  uint32_t *tile, *amap, *misc, *rowbits;
   uint16_t* list;
   int wq0;  // tile word of lane 0
   int zh;
 };
 
-// Quick test over the whole strip, compacted on the fly: lane = one 4-pixel word column (a "quad" per row),
-// walking down the rows with the last 7 rows (7-bit pixels) in registers.  A quad passes when one of its
-// pixels has |v-ring| > t on at least one pixel of each axial ring pair; every row's passing quads are
-// appended to the task list with one ballot (row-major order).  Returns the number of tasks in rows < zh.
+// Quick test over the whole strip: lane = one 4-pixel word column (a "quad" per row), walking down the rows with
+// the last 7 rows (7-bit pixels) in registers.  A quad passes when one of its pixels has |v-ring| > t on at least
+// one pixel of each axial ring pair.  Each row leaves ONE word (the ballot of its passing quads) in rowbits; the
+// row-major task list is expanded from those words afterwards, 32 rows at a time (lane = row: a warp scan of the
+// popcounts, then every lane writes its row's entries) — ~2 instructions per row instead of the ~9 a per-row
+// compacting append costs every lane.  Returns the number of tasks.
+#ifndef FS_QUICK_ROWBITS
+#define FS_QUICK_ROWBITS 1
+#endif
 __device__ __forceinline__ int fs_quick(const FsStrip& s, int th, uint32_t zm, int lane) {
   const uint32_t cadd = (uint32_t)(128 - ((th + 1) >> 1)) * 0x01010101u;
   const int zh = s.zh, nblk = (zh + 6) / 7;
-  const uint32_t ltm = (1u << lane) - 1u;
   const uint32_t* trow = s.tile + s.wq0 + lane;
   uint32_t C[7];
 #pragma unroll
   for (int i = 0; i < 6; i++) C[i] = fs_halve(trow[i * FS_TPW]);
   trow += 6 * FS_TPW;
+#define QT(x) (__vabsdiffu4(v, (x)) + cadd)
+#define FS_QROW(ph)                                                                                                   \
+  C[((ph) + 6) % 7] = fs_halve(trow[(ph) * FS_TPW]);                                                                   \
+  const uint32_t v = C[((ph) + 3) % 7];                                                                                \
+  const uint32_t lw = __shfl_up_sync(0xffffffffu, v, 1), rw = __shfl_down_sync(0xffffffffu, v, 1);                     \
+  const uint32_t l3 = __byte_perm(lw, v, 0x4321), r3 = __byte_perm(v, rw, 0x6543);                                     \
+  uint32_t g = (QT(C[((ph) + 6) % 7]) | QT(C[(ph) % 7])) & zm; /* ring 0 (0,+3) | ring 8 (0,-3); zm: bit 7 of zone bytes */ \
+  g &= QT(r3) | QT(l3);                                         /* ring 4 (+3,0) | ring 12 (-3,0) */                    \
+  const unsigned bal = __ballot_sync(0xffffffffu, g != 0);
+#if FS_QUICK_ROWBITS
+  uint32_t* rb = s.rowbits;
+  int rows_left = zh;
+#pragma unroll 1
+  for (int blk = 0; blk < nblk; blk++, trow += 7 * FS_TPW, rows_left -= 7, rb += 7) {
+    if (rows_left >= 7) {  // warp-uniform
+#pragma unroll
+      for (int ph = 0; ph < 7; ph++) {
+        FS_QROW(ph)
+        if (lane == 0) rb[ph] = bal;
+      }
+    } else {
+#pragma unroll
+      for (int ph = 0; ph < 7; ph++) {
+        if (ph >= rows_left) break;  // the last block of rows may be short
+        FS_QROW(ph)
+        if (lane == 0) rb[ph] = bal;
+      }
+    }
+  }
+  __syncwarp();
+  int base = 0;
+#pragma unroll 1
+  for (int r0 = 0; r0 < zh; r0 += 32) {
+    const int r = r0 + lane;
+    uint32_t bits = r < zh ? s.rowbits[r] : 0u;
+    const int cnt = __popc(bits);
+    int inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    uint16_t* lp = s.list + base + inc - cnt;
+    const uint32_t code = (uint32_t)r << 5;
+    while (bits) {
+      const uint32_t b = (uint32_t)__ffs((int)bits) - 1u;
+      bits &= bits - 1u;
+      *lp++ = (uint16_t)(code | b);
+    }
+    base += __shfl_sync(0xffffffffu, inc, 31);
+  }
+  __syncwarp();
+  return base;
+#else
+  const uint32_t ltm = (1u << lane) - 1u;
   int base = 0;
   uint32_t code = (uint32_t)lane;
   int rows_left = zh;
@@ -76,23 +136,17 @@ __device__ __forceinline__ int fs_quick(const FsStrip& s, int th, uint32_t zm, i
 #pragma unroll
     for (int ph = 0; ph < 7; ph++) {
       if (ph >= rows_left) break;  // warp-uniform: the last block of rows may be short
-      C[(ph + 6) % 7] = fs_halve(trow[ph * FS_TPW]);
-      const uint32_t v = C[(ph + 3) % 7];
-      const uint32_t lw = __shfl_up_sync(0xffffffffu, v, 1), rw = __shfl_down_sync(0xffffffffu, v, 1);
-      const uint32_t l3 = __byte_perm(lw, v, 0x4321), r3 = __byte_perm(v, rw, 0x6543);
-#define QT(x) (__vabsdiffu4(v, (x)) + cadd)
-      uint32_t g = (QT(C[(ph + 6) % 7]) | QT(C[ph % 7])) & zm;  // ring 0 (0,+3) | ring 8 (0,-3); zm keeps bit 7 of zone bytes
-      g &= QT(r3) | QT(l3);                                     // ring 4 (+3,0) | ring 12 (-3,0)
-#undef QT
-      const bool pass = g != 0;
-      const unsigned bal = __ballot_sync(0xffffffffu, pass);
-      if (pass) s.list[base + __popc(bal & ltm)] = (uint16_t)(code + 32u * ph);
+      FS_QROW(ph)
+      if (g != 0) s.list[base + __popc(bal & ltm)] = (uint16_t)(code + 32u * ph);
       base += __popc(bal);
     }
     code += 7u * 32u;
   }
   __syncwarp();
   return base;
+#endif
+#undef FS_QROW
+#undef QT
 }
 
 // Arc strength of the n listed quads into the A map (0 where A <= th or outside the zone); the quads that
@@ -183,7 +237,8 @@ k_fast_strip(const __grid_constant__ DevPlan P, const __grid_constant__ OrbxFast
   s.tile = fs_smem + warp * region_words;
   s.amap = s.tile + FS_TPW * (hmax + 6);
   s.misc = s.amap + FS_APW * (hmax + 2);
-  s.list = reinterpret_cast<uint16_t*>(s.misc + 12);  // misc[10..11] = the warp's mbarrier (8-byte aligned)
+  s.rowbits = s.misc + 12;                              // misc[10..11] = the warp's mbarrier (8-byte aligned)
+  s.list = reinterpret_cast<uint16_t*>(s.rowbits + hmax);
 
   // strip_tab: level << 24 | cell row << 12 | first cell column (built with the plan)
   const uint32_t stt = __ldg(strip_tab + strip);
@@ -364,7 +419,7 @@ k_fast_strip(const __grid_constant__ DevPlan P, const __grid_constant__ OrbxFast
 }
 
 static size_t fs_region_words(int hmax) {
-  const size_t w = (size_t)FS_TPW * (hmax + 6) + (size_t)FS_APW * (hmax + 2) + 12 + (30 * (size_t)(hmax + 6) + 1) / 2;
+  const size_t w = (size_t)FS_TPW * (hmax + 6) + (size_t)FS_APW * (hmax + 2) + 12 + hmax + (30 * (size_t)(hmax + 6) + 1) / 2;
   return (w + 31) & ~(size_t)31;  // the TMA destination (the tile, first in the region) is 128-byte aligned
 }
 
