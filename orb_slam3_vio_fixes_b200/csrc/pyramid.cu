@@ -195,7 +195,7 @@ __device__ __forceinline__ uint32_t rs_vert(const uint32_t (&A)[4], const uint32
 // IDP.2A against the packed coefficients (c0 | c1 << 16) gives h = r0*c0 + r1*c1 (< 2^19); the row keeps h & ~15 and the
 // vertical blend uses umulhi(b << 12, h & ~15) = (b * (h >> 4)) >> 16 — the same integers as cv::resize.
 #ifndef RS_DP2A
-#define RS_DP2A 1
+#define RS_DP2A 2   // 2: rows keep h >> 4 and the vertical blend uses 32-bit products (below); 1: umulhi form
 #endif
 struct RsTapRegs2 {
   uint32_t sel[4];   // PRMT selector: bytes (d, d+1) of the window -> bytes 0, 1; rest zero
@@ -210,7 +210,21 @@ __device__ __forceinline__ void rs_row_smem2(const uint8_t* p, const RsTapRegs2&
   const uint32_t hi = __funnelshift_r(w1, w2, T.sa);
   const uint32_t mid = __funnelshift_r(lo, hi, 16);
 #pragma unroll
+#if RS_DP2A == 2
+  for (int i = 0; i < 4; i++) H[i] = __dp2a_lo(T.coef[i], __byte_perm(i < 2 ? lo : mid, 0, T.sel[i]), 0u) >> 4;
+#else
   for (int i = 0; i < 4; i++) H[i] = __dp2a_lo(T.coef[i], __byte_perm(i < 2 ? lo : mid, 0, T.sel[i]), 0u) & ~15u;
+#endif
+}
+// Vertical blend without the high-half multiplies (IMAD.HI takes two passes of the half-rate fmaheavy pipe, the
+// kernel's busiest, and needs a zeroed addend register): with A = h >> 4 (< 2^15) and b <= 2048 the products fit
+// 32 bits, so (b * A) >> 16 is the upper half of a plain IMAD; the upper halves of two pixels are gathered by one
+// PRMT into 16-bit lanes, summed and rounded there ((x0 + x1 + 2) >> 2 <= 255), and packed by a last PRMT.
+__device__ __forceinline__ uint32_t rs_vert3(const uint32_t (&A)[4], const uint32_t (&B)[4], uint32_t b0, uint32_t b1) {
+  const uint32_t a01 = __byte_perm(b0 * A[0], b0 * A[1], 0x7632), a23 = __byte_perm(b0 * A[2], b0 * A[3], 0x7632);
+  const uint32_t c01 = __byte_perm(b1 * B[0], b1 * B[1], 0x7632), c23 = __byte_perm(b1 * B[2], b1 * B[3], 0x7632);
+  const uint32_t s01 = (a01 + c01 + 0x00020002u) >> 2, s23 = (a23 + c23 + 0x00020002u) >> 2;
+  return __byte_perm(s01, s23, 0x6420);
 }
 __device__ __forceinline__ uint32_t rs_vert2(const uint32_t (&A)[4], const uint32_t (&B)[4], uint32_t b0s, uint32_t b1s) {
   uint32_t v[4];
@@ -301,6 +315,11 @@ k_resize_tile(const __grid_constant__ OrbxTmap map, int box_rows, int zf0,
   uint32_t HA[4], HB[4];
   int sy_b = -1 << 20;  // source row held in the buffer that was the second row of the previous output row
   const int dy1 = min(dy0 + RS_ROWS, dh);
+#if RS_DP2A == 2
+#define RS_VERT(P, Q, ty) rs_vert3(P, Q, (uint32_t)ty.c0, (uint32_t)ty.c1)
+#else
+#define RS_VERT(P, Q, ty) rs_vert2(P, Q, (uint32_t)ty.c0 << 12, (uint32_t)ty.c1 << 12)
+#endif
 #if RS_DP2A
   // two output rows per trip; the buffers swap roles (P = holds the previous second row, Q = receives the new one)
 #define RS_STEP(P, Q, DY)                                                                         \
@@ -310,7 +329,7 @@ k_resize_tile(const __grid_constant__ OrbxTmap map, int box_rows, int zf0,
     if (sy0 != sy_b) rs_row_smem2(base + sy0 * RT_SPITCH, T, P);                                  \
     rs_row_smem2(base + sy1 * RT_SPITCH, T, Q);                                                   \
     sy_b = sy1;                                                                                   \
-    *reinterpret_cast<uint32_t*>(out) = rs_vert2(P, Q, (uint32_t)ty.c0 << 12, (uint32_t)ty.c1 << 12); \
+    *reinterpret_cast<uint32_t*>(out) = RS_VERT(P, Q, ty);                                        \
     out += dpitch;                                                                                \
   } while (0)
 #pragma unroll 1
