@@ -41,6 +41,10 @@ __device__ __forceinline__ uint32_t blur_vsum(uint32_t a0, uint32_t a1, uint32_t
                                               uint32_t a5, uint32_t a6) {
   return 9u * (a0 + a6) + 17u * (a1 + a5) + 24u * (a2 + a4) + 28u * a3;
 }
+// (Measured and dropped: the same sum from adds and rotates on the ALU pipe only — 8 ALU instructions instead of
+//  4 IMAD + 3 adds — for one or both byte parities: describe stage 0.915 / 0.924 ms against 0.905; the fmaheavy pipe
+//  is the busiest unit at 71 % but the kernel also issues at 71 % of its slots, so extra instructions cost as much
+//  as the multiplies they remove.)
 
 // Row pass + pack for this lane's 4 pixels from the column sums of pixels -4..7 around it:
 // Le=(V-4,V-2) Lo=(V-3,V-1) Ce=(V0,V2) Co=(V1,V3) Re=(V4,V6) Ro=(V5,V7), 16-bit lanes (low, high).
