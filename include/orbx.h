@@ -291,6 +291,28 @@ int orbm_search_by_projection_th(const orbx_keypoint* d_kps, const uint8_t* d_de
                                  void* d_scratch, int32_t* d_match, int32_t* d_feat_query,
                                  int32_t* d_nmatches, void* stream);
 
+/* orbm_search_by_projection without any allocation and without a caller scratch buffer.  NO COUNTERPART IN THE
+ * REFERENCE: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, outputs and results as
+ * orbm_search_by_projection minus d_scratch: the candidate lists live in a static device array of
+ * ORBM_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it until exit), so
+ * batch * q_stride * 32 must not exceed it (131 072 queries); larger calls return ORBX_E_CAPACITY with the
+ * sizes in orbx_last_error().  The call itself performs no cudaMalloc / cudaFree.  All calls on a GPU share the
+ * array (it keeps the last call's contents; nothing in it needs clearing, every entry read is written first by
+ * the same call): calls that overlap on one GPU — different streams or host threads — RACE; order them on one
+ * stream.  Calls on different GPUs are independent.  The device must be current, as for every orbm_* call. */
+#define ORBM_STATIC_SCRATCH_BYTES (4u << 20)
+int orbm_search_by_projection_static(const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n,
+                                     int kp_stride, int batch, const int32_t* d_cell_off,
+                                     const int32_t* d_cell_idx, float min_x, float max_x, float min_y,
+                                     float max_y, const float* d_u_right, const uint8_t* d_feat_locked,
+                                     const float* d_qx, const float* d_qy, const float* d_qr,
+                                     const int8_t* d_qmin_level, const int8_t* d_qmax_level,
+                                     const uint8_t* d_qdesc, const int32_t* d_nq, int q_stride,
+                                     const float* d_q_ur, const uint8_t* d_q_flags, const float* d_q_angle,
+                                     int mode, float nn_ratio, int check_orientation, int32_t* d_match,
+                                     int32_t* d_feat_query, int32_t* d_nmatches, void* stream);
+
 /* Hamming stage of Frame::ComputeStereoMatches (Frame.cc:811-894): per left keypoint the best
  * right keypoint in its row band (|dy| within 2*scale[octR], |octave diff|<=1,
  * uL-max_d <= uR <= uL), first minimum below TH_HIGH=100 wins, candidates visited in

@@ -16,6 +16,7 @@ static thread_local char g_err[256] = "";
 static void set_err(const char* what, cudaError_t e) {
   snprintf(g_err, sizeof(g_err), "%s: %s", what, e == cudaSuccess ? "" : cudaGetErrorString(e));
 }
+void orbx_set_error_text(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg ? msg : ""); }
 #define CU(call)                                  \
   do {                                            \
     cudaError_t e_ = (call);                      \

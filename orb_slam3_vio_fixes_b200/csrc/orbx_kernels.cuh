@@ -124,3 +124,5 @@ size_t orbx_octree_smem_bytes(int smem_keys, int node_cap, int max_cells);
 // on different devices, created from different threads never lower or miss each other's opt-in.
 enum OrbxSmemSlot { ORBX_SMEM_FAST = 0, ORBX_SMEM_FAST4, ORBX_SMEM_FAST_STRIP, ORBX_SMEM_OCTREE, ORBX_SMEM_OCTREE_BIG, ORBX_SMEM_OCTREE_X, ORBX_SMEM_BOW_VECTORS, ORBX_SMEM_ROWBAND, ORBX_SMEM_SLOTS };
 cudaError_t orbx_ensure_dyn_smem(OrbxSmemSlot slot, const void* func, size_t bytes);
+// Sets the calling thread's orbx_last_error() text (for entry points outside api.cu).
+void orbx_set_error_text(const char* msg);

@@ -14,6 +14,10 @@
 //                   cannot change it; only when a full list runs out the warp rescans that query's window
 //                   with the current lock bitmap.  The rotation histogram, ComputeThreeMaxima (:2012-2053)
 //                   and the erasure pass follow in the same warp.
+#include <stdio.h>
+
+#include <mutex>
+
 #include "match_core.cuh"
 
 struct ProjArgs {
@@ -372,6 +376,79 @@ extern "C" int orbm_search_by_projection(
                                       d_qmax_level, d_qdesc, d_nq, q_stride, d_q_ur, d_q_flags, d_q_angle, mode,
                                       nn_ratio, check_orientation, 100 /* TH_HIGH */, d_scratch, d_match,
                                       d_feat_query, d_nmatches, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// orbm_search_by_projection_static: the same whole function for callers that cannot allocate (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The candidate lists that orbm_search_by_projection takes from the
+// caller as d_scratch live in a file-scope device array of ORBM_STATIC_SCRATCH_BYTES (4 MiB = 131 072 queries of
+// 32 bytes; every GPU that loads the library holds it until the process exits).
+//  * g_proj_static_scratch is, in host code, only a stand-in for the symbol: the device address comes from
+//    cudaGetSymbolAddress, looked up once per device with that device current, and is what the kernels get.
+//  * The entry point calls no cudaMalloc / cudaFree / allocating library routine.
+//  * Every call shares the array and it keeps the last call's contents.  Nothing in it has to start at zero:
+//    k_proj_score writes entry (frame, query) for every query < nq[frame] before k_proj_resolve reads it, and no
+//    other entry is read.  Two calls that overlap on one GPU (different streams, or two host threads) race on it;
+//    calls on one stream, or on different GPUs, do not.
+// ---------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_proj_static_scratch[ORBM_STATIC_SCRATCH_BYTES];
+
+#define ORBM_STATIC_MAX_DEVICES 64
+static std::mutex g_static_scratch_mu;
+static void* g_static_scratch_addr[ORBM_STATIC_MAX_DEVICES];  // device address of the array, per device (nullptr = not looked up)
+
+// Device address of g_proj_static_scratch on the current device (cached per device).
+static int proj_static_scratch(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= ORBM_STATIC_MAX_DEVICES) {
+    orbx_set_error_text("orbm_search_by_projection_static: no current CUDA device (or device ordinal >= 64)");
+    return e != cudaSuccess ? ORBX_E_CUDA : ORBX_E_INVALID;
+  }
+  std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+  if (!g_static_scratch_addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_proj_static_scratch);
+    if (e != cudaSuccess || !p) {
+      char msg[200];
+      snprintf(msg, sizeof(msg), "orbm_search_by_projection_static: cudaGetSymbolAddress(scratch) on device %d: %s", dev,
+               cudaGetErrorString(e));
+      orbx_set_error_text(msg);
+      return ORBX_E_CUDA;
+    }
+    g_static_scratch_addr[dev] = p;
+  }
+  *out = g_static_scratch_addr[dev];
+  return ORBX_OK;
+}
+
+extern "C" int orbm_search_by_projection_static(
+    const orbx_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_n, int kp_stride, int batch,
+    const int32_t* d_cell_off, const int32_t* d_cell_idx, float min_x, float max_x, float min_y, float max_y,
+    const float* d_u_right, const uint8_t* d_feat_locked, const float* d_qx, const float* d_qy, const float* d_qr,
+    const int8_t* d_qmin_level, const int8_t* d_qmax_level, const uint8_t* d_qdesc, const int32_t* d_nq,
+    int q_stride, const float* d_q_ur, const uint8_t* d_q_flags, const float* d_q_angle, int mode, float nn_ratio,
+    int check_orientation, int32_t* d_match, int32_t* d_feat_query, int32_t* d_nmatches, void* stream) {
+  if (batch < 1 || q_stride < 1) return ORBX_E_INVALID;
+  const unsigned long long need = (unsigned long long)batch * (unsigned long long)q_stride * sizeof(ProjCand);
+  if (need > (unsigned long long)ORBM_STATIC_SCRATCH_BYTES) {
+    char msg[256];
+    snprintf(msg, sizeof(msg),
+             "orbm_search_by_projection_static: %llu queries need %llu bytes of scratch, the static array holds %u; use "
+             "orbm_search_by_projection",
+             (unsigned long long)batch * q_stride, need, (unsigned)ORBM_STATIC_SCRATCH_BYTES);
+    orbx_set_error_text(msg);
+    return ORBX_E_CAPACITY;
+  }
+  void* scratch = nullptr;
+  const int rc = proj_static_scratch(&scratch);
+  if (rc != ORBX_OK) return rc;
+  return orbm_search_by_projection_th(d_kps, d_desc, d_n, kp_stride, batch, d_cell_off, d_cell_idx, min_x, max_x,
+                                      min_y, max_y, d_u_right, d_feat_locked, d_qx, d_qy, d_qr, d_qmin_level,
+                                      d_qmax_level, d_qdesc, d_nq, q_stride, d_q_ur, d_q_flags, d_q_angle, mode,
+                                      nn_ratio, check_orientation, 100 /* TH_HIGH */, scratch, d_match, d_feat_query,
+                                      d_nmatches, stream);
 }
 
 // ---------------------------------------------------------------------------------------------------------
