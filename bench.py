@@ -685,17 +685,15 @@ def main():
     try:
         caps = sorted((ROOT / "profiles").glob("*traffic_batch%d.json" % B)) if cfg == "C1" else []
         if caps:
-            doc = json.loads(caps[-1].read_text())["kernels"]
-            kern = doc.get("k_" + top["kernel"]) or doc.get("k_" + top["kernel"] + "_strip")
-            if kern:
-                # the capture's launches may cover a sub-batch (grid.y = frames in the launch): scale to the B frames
-                # that `alg_bytes_per_launch` and the stage time refer to
-                per = {}
-                for k_ in kern:
-                    fr_ = max(1, int(k_["grid"].strip("()").split(",")[1]))
-                    per.setdefault(k_["grid"].strip("()").split(",")[0], []).append(
-                        (k_["dram_read_bytes"] + k_["dram_write_bytes"]) / fr_)
-                traffic = int(sum(sum(v) / len(v) for v in per.values()) * B)
+            doc = json.loads(caps[-1].read_text())
+            # the capture is ONE step of doc["batch"] frames (tools/profile_step.py B 1): every launch of the stage's
+            # kernels in it, summed, is the stage's DRAM traffic for that many frames
+            names = {"pyramid": ["k_resize_tile", "k_resize_walk", "k_resize"], "fast": ["k_fast_strip"],
+                     "octree": ["k_octree"], "order": ["k_order"],
+                     "describe": ["k_blur_levels", "k_describe_lite4", "k_describe_lite", "k_describe"]}[top["kernel"]]
+            tot = sum(k_["dram_read_bytes"] + k_["dram_write_bytes"] for nm in names for k_ in doc["kernels"].get(nm, []))
+            if tot > 0 and doc.get("steps_captured", 0) == 1:
+                traffic = int(tot / doc["batch"] * B)
     except Exception:
         traffic = None
     total_bytes = sum(ext_bytes.values()) + match_bytes

@@ -9,8 +9,8 @@ timeout 600 python bench.py --config $c --steps 10 --warmup 3 --no-cpu-baseline 
 done
 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-latency > gpurun_out/r2z_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r2z_launches_bench_C1.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-latency > gpurun_out/r2z_ncu_list.log 2>&1
-python tools/profile_step.py 256 1 > gpurun_out/r2z_plain2.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:'k_fast|k_describe|k_resize|k_octree|k_blur|k_search_area' -c 14 -o gpurun_out/r2z_full python tools/profile_step.py 256 1 > gpurun_out/r2z_ncu.log 2>&1
+python tools/profile_step.py 512 1 > gpurun_out/r2z_plain2.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:'k_fast|k_describe|k_resize|k_octree|k_blur|k_search_area' -c 30 -o gpurun_out/r2z_full python tools/profile_step.py 512 1 > gpurun_out/r2z_ncu.log 2>&1
 ncu -i gpurun_out/r2z_full.ncu-rep --page raw --csv > gpurun_out/r2z_full_raw.csv 2>/dev/null
 python __graft_entry__.py smoke > gpurun_out/r2z_smoke.log 2>&1; tail -2 gpurun_out/r2z_smoke.log
 ls -la gpurun_out | tail -16

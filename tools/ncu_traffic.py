@@ -1,6 +1,6 @@
 """Per-launch DRAM traffic of each kernel from an `ncu --page raw --csv` dump -> JSON
 (kernel -> {grid, dram_read_bytes, dram_write_bytes, time_us}); bench.py reads the committed file to
-fill roofline.traffic.  Usage: ncu_traffic.py raw.csv batch out.json"""
+fill roofline.traffic.  Usage: ncu_traffic.py raw.csv batch out.json [steps captured, default 1]"""
 import csv
 import json
 import sys
@@ -17,7 +17,8 @@ def val(r, name):
     return v * mult
 
 
-out = {"batch": int(sys.argv[2]), "source": sys.argv[1], "kernels": {}}
+out = {"batch": int(sys.argv[2]), "steps_captured": int(sys.argv[4]) if len(sys.argv) > 4 else 1, "source": sys.argv[1],
+       "kernels": {}}
 for r in rows[2:]:
     name = r[idx["Kernel Name"]].split("(")[0].replace("void ", "").split("<")[0]
     out["kernels"].setdefault(name, []).append({
