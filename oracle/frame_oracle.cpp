@@ -10,10 +10,14 @@
 //   GeometricCamera::project          src/CameraModels/Pinhole.cpp:49-55, KannalaBrandt8.cpp:67-85 (libm atan2f/cos/sin)
 //
 // PINNING: undistortPoints is pinned bit for bit against the real OpenCV 4.13 binary (cv2.undistortPoints,
-// tests/test_frame_geometry.py).  isInFrustum is Eigen code; Eigen is absent from the image, so it is
-// "parity unpinned" against an executable reference: the restatement follows the source with uncontracted fp32
-// in Eigen's fixed-size evaluation order (3-term dot = c0 + (c1 + c2)) and is cross-checked against an fp64
-// evaluation (the test reports how many decisions / levels differ).
+// tests/test_frame_geometry.py).  isInFrustum / isInFrustumChecks are pinned against the reference's own text:
+// oracle/Makefile target `ref_frame` cuts the two functions verbatim out of /root/reference/src/Frame.cc at build time
+// and compiles them over the stand-in Eigen / Sophus / MapPoint types (oracle/_ref/libref_frame.so);
+// tests/test_ref_frame.py asserts array_equal of every tracking field (single camera and two-camera rig).  What that
+// pins is the reference's logic (gate order, comparisons, the early mTrackProjX/Y write, untouched fields, the right
+// pose composition); the 3-vector arithmetic itself is the stated contract — uncontracted fp32 in Eigen's fixed-size
+// evaluation order (3-term dot = c0 + (c1 + c2)) — because Eigen is not in the image; it is cross-checked against an
+// fp64 evaluation (the test reports how many decisions / levels differ).
 // Must be compiled with -ffp-contract=off.
 #include <cmath>
 #include <cstdint>

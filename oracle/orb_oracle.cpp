@@ -27,8 +27,11 @@
 // that are not in the image) and tests/test_ref_matcher.py asserts array_equal between the reference's
 // SearchByProjection x5 (MapPoints mono + rig, last frame mono + rig, relocalisation, Sim3 x2),
 // SearchByBoW x3, SearchForTriangulation, SearchForInitialization, Fuse and the restatements here.
-// Frame::ComputeStereoMatches (m11) lives in Frame.cc, which cannot be compiled in isolation; its
-// restatement is pinned through cv2 (cv::norm L1 SAD) and hand-derived known answers only.
+// PINNED (m11, (f).1): Frame.cc cannot be compiled as a whole here, but Frame::ComputeStereoMatches
+// (:811-981) and ComputeStereoFromRGBD (:984-1005) can: oracle/Makefile target `ref_frame` cuts them
+// verbatim out of the reference file at build time (scratch directory outside the repository) and compiles
+// that text over the same stand-ins -> oracle/_ref/libref_frame.so; tests/test_ref_frame.py asserts
+// array_equal of mvuRight / mvDepth with the restatement here at C2 and C4 (maxD = fx).
 //
 // Floating-point contract:
 //   * cos/sin: libm sincosf, exactly what the reference's `cos(float)`/`sin(float)`

@@ -31,6 +31,36 @@
 
 #define EIGEN_MAKE_ALIGNED_OPERATOR_NEW
 
+namespace cv {
+// cv::DMatch and the brute-force Hamming matcher of Frame.h:337 (cv::BFMatcher(cv::NORM_HAMMING), crossCheck off).
+// knnMatch: per query row the k nearest train rows by Hamming distance, nearest first; equal distances keep the lower
+// train index first (OpenCV's batch distance + partial sort walks train rows in order and replaces on `<` only).
+struct DMatch {
+  int queryIdx = -1, trainIdx = -1, imgIdx = -1;
+  float distance = 0;
+};
+enum { NORM_HAMMING = 6 };
+class BFMatcher {
+ public:
+  explicit BFMatcher(int /*normType*/ = NORM_HAMMING, bool /*crossCheck*/ = false) {}
+  void knnMatch(const Mat& query, const Mat& train, std::vector<std::vector<DMatch> >& matches, int k) const {
+    matches.assign(query.rows, std::vector<DMatch>());
+    for (int q = 0; q < query.rows; q++) {
+      std::vector<DMatch>& out = matches[q];
+      for (int t = 0; t < train.rows; t++) {
+        int d = 0;
+        const uchar *a = query.ptr(q), *b = train.ptr(t);
+        for (int i = 0; i < query.cols; i++) d += __builtin_popcount((unsigned)(a[i] ^ b[i]));
+        DMatch m; m.queryIdx = q; m.trainIdx = t; m.imgIdx = 0; m.distance = (float)d;
+        std::size_t pos = out.size();
+        while (pos > 0 && m.distance < out[pos - 1].distance) pos--;
+        if ((int)pos < k) { out.insert(out.begin() + pos, m); if ((int)out.size() > k) out.pop_back(); }
+      }
+    }
+  }
+};
+}  // namespace cv
+
 namespace Eigen {
 struct Vector2f {
   float v[2];
@@ -76,6 +106,11 @@ struct Matrix3f {
     return o;
   }
 };
+// Frame.cc:521,524 spell the 3-vector Eigen::Matrix<float,3,1>
+template <class T, int R, int C> struct MatrixSel;
+template <> struct MatrixSel<float, 3, 1> { typedef Vector3f type; };
+template <> struct MatrixSel<float, 3, 3> { typedef Matrix3f type; };
+template <class T, int R, int C> using Matrix = typename MatrixSel<T, R, C>::type;
 }  // namespace Eigen
 
 namespace Sophus {
@@ -116,6 +151,12 @@ namespace ORB_SLAM3 {
 
 class KeyFrame;
 class Frame;
+
+// what Frame::ComputeStereoMatches reads of an extractor (ORBextractor.h:87): the pyramid it left behind
+class ORBextractor {
+ public:
+  std::vector<cv::Mat> mvImagePyramid;
+};
 
 // GeometricCamera surface used by ORBmatcher.cc (:465, :920, :1072, :1210, :1713).  Defined out of line in
 // matcher_ref_api.cpp (compiled with -ffp-contract=off: camera arithmetic is not part of ORBmatcher.cc).
@@ -169,6 +210,22 @@ class MapPoint {
   void Replace(MapPoint* pMP);
 };
 
+// What Frame::ComputeStereoFishEyeMatches (Frame.cc:1126-1166) uses of KannalaBrandt8: TriangulateMatches.  The real one
+// needs Eigen's JacobiSVD (KannalaBrandt8.cpp:306-375; the product's version is on the tolerance contract),
+// so this stand-in answers from a table the test supplies: depth[class_id of kp1][class_id of kp2], p3D = (0, 0, depth).
+class KannalaBrandt8 : public GeometricCamera {
+ public:
+  const float* depth_table = nullptr;
+  int table_cols = 0;
+  float TriangulateMatches(GeometricCamera* /*pCamera2*/, const cv::KeyPoint& kp1, const cv::KeyPoint& kp2,
+                           const Eigen::Matrix3f& /*R12*/, const Eigen::Vector3f& /*t12*/, const float /*sigmaLevel*/,
+                           const float /*unc*/, Eigen::Vector3f& p3D) {
+    const float d = depth_table[(std::size_t)kp1.class_id * table_cols + kp2.class_id];
+    p3D = Eigen::Vector3f(0.f, 0.f, d);
+    return d;
+  }
+};
+
 // 64 x 48 grid shared by Frame and KeyFrame (Frame.h:44-45; Frame.cc:385-416, 657-735; KeyFrame.cc:704-748)
 struct FeatureGrid {
   std::vector<std::size_t> cell[64][48];
@@ -197,6 +254,26 @@ class Frame {
   GeometricCamera *mpCamera = nullptr, *mpCamera2 = nullptr;
   Sophus::SE3f mTcw, mTrl;
   FeatureGrid mGrid, mGridRight;
+
+  // members and functions of the Frame.cc functions compiled by `make ref_frame` (frame_ref_api.cpp): stereo matching
+  // (Frame.cc:811-1005) and the frustum test (:512-586, :1168-1242)
+  ORBextractor *mpORBextractorLeft = nullptr, *mpORBextractorRight = nullptr;
+  cv::Mat mDescriptorsRight;
+  std::vector<float> mvInvScaleFactors, mvDepth;
+  Eigen::Matrix3f mRcw, mRwc;
+  Eigen::Vector3f mtcw, mOw;
+  Sophus::SE3f mTlr;
+  int monoLeft = -1, monoRight = -1, mnCloseMPs = 0;
+  std::vector<Eigen::Vector3f> mvStereo3Dpoints;
+  std::vector<float> mvLevelSigma2;
+  Eigen::Matrix3f mRlr;
+  Eigen::Vector3f mtlr;
+  static cv::BFMatcher BFmatcher;
+  void ComputeStereoFishEyeMatches();
+  void ComputeStereoMatches();
+  void ComputeStereoFromRGBD(const cv::Mat& imDepth);
+  bool isInFrustum(MapPoint* pMP, float viewingCosLimit);
+  bool isInFrustumChecks(MapPoint* pMP, float viewingCosLimit, bool bRight = false);
 
   Sophus::SE3f GetPose() const { return mTcw; }
   Sophus::SE3f GetRelativePoseTrl() { return mTrl; }

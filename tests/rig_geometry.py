@@ -91,3 +91,27 @@ def rel_pose(Ta, Tb):
     """T12 = Ta * Tb^-1 as (R12, t12): maps camera-b coordinates into camera-a coordinates (ORBmatcher.cc:929-937)."""
     R12 = Ta[0] @ Tb[0].T
     return R12, Ta[1] - R12 @ Tb[1]
+
+
+def fisheye_ratio_candidates(desc_l, desc_r, mono_l, mono_r):
+    """Index logic of Frame::ComputeStereoFishEyeMatches before the triangulation (Frame.cc:1126-1152): Hamming
+    knnMatch(k=2) of the lapping-area descriptors (ties to the lower train index), Lowe ratio 0.7 evaluated in double
+    (`float < float * 0.7`).  Returns (left indices, right indices) of the pairs handed to TriangulateMatches, in the
+    order the reference visits them.  Pinned against the reference's own text by tests/test_ref_frame.py."""
+    ham = (np.unpackbits(desc_l[mono_l:], axis=1)[:, None, :] != np.unpackbits(desc_r[mono_r:], axis=1)[None, :, :]).sum(-1)
+    order = np.argsort(ham, axis=1, kind="stable")
+    b0, b1 = order[:, 0], order[:, 1]
+    d0, d1 = ham[np.arange(len(b0)), b0], ham[np.arange(len(b0)), b1]
+    cand = d0.astype(np.float64) < d1.astype(np.float64) * 0.7
+    return np.nonzero(cand)[0] + mono_l, b0[cand] + mono_r
+
+
+def fisheye_tables(n_l, n_r, qi, ti, ok):
+    """mvLeftToRightMatch / mvRightToLeftMatch from the accepted pairs (Frame.cc:1157-1163): a right feature keeps the
+    last left index written to it."""
+    l2r, r2l = np.full(n_l, -1, np.int64), np.full(n_r, -1, np.int64)
+    for q, t, o in zip(qi, ti, ok):
+        if o:
+            l2r[q] = t
+            r2l[t] = q
+    return l2r, r2l

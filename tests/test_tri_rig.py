@@ -199,12 +199,7 @@ def test_gpu_stereo_fisheye_matches(oracle_mod):
     Rlr, tlr = G.rel_pose(K1[0], K1[1])
     Rlr32, tlr32 = Rlr.astype(np.float32), tlr.astype(np.float32)
     # reference evaluation: Hamming knn (ties to the lower train index), ratio in double, gate in fp64
-    ham = (np.unpackbits(dl[mono_l:], axis=1)[:, None, :] != np.unpackbits(dr[mono_r:], axis=1)[None, :, :]).sum(-1)
-    order = np.argsort(ham, axis=1, kind="stable")
-    b0, b1 = order[:, 0], order[:, 1]
-    d0, d1 = ham[np.arange(len(b0)), b0], ham[np.arange(len(b0)), b1]
-    cand = d0.astype(np.float64) < d1.astype(np.float64) * 0.7
-    qi, ti = np.nonzero(cand)[0] + mono_l, b0[cand] + mono_r
+    qi, ti = G.fisheye_ratio_candidates(dl, dr, mono_l, mono_r)
     uv1 = np.stack([kl["x"][qi], kl["y"][qi]], 1).astype(np.float64)
     uv2 = np.stack([kr["x"][ti], kr["y"][ti]], 1).astype(np.float64)
     ok, margin = G.epipolar_gate64(G.CAM_L, G.CAM_R, uv1, uv2, Rlr32.astype(np.float64), tlr32.astype(np.float64),
