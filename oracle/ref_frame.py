@@ -1,4 +1,4 @@
-"""oracle/_ref/libref_frame.so — four functions of the REFERENCE's own src/Frame.cc compiled here, verbatim —
+"""oracle/_ref/libref_frame.so — the hot-path functions of the REFERENCE's own src/Frame.cc compiled here, verbatim —
 TEST INFRASTRUCTURE ONLY.
 
 Frame.cc as a whole cannot be compiled in this image (constructors, IMU and BoW members need Eigen, Sophus, g2o,
@@ -132,3 +132,23 @@ def stereo_fisheye_matches(kps_l, desc_l, mono_l, kps_r, desc_r, mono_r, level_s
     L.ref_stereo_fisheye_matches(_p(kl), _p(dl), kl.size, int(mono_l), _p(kr), _p(dr), kr.size, int(mono_r), _p(sg), sg.size,
                                  _p(td), _p(l2r), _p(r2l), _p(dp))
     return l2r, r2l, dp
+
+
+def grid_queries(kps, bounds, qx, qy, qr, qmin, qmax):
+    """Frame::AssignFeaturesToGrid + GetFeaturesInArea (the reference's text) -> (cand_off [nq+1], cand_idx)."""
+    k = np.ascontiguousarray(kps)
+    qx, qy, qr = _f32(qx), _f32(qy), _f32(qr)
+    qmin, qmax = np.ascontiguousarray(qmin, np.int32), np.ascontiguousarray(qmax, np.int32)
+    b = _f32(bounds)
+    nq = qx.size
+    off = np.zeros(nq + 1, np.int32)
+    cap = max(1, nq * 64)
+    L = lib()
+    L.ref_grid_queries.restype = C.c_int
+    L.ref_grid_queries.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 6 + [C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+    while True:
+        idx = np.zeros(cap, np.int32)
+        tot = L.ref_grid_queries(_p(k), k.size, _p(b), _p(qx), _p(qy), _p(qr), _p(qmin), _p(qmax), nq, _p(off), _p(idx), cap)
+        if tot <= cap:
+            return off, idx[:tot].copy()
+        cap = tot

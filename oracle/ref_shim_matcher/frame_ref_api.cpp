@@ -93,6 +93,29 @@ int ref_compute_stereo_matches(const void* kps_l, const uint8_t* desc_l, int n_l
   return cnt;
 }
 
+// Frame::AssignFeaturesToGrid + GetFeaturesInArea (the reference's own text, grid_ref.cpp) on a single-camera frame:
+// the candidates of query q, in the order the reference returns them, are idx[off[q] .. off[q+1]).  Returns the total
+// number of candidates (idx holds the first `cap` of them).
+int ref_grid_queries(const void* kps, int n, const float* bounds, const float* qx, const float* qy, const float* qr,
+                     const int* qmin, const int* qmax, int nq, int* off, int* idx, int cap) {
+  Frame F;
+  F.N = n;
+  F.mvKeysUn = to_keys(kps, n);
+  F.mnMinX = bounds[0]; F.mnMaxX = bounds[1]; F.mnMinY = bounds[2]; F.mnMaxY = bounds[3];
+  F.mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(F.mnMaxX - F.mnMinX);   // Frame.cc:118-119
+  F.mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(F.mnMaxY - F.mnMinY);
+  F.AssignFeaturesToGrid();
+  int tot = 0;
+  for (int q = 0; q < nq; q++) {
+    off[q] = tot;
+    const std::vector<std::size_t> v = F.GetFeaturesInArea(qx[q], qy[q], qr[q], qmin[q], qmax[q]);
+    for (std::size_t j = 0; j < v.size(); j++, tot++)
+      if (tot < cap) idx[tot] = (int)v[j];
+  }
+  off[nq] = tot;
+  return tot;
+}
+
 // Frame::ComputeStereoFishEyeMatches.  tri_depth[l * n_r + r] = what TriangulateMatches returns for (left l, right r).
 // Outputs: mvLeftToRightMatch [n_l], mvRightToLeftMatch [n_r], mvDepth [n_l].
 void ref_stereo_fisheye_matches(const void* kps_l, const uint8_t* desc_l, int n_l, int mono_l, const void* kps_r,

@@ -87,103 +87,25 @@ void KeyFrame::AddMapPoint(MapPoint* pMP, const std::size_t& idx) {
   if (MapPoint::oplog) MapPoint::oplog->push_back(MapPoint::Op{3, (int)idx, pMP ? pMP->id : -1});
 }
 
-// Frame::AssignFeaturesToGrid (Frame.cc:385-416)
-void Frame::AssignFeaturesToGrid() {
-  mGrid.clear(); mGridRight.clear();
-  for (FeatureGrid* g : {&mGrid, &mGridRight}) {
-    g->mnMinX = mnMinX; g->mnMinY = mnMinY;
-    g->wInv = static_cast<float>(64) / static_cast<float>(mnMaxX - mnMinX);   // Frame.cc:118-119
-    g->hInv = static_cast<float>(48) / static_cast<float>(mnMaxY - mnMinY);
-  }
-  for (int i = 0; i < N; i++) {
-    const cv::KeyPoint& kp = (Nleft == -1) ? mvKeysUn[i] : (i < Nleft) ? mvKeys[i] : mvKeysRight[i - Nleft];
-    int nGridPosX, nGridPosY;
-    if (mGrid.pos(kp, nGridPosX, nGridPosY)) {
-      if (Nleft == -1 || i < Nleft) mGrid.cell[nGridPosX][nGridPosY].push_back(i);
-      else mGridRight.cell[nGridPosX][nGridPosY].push_back(i - Nleft);
+// The grid of a KeyFrame is the grid of the Frame it is made from: KeyFrame::KeyFrame(Frame&, ...) copies the bounds,
+// the cell size and every cell (KeyFrame.cc:34-78).  The stand-in does the same through a temporary Frame whose
+// AssignFeaturesToGrid is the reference's own text (grid_ref.cpp).
+void KeyFrame::AssignFeaturesToGrid() {
+  Frame F;
+  F.N = N; F.Nleft = NLeft;
+  F.mvKeys = mvKeys; F.mvKeysRight = mvKeysRight; F.mvKeysUn = mvKeysUn;
+  F.mnMinX = mnMinX; F.mnMaxX = mnMaxX; F.mnMinY = mnMinY; F.mnMaxY = mnMaxY;
+  F.mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(mnMaxX - mnMinX);   // Frame.cc:118-119
+  F.mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(mnMaxY - mnMinY);
+  F.AssignFeaturesToGrid();
+  mfGridElementWidthInv = F.mfGridElementWidthInv; mfGridElementHeightInv = F.mfGridElementHeightInv;
+  mGrid.assign(mnGridCols, std::vector<std::vector<std::size_t> >(mnGridRows));       // KeyFrame.cc:65-77
+  mGridRight.assign(mnGridCols, std::vector<std::vector<std::size_t> >(mnGridRows));
+  for (int i = 0; i < mnGridCols; i++)
+    for (int j = 0; j < mnGridRows; j++) {
+      mGrid[i][j] = F.mGrid[i][j];
+      if (F.Nleft != -1) mGridRight[i][j] = F.mGridRight[i][j];
     }
-  }
-}
-
-// Frame::GetFeaturesInArea (Frame.cc:657-723)
-std::vector<std::size_t> Frame::GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel,
-                                                  const int maxLevel, const bool bRight) const {
-  std::vector<std::size_t> vIndices;
-  vIndices.reserve(N);
-  float factorX = r;
-  float factorY = r;
-  const int nMinCellX = std::max(0, (int)floor((x - mnMinX - factorX) * mGrid.wInv));
-  if (nMinCellX >= 64) return vIndices;
-  const int nMaxCellX = std::min((int)64 - 1, (int)ceil((x - mnMinX + factorX) * mGrid.wInv));
-  if (nMaxCellX < 0) return vIndices;
-  const int nMinCellY = std::max(0, (int)floor((y - mnMinY - factorY) * mGrid.hInv));
-  if (nMinCellY >= 48) return vIndices;
-  const int nMaxCellY = std::min((int)48 - 1, (int)ceil((y - mnMinY + factorY) * mGrid.hInv));
-  if (nMaxCellY < 0) return vIndices;
-  const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
-  for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
-    for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
-      const std::vector<std::size_t>& vCell = (!bRight) ? mGrid.cell[ix][iy] : mGridRight.cell[ix][iy];
-      if (vCell.empty()) continue;
-      for (std::size_t j = 0, jend = vCell.size(); j < jend; j++) {
-        const cv::KeyPoint& kpUn = (Nleft == -1) ? mvKeysUn[vCell[j]] : (!bRight) ? mvKeys[vCell[j]] : mvKeysRight[vCell[j]];
-        if (bCheckLevels) {
-          if (kpUn.octave < minLevel) continue;
-          if (maxLevel >= 0)
-            if (kpUn.octave > maxLevel) continue;
-        }
-        const float distx = kpUn.pt.x - x;
-        const float disty = kpUn.pt.y - y;
-        if (fabs(distx) < factorX && fabs(disty) < factorY) vIndices.push_back(vCell[j]);
-      }
-    }
-  }
-  return vIndices;
-}
-
-void KeyFrame::AssignFeaturesToGrid() {  // the keyframe copies the frame's grid (KeyFrame.cc:62-75)
-  mGrid.clear(); mGridRight.clear();
-  for (FeatureGrid* g : {&mGrid, &mGridRight}) {
-    g->mnMinX = mnMinX; g->mnMinY = mnMinY;
-    g->wInv = static_cast<float>(64) / static_cast<float>(mnMaxX - mnMinX);
-    g->hInv = static_cast<float>(48) / static_cast<float>(mnMaxY - mnMinY);
-  }
-  for (int i = 0; i < N; i++) {
-    const cv::KeyPoint& kp = (NLeft == -1) ? mvKeysUn[i] : (i < NLeft) ? mvKeys[i] : mvKeysRight[i - NLeft];
-    int px, py;
-    if (mGrid.pos(kp, px, py)) {
-      if (NLeft == -1 || i < NLeft) mGrid.cell[px][py].push_back(i);
-      else mGridRight.cell[px][py].push_back(i - NLeft);
-    }
-  }
-}
-
-// KeyFrame::GetFeaturesInArea (KeyFrame.cc:704-748)
-std::vector<std::size_t> KeyFrame::GetFeaturesInArea(const float& x, const float& y, const float& r, const bool bRight) const {
-  std::vector<std::size_t> vIndices;
-  vIndices.reserve(N);
-  float factorX = r;
-  float factorY = r;
-  const int nMinCellX = std::max(0, (int)floor((x - mnMinX - factorX) * mGrid.wInv));
-  if (nMinCellX >= 64) return vIndices;
-  const int nMaxCellX = std::min((int)64 - 1, (int)ceil((x - mnMinX + factorX) * mGrid.wInv));
-  if (nMaxCellX < 0) return vIndices;
-  const int nMinCellY = std::max(0, (int)floor((y - mnMinY - factorY) * mGrid.hInv));
-  if (nMinCellY >= 48) return vIndices;
-  const int nMaxCellY = std::min((int)48 - 1, (int)ceil((y - mnMinY + factorY) * mGrid.hInv));
-  if (nMaxCellY < 0) return vIndices;
-  for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
-    for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
-      const std::vector<std::size_t>& vCell = (!bRight) ? mGrid.cell[ix][iy] : mGridRight.cell[ix][iy];
-      for (std::size_t j = 0, jend = vCell.size(); j < jend; j++) {
-        const cv::KeyPoint& kpUn = (NLeft == -1) ? mvKeysUn[vCell[j]] : (!bRight) ? mvKeys[vCell[j]] : mvKeysRight[vCell[j]];
-        const float distx = kpUn.pt.x - x;
-        const float disty = kpUn.pt.y - y;
-        if (fabs(distx) < r && fabs(disty) < r) vIndices.push_back(vCell[j]);
-      }
-    }
-  }
-  return vIndices;
 }
 
 }  // namespace ORB_SLAM3
@@ -245,6 +167,8 @@ void fill_frame(Frame& F, const void* kps_l, const uint8_t* desc_l, int n_l, con
   F.mnScaleLevels = nlevels;
   F.mfLogScaleFactor = logf(scale_factors[1]);
   F.mnMinX = bounds[0]; F.mnMaxX = bounds[1]; F.mnMinY = bounds[2]; F.mnMaxY = bounds[3];
+  F.mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(F.mnMaxX - F.mnMinX);   // Frame.cc:118-119
+  F.mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(F.mnMaxY - F.mnMinY);
   F.AssignFeaturesToGrid();
 }
 

@@ -10,8 +10,9 @@
 //   DBoW2::FeatureVector                                          std::map<NodeId, std::vector<unsigned>> (FeatureVector.h:24)
 //   ORB_SLAM3::GeometricCamera / Pinhole                          project + epipolarConstrain (Pinhole.cpp:49-55, 107-129)
 //   ORB_SLAM3::MapPoint / KeyFrame / Frame                        data members under the reference's names; the grid
-//                                                                 (AssignFeaturesToGrid / GetFeaturesInArea / PosInGrid,
-//                                                                 Frame.cc:385-416, 657-735; KeyFrame.cc:704-748) is restated
+//                                                                 functions (AssignFeaturesToGrid / GetFeaturesInArea /
+//                                                                 PosInGrid, Frame.cc:385-416, 657-735; KeyFrame.cc:704-748)
+//                                                                 are the reference's own text (grid_ref.cpp)
 // The OpenCV types come from the shim that already serves ORBextractor.cc (oracle/ref_shim/opencv2).
 // What this pins: every loop, gate, tie rule, `continue`, histogram and index write of ORBmatcher.cc runs as the
 // reference wrote and compiled it (-O3 -march=x86-64-v3 -std=c++14); the stand-ins only hold data.
@@ -226,17 +227,11 @@ class KannalaBrandt8 : public GeometricCamera {
   }
 };
 
-// 64 x 48 grid shared by Frame and KeyFrame (Frame.h:44-45; Frame.cc:385-416, 657-735; KeyFrame.cc:704-748)
-struct FeatureGrid {
-  std::vector<std::size_t> cell[64][48];
-  float mnMinX = 0, mnMinY = 0, wInv = 1, hInv = 1;
-  void clear() { for (auto& c : cell) for (auto& r : c) r.clear(); }
-  bool pos(const cv::KeyPoint& kp, int& posX, int& posY) const {  // Frame::PosInGrid
-    posX = round((kp.pt.x - mnMinX) * wInv);
-    posY = round((kp.pt.y - mnMinY) * hInv);
-    return !(posX < 0 || posX >= 64 || posY < 0 || posY >= 48);
-  }
-};
+// 64 x 48 feature grid (Frame.h:44-45, 250-252, 344; KeyFrame.h:320-321, 458, 518).  AssignFeaturesToGrid, PosInGrid and
+// both GetFeaturesInArea are the REFERENCE's own text: grid_ref.cpp includes them, cut verbatim out of Frame.cc:385-416,
+// 657-735 and KeyFrame.cc:704-748 at build time (oracle/extract_ref_functions.py).
+#define FRAME_GRID_ROWS 48
+#define FRAME_GRID_COLS 64
 
 class Frame {
  public:
@@ -253,7 +248,10 @@ class Frame {
   int mnScaleLevels = 8;
   GeometricCamera *mpCamera = nullptr, *mpCamera2 = nullptr;
   Sophus::SE3f mTcw, mTrl;
-  FeatureGrid mGrid, mGridRight;
+  float mfGridElementWidthInv = 1, mfGridElementHeightInv = 1;  // static in the reference (Frame.h:250-251)
+  std::vector<std::size_t> mGrid[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+  std::vector<std::size_t> mGridRight[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+  bool PosInGrid(const cv::KeyPoint& kp, int& posX, int& posY);
 
   // members and functions of the Frame.cc functions compiled by `make ref_frame` (frame_ref_api.cpp): stereo matching
   // (Frame.cc:811-1005) and the frustum test (:512-586, :1168-1242)
@@ -295,7 +293,9 @@ class KeyFrame {
   int mnScaleLevels = 8;
   GeometricCamera *mpCamera = nullptr, *mpCamera2 = nullptr;
   Sophus::SE3f mTcw, mTrl;
-  FeatureGrid mGrid, mGridRight;
+  int mnGridCols = FRAME_GRID_COLS, mnGridRows = FRAME_GRID_ROWS;
+  float mfGridElementWidthInv = 1, mfGridElementHeightInv = 1;
+  std::vector<std::vector<std::vector<std::size_t> > > mGrid, mGridRight;
 
   Sophus::SE3f GetPose() { return mTcw; }
   Sophus::SE3f GetPoseInverse() { return mTcw.inverse(); }

@@ -157,3 +157,27 @@ def test_stereo_fisheye_index_logic(oracle_mod, RF, seed, accept):
     assert ok.sum() > 60 and (~ok).sum() > 20 and (l2r[:mono_l] == -1).all()
     stolen = (wl2r >= 0) & (wr2l[np.maximum(wl2r, 0)] != np.arange(len(kl)))
     assert stolen.sum() > 3                                          # a right feature claimed by two lefts
+
+
+@pytest.mark.parametrize("cfg,bounds", [("C1", (0.0, 752.0, 0.0, 480.0)), ("C1", (-13.4, 771.2, -9.7, 493.1)),
+                                        ("C5", (0.0, 3840.0, 0.0, 2160.0))])
+def test_grid_and_area_query(oracle_mod, RF, cfg, bounds):
+    """Row m10: Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea (Frame.cc:385-416, 657-735) — the candidates
+    of every window and the ORDER they come in (it decides the ties of every matcher loop): levels open / lower bound
+    only / closed band, windows that leave the image, undistorted bounds that are not the image rectangle."""
+    rng = np.random.default_rng(61)
+    ex = oracle_mod.Extractor(1000 if cfg == "C1" else 5000)
+    k, _, _ = ex.extract(S.make_frames(cfg, 1)[0], (0, 0))
+    w, h = bounds[1] - bounds[0], bounds[3] - bounds[2]
+    nq = 6000
+    qx = (bounds[0] + rng.random(nq) * w * 1.1 - 0.05 * w).astype(f32)
+    qy = (bounds[2] + rng.random(nq) * h * 1.1 - 0.05 * h).astype(f32)
+    qr = (rng.choice([4.0, 12.0, 15.0, 40.0, 120.0], nq) * rng.choice([1.0, 1.2, 1.728], nq)).astype(f32)
+    kind = rng.integers(0, 4, nq)
+    lv = rng.integers(0, 8, nq)
+    qmin = np.where(kind == 0, -1, np.where(kind == 1, lv, lv - 1)).astype(np.int32)
+    qmax = np.where(kind <= 1, -1, np.where(kind == 2, lv, lv + 1)).astype(np.int32)
+    off, idx = oracle_mod.grid_queries(k, bounds, qx, qy, qr, qmin, qmax)
+    roff, ridx = RF.grid_queries(k, bounds, qx, qy, qr, qmin, qmax)
+    assert np.array_equal(roff, off) and np.array_equal(ridx, idx)
+    assert len(idx) > 20 * nq // 10 and (np.diff(off) == 0).sum() > 50
