@@ -152,3 +152,18 @@ def grid_queries(kps, bounds, qx, qy, qr, qmin, qmax):
         if tot <= cap:
             return off, idx[:tot].copy()
         cap = tot
+
+
+def distinctive_descriptor(desc, first, second=None, kf_bad=None):
+    """MapPoint::ComputeDistinctiveDescriptors.  desc [rows, 32]; observation o holds row first[o] (and second[o] when
+    >= 0).  Returns the chosen 32-byte descriptor, or None when the MapPoint kept none."""
+    d = np.ascontiguousarray(desc, np.uint8)
+    f = np.ascontiguousarray(first, np.int32)
+    s2 = np.full(f.size, -1, np.int32) if second is None else np.ascontiguousarray(second, np.int32)
+    kb = np.zeros(f.size, np.uint8) if kf_bad is None else np.ascontiguousarray(kf_bad, np.uint8)
+    out = np.zeros(32, np.uint8)
+    L = lib()
+    L.ref_distinctive_descriptor.restype = C.c_int
+    L.ref_distinctive_descriptor.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    ok = L.ref_distinctive_descriptor(_p(d), d.shape[0], _p(f), _p(s2), _p(kb), f.size, _p(out))
+    return out if ok else None

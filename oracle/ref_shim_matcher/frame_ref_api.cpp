@@ -93,6 +93,25 @@ int ref_compute_stereo_matches(const void* kps_l, const uint8_t* desc_l, int n_l
   return cnt;
 }
 
+// MapPoint::ComputeDistinctiveDescriptors (the reference's own text, mappoint_ref.cpp).  Observation o is keyframe o
+// (keyframes live in one array, so the std::map<KeyFrame*, ...> of the MapPoint visits them in index order); it
+// contributes descriptor row first[o] and, when second[o] >= 0, that row too (the right-camera index of a rig).
+// kf_bad[o] != 0: that keyframe isBad().  Writes the chosen descriptor (32 bytes); returns 1 when one was chosen.
+int ref_distinctive_descriptor(const uint8_t* desc, int n_rows, const int* first, const int* second, const uint8_t* kf_bad,
+                               int n_obs, uint8_t* chosen) {
+  std::vector<KeyFrame> kfs(n_obs);
+  MapPoint p;
+  for (int o = 0; o < n_obs; o++) {
+    kfs[o].mDescriptors = to_desc(desc, n_rows);
+    kfs[o].mbBad = kf_bad && kf_bad[o];
+    p.mObservations[&kfs[o]] = std::tuple<int, int>(first[o], second[o]);
+  }
+  p.ComputeDistinctiveDescriptors();
+  if (p.mDescriptor.empty()) return 0;
+  memcpy(chosen, p.mDescriptor.data, 32);
+  return 1;
+}
+
 // Frame::AssignFeaturesToGrid + GetFeaturesInArea (the reference's own text, grid_ref.cpp) on a single-camera frame:
 // the candidates of query q, in the order the reference returns them, are idx[off[q] .. off[q+1]).  Returns the total
 // number of candidates (idx holds the first `cap` of them).

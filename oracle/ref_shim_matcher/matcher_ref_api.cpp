@@ -2,8 +2,10 @@
 // MapPoint objects (prelude.h) from flat arrays and call the REFERENCE's own ORBmatcher methods, compiled unmodified
 // from /root/reference/src/ORBmatcher.cc.  TEST INFRASTRUCTURE ONLY (tests/test_ref_matcher.py compares these
 // results with the oracle's restatements on the same inputs; that is what pins the matcher rows).
-// Also holds the out-of-line members of the stand-ins.  Compiled with -ffp-contract=off (camera arithmetic and
-// PredictScale are not part of ORBmatcher.cc; the oracle evaluates them uncontracted too).
+// Also holds the out-of-line members of the stand-ins that are NOT reference text (pinhole camera arithmetic, the
+// map-mutation log); the grid functions and MapPoint::PredictScale / Get*DistanceInvariance /
+// ComputeDistinctiveDescriptors are the reference's own text (grid_ref.cpp, mappoint_ref.cpp).  Compiled with
+// -ffp-contract=off (camera arithmetic is not part of ORBmatcher.cc; the oracle evaluates it uncontracted too).
 #include "prelude.h"
 
 #include "ORBmatcher.h"
@@ -53,20 +55,6 @@ bool GeometricCamera::epipolarConstrain(GeometricCamera* pCamera2, const cv::Key
   return dsqr < 3.84 * unc;
 }
 
-int MapPoint::PredictScale(const float& currentDist, KeyFrame* pKF) {  // MapPoint.cc:514-529
-  const float ratio = mfMaxDistance / currentDist;
-  int nScale = ceil(log(ratio) / pKF->mfLogScaleFactor);
-  if (nScale < 0) nScale = 0;
-  else if (nScale >= pKF->mnScaleLevels) nScale = pKF->mnScaleLevels - 1;
-  return nScale;
-}
-int MapPoint::PredictScale(const float& currentDist, Frame* pF) {  // MapPoint.cc:531-546
-  const float ratio = mfMaxDistance / currentDist;
-  int nScale = ceil(log(ratio) / pF->mfLogScaleFactor);
-  if (nScale < 0) nScale = 0;
-  else if (nScale >= pF->mnScaleLevels) nScale = pF->mnScaleLevels - 1;
-  return nScale;
-}
 void MapPoint::AddObservation(KeyFrame* pKF, int idx) {
   mObservations[pKF] = std::tuple<int, int>(idx, -1);
   nObs++;

@@ -174,6 +174,13 @@ class GeometricCamera {
                           const Eigen::Vector3f& t12, float F12[9]);
 };
 
+// std::mutex that survives the copies the test harness makes of its stand-in objects (each copy gets a fresh mutex)
+struct CopyableMutex : std::mutex {
+  CopyableMutex() {}
+  CopyableMutex(const CopyableMutex&) : std::mutex() {}
+  CopyableMutex& operator=(const CopyableMutex&) { return *this; }
+};
+
 class MapPoint {
  public:
   int id = -1;
@@ -198,10 +205,13 @@ class MapPoint {
   cv::Mat GetDescriptor() { return mDescriptor.clone(); }
   Eigen::Vector3f GetWorldPos() { return mWorldPos; }
   Eigen::Vector3f GetNormal() { return mNormalVector; }
-  float GetMinDistanceInvariance() { return 0.8f * mfMinDistance; }   // MapPoint.cc:502-506
-  float GetMaxDistanceInvariance() { return 1.2f * mfMaxDistance; }   // MapPoint.cc:508-512
-  int PredictScale(const float& currentDist, KeyFrame* pKF);          // MapPoint.cc:514-529
-  int PredictScale(const float& currentDist, Frame* pF);              // MapPoint.cc:531-546
+  // the reference's own text, cut out of MapPoint.cc at build time (mappoint_ref.cpp)
+  float GetMinDistanceInvariance();                                   // MapPoint.cc:498-502
+  float GetMaxDistanceInvariance();                                   // MapPoint.cc:504-508
+  int PredictScale(const float& currentDist, KeyFrame* pKF);          // MapPoint.cc:510-525
+  int PredictScale(const float& currentDist, Frame* pF);              // MapPoint.cc:527-542
+  void ComputeDistinctiveDescriptors();                               // MapPoint.cc:328-402
+  CopyableMutex mMutexFeatures, mMutexPos;
   bool IsInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) != 0; }
   std::tuple<int, int> GetIndexInKeyFrame(KeyFrame* pKF) {
     auto it = mObservations.find(pKF);
@@ -297,6 +307,8 @@ class KeyFrame {
   float mfGridElementWidthInv = 1, mfGridElementHeightInv = 1;
   std::vector<std::vector<std::vector<std::size_t> > > mGrid, mGridRight;
 
+  bool mbBad = false;
+  bool isBad() { return mbBad; }
   Sophus::SE3f GetPose() { return mTcw; }
   Sophus::SE3f GetPoseInverse() { return mTcw.inverse(); }
   Eigen::Vector3f GetCameraCenter() { return mTcw.inverse().translation(); }

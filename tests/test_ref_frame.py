@@ -181,3 +181,33 @@ def test_grid_and_area_query(oracle_mod, RF, cfg, bounds):
     roff, ridx = RF.grid_queries(k, bounds, qx, qy, qr, qmin, qmax)
     assert np.array_equal(roff, off) and np.array_equal(ridx, idx)
     assert len(idx) > 20 * nq // 10 and (np.diff(off) == 0).sum() > 50
+
+
+def test_compute_distinctive_descriptors(oracle_mod, RF):
+    """MapPoint.cc:328-402: the observed descriptor with the least median distance to the others (median = element
+    0.5*(N-1) of the sorted row, first minimum wins), bad keyframes skipped, left and right index of a rig keyframe."""
+    rng = np.random.default_rng(71)
+    base = rng.integers(0, 256, (40, 32), dtype=np.uint8)
+    for trial in range(300):
+        n_obs = int(rng.integers(1, 14))
+        rows = int(rng.integers(n_obs, 3 * n_obs + 1))
+        flips = rng.random((rows, 256)) < rng.choice([0.02, 0.1, 0.3])
+        desc = base[trial % 40][None, :] ^ np.packbits(flips, axis=1, bitorder="little")
+        if trial % 5 == 0:
+            desc[rng.integers(0, rows)] = desc[0]                    # ties between identical descriptors
+        first = rng.integers(0, rows, n_obs).astype(np.int32)
+        second = np.where(rng.random(n_obs) < 0.3, rng.integers(0, rows, n_obs), -1).astype(np.int32)
+        bad = (rng.random(n_obs) < 0.15).astype(np.uint8)
+        got = RF.distinctive_descriptor(desc, first, second, bad)
+        order = []
+        for o in range(n_obs):
+            if bad[o]:
+                continue
+            order.append(first[o])
+            if second[o] >= 0:
+                order.append(second[o])
+        if not order:
+            assert got is None
+            continue
+        best = oracle_mod.distinctive_descriptor(desc[order])
+        assert np.array_equal(got, desc[order][best]), trial
