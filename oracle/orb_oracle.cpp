@@ -1392,6 +1392,8 @@ int oracle_search_for_triangulation(const void* kps1_v, const uint8_t* desc1, in
 // word id node_word[i] and weight node_weight[i] (leaves).  Outputs per feature: word / node / weight; the
 // BowVector as (bow_word ascending, bow_val normalised), and the FeatureVector CSR.  Returns the number of
 // BowVector entries; *fv_nn = number of FeatureVector nodes.
+// PINNED: oracle/_ref/libref_dbow.so compiles the reference's own Thirdparty/DBoW2 unmodified (oracle/Makefile target
+// `ref_dbow`); tests/test_ref_dbow.py asserts array_equal with it, the fp64 BowVector values included.
 int oracle_bow_transform(const uint8_t* desc, int n, const int* child_off, const int* child_idx,
                          const uint8_t* node_desc, const int* node_word, const double* node_weight, int L,
                          int levelsup, int* feat_word, int* feat_node, double* feat_weight, int* bow_word,
