@@ -15,11 +15,12 @@ def main():
     lines = open(src).read().split("\n")
     chunks = []
     for sig in sigs:
-        starts = [i for i, l in enumerate(lines) if l.startswith(sig)]
+        starts = [i for i, l in enumerate(lines) if l.lstrip().startswith(sig)]
         if len(starts) != 1:
             sys.exit("extract_ref_functions: %d definitions start with %r in %s" % (len(starts), sig, src))
         a = starts[0]
-        b = next(i for i in range(a + 1, len(lines)) if lines[i].rstrip() == "}")
+        indent = lines[a][:len(lines[a]) - len(lines[a].lstrip())]   # the closing brace sits at the signature's indentation
+        b = next(i for i in range(a + 1, len(lines)) if lines[i].rstrip() == indent + "}")
         chunks.append("#line %d \"%s\"\n" % (a + 1, src) + "\n".join(lines[a:b + 1]) + "\n")
     open(out, "w").write("\n".join(chunks))
 

@@ -7,7 +7,7 @@
 //                                     opencv calib3d undistort.dispatch.cpp cvUndistortPointsInternal, 5 iterations)
 //   Frame::isInFrustum                src/Frame.cc:512-586, isInFrustumChecks :1168-1242
 //   MapPoint::PredictScale            src/MapPoint.cc:531-546 (libm logf)
-//   GeometricCamera::project          src/CameraModels/Pinhole.cpp:49-55, KannalaBrandt8.cpp:67-85 (libm atan2f/cos/sin)
+//   GeometricCamera::project          src/CameraModels/Pinhole.cpp:49-55, KannalaBrandt8.cpp:67-85 (libm atan2f, double cos / sin)
 //
 // PINNING: undistortPoints is pinned bit for bit against the real OpenCV 4.13 binary (cv2.undistortPoints,
 // tests/test_frame_geometry.py).  isInFrustum / isInFrustumChecks are pinned against the reference's own text:
@@ -47,8 +47,11 @@ void project(int model, const float* cam /*fx,fy,cx,cy,k0..k3*/, float X, float 
   const float theta7 = theta5 * theta2;
   const float theta9 = theta7 * theta2;
   const float r = theta + cam[4] * theta3 + cam[5] * theta5 + cam[6] * theta7 + cam[7] * theta9;
-  *u = cam[0] * r * cosf(psi) + cam[2];
-  *v = cam[1] * r * sinf(psi) + cam[3];
+  // `cos(psi)` / `sin(psi)` in KannalaBrandt8.cpp are the double functions (no using-directive for std reaches that
+  // translation unit), so fx * r (float) is multiplied by the cosine and added to cx in double, then stored as float.
+  // Pinned against the reference's own text (oracle/ref_shim_matcher/camera_ref.cpp, tests/test_ref_frame.py).
+  *u = (float)((double)(cam[0] * r) * cos((double)psi) + (double)cam[2]);
+  *v = (float)((double)(cam[1] * r) * sin((double)psi) + (double)cam[3]);
 }
 
 }  // namespace

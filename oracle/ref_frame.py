@@ -167,3 +167,28 @@ def distinctive_descriptor(desc, first, second=None, kf_bad=None):
     L.ref_distinctive_descriptor.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     ok = L.ref_distinctive_descriptor(_p(d), d.shape[0], _p(f), _p(s2), _p(kb), f.size, _p(out))
     return out if ok else None
+
+
+def camera_project(model, cam, xyz):
+    """Pinhole::project (model 0, cam = fx, fy, cx, cy) / KannalaBrandt8::project (model 1, cam + k0..k3) of
+    Eigen::Vector3f points, the reference's own text.  Returns uv [n, 2]."""
+    c = _f32(list(cam) + [0.0] * (8 - len(cam)))
+    P = _f32(xyz).reshape(-1, 3)
+    uv = np.zeros((P.shape[0], 2), np.float32)
+    L = lib()
+    L.ref_camera_project.restype = None
+    L.ref_camera_project.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    L.ref_camera_project(int(model), _p(c), _p(P), P.shape[0], _p(uv))
+    return uv
+
+
+def kb8_unproject(cam, uv):
+    """KannalaBrandt8::unprojectEig (10 Newton steps, precision 1e-6), the reference's own text.  Returns rays [n, 3]."""
+    c = _f32(cam)
+    p = _f32(uv).reshape(-1, 2)
+    ray = np.zeros((p.shape[0], 3), np.float32)
+    L = lib()
+    L.ref_kb8_unproject.restype = None
+    L.ref_kb8_unproject.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    L.ref_kb8_unproject(_p(c), _p(p), p.shape[0], _p(ray))
+    return ray

@@ -33,6 +33,15 @@
 #define EIGEN_MAKE_ALIGNED_OPERATOR_NEW
 
 namespace cv {
+template <typename T> struct Point3_ {
+  T x, y, z;
+  Point3_() : x(0), y(0), z(0) {}
+  Point3_(T _x, T _y, T _z) : x(_x), y(_y), z(_z) {}
+};
+typedef Point3_<float> Point3f;
+}  // namespace cv
+
+namespace cv {
 // cv::DMatch and the brute-force Hamming matcher of Frame.h:337 (cv::BFMatcher(cv::NORM_HAMMING), crossCheck off).
 // knnMatch: per query row the k nearest train rows by Hamming distance, nearest first; equal distances keep the lower
 // train index first (OpenCV's batch distance + partial sort walks train rows in order and replaces on `<` only).
@@ -69,6 +78,8 @@ struct Vector2f {
   Vector2f(float a, float b) : v{a, b} {}
   float operator()(int i) const { return v[i]; }
   float& operator()(int i) { return v[i]; }
+  float operator[](int i) const { return v[i]; }
+  float& operator[](int i) { return v[i]; }
 };
 struct Vector3f {
   float v[3];
@@ -76,6 +87,8 @@ struct Vector3f {
   Vector3f(float a, float b, float c) : v{a, b, c} {}
   float operator()(int i) const { return v[i]; }
   float& operator()(int i) { return v[i]; }
+  float operator[](int i) const { return v[i]; }
+  float& operator[](int i) { return v[i]; }
   Vector3f operator-(const Vector3f& o) const { return Vector3f(v[0] - o.v[0], v[1] - o.v[1], v[2] - o.v[2]); }
   Vector3f operator+(const Vector3f& o) const { return Vector3f(v[0] + o.v[0], v[1] + o.v[1], v[2] + o.v[2]); }
   Vector3f operator/(float s) const { return Vector3f(v[0] / s, v[1] / s, v[2] / s); }
@@ -226,6 +239,12 @@ class MapPoint {
 // so this stand-in answers from a table the test supplies: depth[class_id of kp1][class_id of kp2], p3D = (0, 0, depth).
 class KannalaBrandt8 : public GeometricCamera {
  public:
+  // project / unproject / unprojectEig are the reference's own text (KannalaBrandt8.cpp:67-85, 111-146), camera_ref.cpp
+  std::vector<float> mvParameters;   // fx, fy, cx, cy, k0..k3 (GeometricCamera.h:104)
+  const float precision = 1e-6;      // KannalaBrandt8.h:42-47
+  Eigen::Vector2f project(const Eigen::Vector3f& v3D);
+  cv::Point3f unproject(const cv::Point2f& p2D);
+  Eigen::Vector3f unprojectEig(const cv::Point2f& p2D);
   const float* depth_table = nullptr;
   int table_cols = 0;
   float TriangulateMatches(GeometricCamera* /*pCamera2*/, const cv::KeyPoint& kp1, const cv::KeyPoint& kp2,
@@ -235,6 +254,13 @@ class KannalaBrandt8 : public GeometricCamera {
     p3D = Eigen::Vector3f(0.f, 0.f, d);
     return d;
   }
+};
+
+// Pinhole::project(const Eigen::Vector3f&) is the reference's own text (Pinhole.cpp:49-55), camera_ref.cpp
+class Pinhole : public GeometricCamera {
+ public:
+  std::vector<float> mvParameters;   // fx, fy, cx, cy
+  Eigen::Vector2f project(const Eigen::Vector3f& v3D);
 };
 
 // 64 x 48 feature grid (Frame.h:44-45, 250-252, 344; KeyFrame.h:320-321, 458, 518).  AssignFeaturesToGrid, PosInGrid and
@@ -337,4 +363,6 @@ class KeyFrame {
 
 // include/ORBmatcher.h:76,84,87 write `pair` / `vector` unqualified: the reference gets the names from the global
 // `using namespace std;` of Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:36, reached through KeyFrame.h -> ORBVocabulary.h
+#ifndef ORBX_PRELUDE_NO_USING_STD
 using namespace std;
+#endif

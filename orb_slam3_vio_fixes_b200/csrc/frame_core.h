@@ -100,8 +100,11 @@ ORBX_HD void orbx_project(const OrbxFrustumCam& C, float X, float Y, float Z, fl
   const float psi = orbx_atan2f(Y, X);
   const float t2 = f_mul(theta, theta), t3 = f_mul(theta, t2), t5 = f_mul(t3, t2), t7 = f_mul(t5, t2), t9 = f_mul(t7, t2);
   const float r = f_add(f_add(f_add(f_add(theta, f_mul(C.k[0], t3)), f_mul(C.k[1], t5)), f_mul(C.k[2], t7)), f_mul(C.k[3], t9));
-  *u = f_add(f_mul(f_mul(C.fx, r), orbx_cosf(psi)), C.cx);
-  *v = f_add(f_mul(f_mul(C.fy, r), orbx_sinf(psi)), C.cy);
+  // KannalaBrandt8.cpp:81-82: `cos(psi)` / `sin(psi)` are the double functions there, so fx * r (float) times the cosine
+  // plus cx is evaluated in double and stored as float (tolerance contract: the device's double cos / sin are not
+  // glibc's; after the rounding to float the results agree except for rare double-rounding cases).
+  *u = (float)d_add(d_mul((double)f_mul(C.fx, r), cos((double)psi)), (double)C.cx);
+  *v = (float)d_add(d_mul((double)f_mul(C.fy, r), sin((double)psi)), (double)C.cy);
 }
 
 // One MapPoint against one camera of a frame.  fisheye_rig = 0: Frame::isInFrustum with Nleft == -1 (:514-571);

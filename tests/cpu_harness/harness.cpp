@@ -199,6 +199,15 @@ void h_kb8_epipolar(const float* cam1, const float* cam2, const float* uv1, cons
                                          sigma2[i]) ? 1 : 0;
 }
 
+// tri_core.h for the host: KannalaBrandt8::unprojectEig (cam = fx,fy,cx,cy,k0..k3), uv [n][2] -> ray [n][3]
+void h_kb8_unproject(const float* cam, const float* uv, int n, float* ray) {
+  OrbxFrustumCam C;
+  C.model = 1;
+  C.fx = cam[0]; C.fy = cam[1]; C.cx = cam[2]; C.cy = cam[3];
+  for (int i = 0; i < 4; i++) C.k[i] = cam[4 + i];
+  for (int i = 0; i < n; i++) orbx_kb8_unproject(C, uv[2 * i], uv[2 * i + 1], ray + 3 * i);
+}
+
 void h_fast_atan2(const float* y, const float* x, float* out, int n) {
   for (int i = 0; i < n; i++) out[i] = orbx_fast_atan2(y[i], x[i]);
 }

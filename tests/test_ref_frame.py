@@ -211,3 +211,43 @@ def test_compute_distinctive_descriptors(oracle_mod, RF):
             continue
         best = oracle_mod.distinctive_descriptor(desc[order])
         assert np.array_equal(got, desc[order][best]), trial
+
+
+def _camera_coords(pose, pos):
+    """Rcw * P + tcw the way the oracle / the product evaluate it (3-term dot = c0 + (c1 + c2), uncontracted fp32)."""
+    R, t = pose[:9].reshape(3, 3), pose[9:12]
+    d3 = lambda i: (R[i, 0] * pos[:, 0] + (R[i, 1] * pos[:, 1] + R[i, 2] * pos[:, 2])).astype(f32)
+    return np.stack([(d3(i) + t[i]).astype(f32) for i in range(3)], 1)
+
+
+@pytest.mark.parametrize("model", [0, 1])
+def test_camera_project_is_the_reference_text(oracle_mod, RF, model):
+    """Pinhole::project (Pinhole.cpp:49-55) and KannalaBrandt8::project (KannalaBrandt8.cpp:67-85), cut out of the
+    reference and compiled with the name lookup of its translation units (`cos` / `sin` on a float are the double
+    functions there): bit-exact with the projection inside the oracle's frustum test."""
+    n = 200000
+    pos, normal, mn, mx, pose, cam = frustum_case(n, 5, model=model)
+    bounds = (0.0, 752.0, 0.0, 480.0) if model == 0 else (0.0, 512.0, 0.0, 512.0)
+    log_sf = float(np.log(f32(1.2)).astype(f32))
+    o = oracle_mod.is_in_frustum(pos, normal, mn, mx, pose, cam, 47.9, bounds, 0.5, log_sf, 8, fisheye_rig=(model == 1))
+    iv = o["in_view"] > 0
+    uv = RF.camera_project(model, cam[1:], _camera_coords(pose, pos)[iv])
+    assert iv.sum() > 50000
+    assert np.array_equal(uv[:, 0], o["proj_x"][iv]) and np.array_equal(uv[:, 1], o["proj_y"][iv])
+
+
+def test_kb8_unproject_is_the_reference_text(harness, RF):
+    """KannalaBrandt8::unproject / unprojectEig (KannalaBrandt8.cpp:111-146: 10 Newton steps, precision 1e-6,
+    std::tan) against the product's orbx_kb8_unproject compiled for the host (tests/cpu_harness): bit-exact."""
+    import ctypes as C
+    rng = np.random.default_rng(81)
+    cam = np.array([190.978, 190.973, 254.932, 256.897, 0.0034, 0.00071, -0.0020, 0.00020], f32)   # TUM-VI 512 fisheye
+    uv = (rng.random((100000, 2)) * 512).astype(f32)
+    uv[:50] = cam[2:4]                                              # the principal point: theta_d = 0
+    want = RF.kb8_unproject(cam, uv)
+    got = np.zeros_like(want)
+    harness.h_kb8_unproject.restype = None
+    harness.h_kb8_unproject.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    harness.h_kb8_unproject(cam.ctypes.data, uv.ctypes.data, len(uv), got.ctypes.data)
+    assert np.array_equal(got, want)
+    assert np.isfinite(want).all() and (want[:, 2] == 1).all()
