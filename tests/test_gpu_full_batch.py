@@ -132,3 +132,50 @@ def test_full_step_match_records_partition_invariance(oracle_mod):
                                            kq["octave"] + 1)
         want = oracle_mod.argmin2_csr(desc[f - 1, :n[f - 1]], desc[f, :n[f]], off, idx, kr["octave"].astype(np.int8), 0)
         _same_results(r_all[f, :n[f - 1]], want, with_second=True)
+
+
+@pytest.mark.parametrize("cfg,B,sub", [("C2", 256, 16), ("C4", 128, 8)])
+def test_full_stereo_step_partition_invariance(oracle_mod, cfg, B, sub):
+    """The stereo bench step at its full size (C2: 256 pairs, C4: 128 pairs): both eyes + the whole
+    ComputeStereoMatches.  mvuRight / mvDepth of pair p are the same bytes inside the full step and in a `sub`-pair
+    call; one pair of the step is compared with the oracle's ComputeStereoMatches."""
+    import torch
+    from bench import STEREO
+    from orb_slam3_vio_fixes_b200.extractor import ORBextractor
+    from orb_slam3_vio_fixes_b200.matcher import ORBmatcher
+    w, h, nf, _, _ = S.CONFIGS[cfg]
+    fx, bf = STEREO[cfg]
+    mbf = np.float32(bf)
+    mb = np.float32(bf / fx)
+    max_d = mbf / mb
+    left, right = S.make_frames(cfg, B), S.make_frames(cfg, B, right=True)
+    dl, dr = torch.from_numpy(left).cuda(), torch.from_numpy(right).cuda()
+
+    def run(exl, exr, a, b):
+        ol, orr = exl.extract_batch_device(a, (0, 0)), exr.extract_batch_device(b, (0, 0))
+        sf = exl.GetScaleFactors()
+        bi, bd = ORBmatcher.stereo_rowband(ol["kps"], ol["desc"], ol["n"], orr["kps"], orr["desc"], orr["n"], sf, max_d)
+        r = ORBmatcher.stereo_refine(exl, exr, ol["kps"], ol["n"], orr["kps"], bi, bd, mbf, max_d)
+        torch.cuda.synchronize()
+        n = ol["n"].cpu().numpy()
+        ur, dp = r["u_right"].cpu().numpy(), r["depth"].cpu().numpy()
+        return [_digest(n[p:p + 1], ur[p, :n[p]], dp[p, :n[p]]) for p in range(len(n))], (ol, orr, ur, dp, n)
+
+    exl, exr = ORBextractor(nf, max_batch=B, **ORB), ORBextractor(nf, max_batch=B, **ORB)
+    whole, (ol, orr, ur, dp, n) = run(exl, exr, dl, dr)
+    assert run(exl, exr, dl, dr)[0] == whole                                    # idempotence
+    sl, sr = ORBextractor(nf, max_batch=sub, **ORB), ORBextractor(nf, max_batch=sub, **ORB)
+    parts = []
+    for p0 in range(0, B, sub):
+        parts += run(sl, sr, dl[p0:p0 + sub], dr[p0:p0 + sub])[0]
+    assert _digest(*parts) == _digest(*whole), [p for p in range(B) if parts[p] != whole[p]][:8]
+    # anchor: one pair of the full step against the oracle
+    p = B // 2 + 1
+    el, er = oracle_mod.Extractor(nf, 1.2, 8, 20, 7), oracle_mod.Extractor(nf, 1.2, 8, 20, 7)
+    kl, ddl, _ = el.extract(left[p], (0, 0))
+    kr, ddr, _ = er.extract(right[p], (0, 0))
+    _, _, our, odp, kept = oracle_mod.stereo_matches(kl, ddl, kr, ddr, el.scale_factors, el.inv_scale_factors,
+                                                     [el.pyramid(l) for l in range(8)], [er.pyramid(l) for l in range(8)],
+                                                     mb, mbf)
+    assert n[p] == len(kl) and kept > 100
+    assert np.array_equal(ur[p, :n[p]], our) and np.array_equal(dp[p, :n[p]], odp)
