@@ -124,6 +124,8 @@ k_proj_score(const ProjArgs A, ProjCand* __restrict__ cand, uint8_t* __restrict_
           ix++;
           continue;
         }
+        // (two candidates per trip, which helps k_search_area_tq, loses here: 0.467 vs 0.434 ms whole function — the
+        //  top-4 list and the extra gates leave no registers for the second descriptor)
         const int j = idx[e];
         if (area_any && !any && proj_gate_area(q, k, j)) any = true;
         if (proj_gate(A, q, k, fbase, j)) {
