@@ -12,7 +12,9 @@
 #include "orbx_core.h"
 
 #define ORBX_PLAN_MAX_LEVELS 12
-#define ORBX_BLUR_ROWS 35  // rows per warp tile of k_blur_levels (blur.cu BL_RB)
+#ifndef ORBX_BLUR_ROWS
+#define ORBX_BLUR_ROWS 35
+#endif  // rows per warp tile of k_blur_levels (blur.cu BL_RB); 56 / 70 / 105 measured: describe stage 0.914 / 0.911 / 0.958 ms vs 0.904
 #define ORBX_FAST_STRIP_PX 120  // columns a FAST strip can test per row (lanes 1..30 x 4 px)
 #define ORBX_BLUR_TILE_WORDS 30  // output words (4 px) per warp tile row: lanes 1..30, lanes 0/31 are halo
 
