@@ -480,6 +480,13 @@ int orbm_undistort_keypoints(const orbx_keypoint* d_kps, const int32_t* d_n, int
                              float fx, float fy, float cx, float cy, const float* dist_coef_host,
                              int n_coef, orbx_keypoint* d_kps_un, void* stream);
 
+/* Frame::ComputeImageBounds (Frame.cc:782-808): bounds_host = {mnMinX, mnMaxX, mnMinY, mnMaxY} — the undistorted
+ * image corners (same cv::undistortPoints arithmetic as above, min / max paired as the reference pairs them), or
+ * {0, width, 0, height} when dist_coef_host[0] == 0.  Host only, no stream: these are the `min_x .. max_y` every
+ * grid / search entry point takes. */
+int orbm_compute_image_bounds(int width, int height, float fx, float fy, float cx, float cy,
+                              const float* dist_coef_host, int n_coef, float* bounds_host);
+
 /* GeometricCamera parameters (CameraModels/Pinhole.h, KannalaBrandt8.h: mvParameters). */
 typedef struct orbm_camera {
   int32_t model;          /* 0 = Pinhole, 1 = KannalaBrandt8 */

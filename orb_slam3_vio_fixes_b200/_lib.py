@@ -38,7 +38,7 @@ SYMBOLS = [
     "orbx_create", "orbx_destroy", "orbx_max_keypoints", "orbx_extract", "orbx_extract_batch_device",
     "orbx_extract_batch_host", "orbx_last_outputs_device", "orbx_get_pyramid", "orbx_get_pyramid_all", "orbx_pyramid_device", "orbx_level_size",
     "orbx_get_scale_tables", "orbx_stage_times", "orbx_check_status", "orbx_debug_blur_level", "orbx_debug_sincos_checksum", "orbx_debug_level_keypoints", "orbx_debug_octree", "orbm_argmin2_csr", "orbm_grid_build",
-    "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_search_by_projection_th", "orbm_search_by_projection_static", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
+    "orbm_search_area", "orbm_queries_shift", "orbm_search_by_projection", "orbm_search_by_projection_th", "orbm_search_by_projection_static", "orbm_compute_image_bounds", "orbm_stereo_rowband", "orbm_stereo_refine", "orbm_rgbd_depth", "orbm_knn2_dense",
     "orbm_fuse_candidates", "orbm_descriptor_distance_pairs", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_for_triangulation", "orbm_bow_transform", "orbm_distinctive_descriptors",
     "orbm_undistort_keypoints", "orbm_is_in_frustum",
     "orbm_search_by_projection_rig", "orbm_search_by_bow_rig", "orbm_search_for_triangulation_rig", "orbm_stereo_fisheye_matches",
@@ -139,6 +139,7 @@ def lib():
     L.orbm_stereo_rowband.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, vp, i32, f32, vp, vp, vp]
     L.orbm_search_by_projection.argtypes = [vp, vp, vp, i32, i32, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp, vp,
                                             vp, vp, i32, vp, vp, vp, i32, f32, i32, vp, vp, vp, vp, vp]
+    L.orbm_compute_image_bounds.argtypes = [i32, i32, f32, f32, f32, f32, vp, i32, vp]
     L.orbm_search_by_projection_static.argtypes = [vp, vp, vp, i32, i32, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp,
                                                    vp, vp, vp, i32, vp, vp, vp, i32, f32, i32, vp, vp, vp, vp]
     L.orbm_search_by_projection_th.argtypes = [vp, vp, vp, i32, i32, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp,

@@ -48,6 +48,29 @@ extern "C" int orbm_undistort_keypoints(const orbx_keypoint* d_kps, const int32_
   return cudaGetLastError() == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
 }
 
+// Frame::ComputeImageBounds (Frame.cc:782-808): the four image corners through cv::undistortPoints, min / max taken
+// the way the reference pairs them (left corners for mnMinX, right corners for mnMaxX, ...).  Host only: four points.
+extern "C" int orbm_compute_image_bounds(int width, int height, float fx, float fy, float cx, float cy,
+                                         const float* dist_coef_host, int n_coef, float* bounds_host) {
+  if (!bounds_host || width < 1 || height < 1 || n_coef < 0 || n_coef > 12 || (n_coef > 0 && !dist_coef_host) ||
+      !(fx != 0.0f) || !(fy != 0.0f))
+    return ORBX_E_INVALID;
+  if (n_coef == 0 || dist_coef_host[0] == 0.0f) {  // :802-808
+    bounds_host[0] = 0.0f; bounds_host[1] = (float)width; bounds_host[2] = 0.0f; bounds_host[3] = (float)height;
+    return ORBX_OK;
+  }
+  double k[12];
+  for (int i = 0; i < 12; i++) k[i] = i < n_coef ? (double)dist_coef_host[i] : 0.0;
+  const float cu[4] = {0.0f, (float)width, 0.0f, (float)width}, cv[4] = {0.0f, 0.0f, (float)height, (float)height};
+  float x[4], y[4];
+  for (int i = 0; i < 4; i++) orbx_undistort_point(cu[i], cv[i], fx, fy, cx, cy, k, &x[i], &y[i]);
+  bounds_host[0] = x[0] < x[2] ? x[0] : x[2];  // mnMinX = min(mat(0,0), mat(2,0))
+  bounds_host[1] = x[1] > x[3] ? x[1] : x[3];  // mnMaxX = max(mat(1,0), mat(3,0))
+  bounds_host[2] = y[0] < y[1] ? y[0] : y[1];  // mnMinY = min(mat(0,1), mat(1,1))
+  bounds_host[3] = y[2] > y[3] ? y[2] : y[3];  // mnMaxY = max(mat(2,1), mat(3,1))
+  return ORBX_OK;
+}
+
 struct FrustumArgs {
   const float *pos, *normal, *min_dist, *max_dist;
   const int32_t* nmp;

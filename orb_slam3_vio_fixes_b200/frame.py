@@ -38,6 +38,17 @@ def UndistortKeyPoints(kps, n, fx, fy, cx, cy, dist_coef, out=None):
     return out
 
 
+def ComputeImageBounds(width, height, fx, fy, cx, cy, dist_coef):
+    """Frame::ComputeImageBounds (Frame.cc:782-808).  Returns (mnMinX, mnMaxX, mnMinY, mnMaxY) as float32 values."""
+    d = np.ascontiguousarray(dist_coef, np.float32)
+    out = np.zeros(4, np.float32)
+    rc = _lib.lib().orbm_compute_image_bounds(int(width), int(height), fx, fy, cx, cy,
+                                              d.ctypes.data_as(C.c_void_p) if d.size else None, d.size,
+                                              out.ctypes.data_as(C.c_void_p))
+    _lib.check(rc, "orbm_compute_image_bounds")
+    return tuple(out)
+
+
 def isInFrustum(pos, normal, min_dist, max_dist, nmp, pose, cam, mbf, bounds, viewing_cos_limit, log_scale_factor,
                 n_levels, fisheye_rig=False, th=None, scale_factors=None):
     """Frame::isInFrustum (fisheye_rig=False) / isInFrustumChecks (True) over a batch of frames.

@@ -70,6 +70,25 @@ def test_harness_undistort_matches_oracle(harness, oracle_mod, dist):
     assert np.array_equal(out[:, 0], ref["x"]) and np.array_equal(out[:, 1], ref["y"])
 
 
+@pytest.mark.parametrize("dist", [D_EUROC, D_K3, D_RATIONAL, D_PRISM, [0.0, 0.1, 0.0, 0.0], []])
+@pytest.mark.parametrize("size", [(752, 480), (1241, 376)])
+def test_compute_image_bounds_is_cv2_on_the_corners(dist, size):
+    """Frame::ComputeImageBounds (Frame.cc:782-808): the host entry point against cv2.undistortPoints on the four
+    corners with the reference's min / max pairing; distortion off -> the image rectangle."""
+    cv2 = pytest.importorskip("cv2")
+    from orb_slam3_vio_fixes_b200 import frame as F
+    w, h = size
+    got = F.ComputeImageBounds(w, h, *K_EUROC, dist)
+    if not dist or dist[0] == 0.0:
+        assert got == (0.0, float(w), 0.0, float(h))
+        return
+    K = np.array([[K_EUROC[0], 0, K_EUROC[2]], [0, K_EUROC[1], K_EUROC[3]], [0, 0, 1]], np.float32)
+    pts = np.array([[0, 0], [w, 0], [0, h], [w, h]], np.float32).reshape(-1, 1, 2)
+    m = cv2.undistortPoints(pts, K, np.array(dist, np.float32), None, K).reshape(4, 2)
+    want = (min(m[0, 0], m[2, 0]), max(m[1, 0], m[3, 0]), min(m[0, 1], m[1, 1]), max(m[2, 1], m[3, 1]))
+    assert tuple(np.float32(v) for v in want) == got
+
+
 def frustum_case(n, seed, model=0):
     """A camera looking down +z of a slightly rotated pose at a cloud of MapPoints around it."""
     rng = np.random.default_rng(seed)
